@@ -1,0 +1,230 @@
+/*
+ * lgk.h -- C ABI of liblgk.so: lesion-gnn message-passing kernels for NVIDIA B200 (sm_100a).
+ *
+ * This is the drop-in boundary for the hot path named by BASELINE.json:north_star.  The reference
+ * (zacharielegault/lesion-gnn) has no FFI of its own: its hot path is the set of PyG / torch-scatter /
+ * torch-sparse / torch-cluster operators that its models call.  Each entry point below
+ * cites the reference call site (file:line under /root/reference) whose operator it replaces.
+ *
+ * Contract
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless the name ends in _host
+ *   - the library never allocates or frees device memory and keeps no global mutable state except a
+ *     thread-local error string; workspaces are caller-provided (sizes from the *_workspace_bytes calls)
+ *   - every call only ENQUEUES work on `stream` (a cudaStream_t passed as void*); it never synchronises
+ *     and never reads device data on the host, so all calls are CUDA-graph-capture safe
+ *   - returns 0 on success, a negative lgk_status on failure; lgk_last_error() describes the failure
+ *   - indices inside the library are int32 (N, E < 2^31); the int64 edge_index / batch tensors of the
+ *     PyG API are converted once by lgk_csr_build / lgk_batch_ptr
+ *   - `dtype`: LGK_F32 (fp32 storage, fp32 math) or LGK_BF16 (bf16 storage, fp32 accumulation)
+ *   - there is no CPU fallback: the functions fail if no sm_100 device kernel image can run
+ */
+#ifndef LGK_H_
+#define LGK_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define LGK_API __attribute__((visibility("default")))
+#else
+#define LGK_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  LGK_OK = 0,
+  LGK_ERR_BAD_ARG = -1,     /* null pointer, negative size, unsupported enum value        */
+  LGK_ERR_UNSUPPORTED = -2, /* shape outside what the kernels are instantiated for        */
+  LGK_ERR_WORKSPACE = -3,   /* workspace too small                                        */
+  LGK_ERR_LAUNCH = -4       /* cudaGetLastError() after the launch reported a failure     */
+} lgk_status;
+
+enum { LGK_F32 = 0, LGK_BF16 = 1 };
+enum { LGK_SUM = 0, LGK_MEAN = 1, LGK_MAX = 2 };
+/* self-loop handling inside an aggregation over a CSR row i:
+ *   LGK_SELF_NONE    use the stored entries as they are                (SAGEConv, GraphConv)
+ *   LGK_SELF_REPLACE skip stored (i,i) entries, add exactly one (i,i)  (GATConv remove+add; GCNConv add_remaining)
+ *   LGK_SELF_ADD     keep stored entries, add one extra (i,i) term     (GINConv's (1+eps) x_i)              */
+enum { LGK_SELF_NONE = 0, LGK_SELF_REPLACE = 1, LGK_SELF_ADD = 2 };
+enum { LGK_ACT_NONE = 0, LGK_ACT_ELU = 1, LGK_ACT_RELU = 2 };
+
+LGK_API const char* lgk_last_error(void);
+LGK_API int lgk_version(void);
+/* number of kernel launches this thread has enqueued through the library since the last reset */
+LGK_API int64_t lgk_launch_count(void);
+LGK_API void lgk_reset_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * (1) CSR / CSC / segment builder
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Replaces torch_sparse.SparseTensor(row=edge_index[1], col=edge_index[0]) built by ToSparseTensor()
+ * (reference src/lesion_gnn/datasets/datamodule.py:45; consumed at models/gat.py:87-88, gin.py:59-60,
+ * drgnet.py:98-99), plus the transpose index the backward pass needs.
+ *   edge_index : int64 [2, E] row-major (row 0 = src j, row 1 = dst i), values in [0, N)
+ *   rowptr[N+1], col[E], perm[E]      CSR by dst, entries ordered by (dst, src, original edge id);
+ *                                     col[p] = src of slot p, perm[p] = original edge id of slot p
+ *   colptr[N+1], row[E], csr2csc[E]   CSC by src, entries ordered by CSR slot; row[q] = dst,
+ *                                     csr2csc[q] = CSR slot of CSC slot q.  Pass NULL x3 to skip.
+ * Result is bit-exact equal to a stable sort on key dst*N+src.                                      */
+LGK_API int64_t lgk_csr_workspace_bytes(int64_t num_nodes, int64_t num_edges);
+LGK_API int lgk_csr_build(const int64_t* edge_index, int64_t num_edges, int64_t num_nodes,
+                  int32_t* rowptr, int32_t* col, int32_t* perm,
+                  int32_t* colptr, int32_t* row, int32_t* csr2csc,
+                  void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Graph segment pointer from the sorted `batch` vector of PyG collation:
+ * ptr[g] = first node of graph g, ptr[B] = N; empty graphs get empty segments.
+ * Replaces the implicit segmentation done by scatter(x, batch) in global_*_pool
+ * (reference models/gat.py:56, gin.py:33, pointnet.py:38).                                          */
+LGK_API int lgk_batch_ptr(const int64_t* batch, int64_t num_nodes, int64_t num_graphs, int32_t* ptr, void* stream);
+
+/* gather rows of a per-edge array into CSR order: out[p] = in[perm[p]] (edge_weight -> SparseTensor value,
+ * reference datamodule.py:45 / drgnet.py:55) */
+LGK_API int lgk_gather_f32(const float* in, const int32_t* index, float* out, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * kNN graph (torch_cluster.knn_graph behind torch_geometric.transforms.KNNGraph;
+ * reference src/lesion_gnn/transforms.py:19-23, configs/config.py:47, datasets/datamodule.py:43-48)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* For every centre i of graph g (nodes ptr[g]..ptr[g+1]): its min(k', n_g) nearest nodes of the same
+ * graph by squared L2 distance, k' = k if loop else k+1 with the centre itself then dropped; ties go
+ * to the lower node index.  Edges are written grouped by centre, ascending distance:
+ *   edge_src[eoff(i) + r] = r-th neighbour, edge_dst[...] = i,  eoff(i) = eptr[g] + (i-ptr[g]) * d_g,
+ *   d_g = min(k', n_g) - (loop ? 0 : 1),  eptr = exclusive scan of n_g * d_g  (lgk_knn_edge_ptr).
+ *   pos : [N, dim] row-major, pos_dtype 0 = float32, 1 = float64 (the reference stores float64,
+ *         datasets/nodes/lesions.py:175); dim <= 8; k <= 64
+ *   edge_index_out : int64 [2, E_total] row-major (row 0 = src, row 1 = dst), E_total = eptr[B]      */
+LGK_API int lgk_knn_edge_ptr(const int32_t* ptr, int64_t num_graphs, int k, int loop, int64_t* eptr, void* stream);
+LGK_API int lgk_knn_graph(const void* pos, int pos_dtype, int dim, const int32_t* ptr, const int64_t* eptr,
+                  int64_t num_graphs, int64_t num_nodes, int k, int loop,
+                  int64_t* edge_index_out, int64_t num_edges_total, void* stream);
+
+/* Gaussian edge weights exp(-d^2 / 2 sigma^2) / sqrt(2 pi sigma^2) (reference src/lesion_gnn/transforms.py:50-58) */
+LGK_API int lgk_gaussian_distance(const void* pos, int pos_dtype, int dim, const int64_t* edge_index, int64_t num_edges,
+                          double sigma, float* edge_weight, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (2)+(4) fused gather + segment-reduce aggregation (SpMM) and its transpose
+ * Replaces MessagePassing.propagate = index_select + [mul] + scatter(sum|mean|max), or
+ * torch_sparse.matmul(adj_t, x, reduce) on the adj_t path, behind GINConv (reference models/gin.py:23,31),
+ * GraphConv (drgnet.py:31,33,55), SAGEConv / GCNConv (BASELINE.json configs 1,3,4; SURVEY.md 8a a-6,a-7).
+ * ------------------------------------------------------------------------------------------------ */
+
+/* out[r, :] = post[r] * REDUCE_{p in ptr[r]..ptr[r+1]} ( w(p) * pre[idx[p]] * x[idx[p], :] )  (+ self term) (+ bias)
+ *   w(p)   = ew ? ew[emap ? emap[p] : p] : 1
+ *   self   = self_mode ? (selfw ? selfw[r] : self_fill) * pre[r] * x[r, :] : none
+ *   reduce = LGK_SUM | LGK_MEAN (divide by max(#entries,1); self_mode must be NONE) | LGK_MAX (no weights;
+ *            empty rows give 0; arg_out[r,f] = slot p of the winning entry or -1, may be NULL)
+ *   pre, post, ew, emap, selfw, bias, arg_out may be NULL.  x, out: [n_rows, F] row-major, `dtype`.
+ * The forward pass calls it with the CSR (rowptr, col); the backward pass (dX = A^T dY) calls it with the
+ * CSC (colptr, row, emap = csr2csc), so both directions are atomic-free and deterministic.            */
+LGK_API int lgk_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* emap, const float* ew,
+             const float* pre, const float* post, const float* selfw, float self_fill, int self_mode,
+             const void* x, const float* bias, void* out, int32_t* arg_out,
+             int64_t n_rows, int64_t feat, int reduce, int dtype, void* stream);
+
+/* backward of the max aggregation: dx[j,f] = sum over CSC entries q of column j with
+ * arg[row[q], f] == csr2csc[q] of dy[row[q], f]                                                        */
+LGK_API int lgk_spmm_max_bwd(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const int32_t* arg,
+                     const void* dy, void* dx, int64_t n_rows, int64_t feat, int dtype, void* stream);
+
+/* gcn_norm (torch_geometric.nn.conv.gcn_conv.gcn_norm): with add_remaining_self_loops
+ * semantics computes deg_i = sum_{non-loop p} w_p + selfw_i and writes dinv[i] = deg_i^-1/2 (0 if deg_i == 0);
+ * selfw_out[i] = weight of the last stored (i,i) entry in original edge order, else fill (NULL if ew == NULL
+ * => all self weights equal `fill`).  add_self_loops == 0: plain weighted in-degree.                     */
+LGK_API int lgk_gcn_norm(const int32_t* rowptr, const int32_t* col, const float* ew /* CSR order */,
+                 float fill, int add_self_loops, float* dinv, float* selfw_out, int64_t num_nodes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * GAT edge-softmax attention (torch_geometric.nn.GATConv; reference models/gat.py:31,51)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* a_src[n,h] = <h[n,h,:], att_src[h,:]>, a_dst likewise.  h: [N, H*C] */
+LGK_API int lgk_gat_alpha(const void* h, const float* att_src, const float* att_dst, float* a_src, float* a_dst,
+                  int64_t num_nodes, int heads, int chan, int dtype, void* stream);
+
+/* out[i,h,:] = sum_{j in N(i)} alpha_ij^h * h[j,h,:] + bias, alpha = softmax_j(leaky_relu(a_src[j,h] + a_dst[i,h]))
+ * with denominator + 1e-16; N(i) = stored non-loop entries + one self loop if add_self_loops (GATConv's
+ * remove_self_loops + add_self_loops), else the stored entries.  Single pass, online softmax.
+ * rowmax/rowsum [N,H]: saved softmax statistics for the backward pass.
+ * dropout_p > 0: attention dropout with a counter-based RNG keyed on (seed, CSR slot, head).           */
+LGK_API int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
+                const float* bias, void* out, float* rowmax, float* rowsum,
+                int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
+                float dropout_p, uint64_t seed, int dtype, void* stream);
+
+/* backward, dst side (CSR): da_dst[i,h] = sum_j dz_ij, and the packed per-(node, head) statistics
+ * stats[i,h] = {a_dst, rowmax, 1/(rowsum + 1e-16), delta} with delta = <dout[i,h,:], out[i,h,:] - bias>
+ * (float [N,H,4], 16-byte aligned) from which the src-side pass recomputes every alpha_ij and dz_ij.        */
+LGK_API int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
+                    const float* rowmax, const float* rowsum, const void* out, const float* bias, const void* dout,
+                    float* stats, float* da_dst,
+                    int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
+                    float dropout_p, uint64_t seed, int dtype, void* stream);
+/* backward, src side (CSC): dh[j,h,:] = sum_i alpha_ij dout[i,h,:] + da_src[j,h] att_src[h,:] + da_dst[j,h] att_dst[h,:],
+ * da_src[j,h] = sum_i dz_ij                                                                             */
+LGK_API int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const void* h,
+                    const float* a_src, const float* a_dst, const float* rowmax, const float* rowsum,
+                    const float* stats, const float* da_dst, const float* att_src, const float* att_dst,
+                    const void* dout, void* dh, float* da_src,
+                    int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
+                    float dropout_p, uint64_t seed, int dtype, void* stream);
+/* datt_src[h,c] = sum_n da_src[n,h] h[n,h,c]; datt_dst likewise (two-stage, deterministic) */
+LGK_API int64_t lgk_gat_datt_workspace_bytes(int64_t num_nodes, int heads, int chan);
+LGK_API int lgk_gat_datt(const void* h, const float* da_src, const float* da_dst, float* datt_src, float* datt_dst,
+                 int64_t num_nodes, int heads, int chan, void* workspace, int64_t workspace_bytes, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (3) global pooling = segment reduce over the sorted batch vector
+ * (torch_geometric.nn.global_mean_pool / global_max_pool / global_add_pool; reference models/gat.py:56,
+ *  gin.py:33, pointnet.py:38)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* out_sum[g,:] = sum (or mean if `mean`) of x[ptr[g]..ptr[g+1], :], out_max[g,:] = max (0 if empty),
+ * arg[g,f] = node index of the max or -1.  Either output may be NULL (fused mean||max when both given). */
+LGK_API int64_t lgk_pool_workspace_bytes(int64_t num_nodes, int64_t num_graphs, int64_t feat);
+LGK_API int lgk_pool_fwd(const void* x, const int32_t* ptr, void* out_sum, int mean, void* out_max, int32_t* arg,
+                 int64_t num_nodes, int64_t num_graphs, int64_t feat,
+                 void* workspace, int64_t workspace_bytes, int dtype, void* stream);
+/* dx[n,:] = dsum[g(n),:] * (mean ? 1/max(cnt_g,1) : 1) + (arg[g(n),f] == n ? dmax[g(n),f] : 0) */
+LGK_API int lgk_pool_bwd(const void* dsum, int mean, const void* dmax, const int32_t* arg, const int32_t* ptr, void* dx,
+                 int64_t num_nodes, int64_t num_graphs, int64_t feat, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (5) node-feature transform (the torch_geometric Linear inside every conv: `lin`, `lin_l`, `lin_r`,
+ *     `lin_rel`, `lin_root`, MLP.lins; reference models/gat.py:29,31,46, gin.py:21,23,25)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* out[n,m] = act( rowscale[n] * sum_k x[n,k] W[m,k] + bias[m] + (accumulate ? out[n,m] : 0) )
+ * fp32: FFMA (TF32 would break the 1e-5 parity bar); rowscale, bias may be NULL.                      */
+LGK_API int lgk_linear_fwd(const void* x, const float* weight, const float* bias, const float* rowscale, void* out,
+                   int64_t n, int64_t k, int64_t m, int act, int accumulate, int dtype, void* stream);
+/* dx[n,k] = sum_m dy[n,m] W[m,k]  (+ dx if accumulate) */
+LGK_API int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, int64_t n, int64_t k, int64_t m,
+                     int accumulate, int dtype, void* stream);
+/* dW[m,k] (+)= sum_n dy[n,m] x[n,k]; db[m] (+)= sum_n dy[n,m] (db may be NULL). Split over n, deterministic. */
+LGK_API int64_t lgk_linear_bwd_w_workspace_bytes(int64_t n, int64_t k, int64_t m);
+LGK_API int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float* db, int64_t n, int64_t k, int64_t m,
+                     int accumulate, void* workspace, int64_t workspace_bytes, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * elementwise helpers of the step (activation after each conv: F.elu at reference models/gat.py:51, gin.py:31,
+ * drgnet.py:55; optimiser: torch.optim.Adam at models/base.py:162-170)
+ * ------------------------------------------------------------------------------------------------ */
+LGK_API int lgk_elu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream);
+LGK_API int lgk_elu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);
+/* fused multi-tensor Adam / AdamW over one flat fp32 buffer; grad is multiplied by grad_scale first
+ * (1/world_size after the data-parallel all-reduce).  The 1-based step count is `step`, or -- so that a
+ * captured CUDA graph can be replayed -- read from the device counter `step_dev` when that is non-NULL.   */
+LGK_API int lgk_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
+                  float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                  const int64_t* step_dev, float grad_scale, int adamw, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LGK_H_ */

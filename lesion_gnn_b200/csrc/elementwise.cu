@@ -1,0 +1,130 @@
+// Elementwise pieces of the training step: ELU (F.elu after every conv, reference models/gat.py:51, gin.py:31,
+// drgnet.py:55), the fused multi-tensor Adam/AdamW step over one flat buffer (torch.optim.Adam at
+// models/base.py:162-170), and the library-global error / launch bookkeeping.
+#include "common.cuh"
+
+namespace lgk {
+
+static thread_local char g_error[512] = "";
+static thread_local int64_t g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches += n; }
+
+namespace {
+
+template <typename T>
+__global__ void __launch_bounds__(256) elu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t n4, int64_t n) {
+  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t < n4) {
+    float4 v = Vec4<T>::stream(x, t * 4);
+    v.x = elu1(v.x); v.y = elu1(v.y); v.z = elu1(v.z); v.w = elu1(v.w);
+    Vec4<T>::store(y, t * 4, v);
+  } else if (t == n4) {
+    for (int64_t i = n4 * 4; i < n; ++i) Vec4<T>::store1(y, i, elu1(Vec4<T>::load1(x, i)));
+  }
+}
+// dx = dy * (y > 0 ? 1 : y + 1)   (alpha = 1: elu'(x) = exp(x) = y + 1 on the negative side)
+template <typename T>
+__global__ void __launch_bounds__(256) elu_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
+                                                      int64_t n4, int64_t n) {
+  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t < n4) {
+    const float4 yv = Vec4<T>::stream(y, t * 4), g = Vec4<T>::stream(dy, t * 4);
+    float4 r;
+    r.x = g.x * (yv.x > 0.f ? 1.f : yv.x + 1.f);
+    r.y = g.y * (yv.y > 0.f ? 1.f : yv.y + 1.f);
+    r.z = g.z * (yv.z > 0.f ? 1.f : yv.z + 1.f);
+    r.w = g.w * (yv.w > 0.f ? 1.f : yv.w + 1.f);
+    Vec4<T>::store(dx, t * 4, r);
+  } else if (t == n4) {
+    for (int64_t i = n4 * 4; i < n; ++i) {
+      const float yv = Vec4<T>::load1(y, i);
+      Vec4<T>::store1(dx, i, Vec4<T>::load1(dy, i) * (yv > 0.f ? 1.f : yv + 1.f));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                   float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
+                                                   float wd, float bc1, float bc2_sqrt, const int64_t* __restrict__ step_dev,
+                                                   float gscale, int adamw) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (step_dev) {  // graph-replay mode: bias corrections from the device-resident step counter
+    const double t = double(*step_dev);
+    bc1 = float(1.0 - pow(double(b1), t));
+    bc2_sqrt = float(sqrt(1.0 - pow(double(b2), t)));
+  }
+  float param = p[i];
+  float grad = g[i] * gscale;
+  if (adamw) param *= 1.f - lr * wd;        // decoupled decay (torch.optim.AdamW)
+  else grad = fmaf(wd, param, grad);        // L2 penalty folded into the gradient (torch.optim.Adam)
+  const float mi = fmaf(b1, m[i], (1.f - b1) * grad);
+  const float vi = fmaf(b2, v[i], (1.f - b2) * grad * grad);
+  m[i] = mi;
+  v[i] = vi;
+  const float denom = sqrtf(vi) / bc2_sqrt + eps;
+  p[i] = param - (lr / bc1) * (mi / denom);
+}
+
+}  // namespace
+}  // namespace lgk
+
+using namespace lgk;
+
+extern "C" const char* lgk_last_error(void) { return g_error; }
+extern "C" int lgk_version(void) { return 100; }
+extern "C" int64_t lgk_launch_count(void) { return g_launches; }
+extern "C" void lgk_reset_launch_count(void) { g_launches = 0; }
+
+static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int lgk_elu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0, LGK_ERR_BAD_ARG, "lgk_elu_fwd: negative size");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(x && y, LGK_ERR_BAD_ARG, "lgk_elu_fwd: null pointer");
+  const int64_t n4 = (al16(x) && al16(y)) ? n / 4 : 0;
+  const unsigned grid = unsigned(ceil_div(n4 + 1, 256));
+  if (dtype == LGK_F32) elu_fwd_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(x), static_cast<float*>(y), n4, n);
+  else if (dtype == LGK_BF16) elu_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), n4, n);
+  else LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_elu_fwd: bad dtype");
+  LGK_CHECK_LAUNCH("elu_fwd_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_elu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0, LGK_ERR_BAD_ARG, "lgk_elu_bwd: negative size");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(y && dy && dx, LGK_ERR_BAD_ARG, "lgk_elu_bwd: null pointer");
+  const int64_t n4 = (al16(y) && al16(dy) && al16(dx)) ? n / 4 : 0;
+  const unsigned grid = unsigned(ceil_div(n4 + 1, 256));
+  if (dtype == LGK_F32) elu_bwd_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(y), static_cast<const float*>(dy), static_cast<float*>(dx), n4, n);
+  else if (dtype == LGK_BF16) elu_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), n4, n);
+  else LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_elu_bwd: bad dtype");
+  LGK_CHECK_LAUNCH("elu_bwd_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                             float beta1, float beta2, float eps, float weight_decay, int64_t step, const int64_t* step_dev,
+                             float grad_scale, int adamw, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && (step >= 1 || step_dev), LGK_ERR_BAD_ARG, "lgk_adam_step: bad size or step");
+  if (step < 1) step = 1;
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(param && grad && exp_avg && exp_avg_sq, LGK_ERR_BAD_ARG, "lgk_adam_step: null pointer");
+  const double bc1 = 1.0 - pow(double(beta1), double(step));
+  const double bc2 = 1.0 - pow(double(beta2), double(step));
+  adam_kernel<<<unsigned(ceil_div(n, 256)), 256, 0, stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
+                                                              weight_decay, float(bc1), float(sqrt(bc2)), step_dev, grad_scale, adamw);
+  LGK_CHECK_LAUNCH("adam_kernel");
+  return LGK_OK;
+}

@@ -1,0 +1,546 @@
+// GAT edge-softmax attention, forward and backward (torch_geometric.nn.GATConv; reference models/gat.py:31,51).
+//
+// PyG runs ~15 ATen kernels per layer and materialises [E,H] logits three times and the [E,H,C] messages once.
+// Here one kernel does leaky_relu + per-destination softmax + weighted aggregation in a single pass over the
+// CSR with an online (running max / running sum) softmax, and the backward is two atomic-free passes: one over
+// the CSR (destination side) and one over the CSC (source side) that recompute the attention coefficients
+// from 4 per-(node, head) statistics instead of storing anything per edge.
+//
+// Mapping: one group of LPR lanes per (node, head); a lane owns 4 channels (VPL vectors if C > 128).  Adjacent
+// groups of a warp are adjacent heads of the same node, so a warp still reads whole contiguous feature rows.
+#include "common.cuh"
+#include <math.h>
+
+namespace lgk {
+namespace {
+
+constexpr int kThreads = 256;
+
+struct GatArgs {
+  const int* ptr;      // rowptr (dst side) or colptr (src side)
+  const int* idx;      // col or row
+  const int* slotmap;  // csr2csc on the src side (dropout key), null on the dst side
+  const float* a_src;
+  const float* a_dst;
+  const float* bias;
+  float* rowmax;
+  float* rowsum;
+  float4* stats;       // [N,H] {a_dst, rowmax, 1/(rowsum+1e-16), delta}
+  const float* da_dst;
+  float* da_out;       // da_dst (dst pass) or da_src (src pass)
+  const float* att_src;
+  const float* att_dst;
+  int64_t n_nodes;
+  int heads;
+  int chan;
+  float slope;
+  int add_self;
+  float drop_p;
+  float drop_scale;
+  uint64_t seed;
+};
+
+template <int LPR>
+__device__ __forceinline__ unsigned gmask() {
+  if constexpr (LPR == 32) {
+    return 0xffffffffu;
+  } else {
+    unsigned lane = threadIdx.x & 31;
+    return ((1u << LPR) - 1u) << (lane & ~(LPR - 1));
+  }
+}
+template <int LPR>
+__device__ __forceinline__ float group_sum(float v, unsigned mask) {
+#pragma unroll
+  for (int o = LPR >> 1; o >= 1; o >>= 1) v += __shfl_xor_sync(mask, v, o, LPR);
+  return v;
+}
+template <int LPR>
+__device__ __forceinline__ float group_max(float v, unsigned mask) {
+#pragma unroll
+  for (int o = LPR >> 1; o >= 1; o >>= 1) v = fmaxf(v, __shfl_xor_sync(mask, v, o, LPR));
+  return v;
+}
+__device__ __forceinline__ float lrelu(float z, float slope) { return z > 0.f ? z : slope * z; }
+__device__ __forceinline__ float keep_scale(const GatArgs& a, uint32_t slot, int head) {
+  // attention dropout: 0 (dropped) or 1/(1-p) (kept); identical in forward and both backward passes
+  if (a.drop_p <= 0.f) return 1.f;
+  return uniform_hash(a.seed, slot, uint32_t(head)) < a.drop_p ? 0.f : a.drop_scale;
+}
+constexpr uint32_t kSelfSlotBit = 0x80000000u;
+
+// ---- alpha = <h, att> ------------------------------------------------------------------------------------
+template <typename T, int LPR, int VPL>
+__global__ void __launch_bounds__(kThreads) gat_alpha_kernel(const T* __restrict__ h, const float* __restrict__ att_src,
+                                                             const float* __restrict__ att_dst, float* __restrict__ a_src,
+                                                             float* __restrict__ a_dst, int64_t n_items, int H, int C) {
+  constexpr int GPW = 32 / LPR;
+  const int gl = threadIdx.x & (LPR - 1);
+  const int64_t item = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * GPW + ((threadIdx.x & 31) / LPR);
+  if (item >= n_items) return;
+  const unsigned mask = gmask<LPR>();
+  const int head = int(item % H);
+  const int C4 = C >> 2;
+  float ps = 0.f, pd = 0.f;
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) {
+    const int vec = gl + v * LPR;
+    if (vec < C4) {
+      float4 hv = Vec4<T>::stream(h + item * C, vec * 4);
+      float4 as = __ldg(reinterpret_cast<const float4*>(att_src + head * C) + vec);
+      float4 ad = __ldg(reinterpret_cast<const float4*>(att_dst + head * C) + vec);
+      ps += f4_dot(hv, as);
+      pd += f4_dot(hv, ad);
+    }
+  }
+  ps = group_sum<LPR>(ps, mask);
+  pd = group_sum<LPR>(pd, mask);
+  if (gl == 0) { a_src[item] = ps; a_dst[item] = pd; }
+}
+
+// ---- forward -----------------------------------------------------------------------------------------------
+template <typename T, int LPR, int VPL>
+__global__ void __launch_bounds__(kThreads) gat_fwd_kernel(GatArgs a, const T* __restrict__ h, T* __restrict__ out) {
+  constexpr int GPW = 32 / LPR;
+  const int gl = threadIdx.x & (LPR - 1);
+  const int H = a.heads, C = a.chan, C4 = C >> 2;
+  const int64_t item = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * GPW + ((threadIdx.x & 31) / LPR);
+  if (item >= a.n_nodes * H) return;
+  const unsigned mask = gmask<LPR>();
+  const int i = int(item / H), head = int(item - int64_t(i) * H);
+  const int64_t F = int64_t(H) * C;
+  const int start = a.ptr[i], end = a.ptr[i + 1];
+  const float ad = __ldg(a.a_dst + item);
+
+  float m = -INFINITY, s = 0.f;
+  float4 acc[VPL];
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) acc[v] = f4_zero();
+
+  if (a.add_self) {  // GATConv: remove_self_loops + add_self_loops => exactly one (i,i) entry
+    m = lrelu(__ldg(a.a_src + item) + ad, a.slope);
+    s = 1.f;
+    const float ks = keep_scale(a, kSelfSlotBit | uint32_t(i), head);
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int vec = gl + v * LPR;
+      if (vec < C4) f4_fma(acc[v], ks, Vec4<T>::gather(h + int64_t(i) * F + head * C, vec * 4));
+    }
+  }
+
+  for (int base = start; base < end; base += LPR) {
+    const int p = base + gl;
+    int my_j = i;
+    float my_e = -INFINITY;
+    if (p < end) {
+      const int j = ld_stream_i32(a.idx + p);
+      if (!(a.add_self && j == i)) {
+        my_j = j;
+        my_e = lrelu(__ldg(a.a_src + int64_t(j) * H + head) + ad, a.slope);
+      }
+    }
+    const float cm = group_max<LPR>(my_e, mask);
+    if (cm == -INFINITY) continue;  // every entry of the chunk was a dropped stored loop
+    const float m_new = fmaxf(m, cm);
+    const float rescale = expf(m - m_new);  // m = -inf on the first chunk -> 0
+    float my_p = expf(my_e - m_new);        // my_e = -inf -> 0
+    s = s * rescale + group_sum<LPR>(my_p, mask);
+    if (a.drop_p > 0.f && p < end) my_p *= keep_scale(a, uint32_t(p), head);
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) { acc[v].x *= rescale; acc[v].y *= rescale; acc[v].z *= rescale; acc[v].w *= rescale; }
+    m = m_new;
+    const int cnt = min(LPR, end - base);
+#pragma unroll 4
+    for (int u = 0; u < cnt; ++u) {
+      const int j = __shfl_sync(mask, my_j, u, LPR);
+      const float pu = __shfl_sync(mask, my_p, u, LPR);
+      const T* hr = h + int64_t(j) * F + head * C;
+#pragma unroll
+      for (int v = 0; v < VPL; ++v) {
+        const int vec = gl + v * LPR;
+        if (vec < C4) f4_fma(acc[v], pu, Vec4<T>::gather(hr, vec * 4));
+      }
+    }
+  }
+
+  const float inv = 1.f / (s + 1e-16f);
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) {
+    const int vec = gl + v * LPR;
+    if (vec < C4) {
+      float4 r = acc[v];
+      r.x *= inv; r.y *= inv; r.z *= inv; r.w *= inv;
+      if (a.bias) {
+        float4 b = __ldg(reinterpret_cast<const float4*>(a.bias + head * C) + vec);
+        r.x += b.x; r.y += b.y; r.z += b.z; r.w += b.w;
+      }
+      Vec4<T>::store(out + int64_t(i) * F + head * C, vec * 4, r);
+    }
+  }
+  if (gl == 0) {
+    if (a.rowmax) a.rowmax[item] = m;
+    if (a.rowsum) a.rowsum[item] = s;
+  }
+}
+
+// ---- backward, destination side (CSR) -----------------------------------------------------------------------
+// delta[i,h] = <dout, out - bias>;  da_dst[i,h] = sum_j dz_ij;  stats[i,h] = {a_dst, m, 1/(s+eps), delta}
+template <typename T, int LPR, int VPL>
+__global__ void __launch_bounds__(kThreads) gat_bwd_dst_kernel(GatArgs a, const T* __restrict__ h, const T* __restrict__ out,
+                                                               const T* __restrict__ dout) {
+  constexpr int GPW = 32 / LPR;
+  const int gl = threadIdx.x & (LPR - 1);
+  const int H = a.heads, C = a.chan, C4 = C >> 2;
+  const int64_t item = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * GPW + ((threadIdx.x & 31) / LPR);
+  if (item >= a.n_nodes * H) return;
+  const unsigned mask = gmask<LPR>();
+  const int i = int(item / H), head = int(item - int64_t(i) * H);
+  const int64_t F = int64_t(H) * C;
+  const int start = a.ptr[i], end = a.ptr[i + 1];
+  const float ad = __ldg(a.a_dst + item);
+  const float m = __ldg(a.rowmax + item);
+  const float inv = 1.f / (__ldg(a.rowsum + item) + 1e-16f);
+
+  float4 dO[VPL];
+  float part = 0.f;
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) {
+    const int vec = gl + v * LPR;
+    dO[v] = f4_zero();
+    if (vec < C4) {
+      dO[v] = Vec4<T>::stream(dout + int64_t(i) * F + head * C, vec * 4);
+      float4 o = Vec4<T>::stream(out + int64_t(i) * F + head * C, vec * 4);
+      if (a.bias) {
+        float4 b = __ldg(reinterpret_cast<const float4*>(a.bias + head * C) + vec);
+        o.x -= b.x; o.y -= b.y; o.z -= b.z; o.w -= b.w;
+      }
+      part += f4_dot(dO[v], o);
+    }
+  }
+  const float delta = group_sum<LPR>(part, mask);
+  float da = 0.f;
+
+  auto edge = [&](int j, uint32_t slot) {
+    float dotp = 0.f;
+    const T* hr = h + int64_t(j) * F + head * C;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int vec = gl + v * LPR;
+      if (vec < C4) dotp += f4_dot(dO[v], Vec4<T>::gather(hr, vec * 4));
+    }
+    dotp = group_sum<LPR>(dotp, mask);
+    const float z = __ldg(a.a_src + int64_t(j) * H + head) + ad;
+    const float alpha = expf(lrelu(z, a.slope) - m) * inv;
+    const float dalpha = keep_scale(a, slot, head) * dotp;
+    da += alpha * (dalpha - delta) * (z > 0.f ? 1.f : a.slope);
+  };
+
+  if (a.add_self) edge(i, kSelfSlotBit | uint32_t(i));
+  for (int base = start; base < end; base += LPR) {
+    const int p = base + gl;
+    int my_j = -1;
+    if (p < end) {
+      const int j = ld_stream_i32(a.idx + p);
+      if (!(a.add_self && j == i)) my_j = j;
+    }
+    const int cnt = min(LPR, end - base);
+    for (int u = 0; u < cnt; ++u) {
+      const int j = __shfl_sync(mask, my_j, u, LPR);
+      if (j >= 0) edge(j, uint32_t(base + u));  // uniform across the group
+    }
+  }
+  if (gl == 0) {
+    a.da_out[item] = da;
+    a.stats[item] = make_float4(ad, m, inv, delta);
+  }
+}
+
+// ---- backward, source side (CSC) ------------------------------------------------------------------------------
+// dh[j,h,:] = sum_i alpha_ij keep_ij dout[i,h,:] + da_src att_src + da_dst att_dst;  da_src[j,h] = sum_i dz_ij
+template <typename T, int LPR, int VPL>
+__global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const T* __restrict__ h, const T* __restrict__ dout,
+                                                               T* __restrict__ dh) {
+  constexpr int GPW = 32 / LPR;
+  const int gl = threadIdx.x & (LPR - 1);
+  const int H = a.heads, C = a.chan, C4 = C >> 2;
+  const int64_t item = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * GPW + ((threadIdx.x & 31) / LPR);
+  if (item >= a.n_nodes * H) return;
+  const unsigned mask = gmask<LPR>();
+  const int j = int(item / H), head = int(item - int64_t(j) * H);
+  const int64_t F = int64_t(H) * C;
+  const int start = a.ptr[j], end = a.ptr[j + 1];
+  const float as = __ldg(a.a_src + item);
+
+  float4 hj[VPL], acc[VPL];
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) {
+    const int vec = gl + v * LPR;
+    hj[v] = f4_zero();
+    acc[v] = f4_zero();
+    if (vec < C4) hj[v] = Vec4<T>::stream(h + int64_t(j) * F + head * C, vec * 4);
+  }
+  float da = 0.f;
+
+  auto edge = [&](int i, uint32_t slot) {
+    const float4 st = __ldg(a.stats + int64_t(i) * H + head);  // {a_dst, m, inv, delta}, same address for the group
+    float4 dO[VPL];
+    float dotp = 0.f;
+    const T* dr = dout + int64_t(i) * F + head * C;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int vec = gl + v * LPR;
+      dO[v] = f4_zero();
+      if (vec < C4) {
+        dO[v] = Vec4<T>::gather(dr, vec * 4);
+        dotp += f4_dot(dO[v], hj[v]);
+      }
+    }
+    dotp = group_sum<LPR>(dotp, mask);
+    const float z = as + st.x;
+    const float alpha = expf(lrelu(z, a.slope) - st.y) * st.z;
+    const float ks = keep_scale(a, slot, head);
+    da += alpha * (ks * dotp - st.w) * (z > 0.f ? 1.f : a.slope);
+    const float w = alpha * ks;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) f4_fma(acc[v], w, dO[v]);
+  };
+
+  if (a.add_self) edge(j, kSelfSlotBit | uint32_t(j));
+  for (int base = start; base < end; base += LPR) {
+    const int q = base + gl;
+    int my_i = -1, my_slot = 0;
+    if (q < end) {
+      const int i = ld_stream_i32(a.idx + q);
+      if (!(a.add_self && i == j)) {
+        my_i = i;
+        if (a.drop_p > 0.f) my_slot = ld_stream_i32(a.slotmap + q);
+      }
+    }
+    const int cnt = min(LPR, end - base);
+    for (int u = 0; u < cnt; ++u) {
+      const int i = __shfl_sync(mask, my_i, u, LPR);
+      const int slot = __shfl_sync(mask, my_slot, u, LPR);
+      if (i >= 0) edge(i, uint32_t(slot));
+    }
+  }
+
+  const float dad = __ldg(a.da_dst + item);
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) {
+    const int vec = gl + v * LPR;
+    if (vec < C4) {
+      float4 r = acc[v];
+      f4_fma(r, da, __ldg(reinterpret_cast<const float4*>(a.att_src + head * C) + vec));
+      f4_fma(r, dad, __ldg(reinterpret_cast<const float4*>(a.att_dst + head * C) + vec));
+      Vec4<T>::store(dh + int64_t(j) * F + head * C, vec * 4, r);
+    }
+  }
+  if (gl == 0) a.da_out[item] = da;
+}
+
+// ---- datt = sum_n da[n,h] * h[n,h,c]: slab partials, then a deterministic second stage --------------------------
+constexpr int kDattRowsPerCta = 256;
+template <typename T>
+__global__ void __launch_bounds__(256) gat_datt_partial_kernel(const T* __restrict__ h, const float* __restrict__ da_src,
+                                                               const float* __restrict__ da_dst, float* __restrict__ partial,
+                                                               int64_t N, int H, int C) {
+  __shared__ float s_a[8][32], s_b[8][32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int F = H * C;
+  const int f = blockIdx.y * 32 + tx;
+  const int64_t r0 = int64_t(blockIdx.x) * kDattRowsPerCta;
+  const int64_t r1 = min(N, r0 + kDattRowsPerCta);
+  float sa = 0.f, sb = 0.f;
+  if (f < F) {
+    const int head = f / C;
+    for (int64_t n = r0 + ty; n < r1; n += 8) {
+      const float hv = Vec4<T>::load1(h + n * F, f);
+      sa = fmaf(__ldg(da_src + n * H + head), hv, sa);
+      sb = fmaf(__ldg(da_dst + n * H + head), hv, sb);
+    }
+  }
+  s_a[ty][tx] = sa;
+  s_b[ty][tx] = sb;
+  __syncthreads();
+  if (ty == 0 && f < F) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) { sa += s_a[k][tx]; sb += s_b[k][tx]; }
+    partial[(int64_t(blockIdx.x) * 2 + 0) * F + f] = sa;
+    partial[(int64_t(blockIdx.x) * 2 + 1) * F + f] = sb;
+  }
+}
+__global__ void __launch_bounds__(256) gat_datt_final_kernel(const float* __restrict__ partial, float* __restrict__ datt_src,
+                                                             float* __restrict__ datt_dst, int64_t nslabs, int F) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  float sa = 0.f, sb = 0.f;
+  for (int64_t s = 0; s < nslabs; ++s) {
+    sa += partial[(s * 2 + 0) * F + f];
+    sb += partial[(s * 2 + 1) * F + f];
+  }
+  datt_src[f] = sa;
+  datt_dst[f] = sb;
+}
+
+int check_shape(const char* who, int64_t N, int H, int C) {
+  LGK_REQUIRE(N >= 0 && H > 0 && C > 0, LGK_ERR_BAD_ARG, "%s: bad sizes", who);
+  LGK_REQUIRE(C % 4 == 0 && C <= 1024, LGK_ERR_UNSUPPORTED, "%s: channels per head must be a multiple of 4 and <= 1024 (got %d)", who, C);
+  LGK_REQUIRE(N * H < (int64_t(1) << 31), LGK_ERR_UNSUPPORTED, "%s: N*H out of range", who);
+  return LGK_OK;
+}
+
+// pick (LPR, VPL) from C/4 and launch KERNEL<T, LPR, VPL>
+#define LGK_GAT_DISPATCH(KERNEL, T, n_items, C, stream, ...)                                         \
+  do {                                                                                              \
+    const int c4__ = (C) / 4;                                                                       \
+    const int warps__ = kThreads / 32;                                                              \
+    auto grid__ = [&](int lpr) { return unsigned(ceil_div((n_items), int64_t(warps__) * (32 / lpr))); }; \
+    if (c4__ <= 1) KERNEL<T, 1, 1><<<grid__(1), kThreads, 0, stream>>>(__VA_ARGS__);                \
+    else if (c4__ <= 2) KERNEL<T, 2, 1><<<grid__(2), kThreads, 0, stream>>>(__VA_ARGS__);           \
+    else if (c4__ <= 4) KERNEL<T, 4, 1><<<grid__(4), kThreads, 0, stream>>>(__VA_ARGS__);           \
+    else if (c4__ <= 8) KERNEL<T, 8, 1><<<grid__(8), kThreads, 0, stream>>>(__VA_ARGS__);           \
+    else if (c4__ <= 16) KERNEL<T, 16, 1><<<grid__(16), kThreads, 0, stream>>>(__VA_ARGS__);        \
+    else if (c4__ <= 32) KERNEL<T, 32, 1><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);        \
+    else if (c4__ <= 64) KERNEL<T, 32, 2><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);        \
+    else if (c4__ <= 128) KERNEL<T, 32, 4><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);       \
+    else KERNEL<T, 32, 8><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);                        \
+  } while (0)
+
+GatArgs base_args(int64_t N, int H, int C, float slope, int add_self, float drop_p, uint64_t seed) {
+  GatArgs a{};
+  a.n_nodes = N; a.heads = H; a.chan = C; a.slope = slope; a.add_self = add_self;
+  a.drop_p = drop_p; a.drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f; a.seed = seed;
+  return a;
+}
+
+}  // namespace
+}  // namespace lgk
+
+using namespace lgk;
+
+extern "C" int lgk_gat_alpha(const void* h, const float* att_src, const float* att_dst, float* a_src, float* a_dst,
+                             int64_t N, int H, int C, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_shape("lgk_gat_alpha", N, H, C)) return rc;
+  if (N == 0) return LGK_OK;
+  LGK_REQUIRE(h && att_src && att_dst && a_src && a_dst, LGK_ERR_BAD_ARG, "lgk_gat_alpha: null pointer");
+  const int64_t items = N * H;
+  if (dtype == LGK_F32)
+    LGK_GAT_DISPATCH(gat_alpha_kernel, float, items, C, stream, static_cast<const float*>(h), att_src, att_dst, a_src, a_dst, items, H, C);
+  else if (dtype == LGK_BF16)
+    LGK_GAT_DISPATCH(gat_alpha_kernel, __nv_bfloat16, items, C, stream, static_cast<const __nv_bfloat16*>(h), att_src, att_dst, a_src, a_dst, items, H, C);
+  else
+    LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_alpha: bad dtype");
+  LGK_CHECK_LAUNCH("gat_alpha_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
+                           const float* bias, void* out, float* rowmax, float* rowsum, int64_t N, int H, int C,
+                           float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                           void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_shape("lgk_gat_fwd", N, H, C)) return rc;
+  if (N == 0) return LGK_OK;
+  LGK_REQUIRE(rowptr && h && a_src && a_dst && out, LGK_ERR_BAD_ARG, "lgk_gat_fwd: null pointer");
+  LGK_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_gat_fwd: dropout must be in [0,1)");
+  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
+  a.ptr = rowptr; a.idx = col; a.a_src = a_src; a.a_dst = a_dst; a.bias = bias; a.rowmax = rowmax; a.rowsum = rowsum;
+  const int64_t items = N * H;
+  if (dtype == LGK_F32)
+    LGK_GAT_DISPATCH(gat_fwd_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<float*>(out));
+  else if (dtype == LGK_BF16)
+    LGK_GAT_DISPATCH(gat_fwd_kernel, __nv_bfloat16, items, C, stream, a, static_cast<const __nv_bfloat16*>(h), static_cast<__nv_bfloat16*>(out));
+  else
+    LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_fwd: bad dtype");
+  LGK_CHECK_LAUNCH("gat_fwd_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
+                               const float* a_dst, const float* rowmax, const float* rowsum, const void* out,
+                               const float* bias, const void* dout, float* delta, float* da_dst, int64_t N, int H, int C,
+                               float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                               void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_shape("lgk_gat_bwd_dst", N, H, C)) return rc;
+  if (N == 0) return LGK_OK;
+  LGK_REQUIRE(rowptr && h && a_src && a_dst && rowmax && rowsum && out && dout && delta && da_dst, LGK_ERR_BAD_ARG,
+              "lgk_gat_bwd_dst: null pointer");
+  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
+  a.ptr = rowptr; a.idx = col; a.a_src = a_src; a.a_dst = a_dst; a.bias = bias;
+  a.rowmax = const_cast<float*>(rowmax); a.rowsum = const_cast<float*>(rowsum);
+  a.stats = reinterpret_cast<float4*>(delta); a.da_out = da_dst;
+  const int64_t items = N * H;
+  if (dtype == LGK_F32)
+    LGK_GAT_DISPATCH(gat_bwd_dst_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<const float*>(out), static_cast<const float*>(dout));
+  else if (dtype == LGK_BF16)
+    LGK_GAT_DISPATCH(gat_bwd_dst_kernel, __nv_bfloat16, items, C, stream, a, static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout));
+  else
+    LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_bwd_dst: bad dtype");
+  LGK_CHECK_LAUNCH("gat_bwd_dst_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const void* h,
+                               const float* a_src, const float* a_dst, const float* rowmax, const float* rowsum,
+                               const float* delta, const float* da_dst, const float* att_src, const float* att_dst,
+                               const void* dout, void* dh, float* da_src, int64_t N, int H, int C, float negative_slope,
+                               int add_self_loops, float dropout_p, uint64_t seed, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  (void)a_dst; (void)rowmax; (void)rowsum;  // carried inside the packed statistics written by lgk_gat_bwd_dst
+  if (int rc = check_shape("lgk_gat_bwd_src", N, H, C)) return rc;
+  if (N == 0) return LGK_OK;
+  LGK_REQUIRE(colptr && h && a_src && delta && da_dst && att_src && att_dst && dout && dh && da_src, LGK_ERR_BAD_ARG,
+              "lgk_gat_bwd_src: null pointer");
+  LGK_REQUIRE(dropout_p <= 0.f || csr2csc, LGK_ERR_BAD_ARG, "lgk_gat_bwd_src: dropout needs csr2csc");
+  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
+  a.ptr = colptr; a.idx = row; a.slotmap = csr2csc; a.a_src = a_src;
+  a.stats = reinterpret_cast<float4*>(const_cast<float*>(delta)); a.da_dst = da_dst; a.da_out = da_src;
+  a.att_src = att_src; a.att_dst = att_dst;
+  const int64_t items = N * H;
+  if (dtype == LGK_F32)
+    LGK_GAT_DISPATCH(gat_bwd_src_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<const float*>(dout), static_cast<float*>(dh));
+  else if (dtype == LGK_BF16)
+    LGK_GAT_DISPATCH(gat_bwd_src_kernel, __nv_bfloat16, items, C, stream, a, static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(dout), static_cast<__nv_bfloat16*>(dh));
+  else
+    LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_bwd_src: bad dtype");
+  LGK_CHECK_LAUNCH("gat_bwd_src_kernel");
+  return LGK_OK;
+}
+
+extern "C" int64_t lgk_gat_datt_workspace_bytes(int64_t N, int H, int C) {
+  if (N <= 0 || H <= 0 || C <= 0) return 0;
+  return ceil_div(N, kDattRowsPerCta) * 2 * H * C * 4;
+}
+
+extern "C" int lgk_gat_datt(const void* h, const float* da_src, const float* da_dst, float* datt_src, float* datt_dst,
+                            int64_t N, int H, int C, void* workspace, int64_t workspace_bytes, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(N >= 0 && H > 0 && C > 0, LGK_ERR_BAD_ARG, "lgk_gat_datt: bad sizes");
+  LGK_REQUIRE(datt_src && datt_dst, LGK_ERR_BAD_ARG, "lgk_gat_datt: null pointer");
+  const int F = H * C;
+  if (N == 0) {
+    cudaMemsetAsync(datt_src, 0, 4 * F, stream);
+    cudaMemsetAsync(datt_dst, 0, 4 * F, stream);
+    LGK_CHECK_LAUNCH("lgk_gat_datt(memset)");
+    return LGK_OK;
+  }
+  LGK_REQUIRE(h && da_src && da_dst, LGK_ERR_BAD_ARG, "lgk_gat_datt: null pointer");
+  const int64_t nslabs = ceil_div(N, kDattRowsPerCta);
+  const int64_t need = nslabs * 2 * F * 4;
+  LGK_REQUIRE(workspace && workspace_bytes >= need, LGK_ERR_WORKSPACE, "lgk_gat_datt: workspace %lld < %lld bytes",
+              (long long)workspace_bytes, (long long)need);
+  float* partial = static_cast<float*>(workspace);
+  dim3 grid(unsigned(nslabs), unsigned(ceil_div(F, 32)));
+  if (dtype == LGK_F32)
+    gat_datt_partial_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(h), da_src, da_dst, partial, N, H, C);
+  else if (dtype == LGK_BF16)
+    gat_datt_partial_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(h), da_src, da_dst, partial, N, H, C);
+  else
+    LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_datt: bad dtype");
+  LGK_CHECK_LAUNCH("gat_datt_partial_kernel");
+  gat_datt_final_kernel<<<unsigned(ceil_div(F, 256)), 256, 0, stream>>>(partial, datt_src, datt_dst, nslabs, F);
+  LGK_CHECK_LAUNCH("gat_datt_final_kernel");
+  return LGK_OK;
+}

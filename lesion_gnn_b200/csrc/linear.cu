@@ -1,0 +1,326 @@
+// (5) node-feature transform X W^T and its two backward products, fp32 FFMA.
+//
+// Every Linear inside the PyG convs (`lin`, `lin_l`, `lin_r`, `lin_rel`, `lin_root`, MLP.lins) and the
+// reference's in_proj/out_proj (models/gat.py:29,46, gin.py:21,25) is a tall-skinny product: N = 10^4..10^6 rows
+// against 16..1025 columns.  Arithmetic intensity is 6..57 flop/B, far below the tensor-core
+// ridge, and the fp32 parity bar (1e-5) rules out single-pass TF32, so this path is plain FFMA with the
+// epilogues the layers need fused in (row scale for GCN's D^-1/2, bias, ELU, accumulate for the
+// root-weight term W_r x_i of SAGEConv / GraphConv).
+//
+// One kernel template covers the three products as C[i,j] = sum_r A(i,r) B(j,r):
+//   forward   C = out [N,M]   A = x  (r contiguous)   B = W  (r contiguous)      R = K
+//   grad x    C = dx  [N,K]   A = dy (r contiguous)   B = W  (j contiguous)      R = M
+//   grad W    C = dW^T[K,M]   A = x  (i contiguous)   B = dy (j contiguous)      R = N, split over CTAs
+// 128 x 64 output tile, 16-deep r tile, 256 threads, 8 x 4 micro-tile, register-prefetch double buffering.
+#include "common.cuh"
+
+namespace lgk {
+namespace {
+
+constexpr int BI = 128, BJ = 64, BR = 16, PAD = 4, kThreads = 256;
+constexpr int TI = 8, TJ = 4;
+
+struct GemmArgs {
+  const float* A;
+  const float* B;
+  float* C;
+  int64_t I, J, R;
+  int64_t lda, ldb;   // stride of the non-contiguous index of A / B
+  int64_t sCi, sCj;   // output strides
+  const float* bias;      // [J]
+  const float* rowscale;  // [I]
+  int act;
+  int accumulate;
+  int64_t r_chunk;        // rows of R per blockIdx.z (split)
+  int64_t split_stride;   // elements between split partials (0 when not split)
+};
+
+// load one [rows x BR] tile of an operand whose element (i, r) sits at base[i * ld + r]  (r contiguous)
+template <int ROWS, bool VEC>
+__device__ __forceinline__ void load_rc(const float* __restrict__ base, int64_t ld, int64_t i0, int64_t imax, int64_t r0,
+                                        int64_t rmax, float (&reg)[ROWS / 16]) {
+  if (VEC) {
+    const int r4 = threadIdx.x & 3, ii = threadIdx.x >> 2;  // 64 rows per pass, 4 floats each
+#pragma unroll
+    for (int u = 0; u < ROWS / 64; ++u) {
+      const int64_t i = i0 + ii + 64 * u, r = r0 + r4 * 4;
+      float4 v = f4_zero();
+      if (i < imax && r < rmax) v = __ldg(reinterpret_cast<const float4*>(base + i * ld + r));
+      reg[u * 4 + 0] = v.x; reg[u * 4 + 1] = v.y; reg[u * 4 + 2] = v.z; reg[u * 4 + 3] = v.w;
+    }
+  } else {
+    const int rr = threadIdx.x & 15, ii = threadIdx.x >> 4;  // 16 rows per pass
+#pragma unroll
+    for (int u = 0; u < ROWS / 16; ++u) {
+      const int64_t i = i0 + ii + 16 * u, r = r0 + rr;
+      reg[u] = (i < imax && r < rmax) ? __ldg(base + i * ld + r) : 0.f;
+    }
+  }
+}
+template <int ROWS, bool VEC>
+__device__ __forceinline__ void store_rc(float (*s)[ROWS + PAD], const float (&reg)[ROWS / 16]) {
+  if (VEC) {
+    const int r4 = threadIdx.x & 3, ii = threadIdx.x >> 2;
+#pragma unroll
+    for (int u = 0; u < ROWS / 64; ++u)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) s[r4 * 4 + c][ii + 64 * u] = reg[u * 4 + c];
+  } else {
+    const int rr = threadIdx.x & 15, ii = threadIdx.x >> 4;
+#pragma unroll
+    for (int u = 0; u < ROWS / 16; ++u) s[rr][ii + 16 * u] = reg[u];
+  }
+}
+// operand whose element (i, r) sits at base[r * ld + i]  (i contiguous)
+template <int ROWS, bool VEC>
+__device__ __forceinline__ void load_ic(const float* __restrict__ base, int64_t ld, int64_t i0, int64_t imax, int64_t r0,
+                                        int64_t rmax, float (&reg)[ROWS / 16]) {
+  if (VEC) {
+    constexpr int V = ROWS / 4;           // float4 per r
+    constexpr int RP = kThreads / V;      // r per pass
+    const int i4 = threadIdx.x % V, rr = threadIdx.x / V;
+#pragma unroll
+    for (int u = 0; u < BR / RP; ++u) {
+      const int64_t i = i0 + i4 * 4, r = r0 + rr + RP * u;
+      float4 v = f4_zero();
+      if (i < imax && r < rmax) v = __ldg(reinterpret_cast<const float4*>(base + r * ld + i));
+      reg[u * 4 + 0] = v.x; reg[u * 4 + 1] = v.y; reg[u * 4 + 2] = v.z; reg[u * 4 + 3] = v.w;
+    }
+  } else {
+    constexpr int RP = kThreads / ROWS;
+    const int ii = threadIdx.x % ROWS, rr = threadIdx.x / ROWS;
+#pragma unroll
+    for (int u = 0; u < BR / RP; ++u) {
+      const int64_t i = i0 + ii, r = r0 + rr + RP * u;
+      reg[u] = (i < imax && r < rmax) ? __ldg(base + r * ld + i) : 0.f;
+    }
+  }
+}
+template <int ROWS, bool VEC>
+__device__ __forceinline__ void store_ic(float (*s)[ROWS + PAD], const float (&reg)[ROWS / 16]) {
+  if (VEC) {
+    constexpr int V = ROWS / 4;
+    constexpr int RP = kThreads / V;
+    const int i4 = threadIdx.x % V, rr = threadIdx.x / V;
+#pragma unroll
+    for (int u = 0; u < BR / RP; ++u)
+      *reinterpret_cast<float4*>(&s[rr + RP * u][i4 * 4]) =
+          make_float4(reg[u * 4 + 0], reg[u * 4 + 1], reg[u * 4 + 2], reg[u * 4 + 3]);
+  } else {
+    constexpr int RP = kThreads / ROWS;
+    const int ii = threadIdx.x % ROWS, rr = threadIdx.x / ROWS;
+#pragma unroll
+    for (int u = 0; u < BR / RP; ++u) s[rr + RP * u][ii] = reg[u];
+  }
+}
+
+template <bool A_RC, bool B_RC, bool VEC>
+__global__ void __launch_bounds__(kThreads, 2) gemm_kernel(GemmArgs g) {
+  __shared__ __align__(16) float As[BR][BI + PAD];
+  __shared__ __align__(16) float Bs[BR][BJ + PAD];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int64_t i0 = int64_t(blockIdx.x) * BI, j0 = int64_t(blockIdx.y) * BJ;
+  const int64_t rbeg = int64_t(blockIdx.z) * g.r_chunk;
+  const int64_t rend = min(g.R, rbeg + g.r_chunk);
+
+  float acc[TI][TJ];
+#pragma unroll
+  for (int a = 0; a < TI; ++a)
+#pragma unroll
+    for (int b = 0; b < TJ; ++b) acc[a][b] = 0.f;
+
+  float ra[BI / 16], rb[BJ / 16];
+  auto gload = [&](int64_t r0) {
+    if (A_RC) load_rc<BI, VEC>(g.A, g.lda, i0, g.I, r0, rend, ra); else load_ic<BI, VEC>(g.A, g.lda, i0, g.I, r0, rend, ra);
+    if (B_RC) load_rc<BJ, VEC>(g.B, g.ldb, j0, g.J, r0, rend, rb); else load_ic<BJ, VEC>(g.B, g.ldb, j0, g.J, r0, rend, rb);
+  };
+  auto sstore = [&]() {
+    if (A_RC) store_rc<BI, VEC>(As, ra); else store_ic<BI, VEC>(As, ra);
+    if (B_RC) store_rc<BJ, VEC>(Bs, rb); else store_ic<BJ, VEC>(Bs, rb);
+  };
+
+  if (rbeg < rend) gload(rbeg);
+  for (int64_t r0 = rbeg; r0 < rend; r0 += BR) {
+    sstore();
+    __syncthreads();
+    if (r0 + BR < rend) gload(r0 + BR);  // prefetch the next tile into registers while this one is multiplied
+#pragma unroll
+    for (int r = 0; r < BR; ++r) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[r][ty * TI]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[r][ty * TI + 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[r][tx * TJ]);
+      const float av[TI] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float bv[TJ] = {b0.x, b0.y, b0.z, b0.w};
+#pragma unroll
+      for (int a = 0; a < TI; ++a)
+#pragma unroll
+        for (int b = 0; b < TJ; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+    }
+    __syncthreads();
+  }
+
+  float* C = g.C + int64_t(blockIdx.z) * g.split_stride;
+  const bool split = g.split_stride != 0;
+#pragma unroll
+  for (int a = 0; a < TI; ++a) {
+    const int64_t i = i0 + ty * TI + a;
+    if (i >= g.I) continue;
+    const float rs = (!split && g.rowscale) ? __ldg(g.rowscale + i) : 1.f;
+#pragma unroll
+    for (int b = 0; b < TJ; ++b) {
+      const int64_t j = j0 + tx * TJ + b;
+      if (j >= g.J) continue;
+      float v = acc[a][b];
+      float* dst = C + i * g.sCi + j * g.sCj;
+      if (!split) {
+        v *= rs;
+        if (g.bias) v += __ldg(g.bias + j);
+        if (g.accumulate) v += *dst;
+        if (g.act == LGK_ACT_ELU) v = elu1(v);
+        else if (g.act == LGK_ACT_RELU) v = fmaxf(v, 0.f);
+      }
+      *dst = v;
+    }
+  }
+}
+
+// second stage of grad W: dW[m,k] (+)= sum_s partial[s][k*M + m]
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out,
+                                                            int64_t count, int splits, int accumulate) {
+  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t >= count) return;
+  float s = 0.f;
+  for (int k = 0; k < splits; ++k) s += partial[int64_t(k) * count + t];
+  if (accumulate) s += out[t];
+  out[t] = s;
+}
+
+// db[m] (+)= sum_n dy[n,m]: slab partials + final
+constexpr int kColsumRows = 512;
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __restrict__ dy, float* __restrict__ partial, int64_t N, int M) {
+  __shared__ float s[8][32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int m = blockIdx.y * 32 + tx;
+  const int64_t r0 = int64_t(blockIdx.x) * kColsumRows, r1 = min(N, r0 + kColsumRows);
+  float acc = 0.f;
+  if (m < M)
+    for (int64_t n = r0 + ty; n < r1; n += 8) acc += __ldg(dy + n * M + m);
+  s[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && m < M) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) acc += s[k][tx];
+    partial[int64_t(blockIdx.x) * M + m] = acc;
+  }
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <bool A_RC, bool B_RC>
+int launch_gemm(const GemmArgs& g, int splits, bool vec, cudaStream_t stream, const char* name) {
+  dim3 grid(unsigned(ceil_div(g.I, BI)), unsigned(ceil_div(g.J, BJ)), unsigned(splits));
+  if (vec) gemm_kernel<A_RC, B_RC, true><<<grid, kThreads, 0, stream>>>(g);
+  else gemm_kernel<A_RC, B_RC, false><<<grid, kThreads, 0, stream>>>(g);
+  LGK_CHECK_LAUNCH(name);
+  return LGK_OK;
+}
+
+int choose_wsplits(int64_t n, int64_t k, int64_t m) {
+  const int64_t tiles = ceil_div(k, BI) * ceil_div(m, BJ);
+  int64_t s = ceil_div(int64_t(kNumSMs) * 2, tiles);
+  const int64_t cap = ceil_div(n, 4 * BR);  // at least 64 rows of the reduction per split
+  if (s > cap) s = cap;
+  if (s < 1) s = 1;
+  if (s > 1024) s = 1024;
+  return int(s);
+}
+
+}  // namespace
+}  // namespace lgk
+
+using namespace lgk;
+
+extern "C" int lgk_linear_fwd(const void* x, const float* weight, const float* bias, const float* rowscale, void* out,
+                              int64_t n, int64_t k, int64_t m, int act, int accumulate, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && k > 0 && m > 0, LGK_ERR_BAD_ARG, "lgk_linear_fwd: bad sizes");
+  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_fwd: only fp32 is implemented");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(x && weight && out, LGK_ERR_BAD_ARG, "lgk_linear_fwd: null pointer");
+  GemmArgs g{};
+  g.A = static_cast<const float*>(x); g.B = weight; g.C = static_cast<float*>(out);
+  g.I = n; g.J = m; g.R = k; g.lda = k; g.ldb = k; g.sCi = m; g.sCj = 1;
+  g.bias = bias; g.rowscale = rowscale; g.act = act; g.accumulate = accumulate; g.r_chunk = k; g.split_stride = 0;
+  const bool vec = (k % 4 == 0) && aligned16(x) && aligned16(weight);
+  return launch_gemm<true, true>(g, 1, vec, stream, "gemm_kernel(fwd)");
+}
+
+extern "C" int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, int64_t n, int64_t k, int64_t m,
+                                int accumulate, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && k > 0 && m > 0, LGK_ERR_BAD_ARG, "lgk_linear_bwd_x: bad sizes");
+  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_bwd_x: only fp32 is implemented");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(dy && weight && dx, LGK_ERR_BAD_ARG, "lgk_linear_bwd_x: null pointer");
+  GemmArgs g{};
+  g.A = static_cast<const float*>(dy); g.B = weight; g.C = static_cast<float*>(dx);
+  g.I = n; g.J = k; g.R = m; g.lda = m; g.ldb = k; g.sCi = k; g.sCj = 1;
+  g.accumulate = accumulate; g.r_chunk = m; g.split_stride = 0;
+  const bool vec = (m % 4 == 0) && (k % 4 == 0) && aligned16(dy) && aligned16(weight);
+  return launch_gemm<true, false>(g, 1, vec, stream, "gemm_kernel(bwd_x)");
+}
+
+extern "C" int64_t lgk_linear_bwd_w_workspace_bytes(int64_t n, int64_t k, int64_t m) {
+  if (n <= 0 || k <= 0 || m <= 0) return 0;
+  const int s = choose_wsplits(n, k, m);
+  const int64_t slabs = ceil_div(n, kColsumRows);
+  return align_up(int64_t(s) * k * m * 4, 256) + align_up(slabs * m * 4, 256);
+}
+
+extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float* db, int64_t n, int64_t k, int64_t m,
+                                int accumulate, void* workspace, int64_t workspace_bytes, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && k > 0 && m > 0, LGK_ERR_BAD_ARG, "lgk_linear_bwd_w: bad sizes");
+  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_bwd_w: only fp32 is implemented");
+  LGK_REQUIRE(dw || db, LGK_ERR_BAD_ARG, "lgk_linear_bwd_w: nothing to compute");
+  if (n == 0) {
+    if (!accumulate) {
+      if (dw) cudaMemsetAsync(dw, 0, 4 * k * m, stream);
+      if (db) cudaMemsetAsync(db, 0, 4 * m, stream);
+      LGK_CHECK_LAUNCH("lgk_linear_bwd_w(memset)");
+    }
+    return LGK_OK;
+  }
+  LGK_REQUIRE(dy && (x || !dw), LGK_ERR_BAD_ARG, "lgk_linear_bwd_w: null pointer");
+  const int64_t need = lgk_linear_bwd_w_workspace_bytes(n, k, m);
+  LGK_REQUIRE(workspace && workspace_bytes >= need, LGK_ERR_WORKSPACE, "lgk_linear_bwd_w: workspace %lld < %lld bytes",
+              (long long)workspace_bytes, (long long)need);
+  const int s = choose_wsplits(n, k, m);
+  float* partial = static_cast<float*>(workspace);
+  float* colpart = reinterpret_cast<float*>(static_cast<char*>(workspace) + align_up(int64_t(s) * k * m * 4, 256));
+  if (dw) {
+    GemmArgs g{};
+    g.A = static_cast<const float*>(x); g.B = static_cast<const float*>(dy);
+    g.I = k; g.J = m; g.R = n; g.lda = k; g.ldb = m; g.sCi = 1; g.sCj = k;  // C(i=k_idx, j=m_idx) -> dW[m*K + k]
+    g.r_chunk = align_up(ceil_div(n, s), BR);
+    const bool vec = (k % 4 == 0) && (m % 4 == 0) && aligned16(x) && aligned16(dy);
+    if (s == 1) {
+      g.C = dw; g.split_stride = 0; g.accumulate = accumulate;
+      if (int rc = launch_gemm<false, false>(g, 1, vec, stream, "gemm_kernel(bwd_w)")) return rc;
+    } else {
+      g.C = partial; g.split_stride = k * m;
+      if (int rc = launch_gemm<false, false>(g, s, vec, stream, "gemm_kernel(bwd_w,split)")) return rc;
+      splitk_reduce_kernel<<<unsigned(ceil_div(k * m, 256)), 256, 0, stream>>>(partial, dw, k * m, s, accumulate);
+      LGK_CHECK_LAUNCH("splitk_reduce_kernel");
+    }
+  }
+  if (db) {
+    const int64_t slabs = ceil_div(n, kColsumRows);
+    dim3 grid(unsigned(slabs), unsigned(ceil_div(m, 32)));
+    colsum_partial_kernel<<<grid, 256, 0, stream>>>(static_cast<const float*>(dy), colpart, n, int(m));
+    LGK_CHECK_LAUNCH("colsum_partial_kernel");
+    splitk_reduce_kernel<<<unsigned(ceil_div(m, 256)), 256, 0, stream>>>(colpart, db, m, int(slabs), accumulate);
+    LGK_CHECK_LAUNCH("splitk_reduce_kernel(db)");
+  }
+  return LGK_OK;
+}
