@@ -1,0 +1,132 @@
+"""Graph structure shared by all layers of a step.
+
+`CSRGraph` is the stand-in for the `adj_t` SparseTensor the reference passes to its models when
+`compile=False` (reference datasets/datamodule.py:44-45, models/gat.py:87-90): destination-sorted CSR plus the
+CSC transpose index for the backward pass, int32, built once per batch by lgk_csr_build and shared by every
+layer and both passes.  Layers accept either a `CSRGraph` or the plain `[2, E]` int64 `edge_index`; the latter
+is converted on first use and memoised (keyed on the tensor's storage, shape and version counter) so that
+L layers x (fwd + bwd) still cost one build.
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Optional
+
+import torch
+from torch import Tensor
+
+from . import ops
+
+
+class CSRGraph:
+    """rowptr/col/perm: CSR by destination, entries ordered by (dst, src, original edge id).
+    colptr/row/csr2csc: CSC by source, entries ordered by CSR slot.  value: edge weights in CSR order."""
+
+    __slots__ = ("num_nodes", "num_edges", "rowptr", "col", "perm", "colptr", "row", "csr2csc", "value", "_norm")
+
+    def __init__(self, num_nodes, num_edges, rowptr, col, perm, colptr=None, row=None, csr2csc=None, value=None):
+        self.num_nodes, self.num_edges = int(num_nodes), int(num_edges)
+        self.rowptr, self.col, self.perm = rowptr, col, perm
+        self.colptr, self.row, self.csr2csc = colptr, row, csr2csc
+        self.value = value
+        self._norm = {}
+
+    @staticmethod
+    def from_edge_index(edge_index: Tensor, num_nodes: int, edge_weight: Optional[Tensor] = None,
+                        with_csc: bool = True) -> "CSRGraph":
+        if not edge_index.is_cuda:
+            raise RuntimeError("edge_index must be a CUDA tensor: lesion_gnn_b200 has no CPU path")
+        if edge_index.dtype != torch.int64:
+            edge_index = edge_index.long()
+        edge_index = edge_index.contiguous()
+        rowptr, col, perm, colptr, row, csr2csc = ops.csr_build(edge_index, num_nodes, with_csc)
+        g = CSRGraph(num_nodes, edge_index.size(1), rowptr, col, perm, colptr, row, csr2csc)
+        if edge_weight is not None:
+            g.value = g.permute_edge_values(edge_weight)
+        return g
+
+    def permute_edge_values(self, edge_weight: Tensor) -> Tensor:
+        """per-edge values in original edge order -> CSR slot order (SparseTensor `value`)"""
+        if edge_weight.dim() != 1 or edge_weight.numel() != self.num_edges:
+            raise ValueError("edge_weight must have shape [E]")
+        return ops.gather_f32(edge_weight.detach().float().contiguous(), self.perm)
+
+    def with_value(self, edge_weight: Optional[Tensor]) -> "CSRGraph":
+        """same structure, different edge weights (shares the index tensors)"""
+        g = CSRGraph(self.num_nodes, self.num_edges, self.rowptr, self.col, self.perm, self.colptr, self.row, self.csr2csc)
+        g.value = None if edge_weight is None else self.permute_edge_values(edge_weight)
+        return g
+
+    def gcn_norm(self, improved: bool, add_self_loops: bool):
+        """(dinv, selfw) of gcn_norm for this graph's weights; memoised per (improved, add_self_loops)."""
+        key = (bool(improved), bool(add_self_loops))
+        if key not in self._norm:
+            self._norm[key] = ops.gcn_norm(self.rowptr, self.col, self.value, 2.0 if improved else 1.0, add_self_loops)
+        return self._norm[key]
+
+    def to_edge_index(self) -> Tensor:
+        """[2, E] int64 in CSR order (row 0 = src, row 1 = dst)"""
+        deg = (self.rowptr[1:] - self.rowptr[:-1]).long()
+        dst = torch.repeat_interleave(torch.arange(self.num_nodes, device=self.col.device), deg)
+        return torch.stack([self.col.long(), dst])
+
+
+_CACHE: "OrderedDict[tuple, tuple]" = OrderedDict()
+_CACHE_SIZE = 16
+
+
+def _key(t: Tensor, extra=()) -> tuple:
+    return (t.data_ptr(), tuple(t.shape), t._version, t.device.index) + tuple(extra)
+
+
+def clear_cache() -> None:
+    _CACHE.clear()
+
+
+def as_graph(edge_index, num_nodes: int, edge_weight: Optional[Tensor] = None) -> CSRGraph:
+    """CSRGraph for `edge_index` ([2,E] tensor or already a CSRGraph), memoised per tensor."""
+    if isinstance(edge_index, CSRGraph):
+        if edge_weight is not None:
+            raise ValueError("pass edge weights through CSRGraph.value when handing a CSRGraph to a layer")
+        if edge_index.num_nodes != num_nodes:
+            raise ValueError(f"graph has {edge_index.num_nodes} nodes but x has {num_nodes} rows")
+        return edge_index
+    k = _key(edge_index, (int(num_nodes),))
+    hit = _CACHE.get(k)
+    if hit is None:
+        g = CSRGraph.from_edge_index(edge_index, num_nodes)
+        _CACHE[k] = (g, edge_index, {})  # keep the tensor alive so its storage cannot be recycled under the key
+        while len(_CACHE) > _CACHE_SIZE:
+            _CACHE.popitem(last=False)
+        hit = _CACHE[k]
+    else:
+        _CACHE.move_to_end(k)
+    g, _, weighted = hit
+    if edge_weight is None:
+        return g
+    wk = _key(edge_weight)
+    if wk not in weighted:
+        weighted.clear()
+        weighted[wk] = (g.with_value(edge_weight), edge_weight)
+    return weighted[wk][0]
+
+
+def as_ptr(batch: Tensor, size: Optional[int] = None):
+    """(int32 graph pointer [B+1], B) for a sorted `batch` vector, memoised per tensor.  With size=None this
+    reads batch[-1] on the host once (PyG's global_*_pool does the same through batch.max())."""
+    if not batch.is_cuda:
+        raise RuntimeError("batch must be a CUDA tensor: lesion_gnn_b200 has no CPU path")
+    k = _key(batch, ("ptr", size))
+    hit = _CACHE.get(k)
+    if hit is None:
+        if size is None:
+            size = int(batch[-1].item()) + 1 if batch.numel() > 0 else 0
+        b = batch if batch.dtype == torch.int64 else batch.long()
+        ptr = ops.batch_ptr(b.contiguous(), size)
+        _CACHE[k] = ((ptr, int(size)), batch, {})
+        while len(_CACHE) > _CACHE_SIZE:
+            _CACHE.popitem(last=False)
+        hit = _CACHE[k]
+    else:
+        _CACHE.move_to_end(k)
+    return hit[0]

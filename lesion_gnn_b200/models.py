@@ -1,0 +1,120 @@
+"""The reference's L1 modules on the lgk layers: same constructor arguments, attribute names (state_dict keys)
+and `forward(x, edge_index, batch)` signature as reference src/lesion_gnn/models/gat.py:17-59 and
+gin.py:17-35, plus the GCN / GraphSAGE graph classifiers BASELINE.json's configs 1, 3 and 4 name.
+
+`edge_index` may be the `[2, E]` int64 tensor or a `CSRGraph` (the reference's `adj_t`, gat.py:87-90); `batch`
+may be the int64 graph-id vector or a `Segments` object.  The in_proj / out_proj transforms are
+`lesion_gnn_b200.nn.Linear` (parameter names `weight`, `bias` as in torch.nn.Linear, torch's default init).
+"""
+from __future__ import annotations
+
+import math
+from itertools import pairwise
+
+import torch
+import torch.nn as nn
+from torch import Tensor
+
+from .nn import (GATConv, GCNConv, GINConv, MLP, SAGEConv, Linear, elu, global_max_pool, global_mean_max_pool,
+                 global_mean_pool)
+
+
+class _TorchInitLinear(Linear):
+    """torch.nn.Linear's initialisation (the reference's in_proj / out_proj are torch.nn.Linear)."""
+
+    def reset_parameters(self):
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        if self.bias is not None:
+            bound = 1 / math.sqrt(self.in_channels)
+            nn.init.uniform_(self.bias, -bound, bound)
+
+
+def _readout(x: Tensor, batch, pooling: str) -> Tensor:
+    if pooling == "mean":
+        return global_mean_pool(x, batch)
+    if pooling == "max":
+        return global_max_pool(x, batch)
+    if pooling == "mean+max":
+        return global_mean_max_pool(x, batch)
+    raise ValueError(pooling)
+
+
+class GAT(nn.Module):
+    """reference models/gat.py:17-59 (num_st_seed_points=None branch)."""
+
+    def __init__(self, input_features: int, hiddden_channels: list[int], num_classes: int, heads: int, dropout: float,
+                 num_st_seed_points: int | None = None):
+        super().__init__()
+        if num_st_seed_points is not None:
+            raise NotImplementedError("SetTransformerAggregation is outside the hot path (SURVEY.md 2)")
+        assert all(d % heads == 0 for d in hiddden_channels)
+        self.in_proj = _TorchInitLinear(input_features, hiddden_channels[0])
+        self.convs = nn.ModuleList(
+            [GATConv(d1, d2 // heads, heads=heads, dropout=dropout) for d1, d2 in pairwise(hiddden_channels)]
+        )
+        self.st = None
+        self.out_proj = _TorchInitLinear(hiddden_channels[-1], num_classes)
+
+    def forward(self, x: Tensor, edge_index, batch) -> Tensor:
+        x = self.in_proj(x)
+        for conv in self.convs:
+            x = elu(conv(x, edge_index))
+        x = global_mean_pool(x, batch)
+        return self.out_proj(x)
+
+
+class GIN(nn.Module):
+    """reference models/gin.py:17-35; pooling='mean+max' is BASELINE.json config 3's read-out."""
+
+    def __init__(self, input_features: int, hidden_channels: list[int], num_classes: int, dropout: float,
+                 pooling: str = "mean"):
+        super().__init__()
+        assert all(d > 0 for d in hidden_channels)
+        self.in_proj = _TorchInitLinear(input_features, hidden_channels[0])
+        self.convs = nn.ModuleList(
+            [GINConv(MLP([d1, d2, d2], act="ELU", dropout=dropout)) for d1, d2 in pairwise(hidden_channels)]
+        )
+        self.pooling = pooling
+        mult = 2 if pooling == "mean+max" else 1
+        self.out_proj = _TorchInitLinear(mult * hidden_channels[-1], num_classes)
+        self.dropout = nn.Dropout(dropout)
+
+    def forward(self, x: Tensor, edge_index, batch) -> Tensor:
+        x = self.in_proj(x)
+        for conv in self.convs:
+            x = elu(conv(x, edge_index))
+            x = self.dropout(x)
+        return self.out_proj(_readout(x, batch, self.pooling))
+
+
+class SAGE(nn.Module):
+    """BASELINE.json config 3, GraphSAGE variant: n x (SAGEConv + ELU) -> mean||max -> Linear."""
+
+    def __init__(self, input_features: int, hidden_channels: list[int], num_classes: int, aggr: str = "mean",
+                 pooling: str = "mean+max"):
+        super().__init__()
+        dims = [input_features] + list(hidden_channels)
+        self.convs = nn.ModuleList([SAGEConv(d1, d2, aggr=aggr) for d1, d2 in pairwise(dims)])
+        self.pooling = pooling
+        mult = 2 if pooling == "mean+max" else 1
+        self.out_proj = _TorchInitLinear(mult * hidden_channels[-1], num_classes)
+
+    def forward(self, x: Tensor, edge_index, batch) -> Tensor:
+        for conv in self.convs:
+            x = elu(conv(x, edge_index))
+        return self.out_proj(_readout(x, batch, self.pooling))
+
+
+class GCN(nn.Module):
+    """BASELINE.json configs 1 and 4: n x (GCNConv + ELU) -> global_mean_pool -> Linear."""
+
+    def __init__(self, input_features: int, hidden_channels: list[int], num_classes: int):
+        super().__init__()
+        dims = [input_features] + list(hidden_channels)
+        self.convs = nn.ModuleList([GCNConv(d1, d2) for d1, d2 in pairwise(dims)])
+        self.out_proj = _TorchInitLinear(hidden_channels[-1], num_classes)
+
+    def forward(self, x: Tensor, edge_index, batch, edge_weight=None) -> Tensor:
+        for conv in self.convs:
+            x = elu(conv(x, edge_index, edge_weight))
+        return self.out_proj(global_mean_pool(x, batch))

@@ -1,0 +1,217 @@
+"""Autograd wrappers: one torch.autograd.Function per fused op, saving only what the backward kernels need.
+
+Forward kernels walk the CSR (rows = destinations), backward kernels walk the CSC (rows = sources), so no
+pass uses atomics and every result is bit-reproducible run to run.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+from torch import Tensor
+
+from .. import ops
+from .._lib import ACT_ELU, ACT_NONE, SELF_ADD, SELF_NONE, SELF_REPLACE  # noqa: F401
+from ..graph import CSRGraph
+
+
+def _need_csc(g: CSRGraph):
+    if g.colptr is None:
+        raise RuntimeError("this CSRGraph was built without the CSC transpose index; backward needs with_csc=True")
+
+
+class _Aggregate(torch.autograd.Function):
+    """out = post * sum_p w_p pre[j_p] x[j_p] (+ self term) (+ bias), or mean / max over the row."""
+
+    @staticmethod
+    def forward(ctx, x, bias, g: CSRGraph, reduce, use_value, pre, post, selfw, self_fill, self_mode):
+        ew = g.value if use_value else None
+        ctx.g, ctx.reduce, ctx.ew = g, reduce, ew
+        ctx.pre, ctx.post, ctx.selfw, ctx.self_fill, ctx.self_mode = pre, post, selfw, self_fill, self_mode
+        ctx.has_bias = bias is not None
+        x = x.contiguous()
+        if reduce == "max":
+            out, arg = ops.spmm(g.rowptr, g.col, x, "max", bias=bias, want_arg=True)
+            ctx.arg = arg
+            return out
+        if reduce == "mean":
+            deg = (g.rowptr[1:] - g.rowptr[:-1]).clamp(min=1).float()
+            ctx.inv_deg = deg.reciprocal()
+        return ops.spmm(g.rowptr, g.col, x, reduce, ew=ew, pre=pre, post=post, selfw=selfw, self_fill=self_fill,
+                        self_mode=self_mode, bias=bias)
+
+    @staticmethod
+    def backward(ctx, dout):
+        g = ctx.g
+        _need_csc(g)
+        dout = dout.contiguous()
+        dx = dbias = None
+        if ctx.needs_input_grad[0]:
+            if ctx.reduce == "max":
+                dx = ops.spmm_max_bwd(g.colptr, g.row, g.csr2csc, ctx.arg, dout)
+            elif ctx.reduce == "mean":
+                # d x_j = sum_{i : j -> i} dout_i / max(deg_i, 1)
+                dx = ops.spmm(g.colptr, g.row, dout, "sum", pre=ctx.inv_deg)
+            else:
+                # transpose: scale on the gathered side <-> scale on the output side
+                dx = ops.spmm(g.colptr, g.row, dout, "sum", emap=g.csr2csc if ctx.ew is not None else None, ew=ctx.ew,
+                              pre=ctx.post, post=ctx.pre, selfw=ctx.selfw, self_fill=ctx.self_fill, self_mode=ctx.self_mode)
+        if ctx.has_bias and ctx.needs_input_grad[1]:
+            dbias = ops.colsum(dout.float() if dout.dtype != torch.float32 else dout)
+        return dx, dbias, None, None, None, None, None, None, None, None
+
+
+def aggregate(x: Tensor, g: CSRGraph, reduce: str = "sum", *, use_value: bool = False, pre: Optional[Tensor] = None,
+              post: Optional[Tensor] = None, selfw: Optional[Tensor] = None, self_fill: float = 1.0,
+              self_mode: int = SELF_NONE, bias: Optional[Tensor] = None) -> Tensor:
+    reduce = {"add": "sum"}.get(reduce, reduce)
+    if reduce not in ("sum", "mean", "max"):
+        raise ValueError(f"unsupported aggregation {reduce!r}")
+    return _Aggregate.apply(x, bias, g, reduce, use_value, pre, post, selfw, float(self_fill), int(self_mode))
+
+
+class _GatAttention(torch.autograd.Function):
+    """h [N, H*C] -> edge-softmax attention output [N, H*C] (+ bias)."""
+
+    @staticmethod
+    def forward(ctx, h, att_src, att_dst, bias, g: CSRGraph, heads, chan, negative_slope, add_self_loops, dropout_p, seed):
+        h = h.contiguous()
+        a_s = att_src.detach().reshape(-1).contiguous()
+        a_d = att_dst.detach().reshape(-1).contiguous()
+        a_src, a_dst = ops.gat_alpha(h, a_s, a_d, heads, chan)
+        out, rowmax, rowsum = ops.gat_fwd(g.rowptr, g.col, h, a_src, a_dst, bias, heads, chan, negative_slope,
+                                          add_self_loops, dropout_p, seed)
+        ctx.save_for_backward(h, a_src, a_dst, rowmax, rowsum, out, a_s, a_d, bias if bias is not None else h.new_empty(0))
+        ctx.g, ctx.cfg = g, (heads, chan, negative_slope, add_self_loops, dropout_p, seed)
+        ctx.has_bias = bias is not None
+        ctx.att_shape = att_src.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        h, a_src, a_dst, rowmax, rowsum, out, a_s, a_d, bias = ctx.saved_tensors
+        heads, chan, slope, add_self, p, seed = ctx.cfg
+        g = ctx.g
+        _need_csc(g)
+        dout = dout.contiguous()
+        dh, datt_src, datt_dst = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
+                                             a_s, a_d, dout, heads, chan, slope, add_self, p, seed)
+        dbias = None
+        if ctx.has_bias and ctx.needs_input_grad[3]:
+            dbias = ops.colsum(dout if dout.dtype == torch.float32 else dout.float())
+        return (dh, datt_src.view(ctx.att_shape), datt_dst.view(ctx.att_shape), dbias, None, None, None, None, None,
+                None, None)
+
+
+def gat_attention(h, att_src, att_dst, bias, g, heads, chan, negative_slope=0.2, add_self_loops=True, dropout_p=0.0,
+                  seed=0) -> Tensor:
+    return _GatAttention.apply(h, att_src, att_dst, bias, g, int(heads), int(chan), float(negative_slope),
+                               bool(add_self_loops), float(dropout_p), int(seed))
+
+
+class _Linear(torch.autograd.Function):
+    """out = act(rowscale * x W^T + bias) [+ second product x2 W2^T fused by accumulation]."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, rowscale, act, x2, weight2):
+        x = x.contiguous()
+        w = weight.contiguous()
+        if x2 is not None:
+            # out = x W^T + bias + x2 W2^T  (SAGEConv / GraphConv root term): second kernel accumulates in place
+            if rowscale is not None or act != ACT_NONE:
+                raise ValueError("the fused two-operand form takes no rowscale/activation")
+            x2 = x2.contiguous()
+            w2 = weight2.contiguous()
+            out = ops.linear_fwd(x, w, bias)
+            out = ops.linear_fwd(x2, w2, out=out)
+            ctx.save_for_backward(x, w, x2, w2)
+        else:
+            out = ops.linear_fwd(x, w, bias, rowscale, act)
+            ctx.save_for_backward(x, w, out if act != ACT_NONE else x.new_empty(0), rowscale if rowscale is not None else x.new_empty(0))
+        ctx.two, ctx.act, ctx.has_bias, ctx.has_rs = x2 is not None, act, bias is not None, rowscale is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        dout = dout.contiguous()
+        ni = ctx.needs_input_grad
+        if ctx.two:
+            x, w, x2, w2 = ctx.saved_tensors
+            dx = ops.linear_bwd_x(dout, w) if ni[0] else None
+            dw, db = ops.linear_bwd_w(dout, x, want_dw=ni[1], want_db=ctx.has_bias and ni[2]) if (ni[1] or (ctx.has_bias and ni[2])) else (None, None)
+            dx2 = ops.linear_bwd_x(dout, w2) if ni[5] else None
+            dw2 = ops.linear_bwd_w(dout, x2)[0] if ni[6] else None
+            return dx, dw, db, None, None, dx2, dw2
+        x, w, out, rs = ctx.saved_tensors
+        if ctx.act == ACT_ELU:
+            dout = ops.elu_bwd(out, dout)
+        elif ctx.act != ACT_NONE:
+            raise NotImplementedError
+        db = None
+        if ctx.has_bias and ni[2]:
+            db = ops.colsum(dout)
+        if ctx.has_rs:
+            dout = dout * rs.unsqueeze(1)
+        dx = ops.linear_bwd_x(dout, w) if ni[0] else None
+        dw = ops.linear_bwd_w(dout, x)[0] if ni[1] else None
+        return dx, dw, db, None, None, None, None
+
+
+def linear(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None, *, rowscale: Optional[Tensor] = None,
+           act: int = ACT_NONE, x2: Optional[Tensor] = None, weight2: Optional[Tensor] = None) -> Tensor:
+    if x.dim() != 2:
+        lead = x.shape[:-1]
+        return linear(x.reshape(-1, x.size(-1)), weight, bias, rowscale=rowscale, act=act).reshape(*lead, weight.size(0))
+    return _Linear.apply(x, weight, bias, rowscale, int(act), x2, weight2)
+
+
+class _Elu(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = ops.elu_fwd(x.contiguous())
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return ops.elu_bwd(y, dy.contiguous())
+
+
+def elu(x: Tensor) -> Tensor:
+    return _Elu.apply(x)
+
+
+class _Pool(torch.autograd.Function):
+    """segment reduce over graphs; mode in {'sum','mean','max','mean+max'}"""
+
+    @staticmethod
+    def forward(ctx, x, ptr, mode):
+        x = x.contiguous()
+        want_sum = mode in ("sum", "mean", "mean+max")
+        want_max = mode in ("max", "mean+max")
+        mean = mode in ("mean", "mean+max")
+        out_sum, out_max, arg = ops.pool_fwd(x, ptr, want_sum, mean, want_max)
+        ctx.ptr, ctx.arg, ctx.mode, ctx.mean = ptr, arg, mode, mean
+        ctx.shape, ctx.dtype, ctx.device = x.shape, x.dtype, x.device
+        if mode == "mean+max":
+            return torch.cat([out_sum, out_max], dim=1)
+        return out_sum if want_sum else out_max
+
+    @staticmethod
+    def backward(ctx, dout):
+        n, f = ctx.shape
+        dout = dout.contiguous()
+        dsum = dmax = None
+        if ctx.mode == "mean+max":
+            dsum, dmax = dout[:, :f].contiguous(), dout[:, f:].contiguous()
+        elif ctx.mode == "max":
+            dmax = dout
+        else:
+            dsum = dout
+        dx = ops.pool_bwd(dsum, ctx.mean, dmax, ctx.arg, ctx.ptr, n, f, ctx.dtype, ctx.device)
+        return dx, None, None
+
+
+def segment_pool(x: Tensor, ptr: Tensor, mode: str) -> Tensor:
+    return _Pool.apply(x, ptr, mode)

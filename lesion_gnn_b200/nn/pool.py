@@ -1,0 +1,62 @@
+"""Global pooling with PyG's signatures: global_{mean,max,add}_pool(x, batch, size=None)
+(reference models/gat.py:56, gin.py:33, pointnet.py:38) plus the fused mean||max read-out of BASELINE.json
+config 3.  `batch` is the sorted int64 graph-id vector of PyG collation, or a `Segments` object that already
+carries the graph pointer (no device->host read at all)."""
+from __future__ import annotations
+
+from typing import Optional, Union
+
+import torch
+from torch import Tensor
+
+from .. import ops
+from ..graph import as_ptr
+from . import functional as F
+
+
+class Segments:
+    """Graph segmentation of a collated batch: int32 ptr[B+1] on the device and B on the host."""
+
+    __slots__ = ("ptr", "num_graphs", "batch")
+
+    def __init__(self, ptr: Tensor, num_graphs: int, batch: Optional[Tensor] = None):
+        self.ptr, self.num_graphs, self.batch = ptr, int(num_graphs), batch
+
+    @staticmethod
+    def from_batch(batch: Tensor, num_graphs: int) -> "Segments":
+        b = batch if batch.dtype == torch.int64 else batch.long()
+        return Segments(ops.batch_ptr(b.contiguous(), num_graphs), num_graphs, batch)
+
+
+def _ptr(batch: Union[Tensor, Segments, None], n: int, size: Optional[int], device) -> Tensor:
+    if isinstance(batch, Segments):
+        return batch.ptr
+    if batch is None:  # PyG: a single graph
+        return torch.tensor([0, n], dtype=torch.int32, device=device)
+    return as_ptr(batch, size)[0]
+
+
+def _pool(x: Tensor, batch, size, mode: str) -> Tensor:
+    if not x.is_cuda:
+        raise RuntimeError("x must be a CUDA tensor: lesion_gnn_b200 has no CPU path")
+    squeeze = x.dim() == 1
+    x2 = x.unsqueeze(-1) if squeeze else x
+    out = F.segment_pool(x2, _ptr(batch, x2.size(0), size, x.device), mode)
+    return out.squeeze(-1) if squeeze else out
+
+
+def global_add_pool(x: Tensor, batch, size: Optional[int] = None) -> Tensor:
+    return _pool(x, batch, size, "sum")
+
+
+def global_mean_pool(x: Tensor, batch, size: Optional[int] = None) -> Tensor:
+    return _pool(x, batch, size, "mean")
+
+
+def global_max_pool(x: Tensor, batch, size: Optional[int] = None) -> Tensor:
+    return _pool(x, batch, size, "max")
+
+
+def global_mean_max_pool(x: Tensor, batch, size: Optional[int] = None) -> Tensor:
+    """cat([global_mean_pool, global_max_pool], dim=1) in one pass over x"""
+    return _pool(x, batch, size, "mean+max")

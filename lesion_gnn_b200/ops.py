@@ -1,0 +1,312 @@
+"""Tensor-level wrappers over the C ABI (no autograd; see nn/functional.py for that).
+
+Every function checks that its tensors live on a CUDA device, are contiguous and have the dtype the kernel
+expects, allocates outputs / workspaces with PyTorch's caching allocator, and enqueues on the current stream.
+Nothing here synchronises, so all of it can be captured into a CUDA graph.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import F32, BF16, SUM, MEAN, MAX, SELF_NONE, SELF_REPLACE, SELF_ADD  # noqa: F401
+
+_REDUCE = {"sum": SUM, "add": SUM, "mean": MEAN, "max": MAX}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dt(t: Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError(f"lesion_gnn_b200 kernels take float32 or bfloat16 features, got {t.dtype}")
+
+
+def _chk(t: Optional[Tensor], dtype=None, name="tensor") -> Optional[int]:
+    """validate and return the device pointer (None -> NULL)"""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: lesion_gnn_b200 has no CPU path")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.data_ptr() if t.numel() > 0 else None
+
+
+def _ws(nbytes: int, device) -> Tensor:
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+
+
+def launch_count() -> int:
+    return int(_lib.lib().query("lgk_launch_count"))
+
+
+def reset_launch_count() -> None:
+    _lib.lib().query("lgk_reset_launch_count")
+
+
+# ---------------------------------------------------------------------------------------------- structure
+
+
+def csr_build(edge_index: Tensor, num_nodes: int, with_csc: bool = True):
+    """-> rowptr, col, perm, colptr, row, csr2csc (int32); the last three are None without with_csc."""
+    L = _lib.lib()
+    if edge_index.dim() != 2 or edge_index.size(0) != 2:
+        raise ValueError("edge_index must have shape [2, E]")
+    ei = _chk(edge_index, torch.int64, "edge_index")
+    dev = edge_index.device
+    E, N = edge_index.size(1), int(num_nodes)
+    i32 = dict(dtype=torch.int32, device=dev)
+    rowptr, col, perm = torch.empty(N + 1, **i32), torch.empty(E, **i32), torch.empty(E, **i32)
+    if with_csc:
+        colptr, row, csr2csc = torch.empty(N + 1, **i32), torch.empty(E, **i32), torch.empty(E, **i32)
+    else:
+        colptr = row = csr2csc = None
+    nbytes = L.query("lgk_csr_workspace_bytes", N, E)
+    ws = _ws(nbytes, dev)
+    L.call("lgk_csr_build", ei, E, N, rowptr.data_ptr(), _chk(col), _chk(perm),
+           None if colptr is None else colptr.data_ptr(), _chk(row), _chk(csr2csc),
+           ws.data_ptr(), ws.numel(), _stream())
+    return rowptr, col, perm, colptr, row, csr2csc
+
+
+def batch_ptr(batch: Tensor, num_graphs: int) -> Tensor:
+    L = _lib.lib()
+    b = _chk(batch, torch.int64, "batch")
+    ptr = torch.empty(int(num_graphs) + 1, dtype=torch.int32, device=batch.device)
+    L.call("lgk_batch_ptr", b, batch.numel(), int(num_graphs), ptr.data_ptr(), _stream())
+    return ptr
+
+
+def gather_f32(src: Tensor, index: Tensor) -> Tensor:
+    L = _lib.lib()
+    out = torch.empty(index.numel(), dtype=torch.float32, device=src.device)
+    L.call("lgk_gather_f32", _chk(src, torch.float32, "src"), _chk(index, torch.int32, "index"), _chk(out),
+           index.numel(), _stream())
+    return out
+
+
+def knn_graph_raw(pos: Tensor, ptr: Tensor, k: int, loop: bool, num_edges: Optional[int] = None) -> Tensor:
+    """kNN edges for a collated batch; `ptr` is the int32 graph pointer.  num_edges, when the caller knows it
+    from host-side graph sizes, avoids the one device->host read of eptr[-1]."""
+    L = _lib.lib()
+    if pos.dim() != 2:
+        raise ValueError("pos must be [N, dim]")
+    if pos.dtype not in (torch.float32, torch.float64):
+        raise TypeError("pos must be float32 or float64")
+    B, N = ptr.numel() - 1, pos.size(0)
+    eptr = torch.empty(B + 1, dtype=torch.int64, device=pos.device)
+    L.call("lgk_knn_edge_ptr", _chk(ptr, torch.int32, "ptr"), B, int(k), int(loop), eptr.data_ptr(), _stream())
+    if num_edges is None:
+        num_edges = int(eptr[-1].item())
+    out = torch.empty(2, num_edges, dtype=torch.int64, device=pos.device)
+    L.call("lgk_knn_graph", _chk(pos, None, "pos"), 0 if pos.dtype == torch.float32 else 1, pos.size(1),
+           ptr.data_ptr(), eptr.data_ptr(), B, N, int(k), int(loop), _chk(out), num_edges, _stream())
+    return out
+
+
+def gaussian_distance(pos: Tensor, edge_index: Tensor, sigma: float) -> Tensor:
+    L = _lib.lib()
+    E = edge_index.size(1)
+    out = torch.empty(E, dtype=torch.float32, device=pos.device)
+    L.call("lgk_gaussian_distance", _chk(pos, None, "pos"), 0 if pos.dtype == torch.float32 else 1, pos.size(1),
+           _chk(edge_index, torch.int64, "edge_index"), E, float(sigma), _chk(out), _stream())
+    return out
+
+
+# -------------------------------------------------------------------------------------------- aggregation
+
+
+def spmm(ptr: Tensor, idx: Tensor, x: Tensor, reduce: str = "sum", *, emap: Optional[Tensor] = None,
+         ew: Optional[Tensor] = None, pre: Optional[Tensor] = None, post: Optional[Tensor] = None,
+         selfw: Optional[Tensor] = None, self_fill: float = 1.0, self_mode: int = SELF_NONE,
+         bias: Optional[Tensor] = None, want_arg: bool = False):
+    L = _lib.lib()
+    n, f = x.shape
+    out = torch.empty_like(x)
+    arg = torch.empty(n, f, dtype=torch.int32, device=x.device) if (want_arg and _REDUCE[reduce] == MAX) else None
+    f32 = torch.float32
+    L.call("lgk_spmm", _chk(ptr, torch.int32, "ptr"), _chk(idx, torch.int32, "idx"), _chk(emap, torch.int32, "emap"),
+           _chk(ew, f32, "ew"), _chk(pre, f32, "pre"), _chk(post, f32, "post"), _chk(selfw, f32, "selfw"),
+           float(self_fill), int(self_mode), _chk(x, None, "x"), _chk(bias, f32, "bias"), _chk(out), _chk(arg),
+           n, f, _REDUCE[reduce], _dt(x), _stream())
+    return (out, arg) if want_arg else out
+
+
+def spmm_max_bwd(colptr: Tensor, row: Tensor, csr2csc: Tensor, arg: Tensor, dy: Tensor) -> Tensor:
+    L = _lib.lib()
+    dx = torch.empty_like(dy)
+    L.call("lgk_spmm_max_bwd", _chk(colptr, torch.int32), _chk(row, torch.int32), _chk(csr2csc, torch.int32),
+           _chk(arg, torch.int32), _chk(dy, None, "dy"), _chk(dx), dy.size(0), dy.size(1), _dt(dy), _stream())
+    return dx
+
+
+def gcn_norm(rowptr: Tensor, col: Tensor, ew: Optional[Tensor], fill: float, add_self_loops: bool):
+    L = _lib.lib()
+    n = rowptr.numel() - 1
+    dinv = torch.empty(n, dtype=torch.float32, device=rowptr.device)
+    selfw = torch.empty(n, dtype=torch.float32, device=rowptr.device) if (ew is not None and add_self_loops) else None
+    L.call("lgk_gcn_norm", _chk(rowptr, torch.int32), _chk(col, torch.int32), _chk(ew, torch.float32, "ew"), float(fill),
+           int(add_self_loops), _chk(dinv), _chk(selfw), n, _stream())
+    return dinv, selfw
+
+
+# ---------------------------------------------------------------------------------------------------- GAT
+
+
+def gat_alpha(h: Tensor, att_src: Tensor, att_dst: Tensor, heads: int, chan: int):
+    L = _lib.lib()
+    n = h.size(0)
+    a_src = torch.empty(n, heads, dtype=torch.float32, device=h.device)
+    a_dst = torch.empty_like(a_src)
+    L.call("lgk_gat_alpha", _chk(h, None, "h"), _chk(att_src, torch.float32, "att_src"), _chk(att_dst, torch.float32, "att_dst"),
+           _chk(a_src), _chk(a_dst), n, heads, chan, _dt(h), _stream())
+    return a_src, a_dst
+
+
+def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p=0.0, seed=0):
+    L = _lib.lib()
+    n = h.size(0)
+    out = torch.empty_like(h)
+    rowmax = torch.empty(n, heads, dtype=torch.float32, device=h.device)
+    rowsum = torch.empty_like(rowmax)
+    L.call("lgk_gat_fwd", _chk(rowptr, torch.int32), _chk(col, torch.int32), _chk(h, None, "h"), _chk(a_src, torch.float32),
+           _chk(a_dst, torch.float32), _chk(bias, torch.float32, "bias"), _chk(out), _chk(rowmax), _chk(rowsum), n, heads, chan,
+           float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), _dt(h), _stream())
+    return out, rowmax, rowsum
+
+
+def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst, dout, heads, chan, negative_slope,
+            add_self_loops, dropout_p=0.0, seed=0):
+    """-> dh, datt_src [H*C], datt_dst [H*C]"""
+    L = _lib.lib()
+    n, dev = h.size(0), h.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    stats = torch.empty(n, heads, 4, **f32)
+    da_dst = torch.empty(n, heads, **f32)
+    da_src = torch.empty(n, heads, **f32)
+    dh = torch.empty_like(h)
+    dt, st = _dt(h), _stream()
+    L.call("lgk_gat_bwd_dst", _chk(graph.rowptr), _chk(graph.col), _chk(h), _chk(a_src), _chk(a_dst), _chk(rowmax),
+           _chk(rowsum), _chk(out, None, "out"), _chk(bias, torch.float32), _chk(dout, h.dtype, "dout"), _chk(stats), _chk(da_dst),
+           n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), dt, st)
+    L.call("lgk_gat_bwd_src", _chk(graph.colptr), _chk(graph.row), _chk(graph.csr2csc), _chk(h), _chk(a_src), _chk(a_dst),
+           _chk(rowmax), _chk(rowsum), _chk(stats), _chk(da_dst), _chk(att_src, torch.float32), _chk(att_dst, torch.float32),
+           _chk(dout), _chk(dh), _chk(da_src), n, heads, chan, float(negative_slope), int(add_self_loops),
+           float(dropout_p), int(seed), dt, st)
+    datt_src = torch.empty(heads * chan, **f32)
+    datt_dst = torch.empty(heads * chan, **f32)
+    ws = _ws(L.query("lgk_gat_datt_workspace_bytes", n, heads, chan), dev)
+    L.call("lgk_gat_datt", _chk(h), _chk(da_src), _chk(da_dst), _chk(datt_src), _chk(datt_dst), n, heads, chan,
+           ws.data_ptr(), ws.numel(), dt, st)
+    return dh, datt_src, datt_dst
+
+
+# ------------------------------------------------------------------------------------------------ pooling
+
+
+def pool_fwd(x: Tensor, ptr: Tensor, want_sum: bool, mean: bool, want_max: bool):
+    """-> (out_sum|None, out_max|None, arg|None)"""
+    L = _lib.lib()
+    n, f = x.shape
+    b = ptr.numel() - 1
+    out_sum = torch.empty(b, f, dtype=x.dtype, device=x.device) if want_sum else None
+    out_max = torch.empty(b, f, dtype=x.dtype, device=x.device) if want_max else None
+    arg = torch.empty(b, f, dtype=torch.int32, device=x.device) if want_max else None
+    ws = _ws(L.query("lgk_pool_workspace_bytes", n, b, f), x.device)
+    L.call("lgk_pool_fwd", _chk(x, None, "x"), _chk(ptr, torch.int32, "ptr"), _chk(out_sum), int(mean), _chk(out_max), _chk(arg),
+           n, b, f, ws.data_ptr(), ws.numel(), _dt(x), _stream())
+    return out_sum, out_max, arg
+
+
+def pool_bwd(dsum: Optional[Tensor], mean: bool, dmax: Optional[Tensor], arg: Optional[Tensor], ptr: Tensor,
+             num_nodes: int, feat: int, dtype, device) -> Tensor:
+    L = _lib.lib()
+    dx = torch.empty(num_nodes, feat, dtype=dtype, device=device)
+    b = ptr.numel() - 1
+    L.call("lgk_pool_bwd", _chk(dsum, dtype, "dsum"), int(mean), _chk(dmax, dtype, "dmax"), _chk(arg, torch.int32), _chk(ptr, torch.int32),
+           _chk(dx), num_nodes, b, feat, _dt(dx), _stream())
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------- linear
+
+
+def linear_fwd(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None, rowscale: Optional[Tensor] = None,
+               act: int = 0, out: Optional[Tensor] = None) -> Tensor:
+    """out = act(rowscale * x W^T + bias [+ out]);  passing `out` accumulates into it in place."""
+    L = _lib.lib()
+    n, k = x.shape
+    m = weight.size(0)
+    accumulate = out is not None
+    if out is None:
+        out = torch.empty(n, m, dtype=x.dtype, device=x.device)
+    L.call("lgk_linear_fwd", _chk(x, torch.float32, "x"), _chk(weight, torch.float32, "weight"), _chk(bias, torch.float32, "bias"),
+           _chk(rowscale, torch.float32, "rowscale"), _chk(out, torch.float32, "out"), n, k, m, int(act), int(accumulate), F32, _stream())
+    return out
+
+
+def linear_bwd_x(dy: Tensor, weight: Tensor, out: Optional[Tensor] = None) -> Tensor:
+    L = _lib.lib()
+    n, m = dy.shape
+    k = weight.size(1)
+    accumulate = out is not None
+    if out is None:
+        out = torch.empty(n, k, dtype=dy.dtype, device=dy.device)
+    L.call("lgk_linear_bwd_x", _chk(dy, torch.float32, "dy"), _chk(weight, torch.float32, "weight"), _chk(out, torch.float32),
+           n, k, m, int(accumulate), F32, _stream())
+    return out
+
+
+def linear_bwd_w(dy: Tensor, x: Optional[Tensor], want_dw: bool = True, want_db: bool = False):
+    """-> (dW [M,K] | None, db [M] | None)"""
+    L = _lib.lib()
+    n, m = dy.shape
+    k = x.size(1) if x is not None else 1
+    dev = dy.device
+    dw = torch.empty(m, k, dtype=torch.float32, device=dev) if want_dw else None
+    db = torch.empty(m, dtype=torch.float32, device=dev) if want_db else None
+    ws = _ws(L.query("lgk_linear_bwd_w_workspace_bytes", n, k, m), dev)
+    L.call("lgk_linear_bwd_w", _chk(dy, torch.float32, "dy"), _chk(x, torch.float32, "x") if want_dw else None, _chk(dw), _chk(db),
+           n, k, m, 0, ws.data_ptr(), ws.numel(), F32, _stream())
+    return dw, db
+
+
+def colsum(dy: Tensor) -> Tensor:
+    return linear_bwd_w(dy, None, want_dw=False, want_db=True)[1]
+
+
+# -------------------------------------------------------------------------------------------- elementwise
+
+
+def elu_fwd(x: Tensor) -> Tensor:
+    L = _lib.lib()
+    y = torch.empty_like(x)
+    L.call("lgk_elu_fwd", _chk(x, None, "x"), _chk(y), x.numel(), _dt(x), _stream())
+    return y
+
+
+def elu_bwd(y: Tensor, dy: Tensor) -> Tensor:
+    L = _lib.lib()
+    dx = torch.empty_like(y)
+    L.call("lgk_elu_bwd", _chk(y, None, "y"), _chk(dy, y.dtype, "dy"), _chk(dx), y.numel(), _dt(y), _stream())
+    return dx
+
+
+def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, *, lr: float, betas=(0.9, 0.999),
+              eps: float = 1e-8, weight_decay: float = 0.0, step: int = 1, step_dev: Optional[Tensor] = None,
+              grad_scale: float = 1.0, adamw: bool = False) -> None:
+    L = _lib.lib()
+    f32 = torch.float32
+    L.call("lgk_adam_step", _chk(param, f32, "param"), _chk(grad, f32, "grad"), _chk(exp_avg, f32), _chk(exp_avg_sq, f32),
+           param.numel(), float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
+           _chk(step_dev, torch.int64, "step_dev"), float(grad_scale), int(adamw), _stream())

@@ -1,0 +1,162 @@
+"""The training step of reference models/base.py:196-201 (+ optimiser, base.py:162-170) on the lgk layers, with
+the three things that make it fast on one B200 and scale over eight:
+
+  FlatAdam      parameters, gradients and Adam moments live in four flat fp32 buffers; module parameters are
+                views, backward accumulates straight into the flat gradient bucket, and one lgk_adam_step
+                kernel updates everything (Adam / AdamW, base.py:162-170)
+  GraphedStep   H2D copy of the batch + CSR/CSC build + forward + loss + backward (+ optimiser) captured once
+                per batch shape into a CUDA graph and replayed: the small-batch configs are launch-bound
+  data parallel one NCCL all-reduce over the single flat gradient bucket per step
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as TF
+from torch import Tensor
+
+from . import ops
+from .data import HostBatch
+from .graph import CSRGraph
+from .nn.pool import Segments
+
+_ALIGN = 32  # floats: every parameter starts on a 128-byte boundary inside the flat buffers
+
+
+class FlatAdam:
+    def __init__(self, module: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, adamw: bool = False):
+        params = [p for p in module.parameters() if p.requires_grad]
+        if not params:
+            raise ValueError("no trainable parameters")
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("FlatAdam needs the module on a CUDA device")
+        offs, total = [], 0
+        for p in params:
+            if p.dtype != torch.float32:
+                raise TypeError("master parameters must be float32")
+            offs.append(total)
+            total += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.param = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.grad = torch.zeros_like(self.param)
+        self.exp_avg = torch.zeros_like(self.param)
+        self.exp_avg_sq = torch.zeros_like(self.param)
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.params, self.offsets = params, offs
+        for p, o in zip(params, offs):
+            self.param[o:o + p.numel()].view_as(p).copy_(p.data)
+            p.data = self.param[o:o + p.numel()].view_as(p)
+            p.grad = self.grad[o:o + p.numel()].view_as(p)
+        self.lr, self.betas, self.eps, self.weight_decay, self.adamw = lr, betas, eps, weight_decay, adamw
+        self.numel = total
+
+    def zero_grad(self) -> None:
+        self.grad.zero_()
+        for p, o in zip(self.params, self.offsets):  # keep .grad bound to the bucket
+            if p.grad is None or p.grad.data_ptr() != self.grad.data_ptr() + 4 * o:
+                p.grad = self.grad[o:o + p.numel()].view_as(p)
+
+    def step(self, grad_scale: float = 1.0) -> None:
+        """one fused kernel; the step counter lives on the device so the call can be graph-captured"""
+        self.step_dev.add_(1)
+        ops.adam_step(self.param, self.grad, self.exp_avg, self.exp_avg_sq, lr=self.lr, betas=self.betas, eps=self.eps,
+                      weight_decay=self.weight_decay, step=0, step_dev=self.step_dev, grad_scale=grad_scale,
+                      adamw=self.adamw)
+
+
+def loss_fn(logits: Tensor, y: Tensor, loss_type: str = "MSE", num_classes: int = 5) -> Tensor:
+    """reference models/base.py:88-96,196-199 and the regression clamp of models/gat.py:94-95"""
+    if loss_type == "MSE":
+        return TF.mse_loss(torch.clamp(logits.squeeze(1), min=0, max=num_classes - 1), y.float())
+    if loss_type == "SmoothL1":
+        return TF.smooth_l1_loss(torch.clamp(logits.squeeze(1), min=0, max=num_classes - 1), y.float())
+    if loss_type == "CE":
+        return TF.cross_entropy(logits, y)
+    raise ValueError(loss_type)
+
+
+class DeviceBatch:
+    """static device buffers for one batch shape (what a captured CUDA graph reads)"""
+
+    def __init__(self, hb: HostBatch, device):
+        self.num_graphs, self.num_nodes = hb.num_graphs, hb.num_nodes
+        self.x = torch.empty_like(hb.x, device=device)
+        self.batch = torch.empty_like(hb.batch, device=device)
+        self.y = torch.empty_like(hb.y, device=device)
+        self.edge_index = torch.empty_like(hb.edge_index, device=device)
+        self.edge_weight = torch.empty_like(hb.edge_weight, device=device) if hb.edge_weight is not None else None
+
+    def copy_from(self, hb: HostBatch) -> None:
+        self.x.copy_(hb.x, non_blocking=True)
+        self.batch.copy_(hb.batch, non_blocking=True)
+        self.y.copy_(hb.y, non_blocking=True)
+        self.edge_index.copy_(hb.edge_index, non_blocking=True)
+        if self.edge_weight is not None:
+            self.edge_weight.copy_(hb.edge_weight, non_blocking=True)
+
+
+def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_classes: int,
+                     takes_edge_weight: bool = False) -> Tensor:
+    """CSR/CSC build + segment pointer + forward + loss + backward for the batch resident in `db`"""
+    graph = CSRGraph.from_edge_index(db.edge_index, db.num_nodes, db.edge_weight)
+    seg = Segments.from_batch(db.batch, db.num_graphs)
+    logits = model(db.x, graph, seg)
+    loss = loss_fn(logits, db.y, loss_type, num_classes)
+    loss.backward()
+    return loss.detach()
+
+
+class TrainStep:
+    """One optimisation step over a resident DeviceBatch; optionally CUDA-graph captured.
+
+    world_size > 1: fwd+bwd (graph) -> one NCCL all-reduce of the flat gradient bucket -> fused Adam with
+    grad_scale = 1/world_size.
+    """
+
+    def __init__(self, model: nn.Module, opt: FlatAdam, loss_type: str = "MSE", num_classes: int = 5,
+                 use_cuda_graph: bool = True, process_group=None, world_size: int = 1):
+        self.model, self.opt = model, opt
+        self.loss_type, self.num_classes = loss_type, num_classes
+        self.use_cuda_graph = use_cuda_graph
+        self.pg, self.world_size = process_group, world_size
+        self._graphs = {}
+
+    def _body(self, db: DeviceBatch) -> Tensor:
+        self.opt.zero_grad()
+        loss = forward_backward(self.model, db, self.loss_type, self.num_classes)
+        if self.world_size == 1:
+            self.opt.step()
+        return loss
+
+    def _finish_dp(self) -> None:
+        if self.world_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self.opt.grad, op=dist.ReduceOp.SUM, group=self.pg)
+            self.opt.step(grad_scale=1.0 / self.world_size)
+
+    def __call__(self, db: DeviceBatch) -> Tensor:
+        if not self.use_cuda_graph:
+            loss = self._body(db)
+            self._finish_dp()
+            return loss
+        entry = self._graphs.get(id(db))
+        if entry is None:
+            # warm up on a side stream (autograd and the allocator must have seen the shapes), then capture
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(2):
+                    self._body(db)
+                    self._finish_dp()
+            torch.cuda.current_stream().wait_stream(s)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                loss = self._body(db)
+            entry = (g, loss, db)
+            self._graphs[id(db)] = entry
+        entry[0].replay()
+        self._finish_dp()
+        return entry[1]
