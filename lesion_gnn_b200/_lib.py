@@ -73,15 +73,23 @@ class _Lib:
             fn.restype = restype
             fn.argtypes = argtypes
         self._dll.lgk_last_error.restype = ctypes.c_char_p
+        # optional observer hook(phase, name, args) around every call: bench.py uses it to bracket each entry
+        # point with CUDA events for the per-kernel roofline; None in normal operation
+        self.hook = None
 
     def last_error(self) -> str:
         return self._dll.lgk_last_error().decode()
 
     def call(self, name: str, *args):
         """Call a status-returning entry point; raise RuntimeError(lgk_last_error()) on failure."""
+        hook = self.hook
+        if hook is not None:
+            hook("begin", name, args)
         rc = getattr(self._dll, name)(*args)
         if rc != 0:
             raise RuntimeError(f"{name} failed ({rc}): {self.last_error()}")
+        if hook is not None:
+            hook("end", name, args)
 
     def query(self, name: str, *args):
         """Call a value-returning entry point (workspace sizes, counters)."""

@@ -25,15 +25,16 @@ from .nn.pool import Segments
 _ALIGN = 32  # floats: every parameter starts on a 128-byte boundary inside the flat buffers
 
 
-class FlatAdam:
-    def __init__(self, module: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0, adamw: bool = False):
+class FlatParams:
+    """Parameters and gradients of a module in two flat fp32 buffers (any device): module parameters become
+    views, backward accumulates straight into the gradient bucket, and the data-parallel all-reduce is ONE
+    collective over `grad`."""
+
+    def __init__(self, module: nn.Module):
         params = [p for p in module.parameters() if p.requires_grad]
         if not params:
             raise ValueError("no trainable parameters")
         dev = params[0].device
-        if dev.type != "cuda":
-            raise RuntimeError("FlatAdam needs the module on a CUDA device")
         offs, total = [], 0
         for p in params:
             if p.dtype != torch.float32:
@@ -42,15 +43,11 @@ class FlatAdam:
             total += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
         self.param = torch.zeros(total, dtype=torch.float32, device=dev)
         self.grad = torch.zeros_like(self.param)
-        self.exp_avg = torch.zeros_like(self.param)
-        self.exp_avg_sq = torch.zeros_like(self.param)
-        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
         self.params, self.offsets = params, offs
         for p, o in zip(params, offs):
             self.param[o:o + p.numel()].view_as(p).copy_(p.data)
             p.data = self.param[o:o + p.numel()].view_as(p)
             p.grad = self.grad[o:o + p.numel()].view_as(p)
-        self.lr, self.betas, self.eps, self.weight_decay, self.adamw = lr, betas, eps, weight_decay, adamw
         self.numel = total
 
     def zero_grad(self) -> None:
@@ -58,6 +55,33 @@ class FlatAdam:
         for p, o in zip(self.params, self.offsets):  # keep .grad bound to the bucket
             if p.grad is None or p.grad.data_ptr() != self.grad.data_ptr() + 4 * o:
                 p.grad = self.grad[o:o + p.numel()].view_as(p)
+
+    def all_reduce(self, group=None) -> None:
+        """sum the gradient bucket over the data-parallel group (NCCL on GPUs, gloo in the CPU tests)"""
+        import torch.distributed as dist
+        dist.all_reduce(self.grad, op=dist.ReduceOp.SUM, group=group)
+
+
+def dp_loss_weight(local_graphs: int, global_graphs: int, world_size: int) -> float:
+    """Weight of a rank's mean loss such that (sum over ranks of weighted gradients) / world_size equals the
+    gradient of the mean loss over the WHOLE batch, even when ranks hold different numbers of graphs (shards are
+    balanced by node count, data.shard_counts)."""
+    return float(local_graphs) * world_size / float(global_graphs)
+
+
+class FlatAdam(FlatParams):
+    """torch.optim.Adam / AdamW (reference models/base.py:162-170) as one lgk_adam_step launch over the flat
+    buffers.  CUDA only."""
+
+    def __init__(self, module: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, adamw: bool = False):
+        super().__init__(module)
+        if self.param.device.type != "cuda":
+            raise RuntimeError("FlatAdam needs the module on a CUDA device: lesion_gnn_b200 has no CPU path")
+        self.exp_avg = torch.zeros_like(self.param)
+        self.exp_avg_sq = torch.zeros_like(self.param)
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=self.param.device)
+        self.lr, self.betas, self.eps, self.weight_decay, self.adamw = lr, betas, eps, weight_decay, adamw
 
     def step(self, grad_scale: float = 1.0) -> None:
         """one fused kernel; the step counter lives on the device so the call can be graph-captured"""
@@ -83,6 +107,7 @@ class DeviceBatch:
 
     def __init__(self, hb: HostBatch, device):
         self.num_graphs, self.num_nodes = hb.num_graphs, hb.num_nodes
+        self.loss_weight = 1.0  # dp_loss_weight(...) under data parallelism
         self.x = torch.empty_like(hb.x, device=device)
         self.batch = torch.empty_like(hb.batch, device=device)
         self.y = torch.empty_like(hb.y, device=device)
@@ -98,14 +123,13 @@ class DeviceBatch:
             self.edge_weight.copy_(hb.edge_weight, non_blocking=True)
 
 
-def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_classes: int,
-                     takes_edge_weight: bool = False) -> Tensor:
+def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_classes: int) -> Tensor:
     """CSR/CSC build + segment pointer + forward + loss + backward for the batch resident in `db`"""
     graph = CSRGraph.from_edge_index(db.edge_index, db.num_nodes, db.edge_weight)
     seg = Segments.from_batch(db.batch, db.num_graphs)
     logits = model(db.x, graph, seg)
     loss = loss_fn(logits, db.y, loss_type, num_classes)
-    loss.backward()
+    (loss * db.loss_weight if db.loss_weight != 1.0 else loss).backward()
     return loss.detach()
 
 
@@ -133,8 +157,7 @@ class TrainStep:
 
     def _finish_dp(self) -> None:
         if self.world_size > 1:
-            import torch.distributed as dist
-            dist.all_reduce(self.opt.grad, op=dist.ReduceOp.SUM, group=self.pg)
+            self.opt.all_reduce(self.pg)
             self.opt.step(grad_scale=1.0 / self.world_size)
 
     def __call__(self, db: DeviceBatch) -> Tensor:

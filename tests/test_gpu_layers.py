@@ -1,0 +1,251 @@
+"""GPU parity of the drop-in layers (PyG signatures) against the fp64 oracle and the committed golden vectors:
+transform kernels, GATConv (fused edge softmax), GCNConv, GINConv, SAGEConv, GraphConv."""
+import os
+
+import pytest
+import torch
+
+from oracle import pyg_semantics as O
+from tests.util import TOL_F32, assert_close, random_graph
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "layers.pt")
+
+
+def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what=""):
+    """same weights, same inputs; compares output, dx and every parameter gradient"""
+    layer_gpu.load_state_dict({k: v.float() for k, v in layer_ref.state_dict().items()})
+    layer_gpu = layer_gpu.to(dev)
+    xr = x.clone().requires_grad_(True)
+    want = layer_ref(xr, *args_ref)
+    gen = torch.Generator().manual_seed(17)
+    dy = torch.randn(want.shape, generator=gen, dtype=torch.float64)
+    want.backward(dy)
+    xg = x.float().to(dev).requires_grad_(True)
+    args_gpu = [a.to(dev) if a.dtype == torch.int64 else a.float().to(dev) for a in args_ref]
+    got = layer_gpu(xg, *args_gpu)
+    got.backward(dy.float().to(dev))
+    assert_close(got, want, tol, what + " out")
+    assert_close(xg.grad, xr.grad, tol, what + " dx")
+    ref_grads = {k: p.grad for k, p in layer_ref.named_parameters()}
+    for k, p in layer_gpu.named_parameters():
+        if ref_grads[k] is not None:
+            assert p.grad is not None, k
+            assert_close(p.grad.view_as(ref_grads[k]), ref_grads[k], tol, f"{what} d{k}")
+
+
+@pytest.mark.parametrize("n,k,m", [(1, 1, 1), (7, 3, 5), (300, 16, 64), (1000, 64, 64), (513, 1025, 64), (2000, 128, 128),
+                                   (4096, 64, 5), (100, 64, 1), (129, 20, 130)])
+def test_linear_fwd_bwd(dev, n, k, m):
+    from lesion_gnn_b200.nn import functional as F
+    gen = torch.Generator().manual_seed(n + k + m)
+    x = torch.randn(n, k, generator=gen, dtype=torch.float64)
+    w = torch.randn(m, k, generator=gen, dtype=torch.float64) / k ** 0.5
+    b = torch.randn(m, generator=gen, dtype=torch.float64)
+    dy = torch.randn(n, m, generator=gen, dtype=torch.float64)
+    xr, wr, br = (t.clone().requires_grad_(True) for t in (x, w, b))
+    want = torch.nn.functional.elu(torch.nn.functional.linear(xr, wr, br))
+    want.backward(dy)
+    xg, wg, bg = (t.float().to(dev).requires_grad_(True) for t in (x, w, b))
+    got = F.linear(xg, wg, bg, act=1)
+    got.backward(dy.float().to(dev))
+    assert_close(got, want, TOL_F32, "linear out")
+    assert_close(xg.grad, xr.grad, TOL_F32, "linear dx")
+    assert_close(wg.grad, wr.grad, TOL_F32, "linear dW")
+    assert_close(bg.grad, br.grad, TOL_F32, "linear db")
+
+
+def test_linear_two_operand_form(dev):
+    from lesion_gnn_b200.nn import functional as F
+    gen = torch.Generator().manual_seed(0)
+    x, x2 = (torch.randn(700, 48, generator=gen, dtype=torch.float64) for _ in range(2))
+    w, w2 = (torch.randn(32, 48, generator=gen, dtype=torch.float64) for _ in range(2))
+    b = torch.randn(32, generator=gen, dtype=torch.float64)
+    ts = [t.clone().requires_grad_(True) for t in (x, w, b, x2, w2)]
+    want = ts[0] @ ts[1].t() + ts[2] + ts[3] @ ts[4].t()
+    want.backward(torch.ones_like(want))
+    tg = [t.float().to(dev).requires_grad_(True) for t in (x, w, b, x2, w2)]
+    got = F.linear(tg[0], tg[1], tg[2], x2=tg[3], weight2=tg[4])
+    got.backward(torch.ones_like(got))
+    assert_close(got, want, TOL_F32)
+    for a, r in zip(tg, ts):
+        assert_close(a.grad, r.grad, TOL_F32)
+
+
+@pytest.mark.parametrize("heads,chan", [(1, 4), (2, 64), (4, 16), (4, 32), (8, 8), (3, 20), (1, 260)])
+@pytest.mark.parametrize("add_self_loops", [True, False])
+def test_gatconv(dev, heads, chan, add_self_loops):
+    import lesion_gnn_b200 as lg
+    n, fin = 257, 24
+    ei = random_graph(n, 1800, heads * chan)
+    ei = ei[:, ei[1] != 11]  # node 11: no in-edges (only its added self loop, or nothing at all)
+    gen = torch.Generator().manual_seed(1)
+    x = torch.randn(n, fin, generator=gen, dtype=torch.float64)
+    torch.manual_seed(2)
+    ref = O.GATConv(fin, chan, heads=heads, add_self_loops=add_self_loops).double()
+    ref.bias.data.normal_()
+    _run(lg.nn.GATConv(fin, chan, heads=heads, add_self_loops=add_self_loops), ref, x, [ei], dev,
+         what=f"GAT H={heads} C={chan} loops={add_self_loops}")
+
+
+def test_gatconv_mean_heads(dev):
+    import lesion_gnn_b200 as lg
+    ei = random_graph(100, 600, 0)
+    x = torch.randn(100, 12, dtype=torch.float64)
+    torch.manual_seed(0)
+    ref = O.GATConv(12, 8, heads=3, concat=False).double()
+    _run(lg.nn.GATConv(12, 8, heads=3, concat=False), ref, x, [ei], dev, what="GAT concat=False")
+
+
+def test_gatconv_large_logits_are_stable(dev):
+    """online softmax must survive logits of +-80 (exp overflow territory without the running max)"""
+    import lesion_gnn_b200 as lg
+    ei = random_graph(64, 700, 4)
+    x = torch.randn(64, 8, dtype=torch.float64) * 30
+    torch.manual_seed(1)
+    ref = O.GATConv(8, 4, heads=2).double()
+    ref.att_src.data.mul_(5)
+    ref.att_dst.data.mul_(5)
+    _run(lg.nn.GATConv(8, 4, heads=2), ref, x, [ei], dev, tol=5e-5, what="GAT large logits")
+
+
+def test_gat_attention_dropout_is_consistent_and_unbiased(dev):
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200.nn import functional as F
+    n, H, C = 2000, 2, 8
+    ei = random_graph(n, 30000, 3)
+    g = lg.CSRGraph.from_edge_index(ei.to(dev), n)
+    h = torch.randn(n, H * C, device=dev)
+    att = torch.randn(1, H, C, device=dev)
+    base = F.gat_attention(h, att, att, None, g, H, C)
+    acc = torch.zeros_like(base)
+    reps = 200
+    for s in range(reps):
+        acc += F.gat_attention(h, att, att, None, g, H, C, dropout_p=0.35, seed=1000 + s)
+    # E[dropout(alpha)] = alpha
+    assert float((acc / reps - base).abs().mean() / base.abs().mean()) < 0.05
+    a = F.gat_attention(h, att, att, None, g, H, C, dropout_p=0.35, seed=5)
+    b = F.gat_attention(h, att, att, None, g, H, C, dropout_p=0.35, seed=5)
+    assert torch.equal(a, b) and not torch.equal(a, base)
+    # backward uses the same mask as forward: finite-difference check of d<out, r>/dh along a random direction
+    hd = h.double()
+    r = torch.randn_like(base)
+    hh = h.clone().requires_grad_(True)
+    F.gat_attention(hh, att, att, None, g, H, C, dropout_p=0.35, seed=5).mul(r).sum().backward()
+    d = torch.randn_like(h)
+    eps = 1e-2
+    fp = F.gat_attention((hd + eps * d).float(), att, att, None, g, H, C, dropout_p=0.35, seed=5).double().mul(r).sum()
+    fm = F.gat_attention((hd - eps * d).float(), att, att, None, g, H, C, dropout_p=0.35, seed=5).double().mul(r).sum()
+    fd = float((fp - fm) / (2 * eps))
+    an = float((hh.grad.double() * d).sum())
+    assert abs(fd - an) <= 2e-2 * max(abs(fd), abs(an), 1.0), (fd, an)
+
+
+@pytest.mark.parametrize("fin,fout", [(16, 64), (64, 64), (128, 128), (7, 5)])
+@pytest.mark.parametrize("weighted", [False, True])
+def test_gcnconv(dev, fin, fout, weighted):
+    import lesion_gnn_b200 as lg
+    n = 400
+    ei = torch.cat([random_graph(n, 3000, fin), torch.tensor([[5, 5, 8], [5, 5, 8]])], 1)
+    gen = torch.Generator().manual_seed(fin)
+    x = torch.randn(n, fin, generator=gen, dtype=torch.float64)
+    args = [ei] + ([torch.rand(ei.size(1), generator=gen, dtype=torch.float64) + 0.1] if weighted else [])
+    torch.manual_seed(3)
+    ref = O.GCNConv(fin, fout).double()
+    ref.bias.data.normal_()
+    _run(lg.nn.GCNConv(fin, fout), ref, x, args, dev, what=f"GCN {fin}->{fout} w={weighted}")
+
+
+@pytest.mark.parametrize("opts", [dict(add_self_loops=False), dict(normalize=False), dict(improved=True), dict(bias=False)])
+def test_gcnconv_options(dev, opts):
+    import lesion_gnn_b200 as lg
+    ei = random_graph(150, 900, 2)
+    x = torch.randn(150, 12, dtype=torch.float64)
+    torch.manual_seed(4)
+    ref = O.GCNConv(12, 8, **opts).double()
+    _run(lg.nn.GCNConv(12, 8, **opts), ref, x, [ei], dev, what=f"GCN {opts}")
+
+
+@pytest.mark.parametrize("aggr", ["mean", "max", "sum"])
+def test_sageconv(dev, aggr):
+    import lesion_gnn_b200 as lg
+    ei = random_graph(500, 4000, 6)
+    x = torch.randn(500, 64, dtype=torch.float64)
+    torch.manual_seed(5)
+    ref = O.SAGEConv(64, 48, aggr=aggr).double()
+    _run(lg.nn.SAGEConv(64, 48, aggr=aggr), ref, x, [ei], dev, what=f"SAGE {aggr}")
+
+
+@pytest.mark.parametrize("weighted", [False, True])
+def test_graphconv(dev, weighted):
+    import lesion_gnn_b200 as lg
+    ei = random_graph(300, 2500, 7)
+    gen = torch.Generator().manual_seed(7)
+    x = torch.randn(300, 110, generator=gen, dtype=torch.float64)
+    args = [ei] + ([torch.rand(ei.size(1), generator=gen, dtype=torch.float64)] if weighted else [])
+    torch.manual_seed(6)
+    _run(lg.nn.GraphConv(110, 1), O.GraphConv(110, 1).double(), x, args, dev, what="GraphConv 110->1")
+    _run(lg.nn.GraphConv(110, 110), O.GraphConv(110, 110).double(), x, args, dev, what="GraphConv 110->110")
+
+
+@pytest.mark.parametrize("norm", [None, "batch_norm"])
+def test_ginconv(dev, norm):
+    import lesion_gnn_b200 as lg
+    ei = random_graph(600, 5000, 8)
+    x = torch.randn(600, 64, dtype=torch.float64)
+    torch.manual_seed(7)
+    ref = O.GINConv(O.MLP([64, 64, 64], act="ELU", dropout=0.0, norm=norm)).double()
+    got = lg.nn.GINConv(lg.nn.MLP([64, 64, 64], act="ELU", dropout=0.0, norm=norm))
+    _run(got, ref, x, [ei], dev, tol=2e-5 if norm else TOL_F32, what=f"GIN norm={norm}")
+
+
+def test_state_dict_keys_match_pyg_names():
+    import lesion_gnn_b200 as lg
+    assert set(lg.nn.GATConv(8, 4, heads=2).state_dict()) == {"att_src", "att_dst", "bias", "lin.weight"}
+    assert set(lg.nn.GCNConv(8, 4).state_dict()) == {"bias", "lin.weight"}
+    assert set(lg.nn.SAGEConv(8, 4).state_dict()) == {"lin_l.weight", "lin_l.bias", "lin_r.weight"}
+    assert set(lg.nn.GraphConv(8, 4).state_dict()) == {"lin_rel.weight", "lin_rel.bias", "lin_root.weight"}
+    gin = lg.nn.GINConv(lg.nn.MLP([8, 4, 4]))
+    assert {"eps", "nn.lins.0.weight", "nn.lins.1.bias", "nn.norms.0.module.running_mean"} <= set(gin.state_dict())
+
+
+def test_golden_vectors(dev):
+    """committed fixtures (tests/golden/make_golden.py): two-node, star with stored + duplicate edges, path with
+    an isolated node over two graphs, mixed-size kNN batch incl. a single-node graph"""
+    import lesion_gnn_b200 as lg
+    gold = torch.load(GOLD)
+    makers = {
+        "gcn": (lambda: lg.nn.GCNConv(16, 8), False), "gcn_w": (lambda: lg.nn.GCNConv(16, 8), True),
+        "gat": (lambda: lg.nn.GATConv(16, 4, heads=2), False),
+        "gin": (lambda: lg.nn.GINConv(lg.nn.MLP([16, 8, 8], norm=None)), False),
+        "sage_mean": (lambda: lg.nn.SAGEConv(16, 8, aggr="mean"), False),
+        "sage_max": (lambda: lg.nn.SAGEConv(16, 8, aggr="max"), False),
+        "graphconv_w": (lambda: lg.nn.GraphConv(16, 8), True),
+    }
+    for name, case in gold["cases"].items():
+        ei, n, x = case["edge_index"].to(dev), case["num_nodes"], case["x"]
+        g = lg.CSRGraph.from_edge_index(ei, n)
+        for key in ("rowptr", "col", "perm", "colptr", "row", "csr2csc"):
+            assert torch.equal(getattr(g, key).cpu().long(), case["csr"][key]), (name, key)
+        for lname, (make, weighted) in makers.items():
+            rec = case[lname]
+            layer = make()
+            layer.load_state_dict({k: v.float() for k, v in rec["state"].items()})
+            layer = layer.to(dev)
+            xg = x.float().to(dev).requires_grad_(True)
+            args = [ei] + ([case["edge_weight"].float().to(dev)] if weighted else [])
+            out = layer(xg, *args)
+            out.backward(rec["dy"].float().to(dev))
+            assert_close(out, rec["out"], TOL_F32, f"{name}/{lname} out")
+            assert_close(xg.grad, rec["dx"], TOL_F32, f"{name}/{lname} dx")
+            for k, p in layer.named_parameters():
+                if k in rec["dparams"]:
+                    assert_close(p.grad.view_as(rec["dparams"][k]), rec["dparams"][k], TOL_F32, f"{name}/{lname} d{k}")
+        B = int(case["batch"].max()) + 1
+        for red, fn in (("mean", lg.nn.global_mean_pool), ("max", lg.nn.global_max_pool), ("sum", lg.nn.global_add_pool)):
+            rec = case["pool_" + red]
+            xg = x.float().to(dev).requires_grad_(True)
+            out = fn(xg, case["batch"].to(dev), B)
+            out.backward(rec["dy"].float().to(dev))
+            assert_close(out, rec["out"], TOL_F32, f"{name}/pool_{red}")
+            assert_close(xg.grad, rec["dx"], TOL_F32, f"{name}/pool_{red} dx")

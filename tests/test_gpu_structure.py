@@ -1,0 +1,119 @@
+"""GPU parity, integer work (bit-exact bar): CSR/CSC builder, graph segment pointer, kNN graph, through the
+C ABI against the oracle."""
+import pytest
+import torch
+
+from oracle import pyg_semantics as O
+from tests.util import random_graph
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_csr(ei, n, dev):
+    from lesion_gnn_b200 import ops
+    rowptr, col, perm, colptr, row, csr2csc = ops.csr_build(ei.to(dev), n, with_csc=True)
+    r_rowptr, r_col, r_perm = O.to_csr(ei, n)
+    r_colptr, r_row, r_c2c = O.to_csc(r_rowptr, r_col, n)
+    for got, want, name in ((rowptr, r_rowptr, "rowptr"), (col, r_col, "col"), (perm, r_perm, "perm"),
+                            (colptr, r_colptr, "colptr"), (row, r_row, "row"), (csr2csc, r_c2c, "csr2csc")):
+        assert got.dtype == torch.int32
+        assert torch.equal(got.cpu().long(), want), name
+
+
+@pytest.mark.parametrize("n,e,seed", [(1, 1, 0), (2, 2, 1), (50, 400, 2), (1000, 8000, 3), (3200, 25600, 4),
+                                      (5000, 100, 5), (20000, 200000, 6)])
+def test_csr_random_multigraphs(dev, n, e, seed):
+    _check_csr(random_graph(n, e, seed), n, dev)
+
+
+def test_csr_empty_and_edgeless(dev):
+    _check_csr(torch.zeros(2, 0, dtype=torch.long), 7, dev)
+    _check_csr(torch.zeros(2, 0, dtype=torch.long), 0, dev)
+
+
+def test_csr_big_rows(dev):
+    """rows beyond the rank-by-counting limit (64), the shared-memory bitonic limit (4096) and with duplicates"""
+    g = torch.Generator().manual_seed(0)
+    n = 9000
+    parts = [torch.stack([torch.randint(0, n, (100,), generator=g), torch.full((100,), 3)]),       # 100 -> node 3
+             torch.stack([torch.randint(0, n, (3000,), generator=g), torch.full((3000,), 17)]),    # 3000 -> node 17
+             torch.stack([torch.randint(0, n, (6000,), generator=g), torch.full((6000,), 8999)]),  # 6000 -> last node
+             torch.stack([torch.full((5000,), 42), torch.randint(0, n, (5000,), generator=g)]),    # hub as source
+             random_graph(n, 20000, 1)]
+    ei = torch.cat(parts, dim=1)
+    ei = ei[:, torch.randperm(ei.size(1), generator=g)].contiguous()
+    _check_csr(ei, n, dev)
+
+
+def test_csr_knn_config1(dev):
+    from tests.util import knn_batch
+    hb = knn_batch(32, 100, 16, 8, seed=1234)
+    assert hb.edge_index.size(1) == 25600
+    _check_csr(hb.edge_index, hb.num_nodes, dev)
+
+
+def test_csr_without_csc(dev):
+    from lesion_gnn_b200 import ops
+    ei = random_graph(100, 700, 9)
+    rowptr, col, perm, colptr, row, c2c = ops.csr_build(ei.to(dev), 100, with_csc=False)
+    assert colptr is None and torch.equal(col.cpu().long(), O.to_csr(ei, 100)[1])
+
+
+def test_csr_is_deterministic(dev):
+    from lesion_gnn_b200 import ops
+    ei = random_graph(4000, 60000, 12).to(dev)
+    a = ops.csr_build(ei, 4000)
+    for _ in range(3):
+        b = ops.csr_build(ei, 4000)
+        assert all(torch.equal(x, y) for x, y in zip(a, b))
+
+
+@pytest.mark.parametrize("counts", [[3, 0, 5, 1], [0, 0, 4], [7], [1] * 50, [2, 3, 0, 0]])
+def test_batch_ptr_with_empty_graphs(dev, counts):
+    from lesion_gnn_b200 import ops
+    batch = torch.repeat_interleave(torch.arange(len(counts)), torch.tensor(counts))
+    ptr = ops.batch_ptr(batch.to(dev), len(counts))
+    assert ptr.cpu().long().tolist() == O.batch_to_ptr(batch, len(counts)).tolist()
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("loop", [True, False])
+@pytest.mark.parametrize("k", [1, 6, 8, 16, 33])
+def test_knn_graph_bit_exact(dev, dtype, loop, k):
+    from lesion_gnn_b200 import transforms
+    g = torch.Generator().manual_seed(k)
+    counts = [100, 1, 2, 7, 300, 45, 600]
+    pos = (torch.rand(sum(counts), 2, generator=g, dtype=torch.float64) * 1536).to(dtype)
+    batch = torch.repeat_interleave(torch.arange(len(counts)), torch.tensor(counts))
+    want = O.knn_graph(pos, k, batch, loop=loop)
+    got = transforms.knn_graph(pos.to(dev), k, batch.to(dev), loop=loop)
+    assert got.dtype == torch.int64 and torch.equal(got.cpu(), want)
+    got2 = transforms.knn_graph(pos.to(dev), k, batch.to(dev), loop=loop,
+                                num_edges=transforms.knn_num_edges(counts, k, loop))
+    assert torch.equal(got2.cpu(), want)
+
+
+def test_knn_single_graph_and_ties(dev):
+    from lesion_gnn_b200 import transforms
+    # a regular grid has many exact distance ties: lower index must win, as in the oracle's stable sort
+    xs, ys = torch.meshgrid(torch.arange(6.0), torch.arange(6.0), indexing="ij")
+    pos = torch.stack([xs.flatten(), ys.flatten()], 1).double()
+    want = O.knn_graph(pos, 5, None, loop=False)
+    got = transforms.knn_graph(pos.to(dev), 5, None, loop=False)
+    assert torch.equal(got.cpu(), want)
+
+
+def test_gaussian_distance(dev):
+    from lesion_gnn_b200 import transforms
+    g = torch.Generator().manual_seed(3)
+    pos = torch.rand(200, 2, generator=g, dtype=torch.float64) * 20
+    ei = random_graph(200, 1500, 3)
+    for sigma in (0.5, 1.0, 7.0):
+        got = transforms.GaussianDistance(sigma)(pos.to(dev), ei.to(dev))
+        want = O.gaussian_distance(ei, pos, sigma)
+        assert torch.allclose(got.cpu(), want, rtol=1e-6, atol=1e-30)
+    # the reference's own known answers (/root/reference/test/test_transforms.py:20,29,38)
+    p2 = torch.tensor([[0.0, 0.0], [1.0, 0.0]], device=dev)
+    e2 = torch.tensor([[0, 1], [1, 0]], device=dev)
+    for sigma, want in ((1.0, 0.2420), (0.5, 0.1080), (2.0, 0.1760)):
+        assert torch.allclose(transforms.GaussianDistance(sigma)(p2, e2).cpu(), torch.full((2,), want), rtol=1e-3, atol=1e-3)
