@@ -22,7 +22,6 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -42,8 +41,8 @@ L2_BYTES = 126 * 1024 * 1024
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=60)
-    ap.add_argument("--warmup", type=int, default=6)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-extras", action="store_true", help="skip the aggregation stress and cpu_baseline legs")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
@@ -81,44 +80,52 @@ def make_host_batches(rank: int, count: int, with_edges_on=None):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)"""
+    """SM clock and throttle reasons sampled DURING the timed region through NVML (the same counters as the
+    nvidia-smi clocks line of B200_PROFILING.md, polled every 5 ms so that sub-second runs still get samples)."""
 
-    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    REASONS = (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+               ("hw_power_brake", 0x80))
 
     def __init__(self, index: int):
-        self.index, self.rows, self.proc = index, [], None
+        self.sm, self.bits, self.smax, self.err = [], 0, None, None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:  # noqa: BLE001
+            self.nv, self.err = None, repr(e)
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception as e:  # noqa: BLE001
+                self.err = repr(e)
+                return
+            time.sleep(0.005)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except OSError:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
 
     def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        sm, smax, reasons = [], None, set()
-        for r in self.rows:
-            try:
-                sm.append(float(r[1]))
-                smax = float(r[2])
-            except (ValueError, IndexError):
-                continue
-            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
-                if len(r) > col and r[col].lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join(timeout=1.0)
+        sm = sorted(self.sm)
+        out = {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.smax,
+               "reasons": [n for n, b in self.REASONS if self.bits & b], "samples": len(sm)}
+        if self.err:
+            out["error"] = self.err
+        return out
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -193,7 +200,12 @@ class KernelTimer:
 
 
 def _shape_tag(name: str, a: dict) -> str:
-    keys = [k for k in ("n", "k", "m", "n_rows", "feat", "num_nodes", "heads", "chan", "num_graphs", "num_edges") if k in a]
+    # row counts (n, N, E) vary from batch to batch of the pool: group launches by the per-row shape only
+    keys = [k for k in ("k", "m", "feat", "heads", "chan", "reduce") if k in a]
+    if name == "lgk_linear_bwd_w" and not a.get("dw"):
+        keys = ["m"]  # bias-gradient column sum only
+    if name in ("lgk_linear_fwd", "lgk_linear_bwd_x", "lgk_linear_bwd_w") and a["n"] <= GRAPHS_PER_GPU:
+        keys.append("n")  # per-graph (out_proj) products
     return ",".join(f"{k}={a[k]}" for k in keys)
 
 
@@ -263,17 +275,40 @@ def run_b200(args):
     ms_total = float(ms)
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- e2e: host buffers -> device inside the timed region, loss read back ---------------------------------
-    for i in range(3):
-        devb[i % POOL].copy_from(host[i % POOL])
-        float(step(devb[i % POOL]))
+    # ---- e2e: host buffers -> device inside the timed region, loss read back every step -----------------------
+    # Double buffered: while step i computes, the pinned-host -> device copy of step i+1's inputs runs on a copy
+    # stream; every step's inputs are copied inside the timed region and every step's loss is read on the host.
+    copy_stream = torch.cuda.Stream()
+    ready = [torch.cuda.Event() for _ in range(POOL)]
+    consumed = [torch.cuda.Event() for _ in range(POOL)]
+
+    def prefetch(i):
+        s = i % POOL
+        copy_stream.wait_event(consumed[s])  # the previous user of this device buffer has finished
+        with torch.cuda.stream(copy_stream):
+            devb[s].copy_from(host[s])
+            ready[s].record(copy_stream)
+
+    def e2e_steps(count):
+        main = torch.cuda.current_stream()
+        for s in range(POOL):
+            consumed[s].record(main)
+        prefetch(0)
+        loss = 0.0
+        for i in range(count):
+            if i + 1 < count:
+                prefetch(i + 1)
+            main.wait_event(ready[i % POOL])
+            out_dev = step(devb[i % POOL])
+            consumed[i % POOL].record(main)
+            loss = float(out_dev)  # device->host read of this step's loss (synchronises the host with the step)
+        return loss
+
+    e2e_steps(POOL)
     barrier()
     t0 = time.perf_counter()
     e0.record()
-    for i in range(args.steps):
-        db, hb = devb[i % POOL], host[i % POOL]
-        db.copy_from(hb)
-        loss_host = float(step(db))  # device->host read of the step's loss (synchronises)
+    loss_host = e2e_steps(args.steps)
     e1.record()
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
@@ -296,7 +331,9 @@ def run_b200(args):
     for r in range(reps):
         for i in range(POOL):
             timer.num_edges = host[i].edge_index.size(1)
-            eager(devb[i])
+            torch.cuda._sleep(20_000_000)  # ~10 ms of GPU idle spin: the host runs ahead, so the events bracket
+            eager(devb[i])                 # back-to-back device execution instead of Python launch gaps
+            torch.cuda.synchronize()
     L.hook = None
     agg = timer.summary()
     kern_total = sum(d["ms"] for d in agg.values())

@@ -80,9 +80,12 @@ class GCNConv(nn.Module):
         h = self.lin(x)
         if not self.normalize:
             return F.aggregate(h, g, "sum", use_value=g.value is not None, bias=self.bias)
-        dinv, selfw = g.gcn_norm(self.improved, self.add_self_loops)
+        # PyG 2.5.1's gcn_norm adds the remaining self loops BEFORE it defaults edge_weight to ones, so without
+        # edge weights the added loops weigh 1 even when improved=True (fill_value=2 only reaches weighted graphs)
+        improved = self.improved and g.value is not None
+        dinv, selfw = g.gcn_norm(improved, self.add_self_loops)
         return F.aggregate(h, g, "sum", use_value=g.value is not None, pre=dinv, post=dinv, selfw=selfw,
-                           self_fill=2.0 if self.improved else 1.0,
+                           self_fill=2.0 if improved else 1.0,
                            self_mode=SELF_REPLACE if self.add_self_loops else SELF_NONE, bias=self.bias)
 
 

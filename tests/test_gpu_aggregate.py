@@ -32,7 +32,7 @@ def test_aggregate_fwd_bwd(dev, reduce, feat):
     xg = x.float().to(dev).requires_grad_(True)
     got = F.aggregate(xg, _graph(ei, n, dev), reduce)
     got.backward(dy.float().to(dev))
-    assert float(got[7].abs().max()) == 0.0
+    assert float(got[7].detach().abs().max()) == 0.0
     assert_close(got, want, TOL_F32, f"{reduce} fwd F={feat}")
     assert_close(xg.grad, xr.grad, TOL_F32, f"{reduce} bwd F={feat}")
 
@@ -67,10 +67,11 @@ def test_gcn_norm_matches_oracle(dev, weighted, improved):
     gen = torch.Generator().manual_seed(6)
     ew = (torch.rand(ei.size(1), generator=gen, dtype=torch.float64) + 0.1) if weighted else None
     g = _graph(ei, n, dev, None if ew is None else ew.float())
-    dinv, selfw = g.gcn_norm(improved, True)
+    # (PyG quirk restated by the oracle: fill_value=2 of improved=True only reaches graphs WITH edge weights)
+    fill = 2.0 if (improved and weighted) else 1.0
+    dinv, selfw = g.gcn_norm(fill == 2.0, True)
     ei2, w2 = O.gcn_norm(ei, ew, n, improved, True, torch.float64)
     # recover deg^-1/2 from the oracle: weight of the loop edge (i,i) = dinv_i^2 * selfw_i
-    fill = 2.0 if improved else 1.0
     loop_w = torch.full((n,), fill, dtype=torch.float64)
     if ew is not None:
         for e in range(ei.size(1)):
