@@ -114,9 +114,13 @@ __global__ void __launch_bounds__(128) knn_kernel(const P* __restrict__ pos, int
     if (dist < best_d[K - 1]) {
       P cd = dist;
       int cidx = c;
+      bool placed = false;
 #pragma unroll
       for (int t = 0; t < K; ++t) {
-        const bool sw = cd < best_d[t];  // strict: an equal, earlier (lower-index) entry stays in front
+        // strict <: an equal, earlier (lower-index) entry stays in front; once the candidate is placed the
+        // displaced entries shift down unconditionally (a tie between two of THEM must not drop one)
+        const bool sw = placed || cd < best_d[t];
+        placed = sw;
         const P td = best_d[t];
         const int ti = best_i[t];
         best_d[t] = sw ? cd : td;

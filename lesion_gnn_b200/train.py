@@ -168,6 +168,11 @@ class TrainStep:
         entry = self._graphs.get(id(db))
         if entry is None:
             # warm up on a side stream (autograd and the allocator must have seen the shapes), then capture
+            # -- the warm-up runs must not train: optimiser state, parameters and module buffers (BatchNorm
+            # running statistics) are restored afterwards
+            opt = self.opt
+            saved = [t.clone() for t in (opt.param, opt.exp_avg, opt.exp_avg_sq, opt.step_dev)]
+            bufs = [(b, b.clone()) for b in self.model.buffers()]
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):
@@ -175,6 +180,10 @@ class TrainStep:
                     self._body(db)
                     self._finish_dp()
             torch.cuda.current_stream().wait_stream(s)
+            for dst, src in zip((opt.param, opt.exp_avg, opt.exp_avg_sq, opt.step_dev), saved):
+                dst.copy_(src)
+            for b, src in bufs:
+                b.copy_(src)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 loss = self._body(db)

@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden", "layers.pt")
 
 
-def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what=""):
+def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what="", tol_grad=None):
     """same weights, same inputs; compares output, dx and every parameter gradient"""
     layer_gpu.load_state_dict({k: v.float() for k, v in layer_ref.state_dict().items()})
     layer_gpu = layer_gpu.to(dev)
@@ -26,12 +26,17 @@ def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what=""):
     got = layer_gpu(xg, *args_gpu)
     got.backward(dy.float().to(dev))
     assert_close(got, want, tol, what + " out")
-    assert_close(xg.grad, xr.grad, tol, what + " dx")
+    assert_close(xg.grad, xr.grad, tol_grad or tol, what + " dx")
     ref_grads = {k: p.grad for k, p in layer_ref.named_parameters()}
+    scale = max(float(g.abs().max()) for g in ref_grads.values() if g is not None)
     for k, p in layer_gpu.named_parameters():
         if ref_grads[k] is not None:
             assert p.grad is not None, k
-            assert_close(p.grad.view_as(ref_grads[k]), ref_grads[k], tol, f"{what} d{k}")
+            if float(ref_grads[k].abs().max()) < 1e-9 * scale:
+                # analytically zero gradient (a bias in front of BatchNorm): only rounding noise on either side
+                assert float(p.grad.abs().max()) < 1e-4 * scale, k
+                continue
+            assert_close(p.grad.view_as(ref_grads[k]), ref_grads[k], tol_grad or tol, f"{what} d{k}")
 
 
 @pytest.mark.parametrize("n,k,m", [(1, 1, 1), (7, 3, 5), (300, 16, 64), (1000, 64, 64), (513, 1025, 64), (2000, 128, 128),
@@ -98,7 +103,10 @@ def test_gatconv_mean_heads(dev):
 
 
 def test_gatconv_large_logits_are_stable(dev):
-    """online softmax must survive logits of +-80 (exp overflow territory without the running max)"""
+    """online softmax must survive logits of +-80 (exp overflow territory without the running max).  With
+    near-one-hot attention the gradients are differences of nearly equal terms, so fp32 itself (the oracle run in
+    fp32 included) is only good to ~1e-3 there: forward keeps the 1e-5 bar, backward gets the fp32 oracle's own
+    error (x4) as its bar."""
     import lesion_gnn_b200 as lg
     ei = random_graph(64, 700, 4)
     x = torch.randn(64, 8, dtype=torch.float64) * 30
@@ -106,7 +114,17 @@ def test_gatconv_large_logits_are_stable(dev):
     ref = O.GATConv(8, 4, heads=2).double()
     ref.att_src.data.mul_(5)
     ref.att_dst.data.mul_(5)
-    _run(lg.nn.GATConv(8, 4, heads=2), ref, x, [ei], dev, tol=5e-5, what="GAT large logits")
+    ref32 = O.GATConv(8, 4, heads=2)
+    ref32.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    gen = torch.Generator().manual_seed(17)
+    dy = torch.randn(64, 8, generator=gen, dtype=torch.float64)
+    x64, x32 = x.clone().requires_grad_(True), x.float().requires_grad_(True)
+    ref(x64, ei).backward(dy)
+    ref32(x32, ei).backward(dy.float())
+    from tests.util import rel_err
+    fp32_err = max([rel_err(x32.grad, x64.grad)] + [rel_err(a.grad, b.grad) for a, b in zip(ref32.parameters(), ref.parameters())])
+    ref.zero_grad()
+    _run(lg.nn.GATConv(8, 4, heads=2), ref, x, [ei], dev, tol=TOL_F32, tol_grad=max(4 * fp32_err, TOL_F32), what="GAT large logits")
 
 
 def test_gat_attention_dropout_is_consistent_and_unbiased(dev):
