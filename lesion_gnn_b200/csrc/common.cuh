@@ -67,6 +67,29 @@ __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
 __device__ __forceinline__ float4 ld_gather_f4(const float4* p) { return __ldg(p); }
 __device__ __forceinline__ uint2 ld_gather_u2(const uint2* p) { return __ldg(p); }
 
+// predicated gathers: the load is issued only when `on` (no L1 wavefront otherwise) and the result is 0 when off.
+// Written as volatile asm so that ptxas keeps a run of them back to back (independent loads in flight together)
+// instead of sinking each one next to its consumer.
+__device__ __forceinline__ float4 ld_gather_f4_pred(const float4* p, bool on) {
+  float4 v;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+      "mov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\tmov.f32 %2, 0f00000000;\n\tmov.f32 %3, 0f00000000;\n\t"
+      "@p ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];\n\t}"
+      : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+      : "l"(p), "r"(int(on)));
+  return v;
+}
+__device__ __forceinline__ uint2 ld_gather_u2_pred(const uint2* p, bool on) {
+  uint2 v;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\tmov.b32 %0, 0;\n\tmov.b32 %1, 0;\n\t"
+      "@p ld.global.nc.v2.u32 {%0,%1}, [%2];\n\t}"
+      : "=r"(v.x), "=r"(v.y)
+      : "l"(p), "r"(int(on)));
+  return v;
+}
+
 // streaming stores (written once, consumed by a later kernel): evict-first
 __device__ __forceinline__ void st_stream_f4(float4* p, float4 v) { __stcs(p, v); }
 __device__ __forceinline__ void st_stream_u2(uint2* p, uint2 v) { __stcs(p, v); }
@@ -95,6 +118,9 @@ struct Vec4<float> {
   static __device__ __forceinline__ float4 gather(const float* base, int64_t elem) {
     return ld_gather_f4(reinterpret_cast<const float4*>(base + elem));
   }
+  static __device__ __forceinline__ float4 gather_if(const float* base, int64_t elem, bool on) {
+    return ld_gather_f4_pred(reinterpret_cast<const float4*>(base + elem), on);
+  }
   static __device__ __forceinline__ float4 stream(const float* base, int64_t elem) {
     return ld_stream_f4(reinterpret_cast<const float4*>(base + elem));
   }
@@ -108,6 +134,9 @@ template <>
 struct Vec4<__nv_bfloat16> {
   static __device__ __forceinline__ float4 gather(const __nv_bfloat16* base, int64_t elem) {
     return bf16x4_to_f4(ld_gather_u2(reinterpret_cast<const uint2*>(base + elem)));
+  }
+  static __device__ __forceinline__ float4 gather_if(const __nv_bfloat16* base, int64_t elem, bool on) {
+    return bf16x4_to_f4(ld_gather_u2_pred(reinterpret_cast<const uint2*>(base + elem), on));
   }
   static __device__ __forceinline__ float4 stream(const __nv_bfloat16* base, int64_t elem) {
     return bf16x4_to_f4(ld_gather_u2(reinterpret_cast<const uint2*>(base + elem)));

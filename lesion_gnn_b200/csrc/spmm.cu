@@ -1,16 +1,26 @@
 // (2)+(4) fused gather + segment-reduce aggregation (SpMM) over a CSR (forward) or CSC (backward).
 //
 // Replaces index_select + mul + scatter(sum|mean|max) of MessagePassing.propagate (reference gin.py:31,
-// drgnet.py:55) and torch_sparse.matmul on the adj_t path.  HBM/L2-bound: no tensor cores.
+// drgnet.py:55) and torch_sparse.matmul on the adj_t path.  No tensor cores: 0.25 flop per gathered byte.
 //
-// Mapping: a feature row is split into 128-bit pieces, one piece per lane; a row needs LPR lanes
-// (F/4 rounded up to a power of two, at most 32) so a warp reduces 32/LPR rows at once ("warp per row" for
-// F >= 128, sub-warp groups below).  Each group loads LPR neighbour indices (+ weights) of its row with ONE
-// coalesced streaming load, then broadcasts them with warp shuffles while every lane gathers its 16-byte
-// piece of the neighbour's row through the read-only, L1-allocating path.  Branch-free inner loop (skipped
-// entries become weight-0 reads of the own row) so that the unrolled gathers are all in flight together.
+// What bounds it (profiles/microbench/gather_bw.cu, measured on the B200): an SM pulls a gathered 512-byte row
+// into registers in 4.2 cycles when it hits L1 (122 B/clk, the LSU data path = the shared-memory crossbar), 7.4
+// cycles from L2 and 21 cycles from HBM.  With d neighbours per row the kernel moves d x F x 4 bytes through that
+// path against 2 x F x 4 compulsory HBM bytes, so from d ~ 4 upwards the L1/L2 gather path, not HBM, is the
+// ceiling; everything below is arranged to (a) keep the gathers L1 hits and (b) spend no other LSU or issue
+// slots per edge.
+//
+// Mapping: a feature row is split into 128-bit pieces, one per lane; a row needs LPR lanes (F/4 rounded up to a
+// power of two, at most 32; wider rows are cut into feature slices = grid.y), a warp reduces 32/LPR rows at
+// once.  grid.x = bands of consecutive rows; a CTA walks its band in chunks of R rows.  Per chunk the CTA first
+// stages the chunk's row pointers, neighbour ids and (if any) fully resolved edge weights
+// ew[emap[p]] * pre[idx[p]] in shared memory with coalesced, CTA-wide loads -- so the dependent
+// pointer -> index -> weight -> row chain of a CSR walk costs one latency per chunk instead of one per row -- and
+// then every group reduces its rows reading ids/weights as 16-byte shared-memory broadcasts (1/4 wavefront per
+// edge) and gathering 8 neighbour rows at a time (8 independent 16-byte loads in flight per lane).
 #include "common.cuh"
 #include <float.h>
+#include <stdlib.h>
 
 namespace lgk {
 namespace {
@@ -31,103 +41,184 @@ struct SpmmArgs {
   int self_mode;
   int64_t n_rows;
   int feat;
+  int slice4;    // float4 columns per feature slice (grid.y slices)
+  int64_t band;  // consecutive rows per CTA (grid.x bands)
 };
 
-template <int LPR>
-__device__ __forceinline__ unsigned group_mask() {
-  if constexpr (LPR == 32) {
-    return 0xffffffffu;
-  } else {
-    unsigned lane = threadIdx.x & 31;
-    return ((1u << LPR) - 1u) << (lane & ~(LPR - 1));
-  }
+// ---- vectorised path: feat % 4 == 0 ------------------------------------------------------------------
+constexpr int kStageCap = 5120;  // edges staged per chunk (ids 20 KB + weights 20 KB of shared memory)
+constexpr int kRowsPerGroup = 2; // rows a group reduces per chunk
+
+__device__ __forceinline__ int4 load_idx4(const int* __restrict__ idx, int q, int n_idx) {
+  if (q + 4 <= n_idx) return __ldg(reinterpret_cast<const int4*>(idx + q));
+  int4 r = make_int4(0, 0, 0, 0);
+  if (q + 0 < n_idx) r.x = __ldg(idx + q + 0);
+  if (q + 1 < n_idx) r.y = __ldg(idx + q + 1);
+  if (q + 2 < n_idx) r.z = __ldg(idx + q + 2);
+  return r;
 }
 
-// ---- vectorised path: feat % 4 == 0 ------------------------------------------------------------------
-template <typename T, int LPR, int VPL, int REDUCE>
-__global__ void __launch_bounds__(kThreads) spmm_vec_kernel(SpmmArgs a, const T* __restrict__ x, T* __restrict__ out) {
-  constexpr int RPW = 32 / LPR;
-  const int gl = threadIdx.x & (LPR - 1);  // lane inside the group
-  const int64_t row = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * RPW + ((threadIdx.x & 31) / LPR);
-  if (row >= a.n_rows) return;
-  const unsigned mask = group_mask<LPR>();
-  const int F = a.feat, F4 = F >> 2;
-  const int start = a.ptr[row], end = a.ptr[row + 1];
+__device__ __forceinline__ float edge_weight(const SpmmArgs& a, int p, int j) {
+  float w = 1.f;
+  if (a.ew) w = __ldg(a.ew + (a.emap ? __ldg(a.emap + p) : p));
+  if (a.pre) w *= __ldg(a.pre + j);
+  return w;
+}
 
-  float4 acc[VPL];
-  int4 arg[VPL];
-#pragma unroll
-  for (int v = 0; v < VPL; ++v) {
-    acc[v] = (REDUCE == LGK_MAX) ? make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX) : f4_zero();
-    arg[v] = make_int4(-1, -1, -1, -1);
-  }
+template <typename T, int LPR, int REDUCE, bool WEIGHTED>
+__global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* __restrict__ x, T* __restrict__ out) {
+  extern __shared__ __align__(16) int smem[];
+  const int groups = blockDim.x / LPR;
+  const int R = groups * kRowsPerGroup;
+  int* s_ptr = smem;                                 // [R + 1]
+  int* s_j = smem + ((R + 1 + 3) & ~3);              // [kStageCap + 8], s_j[t] = idx[base + t], base % 4 == 0
+  float* s_w = reinterpret_cast<float*>(s_j + kStageCap + 8);
 
-  for (int base = start; base < end; base += LPR) {
-    const int p = base + gl;
-    int my_j = int(row);
-    float my_w = 0.f;
-    if (p < end) {
-      int j = ld_stream_i32(a.idx + p);
-      float w = 1.f;
-      if (a.ew) w = __ldg(a.ew + (a.emap ? ld_stream_i32(a.emap + p) : p));
-      if (a.pre) w *= __ldg(a.pre + j);
-      if (a.self_mode == LGK_SELF_REPLACE && j == int(row)) w = 0.f;  // stored loop: dropped
-      my_j = j;
-      my_w = w;
+  const int gl = threadIdx.x & (LPR - 1);
+  const int grp = threadIdx.x / LPR;
+  const int vec = blockIdx.y * a.slice4 + gl;  // this lane's float4 column
+  const unsigned F4 = unsigned(a.feat) >> 2;
+  const bool lane_on = gl < a.slice4 && vec < int(F4);
+  // rows are addressed in float4 units with 32-bit offsets (n_rows * F4 < 2^32 is checked by the launcher)
+  const T* xv = x + vec * 4;
+  T* ov = out + vec * 4;
+  const int64_t band_end = min(a.n_rows, (int64_t(blockIdx.x) + 1) * a.band);
+  const int skip_self = (WEIGHTED && a.self_mode == LGK_SELF_REPLACE) ? 1 : 0;
+
+  for (int64_t r0 = int64_t(blockIdx.x) * a.band; r0 < band_end; r0 += R) {
+    const int nrows = (band_end - r0 < R) ? int(band_end - r0) : R;
+    __syncthreads();  // the previous chunk's readers are done with the staging buffers
+    for (int t = threadIdx.x; t <= nrows; t += blockDim.x) s_ptr[t] = __ldg(a.ptr + r0 + t);
+    __syncthreads();
+    const int e0 = s_ptr[0], e1 = s_ptr[nrows];
+    const int base = e0 & ~3;
+    const bool staged = (e1 - base) <= kStageCap;
+    if (staged) {
+      for (int t = threadIdx.x + (e0 - base); t < e1 - base; t += blockDim.x) {
+        const int j = ld_stream_i32(a.idx + base + t);
+        s_j[t] = j;
+        if (WEIGHTED) s_w[t] = edge_weight(a, base + t, j);
+      }
+      __syncthreads();
     }
-    const int cnt = min(LPR, end - base);
-#pragma unroll 4
-    for (int u = 0; u < cnt; ++u) {
-      const int j = __shfl_sync(mask, my_j, u, LPR);
-      const float w = __shfl_sync(mask, my_w, u, LPR);
-      const T* xr = x + int64_t(j) * F;
+    if (!lane_on) continue;
+
+    for (int lr = grp; lr < nrows; lr += groups) {
+      const int64_t row = r0 + lr;
+      const int start = s_ptr[lr], end = s_ptr[lr + 1];
+      const int self_j = skip_self ? int(row) : -1;
+      float4 acc = (REDUCE == LGK_MAX) ? make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX) : f4_zero();
+      int4 arg = make_int4(-1, -1, -1, -1);
+
+      for (int q = start & ~3; q < end; q += 8) {
+        int j[8];
+        float w[8];
+        float4 v[8];
+        // ids (and weights) of two aligned quads
+        {
+          int4 ja, jb = make_int4(0, 0, 0, 0);
+          float4 wa = make_float4(1.f, 1.f, 1.f, 1.f), wb = wa;
+          const bool second = q + 4 < end;
+          if (staged) {
+            ja = *reinterpret_cast<const int4*>(s_j + (q - base));
+            if (second) jb = *reinterpret_cast<const int4*>(s_j + (q - base) + 4);
+            if (WEIGHTED) {
+              wa = *reinterpret_cast<const float4*>(s_w + (q - base));
+              if (second) wb = *reinterpret_cast<const float4*>(s_w + (q - base) + 4);
+            }
+          } else {  // chunk with more than kStageCap edges (very high degrees): read through L1 instead
+            ja = load_idx4(a.idx, q, e1);
+            if (second) jb = load_idx4(a.idx, q + 4, e1);
+            if (WEIGHTED) {
+              const int jj[8] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w};
+              float ww[8];
 #pragma unroll
-      for (int v = 0; v < VPL; ++v) {
-        const int vec = gl + v * LPR;
-        if (vec < F4) {
-          float4 val = Vec4<T>::gather(xr, vec * 4);
-          if (REDUCE == LGK_MAX) {
-            const int slot = base + u;
-            if (val.x > acc[v].x) { acc[v].x = val.x; arg[v].x = slot; }
-            if (val.y > acc[v].y) { acc[v].y = val.y; arg[v].y = slot; }
-            if (val.z > acc[v].z) { acc[v].z = val.z; arg[v].z = slot; }
-            if (val.w > acc[v].w) { acc[v].w = val.w; arg[v].w = slot; }
-          } else {
-            f4_fma(acc[v], w, val);
+              for (int c = 0; c < 8; ++c) ww[c] = (q + c >= start && q + c < end) ? edge_weight(a, q + c, jj[c]) : 0.f;
+              wa = make_float4(ww[0], ww[1], ww[2], ww[3]);
+              wb = make_float4(ww[4], ww[5], ww[6], ww[7]);
+            }
+          }
+          j[0] = ja.x; j[1] = ja.y; j[2] = ja.z; j[3] = ja.w; j[4] = jb.x; j[5] = jb.y; j[6] = jb.z; j[7] = jb.w;
+          w[0] = wa.x; w[1] = wa.y; w[2] = wa.z; w[3] = wa.w; w[4] = wb.x; w[5] = wb.y; w[6] = wb.z; w[7] = wb.w;
+        }
+        const bool full = (q >= start) && (q + 8 <= end);
+        bool ok[8];
+        if (full) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            ok[c] = true;
+            v[c] = Vec4<T>::gather(xv + size_t(unsigned(j[c]) * F4) * 4, 0);
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            ok[c] = (q + c >= start) && (q + c < end);
+            v[c] = Vec4<T>::gather_if(xv + size_t(unsigned(ok[c] ? j[c] : 0) * F4) * 4, 0, ok[c]);
           }
         }
-      }
-    }
-  }
-
-  float scale = 1.f;
-  if (REDUCE == LGK_MEAN) scale = 1.f / float(max(end - start, 1));
-  if (a.post) scale *= __ldg(a.post + row);
-  float wself = 0.f;
-  if (REDUCE != LGK_MAX && a.self_mode != LGK_SELF_NONE) {
-    wself = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
-    if (a.pre) wself *= __ldg(a.pre + row);
-  }
+        if (REDUCE == LGK_MAX) {
 #pragma unroll
-  for (int v = 0; v < VPL; ++v) {
-    const int vec = gl + v * LPR;
-    if (vec < F4) {
-      float4 r = acc[v];
+          for (int c = 0; c < 8; ++c) {
+            if (ok[c]) {
+              const int slot = q + c;
+              if (v[c].x > acc.x) { acc.x = v[c].x; arg.x = slot; }
+              if (v[c].y > acc.y) { acc.y = v[c].y; arg.y = slot; }
+              if (v[c].z > acc.z) { acc.z = v[c].z; arg.z = slot; }
+              if (v[c].w > acc.w) { acc.w = v[c].w; arg.w = slot; }
+            }
+          }
+        } else {
+          // pairwise tree over the step: every gather is needed before the chain into acc can finish, which
+          // keeps the eight loads in flight together; predicated-off gathers are exact zeros
+          if (WEIGHTED) {
+            // first tree level as multiply + FMA: v[c] = w[c] v[c] + w[c+1] v[c+1]
+#pragma unroll
+            for (int c = 0; c < 8; c += 2) {
+              const float w0 = (!ok[c] || j[c] == self_j) ? 0.f : w[c];  // stored self loop: dropped
+              const float w1 = (!ok[c + 1] || j[c + 1] == self_j) ? 0.f : w[c + 1];
+              v[c].x = fmaf(w1, v[c + 1].x, w0 * v[c].x); v[c].y = fmaf(w1, v[c + 1].y, w0 * v[c].y);
+              v[c].z = fmaf(w1, v[c + 1].z, w0 * v[c].z); v[c].w = fmaf(w1, v[c + 1].w, w0 * v[c].w);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 8; c += 2) {
+              v[c].x += v[c + 1].x; v[c].y += v[c + 1].y; v[c].z += v[c + 1].z; v[c].w += v[c + 1].w;
+            }
+          }
+#pragma unroll
+          for (int s = 2; s < 8; s <<= 1)
+#pragma unroll
+            for (int c = 0; c < 8; c += 2 * s) {
+              v[c].x += v[c + s].x; v[c].y += v[c + s].y; v[c].z += v[c + s].z; v[c].w += v[c + s].w;
+            }
+          acc.x += v[0].x; acc.y += v[0].y; acc.z += v[0].z; acc.w += v[0].w;
+        }
+      }
+
+      float4 r = acc;
+      const size_t ro = size_t(unsigned(row) * F4) * 4;
       if (REDUCE == LGK_MAX) {
-        if (arg[v].x < 0) r.x = 0.f;
-        if (arg[v].y < 0) r.y = 0.f;
-        if (arg[v].z < 0) r.z = 0.f;
-        if (arg[v].w < 0) r.w = 0.f;
-        if (a.arg_out) st_stream_i4(reinterpret_cast<int4*>(a.arg_out + row * F + vec * 4), arg[v]);
+        if (arg.x < 0) r.x = 0.f;
+        if (arg.y < 0) r.y = 0.f;
+        if (arg.z < 0) r.z = 0.f;
+        if (arg.w < 0) r.w = 0.f;
+        if (a.arg_out) st_stream_i4(reinterpret_cast<int4*>(a.arg_out + ro + vec * 4), arg);
       } else {
-        if (a.self_mode != LGK_SELF_NONE) f4_fma(r, wself, Vec4<T>::gather(x + row * F, vec * 4));
+        float scale = 1.f;
+        if (REDUCE == LGK_MEAN) scale = 1.f / float(max(end - start, 1));
+        if (a.post) scale *= __ldg(a.post + row);
+        if (a.self_mode != LGK_SELF_NONE) {
+          float wself = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
+          if (a.pre) wself *= __ldg(a.pre + row);
+          f4_fma(r, wself, Vec4<T>::gather(xv + ro, 0));
+        }
         r.x *= scale; r.y *= scale; r.z *= scale; r.w *= scale;
       }
       if (a.bias) {
         float4 b = __ldg(reinterpret_cast<const float4*>(a.bias) + vec);
         r.x += b.x; r.y += b.y; r.z += b.z; r.w += b.w;
       }
-      Vec4<T>::store(out + row * F, vec * 4, r);
+      Vec4<T>::store(ov + ro, 0, r);
     }
   }
 }
@@ -247,33 +338,61 @@ __global__ void __launch_bounds__(256) gcn_norm_kernel(const int* __restrict__ r
   if (selfw_out) selfw_out[i] = sw;
 }
 
+// Launch geometry of the vectorised kernel.  Defaults were chosen on the B200 (profiles/README.md); the
+// environment variables exist for that tuning sweep only and are read once.
+struct SpmmTuning {
+  int threads, max_slice4, waves;
+  int64_t max_band;
+};
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+const SpmmTuning& tuning() {
+  static const SpmmTuning t = {env_int("LGK_SPMM_THREADS", 512), env_int("LGK_SPMM_SLICE4", 32), env_int("LGK_SPMM_WAVES", 8),
+                               int64_t(env_int("LGK_SPMM_MAX_BAND", 1 << 20))};
+  return t;
+}
+
 template <typename T, int REDUCE>
-int launch_spmm(const SpmmArgs& a, const void* x_, void* out_, cudaStream_t stream) {
+int launch_spmm(const SpmmArgs& a_in, const void* x_, void* out_, cudaStream_t stream) {
+  SpmmArgs a = a_in;
   const T* x = static_cast<const T*>(x_);
   T* out = static_cast<T*>(out_);
   const int F = a.feat;
-  const int warps = kThreads / 32;
-  const bool aligned = ((reinterpret_cast<uintptr_t>(x_) | reinterpret_cast<uintptr_t>(out_) |
+  const bool aligned = ((reinterpret_cast<uintptr_t>(x_) | reinterpret_cast<uintptr_t>(out_) | reinterpret_cast<uintptr_t>(a.idx) |
                          reinterpret_cast<uintptr_t>(a.bias) | reinterpret_cast<uintptr_t>(a.arg_out)) & 15) == 0;
-  if (F % 4 == 0 && F <= 1024 && aligned) {
+  if (F % 4 == 0 && aligned && a.n_rows * (F / 4) < (int64_t(1) << 32)) {
+    const SpmmTuning& t = tuning();
     const int F4 = F / 4;
-#define LGK_SPMM_CASE(LPR, VPL)                                                                     \
-  {                                                                                                 \
-    const int64_t rows_per_cta = int64_t(warps) * (32 / (LPR));                                     \
-    spmm_vec_kernel<T, LPR, VPL, REDUCE><<<unsigned(ceil_div(a.n_rows, rows_per_cta)), kThreads, 0, stream>>>(a, x, out); \
-  }
-    if (F4 <= 1) LGK_SPMM_CASE(1, 1)
-    else if (F4 <= 2) LGK_SPMM_CASE(2, 1)
-    else if (F4 <= 4) LGK_SPMM_CASE(4, 1)
-    else if (F4 <= 8) LGK_SPMM_CASE(8, 1)
-    else if (F4 <= 16) LGK_SPMM_CASE(16, 1)
-    else if (F4 <= 32) LGK_SPMM_CASE(32, 1)
-    else if (F4 <= 64) LGK_SPMM_CASE(32, 2)
-    else if (F4 <= 128) LGK_SPMM_CASE(32, 4)
-    else LGK_SPMM_CASE(32, 8)
+    const int nslice = int(ceil_div(F4, min(32, max(1, t.max_slice4))));
+    a.slice4 = int(ceil_div(F4, nslice));
+    int lpr = 1;
+    while (lpr < a.slice4) lpr <<= 1;
+    // at most 64 groups per CTA (so a chunk of 128 rows stages up to kStageCap edges), fewer threads on small inputs
+    int threads = min(max(32, min(512, t.threads)) / 32 * 32, max(64, 64 * lpr));
+    while (threads > 128 && ceil_div(a.n_rows, int64_t(threads / lpr) * kRowsPerGroup) < 2 * kNumSMs) threads >>= 1;
+    const int groups = threads / lpr;
+    const int R = groups * kRowsPerGroup;
+    // bands: enough CTAs for `waves` rounds over the SMs, a whole number of chunks each
+    int64_t band = ceil_div(a.n_rows, int64_t(kNumSMs) * t.waves);
+    if (band > t.max_band) band = t.max_band;
+    band = align_up(band < R ? R : band, R);
+    a.band = band;
+    dim3 grid(unsigned(ceil_div(a.n_rows, band)), unsigned(nslice));
+    const bool weighted = REDUCE != LGK_MAX && (a.ew || a.pre || a.self_mode == LGK_SELF_REPLACE);
+    const size_t smem = 4 * (size_t((R + 1 + 3) & ~3) + (kStageCap + 8) * (weighted ? 2 : 1));
+#define LGK_SPMM_CASE(LPR)                                                                             \
+  case LPR:                                                                                            \
+    if (weighted) spmm_vec_kernel<T, LPR, REDUCE, true><<<grid, threads, smem, stream>>>(a, x, out);   \
+    else spmm_vec_kernel<T, LPR, REDUCE, false><<<grid, threads, smem, stream>>>(a, x, out);           \
+    break;
+    switch (lpr) {
+      LGK_SPMM_CASE(1) LGK_SPMM_CASE(2) LGK_SPMM_CASE(4) LGK_SPMM_CASE(8) LGK_SPMM_CASE(16) LGK_SPMM_CASE(32)
+    }
 #undef LGK_SPMM_CASE
   } else {
-    spmm_scalar_kernel<T, REDUCE><<<unsigned(ceil_div(a.n_rows, warps)), kThreads, 0, stream>>>(a, x, out);
+    spmm_scalar_kernel<T, REDUCE><<<unsigned(ceil_div(a.n_rows, kThreads / 32)), kThreads, 0, stream>>>(a, x, out);
   }
   LGK_CHECK_LAUNCH("spmm_kernel");
   return LGK_OK;
@@ -310,7 +429,7 @@ extern "C" int lgk_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* e
   LGK_REQUIRE(reduce != LGK_MAX || (!ew && !pre && !post), LGK_ERR_BAD_ARG, "lgk_spmm: max takes no weights");
   LGK_REQUIRE(dtype == LGK_F32 || dtype == LGK_BF16, LGK_ERR_BAD_ARG, "lgk_spmm: bad dtype %d", dtype);
   LGK_REQUIRE(x != out, LGK_ERR_BAD_ARG, "lgk_spmm: in-place aggregation is not possible");
-  SpmmArgs a{ptr, idx, emap, ew, pre, post, selfw, bias, arg_out, self_fill, self_mode, n_rows, int(feat)};
+  SpmmArgs a{ptr, idx, emap, ew, pre, post, selfw, bias, arg_out, self_fill, self_mode, n_rows, int(feat), 0, 0};
   return dtype == LGK_F32 ? dispatch_reduce<float>(a, reduce, x, out, stream)
                           : dispatch_reduce<__nv_bfloat16>(a, reduce, x, out, stream);
 }
