@@ -14,8 +14,21 @@
 // 128 x 64 output tile, 16-deep r tile, 256 threads, 8 x 4 micro-tile, register-prefetch double buffering.
 #include "common.cuh"
 
+#include <stdlib.h>
+
 namespace lgk {
+// tensor-core (3xTF32, tcgen05) forward transform, linear_tc.cu
+int launch_linear_tc(const float* x, const float* w, const float* bias, const float* rowscale, float* out, int64_t n,
+                     int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream);
 namespace {
+
+// Products with at least this many rows and a reduction of at least 32 go to the tensor cores; below that the
+// launch is latency-bound either way and the FFMA kernel has the cheaper prologue.  LGK_LINEAR_TC=0 forces the
+// FFMA path (A/B measurements).
+bool use_tensor_cores(int64_t n, int64_t k) {
+  static const int mode = [] { const char* v = getenv("LGK_LINEAR_TC"); return (v && *v) ? atoi(v) : 1; }();
+  return mode != 0 && n >= 512 && k >= 32;
+}
 
 constexpr int BI = 128, BJ = 64, BR = 16, PAD = 4, kThreads = 256;
 constexpr int TI = 8, TJ = 4;
@@ -247,6 +260,9 @@ extern "C" int lgk_linear_fwd(const void* x, const float* weight, const float* b
   LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_fwd: only fp32 is implemented");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(x && weight && out, LGK_ERR_BAD_ARG, "lgk_linear_fwd: null pointer");
+  if (use_tensor_cores(n, k))
+    return launch_linear_tc(static_cast<const float*>(x), weight, bias, rowscale, static_cast<float*>(out), n, k, m, act,
+                            accumulate, stream);
   GemmArgs g{};
   g.A = static_cast<const float*>(x); g.B = weight; g.C = static_cast<float*>(out);
   g.I = n; g.J = m; g.R = k; g.lda = k; g.ldb = k; g.sCi = m; g.sCj = 1;
