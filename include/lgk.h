@@ -173,10 +173,12 @@ LGK_API int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int
                     const void* dout, void* dh, float* da_src,
                     int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
                     float dropout_p, uint64_t seed, int dtype, void* stream);
-/* datt_src[h,c] = sum_n da_src[n,h] h[n,h,c]; datt_dst likewise (two-stage, deterministic) */
+/* datt_src[h,c] (+)= sum_n da_src[n,h] h[n,h,c]; datt_dst likewise (two-stage, deterministic); accumulate != 0 adds to
+ * the outputs (gradient buckets) instead of overwriting them */
 LGK_API int64_t lgk_gat_datt_workspace_bytes(int64_t num_nodes, int heads, int chan);
 LGK_API int lgk_gat_datt(const void* h, const float* da_src, const float* da_dst, float* datt_src, float* datt_dst,
-                 int64_t num_nodes, int heads, int chan, void* workspace, int64_t workspace_bytes, int dtype, void* stream);
+                 int64_t num_nodes, int heads, int chan, int accumulate, void* workspace, int64_t workspace_bytes, int dtype,
+                 void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * (3) global pooling = segment reduce over the sorted batch vector

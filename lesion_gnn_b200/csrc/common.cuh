@@ -175,5 +175,40 @@ __device__ __forceinline__ float uniform_hash(uint64_t seed, uint32_t slot, uint
   return float(uint32_t(z >> 40)) * (1.0f / 16777216.0f);
 }
 
+// Second stage of every slab reduction in the library (weight / bias / attention-vector gradients): out (+)= sum over
+// slabs of partial[slab][t], t < count_a goes to out_a, the rest to out_b.  32 outputs x 8 slab lanes per CTA: a
+// lane adds its slabs in ascending order, the 8 lane sums are combined in a fixed order -- deterministic, and the
+// ~150 partials per output are read with 8 x 4 loads in flight instead of one dependent chain.
+static __global__ void __launch_bounds__(256) slab_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out_a,
+                                                                 float* __restrict__ out_b, int64_t count_a, int64_t count_b,
+                                                                 int slabs, int accumulate) {
+  __shared__ float red[8][33];
+  const int o = threadIdx.x & 31, sl = threadIdx.x >> 5;
+  const int64_t t = int64_t(blockIdx.x) * 32 + o;
+  const int64_t stride = count_a + count_b;
+  float s0 = 0.f, s1 = 0.f;
+  if (t < stride) {
+    int k = sl;
+    for (; k + 8 < slabs; k += 16) {
+      s0 += __ldg(partial + int64_t(k) * stride + t);
+      s1 += __ldg(partial + int64_t(k + 8) * stride + t);
+    }
+    if (k < slabs) s0 += __ldg(partial + int64_t(k) * stride + t);
+  }
+  red[sl][o] = s0 + s1;
+  __syncthreads();
+  if (sl == 0 && t < stride) {
+    float s = red[0][o];
+#pragma unroll
+    for (int l = 1; l < 8; ++l) s += red[l][o];
+    float* dst = t < count_a ? (out_a ? out_a + t : nullptr) : (out_b ? out_b + (t - count_a) : nullptr);
+    if (dst) {
+      if (accumulate) s += *dst;
+      *dst = s;
+    }
+  }
+}
+static inline unsigned slab_reduce_grid(int64_t count) { return unsigned((count + 31) / 32); }
+
 #endif  // __CUDACC__
 }  // namespace lgk

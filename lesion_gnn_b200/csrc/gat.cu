@@ -338,50 +338,50 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
   if (gl == 0) a.da_out[item] = da;
 }
 
-// ---- datt = sum_n da[n,h] * h[n,h,c]: slab partials, then a deterministic second stage --------------------------
-constexpr int kDattRowsPerCta = 256;
+// ---- datt = sum_n da[n,h] * h[n,h,c]: slab partials, then a deterministic second stage ----------------------------
+// At most two CTAs per SM, each reducing a contiguous slab of nodes; threads = (row lane, float4 column) so a row is
+// read with 16-byte loads and the two weights (da_src, da_dst of the column's head) are shared by the 4 channels.
+int datt_slabs(int64_t N) {
+  int64_t g = ceil_div(N, 64);
+  if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  return int(g < 1 ? 1 : g);
+}
 template <typename T>
 __global__ void __launch_bounds__(256) gat_datt_partial_kernel(const T* __restrict__ h, const float* __restrict__ da_src,
                                                                const float* __restrict__ da_dst, float* __restrict__ partial,
-                                                               int64_t N, int H, int C) {
-  __shared__ float s_a[8][32], s_b[8][32];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int F = H * C;
-  const int f = blockIdx.y * 32 + tx;
-  const int64_t r0 = int64_t(blockIdx.x) * kDattRowsPerCta;
-  const int64_t r1 = min(N, r0 + kDattRowsPerCta);
-  float sa = 0.f, sb = 0.f;
-  if (f < F) {
-    const int head = f / C;
-    for (int64_t n = r0 + ty; n < r1; n += 8) {
-      const float hv = Vec4<T>::load1(h + n * F, f);
-      sa = fmaf(__ldg(da_src + n * H + head), hv, sa);
-      sb = fmaf(__ldg(da_dst + n * H + head), hv, sb);
+                                                               int64_t N, int H, int C, int64_t slab_rows) {
+  __shared__ float4 red_s[256], red_d[256];
+  const int F = H * C, F4 = F >> 2;
+  const int64_t r0 = int64_t(blockIdx.x) * slab_rows, r1 = min(N, r0 + slab_rows);
+  float* p = partial + int64_t(blockIdx.x) * 2 * F;
+  for (int c0 = 0; c0 < F4; c0 += 256) {
+    const int width = min(256, F4 - c0);
+    const int lanes = max(1, 256 / width);
+    const int c = threadIdx.x % width, rl = threadIdx.x / width;
+    float4 as = f4_zero(), ad = f4_zero();
+    if (rl < lanes) {
+      const int col = (c0 + c) * 4, head = col / C;
+      for (int64_t n = r0 + rl; n < r1; n += lanes) {
+        const float4 hv = Vec4<T>::stream(h + n * F, col);
+        f4_fma(as, __ldg(da_src + n * H + head), hv);
+        f4_fma(ad, __ldg(da_dst + n * H + head), hv);
+      }
+    }
+    __syncthreads();
+    red_s[threadIdx.x] = as;
+    red_d[threadIdx.x] = ad;
+    __syncthreads();
+    if (rl == 0) {
+      for (int l = 1; l < lanes; ++l) {
+        const float4 u = red_s[l * width + c], v = red_d[l * width + c];
+        as.x += u.x; as.y += u.y; as.z += u.z; as.w += u.w;
+        ad.x += v.x; ad.y += v.y; ad.z += v.z; ad.w += v.w;
+      }
+      reinterpret_cast<float4*>(p)[c0 + c] = as;
+      reinterpret_cast<float4*>(p + F)[c0 + c] = ad;
     }
   }
-  s_a[ty][tx] = sa;
-  s_b[ty][tx] = sb;
-  __syncthreads();
-  if (ty == 0 && f < F) {
-#pragma unroll
-    for (int k = 1; k < 8; ++k) { sa += s_a[k][tx]; sb += s_b[k][tx]; }
-    partial[(int64_t(blockIdx.x) * 2 + 0) * F + f] = sa;
-    partial[(int64_t(blockIdx.x) * 2 + 1) * F + f] = sb;
-  }
 }
-__global__ void __launch_bounds__(256) gat_datt_final_kernel(const float* __restrict__ partial, float* __restrict__ datt_src,
-                                                             float* __restrict__ datt_dst, int64_t nslabs, int F) {
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= F) return;
-  float sa = 0.f, sb = 0.f;
-  for (int64_t s = 0; s < nslabs; ++s) {
-    sa += partial[(s * 2 + 0) * F + f];
-    sb += partial[(s * 2 + 1) * F + f];
-  }
-  datt_src[f] = sa;
-  datt_dst[f] = sb;
-}
-
 int check_shape(const char* who, int64_t N, int H, int C) {
   LGK_REQUIRE(N >= 0 && H > 0 && C > 0, LGK_ERR_BAD_ARG, "%s: bad sizes", who);
   LGK_REQUIRE(C % 4 == 0 && C <= 1024, LGK_ERR_UNSUPPORTED, "%s: channels per head must be a multiple of 4 and <= 1024 (got %d)", who, C);
@@ -511,36 +511,41 @@ extern "C" int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const 
 
 extern "C" int64_t lgk_gat_datt_workspace_bytes(int64_t N, int H, int C) {
   if (N <= 0 || H <= 0 || C <= 0) return 0;
-  return ceil_div(N, kDattRowsPerCta) * 2 * H * C * 4;
+  return int64_t(datt_slabs(N)) * 2 * H * C * 4;
 }
 
 extern "C" int lgk_gat_datt(const void* h, const float* da_src, const float* da_dst, float* datt_src, float* datt_dst,
-                            int64_t N, int H, int C, void* workspace, int64_t workspace_bytes, int dtype, void* stream_) {
+                            int64_t N, int H, int C, int accumulate, void* workspace, int64_t workspace_bytes, int dtype,
+                            void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(N >= 0 && H > 0 && C > 0, LGK_ERR_BAD_ARG, "lgk_gat_datt: bad sizes");
   LGK_REQUIRE(datt_src && datt_dst, LGK_ERR_BAD_ARG, "lgk_gat_datt: null pointer");
   const int F = H * C;
   if (N == 0) {
-    cudaMemsetAsync(datt_src, 0, 4 * F, stream);
-    cudaMemsetAsync(datt_dst, 0, 4 * F, stream);
-    LGK_CHECK_LAUNCH("lgk_gat_datt(memset)");
+    if (!accumulate) {
+      cudaMemsetAsync(datt_src, 0, 4 * F, stream);
+      cudaMemsetAsync(datt_dst, 0, 4 * F, stream);
+      LGK_CHECK_LAUNCH("lgk_gat_datt(memset)");
+    }
     return LGK_OK;
   }
   LGK_REQUIRE(h && da_src && da_dst, LGK_ERR_BAD_ARG, "lgk_gat_datt: null pointer");
-  const int64_t nslabs = ceil_div(N, kDattRowsPerCta);
+  const int64_t nslabs = datt_slabs(N);
+  const int64_t slab_rows = ceil_div(N, nslabs);
+  LGK_REQUIRE(C % 4 == 0, LGK_ERR_UNSUPPORTED, "lgk_gat_datt: channels per head must be a multiple of 4");
   const int64_t need = nslabs * 2 * F * 4;
   LGK_REQUIRE(workspace && workspace_bytes >= need, LGK_ERR_WORKSPACE, "lgk_gat_datt: workspace %lld < %lld bytes",
               (long long)workspace_bytes, (long long)need);
   float* partial = static_cast<float*>(workspace);
-  dim3 grid(unsigned(nslabs), unsigned(ceil_div(F, 32)));
+  const unsigned grid = unsigned(nslabs);
   if (dtype == LGK_F32)
-    gat_datt_partial_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(h), da_src, da_dst, partial, N, H, C);
+    gat_datt_partial_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(h), da_src, da_dst, partial, N, H, C, slab_rows);
   else if (dtype == LGK_BF16)
-    gat_datt_partial_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(h), da_src, da_dst, partial, N, H, C);
+    gat_datt_partial_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(h), da_src, da_dst, partial, N, H, C, slab_rows);
   else
     LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_datt: bad dtype");
   LGK_CHECK_LAUNCH("gat_datt_partial_kernel");
-  gat_datt_final_kernel<<<unsigned(ceil_div(F, 256)), 256, 0, stream>>>(partial, datt_src, datt_dst, nslabs, F);
-  LGK_CHECK_LAUNCH("gat_datt_final_kernel");
+  slab_reduce_kernel<<<slab_reduce_grid(2 * F), 256, 0, stream>>>(partial, datt_src, datt_dst, F, F, int(nslabs), accumulate);
+  LGK_CHECK_LAUNCH("slab_reduce_kernel(datt)");
   return LGK_OK;
 }

@@ -208,24 +208,160 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
   out[t] = s;
 }
 
-// db[m] (+)= sum_n dy[n,m]: slab partials + final
-constexpr int kColsumRows = 512;
-__global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __restrict__ dy, float* __restrict__ partial, int64_t N, int M) {
-  __shared__ float s[8][32];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int m = blockIdx.y * 32 + tx;
-  const int64_t r0 = int64_t(blockIdx.x) * kColsumRows, r1 = min(N, r0 + kColsumRows);
-  float acc = 0.f;
-  if (m < M)
-    for (int64_t n = r0 + ty; n < r1; n += 8) acc += __ldg(dy + n * M + m);
-  s[ty][tx] = acc;
-  __syncthreads();
-  if (ty == 0 && m < M) {
+// ---- small-weight gradients: dW [m,k] and db [m] in one pass, k, m <= 128 ------------------------------------------
+// Every Linear inside the convs has a tiny weight (64 x 64) and a very tall reduction (N nodes).  One launch of at
+// most 2 CTAs per SM: a CTA reduces a contiguous slab of rows -- 32-row chunks of x and dy staged in shared memory,
+// 4 x 4 register micro-tiles per 64 x 64 output block, db as a by-product of the dy tiles already in registers --
+// and writes its partial [m*k + m] to the workspace; a second tiny launch adds the partials in slab order
+// (deterministic, no atomics).  This replaced a generic split GEMM + a separate column-sum pass that together cost
+// ~50 us per layer on the headline batch.
+constexpr int kSlabChunk = 32;
+template <int KB, int MB, bool VEC>  // 64-wide output blocks along k and m; VEC: 16-byte loads (K, M % 4 == 0, aligned)
+__global__ void __launch_bounds__(256) bwd_w_slab_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                         float* __restrict__ partial, int64_t N, int K, int M,
+                                                         int64_t slab_rows, int want_db) {
+  extern __shared__ __align__(16) float sm[];
+  const int kp = KB * 64, mp = MB * 64;
+  float* xs = sm;                       // [kSlabChunk][kp]
+  float* ds = sm + kSlabChunk * kp;     // [kSlabChunk][mp]
+  const int tk = threadIdx.x >> 4, tm = threadIdx.x & 15;  // 16 x 16 threads, 4 x 4 outputs each per block
+  const int64_t r0 = int64_t(blockIdx.x) * slab_rows;
+  const int64_t r1 = min(N, r0 + slab_rows);
+  float acc[KB][MB][4][4];
+  float dbs[MB][4];
 #pragma unroll
-    for (int k = 1; k < 8; ++k) acc += s[k][tx];
-    partial[int64_t(blockIdx.x) * M + m] = acc;
+  for (int a = 0; a < KB; ++a)
+#pragma unroll
+    for (int b = 0; b < MB; ++b)
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[a][b][i][j] = 0.f;
+#pragma unroll
+  for (int b = 0; b < MB; ++b)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dbs[b][j] = 0.f;
+
+  for (int64_t c0 = r0; c0 < r1; c0 += kSlabChunk) {
+    const int rows = (r1 - c0 < kSlabChunk) ? int(r1 - c0) : kSlabChunk;
+    __syncthreads();
+    if (VEC) {
+      for (int e = threadIdx.x; e < kSlabChunk * kp / 4; e += 256) {
+        const int r = e / (kp / 4), c = (e - r * (kp / 4)) * 4;
+        reinterpret_cast<float4*>(xs)[e] = (r < rows && c < K) ? __ldg(reinterpret_cast<const float4*>(x + (c0 + r) * K + c)) : f4_zero();
+      }
+      for (int e = threadIdx.x; e < kSlabChunk * mp / 4; e += 256) {
+        const int r = e / (mp / 4), c = (e - r * (mp / 4)) * 4;
+        reinterpret_cast<float4*>(ds)[e] = (r < rows && c < M) ? __ldg(reinterpret_cast<const float4*>(dy + (c0 + r) * M + c)) : f4_zero();
+      }
+    } else {
+      for (int e = threadIdx.x; e < kSlabChunk * kp; e += 256) {
+        const int r = e / kp, c = e - r * kp;
+        xs[e] = (r < rows && c < K) ? __ldg(x + (c0 + r) * K + c) : 0.f;
+      }
+      for (int e = threadIdx.x; e < kSlabChunk * mp; e += 256) {
+        const int r = e / mp, c = e - r * mp;
+        ds[e] = (r < rows && c < M) ? __ldg(dy + (c0 + r) * M + c) : 0.f;
+      }
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int r = 0; r < kSlabChunk; ++r) {
+      float4 a4[KB], b4[MB];
+#pragma unroll
+      for (int a = 0; a < KB; ++a) a4[a] = *reinterpret_cast<const float4*>(xs + r * kp + a * 64 + tk * 4);
+#pragma unroll
+      for (int b = 0; b < MB; ++b) b4[b] = *reinterpret_cast<const float4*>(ds + r * mp + b * 64 + tm * 4);
+#pragma unroll
+      for (int a = 0; a < KB; ++a) {
+        const float av[4] = {a4[a].x, a4[a].y, a4[a].z, a4[a].w};
+#pragma unroll
+        for (int b = 0; b < MB; ++b) {
+          const float bv[4] = {b4[b].x, b4[b].y, b4[b].z, b4[b].w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[a][b][i][j] = fmaf(av[i], bv[j], acc[a][b][i][j]);
+        }
+      }
+      if (tk == 0) {
+#pragma unroll
+        for (int b = 0; b < MB; ++b) { dbs[b][0] += b4[b].x; dbs[b][1] += b4[b].y; dbs[b][2] += b4[b].z; dbs[b][3] += b4[b].w; }
+      }
+    }
+  }
+  // partial layout = the outputs' own: dW[mi * K + ki] then db[mi]
+  float* p = partial + int64_t(blockIdx.x) * (int64_t(K) * M + M);
+#pragma unroll
+  for (int a = 0; a < KB; ++a)
+#pragma unroll
+    for (int b = 0; b < MB; ++b)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int mi = b * 64 + tm * 4 + j;
+        if (mi >= M) continue;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int ki = a * 64 + tk * 4 + i;
+          if (ki < K) p[int64_t(mi) * K + ki] = acc[a][b][i][j];
+        }
+      }
+  if (want_db && tk == 0) {
+#pragma unroll
+    for (int b = 0; b < MB; ++b)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int mi = b * 64 + tm * 4 + j;
+        if (mi < M) p[int64_t(K) * M + mi] = dbs[b][j];
+      }
   }
 }
+
+// db[m] = sum_n dy[n,m] alone (bias gradients of the fused aggregation kernels): slab partials, same second stage.
+// Threads = (row lane, float4 column); M % 4 == 0 fast path, scalar otherwise.
+__global__ void __launch_bounds__(256) colsum_slab_kernel(const float* __restrict__ dy, float* __restrict__ partial,
+                                                          int64_t N, int M, int64_t slab_rows) {
+  __shared__ float red[256 * 4];
+  const int64_t r0 = int64_t(blockIdx.x) * slab_rows, r1 = min(N, r0 + slab_rows);
+  float* p = partial + int64_t(blockIdx.x) * M;
+  const bool vec = (M & 3) == 0 && ((reinterpret_cast<uintptr_t>(dy) & 15) == 0);
+  const int cols = vec ? M / 4 : M;  // column groups
+  for (int c0 = 0; c0 < cols; c0 += 256) {
+    const int width = min(256, cols - c0);   // column groups handled in this pass
+    const int lanes = max(1, 256 / width);   // row lanes
+    const int c = threadIdx.x % width, rl = threadIdx.x / width;
+    float4 acc = f4_zero();
+    if (rl < lanes) {
+      if (vec) {
+        for (int64_t r = r0 + rl; r < r1; r += lanes) {
+          const float4 v = __ldg(reinterpret_cast<const float4*>(dy + r * M) + c0 + c);
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+      } else {
+        for (int64_t r = r0 + rl; r < r1; r += lanes) acc.x += __ldg(dy + r * M + c0 + c);
+      }
+    }
+    __syncthreads();
+    reinterpret_cast<float4*>(red)[threadIdx.x] = acc;
+    __syncthreads();
+    if (rl == 0) {
+      for (int l = 1; l < lanes; ++l) {
+        const float4 v = reinterpret_cast<const float4*>(red)[l * width + c];
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      if (vec) reinterpret_cast<float4*>(p)[c0 + c] = acc;
+      else p[c0 + c] = acc.x;
+    }
+  }
+}
+
+// slabs for a reduction over n rows: at most two CTAs per SM, at least 64 rows each
+int slab_count(int64_t n) {
+  int64_t g = ceil_div(n, 64);
+  if (g > 2 * kNumSMs) g = 2 * kNumSMs;
+  return int(g < 1 ? 1 : g);
+}
+bool small_weight(int64_t k, int64_t m) { return k <= 128 && m <= 128; }
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
@@ -288,8 +424,9 @@ extern "C" int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, i
 
 extern "C" int64_t lgk_linear_bwd_w_workspace_bytes(int64_t n, int64_t k, int64_t m) {
   if (n <= 0 || k <= 0 || m <= 0) return 0;
+  const int64_t slabs = slab_count(n);
+  if (small_weight(k, m)) return align_up(slabs * (k * m + m) * 4, 256);
   const int s = choose_wsplits(n, k, m);
-  const int64_t slabs = ceil_div(n, kColsumRows);
   return align_up(int64_t(s) * k * m * 4, 256) + align_up(slabs * m * 4, 256);
 }
 
@@ -311,32 +448,62 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
   const int64_t need = lgk_linear_bwd_w_workspace_bytes(n, k, m);
   LGK_REQUIRE(workspace && workspace_bytes >= need, LGK_ERR_WORKSPACE, "lgk_linear_bwd_w: workspace %lld < %lld bytes",
               (long long)workspace_bytes, (long long)need);
-  const int s = choose_wsplits(n, k, m);
+  const int slabs = slab_count(n);
+  const int64_t slab_rows = ceil_div(n, slabs);
+  const float* dyf = static_cast<const float*>(dy);
   float* partial = static_cast<float*>(workspace);
-  float* colpart = reinterpret_cast<float*>(static_cast<char*>(workspace) + align_up(int64_t(s) * k * m * 4, 256));
-  if (dw) {
-    GemmArgs g{};
-    g.A = static_cast<const float*>(x); g.B = static_cast<const float*>(dy);
-    g.I = k; g.J = m; g.R = n; g.lda = k; g.ldb = m; g.sCi = 1; g.sCj = k;  // C(i=k_idx, j=m_idx) -> dW[m*K + k]
-    g.r_chunk = align_up(ceil_div(n, s), BR);
+
+  if (!dw) {  // bias gradient only
+    colsum_slab_kernel<<<slabs, 256, 0, stream>>>(dyf, partial, n, int(m), slab_rows);
+    LGK_CHECK_LAUNCH("colsum_slab_kernel");
+    slab_reduce_kernel<<<slab_reduce_grid(m), 256, 0, stream>>>(partial, nullptr, db, 0, m, slabs, accumulate);
+    LGK_CHECK_LAUNCH("slab_reduce_kernel(db)");
+    return LGK_OK;
+  }
+
+  if (small_weight(k, m)) {  // dW and db in one pass over slabs of rows
+    const int kb = int(ceil_div(k, 64)), mb = int(ceil_div(m, 64));
+    const size_t smem = size_t(kSlabChunk) * (kb + mb) * 64 * sizeof(float);
+    const float* xf = static_cast<const float*>(x);
     const bool vec = (k % 4 == 0) && (m % 4 == 0) && aligned16(x) && aligned16(dy);
-    if (s == 1) {
-      g.C = dw; g.split_stride = 0; g.accumulate = accumulate;
-      if (int rc = launch_gemm<false, false>(g, 1, vec, stream, "gemm_kernel(bwd_w)")) return rc;
-    } else {
-      g.C = partial; g.split_stride = k * m;
-      if (int rc = launch_gemm<false, false>(g, s, vec, stream, "gemm_kernel(bwd_w,split)")) return rc;
-      splitk_reduce_kernel<<<unsigned(ceil_div(k * m, 256)), 256, 0, stream>>>(partial, dw, k * m, s, accumulate);
-      LGK_CHECK_LAUNCH("splitk_reduce_kernel");
-    }
+#define LGK_SLAB(KB, MB)                                                                                                       \
+  do {                                                                                                                         \
+    if (vec) bwd_w_slab_kernel<KB, MB, true><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, db != nullptr); \
+    else bwd_w_slab_kernel<KB, MB, false><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, db != nullptr);    \
+  } while (0)
+    if (kb == 1 && mb == 1) LGK_SLAB(1, 1);
+    else if (kb == 1) LGK_SLAB(1, 2);
+    else if (mb == 1) LGK_SLAB(2, 1);
+    else LGK_SLAB(2, 2);
+#undef LGK_SLAB
+    LGK_CHECK_LAUNCH("bwd_w_slab_kernel");
+    slab_reduce_kernel<<<slab_reduce_grid(k * m + m), 256, 0, stream>>>(partial, dw, db, k * m, m, slabs, accumulate);
+    LGK_CHECK_LAUNCH("slab_reduce_kernel");
+    return LGK_OK;
+  }
+
+  // wide weights (the 1025-wide in_proj): split GEMM over the rows + deterministic reduce, db from a slab pass
+  const int s = choose_wsplits(n, k, m);
+  float* colpart = reinterpret_cast<float*>(static_cast<char*>(workspace) + align_up(int64_t(s) * k * m * 4, 256));
+  GemmArgs g{};
+  g.A = static_cast<const float*>(x); g.B = dyf;
+  g.I = k; g.J = m; g.R = n; g.lda = k; g.ldb = m; g.sCi = 1; g.sCj = k;  // C(i=k_idx, j=m_idx) -> dW[m*K + k]
+  g.r_chunk = align_up(ceil_div(n, s), BR);
+  const bool vec = (k % 4 == 0) && (m % 4 == 0) && aligned16(x) && aligned16(dy);
+  if (s == 1) {
+    g.C = dw; g.split_stride = 0; g.accumulate = accumulate;
+    if (int rc = launch_gemm<false, false>(g, 1, vec, stream, "gemm_kernel(bwd_w)")) return rc;
+  } else {
+    g.C = partial; g.split_stride = k * m;
+    if (int rc = launch_gemm<false, false>(g, s, vec, stream, "gemm_kernel(bwd_w,split)")) return rc;
+    splitk_reduce_kernel<<<unsigned(ceil_div(k * m, 256)), 256, 0, stream>>>(partial, dw, k * m, s, accumulate);
+    LGK_CHECK_LAUNCH("splitk_reduce_kernel");
   }
   if (db) {
-    const int64_t slabs = ceil_div(n, kColsumRows);
-    dim3 grid(unsigned(slabs), unsigned(ceil_div(m, 32)));
-    colsum_partial_kernel<<<grid, 256, 0, stream>>>(static_cast<const float*>(dy), colpart, n, int(m));
-    LGK_CHECK_LAUNCH("colsum_partial_kernel");
-    splitk_reduce_kernel<<<unsigned(ceil_div(m, 256)), 256, 0, stream>>>(colpart, db, m, int(slabs), accumulate);
-    LGK_CHECK_LAUNCH("splitk_reduce_kernel(db)");
+    colsum_slab_kernel<<<slabs, 256, 0, stream>>>(dyf, colpart, n, int(m), slab_rows);
+    LGK_CHECK_LAUNCH("colsum_slab_kernel");
+    slab_reduce_kernel<<<slab_reduce_grid(m), 256, 0, stream>>>(colpart, nullptr, db, 0, m, slabs, accumulate);
+    LGK_CHECK_LAUNCH("slab_reduce_kernel(db)");
   }
   return LGK_OK;
 }

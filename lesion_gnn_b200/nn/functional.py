@@ -15,6 +15,35 @@ from .._lib import ACT_ELU, ACT_NONE, SELF_ADD, SELF_NONE, SELF_REPLACE  # noqa:
 from ..graph import CSRGraph
 
 
+# ---- gradients written straight into the parameters' .grad buffers --------------------------------------------
+# With train.FlatParams every parameter's .grad is a view into one flat bucket.  Autograd would materialise each
+# weight / bias / attention-vector gradient and then launch one `add` kernel per parameter to accumulate it; inside
+# `direct_param_grads()` the backward kernels instead ADD into p.grad themselves (their second reduction stage has
+# an accumulate flag) and hand autograd None for that input.  Off by default: plain autograd semantics.
+_DIRECT = [False]
+
+
+class direct_param_grads:
+    def __enter__(self):
+        self._old = _DIRECT[0]
+        _DIRECT[0] = True
+        return self
+
+    def __exit__(self, *exc):
+        _DIRECT[0] = self._old
+        return False
+
+
+def _bucket(p) -> Optional[Tensor]:
+    """p.grad when gradients may be accumulated in place: a leaf parameter whose fp32, contiguous .grad is bound"""
+    if not _DIRECT[0] or p is None or not isinstance(p, Tensor) or not p.is_leaf or not p.requires_grad:
+        return None
+    g = p.grad
+    if g is None or g.dtype != torch.float32 or not g.is_contiguous() or g.shape != p.shape:
+        return None
+    return g
+
+
 def _need_csc(g: CSRGraph):
     if g.colptr is None:
         raise RuntimeError("this CSRGraph was built without the CSC transpose index; backward needs with_csc=True")
@@ -29,6 +58,7 @@ class _Aggregate(torch.autograd.Function):
         ctx.g, ctx.reduce, ctx.ew = g, reduce, ew
         ctx.pre, ctx.post, ctx.selfw, ctx.self_fill, ctx.self_mode = pre, post, selfw, self_fill, self_mode
         ctx.has_bias = bias is not None
+        ctx.bias_ref = bias
         x = x.contiguous()
         if reduce == "max":
             out, arg = ops.spmm(g.rowptr, g.col, x, "max", bias=bias, want_arg=True)
@@ -57,7 +87,7 @@ class _Aggregate(torch.autograd.Function):
                 dx = ops.spmm(g.colptr, g.row, dout, "sum", emap=g.csr2csc if ctx.ew is not None else None, ew=ctx.ew,
                               pre=ctx.post, post=ctx.pre, selfw=ctx.selfw, self_fill=ctx.self_fill, self_mode=ctx.self_mode)
         if ctx.has_bias and ctx.needs_input_grad[1]:
-            dbias = ops.colsum(dout.float() if dout.dtype != torch.float32 else dout)
+            dbias = ops.colsum(dout.float() if dout.dtype != torch.float32 else dout, out=_bucket(ctx.bias_ref))
         return dx, dbias, None, None, None, None, None, None, None, None
 
 
@@ -85,6 +115,7 @@ class _GatAttention(torch.autograd.Function):
         ctx.g, ctx.cfg = g, (heads, chan, negative_slope, add_self_loops, dropout_p, seed)
         ctx.has_bias = bias is not None
         ctx.att_shape = att_src.shape
+        ctx.refs = (att_src, att_dst, bias)
         return out
 
     @staticmethod
@@ -94,13 +125,19 @@ class _GatAttention(torch.autograd.Function):
         g = ctx.g
         _need_csc(g)
         dout = dout.contiguous()
+        p_src, p_dst, p_bias = ctx.refs
+        g_src, g_dst = _bucket(p_src), _bucket(p_dst)
+        direct = g_src is not None and g_dst is not None
         dh, datt_src, datt_dst = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
-                                             a_s, a_d, dout, heads, chan, slope, add_self, p, seed)
+                                             a_s, a_d, dout, heads, chan, slope, add_self, p, seed,
+                                             datt_src_out=g_src.view(-1) if direct else None,
+                                             datt_dst_out=g_dst.view(-1) if direct else None)
         dbias = None
         if ctx.has_bias and ctx.needs_input_grad[3]:
-            dbias = ops.colsum(dout if dout.dtype == torch.float32 else dout.float())
-        return (dh, datt_src.view(ctx.att_shape), datt_dst.view(ctx.att_shape), dbias, None, None, None, None, None,
-                None, None)
+            dbias = ops.colsum(dout if dout.dtype == torch.float32 else dout.float(), out=_bucket(p_bias))
+        if not direct:
+            datt_src, datt_dst = datt_src.view(ctx.att_shape), datt_dst.view(ctx.att_shape)
+        return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None)
 
 
 def gat_attention(h, att_src, att_dst, bias, g, heads, chan, negative_slope=0.2, add_self_loops=True, dropout_p=0.0,
@@ -129,31 +166,45 @@ class _Linear(torch.autograd.Function):
             out = ops.linear_fwd(x, w, bias, rowscale, act)
             ctx.save_for_backward(x, w, out if act != ACT_NONE else x.new_empty(0), rowscale if rowscale is not None else x.new_empty(0))
         ctx.two, ctx.act, ctx.has_bias, ctx.has_rs = x2 is not None, act, bias is not None, rowscale is not None
+        ctx.refs = (weight, bias, weight2)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         dout = dout.contiguous()
         ni = ctx.needs_input_grad
+        p_w, p_b, p_w2 = ctx.refs
+
+        def grads_w(dy, xin, want_dw, want_db, pw, pb):
+            """dW / db, added straight into the .grad buckets when both are bound (see direct_param_grads)"""
+            if not (want_dw or want_db):
+                return None, None
+            gw, gb = (_bucket(pw) if want_dw else None), (_bucket(pb) if want_db else None)
+            if (not want_dw or gw is not None) and (not want_db or gb is not None):
+                return ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db, dw_out=gw, db_out=gb)
+            return ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db)
+
         if ctx.two:
             x, w, x2, w2 = ctx.saved_tensors
             dx = ops.linear_bwd_x(dout, w) if ni[0] else None
-            dw, db = ops.linear_bwd_w(dout, x, want_dw=ni[1], want_db=ctx.has_bias and ni[2]) if (ni[1] or (ctx.has_bias and ni[2])) else (None, None)
+            dw, db = grads_w(dout, x, ni[1], ctx.has_bias and ni[2], p_w, p_b)
             dx2 = ops.linear_bwd_x(dout, w2) if ni[5] else None
-            dw2 = ops.linear_bwd_w(dout, x2)[0] if ni[6] else None
+            dw2 = grads_w(dout, x2, ni[6], False, p_w2, None)[0]
             return dx, dw, db, None, None, dx2, dw2
         x, w, out, rs = ctx.saved_tensors
         if ctx.act == ACT_ELU:
             dout = ops.elu_bwd(out, dout)
         elif ctx.act != ACT_NONE:
             raise NotImplementedError
-        db = None
-        if ctx.has_bias and ni[2]:
-            db = ops.colsum(dout)
+        want_db = ctx.has_bias and ni[2]
         if ctx.has_rs:
+            # the bias sits outside the row scale: db = colsum(dout), dW uses the scaled dout
+            db = ops.colsum(dout, out=_bucket(p_b)) if want_db else None
             dout = dout * rs.unsqueeze(1)
+            dw = grads_w(dout, x, ni[1], False, p_w, None)[0]
+        else:
+            dw, db = grads_w(dout, x, ni[1], want_db, p_w, p_b)  # one pass: db falls out of the dy tiles of dW
         dx = ops.linear_bwd_x(dout, w) if ni[0] else None
-        dw = ops.linear_bwd_w(dout, x)[0] if ni[1] else None
         return dx, dw, db, None, None, None, None
 
 

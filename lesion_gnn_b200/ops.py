@@ -186,8 +186,9 @@ def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add
 
 
 def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst, dout, heads, chan, negative_slope,
-            add_self_loops, dropout_p=0.0, seed=0):
-    """-> dh, datt_src [H*C], datt_dst [H*C]"""
+            add_self_loops, dropout_p=0.0, seed=0, datt_src_out=None, datt_dst_out=None):
+    """-> dh, datt_src [H*C], datt_dst [H*C]; with datt_*_out the attention-vector gradients are ADDED into those
+    buffers (gradient bucket) and None is returned for them"""
     L = _lib.lib()
     n, dev = h.size(0), h.device
     f32 = dict(dtype=torch.float32, device=dev)
@@ -203,12 +204,13 @@ def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst,
            _chk(rowmax), _chk(rowsum), _chk(stats), _chk(da_dst), _chk(att_src, torch.float32), _chk(att_dst, torch.float32),
            _chk(dout), _chk(dh), _chk(da_src), n, heads, chan, float(negative_slope), int(add_self_loops),
            float(dropout_p), int(seed), dt, st)
-    datt_src = torch.empty(heads * chan, **f32)
-    datt_dst = torch.empty(heads * chan, **f32)
+    direct = datt_src_out is not None
+    datt_src = datt_src_out if direct else torch.empty(heads * chan, **f32)
+    datt_dst = datt_dst_out if direct else torch.empty(heads * chan, **f32)
     ws = _ws(L.query("lgk_gat_datt_workspace_bytes", n, heads, chan), dev)
-    L.call("lgk_gat_datt", _chk(h), _chk(da_src), _chk(da_dst), _chk(datt_src), _chk(datt_dst), n, heads, chan,
-           ws.data_ptr(), ws.numel(), dt, st)
-    return dh, datt_src, datt_dst
+    L.call("lgk_gat_datt", _chk(h), _chk(da_src), _chk(da_dst), _chk(datt_src, torch.float32, "datt_src"),
+           _chk(datt_dst, torch.float32, "datt_dst"), n, heads, chan, int(direct), ws.data_ptr(), ws.numel(), dt, st)
+    return (dh, None, None) if direct else (dh, datt_src, datt_dst)
 
 
 # ------------------------------------------------------------------------------------------------ pooling
@@ -267,22 +269,28 @@ def linear_bwd_x(dy: Tensor, weight: Tensor, out: Optional[Tensor] = None) -> Te
     return out
 
 
-def linear_bwd_w(dy: Tensor, x: Optional[Tensor], want_dw: bool = True, want_db: bool = False):
-    """-> (dW [M,K] | None, db [M] | None)"""
+def linear_bwd_w(dy: Tensor, x: Optional[Tensor], want_dw: bool = True, want_db: bool = False,
+                 dw_out: Optional[Tensor] = None, db_out: Optional[Tensor] = None):
+    """-> (dW [M,K] | None, db [M] | None).  dw_out / db_out: ADD the gradients into these buffers (the flat gradient
+    bucket of train.FlatParams) instead of returning fresh tensors -- both must be given for the outputs wanted."""
     L = _lib.lib()
     n, m = dy.shape
     k = x.size(1) if x is not None else 1
     dev = dy.device
-    dw = torch.empty(m, k, dtype=torch.float32, device=dev) if want_dw else None
-    db = torch.empty(m, dtype=torch.float32, device=dev) if want_db else None
+    accumulate = (dw_out is not None) or (db_out is not None)
+    if accumulate and ((want_dw and dw_out is None) or (want_db and db_out is None)):
+        raise ValueError("accumulating form needs an output buffer for every requested gradient")
+    dw = (dw_out if accumulate else torch.empty(m, k, dtype=torch.float32, device=dev)) if want_dw else None
+    db = (db_out if accumulate else torch.empty(m, dtype=torch.float32, device=dev)) if want_db else None
     ws = _ws(L.query("lgk_linear_bwd_w_workspace_bytes", n, k, m), dev)
-    L.call("lgk_linear_bwd_w", _chk(dy, torch.float32, "dy"), _chk(x, torch.float32, "x") if want_dw else None, _chk(dw), _chk(db),
-           n, k, m, 0, ws.data_ptr(), ws.numel(), F32, _stream())
-    return dw, db
+    L.call("lgk_linear_bwd_w", _chk(dy, torch.float32, "dy"), _chk(x, torch.float32, "x") if want_dw else None,
+           _chk(dw, torch.float32, "dw"), _chk(db, torch.float32, "db"),
+           n, k, m, int(accumulate), ws.data_ptr(), ws.numel(), F32, _stream())
+    return (None, None) if accumulate else (dw, db)
 
 
-def colsum(dy: Tensor) -> Tensor:
-    return linear_bwd_w(dy, None, want_dw=False, want_db=True)[1]
+def colsum(dy: Tensor, out: Optional[Tensor] = None) -> Optional[Tensor]:
+    return linear_bwd_w(dy, None, want_dw=False, want_db=True, db_out=out)[1]
 
 
 # -------------------------------------------------------------------------------------------- elementwise

@@ -20,6 +20,7 @@ from torch import Tensor
 from . import ops
 from .data import HostBatch
 from .graph import CSRGraph
+from .nn.functional import direct_param_grads
 from .nn.pool import Segments
 
 _ALIGN = 32  # floats: every parameter starts on a 128-byte boundary inside the flat buffers
@@ -150,7 +151,10 @@ class TrainStep:
 
     def _body(self, db: DeviceBatch) -> Tensor:
         self.opt.zero_grad()
-        loss = forward_backward(self.model, db, self.loss_type, self.num_classes)
+        # the backward kernels add weight / bias / attention gradients straight into the flat bucket (no per-parameter
+        # autograd `add` launches); the bucket was just zeroed, so this equals plain accumulation
+        with direct_param_grads():
+            loss = forward_backward(self.model, db, self.loss_type, self.num_classes)
         if self.world_size == 1:
             self.opt.step()
         return loss
