@@ -44,6 +44,46 @@ def _bucket(p) -> Optional[Tensor]:
     return g
 
 
+# ---- parameter-gradient kernels on a side stream -----------------------------------------------------------------
+# Weight / bias / attention-vector gradients are leaves of the backward graph: nothing downstream waits for them
+# until the optimiser.  Inside `side_stream(s)` (and only when they are written straight into the bucket, see above)
+# they are enqueued on `s`, forked from the point of the main stream where their inputs are ready, so they overlap
+# with the main chain (dX of this layer, the next layer's attention backward, ...) -- each of these launches fills
+# only part of the GPU.  `join()` makes the main stream wait for them; tensors they read are kept alive until then,
+# so the caching allocator cannot hand their memory to a later main-stream allocation.
+_SIDE = [None]
+
+
+class side_stream:
+    def __init__(self, stream):
+        self.stream, self.keep = stream, []
+
+    def __enter__(self):
+        self._old = _SIDE[0]
+        _SIDE[0] = self
+        return self
+
+    def join(self):
+        torch.cuda.current_stream().wait_stream(self.stream)
+        self.keep.clear()
+
+    def __exit__(self, *exc):
+        self.join()
+        _SIDE[0] = self._old
+        return False
+
+
+def _on_side(fn, *keep):
+    sc = _SIDE[0]
+    if sc is None:
+        return fn()
+    sc.stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(sc.stream):
+        fn()
+    sc.keep.extend(t for t in keep if t is not None)
+    return None
+
+
 def _need_csc(g: CSRGraph):
     if g.colptr is None:
         raise RuntimeError("this CSRGraph was built without the CSC transpose index; backward needs with_csc=True")
@@ -87,7 +127,12 @@ class _Aggregate(torch.autograd.Function):
                 dx = ops.spmm(g.colptr, g.row, dout, "sum", emap=g.csr2csc if ctx.ew is not None else None, ew=ctx.ew,
                               pre=ctx.post, post=ctx.pre, selfw=ctx.selfw, self_fill=ctx.self_fill, self_mode=ctx.self_mode)
         if ctx.has_bias and ctx.needs_input_grad[1]:
-            dbias = ops.colsum(dout.float() if dout.dtype != torch.float32 else dout, out=_bucket(ctx.bias_ref))
+            d32 = dout.float() if dout.dtype != torch.float32 else dout
+            gb = _bucket(ctx.bias_ref)
+            if gb is not None:
+                _on_side(lambda: ops.colsum(d32, out=gb), d32)
+            else:
+                dbias = ops.colsum(d32)
         return dx, dbias, None, None, None, None, None, None, None, None
 
 
@@ -126,17 +171,23 @@ class _GatAttention(torch.autograd.Function):
         _need_csc(g)
         dout = dout.contiguous()
         p_src, p_dst, p_bias = ctx.refs
+        dh, da_src, da_dst = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
+                                         a_s, a_d, dout, heads, chan, slope, add_self, p, seed)
         g_src, g_dst = _bucket(p_src), _bucket(p_dst)
-        direct = g_src is not None and g_dst is not None
-        dh, datt_src, datt_dst = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
-                                             a_s, a_d, dout, heads, chan, slope, add_self, p, seed,
-                                             datt_src_out=g_src.view(-1) if direct else None,
-                                             datt_dst_out=g_dst.view(-1) if direct else None)
+        if g_src is not None and g_dst is not None:
+            _on_side(lambda: ops.gat_datt(h, da_src, da_dst, heads, chan, g_src.view(-1), g_dst.view(-1)), h, da_src, da_dst)
+            datt_src = datt_dst = None
+        else:
+            datt_src, datt_dst = ops.gat_datt(h, da_src, da_dst, heads, chan)
+            datt_src, datt_dst = datt_src.view(ctx.att_shape), datt_dst.view(ctx.att_shape)
         dbias = None
         if ctx.has_bias and ctx.needs_input_grad[3]:
-            dbias = ops.colsum(dout if dout.dtype == torch.float32 else dout.float(), out=_bucket(p_bias))
-        if not direct:
-            datt_src, datt_dst = datt_src.view(ctx.att_shape), datt_dst.view(ctx.att_shape)
+            d32 = dout if dout.dtype == torch.float32 else dout.float()
+            gb = _bucket(p_bias)
+            if gb is not None:
+                _on_side(lambda: ops.colsum(d32, out=gb), d32)
+            else:
+                dbias = ops.colsum(d32)
         return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None)
 
 
@@ -181,7 +232,8 @@ class _Linear(torch.autograd.Function):
                 return None, None
             gw, gb = (_bucket(pw) if want_dw else None), (_bucket(pb) if want_db else None)
             if (not want_dw or gw is not None) and (not want_db or gb is not None):
-                return ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db, dw_out=gw, db_out=gb)
+                _on_side(lambda: ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db, dw_out=gw, db_out=gb), dy, xin)
+                return None, None
             return ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db)
 
         if ctx.two:
@@ -199,7 +251,13 @@ class _Linear(torch.autograd.Function):
         want_db = ctx.has_bias and ni[2]
         if ctx.has_rs:
             # the bias sits outside the row scale: db = colsum(dout), dW uses the scaled dout
-            db = ops.colsum(dout, out=_bucket(p_b)) if want_db else None
+            db = None
+            if want_db:
+                gb, d0 = _bucket(p_b), dout
+                if gb is not None:
+                    _on_side(lambda: ops.colsum(d0, out=gb), d0)
+                else:
+                    db = ops.colsum(d0)
             dout = dout * rs.unsqueeze(1)
             dw = grads_w(dout, x, ni[1], False, p_w, None)[0]
         else:

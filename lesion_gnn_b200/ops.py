@@ -186,9 +186,8 @@ def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add
 
 
 def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst, dout, heads, chan, negative_slope,
-            add_self_loops, dropout_p=0.0, seed=0, datt_src_out=None, datt_dst_out=None):
-    """-> dh, datt_src [H*C], datt_dst [H*C]; with datt_*_out the attention-vector gradients are ADDED into those
-    buffers (gradient bucket) and None is returned for them"""
+            add_self_loops, dropout_p=0.0, seed=0):
+    """-> dh, da_src [N,H], da_dst [N,H] (the attention-vector gradients follow from gat_datt)"""
     L = _lib.lib()
     n, dev = h.size(0), h.device
     f32 = dict(dtype=torch.float32, device=dev)
@@ -204,13 +203,21 @@ def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst,
            _chk(rowmax), _chk(rowsum), _chk(stats), _chk(da_dst), _chk(att_src, torch.float32), _chk(att_dst, torch.float32),
            _chk(dout), _chk(dh), _chk(da_src), n, heads, chan, float(negative_slope), int(add_self_loops),
            float(dropout_p), int(seed), dt, st)
+    return dh, da_src, da_dst
+
+
+def gat_datt(h, da_src, da_dst, heads, chan, datt_src_out=None, datt_dst_out=None):
+    """datt_src / datt_dst [H*C] = sum_n da[n,h] h[n,h,:]; with the *_out buffers given the sums are ADDED into them
+    (gradient bucket) and (None, None) is returned"""
+    L = _lib.lib()
+    n, dev = h.size(0), h.device
     direct = datt_src_out is not None
-    datt_src = datt_src_out if direct else torch.empty(heads * chan, **f32)
-    datt_dst = datt_dst_out if direct else torch.empty(heads * chan, **f32)
+    datt_src = datt_src_out if direct else torch.empty(heads * chan, dtype=torch.float32, device=dev)
+    datt_dst = datt_dst_out if direct else torch.empty(heads * chan, dtype=torch.float32, device=dev)
     ws = _ws(L.query("lgk_gat_datt_workspace_bytes", n, heads, chan), dev)
     L.call("lgk_gat_datt", _chk(h), _chk(da_src), _chk(da_dst), _chk(datt_src, torch.float32, "datt_src"),
-           _chk(datt_dst, torch.float32, "datt_dst"), n, heads, chan, int(direct), ws.data_ptr(), ws.numel(), dt, st)
-    return (dh, None, None) if direct else (dh, datt_src, datt_dst)
+           _chk(datt_dst, torch.float32, "datt_dst"), n, heads, chan, int(direct), ws.data_ptr(), ws.numel(), _dt(h), _stream())
+    return (None, None) if direct else (datt_src, datt_dst)
 
 
 # ------------------------------------------------------------------------------------------------ pooling

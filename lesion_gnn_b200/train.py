@@ -20,7 +20,7 @@ from torch import Tensor
 from . import ops
 from .data import HostBatch
 from .graph import CSRGraph
-from .nn.functional import direct_param_grads
+from .nn.functional import direct_param_grads, side_stream
 from .nn.pool import Segments
 
 _ALIGN = 32  # floats: every parameter starts on a 128-byte boundary inside the flat buffers
@@ -148,12 +148,14 @@ class TrainStep:
         self.use_cuda_graph = use_cuda_graph
         self.pg, self.world_size = process_group, world_size
         self._graphs = {}
+        self._side = torch.cuda.Stream() if torch.cuda.is_available() else None
 
     def _body(self, db: DeviceBatch) -> Tensor:
         self.opt.zero_grad()
         # the backward kernels add weight / bias / attention gradients straight into the flat bucket (no per-parameter
         # autograd `add` launches); the bucket was just zeroed, so this equals plain accumulation
-        with direct_param_grads():
+        # ... and run on a side stream, overlapping the main backward chain; joined before the optimiser reads them
+        with direct_param_grads(), side_stream(self._side):
             loss = forward_backward(self.model, db, self.loss_type, self.num_classes)
         if self.world_size == 1:
             self.opt.step()
