@@ -21,6 +21,7 @@
 #include "common.cuh"
 #include <float.h>
 #include <stdlib.h>
+#include <algorithm>
 
 namespace lgk {
 namespace {
@@ -41,14 +42,31 @@ struct SpmmArgs {
   int self_mode;
   int64_t n_rows;
   int feat;
-  int slice4;    // float4 columns per feature slice (grid.y slices)
-  int64_t band;  // consecutive rows per CTA (grid.x bands)
+  int slice4;     // float4 columns per feature slice (grid.y slices)
+  int64_t band;   // consecutive rows per CTA (grid.x bands)
+  int ptr_words;  // shared-memory words reserved for the band's row pointers
 };
 
 // ---- vectorised path: feat % 4 == 0 ------------------------------------------------------------------
-constexpr int kStageCap = 5120;  // edges staged per chunk (ids 20 KB + weights 20 KB of shared memory)
-constexpr int kRowsPerGroup = 2; // rows a group reduces per chunk
+// A CTA owns a band of consecutive rows and walks it in chunks of R rows through a three-deep pipeline:
+//   * the band's row pointers are read once, up front, into shared memory;
+//   * while the groups reduce chunk c, the ids of chunk c+2 are already in flight into registers; when the
+//   * while the groups reduce chunk c, the ids of chunk c+2 are in flight (cp.async) into the third staging
+//     buffer; when the reduction is done they are rewritten in place as pre-multiplied row offsets, with the
+//     weights fully resolved beside them;
+//   * one barrier per chunk.
+// So the ptr -> idx -> weight -> row dependency chain never stalls a reduction.  (Prefetching the neighbour rows
+// of chunk c+2 into L2 -- per line through the LSU, per row with cp.async.bulk.prefetch, or the band's own rows in
+// bulk -- was measured and does not pay: profiles/README.md, r01 v1.)
+constexpr int kIdRegs = 3;       // staged edges per thread and chunk: a staging buffer holds kIdRegs * blockDim.x edges
+constexpr int kStageBufs = 3;
+constexpr int kMaxBand = 2044;   // rows per CTA (their row pointers: 8 KB of shared memory)
 
+__device__ __forceinline__ void cp_async_4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(uint32_t(__cvta_generic_to_shared(smem_dst))), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ int4 load_idx4(const int* __restrict__ idx, int q, int n_idx) {
   if (q + 4 <= n_idx) return __ldg(reinterpret_cast<const int4*>(idx + q));
   int4 r = make_int4(0, 0, 0, 0);
@@ -68,11 +86,12 @@ __device__ __forceinline__ float edge_weight(const SpmmArgs& a, int p, int j) {
 template <typename T, int LPR, int REDUCE, bool WEIGHTED>
 __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* __restrict__ x, T* __restrict__ out) {
   extern __shared__ __align__(16) int smem[];
-  const int groups = blockDim.x / LPR;
-  const int R = groups * kRowsPerGroup;
-  int* s_ptr = smem;                                 // [R + 1]
-  int* s_j = smem + ((R + 1 + 3) & ~3);              // [kStageCap + 8], s_j[t] = idx[base + t], base % 4 == 0
-  float* s_w = reinterpret_cast<float*>(s_j + kStageCap + 8);
+  const int nthreads = blockDim.x;
+  const int groups = nthreads / LPR;
+  const int cap = nthreads * kIdRegs;
+  int* s_ptr = smem;                                                   // [band + 1]
+  unsigned* s_off = reinterpret_cast<unsigned*>(smem + a.ptr_words);   // [kStageBufs][cap + 8]: idx * F4
+  float* s_w = reinterpret_cast<float*>(s_off + kStageBufs * (cap + 8));
 
   const int gl = threadIdx.x & (LPR - 1);
   const int grp = threadIdx.x / LPR;
@@ -82,144 +101,195 @@ __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* _
   // rows are addressed in float4 units with 32-bit offsets (n_rows * F4 < 2^32 is checked by the launcher)
   const T* xv = x + vec * 4;
   T* ov = out + vec * 4;
-  const int64_t band_end = min(a.n_rows, (int64_t(blockIdx.x) + 1) * a.band);
+  const int64_t band_start = int64_t(blockIdx.x) * a.band;
+  const int nb = int(min(a.n_rows, band_start + a.band) - band_start);
   const int skip_self = (WEIGHTED && a.self_mode == LGK_SELF_REPLACE) ? 1 : 0;
 
-  for (int64_t r0 = int64_t(blockIdx.x) * a.band; r0 < band_end; r0 += R) {
-    const int nrows = (band_end - r0 < R) ? int(band_end - r0) : R;
-    __syncthreads();  // the previous chunk's readers are done with the staging buffers
-    for (int t = threadIdx.x; t <= nrows; t += blockDim.x) s_ptr[t] = __ldg(a.ptr + r0 + t);
-    __syncthreads();
-    const int e0 = s_ptr[0], e1 = s_ptr[nrows];
+  for (int t = threadIdx.x; t <= nb; t += nthreads) s_ptr[t] = __ldg(a.ptr + band_start + t);
+  __syncthreads();
+  // rows per chunk: as many per group (1..8) as keep an average chunk within ~3/4 of a staging buffer
+  const int band_edges = s_ptr[nb] - s_ptr[0];
+  const int R = groups * max(1, min(8, int((int64_t(cap) * 3 / 4 * nb) / (int64_t(groups) * max(band_edges, 1)))));
+  const int nchunks = (nb + R - 1) / R;
+
+  // ids of chunk c -> staging buffer c % kStageBufs, asynchronously (cp.async: no registers held meanwhile)
+  auto load_ids = [&](int c) {
+    const int e0 = s_ptr[c * R], e1 = s_ptr[min(nb, (c + 1) * R)];
     const int base = e0 & ~3;
-    const bool staged = (e1 - base) <= kStageCap;
-    if (staged) {
-      for (int t = threadIdx.x + (e0 - base); t < e1 - base; t += blockDim.x) {
-        const int j = ld_stream_i32(a.idx + base + t);
-        s_j[t] = j;
-        if (WEIGHTED) s_w[t] = edge_weight(a, base + t, j);
+    if (e1 - base <= cap) {
+      unsigned* so = s_off + (c % kStageBufs) * (cap + 8);
+#pragma unroll
+      for (int k = 0; k < kIdRegs; ++k) {
+        const int t = threadIdx.x + k * nthreads;
+        const int p = base + t;
+        if (p >= e0 && p < e1) cp_async_4(so + t, a.idx + p);
       }
-      __syncthreads();
     }
-    if (!lane_on) continue;
+    cp_async_commit();
+  };
+  // in place: raw ids -> pre-multiplied row offsets, weights resolved.
+  // Every thread converts exactly the entries it copied itself.
+  auto store_ids = [&](int c) {
+    cp_async_wait_all();
+    const int e0 = s_ptr[c * R], e1 = s_ptr[min(nb, (c + 1) * R)];
+    const int base = e0 & ~3;
+    if (e1 - base > cap) return;
+    unsigned* so = s_off + (c % kStageBufs) * (cap + 8);
+    float* sw = s_w + (c % kStageBufs) * (cap + 8);
+#pragma unroll
+    for (int k = 0; k < kIdRegs; ++k) {
+      const int t = threadIdx.x + k * nthreads;
+      const int p = base + t;
+      if (p >= e0 && p < e1) {
+        const int j = int(so[t]);
+        const unsigned off = unsigned(j) * F4;
+        so[t] = off;
+        if (WEIGHTED) sw[t] = edge_weight(a, p, j);
+      }
+    }
+  };
+  load_ids(0);
+  store_ids(0);
+  if (nchunks > 1) {
+    load_ids(1);
+    store_ids(1);
+  }
+  __syncthreads();
 
-    for (int lr = grp; lr < nrows; lr += groups) {
-      const int64_t row = r0 + lr;
-      const int start = s_ptr[lr], end = s_ptr[lr + 1];
-      const int self_j = skip_self ? int(row) : -1;
-      float4 acc = (REDUCE == LGK_MAX) ? make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX) : f4_zero();
-      int4 arg = make_int4(-1, -1, -1, -1);
+  for (int c = 0; c < nchunks; ++c) {
+    if (c + 2 < nchunks) load_ids(c + 2);
+    const int r_lo = c * R;
+    const int nrows = min(R, nb - r_lo);
+    const int e1 = s_ptr[r_lo + nrows];
+    const int base = s_ptr[r_lo] & ~3;
+    const bool staged = (e1 - base) <= cap;
+    const unsigned* so = s_off + (c % kStageBufs) * (cap + 8);
+    const float* sw = s_w + (c % kStageBufs) * (cap + 8);
 
-      for (int q = start & ~3; q < end; q += 8) {
-        int j[8];
-        float w[8];
-        float4 v[8];
-        // ids (and weights) of two aligned quads
-        {
-          int4 ja, jb = make_int4(0, 0, 0, 0);
-          float4 wa = make_float4(1.f, 1.f, 1.f, 1.f), wb = wa;
-          const bool second = q + 4 < end;
-          if (staged) {
-            ja = *reinterpret_cast<const int4*>(s_j + (q - base));
-            if (second) jb = *reinterpret_cast<const int4*>(s_j + (q - base) + 4);
-            if (WEIGHTED) {
-              wa = *reinterpret_cast<const float4*>(s_w + (q - base));
-              if (second) wb = *reinterpret_cast<const float4*>(s_w + (q - base) + 4);
+    if (lane_on) {
+      for (int lr = grp; lr < nrows; lr += groups) {
+        const int64_t row = band_start + r_lo + lr;
+        const int start = s_ptr[r_lo + lr], end = s_ptr[r_lo + lr + 1];
+        const unsigned self_off = skip_self ? unsigned(row) * F4 : 0xffffffffu;
+        float4 acc = (REDUCE == LGK_MAX) ? make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX) : f4_zero();
+        int4 arg = make_int4(-1, -1, -1, -1);
+
+        for (int q = start & ~3; q < end; q += 8) {
+          unsigned off[8];
+          float w[8];
+          float4 v[8];
+          // row offsets (and weights) of two aligned quads
+          {
+            uint4 ja, jb = make_uint4(0, 0, 0, 0);
+            float4 wa = make_float4(1.f, 1.f, 1.f, 1.f), wb = wa;
+            const bool second = q + 4 < end;
+            if (staged) {
+              ja = *reinterpret_cast<const uint4*>(so + (q - base));
+              if (second) jb = *reinterpret_cast<const uint4*>(so + (q - base) + 4);
+              if (WEIGHTED) {
+                wa = *reinterpret_cast<const float4*>(sw + (q - base));
+                if (second) wb = *reinterpret_cast<const float4*>(sw + (q - base) + 4);
+              }
+            } else {  // chunk with more edges than a staging buffer holds (very high degrees): read through L1
+              const int4 ia = load_idx4(a.idx, q, e1);
+              int4 ib = make_int4(0, 0, 0, 0);
+              if (second) ib = load_idx4(a.idx, q + 4, e1);
+              if (WEIGHTED) {
+                const int jj[8] = {ia.x, ia.y, ia.z, ia.w, ib.x, ib.y, ib.z, ib.w};
+                float ww[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) ww[k] = (q + k >= start && q + k < end) ? edge_weight(a, q + k, jj[k]) : 0.f;
+                wa = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                wb = make_float4(ww[4], ww[5], ww[6], ww[7]);
+              }
+              ja = make_uint4(unsigned(ia.x) * F4, unsigned(ia.y) * F4, unsigned(ia.z) * F4, unsigned(ia.w) * F4);
+              jb = make_uint4(unsigned(ib.x) * F4, unsigned(ib.y) * F4, unsigned(ib.z) * F4, unsigned(ib.w) * F4);
             }
-          } else {  // chunk with more than kStageCap edges (very high degrees): read through L1 instead
-            ja = load_idx4(a.idx, q, e1);
-            if (second) jb = load_idx4(a.idx, q + 4, e1);
-            if (WEIGHTED) {
-              const int jj[8] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w};
-              float ww[8];
-#pragma unroll
-              for (int c = 0; c < 8; ++c) ww[c] = (q + c >= start && q + c < end) ? edge_weight(a, q + c, jj[c]) : 0.f;
-              wa = make_float4(ww[0], ww[1], ww[2], ww[3]);
-              wb = make_float4(ww[4], ww[5], ww[6], ww[7]);
-            }
+            off[0] = ja.x; off[1] = ja.y; off[2] = ja.z; off[3] = ja.w; off[4] = jb.x; off[5] = jb.y; off[6] = jb.z; off[7] = jb.w;
+            w[0] = wa.x; w[1] = wa.y; w[2] = wa.z; w[3] = wa.w; w[4] = wb.x; w[5] = wb.y; w[6] = wb.z; w[7] = wb.w;
           }
-          j[0] = ja.x; j[1] = ja.y; j[2] = ja.z; j[3] = ja.w; j[4] = jb.x; j[5] = jb.y; j[6] = jb.z; j[7] = jb.w;
-          w[0] = wa.x; w[1] = wa.y; w[2] = wa.z; w[3] = wa.w; w[4] = wb.x; w[5] = wb.y; w[6] = wb.z; w[7] = wb.w;
-        }
-        const bool full = (q >= start) && (q + 8 <= end);
-        bool ok[8];
-        if (full) {
+          const bool full = (q >= start) && (q + 8 <= end);
+          bool ok[8];
+          if (full) {
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            ok[c] = true;
-            v[c] = Vec4<T>::gather(xv + size_t(unsigned(j[c]) * F4) * 4, 0);
-          }
-        } else {
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            ok[c] = (q + c >= start) && (q + c < end);
-            v[c] = Vec4<T>::gather_if(xv + size_t(unsigned(ok[c] ? j[c] : 0) * F4) * 4, 0, ok[c]);
-          }
-        }
-        if (REDUCE == LGK_MAX) {
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            if (ok[c]) {
-              const int slot = q + c;
-              if (v[c].x > acc.x) { acc.x = v[c].x; arg.x = slot; }
-              if (v[c].y > acc.y) { acc.y = v[c].y; arg.y = slot; }
-              if (v[c].z > acc.z) { acc.z = v[c].z; arg.z = slot; }
-              if (v[c].w > acc.w) { acc.w = v[c].w; arg.w = slot; }
-            }
-          }
-        } else {
-          // pairwise tree over the step: every gather is needed before the chain into acc can finish, which
-          // keeps the eight loads in flight together; predicated-off gathers are exact zeros
-          if (WEIGHTED) {
-            // first tree level as multiply + FMA: v[c] = w[c] v[c] + w[c+1] v[c+1]
-#pragma unroll
-            for (int c = 0; c < 8; c += 2) {
-              const float w0 = (!ok[c] || j[c] == self_j) ? 0.f : w[c];  // stored self loop: dropped
-              const float w1 = (!ok[c + 1] || j[c + 1] == self_j) ? 0.f : w[c + 1];
-              v[c].x = fmaf(w1, v[c + 1].x, w0 * v[c].x); v[c].y = fmaf(w1, v[c + 1].y, w0 * v[c].y);
-              v[c].z = fmaf(w1, v[c + 1].z, w0 * v[c].z); v[c].w = fmaf(w1, v[c + 1].w, w0 * v[c].w);
+            for (int k = 0; k < 8; ++k) {
+              ok[k] = true;
+              v[k] = Vec4<T>::gather(xv + size_t(off[k]) * 4, 0);
             }
           } else {
 #pragma unroll
-            for (int c = 0; c < 8; c += 2) {
-              v[c].x += v[c + 1].x; v[c].y += v[c + 1].y; v[c].z += v[c + 1].z; v[c].w += v[c + 1].w;
+            for (int k = 0; k < 8; ++k) {
+              ok[k] = (q + k >= start) && (q + k < end);
+              v[k] = Vec4<T>::gather_if(xv + size_t(ok[k] ? off[k] : 0u) * 4, 0, ok[k]);
             }
           }
+          if (REDUCE == LGK_MAX) {
 #pragma unroll
-          for (int s = 2; s < 8; s <<= 1)
-#pragma unroll
-            for (int c = 0; c < 8; c += 2 * s) {
-              v[c].x += v[c + s].x; v[c].y += v[c + s].y; v[c].z += v[c + s].z; v[c].w += v[c + s].w;
+            for (int k = 0; k < 8; ++k) {
+              if (ok[k]) {
+                const int slot = q + k;
+                if (v[k].x > acc.x) { acc.x = v[k].x; arg.x = slot; }
+                if (v[k].y > acc.y) { acc.y = v[k].y; arg.y = slot; }
+                if (v[k].z > acc.z) { acc.z = v[k].z; arg.z = slot; }
+                if (v[k].w > acc.w) { acc.w = v[k].w; arg.w = slot; }
+              }
             }
-          acc.x += v[0].x; acc.y += v[0].y; acc.z += v[0].z; acc.w += v[0].w;
+          } else {
+            // pairwise tree over the step: every gather is needed before the chain into acc can finish, which
+            // keeps the eight loads in flight together; predicated-off gathers are exact zeros
+            if (WEIGHTED) {
+              // first tree level as multiply + FMA: v[k] = w[k] v[k] + w[k+1] v[k+1]
+#pragma unroll
+              for (int k = 0; k < 8; k += 2) {
+                const float w0 = (!ok[k] || off[k] == self_off) ? 0.f : w[k];  // stored self loop: dropped
+                const float w1 = (!ok[k + 1] || off[k + 1] == self_off) ? 0.f : w[k + 1];
+                v[k].x = fmaf(w1, v[k + 1].x, w0 * v[k].x); v[k].y = fmaf(w1, v[k + 1].y, w0 * v[k].y);
+                v[k].z = fmaf(w1, v[k + 1].z, w0 * v[k].z); v[k].w = fmaf(w1, v[k + 1].w, w0 * v[k].w);
+              }
+            } else {
+#pragma unroll
+              for (int k = 0; k < 8; k += 2) {
+                v[k].x += v[k + 1].x; v[k].y += v[k + 1].y; v[k].z += v[k + 1].z; v[k].w += v[k + 1].w;
+              }
+            }
+#pragma unroll
+            for (int s = 2; s < 8; s <<= 1)
+#pragma unroll
+              for (int k = 0; k < 8; k += 2 * s) {
+                v[k].x += v[k + s].x; v[k].y += v[k + s].y; v[k].z += v[k + s].z; v[k].w += v[k + s].w;
+              }
+            acc.x += v[0].x; acc.y += v[0].y; acc.z += v[0].z; acc.w += v[0].w;
+          }
         }
-      }
 
-      float4 r = acc;
-      const size_t ro = size_t(unsigned(row) * F4) * 4;
-      if (REDUCE == LGK_MAX) {
-        if (arg.x < 0) r.x = 0.f;
-        if (arg.y < 0) r.y = 0.f;
-        if (arg.z < 0) r.z = 0.f;
-        if (arg.w < 0) r.w = 0.f;
-        if (a.arg_out) st_stream_i4(reinterpret_cast<int4*>(a.arg_out + ro + vec * 4), arg);
-      } else {
-        float scale = 1.f;
-        if (REDUCE == LGK_MEAN) scale = 1.f / float(max(end - start, 1));
-        if (a.post) scale *= __ldg(a.post + row);
-        if (a.self_mode != LGK_SELF_NONE) {
-          float wself = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
-          if (a.pre) wself *= __ldg(a.pre + row);
-          f4_fma(r, wself, Vec4<T>::gather(xv + ro, 0));
+        float4 r = acc;
+        const size_t ro = size_t(unsigned(row) * F4) * 4;
+        if (REDUCE == LGK_MAX) {
+          if (arg.x < 0) r.x = 0.f;
+          if (arg.y < 0) r.y = 0.f;
+          if (arg.z < 0) r.z = 0.f;
+          if (arg.w < 0) r.w = 0.f;
+          if (a.arg_out) st_stream_i4(reinterpret_cast<int4*>(a.arg_out + ro + vec * 4), arg);
+        } else {
+          float scale = 1.f;
+          if (REDUCE == LGK_MEAN) scale = 1.f / float(max(end - start, 1));
+          if (a.post) scale *= __ldg(a.post + row);
+          if (a.self_mode != LGK_SELF_NONE) {
+            float wself = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
+            if (a.pre) wself *= __ldg(a.pre + row);
+            f4_fma(r, wself, Vec4<T>::gather(xv + ro, 0));
+          }
+          r.x *= scale; r.y *= scale; r.z *= scale; r.w *= scale;
         }
-        r.x *= scale; r.y *= scale; r.z *= scale; r.w *= scale;
+        if (a.bias) {
+          float4 b = __ldg(reinterpret_cast<const float4*>(a.bias) + vec);
+          r.x += b.x; r.y += b.y; r.z += b.z; r.w += b.w;
+        }
+        Vec4<T>::store(ov + ro, 0, r);
       }
-      if (a.bias) {
-        float4 b = __ldg(reinterpret_cast<const float4*>(a.bias) + vec);
-        r.x += b.x; r.y += b.y; r.z += b.z; r.w += b.w;
-      }
-      Vec4<T>::store(ov + ro, 0, r);
     }
+    if (c + 2 < nchunks) store_ids(c + 2);
+    __syncthreads();
   }
 }
 
@@ -349,8 +419,8 @@ int env_int(const char* name, int dflt) {
   return (v && *v) ? atoi(v) : dflt;
 }
 const SpmmTuning& tuning() {
-  static const SpmmTuning t = {env_int("LGK_SPMM_THREADS", 512), env_int("LGK_SPMM_SLICE4", 32), env_int("LGK_SPMM_WAVES", 8),
-                               int64_t(env_int("LGK_SPMM_MAX_BAND", 1 << 20))};
+  static const SpmmTuning t = {env_int("LGK_SPMM_THREADS", 512), env_int("LGK_SPMM_SLICE4", 32), env_int("LGK_SPMM_WAVES", 16),
+                               int64_t(env_int("LGK_SPMM_MAX_BAND", kMaxBand))};
   return t;
 }
 
@@ -369,19 +439,17 @@ int launch_spmm(const SpmmArgs& a_in, const void* x_, void* out_, cudaStream_t s
     a.slice4 = int(ceil_div(F4, nslice));
     int lpr = 1;
     while (lpr < a.slice4) lpr <<= 1;
-    // at most 64 groups per CTA (so a chunk of 128 rows stages up to kStageCap edges), fewer threads on small inputs
+    // at most 64 groups per CTA, fewer threads on small inputs
     int threads = min(max(32, min(512, t.threads)) / 32 * 32, max(64, 64 * lpr));
-    while (threads > 128 && ceil_div(a.n_rows, int64_t(threads / lpr) * kRowsPerGroup) < 2 * kNumSMs) threads >>= 1;
-    const int groups = threads / lpr;
-    const int R = groups * kRowsPerGroup;
-    // bands: enough CTAs for `waves` rounds over the SMs, a whole number of chunks each
+    while (threads > 128 && ceil_div(a.n_rows, int64_t(threads / lpr) * 2) < 2 * kNumSMs) threads >>= 1;
+    // bands: enough CTAs for `waves` rounds over the SMs
     int64_t band = ceil_div(a.n_rows, int64_t(kNumSMs) * t.waves);
-    if (band > t.max_band) band = t.max_band;
-    band = align_up(band < R ? R : band, R);
+    band = std::max<int64_t>(threads / lpr, std::min<int64_t>(band, std::min<int64_t>(t.max_band, kMaxBand)));
     a.band = band;
+    a.ptr_words = int((band + 1 + 3) & ~int64_t(3));
     dim3 grid(unsigned(ceil_div(a.n_rows, band)), unsigned(nslice));
     const bool weighted = REDUCE != LGK_MAX && (a.ew || a.pre || a.self_mode == LGK_SELF_REPLACE);
-    const size_t smem = 4 * (size_t((R + 1 + 3) & ~3) + (kStageCap + 8) * (weighted ? 2 : 1));
+    const size_t smem = 4 * (size_t(a.ptr_words) + size_t(kStageBufs) * (threads * kIdRegs + 8) * (weighted ? 2 : 1));
 #define LGK_SPMM_CASE(LPR)                                                                             \
   case LPR:                                                                                            \
     if (weighted) spmm_vec_kernel<T, LPR, REDUCE, true><<<grid, threads, smem, stream>>>(a, x, out);   \

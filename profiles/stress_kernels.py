@@ -27,6 +27,7 @@ a_s, a_d = ops.gat_alpha(x, att, att, 4, 32)
 xin = torch.randn(11583, 1025, device=dev)
 w = torch.randn(64, 1025, device=dev)
 for _ in range(reps):
+    ops.spmm(g.rowptr, g.col, x, "sum")
     ops.spmm(g.rowptr, g.col, x, "sum", pre=dinv, post=dinv, self_mode=ops.SELF_REPLACE)
     ops.spmm(g.colptr, g.row, x, "sum", pre=dinv, post=dinv, self_mode=ops.SELF_REPLACE)
     ops.spmm(g.rowptr, g.col, x, "max", want_arg=True)
