@@ -67,14 +67,6 @@ __device__ __forceinline__ void cp_async_4(void* smem_dst, const void* gmem_src)
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-__device__ __forceinline__ int4 load_idx4(const int* __restrict__ idx, int q, int n_idx) {
-  if (q + 4 <= n_idx) return __ldg(reinterpret_cast<const int4*>(idx + q));
-  int4 r = make_int4(0, 0, 0, 0);
-  if (q + 0 < n_idx) r.x = __ldg(idx + q + 0);
-  if (q + 1 < n_idx) r.y = __ldg(idx + q + 1);
-  if (q + 2 < n_idx) r.z = __ldg(idx + q + 2);
-  return r;
-}
 
 __device__ __forceinline__ float edge_weight(const SpmmArgs& a, int p, int j) {
   float w = 1.f;
@@ -83,7 +75,7 @@ __device__ __forceinline__ float edge_weight(const SpmmArgs& a, int p, int j) {
   return w;
 }
 
-template <typename T, int LPR, int REDUCE, bool WEIGHTED>
+template <typename T, int LPR, int REDUCE, bool WEIGHTED, bool EPI>
 __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* __restrict__ x, T* __restrict__ out) {
   extern __shared__ __align__(16) int smem[];
   const int nthreads = blockDim.x;
@@ -117,13 +109,8 @@ __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* _
     const int e0 = s_ptr[c * R], e1 = s_ptr[min(nb, (c + 1) * R)];
     const int base = e0 & ~3;
     if (e1 - base <= cap) {
-      unsigned* so = s_off + (c % kStageBufs) * (cap + 8);
-#pragma unroll
-      for (int k = 0; k < kIdRegs; ++k) {
-        const int t = threadIdx.x + k * nthreads;
-        const int p = base + t;
-        if (p >= e0 && p < e1) cp_async_4(so + t, a.idx + p);
-      }
+      unsigned* so = s_off + (c % kStageBufs) * (cap + 8) - base;
+      for (int p = e0 + threadIdx.x; p < e1; p += nthreads) cp_async_4(so + p, a.idx + p);
     }
     cp_async_commit();
   };
@@ -134,17 +121,22 @@ __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* _
     const int e0 = s_ptr[c * R], e1 = s_ptr[min(nb, (c + 1) * R)];
     const int base = e0 & ~3;
     if (e1 - base > cap) return;
-    unsigned* so = s_off + (c % kStageBufs) * (cap + 8);
-    float* sw = s_w + (c % kStageBufs) * (cap + 8);
-#pragma unroll
-    for (int k = 0; k < kIdRegs; ++k) {
-      const int t = threadIdx.x + k * nthreads;
-      const int p = base + t;
-      if (p >= e0 && p < e1) {
-        const int j = int(so[t]);
-        const unsigned off = unsigned(j) * F4;
-        so[t] = off;
-        if (WEIGHTED) sw[t] = edge_weight(a, p, j);
+    unsigned* so = s_off + (c % kStageBufs) * (cap + 8) - base;
+    float* sw = s_w + (c % kStageBufs) * (cap + 8) - base;
+    for (int p = e0 + threadIdx.x; p < e1; p += nthreads) {
+      const int j = int(so[p]);
+      so[p] = unsigned(j) * F4;
+      if (WEIGHTED) {
+        float w = edge_weight(a, p, j);
+        if (skip_self) {  // the row of slot p: largest r with s_ptr[r] <= p (rows of this chunk)
+          int lo = c * R, hi = min(nb, (c + 1) * R) - 1;
+          while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s_ptr[mid] <= p) lo = mid; else hi = mid - 1;
+          }
+          if (band_start + lo == j) w = 0.f;
+        }
+        sw[p] = w;
       }
     }
   };
@@ -174,93 +166,101 @@ __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* _
         float4 acc = (REDUCE == LGK_MAX) ? make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX) : f4_zero();
         int4 arg = make_int4(-1, -1, -1, -1);
 
-        for (int q = start & ~3; q < end; q += 8) {
-          unsigned off[8];
-          float w[8];
+        float4 acc2 = f4_zero();  // second accumulator chain of the sum
+        // a row = head (up to the first 16-byte aligned slot) + blocks of eight aligned slots + tail
+        const int q0 = min(end, (start + 3) & ~3);
+        const int qe = staged ? q0 + ((end - q0) & ~7) : q0;
+        // ---- main loop: eight staged entries per step, no predicates; a stored self loop that is to be dropped
+        // already carries weight 0
+#pragma unroll 1
+        for (int q = q0; q < qe; q += 8) {
+          const uint4 ja = *reinterpret_cast<const uint4*>(so + (q - base));
+          const uint4 jb = *reinterpret_cast<const uint4*>(so + (q - base) + 4);
+          const unsigned off[8] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w};
           float4 v[8];
-          // row offsets (and weights) of two aligned quads
-          {
-            uint4 ja, jb = make_uint4(0, 0, 0, 0);
-            float4 wa = make_float4(1.f, 1.f, 1.f, 1.f), wb = wa;
-            const bool second = q + 4 < end;
-            if (staged) {
-              ja = *reinterpret_cast<const uint4*>(so + (q - base));
-              if (second) jb = *reinterpret_cast<const uint4*>(so + (q - base) + 4);
-              if (WEIGHTED) {
-                wa = *reinterpret_cast<const float4*>(sw + (q - base));
-                if (second) wb = *reinterpret_cast<const float4*>(sw + (q - base) + 4);
-              }
-            } else {  // chunk with more edges than a staging buffer holds (very high degrees): read through L1
-              const int4 ia = load_idx4(a.idx, q, e1);
-              int4 ib = make_int4(0, 0, 0, 0);
-              if (second) ib = load_idx4(a.idx, q + 4, e1);
-              if (WEIGHTED) {
-                const int jj[8] = {ia.x, ia.y, ia.z, ia.w, ib.x, ib.y, ib.z, ib.w};
-                float ww[8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) ww[k] = (q + k >= start && q + k < end) ? edge_weight(a, q + k, jj[k]) : 0.f;
-                wa = make_float4(ww[0], ww[1], ww[2], ww[3]);
-                wb = make_float4(ww[4], ww[5], ww[6], ww[7]);
-              }
-              ja = make_uint4(unsigned(ia.x) * F4, unsigned(ia.y) * F4, unsigned(ia.z) * F4, unsigned(ia.w) * F4);
-              jb = make_uint4(unsigned(ib.x) * F4, unsigned(ib.y) * F4, unsigned(ib.z) * F4, unsigned(ib.w) * F4);
-            }
-            off[0] = ja.x; off[1] = ja.y; off[2] = ja.z; off[3] = ja.w; off[4] = jb.x; off[5] = jb.y; off[6] = jb.z; off[7] = jb.w;
-            w[0] = wa.x; w[1] = wa.y; w[2] = wa.z; w[3] = wa.w; w[4] = wb.x; w[5] = wb.y; w[6] = wb.z; w[7] = wb.w;
-          }
-          const bool full = (q >= start) && (q + 8 <= end);
-          bool ok[8];
-          if (full) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              ok[k] = true;
-              v[k] = Vec4<T>::gather(xv + size_t(off[k]) * 4, 0);
-            }
-          } else {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              ok[k] = (q + k >= start) && (q + k < end);
-              v[k] = Vec4<T>::gather_if(xv + size_t(ok[k] ? off[k] : 0u) * 4, 0, ok[k]);
-            }
-          }
+          for (int k = 0; k < 8; ++k) v[k] = Vec4<T>::gather(xv + size_t(off[k]) * 4, 0);
           if (REDUCE == LGK_MAX) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-              if (ok[k]) {
-                const int slot = q + k;
-                if (v[k].x > acc.x) { acc.x = v[k].x; arg.x = slot; }
-                if (v[k].y > acc.y) { acc.y = v[k].y; arg.y = slot; }
-                if (v[k].z > acc.z) { acc.z = v[k].z; arg.z = slot; }
-                if (v[k].w > acc.w) { acc.w = v[k].w; arg.w = slot; }
-              }
+              const int slot = q + k;
+              if (v[k].x > acc.x) { acc.x = v[k].x; arg.x = slot; }
+              if (v[k].y > acc.y) { acc.y = v[k].y; arg.y = slot; }
+              if (v[k].z > acc.z) { acc.z = v[k].z; arg.z = slot; }
+              if (v[k].w > acc.w) { acc.w = v[k].w; arg.w = slot; }
+            }
+          } else if (WEIGHTED) {
+            const float4 wa = *reinterpret_cast<const float4*>(sw + (q - base));
+            const float4 wb = *reinterpret_cast<const float4*>(sw + (q - base) + 4);
+            const float w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+            for (int k = 0; k < 8; k += 2) {
+              f4_fma(acc, w[k], v[k]);
+              f4_fma(acc2, w[k + 1], v[k + 1]);
             }
           } else {
-            // pairwise tree over the step: every gather is needed before the chain into acc can finish, which
-            // keeps the eight loads in flight together; predicated-off gathers are exact zeros
-            if (WEIGHTED) {
-              // first tree level as multiply + FMA: v[k] = w[k] v[k] + w[k+1] v[k+1]
 #pragma unroll
-              for (int k = 0; k < 8; k += 2) {
-                const float w0 = (!ok[k] || off[k] == self_off) ? 0.f : w[k];  // stored self loop: dropped
-                const float w1 = (!ok[k + 1] || off[k + 1] == self_off) ? 0.f : w[k + 1];
-                v[k].x = fmaf(w1, v[k + 1].x, w0 * v[k].x); v[k].y = fmaf(w1, v[k + 1].y, w0 * v[k].y);
-                v[k].z = fmaf(w1, v[k + 1].z, w0 * v[k].z); v[k].w = fmaf(w1, v[k + 1].w, w0 * v[k].w);
+            for (int k = 0; k < 8; k += 2) {
+              acc.x += v[k].x; acc.y += v[k].y; acc.z += v[k].z; acc.w += v[k].w;
+              acc2.x += v[k + 1].x; acc2.y += v[k + 1].y; acc2.z += v[k + 1].z; acc2.w += v[k + 1].w;
+            }
+          }
+        }
+        // ---- head and tail (and every slot of a chunk that was too large to stage): up to eight slots per step,
+        // predicated
+        if (start < q0 || qe < end)
+#pragma unroll 1
+        for (int part = 0; part < 2; ++part) {
+          const int lo = part ? qe : start, hi = part ? end : q0;
+#pragma unroll 1
+          for (int q = lo; q < hi; q += 8) {
+            unsigned off[8];
+            float w[8];
+            bool ok[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) ok[k] = q + k < hi;
+            if (staged) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                off[k] = ok[k] ? so[q - base + k] : 0u;
+                w[k] = ok[k] ? (WEIGHTED ? sw[q - base + k] : 1.f) : 0.f;
+              }
+            } else {  // read through L1
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                const int j = ok[k] ? __ldg(a.idx + q + k) : 0;
+                off[k] = unsigned(j) * F4;
+                w[k] = ok[k] ? 1.f : 0.f;
+                if (WEIGHTED && ok[k]) w[k] = (off[k] == self_off) ? 0.f : edge_weight(a, q + k, j);
+              }
+            }
+            float4 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              v[k] = f4_zero();
+              if (ok[k]) v[k] = Vec4<T>::gather(xv + size_t(off[k]) * 4, 0);
+            }
+            if (REDUCE == LGK_MAX) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                if (ok[k]) {
+                  const int slot = q + k;
+                  if (v[k].x > acc.x) { acc.x = v[k].x; arg.x = slot; }
+                  if (v[k].y > acc.y) { acc.y = v[k].y; arg.y = slot; }
+                  if (v[k].z > acc.z) { acc.z = v[k].z; arg.z = slot; }
+                  if (v[k].w > acc.w) { acc.w = v[k].w; arg.w = slot; }
+                }
               }
             } else {
 #pragma unroll
               for (int k = 0; k < 8; k += 2) {
-                v[k].x += v[k + 1].x; v[k].y += v[k + 1].y; v[k].z += v[k + 1].z; v[k].w += v[k + 1].w;
+                f4_fma(acc, w[k], v[k]);
+                f4_fma(acc2, w[k + 1], v[k + 1]);
               }
             }
-#pragma unroll
-            for (int s = 2; s < 8; s <<= 1)
-#pragma unroll
-              for (int k = 0; k < 8; k += 2 * s) {
-                v[k].x += v[k + s].x; v[k].y += v[k + s].y; v[k].z += v[k + s].z; v[k].w += v[k + s].w;
-              }
-            acc.x += v[0].x; acc.y += v[0].y; acc.z += v[0].z; acc.w += v[0].w;
           }
         }
+        if (REDUCE != LGK_MAX) { acc.x += acc2.x; acc.y += acc2.y; acc.z += acc2.z; acc.w += acc2.w; }
 
         float4 r = acc;
         const size_t ro = size_t(unsigned(row) * F4) * 4;
@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* _
           if (arg.z < 0) r.z = 0.f;
           if (arg.w < 0) r.w = 0.f;
           if (a.arg_out) st_stream_i4(reinterpret_cast<int4*>(a.arg_out + ro + vec * 4), arg);
-        } else {
+        } else if (EPI) {  // any of: mean, post-scale, self term (bias below)
           float scale = 1.f;
           if (REDUCE == LGK_MEAN) scale = 1.f / float(max(end - start, 1));
           if (a.post) scale *= __ldg(a.post + row);
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* _
           }
           r.x *= scale; r.y *= scale; r.z *= scale; r.w *= scale;
         }
-        if (a.bias) {
+        if (EPI && a.bias) {
           float4 b = __ldg(reinterpret_cast<const float4*>(a.bias) + vec);
           r.x += b.x; r.y += b.y; r.z += b.z; r.w += b.w;
         }
@@ -413,6 +413,7 @@ __global__ void __launch_bounds__(256) gcn_norm_kernel(const int* __restrict__ r
 struct SpmmTuning {
   int threads, max_slice4, waves;
   int64_t max_band;
+  int carveout;  // preferred shared-memory carve-out in percent (-1: driver default)
 };
 int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
@@ -420,8 +421,21 @@ int env_int(const char* name, int dflt) {
 }
 const SpmmTuning& tuning() {
   static const SpmmTuning t = {env_int("LGK_SPMM_THREADS", 512), env_int("LGK_SPMM_SLICE4", 32), env_int("LGK_SPMM_WAVES", 16),
-                               int64_t(env_int("LGK_SPMM_MAX_BAND", kMaxBand))};
+                               int64_t(env_int("LGK_SPMM_MAX_BAND", kMaxBand)), env_int("LGK_SPMM_CARVEOUT", -1)};
   return t;
+}
+
+// The gathers live on L1 hits: ask for the smallest shared-memory carve-out that still holds the resident CTAs'
+// staging buffers, once per instantiation (a function attribute, not a device-wide setting).
+template <typename T, int LPR, int REDUCE, bool WEIGHTED, bool EPI>
+void launch_vec(dim3 grid, int threads, size_t smem, cudaStream_t stream, const SpmmArgs& a, const T* x, T* out) {
+  static const bool once = [] {
+    const int pct = tuning().carveout;
+    if (pct >= 0) cudaFuncSetAttribute(spmm_vec_kernel<T, LPR, REDUCE, WEIGHTED, EPI>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    return true;
+  }();
+  (void)once;
+  spmm_vec_kernel<T, LPR, REDUCE, WEIGHTED, EPI><<<grid, threads, smem, stream>>>(a, x, out);
 }
 
 template <typename T, int REDUCE>
@@ -449,11 +463,13 @@ int launch_spmm(const SpmmArgs& a_in, const void* x_, void* out_, cudaStream_t s
     a.ptr_words = int((band + 1 + 3) & ~int64_t(3));
     dim3 grid(unsigned(ceil_div(a.n_rows, band)), unsigned(nslice));
     const bool weighted = REDUCE != LGK_MAX && (a.ew || a.pre || a.self_mode == LGK_SELF_REPLACE);
+    const bool epi = REDUCE == LGK_MEAN || a.post || a.bias || a.self_mode != LGK_SELF_NONE;
     const size_t smem = 4 * (size_t(a.ptr_words) + size_t(kStageBufs) * (threads * kIdRegs + 8) * (weighted ? 2 : 1));
 #define LGK_SPMM_CASE(LPR)                                                                             \
   case LPR:                                                                                            \
-    if (weighted) spmm_vec_kernel<T, LPR, REDUCE, true><<<grid, threads, smem, stream>>>(a, x, out);   \
-    else spmm_vec_kernel<T, LPR, REDUCE, false><<<grid, threads, smem, stream>>>(a, x, out);           \
+    if (weighted) launch_vec<T, LPR, REDUCE, true, true>(grid, threads, smem, stream, a, x, out);        \
+    else if (epi) launch_vec<T, LPR, REDUCE, false, true>(grid, threads, smem, stream, a, x, out);       \
+    else launch_vec<T, LPR, REDUCE, false, false>(grid, threads, smem, stream, a, x, out);               \
     break;
     switch (lpr) {
       LGK_SPMM_CASE(1) LGK_SPMM_CASE(2) LGK_SPMM_CASE(4) LGK_SPMM_CASE(8) LGK_SPMM_CASE(16) LGK_SPMM_CASE(32)

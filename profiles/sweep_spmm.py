@@ -50,7 +50,7 @@ def child(graphs: int):
         return e0.elapsed_time(e1) / iters * 1e3
 
     plain = 2 * N * F * 4 + 4 * E + 4 * (N + 1)
-    out = {"cfg": {k_: os.environ.get(k_) for k_ in ("LGK_SPMM_THREADS", "LGK_SPMM_SLICE4", "LGK_SPMM_WAVES", "LGK_SPMM_MAX_BAND", "LGK_SPMM_PREFETCH")}}
+    out = {"cfg": {k_: os.environ.get(k_) for k_ in ("LGK_SPMM_THREADS", "LGK_SPMM_SLICE4", "LGK_SPMM_WAVES", "LGK_SPMM_MAX_BAND", "LGK_SPMM_CARVEOUT")}}
     us = t(lambda: ops.spmm(g.rowptr, g.col, x, "sum"))
     out["sum_us"], out["sum_GBs"] = round(us, 1), round(plain / us / 1e3, 1)
     us = t(lambda: ops.spmm(g.rowptr, g.col, x, "sum", pre=dinv, post=dinv, self_mode=ops.SELF_REPLACE))
@@ -71,13 +71,11 @@ def child(graphs: int):
 def main():
     graphs = int(sys.argv[1]) if len(sys.argv) > 1 else 128
     grid = []
-    for pf, slice4, threads, waves in itertools.product((2, 3, 0), (32,), (512,), (8, 16)):
-        grid.append((threads, slice4, waves, 2044, pf))
-    grid.append((512, 32, 16, 2044, 30))
-    grid.append((512, 32, 16, 2044, 38))
+    for carve in (-1, 25, 40, 60):
+        grid.append((512, 32, 16, 2044, carve))
     for threads, slice4, waves, max_band, pf in grid:
         env = dict(os.environ, LGK_SPMM_THREADS=str(threads), LGK_SPMM_SLICE4=str(slice4), LGK_SPMM_WAVES=str(waves),
-                   LGK_SPMM_MAX_BAND=str(max_band), LGK_SPMM_PREFETCH=str(pf % 10), LGK_SPMM_PFDIST=str(pf // 10 if pf >= 10 else 3))
+                   LGK_SPMM_MAX_BAND=str(max_band), LGK_SPMM_CARVEOUT=str(pf))
         r = subprocess.run([sys.executable, __file__, "--child", str(graphs)], env=env, capture_output=True, text=True)
         line = r.stdout.strip().splitlines()[-1] if r.stdout.strip() else "ERR " + r.stderr[-300:]
         print(line, flush=True)
