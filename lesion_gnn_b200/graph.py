@@ -22,7 +22,7 @@ class CSRGraph:
     """rowptr/col/perm: CSR by destination, entries ordered by (dst, src, original edge id).
     colptr/row/csr2csc: CSC by source, entries ordered by CSR slot.  value: edge weights in CSR order."""
 
-    __slots__ = ("num_nodes", "num_edges", "rowptr", "col", "perm", "colptr", "row", "csr2csc", "value", "_norm")
+    __slots__ = ("num_nodes", "num_edges", "rowptr", "col", "perm", "colptr", "row", "csr2csc", "value", "_norm", "_ready")
 
     def __init__(self, num_nodes, num_edges, rowptr, col, perm, colptr=None, row=None, csr2csc=None, value=None):
         self.num_nodes, self.num_edges = int(num_nodes), int(num_edges)
@@ -30,12 +30,23 @@ class CSRGraph:
         self.colptr, self.row, self.csr2csc = colptr, row, csr2csc
         self.value = value
         self._norm = {}
+        self._ready = None  # event recorded on the stream that built the graph (from_edge_index(..., stream=))
 
     @staticmethod
     def from_edge_index(edge_index: Tensor, num_nodes: int, edge_weight: Optional[Tensor] = None,
-                        with_csc: bool = True) -> "CSRGraph":
+                        with_csc: bool = True, stream: Optional["torch.cuda.Stream"] = None) -> "CSRGraph":
+        """`stream`: build on that stream, forked from the current one (the build overlaps whatever the current
+        stream does next, e.g. the in_proj transform, which does not need the graph); the first layer that uses
+        the graph joins it (`join()`, called by `as_graph`)."""
         if not edge_index.is_cuda:
             raise RuntimeError("edge_index must be a CUDA tensor: lesion_gnn_b200 has no CPU path")
+        if stream is not None:
+            stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(stream):
+                g = CSRGraph.from_edge_index(edge_index, num_nodes, edge_weight, with_csc)
+                g._ready = torch.cuda.Event()
+                g._ready.record(stream)
+            return g
         if edge_index.dtype != torch.int64:
             edge_index = edge_index.long()
         edge_index = edge_index.contiguous()
@@ -44,6 +55,18 @@ class CSRGraph:
         if edge_weight is not None:
             g.value = g.permute_edge_values(edge_weight)
         return g
+
+    def join(self) -> "CSRGraph":
+        """make the current stream wait for a graph that was built on another stream (no-op otherwise)"""
+        ev = self._ready
+        if ev is not None:
+            self._ready = None
+            cur = torch.cuda.current_stream()
+            cur.wait_event(ev)
+            for t in (self.rowptr, self.col, self.perm, self.colptr, self.row, self.csr2csc, self.value):
+                if t is not None:
+                    t.record_stream(cur)  # allocated on the build stream, used on this one
+        return self
 
     def permute_edge_values(self, edge_weight: Tensor) -> Tensor:
         """per-edge values in original edge order -> CSR slot order (SparseTensor `value`)"""
@@ -90,7 +113,7 @@ def as_graph(edge_index, num_nodes: int, edge_weight: Optional[Tensor] = None) -
             raise ValueError("pass edge weights through CSRGraph.value when handing a CSRGraph to a layer")
         if edge_index.num_nodes != num_nodes:
             raise ValueError(f"graph has {edge_index.num_nodes} nodes but x has {num_nodes} rows")
-        return edge_index
+        return edge_index.join()
     k = _key(edge_index, (int(num_nodes),))
     hit = _CACHE.get(k)
     if hit is None:

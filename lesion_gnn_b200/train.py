@@ -124,11 +124,13 @@ class DeviceBatch:
             self.edge_weight.copy_(hb.edge_weight, non_blocking=True)
 
 
-def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_classes: int) -> Tensor:
-    """CSR/CSC build + segment pointer + forward + loss + backward for the batch resident in `db`"""
-    graph = CSRGraph.from_edge_index(db.edge_index, db.num_nodes, db.edge_weight)
+def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_classes: int, build_stream=None) -> Tensor:
+    """CSR/CSC build + segment pointer + forward + loss + backward for the batch resident in `db`.  With
+    `build_stream` the CSR/CSC build runs beside the model's first transform (in_proj needs no graph)."""
+    graph = CSRGraph.from_edge_index(db.edge_index, db.num_nodes, db.edge_weight, stream=build_stream)
     seg = Segments.from_batch(db.batch, db.num_graphs)
     logits = model(db.x, graph, seg)
+    graph.join()  # a model that never touched the graph must still join the build stream
     loss = loss_fn(logits, db.y, loss_type, num_classes)
     (loss * db.loss_weight if db.loss_weight != 1.0 else loss).backward()
     return loss.detach()
@@ -149,6 +151,7 @@ class TrainStep:
         self.pg, self.world_size = process_group, world_size
         self._graphs = {}
         self._side = torch.cuda.Stream() if torch.cuda.is_available() else None
+        self._build = torch.cuda.Stream() if torch.cuda.is_available() else None
 
     def _body(self, db: DeviceBatch) -> Tensor:
         self.opt.zero_grad()
@@ -156,7 +159,7 @@ class TrainStep:
         # autograd `add` launches); the bucket was just zeroed, so this equals plain accumulation
         # ... and run on a side stream, overlapping the main backward chain; joined before the optimiser reads them
         with direct_param_grads(), side_stream(self._side):
-            loss = forward_backward(self.model, db, self.loss_type, self.num_classes)
+            loss = forward_backward(self.model, db, self.loss_type, self.num_classes, self._build)
         if self.world_size == 1:
             self.opt.step()
         return loss

@@ -68,6 +68,24 @@ def test_csr_is_deterministic(dev):
         assert all(torch.equal(x, y) for x, y in zip(a, b))
 
 
+def test_csr_built_on_a_side_stream_joins_on_first_use(dev):
+    """CSRGraph.from_edge_index(stream=...) forks the build; as_graph joins it before a layer reads it"""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200.graph import as_graph
+    ei = random_graph(3000, 40000, 21).to(dev)
+    ref = lg.CSRGraph.from_edge_index(ei, 3000)
+    side = torch.cuda.Stream()
+    for _ in range(3):
+        g = lg.CSRGraph.from_edge_index(ei, 3000, stream=side)
+        assert g._ready is not None
+        g2 = as_graph(g, 3000)
+        assert g2 is g and g._ready is None
+        x = torch.ones(3000, 8, device=dev)
+        out = lg.ops.spmm(g.rowptr, g.col, x, "sum")
+        assert torch.equal(out[:, 0].cpu().long(), (ref.rowptr[1:] - ref.rowptr[:-1]).cpu().long())
+        assert torch.equal(g.col, ref.col) and torch.equal(g.csr2csc, ref.csr2csc)
+
+
 @pytest.mark.parametrize("counts", [[3, 0, 5, 1], [0, 0, 4], [7], [1] * 50, [2, 3, 0, 0]])
 def test_batch_ptr_with_empty_graphs(dev, counts):
     from lesion_gnn_b200 import ops
