@@ -57,6 +57,20 @@ def peaks():
     return 6650.0, "fallback"
 
 
+def measured_traffic(name: str, tag: str):
+    """ncu `dram__bytes_read.sum + dram__bytes_write.sum` per launch for an entry point, from the newest
+    profiles/r*/traffic.json that has it (one `ncu --set full` capture per round); None if never captured"""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", "traffic.json")), reverse=True):
+        try:
+            hit = json.load(open(path)).get(f"{name}|{tag}")
+        except (OSError, ValueError):
+            continue
+        if hit:
+            return int(hit["bytes"])
+    return None
+
+
 def make_host_batches(rank: int, count: int, with_edges_on=None):
     """`count` distinct synthetic batches for this rank; kNN edges are built on `with_edges_on` (a CUDA device,
     lgk_knn_graph) or by the oracle on the CPU (reference arm) -- graph construction is outside the timed step,
@@ -345,7 +359,8 @@ def run_b200(args):
     (dom_name, dom_tag), dom = top[0]
     achieved = (dom["bytes"] / dom["calls"]) / (dom["ms"] / dom["calls"] * 1e-3) / 1e9
     roofline = {"kernel": dom_name, "shape": dom_tag, "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
-                "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
+                "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                "traffic": measured_traffic(dom_name, dom_tag),
                 "bytes_per_launch": dom["bytes"] // dom["calls"], "us_per_launch": round(1e3 * dom["ms"] / dom["calls"], 2),
                 "share_of_step_kernel_time": round(dom["ms"] / kern_total, 3)}
 

@@ -26,6 +26,7 @@ att = torch.randn(128, device=dev) * 0.1
 a_s, a_d = ops.gat_alpha(x, att, att, 4, 32)
 xin = torch.randn(11583, 1025, device=dev)
 w = torch.randn(64, 1025, device=dev)
+dyin = torch.randn(11583, 64, device=dev)
 for _ in range(reps):
     ops.spmm(g.rowptr, g.col, x, "sum")
     ops.spmm(g.rowptr, g.col, x, "sum", pre=dinv, post=dinv, self_mode=ops.SELF_REPLACE)
@@ -34,6 +35,7 @@ for _ in range(reps):
     ops.gat_fwd(g.rowptr, g.col, x, a_s, a_d, None, 4, 32, 0.2, True)
     ops.pool_fwd(x, seg.ptr, True, True, True)
     ops.linear_fwd(xin, w)
+    ops.linear_bwd_w(dyin, xin)
     lg.CSRGraph.from_edge_index(ei, N)
 torch.cuda.synchronize()
 print("ok", N, ei.size(1))
