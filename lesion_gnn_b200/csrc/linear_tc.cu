@@ -26,6 +26,7 @@
 // dependency chains instead of one.  Tensor memory: 2 buffers x 4 accumulators x 64 columns.
 #include "common.cuh"
 #include "umma.cuh"
+#include <stdlib.h>
 
 namespace lgk {
 namespace {
@@ -55,6 +56,7 @@ struct TcArgs {
   int act, accumulate;
   int64_t tiles_n;      // column tiles (fastest tile index)
   int64_t tiles_total;
+  int debug;  // profiling only (LGK_TC_DEBUG): 1 = no MMAs, 2 = no conversion, 4 = no global copies (bit mask)
 };
 
 struct Bars {
@@ -222,19 +224,27 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
         const int s = it % kTileStages;
         umma::mbar_wait(bars->tile_full + s, (it / kTileStages) & 1);
         umma::tc_fence_after();
-        if (lane == 0) {
+        if (lane == 0 && (g.debug & 1)) {
+          umma::mma_commit(bars->tile_empty + s);
+          if (kb == nkb - 1) umma::mma_commit(bars->acc_full + ab);
+        } else if (lane == 0) {
           const uint32_t sa = tiles + s * kTileBytes;
           const uint64_t a_hi = umma::smem_desc_k_sw128(sa), a_lo = umma::smem_desc_k_sw128(sa + kTileA);
           const uint64_t b_hi = umma::smem_desc_k_sw128(sa + 2 * kTileA), b_lo = umma::smem_desc_k_sw128(sa + 2 * kTileA + kTileB);
           // Dependent MMAs on one accumulator serialise with their full latency (~240 cycles each at this tile
-          // size), so the four K steps of a block go to four different accumulators: four independent chains.
+          // size), so the four K steps of a block go to four different accumulators AND the issue order is
+          // term-major: consecutive instructions always target different accumulators, a dependent one follows
+          // four issue slots later.  Per accumulator the order of additions (lo*hi, hi*lo, hi*hi) is unchanged.
 #pragma unroll
-          for (int kk = 0; kk < BK / 8; ++kk) {
-            const uint32_t acc = tmem_base + (ab * kAcc + uint32_t(kk)) * BN;
-            const uint64_t adv = uint64_t(kk * 32 >> 4);  // +32 bytes along K inside the 128-byte swizzled row
-            umma::mma_tf32(acc, a_lo + adv, b_hi + adv, idesc, kb > 0);  // small terms first
-            umma::mma_tf32(acc, a_hi + adv, b_lo + adv, idesc, true);
-            umma::mma_tf32(acc, a_hi + adv, b_hi + adv, idesc, true);
+          for (int term = 0; term < 3; ++term) {
+#pragma unroll
+            for (int kk = 0; kk < BK / 8; ++kk) {
+              const uint32_t acc = tmem_base + (ab * kAcc + uint32_t(kk)) * BN;
+              const uint64_t adv = uint64_t(kk * 32 >> 4);  // +32 bytes along K inside the 128-byte swizzled row
+              if (term == 0) umma::mma_tf32(acc, a_lo + adv, b_hi + adv, idesc, kb > 0);  // small terms first
+              else if (term == 1) umma::mma_tf32(acc, a_hi + adv, b_lo + adv, idesc, true);
+              else umma::mma_tf32(acc, a_hi + adv, b_hi + adv, idesc, true);
+            }
           }
           umma::mma_commit(bars->tile_empty + s);                      // frees the tile when these MMAs have read it
           if (kb == nkb - 1) umma::mma_commit(bars->acc_full + ab);    // all accumulators of the tile complete
@@ -279,7 +289,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
       tile_of_ctx = lt;
     };
     auto issue = [&](int64_t q) {
-      if (q < total) {
+      if (q < total && !(g.debug & 4)) {
         const int64_t lt = q / nkb;
         if (lt != tile_of_ctx) set_tile(lt);
         issue_block(g, c, raws + uint32_t(q % kRawStages) * kRawBytes, lane, (q - lt * nkb) * BK);
@@ -291,7 +301,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
       cp_async_wait<kRawStages - 1>();  // this thread's copies of block q have landed
       const int ts = int(q % kTileStages);
       umma::mbar_wait(bars->tile_empty + ts, uint32_t((q / kTileStages) & 1) ^ 1);
-      convert_block(c, raws + uint32_t(q % kRawStages) * kRawBytes, tiles + ts * kTileBytes);
+      if (!(g.debug & 2)) convert_block(c, raws + uint32_t(q % kRawStages) * kRawBytes, tiles + ts * kTileBytes);
       umma::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(bars->tile_full + ts);
@@ -331,7 +341,9 @@ int launch_linear_tc(const float* x, const float* w, const float* bias, const fl
     }
     configured = true;
   }
-  TcArgs g{x, w, bias, rowscale, out, n, k, m, act, accumulate, 0, 0};
+  TcArgs g{x, w, bias, rowscale, out, n, k, m, act, accumulate, 0, 0, 0};
+  static const int debug = [] { const char* v = getenv("LGK_TC_DEBUG"); return (v && *v) ? atoi(v) : 0; }();
+  g.debug = debug;
   g.tiles_n = ceil_div(m, BN);
   g.tiles_total = ceil_div(n, BM) * g.tiles_n;
   const unsigned grid = unsigned(g.tiles_total < kNumSMs ? g.tiles_total : kNumSMs);
