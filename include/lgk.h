@@ -196,6 +196,15 @@ LGK_API int lgk_pool_fwd(const void* x, const int32_t* ptr, void* out_sum, int m
 LGK_API int lgk_pool_bwd(const void* dsum, int mean, const void* dmax, const int32_t* arg, const int32_t* ptr, void* dx,
                  int64_t num_nodes, int64_t num_graphs, int64_t feat, int dtype, void* stream);
 
+/* SortAggregation(k) (torch_geometric.nn.aggr.SortAggregation; reference models/drgnet.py:37,59):
+ * per graph, nodes ordered by their LAST channel, descending, stable (ties: lower node index first; NaN first, as
+ * torch.sort); out[g, r*F:(r+1)*F] = x[node of rank r, :] for r < min(k, n_g), zeros beyond;
+ * sel[g, r] = that node's index or -1.  The backward writes dx (zero-filled here) through `sel`.          */
+LGK_API int lgk_sort_pool_fwd(const void* x, const int32_t* ptr, void* out, int32_t* sel,
+                      int64_t num_graphs, int64_t feat, int64_t k, int dtype, void* stream);
+LGK_API int lgk_sort_pool_bwd(const void* dy, const int32_t* sel, void* dx,
+                      int64_t num_nodes, int64_t num_graphs, int64_t feat, int64_t k, int dtype, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * (5) node-feature transform (the torch_geometric Linear inside every conv: `lin`, `lin_l`, `lin_r`,
  *     `lin_rel`, `lin_root`, MLP.lins; reference models/gat.py:29,31,46, gin.py:21,23,25)

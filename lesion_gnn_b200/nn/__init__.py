@@ -1,9 +1,9 @@
 from .conv import GATConv, GCNConv, GINConv, GraphConv, SAGEConv, MLP, Linear, BatchNorm
-from .pool import Segments, global_add_pool, global_max_pool, global_mean_pool, global_mean_max_pool
-from .functional import elu, aggregate, gat_attention, linear, segment_pool
+from .pool import Segments, SortAggregation, global_add_pool, global_max_pool, global_mean_pool, global_mean_max_pool
+from .functional import elu, aggregate, gat_attention, linear, segment_pool, sort_pool
 
 __all__ = [
     "GATConv", "GCNConv", "GINConv", "GraphConv", "SAGEConv", "MLP", "Linear", "BatchNorm",
-    "Segments", "global_add_pool", "global_max_pool", "global_mean_pool", "global_mean_max_pool",
-    "elu", "aggregate", "gat_attention", "linear", "segment_pool",
+    "Segments", "SortAggregation", "global_add_pool", "global_max_pool", "global_mean_pool", "global_mean_max_pool",
+    "elu", "aggregate", "gat_attention", "linear", "segment_pool", "sort_pool",
 ]

@@ -324,3 +324,24 @@ class _Pool(torch.autograd.Function):
 
 def segment_pool(x: Tensor, ptr: Tensor, mode: str) -> Tensor:
     return _Pool.apply(x, ptr, mode)
+
+
+class _SortPool(torch.autograd.Function):
+    """SortAggregation(k): saves only the [B, k] selection"""
+
+    @staticmethod
+    def forward(ctx, x, ptr, k):
+        out, sel = ops.sort_pool_fwd(x.contiguous(), ptr, k)
+        ctx.save_for_backward(sel)
+        ctx.shape = x.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        (sel,) = ctx.saved_tensors
+        n, f = ctx.shape
+        return ops.sort_pool_bwd(dy.contiguous(), sel, n, f), None, None
+
+
+def sort_pool(x: Tensor, ptr: Tensor, k: int) -> Tensor:
+    return _SortPool.apply(x, ptr, int(k))

@@ -60,3 +60,23 @@ def global_max_pool(x: Tensor, batch, size: Optional[int] = None) -> Tensor:
 def global_mean_max_pool(x: Tensor, batch, size: Optional[int] = None) -> Tensor:
     """cat([global_mean_pool, global_max_pool], dim=1) in one pass over x"""
     return _pool(x, batch, size, "mean+max")
+
+
+class SortAggregation(torch.nn.Module):
+    """torch_geometric.nn.aggr.SortAggregation(k) as the reference calls it (models/drgnet.py:37,59):
+    `sort_pool(x, batch)` -> [B, k * F], nodes of each graph ordered by their last channel (descending, stable),
+    first k kept, zero padded.  One lgk_sort_pool_fwd launch instead of to_dense_batch + sort + gather."""
+
+    def __init__(self, k: int):
+        super().__init__()
+        self.k = int(k)
+
+    def forward(self, x: Tensor, index=None, ptr: Optional[Tensor] = None, dim_size: Optional[int] = None, dim: int = -2) -> Tensor:
+        if not x.is_cuda:
+            raise RuntimeError("x must be a CUDA tensor: lesion_gnn_b200 has no CPU path")
+        if dim not in (-2, 0) or x.dim() != 2:
+            raise NotImplementedError("SortAggregation is implemented for [N, F] node features")
+        return F.sort_pool(x, _ptr(index, x.size(0), dim_size, x.device), self.k)
+
+    def __repr__(self) -> str:
+        return f"SortAggregation(k={self.k})"

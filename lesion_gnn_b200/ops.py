@@ -247,6 +247,25 @@ def pool_bwd(dsum: Optional[Tensor], mean: bool, dmax: Optional[Tensor], arg: Op
     return dx
 
 
+def sort_pool_fwd(x: Tensor, ptr: Tensor, k: int):
+    """SortAggregation(k) -> (out [B, k*F], sel [B, k] int32 node index or -1)"""
+    L = _lib.lib()
+    n, f = x.shape
+    b = ptr.numel() - 1
+    out = torch.empty(b, k * f, dtype=x.dtype, device=x.device)
+    sel = torch.empty(b, k, dtype=torch.int32, device=x.device)
+    L.call("lgk_sort_pool_fwd", _chk(x, None, "x"), _chk(ptr, torch.int32, "ptr"), _chk(out), _chk(sel), b, f, int(k), _dt(x), _stream())
+    return out, sel
+
+
+def sort_pool_bwd(dy: Tensor, sel: Tensor, num_nodes: int, feat: int) -> Tensor:
+    L = _lib.lib()
+    b, k = sel.shape
+    dx = torch.empty(num_nodes, feat, dtype=dy.dtype, device=dy.device)
+    L.call("lgk_sort_pool_bwd", _chk(dy, None, "dy"), _chk(sel, torch.int32, "sel"), _chk(dx), num_nodes, b, feat, k, _dt(dy), _stream())
+    return dx
+
+
 # ------------------------------------------------------------------------------------------------- linear
 
 
