@@ -103,6 +103,15 @@ LGK_API int lgk_knn_graph(const void* pos, int pos_dtype, int dim, const int32_t
                   int64_t num_graphs, int64_t num_nodes, int k, int loop,
                   int64_t* edge_index_out, int64_t num_edges_total, void* stream);
 
+/* Radius graph (torch_cluster.radius_graph behind torch_geometric.transforms.RadiusGraph; reference
+ * scripts/sweep.py:113-117): for every centre i the nodes j of the same graph with |p_j - p_i|^2 < r^2 (distance in
+ * the dtype of pos), ascending node index, at most max_num_neighbors; the centre itself only if loop.
+ * Pass 1 (edge_index_out == NULL): counts[i] = number of neighbours kept.  Pass 2: offsets = exclusive scan of the
+ * counts (int64 [N]), edge_index_out int64 [2, E] (row 0 = src j, row 1 = dst i), E = total count.        */
+LGK_API int lgk_radius_graph(const void* pos, int pos_dtype, int dim, const int32_t* ptr, int64_t num_graphs, int64_t num_nodes,
+                     double r, int loop, int max_num_neighbors, int32_t* counts, const int64_t* offsets,
+                     int64_t* edge_index_out, int64_t num_edges_total, void* stream);
+
 /* Gaussian edge weights exp(-d^2 / 2 sigma^2) / sqrt(2 pi sigma^2) (reference src/lesion_gnn/transforms.py:50-58) */
 LGK_API int lgk_gaussian_distance(const void* pos, int pos_dtype, int dim, const int64_t* edge_index, int64_t num_edges,
                           double sigma, float* edge_weight, void* stream);

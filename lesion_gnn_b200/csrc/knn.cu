@@ -175,6 +175,67 @@ int launch_knn(const void* pos, int dim, const int* ptr, const int64_t* eptr, in
 
 using namespace lgk;
 
+// ---- radius graph (torch_cluster.radius_graph behind torch_geometric.transforms.RadiusGraph; reference
+// scripts/sweep.py:113-117): every j of the same graph with |p_j - p_i|^2 < r^2, in ascending index order, at most
+// max_nb per centre.  Two passes over the same scan: count, then (after an exclusive scan of the counts) fill.
+namespace lgk {
+namespace {
+template <typename P, bool FILL>
+__global__ void __launch_bounds__(128) radius_kernel(const P* __restrict__ pos, int dim, const int* __restrict__ ptr, int B,
+                                                     int64_t N, P r2, int loop, int max_nb, int* __restrict__ counts,
+                                                     const int64_t* __restrict__ offsets, int64_t* __restrict__ src_out,
+                                                     int64_t* __restrict__ dst_out) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int g = graph_of(ptr, B, int(i));
+  const int lo = ptr[g], hi = ptr[g + 1];
+  P pi[kMaxDim];
+  for (int d = 0; d < dim; ++d) pi[d] = pos[i * dim + d];
+  int cnt = 0;
+  const int64_t base = FILL ? offsets[i] : 0;
+  for (int j = lo; j < hi && cnt < max_nb; ++j) {
+    if (!loop && j == int(i)) continue;
+    P acc = P(0);
+    for (int d = 0; d < dim; ++d) acc = sq_add(acc, pi[d], pos[int64_t(j) * dim + d]);
+    if (acc < r2) {
+      if (FILL) {
+        src_out[base + cnt] = j;
+        dst_out[base + cnt] = i;
+      }
+      ++cnt;
+    }
+  }
+  if (!FILL) counts[i] = cnt;
+}
+}  // namespace
+}  // namespace lgk
+
+extern "C" int lgk_radius_graph(const void* pos, int pos_dtype, int dim, const int32_t* ptr, int64_t B, int64_t N, double r,
+                                int loop, int max_num_neighbors, int32_t* counts, const int64_t* offsets,
+                                int64_t* edge_index_out, int64_t E, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(B >= 0 && N >= 0 && E >= 0 && r >= 0 && max_num_neighbors > 0, LGK_ERR_BAD_ARG, "lgk_radius_graph: bad argument");
+  LGK_REQUIRE(dim > 0 && dim <= kMaxDim, LGK_ERR_UNSUPPORTED, "lgk_radius_graph: dim must be in [1, %d]", kMaxDim);
+  LGK_REQUIRE(pos_dtype == 0 || pos_dtype == 1, LGK_ERR_BAD_ARG, "lgk_radius_graph: pos_dtype must be 0 (f32) or 1 (f64)");
+  const bool fill = edge_index_out != nullptr;
+  LGK_REQUIRE(fill ? offsets != nullptr : counts != nullptr, LGK_ERR_BAD_ARG, "lgk_radius_graph: counts (pass 1) or offsets + edge_index_out (pass 2)");
+  if (N == 0 || (fill && E == 0)) return LGK_OK;
+  LGK_REQUIRE(pos && ptr, LGK_ERR_BAD_ARG, "lgk_radius_graph: null pointer");
+  const unsigned grid = unsigned(ceil_div(N, 128));
+  const double r2 = r * r;
+  if (pos_dtype == 0) {
+    const float* p = static_cast<const float*>(pos);
+    if (fill) radius_kernel<float, true><<<grid, 128, 0, stream>>>(p, dim, ptr, int(B), N, float(r2), loop, max_num_neighbors, nullptr, offsets, edge_index_out, edge_index_out + E);
+    else radius_kernel<float, false><<<grid, 128, 0, stream>>>(p, dim, ptr, int(B), N, float(r2), loop, max_num_neighbors, counts, nullptr, nullptr, nullptr);
+  } else {
+    const double* p = static_cast<const double*>(pos);
+    if (fill) radius_kernel<double, true><<<grid, 128, 0, stream>>>(p, dim, ptr, int(B), N, r2, loop, max_num_neighbors, nullptr, offsets, edge_index_out, edge_index_out + E);
+    else radius_kernel<double, false><<<grid, 128, 0, stream>>>(p, dim, ptr, int(B), N, r2, loop, max_num_neighbors, counts, nullptr, nullptr, nullptr);
+  }
+  LGK_CHECK_LAUNCH("radius_kernel");
+  return LGK_OK;
+}
+
 extern "C" int lgk_knn_edge_ptr(const int32_t* ptr, int64_t B, int k, int loop, int64_t* eptr, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(B >= 0 && k > 0 && ptr && eptr, LGK_ERR_BAD_ARG, "lgk_knn_edge_ptr: bad argument");

@@ -114,6 +114,29 @@ def knn_graph_raw(pos: Tensor, ptr: Tensor, k: int, loop: bool, num_edges: Optio
     return out
 
 
+def radius_graph_raw(pos: Tensor, ptr: Tensor, r: float, loop: bool, max_num_neighbors: int) -> Tensor:
+    """radius-graph edges for a collated batch (two passes: count, exclusive scan, fill).  The edge count depends on
+    the data, so this reads one int64 back from the device -- graph construction is outside the captured step."""
+    L = _lib.lib()
+    if pos.dim() != 2:
+        raise ValueError("pos must be [N, dim]")
+    if pos.dtype not in (torch.float32, torch.float64):
+        raise TypeError("pos must be float32 or float64")
+    B, N = ptr.numel() - 1, pos.size(0)
+    dt = 0 if pos.dtype == torch.float32 else 1
+    counts = torch.empty(N, dtype=torch.int32, device=pos.device)
+    L.call("lgk_radius_graph", _chk(pos, None, "pos"), dt, pos.size(1), _chk(ptr, torch.int32, "ptr"), B, N, float(r), int(loop),
+           int(max_num_neighbors), _chk(counts), None, None, 0, _stream())
+    incl = torch.cumsum(counts, 0, dtype=torch.int64)
+    num_edges = int(incl[-1].item()) if N > 0 else 0
+    out = torch.empty(2, num_edges, dtype=torch.int64, device=pos.device)
+    if num_edges > 0:
+        offsets = (incl - counts).contiguous()
+        L.call("lgk_radius_graph", _chk(pos, None, "pos"), dt, pos.size(1), _chk(ptr, torch.int32, "ptr"), B, N, float(r), int(loop),
+               int(max_num_neighbors), None, _chk(offsets, torch.int64, "offsets"), _chk(out), num_edges, _stream())
+    return out
+
+
 def gaussian_distance(pos: Tensor, edge_index: Tensor, sigma: float) -> Tensor:
     L = _lib.lib()
     E = edge_index.size(1)

@@ -34,6 +34,27 @@ def knn_graph(pos: Tensor, k: int, batch=None, loop: bool = False, flow: str = "
     return ops.knn_graph_raw(pos, ptr, k, loop, num_edges)
 
 
+def radius_graph(pos: Tensor, r: float, batch=None, loop: bool = False, max_num_neighbors: int = 32,
+                 flow: str = "source_to_target") -> Tensor:
+    """torch_cluster.radius_graph semantics (torch_geometric.transforms.RadiusGraph; reference scripts/sweep.py:113-117):
+    [2, E] int64, row 0 = neighbour (source), row 1 = centre (target); neighbours with |p_j - p_i| < r in ascending
+    index order, at most `max_num_neighbors` per centre."""
+    if flow != "source_to_target":
+        raise NotImplementedError("only flow='source_to_target' is on the reference's path")
+    if not pos.is_cuda:
+        raise RuntimeError("pos must be a CUDA tensor: lesion_gnn_b200 has no CPU path")
+    if pos.dim() == 1:
+        pos = pos.unsqueeze(-1)
+    pos = pos.contiguous()
+    if isinstance(batch, Segments):
+        ptr = batch.ptr
+    elif batch is None:
+        ptr = torch.tensor([0, pos.size(0)], dtype=torch.int32, device=pos.device)
+    else:
+        ptr = as_ptr(batch)[0]
+    return ops.radius_graph_raw(pos, ptr, r, loop, max_num_neighbors)
+
+
 def knn_num_edges(counts, k: int, loop: bool) -> int:
     """E of knn_graph from host-side graph sizes (avoids the device->host read)."""
     total = 0

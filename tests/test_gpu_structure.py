@@ -135,3 +135,24 @@ def test_gaussian_distance(dev):
     e2 = torch.tensor([[0, 1], [1, 0]], device=dev)
     for sigma, want in ((1.0, 0.2420), (0.5, 0.1080), (2.0, 0.1760)):
         assert torch.allclose(transforms.GaussianDistance(sigma)(p2, e2).cpu(), torch.full((2,), want), rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("r,loop,cap", [(150.0, False, 32), (150.0, True, 32), (400.0, False, 8), (5.0, False, 32), (4000.0, True, 32)])
+def test_radius_graph_bit_exact(dev, dtype, r, loop, cap):
+    """RadiusGraph (reference scripts/sweep.py:113-117) on the device == the oracle's torch_cluster restatement"""
+    from lesion_gnn_b200 import data, transforms
+    hb = data.synth_batch(9, "ddr", 4, seed=31)
+    pos = hb.pos.to(dtype)
+    ref = O.radius_graph(pos, r, hb.batch, loop=loop, max_num_neighbors=cap)
+    got = transforms.radius_graph(pos.to(dev), r, hb.batch.to(dev), loop=loop, max_num_neighbors=cap)
+    assert got.dtype == torch.int64 and torch.equal(got.cpu(), ref)
+
+
+def test_radius_graph_empty_and_single(dev):
+    from lesion_gnn_b200 import transforms
+    pos = torch.tensor([[0.0, 0.0], [3.0, 4.0], [100.0, 100.0]], dtype=torch.float64)
+    got = transforms.radius_graph(pos.to(dev), 5.0)  # |p0 - p1| = 5 exactly: strict <, no edge
+    assert got.shape == (2, 0)
+    got = transforms.radius_graph(pos.to(dev), 5.0001)
+    assert torch.equal(got.cpu(), torch.tensor([[1, 0], [0, 1]]))
