@@ -106,8 +106,46 @@ def clear_cache() -> None:
     _CACHE.clear()
 
 
+def _from_adj_t(adj) -> Optional[Tensor]:
+    """(edge_index, value) of an `adj_t`-style sparse adjacency (rows = destinations, reference models/gat.py:87-90):
+    a torch_sparse.SparseTensor-like object with `.csr()` -> (rowptr, col, value), or a torch sparse CSR / COO tensor."""
+    if isinstance(adj, Tensor):
+        if adj.layout == torch.sparse_csr:
+            rowptr, col, value = adj.crow_indices(), adj.col_indices(), adj.values()
+        elif adj.layout == torch.sparse_coo:
+            adj = adj.coalesce()
+            idx = adj.indices()
+            return torch.stack([idx[1], idx[0]]), adj.values()
+        else:
+            return None
+    elif hasattr(adj, "csr") and callable(adj.csr):
+        rowptr, col, value = adj.csr()
+    else:
+        return None
+    deg = (rowptr[1:] - rowptr[:-1]).long()
+    dst = torch.repeat_interleave(torch.arange(rowptr.numel() - 1, device=col.device), deg)
+    return torch.stack([col.long(), dst]), value
+
+
 def as_graph(edge_index, num_nodes: int, edge_weight: Optional[Tensor] = None) -> CSRGraph:
-    """CSRGraph for `edge_index` ([2,E] tensor or already a CSRGraph), memoised per tensor."""
+    """CSRGraph for `edge_index`: the [2,E] tensor, a CSRGraph, or an `adj_t` (torch_sparse.SparseTensor-like object
+    or torch sparse CSR/COO tensor whose rows are destinations); memoised per tensor."""
+    if not isinstance(edge_index, CSRGraph) and not (isinstance(edge_index, Tensor) and edge_index.layout == torch.strided):
+        conv = _from_adj_t(edge_index)
+        if conv is None:
+            raise TypeError(f"cannot interpret {type(edge_index).__name__} as a graph")
+        if edge_weight is not None:
+            raise ValueError("an adj_t carries its own values; do not pass edge_weight as well")
+        ei, value = conv
+        attr = getattr(edge_index, "_lgk_graph", None)  # memoised on the object when it allows attributes
+        if attr is not None and attr.num_nodes == num_nodes:
+            return attr.join()
+        g = CSRGraph.from_edge_index(ei.contiguous(), num_nodes, None if value is None or value.dim() != 1 else value.float())
+        try:
+            edge_index._lgk_graph = g
+        except AttributeError:
+            pass
+        return g
     if isinstance(edge_index, CSRGraph):
         if edge_weight is not None:
             raise ValueError("pass edge weights through CSRGraph.value when handing a CSRGraph to a layer")

@@ -267,3 +267,29 @@ def test_golden_vectors(dev):
             out.backward(rec["dy"].float().to(dev))
             assert_close(out, rec["out"], TOL_F32, f"{name}/pool_{red}")
             assert_close(xg.grad, rec["dx"], TOL_F32, f"{name}/pool_{red} dx")
+
+
+def test_layers_accept_adj_t_sparse_tensors(dev):
+    """reference models/gat.py:87-90 hands the models `adj_t` (a torch_sparse.SparseTensor, rows = destinations) when
+    compile=False: a torch sparse CSR tensor, a sparse COO tensor and any object with SparseTensor's `.csr()` work"""
+    import lesion_gnn_b200 as lg
+    from tests.util import random_graph
+    n = 300
+    ei = random_graph(n, 2500, 4, duplicates=False).to(dev)
+    w = torch.rand(ei.size(1), device=dev) + 0.1
+    x = torch.randn(n, 32, device=dev)
+    conv = lg.nn.GraphConv(32, 16).to(dev)
+    want = conv(x, ei, w)
+    g = lg.CSRGraph.from_edge_index(ei, n, w)
+    adj_csr = torch.sparse_csr_tensor(g.rowptr.long(), g.col.long(), g.value, size=(n, n))
+
+    class FakeSparseTensor:  # torch_sparse.SparseTensor's accessor
+        def csr(self):
+            return g.rowptr.long(), g.col.long(), g.value
+
+    for adj in (adj_csr, adj_csr.to_sparse_coo(), FakeSparseTensor()):
+        got = conv(x, adj)
+        assert torch.equal(got, want)
+    gcn = lg.nn.GCNConv(32, 8).to(dev)
+    unweighted = torch.sparse_csr_tensor(g.rowptr.long(), g.col.long(), torch.ones_like(g.value), size=(n, n))
+    assert_close(gcn(x, unweighted), gcn(x, ei, torch.ones_like(w)), 1e-6, "gcn adj_t")
