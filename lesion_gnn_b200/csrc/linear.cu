@@ -376,7 +376,9 @@ int launch_gemm(const GemmArgs& g, int splits, bool vec, cudaStream_t stream, co
 
 int choose_wsplits(int64_t n, int64_t k, int64_t m) {
   const int64_t tiles = ceil_div(k, BI) * ceil_div(m, BJ);
-  int64_t s = ceil_div(int64_t(kNumSMs) * 2, tiles);
+  // all CTAs of the split GEMM in ONE wave: 2 resident CTAs per SM (launch bounds), so at most 2 * 148 of them --
+  // rounding the split count up (9 tiles x 33 = 297 CTAs for in_proj) cost a second, nearly empty wave
+  int64_t s = int64_t(kNumSMs) * 2 / tiles;
   const int64_t cap = ceil_div(n, 4 * BR);  // at least 64 rows of the reduction per split
   if (s > cap) s = cap;
   if (s < 1) s = 1;
