@@ -55,17 +55,35 @@ _SIDE = [None]
 
 
 class side_stream:
+    """`stream`: one stream or a list of them.  With several, the kernels are dealt round-robin -- the parameter-gradient
+    chain of the headline step (three slab reductions, four column sums, three attention-vector reductions and the
+    in_proj dW) is longer than the main backward chain when it runs on a single stream -- except that all kernels adding
+    into the same gradient buffer (`key`) stay on one stream, i.e. ordered."""
+
     def __init__(self, stream):
-        self.stream, self.keep = stream, []
+        self.streams = list(stream) if isinstance(stream, (list, tuple)) else [stream]
+        self.keep, self._next, self._by_key = [], 0, {}
 
     def __enter__(self):
         self._old = _SIDE[0]
         _SIDE[0] = self
         return self
 
+    def pick(self, key=None):
+        if key is not None and key in self._by_key:
+            return self._by_key[key]
+        s = self.streams[self._next % len(self.streams)]
+        self._next += 1
+        if key is not None:
+            self._by_key[key] = s
+        return s
+
     def join(self):
-        torch.cuda.current_stream().wait_stream(self.stream)
+        cur = torch.cuda.current_stream()
+        for s in self.streams:
+            cur.wait_stream(s)
         self.keep.clear()
+        self._by_key.clear()
 
     def __exit__(self, *exc):
         self.join()
@@ -73,12 +91,13 @@ class side_stream:
         return False
 
 
-def _on_side(fn, *keep):
+def _on_side(fn, *keep, key=None):
     sc = _SIDE[0]
     if sc is None:
         return fn()
-    sc.stream.wait_stream(torch.cuda.current_stream())
-    with torch.cuda.stream(sc.stream):
+    stream = sc.pick(key)
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
         fn()
     sc.keep.extend(t for t in keep if t is not None)
     return None
@@ -130,7 +149,7 @@ class _Aggregate(torch.autograd.Function):
             d32 = dout.float() if dout.dtype != torch.float32 else dout
             gb = _bucket(ctx.bias_ref)
             if gb is not None:
-                _on_side(lambda: ops.colsum(d32, out=gb), d32)
+                _on_side(lambda: ops.colsum(d32, out=gb), d32, key=gb.data_ptr())
             else:
                 dbias = ops.colsum(d32)
         return dx, dbias, None, None, None, None, None, None, None, None
@@ -175,7 +194,7 @@ class _GatAttention(torch.autograd.Function):
                                          a_s, a_d, dout, heads, chan, slope, add_self, p, seed)
         g_src, g_dst = _bucket(p_src), _bucket(p_dst)
         if g_src is not None and g_dst is not None:
-            _on_side(lambda: ops.gat_datt(h, da_src, da_dst, heads, chan, g_src.view(-1), g_dst.view(-1)), h, da_src, da_dst)
+            _on_side(lambda: ops.gat_datt(h, da_src, da_dst, heads, chan, g_src.view(-1), g_dst.view(-1)), h, da_src, da_dst, key=g_src.data_ptr())
             datt_src = datt_dst = None
         else:
             datt_src, datt_dst = ops.gat_datt(h, da_src, da_dst, heads, chan)
@@ -185,7 +204,7 @@ class _GatAttention(torch.autograd.Function):
             d32 = dout if dout.dtype == torch.float32 else dout.float()
             gb = _bucket(p_bias)
             if gb is not None:
-                _on_side(lambda: ops.colsum(d32, out=gb), d32)
+                _on_side(lambda: ops.colsum(d32, out=gb), d32, key=gb.data_ptr())
             else:
                 dbias = ops.colsum(d32)
         return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None)
@@ -232,7 +251,8 @@ class _Linear(torch.autograd.Function):
                 return None, None
             gw, gb = (_bucket(pw) if want_dw else None), (_bucket(pb) if want_db else None)
             if (not want_dw or gw is not None) and (not want_db or gb is not None):
-                _on_side(lambda: ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db, dw_out=gw, db_out=gb), dy, xin)
+                _on_side(lambda: ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db, dw_out=gw, db_out=gb), dy, xin,
+                         key=(gw if gw is not None else gb).data_ptr())
                 return None, None
             return ops.linear_bwd_w(dy, xin, want_dw=want_dw, want_db=want_db)
 
@@ -255,7 +275,7 @@ class _Linear(torch.autograd.Function):
             if want_db:
                 gb, d0 = _bucket(p_b), dout
                 if gb is not None:
-                    _on_side(lambda: ops.colsum(d0, out=gb), d0)
+                    _on_side(lambda: ops.colsum(d0, out=gb), d0, key=gb.data_ptr())
                 else:
                     db = ops.colsum(d0)
             dout = dout * rs.unsqueeze(1)

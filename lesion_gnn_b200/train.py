@@ -150,7 +150,7 @@ class TrainStep:
         self.use_cuda_graph = use_cuda_graph
         self.pg, self.world_size = process_group, world_size
         self._graphs = {}
-        self._side = torch.cuda.Stream() if torch.cuda.is_available() else None
+        self._side = [torch.cuda.Stream() for _ in range(3)] if torch.cuda.is_available() else None
         self._build = torch.cuda.Stream() if torch.cuda.is_available() else None
 
     def _body(self, db: DeviceBatch) -> Tensor:
