@@ -62,7 +62,7 @@ class side_stream:
 
     def __init__(self, stream):
         self.streams = list(stream) if isinstance(stream, (list, tuple)) else [stream]
-        self.keep, self._next, self._by_key = [], 0, {}
+        self.keep, self._next, self._by_key, self._used = [], 0, {}, []
 
     def __enter__(self):
         self._old = _SIDE[0]
@@ -76,14 +76,17 @@ class side_stream:
         self._next += 1
         if key is not None:
             self._by_key[key] = s
+        if s not in self._used:
+            self._used.append(s)
         return s
 
     def join(self):
         cur = torch.cuda.current_stream()
-        for s in self.streams:
+        for s in self._used:  # only streams forked since the last join (a wait on an idle stream breaks graph capture)
             cur.wait_stream(s)
         self.keep.clear()
         self._by_key.clear()
+        self._used.clear()
 
     def __exit__(self, *exc):
         self.join()
