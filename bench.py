@@ -334,6 +334,7 @@ def run_b200(args):
 
     # ---- instrumented pass: per entry point CUDA-event times on the same steps (eager, same kernels) -----------
     eager = train.TrainStep(model, opt, "MSE", 5, use_cuda_graph=False, world_size=world)
+    eager._side = eager._build = None  # one stream: every launch is timed alone, not beside the side-stream kernels
     L = _lib.lib()
     eager(devb[0])
     ops.reset_launch_count()

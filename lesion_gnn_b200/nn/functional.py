@@ -61,7 +61,8 @@ class side_stream:
     into the same gradient buffer (`key`) stay on one stream, i.e. ordered."""
 
     def __init__(self, stream):
-        self.streams = list(stream) if isinstance(stream, (list, tuple)) else [stream]
+        # None: no side streams, every kernel stays on the current stream (per-kernel timing, debugging)
+        self.streams = list(stream) if isinstance(stream, (list, tuple)) else ([] if stream is None else [stream])
         self.keep, self._next, self._by_key, self._used = [], 0, {}, []
 
     def __enter__(self):
@@ -96,7 +97,7 @@ class side_stream:
 
 def _on_side(fn, *keep, key=None):
     sc = _SIDE[0]
-    if sc is None:
+    if sc is None or not sc.streams:
         return fn()
     stream = sc.pick(key)
     stream.wait_stream(torch.cuda.current_stream())
