@@ -20,6 +20,9 @@ namespace lgk {
 // tensor-core (3xTF32, tcgen05) forward transform, linear_tc.cu
 int launch_linear_tc(const float* x, const float* w, const float* bias, const float* rowscale, float* out, int64_t n,
                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream);
+// TMA-fed tensor-core transform for 16-byte aligned rows (K % 4 == 0), linear_tma.cu
+int launch_linear_tma(const float* x, const float* w, const float* bias, const float* rowscale, float* out, int64_t n,
+                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream, bool* done);
 namespace {
 
 // Products with at least this many rows and a reduction of at least 32 go to the tensor cores; below that the
@@ -398,9 +401,17 @@ extern "C" int lgk_linear_fwd(const void* x, const float* weight, const float* b
   LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_fwd: only fp32 is implemented");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(x && weight && out, LGK_ERR_BAD_ARG, "lgk_linear_fwd: null pointer");
-  if (use_tensor_cores(n, k))
+  if (use_tensor_cores(n, k)) {
+    bool done = false;
+    if ((k & 3) == 0) {  // aligned rows: tensor-map TMA feeds the tensor core
+      if (int rc = launch_linear_tma(static_cast<const float*>(x), weight, bias, rowscale, static_cast<float*>(out), n, k, m,
+                                     act, accumulate, stream, &done))
+        return rc;
+      if (done) return LGK_OK;
+    }
     return launch_linear_tc(static_cast<const float*>(x), weight, bias, rowscale, static_cast<float*>(out), n, k, m, act,
                             accumulate, stream);
+  }
   GemmArgs g{};
   g.A = static_cast<const float*>(x); g.B = weight; g.C = static_cast<float*>(out);
   g.I = n; g.J = m; g.R = k; g.lda = k; g.ldb = k; g.sCi = m; g.sCj = 1;

@@ -307,9 +307,14 @@ def linear_fwd(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None, rowscal
 
 
 def linear_bwd_x(dy: Tensor, weight: Tensor, out: Optional[Tensor] = None) -> Tensor:
+    """dx = dy W (+ out).  Large aligned products (the hidden transforms of the 1e5..1e6-node configs) go through the
+    tensor-core transform as dy (W^T)^T: dX is a forward product against the transposed weight, a [K, M] copy that
+    costs nothing next to N x M; the FFMA kernel lgk_linear_bwd_x keeps the small and unaligned ones."""
     L = _lib.lib()
     n, m = dy.shape
     k = weight.size(1)
+    if n >= 32768 and m >= 32 and m % 4 == 0 and k % 4 == 0:
+        return linear_fwd(dy, weight.t().contiguous(), out=out)
     accumulate = out is not None
     if out is None:
         out = torch.empty(n, k, dtype=dy.dtype, device=dy.device)
