@@ -40,7 +40,10 @@ def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what="", tol_grad=
 
 
 @pytest.mark.parametrize("n,k,m", [(1, 1, 1), (7, 3, 5), (300, 16, 64), (1000, 64, 64), (513, 1025, 64), (2000, 128, 128),
-                                   (4096, 64, 5), (100, 64, 1), (129, 20, 130)])
+                                   (4096, 64, 5), (100, 64, 1), (129, 20, 130),
+                                   # TMA-fed tensor-core kernel: K not a multiple of the 32-wide block, partial row and
+                                   # column tiles, and n >= 32768 where dX runs as a forward product against W^T
+                                   (600, 36, 70), (33000, 100, 36), (40000, 64, 64)])
 def test_linear_fwd_bwd(dev, n, k, m):
     from lesion_gnn_b200.nn import functional as F
     gen = torch.Generator().manual_seed(n + k + m)
@@ -293,3 +296,22 @@ def test_layers_accept_adj_t_sparse_tensors(dev):
     gcn = lg.nn.GCNConv(32, 8).to(dev)
     unweighted = torch.sparse_csr_tensor(g.rowptr.long(), g.col.long(), torch.ones_like(g.value), size=(n, n))
     assert_close(gcn(x, unweighted), gcn(x, ei, torch.ones_like(w)), 1e-6, "gcn adj_t")
+
+
+def test_linear_tensor_core_epilogue_options(dev):
+    """row scale, bias, accumulate-into-out and ELU of the tensor-core transform (aligned rows -> linear_tma.cu,
+    1025-float rows -> linear_tc.cu), against fp64"""
+    from lesion_gnn_b200 import ops
+    gen = torch.Generator().manual_seed(9)
+    for n, k, m in [(777, 64, 48), (900, 1025, 64)]:
+        x = torch.randn(n, k, generator=gen, dtype=torch.float64)
+        w = torch.randn(m, k, generator=gen, dtype=torch.float64) / k ** 0.5
+        b = torch.randn(m, generator=gen, dtype=torch.float64)
+        rs = torch.rand(n, generator=gen, dtype=torch.float64) + 0.5
+        base = torch.randn(n, m, generator=gen, dtype=torch.float64)
+        want = torch.nn.functional.elu(rs[:, None] * (x @ w.t()) + b)
+        got = ops.linear_fwd(x.float().to(dev), w.float().to(dev), b.float().to(dev), rs.float().to(dev), act=1)
+        assert_close(got, want, TOL_F32, f"rowscale+bias+elu {n}x{k}->{m}")
+        out = base.float().to(dev).clone()
+        ops.linear_fwd(x.float().to(dev), w.float().to(dev), out=out)
+        assert_close(out, base + x @ w.t(), TOL_F32, f"accumulate {n}x{k}->{m}")
