@@ -206,57 +206,60 @@ __global__ void __launch_bounds__(512, 2) spmm_vec_kernel(SpmmArgs a, const T* _
             }
           }
         }
-        // ---- head and tail (and every slot of a chunk that was too large to stage): up to eight slots per step,
-        // predicated
-        if (start < q0 || qe < end)
+        // ---- head and tail together (and every slot of a chunk that was too large to stage): one list of
+        // nh + nt slots taken up to eight per step, predicated -- a step costs a full gather latency, so a head of
+        // two and a tail of six are one step, not two
+        const int nh = q0 - start, cnt = nh + (end - qe);
 #pragma unroll 1
-        for (int part = 0; part < 2; ++part) {
-          const int lo = part ? qe : start, hi = part ? end : q0;
-#pragma unroll 1
-          for (int q = lo; q < hi; q += 8) {
-            unsigned off[8];
-            float w[8];
-            bool ok[8];
+        for (int b0 = 0; b0 < cnt; b0 += 8) {
+          unsigned off[8];
+          float w[8];
+          int slot[8];
+          bool ok[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) ok[k] = q + k < hi;
-            if (staged) {
-#pragma unroll
-              for (int k = 0; k < 8; ++k) {
-                off[k] = ok[k] ? so[q - base + k] : 0u;
-                w[k] = ok[k] ? (WEIGHTED ? sw[q - base + k] : 1.f) : 0.f;
-              }
-            } else {  // read through L1
-#pragma unroll
-              for (int k = 0; k < 8; ++k) {
-                const int j = ok[k] ? __ldg(a.idx + q + k) : 0;
-                off[k] = unsigned(j) * F4;
-                w[k] = ok[k] ? 1.f : 0.f;
-                if (WEIGHTED && ok[k]) w[k] = (off[k] == self_off) ? 0.f : edge_weight(a, q + k, j);
-              }
-            }
-            float4 v[8];
+          for (int k = 0; k < 8; ++k) {
+            const int t = b0 + k;
+            ok[k] = t < cnt;
+            slot[k] = t < nh ? start + t : qe + (t - nh);
+          }
+          if (staged) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-              v[k] = f4_zero();
-              if (ok[k]) v[k] = Vec4<T>::gather(xv + size_t(off[k]) * 4, 0);
+              off[k] = ok[k] ? so[slot[k] - base] : 0u;
+              w[k] = ok[k] ? (WEIGHTED ? sw[slot[k] - base] : 1.f) : 0.f;
             }
-            if (REDUCE == LGK_MAX) {
+          } else {  // read through L1
 #pragma unroll
-              for (int k = 0; k < 8; ++k) {
-                if (ok[k]) {
-                  const int slot = q + k;
-                  if (v[k].x > acc.x) { acc.x = v[k].x; arg.x = slot; }
-                  if (v[k].y > acc.y) { acc.y = v[k].y; arg.y = slot; }
-                  if (v[k].z > acc.z) { acc.z = v[k].z; arg.z = slot; }
-                  if (v[k].w > acc.w) { acc.w = v[k].w; arg.w = slot; }
-                }
-              }
-            } else {
+            for (int k = 0; k < 8; ++k) {
+              const int j = ok[k] ? __ldg(a.idx + slot[k]) : 0;
+              off[k] = unsigned(j) * F4;
+              w[k] = ok[k] ? 1.f : 0.f;
+              if (WEIGHTED && ok[k]) w[k] = (off[k] == self_off) ? 0.f : edge_weight(a, slot[k], j);
+            }
+          }
+          float4 v[8];
 #pragma unroll
-              for (int k = 0; k < 8; k += 2) {
-                f4_fma(acc, w[k], v[k]);
-                f4_fma(acc2, w[k + 1], v[k + 1]);
+          for (int k = 0; k < 8; ++k) {
+            v[k] = f4_zero();
+            if (ok[k]) v[k] = Vec4<T>::gather(xv + size_t(off[k]) * 4, 0);
+          }
+          if (REDUCE == LGK_MAX) {
+            // the main loop ran first: on ties the LOWER slot must still win (first arg-max, torch-scatter's rule)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              if (ok[k]) {
+                const int sl = slot[k];
+                if (v[k].x > acc.x || (v[k].x == acc.x && sl < arg.x)) { acc.x = v[k].x; arg.x = sl; }
+                if (v[k].y > acc.y || (v[k].y == acc.y && sl < arg.y)) { acc.y = v[k].y; arg.y = sl; }
+                if (v[k].z > acc.z || (v[k].z == acc.z && sl < arg.z)) { acc.z = v[k].z; arg.z = sl; }
+                if (v[k].w > acc.w || (v[k].w == acc.w && sl < arg.w)) { acc.w = v[k].w; arg.w = sl; }
               }
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 8; k += 2) {
+              f4_fma(acc, w[k], v[k]);
+              f4_fma(acc2, w[k + 1], v[k + 1]);
             }
           }
         }

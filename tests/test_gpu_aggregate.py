@@ -164,3 +164,29 @@ def test_aggregate_is_bitwise_deterministic(dev):
         outs.append(y.detach().clone())
         grads.append(x.grad.clone())
     assert all(torch.equal(outs[0], o) for o in outs) and all(torch.equal(grads[0], gr) for gr in grads)
+
+
+@pytest.mark.parametrize("feat", [8, 128, 5])
+def test_max_aggregation_ties_go_to_the_first_slot(dev, feat):
+    """torch-scatter's rule (what PyG's scatter(reduce='max') uses for gradients on CUDA): among equal maxima the FIRST
+    entry of the destination's list wins.  Integer-valued features give many ties; rows of every length and alignment."""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import ops
+    n = 500
+    ei = random_graph(n, 9000, 17)
+    x = torch.randint(0, 3, (n, feat), generator=torch.Generator().manual_seed(1)).float()
+    g = lg.CSRGraph.from_edge_index(ei.to(dev), n)
+    out, arg = ops.spmm(g.rowptr, g.col, x.to(dev), "max", want_arg=True)
+    rowptr, col = g.rowptr.cpu().long(), g.col.cpu().long()
+    want_out = torch.zeros(n, feat)
+    want_arg = torch.full((n, feat), -1, dtype=torch.long)
+    for i in range(n):
+        lo, hi = int(rowptr[i]), int(rowptr[i + 1])
+        if hi > lo:
+            vals = x[col[lo:hi]]                       # [deg, F]
+            m, _ = vals.max(0)
+            first = (vals == m).float().argmax(0)      # first position attaining the maximum
+            want_out[i] = m
+            want_arg[i] = lo + first
+    assert torch.equal(out.cpu(), want_out)
+    assert torch.equal(arg.cpu().long(), want_arg)
