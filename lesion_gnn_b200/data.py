@@ -46,6 +46,59 @@ class HostBatch:
                    if v is not None)
 
 
+@dataclasses.dataclass
+class GraphSample:
+    """one graph as the reference's datasets yield it (torch_geometric.data.Data: x, pos, edge_index, y and the optional
+    edge weight of GaussianDistance; reference datasets/nodes/lesions.py:170-176)"""
+    x: Tensor
+    pos: Optional[Tensor] = None
+    edge_index: Optional[Tensor] = None
+    y: Optional[Tensor] = None
+    edge_weight: Optional[Tensor] = None
+
+
+def collate(samples) -> HostBatch:
+    """PyG DataLoader collation (Batch.from_data_list; reference datasets/datamodule.py:64-69): node
+    tensors concatenated, every graph's edge_index shifted by the number of nodes before it, `batch` = the graph id of
+    every node (ascending, so graphs are contiguous slabs), y concatenated.  Host-side index work: exact."""
+    samples = list(samples)
+    if not samples:
+        raise ValueError("collate() needs at least one graph")
+    counts = [int(s.x.size(0)) for s in samples]
+    offsets = [0]
+    for n in counts:
+        offsets.append(offsets[-1] + n)
+    x = torch.cat([s.x for s in samples], dim=0)
+    pos = None
+    if all(s.pos is not None for s in samples):
+        pos = torch.cat([s.pos for s in samples], dim=0)
+    has_edges = [s.edge_index is not None for s in samples]
+    if any(has_edges) and not all(has_edges):
+        raise ValueError("either every graph or none carries edge_index")
+    edge_index = edge_weight = None
+    if all(has_edges):
+        for s, n in zip(samples, counts):
+            if s.edge_index.numel() and (int(s.edge_index.min()) < 0 or int(s.edge_index.max()) >= n):
+                raise ValueError("edge_index refers to a node outside its graph")
+        edge_index = torch.cat([s.edge_index.long() + o for s, o in zip(samples, offsets)], dim=1)
+        has_w = [s.edge_weight is not None for s in samples]
+        if any(has_w) and not all(has_w):
+            raise ValueError("either every graph or none carries edge_weight")
+        if all(has_w):
+            edge_weight = torch.cat([s.edge_weight for s in samples])
+    batch = torch.repeat_interleave(torch.arange(len(samples)), torch.tensor(counts, dtype=torch.long))
+    ys = [s.y for s in samples]
+    y = torch.cat([t.reshape(-1) for t in ys]) if all(t is not None for t in ys) else torch.zeros(len(samples), dtype=torch.long)
+    if pos is None:
+        pos = torch.zeros(x.size(0), 2, dtype=torch.float64)
+    return HostBatch(x=x, pos=pos, batch=batch, y=y, counts=counts, edge_index=edge_index, edge_weight=edge_weight)
+
+
+def ptr_from_counts(counts) -> Tensor:
+    """PyG Batch.ptr: int64 [B + 1] cumulative node counts"""
+    return torch.cat([torch.zeros(1, dtype=torch.long), torch.tensor(list(counts), dtype=torch.long).cumsum(0)])
+
+
 def node_counts(num_graphs: int, spec, gen: torch.Generator) -> list:
     """spec = int (fixed size) or 'ddr': ceil(LogNormal(ln 30, 0.9)) clipped to [1, 600] -- long-tailed like the
     reference's DDR lesion graphs (notebooks/viz.ipynb cells 4-6); node 0 of each graph is the background."""

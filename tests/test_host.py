@@ -116,3 +116,37 @@ def test_data_parallel_gradient_equals_full_batch_gloo():
     for r in range(world):
         assert torch.allclose(got[r], fp.grad, rtol=1e-4, atol=1e-6)
     assert torch.equal(got[0], got[1])
+
+
+def test_collate_matches_pyg_batching():
+    """PyG collation (reference datasets/datamodule.py:64-69): cat, cumulative node offsets on edge_index, batch vector,
+    ptr; splitting the collated batch again (take_graphs) returns every graph"""
+    import torch
+    from lesion_gnn_b200 import data
+    from oracle import pyg_semantics as O
+    g = torch.Generator().manual_seed(3)
+    samples = []
+    for n in (5, 1, 9, 4):
+        pos = torch.rand(n, 2, generator=g, dtype=torch.float64) * 100
+        ei = O.knn_graph(pos, 3, None, loop=True)
+        samples.append(data.GraphSample(x=torch.randn(n, 6, generator=g), pos=pos, edge_index=ei,
+                                        y=torch.randint(0, 5, (1,), generator=g), edge_weight=torch.rand(ei.size(1), generator=g)))
+    hb = data.collate(samples)
+    assert hb.counts == [5, 1, 9, 4] and hb.num_graphs == 4 and hb.num_nodes == 19
+    assert torch.equal(hb.batch, torch.tensor([0] * 5 + [1] + [2] * 9 + [3] * 4))
+    assert torch.equal(data.ptr_from_counts(hb.counts), torch.tensor([0, 5, 6, 15, 19]))
+    assert torch.equal(hb.y, torch.cat([s.y for s in samples]))
+    off = 0
+    for i, s in enumerate(samples):
+        sub = data.take_graphs(hb, i, i + 1)
+        assert torch.equal(sub.x, s.x) and torch.equal(sub.pos, s.pos)
+        assert torch.equal(sub.edge_index, s.edge_index) and torch.equal(sub.edge_weight, s.edge_weight)
+        lo, hi = off, off + s.x.size(0)
+        m = (hb.edge_index[1] >= lo) & (hb.edge_index[1] < hi)
+        assert bool(((hb.edge_index[0][m] >= lo) & (hb.edge_index[0][m] < hi)).all()), "an edge crosses graphs"
+        off = hi
+    # batching == building the kNN graph of the whole batch at once (what the device pipeline does)
+    assert torch.equal(hb.edge_index, O.knn_graph(hb.pos, 3, hb.batch, loop=True))
+    import pytest
+    with pytest.raises(ValueError):
+        data.collate([data.GraphSample(x=torch.zeros(2, 3), edge_index=torch.tensor([[0], [5]]))])
