@@ -315,3 +315,28 @@ def test_linear_tensor_core_epilogue_options(dev):
         out = base.float().to(dev).clone()
         ops.linear_fwd(x.float().to(dev), w.float().to(dev), out=out)
         assert_close(out, base + x @ w.t(), TOL_F32, f"accumulate {n}x{k}->{m}")
+
+
+@pytest.mark.parametrize("n,k,m", [(11583, 1025, 64), (2048, 256, 128), (5000, 300, 100), (3001, 257, 40),
+                                   (2500, 1024, 7), (4100, 513, 64)])
+def test_wide_weight_gradient_on_tensor_cores(dev, n, k, m):
+    """dW of a wide transform (grad_w_tc.cu: nodes as the MMA K dimension, both operands MN-major as they lie in
+    memory): ragged last node block, last feature tile of one column, m not a multiple of 32, accumulate form"""
+    from lesion_gnn_b200 import ops
+    gen = torch.Generator().manual_seed(n + k + m)
+    x = torch.randn(n, k, generator=gen, dtype=torch.float64)
+    dy = torch.randn(n, m, generator=gen, dtype=torch.float64)
+    want_w, want_b = dy.t() @ x, dy.sum(0)
+    xg, dyg = x.float().to(dev), dy.float().to(dev)
+    dw, db = ops.linear_bwd_w(dyg, xg, want_dw=True, want_db=True)
+    assert_close(dw, want_w, TOL_F32, "dW")
+    assert_close(db, want_b, TOL_F32, "db")
+    # every element on its own, not only the largest: a misplaced tile would hide under max-normalisation
+    assert float((dw.double().cpu() - want_w).abs().max()) <= 1e-5 * float(want_w.abs().max())
+    base_w = torch.randn(m, k, generator=gen).to(dev)
+    base_b = torch.randn(m, generator=gen).to(dev)
+    acc_w, acc_b = base_w.clone(), base_b.clone()
+    ops.linear_bwd_w(dyg, xg, want_dw=True, want_db=True, dw_out=acc_w, db_out=acc_b)
+    assert_close(acc_w, base_w.double().cpu() + want_w, TOL_F32, "dW accumulate")
+    assert_close(acc_b, base_b.double().cpu() + want_b, TOL_F32, "db accumulate")
+    assert torch.equal(ops.linear_bwd_w(dyg, xg)[0], dw)   # deterministic
