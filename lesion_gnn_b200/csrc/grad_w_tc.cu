@@ -1,45 +1,52 @@
-// (5c) weight gradient of a wide node-feature transform on the tensor cores: dW[m,k] = sum_i dy[i,m] x[i,k].
+// (5c) weight (and bias) gradient of a wide node-feature transform on the tensor cores:
+//   dW[m,k] = sum_i dy[i,m] x[i,k],   db[m] = sum_i dy[i,m].
 //
 // The gradient of the reference's in_proj (models/gat.py:29, gin.py:21: Linear(1025 -> d)) reduces over the nodes
 // of the batch: 2*N*1025*d flops over N*(1025 + d)*4 bytes.  On the FFMA pipe it was the longest kernel of the
 // training step (72 us on the headline batch, 9 % of the HBM roofline).  Here both operands are read exactly as
-// they lie in memory: with the node index as the MMA's K dimension, dy [N, m] IS the MN-major A operand
-// (m contiguous) and x [N, k] IS the MN-major B operand (features contiguous) -- no transposition anywhere, and
-// a warp that copies 32 consecutive features of one node writes exactly one 128-byte row of a SWIZZLE_128B
-// MN-major atom (8 nodes x 32 features), conflict free.  3xTF32 as in linear_tc.cu (hi/lo split on the fly, three
-// MMAs per K step, four independent accumulators in tensor memory added in fp32 by the epilogue).
+// they lie in memory: with the node index as the MMA's K dimension, x [N, k] IS an MN-major A operand (features
+// contiguous) and dy [N, m] IS an MN-major B operand (m contiguous) -- no transposition anywhere, and a warp that
+// copies 32 consecutive floats of one node writes exactly one 128-byte row of an MN-major atom, conflict free.
+// D[feature, m] = dW^T accumulates in tensor memory (lane = feature, column = m), so the epilogue's stores to
+// dW[m*K + feature] are coalesced over the lanes.  3xTF32 as in linear_tc.cu (hi/lo split on the fly, three MMAs
+// per K step, four independent accumulators added in fp32 by the epilogue).
+// The bias gradient rides along: when K is not a multiple of 128 the first unused feature row of the last tile is
+// fed with ones, so D[K, m] = db[m] -- no separate column-sum pass over dy.
 //
 // Grid: feature tiles of 128 columns of x  x  slabs of nodes, ntiles * slabs <= 148 CTAs (one per SM, one wave).
-// A CTA walks its slab in blocks of 32 nodes: 16 stager warps cp.async (4 bytes per lane: the reference's
-// 1025-float rows are not 16-byte aligned) the raw block into a 3-deep ring, read back their own bytes, split and
-// write the hi/lo tiles; one lane issues 12 tcgen05.mma (M128 N128 K8) per block; at the end 4 warps drain the
-// accumulators into partial[slab][m*K + k] (the layout of dW), which lgk_linear_bwd_w reduces in slab order
-// (deterministic).
-// m <= 128 (rows of dW above m are zero rows of the A tile, written once).
+// A CTA walks its slab in blocks of 32 nodes: 16 stager warps load the block (4 bytes per lane, 128 bytes per warp
+// load: the reference's 1025-float rows are not 16-byte aligned) into registers one block ahead, split it and write
+// the hi/lo tiles of a 3-deep ring (4-byte cp.async into a raw ring, as linear_tc.cu does, measured 56 us against
+// 41 us: the LDGSTS issue rate, ~10 cycles per warp instruction, was the cost); one lane issues 12 tcgen05.mma
+// (M128 N=m K8) per block; at the end 4 warps drain the
+// accumulators into partial[slab][m*K + k | m] (the layout of dW, then db), which lgk_linear_bwd_w reduces in
+// slab order (deterministic).  m <= 128.
 #include "common.cuh"
 #include "umma.cuh"
+#include <stdlib.h>
 
 namespace lgk {
 namespace {
 
-constexpr int BF = 128;          // features (columns of x) per CTA = MMA N
-constexpr int BMM = 128;         // MMA M (rows of dW, zero padded above m)
+constexpr int BF = 128;          // features (columns of x) per CTA = MMA M
 constexpr int BNODE = 32;        // nodes per block = 4 MMA K steps of 8
 constexpr int kAcc = 4;
-constexpr int kRawStages = 3, kTileStages = 2;
+constexpr int kAccCols = 128;    // tensor-memory columns reserved per accumulator (N = m rounded up to 16 <= 128)
 constexpr int kAtom = 1024;                   // 8 nodes (one MMA K step) x 128 bytes
 constexpr int kGroupStride = 4 * kAtom;       // one 32-column group: 4 node atoms back to back
-constexpr int kTileA = 4 * kGroupStride, kTileB = 4 * kGroupStride;  // hi (or lo) operand tile: 16 KB each
-constexpr int kTileBytes = 2 * (kTileA + kTileB);
+constexpr int kTileA = 4 * kGroupStride;      // hi (or lo) tile of x: 128 features x 32 nodes, 16 KB
 constexpr int kConvWarps = 16;
 constexpr int kWarpMma = 4, kWarpConv = 5;
 constexpr int kThreads = (kWarpConv + kConvWarps) * 32;
-constexpr int kTmemCols = kAcc * BF;
+constexpr int kTmemCols = kAcc * kAccCols;
 static_assert(kTmemCols == 512, "tensor memory allocation must be a power of two");
 
-template <int MG> constexpr int raw_bytes() { return (BF / 32 + MG) * BNODE * 128; }
-template <int MG> constexpr int smem_bytes() { return kTileStages * kTileBytes + kRawStages * raw_bytes<MG>() + 256; }
-static_assert(smem_bytes<4>() <= 227 * 1024, "shared memory budget");
+// MG = 32-column groups of dy (m <= 32 MG): the dy tiles take MG * 4 KB each
+template <int MG> constexpr int tile_b() { return MG * kGroupStride; }
+template <int MG> constexpr int tile_bytes() { return 2 * (kTileA + tile_b<MG>()); }
+template <int MG> constexpr int tile_stages() { return 3; }
+template <int MG> constexpr int smem_bytes() { return tile_stages<MG>() * tile_bytes<MG>() + 256; }
+static_assert(smem_bytes<4>() <= 227 * 1024 && smem_bytes<2>() <= 227 * 1024, "shared memory budget");
 
 struct GwArgs {
   const float* dy;
@@ -47,10 +54,12 @@ struct GwArgs {
   float* partial;
   int64_t n, k, m;
   int64_t slab_nodes;  // multiple of 32
+  int fuse_db;         // feature row K of the last tile is fed with ones: D[K, :] = db
+  int debug;           // profiling only (LGK_GW_DEBUG): 1 = no MMAs, 2 = no conversion, 4 = no global copies
 };
 
 struct Bars {
-  uint64_t tile_full[kTileStages], tile_empty[kTileStages];
+  uint64_t tile_full[3], tile_empty[3];
   uint64_t acc_full;
   uint32_t tmem_slot;
 };
@@ -59,16 +68,6 @@ __device__ __forceinline__ void split_mask(float x, float& hi, float& lo) {
   hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
   lo = x - hi;
 }
-__device__ __forceinline__ void cp_async4(uint32_t dst, const float* src, uint32_t src_bytes) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-__device__ __forceinline__ void cp_async4(uint32_t dst, const float* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
 // MN-major tf32 operands exist in one shared-memory layout only, SWIZZLE_128B with a 32-byte base (layout type 1):
 // atoms of 4 K rows (nodes) x 128 bytes (32 columns), the four 32-byte chunks of a row XOR-permuted by the row index
 // (address bits [5,7) ^= bits [7,9)); atoms of consecutive nodes kSbo bytes apart, the next 32 columns kGroupStride
@@ -82,16 +81,15 @@ __device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t saddr) {
 __device__ __forceinline__ uint32_t mn_offset(uint32_t r, uint32_t cg, uint32_t lane) {
   return cg * kGroupStride + r * 128u + ((((lane >> 3) ^ r) & 3u) << 5) + ((lane & 7u) << 2);
 }
-constexpr uint32_t idesc_tf32_mn(int m, int n) { return umma::idesc_tf32(m, n) | (1u << 15) | (1u << 16); }  // A, B MN-major
+__host__ __device__ constexpr uint32_t idesc_tf32_mn(int m, int n) { return umma::idesc_tf32(m, n) | (1u << 15) | (1u << 16); }  // A, B MN-major
 
 template <int MG>
 __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
-  constexpr int kRaw = raw_bytes<MG>();
+  constexpr int kTileB = tile_b<MG>(), kTileBytes = tile_bytes<MG>(), kTileStages = tile_stages<MG>();
   constexpr int RX = 8, RY = 2 * MG;  // (node, column group) slots per stager warp: x and dy
   extern __shared__ __align__(1024) uint8_t smem_dyn[];
   const uint32_t tiles = umma::smem_u32(smem_dyn);
-  const uint32_t raws = tiles + kTileStages * kTileBytes;
-  Bars* bars = reinterpret_cast<Bars*>(smem_dyn + kTileStages * kTileBytes + kRawStages * kRaw);
+  Bars* bars = reinterpret_cast<Bars*>(smem_dyn + kTileStages * kTileBytes);
   if ((tiles & 1023u) != 0) __trap();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -101,8 +99,9 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
   const int64_t node0 = sl * g.slab_nodes;
   const int64_t slab = min(g.slab_nodes, g.n - node0);   // nodes of this slab (> 0 by construction of the grid)
   const int nkb = int((slab + BNODE - 1) / BNODE);
+  const int ncols = int((g.m + 15) / 16) * 16;           // MMA N
 
-  // operand tiles start as zeros: rows of the A tile above m are never written
+  // operand tiles start as zeros: columns of the dy tiles between m and N are never written
   for (int i = threadIdx.x; i < kTileStages * kTileBytes / 16; i += kThreads)
     *reinterpret_cast<uint4*>(smem_dyn + i * 16) = make_uint4(0, 0, 0, 0);
   umma::fence_proxy_async_smem();
@@ -121,12 +120,15 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
   const uint32_t tmem_base = bars->tmem_slot;
 
   if (warp == kWarpMma) {
-    constexpr uint32_t idesc = idesc_tf32_mn(BMM, BF);
+    const uint32_t idesc = idesc_tf32_mn(BF, ncols);
     for (int kb = 0; kb < nkb; ++kb) {
       const int s = kb % kTileStages;
       umma::mbar_wait(bars->tile_full + s, (kb / kTileStages) & 1);
       umma::tc_fence_after();
-      if (lane == 0) {
+      if (lane == 0 && (g.debug & 1)) {
+        umma::mma_commit(bars->tile_empty + s);
+        if (kb == nkb - 1) umma::mma_commit(&bars->acc_full);
+      } else if (lane == 0) {
         const uint32_t sa = tiles + s * kTileBytes;
         const uint64_t a_hi = smem_desc_mn_sw128(sa), a_lo = smem_desc_mn_sw128(sa + kTileA);
         const uint64_t b_hi = smem_desc_mn_sw128(sa + 2 * kTileA), b_lo = smem_desc_mn_sw128(sa + 2 * kTileA + kTileB);
@@ -134,8 +136,8 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
         for (int term = 0; term < 3; ++term) {
 #pragma unroll
           for (int kk = 0; kk < BNODE / 8; ++kk) {  // term-major: consecutive MMAs target different accumulators
-            const uint32_t acc = tmem_base + uint32_t(kk) * BF;
-            const uint64_t adv = uint64_t(kk * kAtom >> 4);  // next 8 nodes: next atom
+            const uint32_t acc = tmem_base + uint32_t(kk) * kAccCols;
+            const uint64_t adv = uint64_t(kk * kAtom >> 4);  // next 8 nodes
             if (term == 0) umma::mma_tf32(acc, a_lo + adv, b_hi + adv, idesc, kb > 0);
             else if (term == 1) umma::mma_tf32(acc, a_hi + adv, b_lo + adv, idesc, true);
             else umma::mma_tf32(acc, a_hi + adv, b_hi + adv, idesc, true);
@@ -152,13 +154,14 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
     const float* xp[RX];
     const float* yp[RY];
     uint32_t tx[RX], ty[RY];
-    uint32_t okx = 0, oky = 0;  // column-valid bits per slot
+    uint32_t okx = 0, oky = 0, onex = 0;  // per slot: column inside the matrix / the ones column that yields db
 #pragma unroll
     for (int r = 0; r < RX; ++r) {
       const uint32_t node = 2 * cw + (r >> 2), cg = r & 3;
       const int64_t col = j0 + cg * 32 + lane;
       const bool ok = col < g.k;
       okx |= uint32_t(ok) << r;
+      onex |= uint32_t(g.fuse_db && col == g.k) << r;
       xp[r] = g.x + (node0 + node) * g.k + (ok ? col : 0);
       tx[r] = mn_offset(node, cg, lane);
     }
@@ -171,90 +174,90 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
       yp[r] = g.dy + (node0 + node) * g.m + (ok ? col : 0);
       ty[r] = mn_offset(node, cg, lane);
     }
-    const uint32_t raw_x = uint32_t(cw * RX) * 128 + lane * 4;
-    const uint32_t raw_y = uint32_t(BF / 32 * BNODE + cw * RY) * 128 + lane * 4;
     const bool cols_full = (j0 + BF <= g.k) && (g.m == MG * 32);
     const int64_t step_x = int64_t(BNODE) * g.k, step_y = int64_t(BNODE) * g.m;
 
-    auto issue = [&](int q) {
-      if (q < nkb) {
-        const uint32_t raw = raws + uint32_t(q % kRawStages) * kRaw;
-        const int64_t left = slab - int64_t(q) * BNODE;  // nodes of the slab from this block on
-        if (cols_full && left >= BNODE) {
+    // global -> registers one block ahead of the conversion (coalesced 128-byte warp loads; zeros outside the matrix)
+    auto load = [&](int q, float (&vx)[RX], float (&vy)[RY]) {
+      const int64_t left = slab - int64_t(q) * BNODE;  // nodes of the slab from this block on
+      if (q >= nkb || (g.debug & 4)) {
 #pragma unroll
-          for (int r = 0; r < RX; ++r) cp_async4(raw + raw_x + r * 128, xp[r] + q * step_x);
+        for (int r = 0; r < RX; ++r) vx[r] = 0.f;
 #pragma unroll
-          for (int r = 0; r < RY; ++r) cp_async4(raw + raw_y + r * 128, yp[r] + q * step_y);
-        } else {
-          const bool v0 = 2 * cw < left, v1 = 2 * cw + 1 < left;
+        for (int r = 0; r < RY; ++r) vy[r] = 0.f;
+      } else if (cols_full && left >= BNODE) {
 #pragma unroll
-          for (int r = 0; r < RX; ++r) {
-            const bool ok = ((okx >> r) & 1) && ((r >> 2) ? v1 : v0);
-            cp_async4(raw + raw_x + r * 128, ok ? xp[r] + q * step_x : g.x, ok ? 4u : 0u);
-          }
+        for (int r = 0; r < RX; ++r) vx[r] = __ldg(xp[r] + q * step_x);
 #pragma unroll
-          for (int r = 0; r < RY; ++r) {
-            const bool ok = ((oky >> r) & 1) && ((r / MG) ? v1 : v0);
-            cp_async4(raw + raw_y + r * 128, ok ? yp[r] + q * step_y : g.dy, ok ? 4u : 0u);
-          }
+        for (int r = 0; r < RY; ++r) vy[r] = __ldg(yp[r] + q * step_y);
+      } else {
+        const bool v0 = 2 * cw < left, v1 = 2 * cw + 1 < left;
+#pragma unroll
+        for (int r = 0; r < RX; ++r) {
+          const bool nv = (r >> 2) ? v1 : v0;
+          vx[r] = (((okx >> r) & 1) && nv) ? __ldg(xp[r] + q * step_x) : (((onex >> r) & 1) && nv) ? 1.f : 0.f;
         }
+#pragma unroll
+        for (int r = 0; r < RY; ++r) vy[r] = (((oky >> r) & 1) && ((r / MG) ? v1 : v0)) ? __ldg(yp[r] + q * step_y) : 0.f;
       }
-      cp_async_commit();
     };
-    for (int q = 0; q < kRawStages; ++q) issue(q);
+    float vx[RX], vy[RY];
+    load(0, vx, vy);
+#pragma unroll 1
     for (int q = 0; q < nkb; ++q) {
-      cp_async_wait<kRawStages - 1>();
+      float nx[RX], ny[RY];
+      load(q + 1, nx, ny);
       const int ts = q % kTileStages;
       umma::mbar_wait(bars->tile_empty + ts, uint32_t((q / kTileStages) & 1) ^ 1);
-      const uint32_t raw = raws + uint32_t(q % kRawStages) * kRaw, tile = tiles + ts * kTileBytes;
-      float vx[RX], vy[RY];
+      const uint32_t tile = tiles + ts * kTileBytes;
+      if (!(g.debug & 2)) {
 #pragma unroll
-      for (int r = 0; r < RX; ++r) vx[r] = umma::lds_f32(raw + raw_x + r * 128);
+        for (int r = 0; r < RX; ++r) {
+          float hi, lo;
+          split_mask(vx[r], hi, lo);
+          umma::sts_f32(tile + tx[r], hi);
+          umma::sts_f32(tile + kTileA + tx[r], lo);
+        }
 #pragma unroll
-      for (int r = 0; r < RY; ++r) vy[r] = umma::lds_f32(raw + raw_y + r * 128);
-#pragma unroll
-      for (int r = 0; r < RY; ++r) {
-        float hi, lo;
-        split_mask(vy[r], hi, lo);
-        umma::sts_f32(tile + ty[r], hi);
-        umma::sts_f32(tile + kTileA + ty[r], lo);
-      }
-#pragma unroll
-      for (int r = 0; r < RX; ++r) {
-        float hi, lo;
-        split_mask(vx[r], hi, lo);
-        umma::sts_f32(tile + 2 * kTileA + tx[r], hi);
-        umma::sts_f32(tile + 2 * kTileA + kTileB + tx[r], lo);
+        for (int r = 0; r < RY; ++r) {
+          float hi, lo;
+          split_mask(vy[r], hi, lo);
+          umma::sts_f32(tile + 2 * kTileA + ty[r], hi);
+          umma::sts_f32(tile + 2 * kTileA + kTileB + ty[r], lo);
+        }
       }
       umma::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(bars->tile_full + ts);
-      issue(q + kRawStages);
+#pragma unroll
+      for (int r = 0; r < RX; ++r) vx[r] = nx[r];
+#pragma unroll
+      for (int r = 0; r < RY; ++r) vy[r] = ny[r];
     }
   } else {
-    // ---- epilogue: warp w owns TMEM lanes [32w, 32w+32) = rows of dW; a thread writes runs of 16 columns ----
+    // ---- epilogue: warp w owns TMEM lanes [32w, 32w+32) = features j0 + 32w + lane; per output column the 32
+    // lanes store 32 consecutive floats of a row of dW ----
     umma::mbar_wait_relaxed(&bars->acc_full, 0);
     umma::tc_fence_after();
-    const int64_t mrow = warp * 32 + lane;
-    if (warp * 32 < g.m) {
-      float* dst = g.partial + sl * g.k * g.m;
+    const int64_t f = j0 + warp * 32 + lane;
+    float* dst = g.partial + sl * (g.k * g.m + (g.fuse_db ? g.m : 0));
 #pragma unroll 1
-      for (int c = 0; c < BF / 16; ++c) {
-        float v[16];
-        umma::tmem_ld16(tmem_base + (uint32_t(warp * 32) << 16) + c * 16, v);
+    for (int c = 0; c < ncols / 16; ++c) {
+      float v[16];
+      umma::tmem_ld16(tmem_base + (uint32_t(warp * 32) << 16) + c * 16, v);
 #pragma unroll
-        for (int a = 1; a < kAcc; ++a) {
-          float u[16];
-          umma::tmem_ld16(tmem_base + (uint32_t(warp * 32) << 16) + a * BF + c * 16, u);
+      for (int a = 1; a < kAcc; ++a) {
+        float u[16];
+        umma::tmem_ld16(tmem_base + (uint32_t(warp * 32) << 16) + a * kAccCols + c * 16, u);
 #pragma unroll
-          for (int t = 0; t < 16; ++t) v[t] += u[t];
-        }
-        if (mrow < g.m) {
+        for (int t = 0; t < 16; ++t) v[t] += u[t];
+      }
 #pragma unroll
-          for (int t = 0; t < 16; ++t) {
-            const int64_t col = j0 + c * 16 + t;
-            if (col < g.k) dst[mrow * g.k + col] = v[t];
-          }
+      for (int t = 0; t < 16; ++t) {
+        const int64_t mc = c * 16 + t;
+        if (mc < g.m) {
+          if (f < g.k) dst[mc * g.k + f] = v[t];
+          else if (f == g.k && g.fuse_db) dst[g.k * g.m + mc] = v[t];
         }
       }
     }
@@ -269,7 +272,7 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
 
 // number of node slabs the tensor-core weight gradient uses (0 = shape not supported by this kernel)
 int grad_w_tc_slabs(int64_t n, int64_t k, int64_t m, int64_t* slab_nodes) {
-  if (m > BMM || k < 2 * BF || n < 2048) return 0;
+  if (m > 128 || k < 2 * BF || n < 2048) return 0;
   const int64_t ntile = ceil_div(k, BF);
   if (ntile > kNumSMs) return 0;
   int64_t s = kNumSMs / ntile;
@@ -278,11 +281,15 @@ int grad_w_tc_slabs(int64_t n, int64_t k, int64_t m, int64_t* slab_nodes) {
   return int(ceil_div(n, sn));
 }
 
-// partial[s][m*K + k] for s < grad_w_tc_slabs(n, k, m)
-int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n, int64_t k, int64_t m, cudaStream_t stream) {
+// the bias gradient comes out of the same launch when the last feature tile has a free row
+bool grad_w_tc_fuses_db(int64_t k) { return k % BF != 0; }
+
+// partial[s][m*K + k | m] for s < grad_w_tc_slabs(n, k, m); the trailing m floats (db) only with fuse_db
+int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n, int64_t k, int64_t m, int fuse_db,
+                     cudaStream_t stream) {
   int64_t slab_nodes = 0;
   const int slabs = grad_w_tc_slabs(n, k, m, &slab_nodes);
-  if (slabs <= 0) {
+  if (slabs <= 0 || (fuse_db && !grad_w_tc_fuses_db(k))) {
     set_error("grad_w_tc: unsupported shape n=%lld k=%lld m=%lld", (long long)n, (long long)k, (long long)m);
     return LGK_ERR_UNSUPPORTED;
   }
@@ -297,7 +304,8 @@ int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n,
     }
     configured = true;
   }
-  GwArgs g{dy, x, partial, n, k, m, slab_nodes};
+  static const int debug = [] { const char* v = getenv("LGK_GW_DEBUG"); return (v && *v) ? atoi(v) : 0; }();
+  GwArgs g{dy, x, partial, n, k, m, slab_nodes, fuse_db, debug};
   const unsigned grid = unsigned(ceil_div(k, BF) * slabs);
   if (m <= 64) grad_w_tc_kernel<2><<<grid, kThreads, smem_bytes<2>(), stream>>>(g);
   else grad_w_tc_kernel<4><<<grid, kThreads, smem_bytes<4>(), stream>>>(g);

@@ -23,7 +23,9 @@ int launch_linear_tc(const float* x, const float* w, const float* bias, const fl
 // TMA-fed tensor-core transform for 16-byte aligned rows (K % 4 == 0), linear_tma.cu
 // tensor-core weight gradient of a wide transform, grad_w_tc.cu
 int grad_w_tc_slabs(int64_t n, int64_t k, int64_t m, int64_t* slab_nodes);
-int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n, int64_t k, int64_t m, cudaStream_t stream);
+bool grad_w_tc_fuses_db(int64_t k);
+int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n, int64_t k, int64_t m, int fuse_db,
+                     cudaStream_t stream);
 int launch_linear_tma(const float* x, const float* w, const float* bias, const float* rowscale, float* out, int64_t n,
                       int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream, bool* done);
 namespace {
@@ -449,7 +451,7 @@ extern "C" int64_t lgk_linear_bwd_w_workspace_bytes(int64_t n, int64_t k, int64_
   const int64_t slabs = slab_count(n);
   if (small_weight(k, m)) return align_up(slabs * (k * m + m) * 4, 256);
   const int s = std::max(choose_wsplits(n, k, m), grad_w_tc_slabs(n, k, m, nullptr));
-  return align_up(int64_t(s) * k * m * 4, 256) + align_up(slabs * m * 4, 256);
+  return align_up(int64_t(s) * (k * m + m) * 4, 256) + align_up(slabs * m * 4, 256);
 }
 
 extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float* db, int64_t n, int64_t k, int64_t m,
@@ -508,16 +510,19 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
   const int tc_slabs = use_grad_w_tc() ? grad_w_tc_slabs(n, k, m, nullptr) : 0;
   const int s = choose_wsplits(n, k, m);
   float* colpart = reinterpret_cast<float*>(static_cast<char*>(workspace) +
-                                            align_up(int64_t(std::max(s, grad_w_tc_slabs(n, k, m, nullptr))) * k * m * 4, 256));
+                                            align_up(int64_t(std::max(s, grad_w_tc_slabs(n, k, m, nullptr))) * (k * m + m) * 4, 256));
   GemmArgs g{};
   g.A = static_cast<const float*>(x); g.B = dyf;
   g.I = k; g.J = m; g.R = n; g.lda = k; g.ldb = m; g.sCi = 1; g.sCj = k;  // C(i=k_idx, j=m_idx) -> dW[m*K + k]
   g.r_chunk = align_up(ceil_div(n, s), BR);
   const bool vec = (k % 4 == 0) && (m % 4 == 0) && aligned16(x) && aligned16(dy);
-  if (tc_slabs > 0) {  // tensor cores: partial[slab][k*M + m], reduced in slab order
-    if (int rc = launch_grad_w_tc(dyf, static_cast<const float*>(x), partial, n, k, m, stream)) return rc;
-    splitk_reduce_kernel<<<unsigned(ceil_div(k * m, 256)), 256, 0, stream>>>(partial, dw, k * m, tc_slabs, accumulate);
-    LGK_CHECK_LAUNCH("splitk_reduce_kernel");
+  if (tc_slabs > 0) {  // tensor cores: partial[slab][m*K + k | m], reduced in slab order; db rides along when it can
+    const bool fuse_db = db && grad_w_tc_fuses_db(k);
+    if (int rc = launch_grad_w_tc(dyf, static_cast<const float*>(x), partial, n, k, m, fuse_db, stream)) return rc;
+    slab_reduce_kernel<<<slab_reduce_grid(k * m + (fuse_db ? m : 0)), 256, 0, stream>>>(partial, dw, fuse_db ? db : nullptr, k * m,
+                                                                                       fuse_db ? m : 0, tc_slabs, accumulate);
+    LGK_CHECK_LAUNCH("slab_reduce_kernel");
+    if (fuse_db) return LGK_OK;
   } else if (s == 1) {
     g.C = dw; g.split_stride = 0; g.accumulate = accumulate;
     if (int rc = launch_gemm<false, false>(g, 1, vec, stream, "gemm_kernel(bwd_w)")) return rc;
