@@ -15,7 +15,7 @@
 //
 // Grid: feature tiles of 128 columns of x  x  slabs of nodes, ntiles * slabs <= 148 CTAs (one per SM, one wave).
 // A CTA walks its slab in blocks of 32 nodes: 16 stager warps load the block (4 bytes per lane, 128 bytes per warp
-// load: the reference's 1025-float rows are not 16-byte aligned) into registers one block ahead, split it and write
+// load: the reference's 1025-float rows are not 16-byte aligned) into registers two blocks ahead, split it and write
 // the hi/lo tiles of a 3-deep ring (4-byte cp.async into a raw ring, as linear_tc.cu does, measured 56 us against
 // 41 us: the LDGSTS issue rate, ~10 cycles per warp instruction, was the cost); one lane issues 12 tcgen05.mma
 // (M128 N=m K8) per block; at the end 4 warps drain the
@@ -123,7 +123,8 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
     const uint32_t idesc = idesc_tf32_mn(BF, ncols);
     for (int kb = 0; kb < nkb; ++kb) {
       const int s = kb % kTileStages;
-      umma::mbar_wait(bars->tile_full + s, (kb / kTileStages) & 1);
+      umma::mbar_wait(bars->tile_full + s, (kb / kTileStages) & 1);  // acquires the stagers' generic-proxy writes
+      umma::fence_proxy_async_smem();                                // ... and hands them to the async proxy (the MMA)
       umma::tc_fence_after();
       if (lane == 0 && (g.debug & 1)) {
         umma::mma_commit(bars->tile_empty + s);
@@ -151,29 +152,20 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
   } else if (warp >= kWarpConv) {
     // ---- stagers: warp cw owns nodes 2cw and 2cw+1 of every block (all their column groups of x and dy) ----
     const int cw = warp - kWarpConv;
-    const float* xp[RX];
-    const float* yp[RY];
-    uint32_t tx[RX], ty[RY];
-    uint32_t okx = 0, oky = 0, onex = 0;  // per slot: column inside the matrix / the ones column that yields db
+    // slot r of x: node 2cw + (r >> 2), column group r & 3; of dy: node 2cw + r / MG, column group r % MG.  One base
+    // pointer and one tile offset per node parity instead of one per slot: the registers go to the staged values.
+    uint32_t okx = 0, oky = 0, onex = 0;  // per column group: inside the matrix / the ones column that yields db
 #pragma unroll
-    for (int r = 0; r < RX; ++r) {
-      const uint32_t node = 2 * cw + (r >> 2), cg = r & 3;
+    for (int cg = 0; cg < 4; ++cg) {
       const int64_t col = j0 + cg * 32 + lane;
-      const bool ok = col < g.k;
-      okx |= uint32_t(ok) << r;
-      onex |= uint32_t(g.fuse_db && col == g.k) << r;
-      xp[r] = g.x + (node0 + node) * g.k + (ok ? col : 0);
-      tx[r] = mn_offset(node, cg, lane);
+      okx |= uint32_t(col < g.k) << cg;
+      onex |= uint32_t(g.fuse_db && col == g.k) << cg;
     }
 #pragma unroll
-    for (int r = 0; r < RY; ++r) {
-      const uint32_t node = 2 * cw + r / MG, cg = r % MG;
-      const int64_t col = cg * 32 + lane;
-      const bool ok = col < g.m;
-      oky |= uint32_t(ok) << r;
-      yp[r] = g.dy + (node0 + node) * g.m + (ok ? col : 0);
-      ty[r] = mn_offset(node, cg, lane);
-    }
+    for (int cg = 0; cg < MG; ++cg) oky |= uint32_t(cg * 32 + lane < g.m) << cg;
+    const float* xb = g.x + (node0 + 2 * cw) * g.k + j0 + lane;
+    const float* yb = g.dy + (node0 + 2 * cw) * g.m + lane;
+    const uint32_t t0 = mn_offset(2 * cw, 0, lane), t1 = mn_offset(2 * cw + 1, 0, lane);
     const bool cols_full = (j0 + BF <= g.k) && (g.m == MG * 32);
     const int64_t step_x = int64_t(BNODE) * g.k, step_y = int64_t(BNODE) * g.m;
 
@@ -187,26 +179,26 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
         for (int r = 0; r < RY; ++r) vy[r] = 0.f;
       } else if (cols_full && left >= BNODE) {
 #pragma unroll
-        for (int r = 0; r < RX; ++r) vx[r] = __ldg(xp[r] + q * step_x);
+        for (int r = 0; r < RX; ++r) vx[r] = __ldg(xb + q * step_x + (r >> 2) * g.k + (r & 3) * 32);
 #pragma unroll
-        for (int r = 0; r < RY; ++r) vy[r] = __ldg(yp[r] + q * step_y);
+        for (int r = 0; r < RY; ++r) vy[r] = __ldg(yb + q * step_y + (r / MG) * g.m + (r % MG) * 32);
       } else {
         const bool v0 = 2 * cw < left, v1 = 2 * cw + 1 < left;
 #pragma unroll
         for (int r = 0; r < RX; ++r) {
           const bool nv = (r >> 2) ? v1 : v0;
-          vx[r] = (((okx >> r) & 1) && nv) ? __ldg(xp[r] + q * step_x) : (((onex >> r) & 1) && nv) ? 1.f : 0.f;
+          vx[r] = (((okx >> (r & 3)) & 1) && nv) ? __ldg(xb + q * step_x + (r >> 2) * g.k + (r & 3) * 32)
+                                                 : (((onex >> (r & 3)) & 1) && nv) ? 1.f : 0.f;
         }
 #pragma unroll
-        for (int r = 0; r < RY; ++r) vy[r] = (((oky >> r) & 1) && ((r / MG) ? v1 : v0)) ? __ldg(yp[r] + q * step_y) : 0.f;
+        for (int r = 0; r < RY; ++r)
+          vy[r] = (((oky >> (r % MG)) & 1) && ((r / MG) ? v1 : v0)) ? __ldg(yb + q * step_y + (r / MG) * g.m + (r % MG) * 32) : 0.f;
       }
     };
-    float vx[RX], vy[RY];
-    load(0, vx, vy);
-#pragma unroll 1
-    for (int q = 0; q < nkb; ++q) {
-      float nx[RX], ny[RY];
-      load(q + 1, nx, ny);
+    // Loads run two blocks ahead of the conversion; the loop is unrolled three times with the register sets changing
+    // roles (copying a set whose loads are in flight would stall on them and serialise the loop on memory latency).
+    auto step = [&](int q, const float (&vx)[RX], const float (&vy)[RY]) {
+      if (q >= nkb) return;
       const int ts = q % kTileStages;
       umma::mbar_wait(bars->tile_empty + ts, uint32_t((q / kTileStages) & 1) ^ 1);
       const uint32_t tile = tiles + ts * kTileBytes;
@@ -215,24 +207,35 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
         for (int r = 0; r < RX; ++r) {
           float hi, lo;
           split_mask(vx[r], hi, lo);
-          umma::sts_f32(tile + tx[r], hi);
-          umma::sts_f32(tile + kTileA + tx[r], lo);
+          const uint32_t to = ((r >> 2) ? t1 : t0) + (r & 3) * kGroupStride;
+          umma::sts_f32(tile + to, hi);
+          umma::sts_f32(tile + kTileA + to, lo);
         }
 #pragma unroll
         for (int r = 0; r < RY; ++r) {
           float hi, lo;
           split_mask(vy[r], hi, lo);
-          umma::sts_f32(tile + 2 * kTileA + ty[r], hi);
-          umma::sts_f32(tile + 2 * kTileA + kTileB + ty[r], lo);
+          const uint32_t to = ((r / MG) ? t1 : t0) + (r % MG) * kGroupStride;
+          umma::sts_f32(tile + 2 * kTileA + to, hi);
+          umma::sts_f32(tile + 2 * kTileA + kTileB + to, lo);
         }
       }
-      umma::fence_proxy_async_smem();
+      // no proxy fence here: fence.proxy.async compiles to MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC, and the membar would
+      // wait for this thread's prefetched loads of the next two blocks -- the MMA thread fences after its wait
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(bars->tile_full + ts);
-#pragma unroll
-      for (int r = 0; r < RX; ++r) vx[r] = nx[r];
-#pragma unroll
-      for (int r = 0; r < RY; ++r) vy[r] = ny[r];
+    };
+    float x0[RX], y0[RY], x1[RX], y1[RY], x2[RX], y2[RY];
+    load(0, x0, y0);
+    load(1, x1, y1);
+#pragma unroll 1
+    for (int q = 0; q < nkb; q += 3) {
+      load(q + 2, x2, y2);
+      step(q, x0, y0);
+      load(q + 3, x0, y0);
+      step(q + 1, x1, y1);
+      load(q + 4, x1, y1);
+      step(q + 2, x2, y2);
     }
   } else {
     // ---- epilogue: warp w owns TMEM lanes [32w, 32w+32) = features j0 + 32w + lane; per output column the 32

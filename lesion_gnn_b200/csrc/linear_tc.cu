@@ -9,14 +9,14 @@
 // the truncation of lo are ~2^-22 relative).
 //
 // Persistent kernel, one CTA per SM, tiles of 128 rows of x against 64 rows of W.  21 warps in three roles:
-//   stagers (16 warps)    cp.async (4 bytes per lane, lane = k: the reference's 1025-float rows are not 16-byte
-//                         aligned, so neither TMA tensor maps nor vector loads apply, and per-row bulk copies
-//                         of ~270 bytes measured 3x slower, 16-byte chunk copies 1.5x slower) of the raw K
-//                         blocks into a 3-deep ring in shared memory without holding a register; every thread reads
-//                         back exactly the bytes it copied (cp.async.wait_group, no barrier), splits them and
-//                         writes the hi and lo operand tiles in the K-major SWIZZLE_128B layout the tensor core
-//                         reads (a warp writes one 128-byte tile row per store: conflict free),
-//                         fence.proxy.async, arrive
+//   stagers (16 warps)    plain 4-byte loads (lane = k, 128 bytes per warp load: the reference's 1025-float rows
+//                         are not 16-byte aligned, so neither TMA tensor maps nor vector loads apply) of the K
+//                         blocks into registers, two blocks ahead of their use; split, and the hi and lo operand
+//                         tiles written in the K-major SWIZZLE_128B layout the tensor core reads (a warp writes one
+//                         128-byte tile row per store: conflict free), fence.proxy.async, arrive.  (Until r01 v3
+//                         the blocks went through a raw shared-memory ring with 4-byte cp.async: the LDGSTS issue
+//                         rate, ~10 cycles per warp instruction, made that the cost of the kernel; per-row bulk
+//                         copies of ~270 bytes measured 3x slower still, 16-byte chunk copies 1.5x slower.)
 //   MMA (1 lane)          12 tcgen05.mma.kind::tf32 (M128 N64 K8) per 32-wide K block, commit -> frees the tile
 //   epilogue (4 warps)    tcgen05.ld of the finished accumulators, row scale / bias / accumulate / ELU, store;
 //                         overlaps the next tile's main loop (two accumulator buffers in tensor memory)
@@ -27,20 +27,19 @@
 #include "common.cuh"
 #include "umma.cuh"
 #include <stdlib.h>
+#include <algorithm>
 
 namespace lgk {
 namespace {
 
 constexpr int BM = 128, BN = 64, BK = 32, kAcc = 4;
-constexpr int kRawStages = 3, kTileStages = 3;
-constexpr int kRawBytes = (BM + BN) * BK * 4;                  // one raw K block: x rows then W rows, 128 bytes each
+constexpr int kTileStages = 4;   // = stager groups
 constexpr int kTileA = BM * BK * 4, kTileB = BN * BK * 4;      // bytes of one hi (or lo) operand tile
 constexpr int kTileBytes = 2 * (kTileA + kTileB);              // A_hi, A_lo, B_hi, B_lo
-constexpr int kSmemBytes = kTileStages * kTileBytes + kRawStages * kRawBytes + 256 /*barriers*/;
+constexpr int kSmemBytes = kTileStages * kTileBytes + 256 /*barriers*/;
 constexpr int kConvWarps = 16;
 constexpr int kWarpMma = 4, kWarpConv = 5;                     // warps 0-3: epilogue (TMEM lane quadrant = warp id)
 constexpr int kThreadsTc = (kWarpConv + kConvWarps) * 32;
-constexpr int kRowsA = BM / kConvWarps, kRowsB = BN / kConvWarps;  // tile rows staged per warp: 8 and 4
 constexpr int kTmemCols = 2 * kAcc * BN;
 static_assert(BK / 8 == kAcc, "one accumulator per K step of a block");
 static_assert(kTmemCols == 512, "tensor memory allocation must be a power of two >= 32 columns");
@@ -54,6 +53,7 @@ struct TcArgs {
   float* out;
   int64_t n, k, m;
   int act, accumulate;
+  int bm;               // rows of x per tile (multiple of 16, <= BM): the MMA is always M = 128, rows >= bm are not stored
   int64_t tiles_n;      // column tiles (fastest tile index)
   int64_t tiles_total;
   int debug;  // profiling only (LGK_TC_DEBUG): 1 = no MMAs, 2 = no conversion, 4 = no global copies (bit mask)
@@ -71,73 +71,10 @@ __device__ __forceinline__ void split_mask(float x, float& hi, float& lo) {
   lo = x - hi;
 }
 
-// 4-byte asynchronous copy global -> shared (32-bit shared address); src_bytes 0 writes zeros without reading
-__device__ __forceinline__ void cp_async4(uint32_t dst, const float* src, uint32_t src_bytes) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-__device__ __forceinline__ void cp_async4(uint32_t dst, const float* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-// ---- stager ---------------------------------------------------------------------------------------------------
-// Per K block, lane = k and a warp owns 8 x rows and 4 W rows: raw element (slot, lane) lives at slot * 128 + lane * 4
-// of the raw stage (a warp touches 128 consecutive bytes: conflict free both ways).  Every thread reads back exactly
-// the bytes it copied, so cp.async.wait_group is the only synchronisation the raw ring needs.  All shared-memory
-// addresses are 32-bit shared-window addresses.
-struct StageCtx {
-  const float* xa[kRowsA];   // &x[row, lane] (clamped to row 0 when the row is outside the matrix)
-  const float* wb[kRowsB];
-  uint32_t ta[kRowsA], tb[kRowsB];   // swizzled tile byte offsets of (row, lane)
-  uint32_t raw_a, raw_b;             // raw byte offsets of this thread's first x / W element
-  uint32_t va, vb;                   // row-valid bit masks
-  bool rows_full;
-};
-
-__device__ __forceinline__ void issue_block(const TcArgs& g, const StageCtx& c, uint32_t raw, int lane, int64_t k0) {
-  if (c.rows_full && k0 + BK <= g.k) {  // interior block: no predicates
-#pragma unroll
-    for (int r = 0; r < kRowsA; ++r) cp_async4(raw + c.raw_a + r * 128, c.xa[r] + k0);
-#pragma unroll
-    for (int r = 0; r < kRowsB; ++r) cp_async4(raw + c.raw_b + r * 128, c.wb[r] + k0);
-  } else {
-    const bool kin = k0 + lane < g.k;
-    const int64_t ko = kin ? k0 : 0;
-#pragma unroll
-    for (int r = 0; r < kRowsA; ++r) cp_async4(raw + c.raw_a + r * 128, c.xa[r] + ko, (kin && ((c.va >> r) & 1)) ? 4u : 0u);
-#pragma unroll
-    for (int r = 0; r < kRowsB; ++r) cp_async4(raw + c.raw_b + r * 128, c.wb[r] + ko, (kin && ((c.vb >> r) & 1)) ? 4u : 0u);
-  }
-}
-
-__device__ __forceinline__ void convert_block(const StageCtx& c, uint32_t raw, uint32_t tile) {
-  float va[kRowsA], vb[kRowsB];
-#pragma unroll
-  for (int r = 0; r < kRowsA; ++r) va[r] = umma::lds_f32(raw + c.raw_a + r * 128);
-#pragma unroll
-  for (int r = 0; r < kRowsB; ++r) vb[r] = umma::lds_f32(raw + c.raw_b + r * 128);
-#pragma unroll
-  for (int r = 0; r < kRowsA; ++r) {
-    float hi, lo;
-    split_mask(va[r], hi, lo);
-    umma::sts_f32(tile + c.ta[r], hi);
-    umma::sts_f32(tile + kTileA + c.ta[r], lo);
-  }
-#pragma unroll
-  for (int r = 0; r < kRowsB; ++r) {
-    float hi, lo;
-    split_mask(vb[r], hi, lo);
-    umma::sts_f32(tile + 2 * kTileA + c.tb[r], hi);
-    umma::sts_f32(tile + 2 * kTileA + kTileB + c.tb[r], lo);
-  }
-}
-
 // ---- epilogue -------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void epilogue_tile(const TcArgs& g, uint32_t tmem_acc, int nacc, int warp, int lane, int64_t i0,
                                               int64_t j0) {
-  const int64_t i = i0 + warp * 32 + lane;
+  const int64_t i = (warp * 32 + lane < g.bm) ? i0 + warp * 32 + lane : g.n;  // rows of the MMA above bm: not stored
   const float rs = (g.rowscale && i < g.n) ? __ldg(g.rowscale + i) : 1.f;
 #pragma unroll 1
   for (int c = 0; c < BN / 16; ++c) {
@@ -185,11 +122,11 @@ __device__ __forceinline__ void epilogue_tile(const TcArgs& g, uint32_t tmem_acc
 }
 
 // ---- kernel ---------------------------------------------------------------------------------------------------
+template <int NA>
 __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
   extern __shared__ __align__(1024) uint8_t smem_dyn[];  // SWIZZLE_128B tiles need a 1024-byte aligned base
   const uint32_t tiles = umma::smem_u32(smem_dyn);        // operand tile ring
-  const uint32_t raws = tiles + kTileStages * kTileBytes;  // raw K block ring
-  Bars* bars = reinterpret_cast<Bars*>(smem_dyn + kTileStages * kTileBytes + kRawStages * kRawBytes);
+  Bars* bars = reinterpret_cast<Bars*>(smem_dyn + kTileStages * kTileBytes);
   if ((tiles & 1023u) != 0) __trap();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -197,7 +134,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTileStages; ++s) {
-      umma::mbar_init(bars->tile_full + s, kConvWarps);
+      umma::mbar_init(bars->tile_full + s, kConvWarps / kTileStages);  // the warps of one stager group
       umma::mbar_init(bars->tile_empty + s, 1);
     }
     for (int s = 0; s < 2; ++s) {
@@ -222,7 +159,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
       umma::tc_fence_after();
       for (int kb = 0; kb < nkb; ++kb, ++it) {
         const int s = it % kTileStages;
-        umma::mbar_wait(bars->tile_full + s, (it / kTileStages) & 1);
+        umma::mbar_wait(bars->tile_full + s, (it / kTileStages) & 1);  // acquires the stagers' generic-proxy writes
+        umma::fence_proxy_async_smem();                                // ... and hands them to the async proxy (the MMA)
         umma::tc_fence_after();
         if (lane == 0 && (g.debug & 1)) {
           umma::mma_commit(bars->tile_empty + s);
@@ -253,66 +191,74 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
       }
     }
   } else if (warp >= kWarpConv) {
-    // ---- stagers ----
+    // ---- stagers: group grp (4 warps) stages the K blocks q = grp (mod 4) into tile stage grp ----
+    // One batch of loads per block and thread (bm/4 x rows + 16 W rows of this warp, lane = k), consumed in the same
+    // iteration: the four groups are in different phases of load / wait / convert, which is what overlaps the
+    // memory latency (four blocks = 4 x 18-24 KB in flight per SM).
     const int cw = warp - kWarpConv;
-    StageCtx c;
-#pragma unroll
-    for (int r = 0; r < kRowsA; ++r) c.ta[r] = umma::sw128_offset_f32(cw * kRowsA + r, lane);
-#pragma unroll
-    for (int r = 0; r < kRowsB; ++r) c.tb[r] = umma::sw128_offset_f32(cw * kRowsB + r, lane);
-    c.raw_a = uint32_t(cw * kRowsA) * 128 + lane * 4;
-    c.raw_b = uint32_t(BM + cw * kRowsB) * 128 + lane * 4;
-    // the K blocks of all tiles of this CTA form one sequence: block q = (tile q / nkb, K block q % nkb); copies
-    // run kRawStages blocks ahead of the conversion, across tile boundaries
+    const int grp = cw >> 2, wg = cw & 3;
+    constexpr int RA = 4 * NA, RB = BN / 4;
     const int64_t my_tiles = (g.tiles_total - blockIdx.x + gridDim.x - 1) / gridDim.x;
-    const int64_t total = my_tiles * nkb;
-    int64_t tile_of_ctx = -1;
-    auto set_tile = [&](int64_t lt) {  // row pointers of local tile lt
-      const int64_t t = blockIdx.x + lt * gridDim.x;
-      const int64_t i0 = (t / g.tiles_n) * BM, j0 = (t % g.tiles_n) * BN;
-      c.va = c.vb = 0;
+    const int64_t total = my_tiles * nkb;   // the K blocks of all tiles of this CTA form one sequence
+    const uint32_t swz = uint32_t(lane) >> 2, lo2 = (uint32_t(lane) & 3u) << 2;
+    const uint32_t tile = tiles + grp * kTileBytes;
+#pragma unroll 1
+    for (int64_t q = grp; q < total; q += kTileStages) {
+      const int64_t lt = q / nkb, t = blockIdx.x + lt * gridDim.x;
+      const int64_t i0 = (t / g.tiles_n) * g.bm + wg * RA, j0 = (t % g.tiles_n) * BN + wg * RB;  // first rows of this warp
+      const int64_t k0 = (q - lt * nkb) * BK;
+      const float* xa = g.x + i0 * g.k + k0 + lane;
+      const float* wb = g.w + j0 * g.k + k0 + lane;
+      float va[RA], vb[RB];
+      if (g.debug & 4) {
 #pragma unroll
-      for (int r = 0; r < kRowsA; ++r) {
-        const int64_t row = i0 + cw * kRowsA + r;
-        const bool ok = row < g.n;
-        c.va |= uint32_t(ok) << r;
-        c.xa[r] = g.x + (ok ? row : 0) * g.k + lane;
-      }
+        for (int r = 0; r < RA; ++r) va[r] = 0.f;
 #pragma unroll
-      for (int r = 0; r < kRowsB; ++r) {
-        const int64_t row = j0 + cw * kRowsB + r;
-        const bool ok = row < g.m;
-        c.vb |= uint32_t(ok) << r;
-        c.wb[r] = g.w + (ok ? row : 0) * g.k + lane;
+        for (int r = 0; r < RB; ++r) vb[r] = 0.f;
+      } else if (i0 + RA <= g.n && j0 + RB <= g.m && k0 + BK <= g.k) {  // interior: no predicates
+#pragma unroll
+        for (int r = 0; r < RA; ++r) va[r] = __ldg(xa + r * g.k);
+#pragma unroll
+        for (int r = 0; r < RB; ++r) vb[r] = __ldg(wb + r * g.k);
+      } else {
+        const bool kin = k0 + lane < g.k;
+#pragma unroll
+        for (int r = 0; r < RA; ++r) va[r] = (kin && i0 + r < g.n) ? __ldg(xa + r * g.k) : 0.f;
+#pragma unroll
+        for (int r = 0; r < RB; ++r) vb[r] = (kin && j0 + r < g.m) ? __ldg(wb + r * g.k) : 0.f;
       }
-      c.rows_full = (i0 + BM <= g.n) && (j0 + BN <= g.m);
-      tile_of_ctx = lt;
-    };
-    auto issue = [&](int64_t q) {
-      if (q < total && !(g.debug & 4)) {
-        const int64_t lt = q / nkb;
-        if (lt != tile_of_ctx) set_tile(lt);
-        issue_block(g, c, raws + uint32_t(q % kRawStages) * kRawBytes, lane, (q - lt * nkb) * BK);
+      umma::mbar_wait(bars->tile_empty + grp, uint32_t((q / kTileStages) & 1) ^ 1);
+      if (!(g.debug & 2)) {
+#pragma unroll
+        for (int r = 0; r < RA; ++r) {
+          const uint32_t row = uint32_t(wg * RA + r);
+          const uint32_t off = tile + row * 128u + (((swz ^ row) & 7u) << 4) + lo2;
+          float hi, lo;
+          split_mask(va[r], hi, lo);
+          umma::sts_f32(off, hi);
+          umma::sts_f32(off + kTileA, lo);
+        }
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          const uint32_t row = uint32_t(wg * RB + r);
+          const uint32_t off = tile + 2 * kTileA + row * 128u + (((swz ^ row) & 7u) << 4) + lo2;
+          float hi, lo;
+          split_mask(vb[r], hi, lo);
+          umma::sts_f32(off, hi);
+          umma::sts_f32(off + kTileB, lo);
+        }
       }
-      cp_async_commit();  // an (empty) group per block keeps the wait_group arithmetic uniform
-    };
-    for (int q = 0; q < kRawStages; ++q) issue(q);
-    for (int64_t q = 0; q < total; ++q) {
-      cp_async_wait<kRawStages - 1>();  // this thread's copies of block q have landed
-      const int ts = int(q % kTileStages);
-      umma::mbar_wait(bars->tile_empty + ts, uint32_t((q / kTileStages) & 1) ^ 1);
-      if (!(g.debug & 2)) convert_block(c, raws + uint32_t(q % kRawStages) * kRawBytes, tiles + ts * kTileBytes);
-      umma::fence_proxy_async_smem();
+      // no proxy fence here: fence.proxy.async compiles to MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC; the MMA thread fences
+      // after it has acquired these writes through the barrier
       __syncwarp();
-      if (lane == 0) umma::mbar_arrive(bars->tile_full + ts);
-      issue(q + kRawStages);  // refill the raw slot just consumed (the same thread wrote and read it)
+      if (lane == 0) umma::mbar_arrive(bars->tile_full + grp);
     }
   } else {
     // ---- epilogue: warp w < 4 owns TMEM lanes [32w, 32w+32) = rows i0 + 32w + lane ----
     const int nacc = kAcc;  // every K block feeds all four accumulators (one per K step of 8)
     uint32_t li = 0;
     for (int64_t t = blockIdx.x; t < g.tiles_total; t += gridDim.x, ++li) {
-      const int64_t i0 = (t / g.tiles_n) * BM, j0 = (t % g.tiles_n) * BN;
+      const int64_t i0 = (t / g.tiles_n) * g.bm, j0 = (t % g.tiles_n) * BN;
       const uint32_t ab = li & 1;
       umma::mbar_wait_relaxed(bars->acc_full + ab, (li >> 1) & 1);
       umma::tc_fence_after();
@@ -334,20 +280,36 @@ int launch_linear_tc(const float* x, const float* w, const float* bias, const fl
                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream) {
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(linear_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    cudaError_t e = cudaSuccess;
+    for (auto* fn : {linear_tc_kernel<4>, linear_tc_kernel<5>, linear_tc_kernel<6>, linear_tc_kernel<7>, linear_tc_kernel<8>})
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     if (e != cudaSuccess) {
       set_error("linear_tc_kernel: cannot reserve %d bytes of shared memory: %s", kSmemBytes, cudaGetErrorString(e));
       return LGK_ERR_LAUNCH;
     }
     configured = true;
   }
-  TcArgs g{x, w, bias, rowscale, out, n, k, m, act, accumulate, 0, 0, 0};
+  TcArgs g{x, w, bias, rowscale, out, n, k, m, act, accumulate, BM, 0, 0, 0};
   static const int debug = [] { const char* v = getenv("LGK_TC_DEBUG"); return (v && *v) ? atoi(v) : 0; }();
   g.debug = debug;
   g.tiles_n = ceil_div(m, BN);
-  g.tiles_total = ceil_div(n, BM) * g.tiles_n;
+  // tile height: the smallest multiple of 16 rows that still covers the matrix in the same number of waves, so that a
+  // batch of 11 583 nodes becomes 145 tiles of 80 rows on 145 SMs instead of 91 tiles of 128 rows on 91 SMs (the
+  // kernel is bound by what one SM can pull from memory, not by the MMAs, whose M stays 128)
+  {
+    const int64_t waves = ceil_div(ceil_div(n, BM) * g.tiles_n, kNumSMs);
+    const int64_t row_tiles = std::max<int64_t>(1, waves * kNumSMs / g.tiles_n);
+    g.bm = int(std::min<int64_t>(BM, std::max<int64_t>(64, align_up(ceil_div(n, row_tiles), 16))));
+  }
+  g.tiles_total = ceil_div(n, g.bm) * g.tiles_n;
   const unsigned grid = unsigned(g.tiles_total < kNumSMs ? g.tiles_total : kNumSMs);
-  linear_tc_kernel<<<grid, kThreadsTc, kSmemBytes, stream>>>(g);
+  switch (g.bm / kConvWarps) {  // x rows per stager warp
+    case 4: linear_tc_kernel<4><<<grid, kThreadsTc, kSmemBytes, stream>>>(g); break;
+    case 5: linear_tc_kernel<5><<<grid, kThreadsTc, kSmemBytes, stream>>>(g); break;
+    case 6: linear_tc_kernel<6><<<grid, kThreadsTc, kSmemBytes, stream>>>(g); break;
+    case 7: linear_tc_kernel<7><<<grid, kThreadsTc, kSmemBytes, stream>>>(g); break;
+    default: linear_tc_kernel<8><<<grid, kThreadsTc, kSmemBytes, stream>>>(g); break;
+  }
   LGK_CHECK_LAUNCH("linear_tc_kernel");
   return LGK_OK;
 }

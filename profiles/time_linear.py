@@ -16,6 +16,7 @@ if len(sys.argv) > 1:
     shapes = shapes[:int(sys.argv[1])]
 for (n, k, m) in shapes:
     nv = max(2, min(8, int(300e6 / (4 * n * (k + m))) + 1))
+    nv = int(os.environ.get("NV", nv))   # NV=1: inputs stay in L2 (is DRAM the limiter?)
     xs = [torch.randn(n, k, device=dev) for _ in range(nv)]
     dys = [torch.randn(n, m, device=dev) for _ in range(nv)]
     outs = [torch.empty(n, m, device=dev) for _ in range(nv)]
