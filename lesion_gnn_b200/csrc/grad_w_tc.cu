@@ -14,11 +14,11 @@
 // fed with ones, so D[K, m] = db[m] -- no separate column-sum pass over dy.
 //
 // Grid: feature tiles of 128 columns of x  x  slabs of nodes, ntiles * slabs <= 148 CTAs (one per SM, one wave).
-// A CTA walks its slab in blocks of 32 nodes: 16 stager warps load the block (4 bytes per lane, 128 bytes per warp
-// load: the reference's 1025-float rows are not 16-byte aligned) into registers two blocks ahead, split it and write
-// the hi/lo tiles of a 3-deep ring (4-byte cp.async into a raw ring, as linear_tc.cu does, measured 56 us against
-// 41 us: the LDGSTS issue rate, ~10 cycles per warp instruction, was the cost); one lane issues 12 tcgen05.mma
-// (M128 N=m K8) per block; at the end 4 warps drain the
+// A CTA walks its slab in blocks of 32 nodes: 16 stager warps in four phase-shifted groups (group = block index
+// mod 4) load their block (4 bytes per lane, 128 bytes per warp load: the reference's 1025-float rows are not
+// 16-byte aligned) into registers, split it and write the hi/lo tiles of a 4-deep ring (4-byte cp.async into a
+// raw ring measured 56 us against 38 us: the LDGSTS issue rate, ~10 cycles per warp instruction, was the cost);
+// one lane issues 12 tcgen05.mma (M128 N=m K8) per block; at the end 4 warps drain the
 // accumulators into partial[slab][m*K + k | m] (the layout of dW, then db), which lgk_linear_bwd_w reduces in
 // slab order (deterministic).  m <= 128.
 #include "common.cuh"
@@ -44,7 +44,8 @@ static_assert(kTmemCols == 512, "tensor memory allocation must be a power of two
 // MG = 32-column groups of dy (m <= 32 MG): the dy tiles take MG * 4 KB each
 template <int MG> constexpr int tile_b() { return MG * kGroupStride; }
 template <int MG> constexpr int tile_bytes() { return 2 * (kTileA + tile_b<MG>()); }
-template <int MG> constexpr int tile_stages() { return 3; }
+template <int MG> constexpr int tile_stages() { return MG <= 2 ? 4 : 3; }
+template <int MG> constexpr int stager_groups() { return MG <= 2 ? 4 : 2; }
 template <int MG> constexpr int smem_bytes() { return tile_stages<MG>() * tile_bytes<MG>() + 256; }
 static_assert(smem_bytes<4>() <= 227 * 1024 && smem_bytes<2>() <= 227 * 1024, "shared memory budget");
 
@@ -59,7 +60,7 @@ struct GwArgs {
 };
 
 struct Bars {
-  uint64_t tile_full[3], tile_empty[3];
+  uint64_t tile_full[4], tile_empty[4];
   uint64_t acc_full;
   uint32_t tmem_slot;
 };
@@ -77,16 +78,13 @@ __device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t saddr) {
   return uint64_t((saddr & 0x3FFFFu) >> 4) | (uint64_t(kGroupStride >> 4) << 16) | (uint64_t(kSbo >> 4) << 32) |
          (uint64_t(1) << 46) | (uint64_t(1) << 61);
 }
-// byte offset of (node r of the block, column group cg, column lane) inside an operand tile
-__device__ __forceinline__ uint32_t mn_offset(uint32_t r, uint32_t cg, uint32_t lane) {
-  return cg * kGroupStride + r * 128u + ((((lane >> 3) ^ r) & 3u) << 5) + ((lane & 7u) << 2);
-}
+// element (node r of the block, column group cg, column c) of an operand tile lives at
+//   cg * kGroupStride + r * 128 + (((c >> 3) ^ r) & 3) * 32 + (c & 7) * 4
 __host__ __device__ constexpr uint32_t idesc_tf32_mn(int m, int n) { return umma::idesc_tf32(m, n) | (1u << 15) | (1u << 16); }  // A, B MN-major
 
 template <int MG>
 __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
   constexpr int kTileB = tile_b<MG>(), kTileBytes = tile_bytes<MG>(), kTileStages = tile_stages<MG>();
-  constexpr int RX = 8, RY = 2 * MG;  // (node, column group) slots per stager warp: x and dy
   extern __shared__ __align__(1024) uint8_t smem_dyn[];
   const uint32_t tiles = umma::smem_u32(smem_dyn);
   Bars* bars = reinterpret_cast<Bars*>(smem_dyn + kTileStages * kTileBytes);
@@ -107,7 +105,7 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
   umma::fence_proxy_async_smem();
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTileStages; ++s) {
-      umma::mbar_init(bars->tile_full + s, kConvWarps);
+      umma::mbar_init(bars->tile_full + s, kConvWarps / stager_groups<MG>());  // the warps of one stager group
       umma::mbar_init(bars->tile_empty + s, 1);
     }
     umma::mbar_init(&bars->acc_full, 1);
@@ -150,10 +148,15 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
       __syncwarp();
     }
   } else if (warp >= kWarpConv) {
-    // ---- stagers: warp cw owns nodes 2cw and 2cw+1 of every block (all their column groups of x and dy) ----
+    // ---- stagers: group grp stages the node blocks q = grp (mod kGroups); inside a group a warp owns NPW nodes of
+    // the block with all their column groups of x and dy.  One batch of loads per block and thread, consumed in the
+    // same iteration: the groups are in different phases of load / wait / convert, which is what overlaps the memory
+    // latency.  (Register prefetch across iterations does not: the compiler tracks all loads of the loop with one
+    // scoreboard, so the first use of the oldest batch waits for the newest as well.)
+    constexpr int kGroups = stager_groups<MG>(), WPG = kConvWarps / kGroups, NPW = BNODE / WPG;
+    constexpr int RX = NPW * 4, RY = NPW * MG;
     const int cw = warp - kWarpConv;
-    // slot r of x: node 2cw + (r >> 2), column group r & 3; of dy: node 2cw + r / MG, column group r % MG.  One base
-    // pointer and one tile offset per node parity instead of one per slot: the registers go to the staged values.
+    const int grp = cw / WPG, wg = cw % WPG;
     uint32_t okx = 0, oky = 0, onex = 0;  // per column group: inside the matrix / the ones column that yields db
 #pragma unroll
     for (int cg = 0; cg < 4; ++cg) {
@@ -163,79 +166,61 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
     }
 #pragma unroll
     for (int cg = 0; cg < MG; ++cg) oky |= uint32_t(cg * 32 + lane < g.m) << cg;
-    const float* xb = g.x + (node0 + 2 * cw) * g.k + j0 + lane;
-    const float* yb = g.dy + (node0 + 2 * cw) * g.m + lane;
-    const uint32_t t0 = mn_offset(2 * cw, 0, lane), t1 = mn_offset(2 * cw + 1, 0, lane);
     const bool cols_full = (j0 + BF <= g.k) && (g.m == MG * 32);
-    const int64_t step_x = int64_t(BNODE) * g.k, step_y = int64_t(BNODE) * g.m;
-
-    // global -> registers one block ahead of the conversion (coalesced 128-byte warp loads; zeros outside the matrix)
-    auto load = [&](int q, float (&vx)[RX], float (&vy)[RY]) {
-      const int64_t left = slab - int64_t(q) * BNODE;  // nodes of the slab from this block on
-      if (q >= nkb || (g.debug & 4)) {
+    const uint32_t sw = uint32_t(lane) >> 3, lo3 = (uint32_t(lane) & 7u) << 2;
+#pragma unroll 1
+    for (int q = grp; q < nkb; q += kGroups) {
+      const int64_t nb = int64_t(q) * BNODE + wg * NPW;  // first node of this warp, relative to the slab
+      const float* xb = g.x + (node0 + nb) * g.k + j0 + lane;
+      const float* yb = g.dy + (node0 + nb) * g.m + lane;
+      float vx[RX], vy[RY];
+      if (g.debug & 4) {
 #pragma unroll
         for (int r = 0; r < RX; ++r) vx[r] = 0.f;
 #pragma unroll
         for (int r = 0; r < RY; ++r) vy[r] = 0.f;
-      } else if (cols_full && left >= BNODE) {
+      } else if (cols_full && nb + NPW <= slab) {
 #pragma unroll
-        for (int r = 0; r < RX; ++r) vx[r] = __ldg(xb + q * step_x + (r >> 2) * g.k + (r & 3) * 32);
+        for (int r = 0; r < RX; ++r) vx[r] = __ldg(xb + (r >> 2) * g.k + (r & 3) * 32);
 #pragma unroll
-        for (int r = 0; r < RY; ++r) vy[r] = __ldg(yb + q * step_y + (r / MG) * g.m + (r % MG) * 32);
+        for (int r = 0; r < RY; ++r) vy[r] = __ldg(yb + (r / MG) * g.m + (r % MG) * 32);
       } else {
-        const bool v0 = 2 * cw < left, v1 = 2 * cw + 1 < left;
 #pragma unroll
         for (int r = 0; r < RX; ++r) {
-          const bool nv = (r >> 2) ? v1 : v0;
-          vx[r] = (((okx >> (r & 3)) & 1) && nv) ? __ldg(xb + q * step_x + (r >> 2) * g.k + (r & 3) * 32)
+          const bool nv = nb + (r >> 2) < slab;
+          vx[r] = (((okx >> (r & 3)) & 1) && nv) ? __ldg(xb + (r >> 2) * g.k + (r & 3) * 32)
                                                  : (((onex >> (r & 3)) & 1) && nv) ? 1.f : 0.f;
         }
 #pragma unroll
         for (int r = 0; r < RY; ++r)
-          vy[r] = (((oky >> (r % MG)) & 1) && ((r / MG) ? v1 : v0)) ? __ldg(yb + q * step_y + (r / MG) * g.m + (r % MG) * 32) : 0.f;
+          vy[r] = (((oky >> (r % MG)) & 1) && nb + r / MG < slab) ? __ldg(yb + (r / MG) * g.m + (r % MG) * 32) : 0.f;
       }
-    };
-    // Loads run two blocks ahead of the conversion; the loop is unrolled three times with the register sets changing
-    // roles (copying a set whose loads are in flight would stall on them and serialise the loop on memory latency).
-    auto step = [&](int q, const float (&vx)[RX], const float (&vy)[RY]) {
-      if (q >= nkb) return;
       const int ts = q % kTileStages;
       umma::mbar_wait(bars->tile_empty + ts, uint32_t((q / kTileStages) & 1) ^ 1);
       const uint32_t tile = tiles + ts * kTileBytes;
       if (!(g.debug & 2)) {
 #pragma unroll
         for (int r = 0; r < RX; ++r) {
+          const uint32_t node = uint32_t(wg * NPW + (r >> 2));
+          const uint32_t to = tile + (r & 3) * kGroupStride + node * 128u + (((sw ^ node) & 3u) << 5) + lo3;
           float hi, lo;
           split_mask(vx[r], hi, lo);
-          const uint32_t to = ((r >> 2) ? t1 : t0) + (r & 3) * kGroupStride;
-          umma::sts_f32(tile + to, hi);
-          umma::sts_f32(tile + kTileA + to, lo);
+          umma::sts_f32(to, hi);
+          umma::sts_f32(to + kTileA, lo);
         }
 #pragma unroll
         for (int r = 0; r < RY; ++r) {
+          const uint32_t node = uint32_t(wg * NPW + r / MG);
+          const uint32_t to = tile + 2 * kTileA + (r % MG) * kGroupStride + node * 128u + (((sw ^ node) & 3u) << 5) + lo3;
           float hi, lo;
           split_mask(vy[r], hi, lo);
-          const uint32_t to = ((r / MG) ? t1 : t0) + (r % MG) * kGroupStride;
-          umma::sts_f32(tile + 2 * kTileA + to, hi);
-          umma::sts_f32(tile + 2 * kTileA + kTileB + to, lo);
+          umma::sts_f32(to, hi);
+          umma::sts_f32(to + kTileB, lo);
         }
       }
-      // no proxy fence here: fence.proxy.async compiles to MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC, and the membar would
-      // wait for this thread's prefetched loads of the next two blocks -- the MMA thread fences after its wait
+      // no proxy fence here (it would compile to a MEMBAR.ALL.CTA per block): the MMA thread fences after its wait
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(bars->tile_full + ts);
-    };
-    float x0[RX], y0[RY], x1[RX], y1[RY], x2[RX], y2[RY];
-    load(0, x0, y0);
-    load(1, x1, y1);
-#pragma unroll 1
-    for (int q = 0; q < nkb; q += 3) {
-      load(q + 2, x2, y2);
-      step(q, x0, y0);
-      load(q + 3, x0, y0);
-      step(q + 1, x1, y1);
-      load(q + 4, x1, y1);
-      step(q + 2, x2, y2);
     }
   } else {
     // ---- epilogue: warp w owns TMEM lanes [32w, 32w+32) = features j0 + 32w + lane; per output column the 32
