@@ -19,12 +19,12 @@ namespace {
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;  // 2048
+constexpr int kSingleScanBlocks = 16;                  // up to 32 768 nodes: the whole scan in one CTA per array
 
 constexpr int kSortRows = 128;     // rows per CTA window
 constexpr int kSortThreads = 256;
 constexpr int kSortCap = 4096;     // keys staged in shared memory per CTA (32 KB)
 constexpr int kSmallRow = 64;      // rank-by-counting up to this bucket size
-constexpr int kBigSmem = 4096;     // bitonic in shared memory up to this bucket size
 
 // ---- histogram of dst and src in one pass over edge_index ---------------------------------------
 __global__ void __launch_bounds__(256) hist_kernel(const int64_t* __restrict__ src, const int64_t* __restrict__ dst,
@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(256) hist_kernel(const int64_t* __restrict__ s
 
 // ---- exclusive scan: ptr[0..n] from cnt[0..n), three small kernels, gridDim.y selects the array --
 struct ScanArgs {
-  const int* in[2];
+  int* in[2];
   int* out[2];
   int* sums[2];
 };
@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_sums_kernel(ScanArgs a, int
 
 __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(ScanArgs a, int64_t n) {
   __shared__ int s_warp[32];
-  const int* in = a.in[blockIdx.y];
+  int* in = a.in[blockIdx.y];
   int* out = a.out[blockIdx.y];
   int64_t base = int64_t(blockIdx.x) * kScanTile + int64_t(threadIdx.x) * kScanItems;
   int v[kScanItems];
@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(ScanArgs a, in
 #pragma unroll
   for (int i = 0; i < kScanItems; ++i) {
     v[i] = (base + i < n) ? in[base + i] : 0;
+    if (base + i < n) in[base + i] = 0;  // the counts become the cursors of the bucket fill
     sum += v[i];
   }
   int total;
@@ -125,6 +126,35 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(ScanArgs a, in
   }
   // out[n] = grand total, written by the thread that owns element n-1
   if (base <= n - 1 && n - 1 < base + kScanItems) out[n] = ex;
+}
+
+// the whole scan in one CTA per array (a batch of lesion graphs has ~10^4 nodes: three dependent launches of a few
+// CTAs each cost more in launch latency than the scan itself)
+__global__ void __launch_bounds__(kScanThreads) scan_single_kernel(ScanArgs a, int64_t n) {
+  __shared__ int s_warp[32];
+  int* in = a.in[blockIdx.y];
+  int* out = a.out[blockIdx.y];
+  int carry = 0;
+  for (int64_t tile = 0; tile < n; tile += kScanTile) {
+    const int64_t base = tile + int64_t(threadIdx.x) * kScanItems;
+    int v[kScanItems];
+    int sum = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      v[i] = (base + i < n) ? in[base + i] : 0;
+      if (base + i < n) in[base + i] = 0;
+      sum += v[i];
+    }
+    int total;
+    int ex = block_exclusive_scan(sum, &total, s_warp) + carry;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      if (base + i < n) out[base + i] = ex;
+      ex += v[i];
+    }
+    if (base <= n - 1 && n - 1 < base + kScanItems) out[n] = ex;
+    carry += total;
+  }
 }
 
 // ---- bucket fill: CSR keys ------------------------------------------------------------------------
@@ -163,9 +193,42 @@ __device__ __forceinline__ void emit(const EmitArgs& ea, int f, int bucket, uint
   }
 }
 
+// ---- big buckets: the whole CTA sorts one bucket with a bitonic network (ascending comparators only, so the
+//      virtual +inf padding above `d` never moves) ------------------------------------------------------
+template <typename KeyPtr>
+__device__ __forceinline__ void bitonic_sort(KeyPtr k, int d) {
+  int n2 = 1;
+  while (n2 < d) n2 <<= 1;
+  for (int size = 2; size <= n2; size <<= 1) {
+    int half = size >> 1;
+    for (int i = threadIdx.x; i < (n2 >> 1); i += blockDim.x) {  // flip
+      int blk = i / half, off = i - blk * half;
+      int a = blk * size + off, b = blk * size + size - 1 - off;
+      if (b < d) {
+        uint64_t ka = k[a], kb = k[b];
+        if (ka > kb) { k[a] = kb; k[b] = ka; }
+      }
+    }
+    __syncthreads();
+    for (int j = half >> 1; j >= 1; j >>= 1) {  // disperse
+      for (int i = threadIdx.x; i < (n2 >> 1); i += blockDim.x) {
+        int blk = i / j, off = i - blk * j;
+        int a = blk * 2 * j + off, b = a + j;
+        if (b < d) {
+          uint64_t ka = k[a], kb = k[b];
+          if (ka > kb) { k[a] = kb; k[b] = ka; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
 // ---- small buckets: rank by counting, thread per entry ----------------------------------------------
-__global__ void __launch_bounds__(kSortThreads) sort_small_kernel(const int* __restrict__ ptr, const uint64_t* __restrict__ keys,
-                                                                  int64_t N, EmitArgs ea, int* __restrict__ big_flag) {
+// Buckets above kSmallRow entries (rare: hubs of a non-kNN graph) are sorted afterwards by the same CTA, one at a
+// time -- a separate launch for them cost ~4 us per build whether or not a big bucket existed.
+__global__ void __launch_bounds__(kSortThreads) sort_window_kernel(const int* __restrict__ ptr, uint64_t* __restrict__ keys,
+                                                                   int64_t N, EmitArgs ea) {
   __shared__ int s_ptr[kSortRows + 1];
   __shared__ uint64_t s_keys[kSortCap];
   int64_t r0 = int64_t(blockIdx.x) * kSortRows;
@@ -200,68 +263,18 @@ __global__ void __launch_bounds__(kSortThreads) sort_small_kernel(const int* __r
     }
     emit(ea, w0 + a + rank, int(r0) + lo, mine);
   }
-  if (saw_big) *big_flag = 1;  // benign race: every writer stores 1
-}
-
-// ---- big buckets: one CTA per bucket, bitonic network (ascending comparators only, so the virtual
-//      +inf padding above `d` never moves) -------------------------------------------------------------
-template <typename KeyPtr>
-__device__ __forceinline__ void bitonic_sort(KeyPtr k, int d) {
-  int n2 = 1;
-  while (n2 < d) n2 <<= 1;
-  for (int size = 2; size <= n2; size <<= 1) {
-    int half = size >> 1;
-    for (int i = threadIdx.x; i < (n2 >> 1); i += blockDim.x) {  // flip
-      int blk = i / half, off = i - blk * half;
-      int a = blk * size + off, b = blk * size + size - 1 - off;
-      if (b < d) {
-        uint64_t ka = k[a], kb = k[b];
-        if (ka > kb) { k[a] = kb; k[b] = ka; }
-      }
-    }
-    __syncthreads();
-    for (int j = half >> 1; j >= 1; j >>= 1) {  // disperse
-      for (int i = threadIdx.x; i < (n2 >> 1); i += blockDim.x) {
-        int blk = i / j, off = i - blk * j;
-        int a = blk * 2 * j + off, b = a + j;
-        if (b < d) {
-          uint64_t ka = k[a], kb = k[b];
-          if (ka > kb) { k[a] = kb; k[b] = ka; }
-        }
-      }
+  if (!__syncthreads_or(saw_big)) return;
+  for (int lo = 0; lo < nrows; ++lo) {  // CTA-uniform walk over the window's rows
+    const int a = s_ptr[lo], d = s_ptr[lo + 1] - a;
+    if (d <= kSmallRow) continue;
+    if (d <= kSortCap) {
+      for (int i = threadIdx.x; i < d; i += blockDim.x) s_keys[i] = keys[a + i];
       __syncthreads();
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256) sort_big_kernel(const int* __restrict__ ptr, uint64_t* __restrict__ keys, int64_t N,
-                                                       EmitArgs ea, const int* __restrict__ big_flag) {
-  __shared__ uint64_t s_keys[kBigSmem];
-  __shared__ int s_rows[256];
-  __shared__ int s_nbig;
-  if (*big_flag == 0) return;
-  for (int64_t base = int64_t(blockIdx.x) * blockDim.x; base < N; base += int64_t(gridDim.x) * blockDim.x) {
-    if (threadIdx.x == 0) s_nbig = 0;
-    __syncthreads();
-    int64_t r = base + threadIdx.x;
-    if (r < N && ptr[r + 1] - ptr[r] > kSmallRow) s_rows[atomicAdd(&s_nbig, 1)] = int(r);
-    __syncthreads();
-    int nbig = s_nbig;
-    for (int t = 0; t < nbig; ++t) {
-      // (order inside s_rows is arbitrary; every row is handled independently, so the result is not)
-      int row = s_rows[t];
-      int a = ptr[row], d = ptr[row + 1] - a;
-      if (d <= kBigSmem) {
-        for (int i = threadIdx.x; i < d; i += blockDim.x) s_keys[i] = keys[a + i];
-        __syncthreads();
-        bitonic_sort(s_keys, d);
-        for (int i = threadIdx.x; i < d; i += blockDim.x) emit(ea, a + i, row, s_keys[i]);
-      } else {
-        __syncthreads();
-        bitonic_sort(keys + a, d);
-        for (int i = threadIdx.x; i < d; i += blockDim.x) emit(ea, a + i, row, keys[a + i]);
-      }
-      __syncthreads();
+      bitonic_sort(s_keys, d);
+      for (int i = threadIdx.x; i < d; i += blockDim.x) emit(ea, a + i, int(r0) + lo, s_keys[i]);
+    } else {
+      bitonic_sort(keys + a, d);
+      for (int i = threadIdx.x; i < d; i += blockDim.x) emit(ea, a + i, int(r0) + lo, keys[a + i]);
     }
     __syncthreads();
   }
@@ -357,10 +370,8 @@ extern "C" int lgk_csr_build(const int64_t* edge_index, int64_t E, int64_t N, in
   const int64_t* src = edge_index;
   const int64_t* dst = edge_index + E;
 
-  // counters: cnt_dst | cnt_src are adjacent-but-aligned; clear both (and the flags) with three memsets
-  cudaMemsetAsync(w.cnt_dst, 0, 4 * (N + 1), stream);
-  if (want_csc) cudaMemsetAsync(w.cnt_src, 0, 4 * (N + 1), stream);
-  cudaMemsetAsync(w.flags, 0, 16, stream);
+  // counters: cnt_dst | cnt_src | block sums are one contiguous region of the workspace: one memset
+  cudaMemsetAsync(w.cnt_dst, 0, size_t(reinterpret_cast<char*>(w.flags) + 16 - reinterpret_cast<char*>(w.cnt_dst)), stream);
 
   hist_kernel<<<grid_for(E, 256), 256, 0, stream>>>(src, dst, E, N, w.cnt_dst, want_csc ? w.cnt_src : nullptr);
   LGK_CHECK_LAUNCH("hist_kernel");
@@ -370,16 +381,19 @@ extern "C" int lgk_csr_build(const int64_t* edge_index, int64_t E, int64_t N, in
   sa.in[1] = w.cnt_src; sa.out[1] = colptr; sa.sums[1] = w.sums_b;
   int nblocks = int(ceil_div(N, kScanTile));
   dim3 sgrid(nblocks, want_csc ? 2 : 1);
-  scan_reduce_kernel<<<sgrid, kScanThreads, 0, stream>>>(sa, N);
-  LGK_CHECK_LAUNCH("scan_reduce_kernel");
-  scan_sums_kernel<<<dim3(1, want_csc ? 2 : 1), kScanThreads, 0, stream>>>(sa, nblocks);
-  LGK_CHECK_LAUNCH("scan_sums_kernel");
-  scan_apply_kernel<<<sgrid, kScanThreads, 0, stream>>>(sa, N);
-  LGK_CHECK_LAUNCH("scan_apply_kernel");
+  if (nblocks <= kSingleScanBlocks) {
+    scan_single_kernel<<<dim3(1, want_csc ? 2 : 1), kScanThreads, 0, stream>>>(sa, N);
+    LGK_CHECK_LAUNCH("scan_single_kernel");
+  } else {
+    scan_reduce_kernel<<<sgrid, kScanThreads, 0, stream>>>(sa, N);
+    LGK_CHECK_LAUNCH("scan_reduce_kernel");
+    scan_sums_kernel<<<dim3(1, want_csc ? 2 : 1), kScanThreads, 0, stream>>>(sa, nblocks);
+    LGK_CHECK_LAUNCH("scan_sums_kernel");
+    scan_apply_kernel<<<sgrid, kScanThreads, 0, stream>>>(sa, N);
+    LGK_CHECK_LAUNCH("scan_apply_kernel");
+  }
 
-  // cursors: reuse the count arrays (zeroed again)
-  cudaMemsetAsync(w.cnt_dst, 0, 4 * (N + 1), stream);
-  if (want_csc) cudaMemsetAsync(w.cnt_src, 0, 4 * (N + 1), stream);
+  // cursors: the count arrays again -- the scan zeroed every count it read
   fill_csr_kernel<<<grid_for(E, 256), 256, 0, stream>>>(src, dst, E, N, rowptr, w.cnt_dst, w.keys);
   LGK_CHECK_LAUNCH("fill_csr_kernel");
 
@@ -388,18 +402,13 @@ extern "C" int lgk_csr_build(const int64_t* edge_index, int64_t E, int64_t N, in
   uint64_t* keys2 = want_csc ? w.keys + E : nullptr;
   EmitArgs ea1{col, perm, colptr, w.cnt_src, keys2};
   int sgrid1 = int(ceil_div(N, kSortRows));
-  sort_small_kernel<<<sgrid1, kSortThreads, 0, stream>>>(rowptr, w.keys, N, ea1, w.flags + 0);
-  LGK_CHECK_LAUNCH("sort_small_kernel(csr)");
-  int big_grid = grid_for(N, 256, 4);
-  sort_big_kernel<<<big_grid, 256, 0, stream>>>(rowptr, w.keys, N, ea1, w.flags + 0);
-  LGK_CHECK_LAUNCH("sort_big_kernel(csr)");
+  sort_window_kernel<<<sgrid1, kSortThreads, 0, stream>>>(rowptr, w.keys, N, ea1);
+  LGK_CHECK_LAUNCH("sort_window_kernel(csr)");
 
   if (want_csc) {
     EmitArgs ea2{csr2csc, row, nullptr, nullptr, nullptr};
-    sort_small_kernel<<<sgrid1, kSortThreads, 0, stream>>>(colptr, keys2, N, ea2, w.flags + 1);
-    LGK_CHECK_LAUNCH("sort_small_kernel(csc)");
-    sort_big_kernel<<<big_grid, 256, 0, stream>>>(colptr, keys2, N, ea2, w.flags + 1);
-    LGK_CHECK_LAUNCH("sort_big_kernel(csc)");
+    sort_window_kernel<<<sgrid1, kSortThreads, 0, stream>>>(colptr, keys2, N, ea2);
+    LGK_CHECK_LAUNCH("sort_window_kernel(csc)");
   }
   return LGK_OK;
 }

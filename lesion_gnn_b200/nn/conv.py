@@ -76,8 +76,8 @@ class GCNConv(nn.Module):
         self.bias = nn.Parameter(torch.zeros(out_channels)) if bias else None
 
     def forward(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None) -> Tensor:
-        g = as_graph(edge_index, x.size(0), edge_weight)
-        h = self.lin(x)
+        h = self.lin(x)  # before as_graph: the transform does not read the graph, whose build may still be running on
+        g = as_graph(edge_index, x.size(0), edge_weight)  # its own stream (as_graph joins it)
         if not self.normalize:
             return F.aggregate(h, g, "sum", use_value=g.value is not None, bias=self.bias)
         # PyG 2.5.1's gcn_norm adds the remaining self loops BEFORE it defaults edge_weight to ones, so without
@@ -117,8 +117,8 @@ class GATConv(nn.Module):
     def forward(self, x: Tensor, edge_index, edge_attr=None, size=None, return_attention_weights=None) -> Tensor:
         if edge_attr is not None or return_attention_weights:
             raise NotImplementedError("edge_attr / return_attention_weights are not on the reference's path")
-        g = as_graph(edge_index, x.size(0))
-        h = self.lin(x)
+        h = self.lin(x)  # before as_graph: the transform does not read the graph, whose build may still be running on
+        g = as_graph(edge_index, x.size(0))  # its own stream (as_graph joins it)
         p = self.dropout if self.training else 0.0
         seed = _next_seed() if p > 0 else 0
         fused_bias = self.bias if self.concat else None
