@@ -19,7 +19,6 @@ namespace {
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;  // 2048
-constexpr int kSingleScanBlocks = 16;                  // up to 32 768 nodes: the whole scan in one CTA per array
 
 constexpr int kSortRows = 128;     // rows per CTA window
 constexpr int kSortThreads = 256;
@@ -128,33 +127,52 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(ScanArgs a, in
   if (base <= n - 1 && n - 1 < base + kScanItems) out[n] = ex;
 }
 
-// the whole scan in one CTA per array (a batch of lesion graphs has ~10^4 nodes: three dependent launches of a few
-// CTAs each cost more in launch latency than the scan itself)
-__global__ void __launch_bounds__(kScanThreads) scan_single_kernel(ScanArgs a, int64_t n) {
+// the whole scan in one CTA of 1024 threads per array (a batch of lesion graphs has ~10^4 nodes: three dependent
+// launches of a few CTAs each cost more in launch latency than the scan itself).  Thread t owns the contiguous
+// range [t * ipt, (t + 1) * ipt): one pass of independent loads, one block scan, one pass of stores.
+constexpr int kSingleThreads = 1024, kSingleItems = 32;
+__global__ void __launch_bounds__(kSingleThreads) scan_single_kernel(ScanArgs a, int64_t n) {
   __shared__ int s_warp[32];
   int* in = a.in[blockIdx.y];
   int* out = a.out[blockIdx.y];
-  int carry = 0;
-  for (int64_t tile = 0; tile < n; tile += kScanTile) {
-    const int64_t base = tile + int64_t(threadIdx.x) * kScanItems;
-    int v[kScanItems];
-    int sum = 0;
+  const int ipt = int((n + kSingleThreads - 1) / kSingleThreads);  // <= kSingleItems
+  const int64_t base = int64_t(threadIdx.x) * ipt;
+  int v[kSingleItems];
+  int sum = 0;
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-      v[i] = (base + i < n) ? in[base + i] : 0;
-      if (base + i < n) in[base + i] = 0;
-      sum += v[i];
-    }
-    int total;
-    int ex = block_exclusive_scan(sum, &total, s_warp) + carry;
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-      if (base + i < n) out[base + i] = ex;
-      ex += v[i];
-    }
-    if (base <= n - 1 && n - 1 < base + kScanItems) out[n] = ex;
-    carry += total;
+  for (int i = 0; i < kSingleItems; ++i) {
+    v[i] = (i < ipt && base + i < n) ? in[base + i] : 0;
+    sum += v[i];
   }
+#pragma unroll
+  for (int i = 0; i < kSingleItems; ++i)
+    if (i < ipt && base + i < n) in[base + i] = 0;  // the counts become the cursors of the bucket fill
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += t;
+    }
+    s_warp[lane] = w;  // inclusive warp totals
+  }
+  __syncthreads();
+  int ex = (warp ? s_warp[warp - 1] : 0) + inc - sum;
+#pragma unroll
+  for (int i = 0; i < kSingleItems; ++i) {
+    if (i < ipt && base + i < n) out[base + i] = ex;
+    ex += v[i];
+  }
+  if (threadIdx.x == kSingleThreads - 1) out[n] = ex;  // grand total (threads past the end hold zeros)
 }
 
 // ---- bucket fill: CSR keys ------------------------------------------------------------------------
@@ -381,8 +399,8 @@ extern "C" int lgk_csr_build(const int64_t* edge_index, int64_t E, int64_t N, in
   sa.in[1] = w.cnt_src; sa.out[1] = colptr; sa.sums[1] = w.sums_b;
   int nblocks = int(ceil_div(N, kScanTile));
   dim3 sgrid(nblocks, want_csc ? 2 : 1);
-  if (nblocks <= kSingleScanBlocks) {
-    scan_single_kernel<<<dim3(1, want_csc ? 2 : 1), kScanThreads, 0, stream>>>(sa, N);
+  if (N <= int64_t(kSingleThreads) * kSingleItems) {
+    scan_single_kernel<<<dim3(1, want_csc ? 2 : 1), kSingleThreads, 0, stream>>>(sa, N);
     LGK_CHECK_LAUNCH("scan_single_kernel");
   } else {
     scan_reduce_kernel<<<sgrid, kScanThreads, 0, stream>>>(sa, N);
