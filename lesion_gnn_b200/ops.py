@@ -372,3 +372,15 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
     L.call("lgk_adam_step", _chk(param, f32, "param"), _chk(grad, f32, "grad"), _chk(exp_avg, f32), _chk(exp_avg_sq, f32),
            param.numel(), float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
            _chk(step_dev, torch.int64, "step_dev"), float(grad_scale), int(adamw), _stream())
+
+
+def clamped_regression_loss(logits: Tensor, y: Tensor, lo: float, hi: float, kind: int, want_grad: bool = True):
+    """-> (loss [] f32, d loss / d logits [n] f32 | None): MSE (kind 0) / SmoothL1 (kind 1) of clamp(logits, lo, hi)
+    against int64 labels, forward and gradient in one launch (reference models/base.py:196-199, gat.py:94-95)"""
+    L = _lib.lib()
+    n = logits.numel()
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    dl = torch.empty(n, dtype=torch.float32, device=logits.device) if want_grad else None
+    L.call("lgk_clamped_regression_loss", _chk(logits, torch.float32, "logits"), _chk(y, torch.int64, "y"), n,
+           float(lo), float(hi), int(kind), loss.data_ptr(), _chk(dl, torch.float32, "dlogits"), _stream())
+    return loss, dl

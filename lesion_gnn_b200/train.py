@@ -92,8 +92,28 @@ class FlatAdam(FlatParams):
                       adamw=self.adamw)
 
 
+class _ClampedRegressionLoss(torch.autograd.Function):
+    """loss and its gradient from one launch (ops.clamped_regression_loss) instead of a dozen elementwise torch kernels"""
+
+    @staticmethod
+    def forward(ctx, logits, y, hi, kind):
+        loss, dl = ops.clamped_regression_loss(logits.reshape(-1), y, 0.0, hi, kind, want_grad=ctx.needs_input_grad[0])
+        ctx.save_for_backward(dl)
+        ctx.shape = logits.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return (dl * g).view(ctx.shape), None, None, None
+
+
 def loss_fn(logits: Tensor, y: Tensor, loss_type: str = "MSE", num_classes: int = 5) -> Tensor:
     """reference models/base.py:88-96,196-199 and the regression clamp of models/gat.py:94-95"""
+    if loss_type in ("MSE", "SmoothL1") and logits.is_cuda and logits.dtype == torch.float32 and y.dtype == torch.int64 \
+            and logits.dim() == 2 and logits.size(1) == 1:
+        return _ClampedRegressionLoss.apply(logits.contiguous(), y.contiguous(), float(num_classes - 1),
+                                            0 if loss_type == "MSE" else 1)
     if loss_type == "MSE":
         return TF.mse_loss(torch.clamp(logits.squeeze(1), min=0, max=num_classes - 1), y.float())
     if loss_type == "SmoothL1":

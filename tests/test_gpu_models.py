@@ -90,6 +90,33 @@ def test_csrgraph_input_equals_edge_index_input(dev):
     assert torch.equal(a, c)
 
 
+@pytest.mark.parametrize("loss_type", ["MSE", "SmoothL1"])
+def test_clamped_regression_loss_matches_torch(dev, loss_type):
+    """loss + gradient in one launch (lgk_clamped_regression_loss) vs the reference's criterion on clamped logits
+    (models/base.py:196-199, gat.py:94-95): values below, inside, above and exactly on the clamp bounds"""
+    from lesion_gnn_b200 import train
+    torch.manual_seed(3)
+    n = 777
+    x = (torch.randn(n, 1, dtype=torch.float64) * 3 + 2)
+    x[:6, 0] = torch.tensor([0.0, 4.0, -0.0, 4.0000001, -1e-7, 2.5])
+    y = torch.randint(0, 5, (n,))
+    xr = x.clone().requires_grad_(True)
+    c = torch.clamp(xr.squeeze(1), 0, 4)
+    want = (torch.nn.functional.mse_loss if loss_type == "MSE" else torch.nn.functional.smooth_l1_loss)(c, y.double())
+    (want * 0.7).backward()
+    xg = x.float().to(dev).requires_grad_(True)
+    got = train.loss_fn(xg, y.to(dev), loss_type, 5)
+    (got * 0.7).backward()
+    assert_close(got, want, TOL_F32, "loss")
+    # the clamp mask is decided on the fp32 logits: compare against the fp64 reference evaluated at those values
+    xr2 = x.float().double().requires_grad_(True)
+    c2 = torch.clamp(xr2.squeeze(1), 0, 4)
+    w2 = (torch.nn.functional.mse_loss if loss_type == "MSE" else torch.nn.functional.smooth_l1_loss)(c2, y.double())
+    (w2 * 0.7).backward()
+    assert_close(xg.grad, xr2.grad, TOL_F32, "dlogits")
+    assert torch.equal(train.loss_fn(xg, y.to(dev), loss_type, 5), got.detach())   # deterministic
+
+
 def test_adam_matches_torch(dev):
     from lesion_gnn_b200 import ops
     torch.manual_seed(0)
