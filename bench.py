@@ -514,8 +514,19 @@ def run_reference(args):
     }), flush=True)
 
 
+def _keep_stdout_for_the_json_line():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the
+    first collective when NCCL_DEBUG is set on the box), so file descriptor 1 is pointed at stderr for the whole run
+    and `print` gets a private duplicate of the real stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 if __name__ == "__main__":
     a = parse_args()
+    _keep_stdout_for_the_json_line()
     if a.impl == "reference":
         run_reference(a)
     else:
