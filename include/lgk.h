@@ -247,10 +247,11 @@ LGK_API int lgk_adam_step(float* param, const float* grad, float* exp_avg, float
 /* Clamped regression loss of the reference's training step, forward and gradient in one launch
  * (models/base.py:196-199 `criterion(logits, y)` with the regression clamp of models/gat.py:94-95:
  * loss = mean_i L(clamp(logits[i], lo, hi) - y[i]), L = d^2 (kind 0, nn.MSELoss) or SmoothL1 with beta 1 (kind 1)).
- * loss_out[0] receives the loss, dlogits (may be NULL) d loss / d logits[i] (zero outside [lo, hi], as
- * torch.clamp's backward).  Labels are int64 as the DataLoader delivers them.  One CTA: n is a batch of graphs.  */
+ * loss_out[0] receives the loss, dlogits (may be NULL) grad_scale * d loss / d logits[i] (zero outside [lo, hi], as
+ * torch.clamp's backward; grad_scale = the weight of this rank's loss under data parallelism, 1 otherwise).
+ * Labels are int64 as the DataLoader delivers them.  One CTA: n is a batch of graphs.  */
 LGK_API int lgk_clamped_regression_loss(const float* logits, const int64_t* y, int64_t n, float lo, float hi, int kind,
-                                float* loss_out, float* dlogits, void* stream);
+                                float grad_scale, float* loss_out, float* dlogits, void* stream);
 
 #ifdef __cplusplus
 }

@@ -136,7 +136,7 @@ extern "C" int lgk_adam_step(float* param, const float* grad, float* exp_avg, fl
 namespace lgk {
 namespace {
 __global__ void __launch_bounds__(1024) clamped_loss_kernel(const float* __restrict__ logits, const int64_t* __restrict__ y,
-                                                            int64_t n, float lo, float hi, int kind,
+                                                            int64_t n, float lo, float hi, int kind, float grad_scale,
                                                             float* __restrict__ loss_out, float* __restrict__ dlogits) {
   __shared__ float red[1024];
   const float inv_n = 1.f / float(n);
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(1024) clamped_loss_kernel(const float* __restr
     else if (fabsf(d) < 1.f) { l = 0.5f * d * d; g = d; }
     else { l = fabsf(d) - 0.5f; g = d > 0.f ? 1.f : -1.f; }
     s += l;
-    if (dlogits) dlogits[i] = (x >= lo && x <= hi) ? g * inv_n : 0.f;
+    if (dlogits) dlogits[i] = (x >= lo && x <= hi) ? g * inv_n * grad_scale : 0.f;
   }
   red[threadIdx.x] = s;
   __syncthreads();
@@ -164,12 +164,12 @@ __global__ void __launch_bounds__(1024) clamped_loss_kernel(const float* __restr
 }  // namespace lgk
 
 extern "C" int lgk_clamped_regression_loss(const float* logits, const int64_t* y, int64_t n, float lo, float hi, int kind,
-                                           float* loss_out, float* dlogits, void* stream_) {
+                                           float grad_scale, float* loss_out, float* dlogits, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n > 0, LGK_ERR_BAD_ARG, "lgk_clamped_regression_loss: empty batch");
   LGK_REQUIRE(logits && y && loss_out, LGK_ERR_BAD_ARG, "lgk_clamped_regression_loss: null pointer");
   LGK_REQUIRE(kind == 0 || kind == 1, LGK_ERR_BAD_ARG, "lgk_clamped_regression_loss: kind must be 0 (MSE) or 1 (SmoothL1)");
-  lgk::clamped_loss_kernel<<<1, 1024, 0, stream>>>(logits, y, n, lo, hi, kind, loss_out, dlogits);
+  lgk::clamped_loss_kernel<<<1, 1024, 0, stream>>>(logits, y, n, lo, hi, kind, grad_scale, loss_out, dlogits);
   LGK_CHECK_LAUNCH("clamped_loss_kernel");
   return LGK_OK;
 }

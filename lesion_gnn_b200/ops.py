@@ -374,13 +374,14 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
            _chk(step_dev, torch.int64, "step_dev"), float(grad_scale), int(adamw), _stream())
 
 
-def clamped_regression_loss(logits: Tensor, y: Tensor, lo: float, hi: float, kind: int, want_grad: bool = True):
-    """-> (loss [] f32, d loss / d logits [n] f32 | None): MSE (kind 0) / SmoothL1 (kind 1) of clamp(logits, lo, hi)
+def clamped_regression_loss(logits: Tensor, y: Tensor, lo: float, hi: float, kind: int, want_grad: bool = True,
+                            grad_scale: float = 1.0):
+    """-> (loss [] f32, grad_scale * d loss / d logits [n] f32 | None): MSE (kind 0) / SmoothL1 (kind 1) of clamp(logits, lo, hi)
     against int64 labels, forward and gradient in one launch (reference models/base.py:196-199, gat.py:94-95)"""
     L = _lib.lib()
     n = logits.numel()
     loss = torch.empty((), dtype=torch.float32, device=logits.device)
     dl = torch.empty(n, dtype=torch.float32, device=logits.device) if want_grad else None
     L.call("lgk_clamped_regression_loss", _chk(logits, torch.float32, "logits"), _chk(y, torch.int64, "y"), n,
-           float(lo), float(hi), int(kind), loss.data_ptr(), _chk(dl, torch.float32, "dlogits"), _stream())
+           float(lo), float(hi), int(kind), float(grad_scale), loss.data_ptr(), _chk(dl, torch.float32, "dlogits"), _stream())
     return loss, dl
