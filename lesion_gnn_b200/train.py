@@ -10,6 +10,7 @@ the three things that make it fast on one B200 and scale over eight:
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, Optional
 
 import torch
@@ -170,7 +171,9 @@ class TrainStep:
         self.use_cuda_graph = use_cuda_graph
         self.pg, self.world_size = process_group, world_size
         self._graphs = {}
-        self._side = [torch.cuda.Stream() for _ in range(3)] if torch.cuda.is_available() else None
+        # parameter-gradient kernels are dealt over this many side streams (tuning knob: LGK_SIDE_STREAMS, 0 = none)
+        nside = int(os.environ.get("LGK_SIDE_STREAMS", "2"))
+        self._side = [torch.cuda.Stream() for _ in range(nside)] if torch.cuda.is_available() and nside > 0 else None
         self._build = torch.cuda.Stream() if torch.cuda.is_available() else None
 
     def _body(self, db: DeviceBatch) -> Tensor:
