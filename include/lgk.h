@@ -166,6 +166,13 @@ LGK_API int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void* h
                 int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
                 float dropout_p, uint64_t seed, int dtype, void* stream);
 
+/* lgk_gat_fwd with the activation that follows every GAT layer of the reference (models/gat.py:51 `F.elu(conv(x))`)
+ * written by the same launch: out as above (the backward needs it), out_elu = elu(out).                        */
+LGK_API int lgk_gat_fwd_elu(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
+                    const float* bias, void* out, void* out_elu, float* rowmax, float* rowsum,
+                    int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
+                    float dropout_p, uint64_t seed, int dtype, void* stream);
+
 /* backward, dst side (CSR): da_dst[i,h] = sum_j dz_ij, and the packed per-(node, head) statistics
  * stats[i,h] = {a_dst, rowmax, 1/(rowsum + 1e-16), delta} with delta = <dout[i,h,:], out[i,h,:] - bias>
  * (float [N,H,4], 16-byte aligned) from which the src-side pass recomputes every alpha_ij and dz_ij.        */

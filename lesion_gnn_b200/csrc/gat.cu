@@ -30,6 +30,7 @@ struct GatArgs {
   float* da_out;       // da_dst (dst pass) or da_src (src pass)
   const float* att_src;
   const float* att_dst;
+  void* act_out;       // forward only: second output elu(out), same type and shape as out (null: not wanted)
   int64_t n_nodes;
   int heads;
   int chan;
@@ -175,6 +176,10 @@ __global__ void __launch_bounds__(kThreads) gat_fwd_kernel(GatArgs a, const T* _
         r.x += b.x; r.y += b.y; r.z += b.z; r.w += b.w;
       }
       Vec4<T>::store(out + int64_t(i) * F + head * C, vec * 4, r);
+      if (a.act_out) {  // the ELU that follows every GAT layer of the reference (models/gat.py:51), same launch
+        r.x = elu1(r.x); r.y = elu1(r.y); r.z = elu1(r.z); r.w = elu1(r.w);
+        Vec4<T>::store(static_cast<T*>(a.act_out) + int64_t(i) * F + head * C, vec * 4, r);
+      }
     }
   }
   if (gl == 0) {
@@ -435,10 +440,10 @@ extern "C" int lgk_gat_alpha(const void* h, const float* att_src, const float* a
   return LGK_OK;
 }
 
-extern "C" int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
+static int gat_fwd_impl(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
                            const float* bias, void* out, float* rowmax, float* rowsum, int64_t N, int H, int C,
-                           float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
-                           void* stream_) {
+                        float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                        void* stream_, void* out_elu) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_shape("lgk_gat_fwd", N, H, C)) return rc;
   if (N == 0) return LGK_OK;
@@ -446,6 +451,7 @@ extern "C" int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void
   LGK_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_gat_fwd: dropout must be in [0,1)");
   GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
   a.ptr = rowptr; a.idx = col; a.a_src = a_src; a.a_dst = a_dst; a.bias = bias; a.rowmax = rowmax; a.rowsum = rowsum;
+  a.act_out = out_elu;
   const int64_t items = N * H;
   if (dtype == LGK_F32)
     LGK_GAT_DISPATCH(gat_fwd_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<float*>(out));
@@ -455,6 +461,23 @@ extern "C" int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void
     LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_fwd: bad dtype");
   LGK_CHECK_LAUNCH("gat_fwd_kernel");
   return LGK_OK;
+}
+
+extern "C" int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
+                           const float* bias, void* out, float* rowmax, float* rowsum, int64_t N, int H, int C,
+                           float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                           void* stream_) {
+  return gat_fwd_impl(rowptr, col, h, a_src, a_dst, bias, out, rowmax, rowsum, N, H, C, negative_slope, add_self_loops,
+                      dropout_p, seed, dtype, stream_, nullptr);
+}
+
+extern "C" int lgk_gat_fwd_elu(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
+                               const float* a_dst, const float* bias, void* out, void* out_elu, float* rowmax,
+                               float* rowsum, int64_t N, int H, int C, float negative_slope, int add_self_loops,
+                               float dropout_p, uint64_t seed, int dtype, void* stream_) {
+  LGK_REQUIRE(out_elu || N == 0, LGK_ERR_BAD_ARG, "lgk_gat_fwd_elu: null pointer");
+  return gat_fwd_impl(rowptr, col, h, a_src, a_dst, bias, out, rowmax, rowsum, N, H, C, negative_slope, add_self_loops,
+                      dropout_p, seed, dtype, stream_, out_elu);
 }
 
 extern "C" int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,

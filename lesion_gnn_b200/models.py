@@ -11,6 +11,8 @@ from __future__ import annotations
 import math
 from itertools import pairwise
 
+import os
+
 import torch
 import torch.nn as nn
 from torch import Tensor
@@ -19,6 +21,8 @@ from ._lib import ACT_ELU
 from .nn import (GATConv, GCNConv, GINConv, GraphConv, MLP, SAGEConv, SortAggregation, Linear, elu, global_max_pool,
                  global_mean_max_pool, global_mean_pool, linear)
 
+
+_FUSED_ELU = os.environ.get("LGK_FUSED_ELU", "1") != "0"  # profiling knob: 0 = separate lgk_elu_fwd launch after every GAT layer
 
 class _TorchInitLinear(Linear):
     """torch.nn.Linear's initialisation (the reference's in_proj / out_proj are torch.nn.Linear)."""
@@ -51,15 +55,15 @@ class GAT(nn.Module):
         assert all(d % heads == 0 for d in hiddden_channels)
         self.in_proj = _TorchInitLinear(input_features, hiddden_channels[0])
         self.convs = nn.ModuleList(
-            [GATConv(d1, d2 // heads, heads=heads, dropout=dropout) for d1, d2 in pairwise(hiddden_channels)]
-        )
+            [GATConv(d1, d2 // heads, heads=heads, dropout=dropout, fused_elu=_FUSED_ELU) for d1, d2 in pairwise(hiddden_channels)]
+        )  # fused_elu: the F.elu of gat.py:51 is written by the attention kernel (one launch less per layer)
         self.st = None
         self.out_proj = _TorchInitLinear(hiddden_channels[-1], num_classes)
 
     def forward(self, x: Tensor, edge_index, batch) -> Tensor:
         x = self.in_proj(x)
         for conv in self.convs:
-            x = elu(conv(x, edge_index))
+            x = conv(x, edge_index) if conv.fused_elu else elu(conv(x, edge_index))  # F.elu(GATConv(x)) of the reference
         x = global_mean_pool(x, batch)
         return self.out_proj(x)
 

@@ -95,8 +95,13 @@ class GATConv(nn.Module):
 
     def __init__(self, in_channels: int, out_channels: int, heads: int = 1, concat: bool = True,
                  negative_slope: float = 0.2, dropout: float = 0.0, add_self_loops: bool = True,
-                 edge_dim: Optional[int] = None, fill_value="mean", bias: bool = True):
+                 edge_dim: Optional[int] = None, fill_value="mean", bias: bool = True, fused_elu: bool = False):
+        """fused_elu (not a PyG argument): the layer returns elu(output) -- the `F.elu(conv(x))` of the reference's
+        models/gat.py:51 written by the attention kernel itself; concat=True only."""
         super().__init__()
+        if fused_elu and not concat:
+            raise ValueError("fused_elu needs concat=True (the head mean comes before the activation otherwise)")
+        self.fused_elu = fused_elu
         if edge_dim is not None:
             raise NotImplementedError("edge features (edge_dim) are not on the reference's path")
         if not isinstance(in_channels, int):
@@ -123,7 +128,7 @@ class GATConv(nn.Module):
         seed = _next_seed() if p > 0 else 0
         fused_bias = self.bias if self.concat else None
         out = F.gat_attention(h, self.att_src, self.att_dst, fused_bias, g, self.heads, self.out_channels,
-                              self.negative_slope, self.add_self_loops, p, seed)
+                              self.negative_slope, self.add_self_loops, p, seed, fused_elu=self.fused_elu)
         if not self.concat:
             out = out.view(-1, self.heads, self.out_channels).mean(dim=1)
             if self.bias is not None:

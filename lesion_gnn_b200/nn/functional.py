@@ -172,27 +172,33 @@ class _GatAttention(torch.autograd.Function):
     """h [N, H*C] -> edge-softmax attention output [N, H*C] (+ bias)."""
 
     @staticmethod
-    def forward(ctx, h, att_src, att_dst, bias, g: CSRGraph, heads, chan, negative_slope, add_self_loops, dropout_p, seed):
+    def forward(ctx, h, att_src, att_dst, bias, g: CSRGraph, heads, chan, negative_slope, add_self_loops, dropout_p, seed,
+                fused_elu=False):
         h = h.contiguous()
         a_s = att_src.detach().reshape(-1).contiguous()
         a_d = att_dst.detach().reshape(-1).contiguous()
         a_src, a_dst = ops.gat_alpha(h, a_s, a_d, heads, chan)
-        out, rowmax, rowsum = ops.gat_fwd(g.rowptr, g.col, h, a_src, a_dst, bias, heads, chan, negative_slope,
-                                          add_self_loops, dropout_p, seed)
-        ctx.save_for_backward(h, a_src, a_dst, rowmax, rowsum, out, a_s, a_d, bias if bias is not None else h.new_empty(0))
+        res = ops.gat_fwd(g.rowptr, g.col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p,
+                          seed, with_elu=fused_elu)
+        out, rowmax, rowsum = res[:3]
+        y = res[3] if fused_elu else h.new_empty(0)
+        ctx.fused_elu = fused_elu
+        ctx.save_for_backward(h, a_src, a_dst, rowmax, rowsum, out, a_s, a_d, bias if bias is not None else h.new_empty(0), y)
         ctx.g, ctx.cfg = g, (heads, chan, negative_slope, add_self_loops, dropout_p, seed)
         ctx.has_bias = bias is not None
         ctx.att_shape = att_src.shape
         ctx.refs = (att_src, att_dst, bias)
-        return out
+        return y if fused_elu else out
 
     @staticmethod
     def backward(ctx, dout):
-        h, a_src, a_dst, rowmax, rowsum, out, a_s, a_d, bias = ctx.saved_tensors
+        h, a_src, a_dst, rowmax, rowsum, out, a_s, a_d, bias, y = ctx.saved_tensors
         heads, chan, slope, add_self, p, seed = ctx.cfg
         g = ctx.g
         _need_csc(g)
         dout = dout.contiguous()
+        if ctx.fused_elu:
+            dout = ops.elu_bwd(y, dout)  # gradient w.r.t. the pre-activation output, as autograd's elu node would give
         p_src, p_dst, p_bias = ctx.refs
         dh, da_src, da_dst = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
                                          a_s, a_d, dout, heads, chan, slope, add_self, p, seed)
@@ -211,13 +217,14 @@ class _GatAttention(torch.autograd.Function):
                 _on_side(lambda: ops.colsum(d32, out=gb), d32, key=gb.data_ptr())
             else:
                 dbias = ops.colsum(d32)
-        return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None)
+        return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None, None)
 
 
 def gat_attention(h, att_src, att_dst, bias, g, heads, chan, negative_slope=0.2, add_self_loops=True, dropout_p=0.0,
-                  seed=0) -> Tensor:
+                  seed=0, fused_elu=False) -> Tensor:
+    """fused_elu: return elu(attention output + bias) from the same launch (the bias must be the fused one)"""
     return _GatAttention.apply(h, att_src, att_dst, bias, g, int(heads), int(chan), float(negative_slope),
-                               bool(add_self_loops), float(dropout_p), int(seed))
+                               bool(add_self_loops), float(dropout_p), int(seed), bool(fused_elu))
 
 
 class _Linear(torch.autograd.Function):

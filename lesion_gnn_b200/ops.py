@@ -196,12 +196,20 @@ def gat_alpha(h: Tensor, att_src: Tensor, att_dst: Tensor, heads: int, chan: int
     return a_src, a_dst
 
 
-def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p=0.0, seed=0):
+def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p=0.0, seed=0,
+            with_elu=False):
+    """-> out, rowmax, rowsum [, elu(out)]"""
     L = _lib.lib()
     n = h.size(0)
     out = torch.empty_like(h)
     rowmax = torch.empty(n, heads, dtype=torch.float32, device=h.device)
     rowsum = torch.empty_like(rowmax)
+    if with_elu:
+        y = torch.empty_like(h)
+        L.call("lgk_gat_fwd_elu", _chk(rowptr, torch.int32), _chk(col, torch.int32), _chk(h, None, "h"), _chk(a_src, torch.float32),
+               _chk(a_dst, torch.float32), _chk(bias, torch.float32, "bias"), _chk(out), _chk(y), _chk(rowmax), _chk(rowsum), n,
+               heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), _dt(h), _stream())
+        return out, rowmax, rowsum, y
     L.call("lgk_gat_fwd", _chk(rowptr, torch.int32), _chk(col, torch.int32), _chk(h, None, "h"), _chk(a_src, torch.float32),
            _chk(a_dst, torch.float32), _chk(bias, torch.float32, "bias"), _chk(out), _chk(rowmax), _chk(rowsum), n, heads, chan,
            float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), _dt(h), _stream())

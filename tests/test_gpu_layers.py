@@ -340,3 +340,27 @@ def test_wide_weight_gradient_on_tensor_cores(dev, n, k, m):
     assert_close(acc_w, base_w.double().cpu() + want_w, TOL_F32, "dW accumulate")
     assert_close(acc_b, base_b.double().cpu() + want_b, TOL_F32, "db accumulate")
     assert torch.equal(ops.linear_bwd_w(dyg, xg)[0], dw)   # deterministic
+
+
+def test_gat_fused_elu_equals_separate_activation(dev):
+    """GATConv(fused_elu=True) (the attention kernel writes elu(out) itself) against elu(GATConv(x)): bit-identical
+    output, gradients within the fp32 bar"""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200.nn import functional as F
+    from tests.util import knn_batch
+    hb = knn_batch(12, "ddr", 32, 6, seed=9)
+    torch.manual_seed(4)
+    a = lg.nn.GATConv(32, 16, heads=4).to(dev)
+    b = lg.nn.GATConv(32, 16, heads=4, fused_elu=True).to(dev)
+    b.load_state_dict(a.state_dict())
+    ei = hb.edge_index.to(dev)
+    xa = hb.x.to(dev).requires_grad_(True)
+    xb = hb.x.to(dev).requires_grad_(True)
+    ya, yb = F.elu(a(xa, ei)), b(xb, ei)
+    assert torch.equal(ya, yb)
+    dy = torch.randn_like(ya)
+    ya.backward(dy)
+    yb.backward(dy)
+    assert_close(xb.grad, xa.grad, TOL_F32, "dx")
+    for (k, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+        assert_close(pb.grad, pa.grad, TOL_F32, "d" + k)
