@@ -181,6 +181,14 @@ LGK_API int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const voi
                     float* stats, float* da_dst,
                     int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
                     float dropout_p, uint64_t seed, int dtype, void* stream);
+/* lgk_gat_bwd_dst for a layer run with lgk_gat_fwd_elu: dy is the gradient of elu(out); the kernel forms
+ * dout = dy * elu'(out) on the fly, uses it as above and writes it to `dout` (same type and shape as out) for
+ * lgk_gat_bwd_src and the bias gradient -- no separate lgk_elu_bwd launch.                                    */
+LGK_API int lgk_gat_bwd_dst_elu(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
+                        const float* rowmax, const float* rowsum, const void* out, const float* bias, const void* dy,
+                        void* dout, float* stats, float* da_dst,
+                        int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
+                        float dropout_p, uint64_t seed, int dtype, void* stream);
 /* backward, src side (CSC): dh[j,h,:] = sum_i alpha_ij dout[i,h,:] + da_src[j,h] att_src[h,:] + da_dst[j,h] att_dst[h,:],
  * da_src[j,h] = sum_i dz_ij                                                                             */
 LGK_API int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const void* h,

@@ -215,6 +215,14 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_dst_kernel(GatArgs a, const 
     if (vec < C4) {
       dO[v] = Vec4<T>::stream(dout + int64_t(i) * F + head * C, vec * 4);
       float4 o = Vec4<T>::stream(out + int64_t(i) * F + head * C, vec * 4);
+      if (a.act_out) {  // `dout` is the gradient of elu(out): turn it into the gradient of out (elu' = y > 0 ? 1 : y + 1
+                        // with y = elu(out), as lgk_elu_bwd computes it) and keep it for the src-side pass and db
+        dO[v].x *= o.x > 0.f ? 1.f : elu1(o.x) + 1.f;
+        dO[v].y *= o.y > 0.f ? 1.f : elu1(o.y) + 1.f;
+        dO[v].z *= o.z > 0.f ? 1.f : elu1(o.z) + 1.f;
+        dO[v].w *= o.w > 0.f ? 1.f : elu1(o.w) + 1.f;
+        Vec4<T>::store(static_cast<T*>(a.act_out) + int64_t(i) * F + head * C, vec * 4, dO[v]);
+      }
       if (a.bias) {
         float4 b = __ldg(reinterpret_cast<const float4*>(a.bias + head * C) + vec);
         o.x -= b.x; o.y -= b.y; o.z -= b.z; o.w -= b.w;
@@ -480,11 +488,11 @@ extern "C" int lgk_gat_fwd_elu(const int32_t* rowptr, const int32_t* col, const 
                       dropout_p, seed, dtype, stream_, out_elu);
 }
 
-extern "C" int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
+static int gat_bwd_dst_impl(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
                                const float* a_dst, const float* rowmax, const float* rowsum, const void* out,
                                const float* bias, const void* dout, float* delta, float* da_dst, int64_t N, int H, int C,
                                float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
-                               void* stream_) {
+                               void* stream_, void* dpre_out) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_shape("lgk_gat_bwd_dst", N, H, C)) return rc;
   if (N == 0) return LGK_OK;
@@ -493,7 +501,7 @@ extern "C" int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const 
   GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
   a.ptr = rowptr; a.idx = col; a.a_src = a_src; a.a_dst = a_dst; a.bias = bias;
   a.rowmax = const_cast<float*>(rowmax); a.rowsum = const_cast<float*>(rowsum);
-  a.stats = reinterpret_cast<float4*>(delta); a.da_out = da_dst;
+  a.stats = reinterpret_cast<float4*>(delta); a.da_out = da_dst; a.act_out = dpre_out;
   const int64_t items = N * H;
   if (dtype == LGK_F32)
     LGK_GAT_DISPATCH(gat_bwd_dst_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<const float*>(out), static_cast<const float*>(dout));
@@ -503,6 +511,25 @@ extern "C" int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const 
     LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_bwd_dst: bad dtype");
   LGK_CHECK_LAUNCH("gat_bwd_dst_kernel");
   return LGK_OK;
+}
+
+extern "C" int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
+                               const float* a_dst, const float* rowmax, const float* rowsum, const void* out,
+                               const float* bias, const void* dout, float* delta, float* da_dst, int64_t N, int H, int C,
+                               float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                               void* stream_) {
+  return gat_bwd_dst_impl(rowptr, col, h, a_src, a_dst, rowmax, rowsum, out, bias, dout, delta, da_dst, N, H, C,
+                          negative_slope, add_self_loops, dropout_p, seed, dtype, stream_, nullptr);
+}
+
+extern "C" int lgk_gat_bwd_dst_elu(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
+                                   const float* a_dst, const float* rowmax, const float* rowsum, const void* out,
+                                   const float* bias, const void* dy, void* dout, float* delta, float* da_dst, int64_t N,
+                                   int H, int C, float negative_slope, int add_self_loops, float dropout_p, uint64_t seed,
+                                   int dtype, void* stream_) {
+  LGK_REQUIRE(dout || N == 0, LGK_ERR_BAD_ARG, "lgk_gat_bwd_dst_elu: null pointer");
+  return gat_bwd_dst_impl(rowptr, col, h, a_src, a_dst, rowmax, rowsum, out, bias, dy, delta, da_dst, N, H, C,
+                          negative_slope, add_self_loops, dropout_p, seed, dtype, stream_, dout);
 }
 
 extern "C" int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const void* h,

@@ -197,11 +197,12 @@ class _GatAttention(torch.autograd.Function):
         g = ctx.g
         _need_csc(g)
         dout = dout.contiguous()
-        if ctx.fused_elu:
-            dout = ops.elu_bwd(y, dout)  # gradient w.r.t. the pre-activation output, as autograd's elu node would give
         p_src, p_dst, p_bias = ctx.refs
-        dh, da_src, da_dst = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
-                                         a_s, a_d, dout, heads, chan, slope, add_self, p, seed)
+        res = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
+                          a_s, a_d, dout, heads, chan, slope, add_self, p, seed, through_elu=ctx.fused_elu)
+        dh, da_src, da_dst = res[:3]
+        if ctx.fused_elu:
+            dout = res[3]  # gradient w.r.t. the pre-activation output (formed by the dst-side kernel), for db below
         g_src, g_dst = _bucket(p_src), _bucket(p_dst)
         if g_src is not None and g_dst is not None:
             _on_side(lambda: ops.gat_datt(h, da_src, da_dst, heads, chan, g_src.view(-1), g_dst.view(-1)), h, da_src, da_dst, key=g_src.data_ptr())

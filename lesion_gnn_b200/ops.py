@@ -217,8 +217,10 @@ def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add
 
 
 def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst, dout, heads, chan, negative_slope,
-            add_self_loops, dropout_p=0.0, seed=0):
-    """-> dh, da_src [N,H], da_dst [N,H] (the attention-vector gradients follow from gat_datt)"""
+            add_self_loops, dropout_p=0.0, seed=0, through_elu=False):
+    """-> dh, da_src [N,H], da_dst [N,H] (the attention-vector gradients follow from gat_datt).
+    through_elu: `dout` is the gradient of elu(out) (layer run with gat_fwd(with_elu=True)); the gradient of out is
+    formed by the dst-side kernel and returned as a fourth value"""
     L = _lib.lib()
     n, dev = h.size(0), h.device
     f32 = dict(dtype=torch.float32, device=dev)
@@ -227,14 +229,20 @@ def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst,
     da_src = torch.empty(n, heads, **f32)
     dh = torch.empty_like(h)
     dt, st = _dt(h), _stream()
-    L.call("lgk_gat_bwd_dst", _chk(graph.rowptr), _chk(graph.col), _chk(h), _chk(a_src), _chk(a_dst), _chk(rowmax),
-           _chk(rowsum), _chk(out, None, "out"), _chk(bias, torch.float32), _chk(dout, h.dtype, "dout"), _chk(stats), _chk(da_dst),
-           n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), dt, st)
+    if through_elu:
+        dy, dout = dout, torch.empty_like(h)
+        L.call("lgk_gat_bwd_dst_elu", _chk(graph.rowptr), _chk(graph.col), _chk(h), _chk(a_src), _chk(a_dst), _chk(rowmax),
+               _chk(rowsum), _chk(out, None, "out"), _chk(bias, torch.float32), _chk(dy, h.dtype, "dy"), _chk(dout), _chk(stats),
+               _chk(da_dst), n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), dt, st)
+    else:
+        L.call("lgk_gat_bwd_dst", _chk(graph.rowptr), _chk(graph.col), _chk(h), _chk(a_src), _chk(a_dst), _chk(rowmax),
+               _chk(rowsum), _chk(out, None, "out"), _chk(bias, torch.float32), _chk(dout, h.dtype, "dout"), _chk(stats),
+               _chk(da_dst), n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), dt, st)
     L.call("lgk_gat_bwd_src", _chk(graph.colptr), _chk(graph.row), _chk(graph.csr2csc), _chk(h), _chk(a_src), _chk(a_dst),
            _chk(rowmax), _chk(rowsum), _chk(stats), _chk(da_dst), _chk(att_src, torch.float32), _chk(att_dst, torch.float32),
            _chk(dout), _chk(dh), _chk(da_src), n, heads, chan, float(negative_slope), int(add_self_loops),
            float(dropout_p), int(seed), dt, st)
-    return dh, da_src, da_dst
+    return (dh, da_src, da_dst, dout) if through_elu else (dh, da_src, da_dst)
 
 
 def gat_datt(h, da_src, da_dst, heads, chan, datt_src_out=None, datt_dst_out=None):
