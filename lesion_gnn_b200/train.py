@@ -109,10 +109,18 @@ class _ClampedRegressionLoss(torch.autograd.Function):
         return (dl * g).view(ctx.shape), None, None, None
 
 
+def _fused_regression(logits: Tensor, y: Tensor, loss_type: str) -> bool:
+    return (loss_type in ("MSE", "SmoothL1") and logits.is_cuda and logits.dtype == torch.float32 and y.dtype == torch.int64
+            and logits.dim() == 2 and logits.size(1) == 1)
+
+
+# profiling knob: 0 = the loss goes through its autograd node (ones_like seed + multiply by the upstream gradient)
+_DIRECT_LOSS_GRAD = os.environ.get("LGK_DIRECT_LOSS_GRAD", "1") != "0"
+
+
 def loss_fn(logits: Tensor, y: Tensor, loss_type: str = "MSE", num_classes: int = 5) -> Tensor:
     """reference models/base.py:88-96,196-199 and the regression clamp of models/gat.py:94-95"""
-    if loss_type in ("MSE", "SmoothL1") and logits.is_cuda and logits.dtype == torch.float32 and y.dtype == torch.int64 \
-            and logits.dim() == 2 and logits.size(1) == 1:
+    if _fused_regression(logits, y, loss_type):
         return _ClampedRegressionLoss.apply(logits.contiguous(), y.contiguous(), float(num_classes - 1),
                                             0 if loss_type == "MSE" else 1)
     if loss_type == "MSE":
@@ -152,6 +160,13 @@ def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_clas
     seg = Segments.from_batch(db.batch, db.num_graphs)
     logits = model(db.x, graph, seg)
     graph.join()  # a model that never touched the graph must still join the build stream
+    if _DIRECT_LOSS_GRAD and _fused_regression(logits, db.y, loss_type) and logits.requires_grad:
+        # loss and (weighted) d loss / d logits from one launch; the backward starts at the logits: no autograd node
+        # for the loss, no ones_like seed, no multiply by the upstream gradient
+        loss, dl = ops.clamped_regression_loss(logits.detach().reshape(-1), db.y, 0.0, float(num_classes - 1),
+                                               0 if loss_type == "MSE" else 1, grad_scale=db.loss_weight)
+        logits.backward(dl.view_as(logits))
+        return loss
     loss = loss_fn(logits, db.y, loss_type, num_classes)
     (loss * db.loss_weight if db.loss_weight != 1.0 else loss).backward()
     return loss.detach()
