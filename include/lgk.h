@@ -254,10 +254,12 @@ LGK_API int lgk_elu_fwd(const void* x, void* y, int64_t n, int dtype, void* stre
 LGK_API int lgk_elu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);
 /* fused multi-tensor Adam / AdamW over one flat fp32 buffer; grad is multiplied by grad_scale first
  * (1/world_size after the data-parallel all-reduce).  The 1-based step count is `step`, or -- so that a
- * captured CUDA graph can be replayed -- read from the device counter `step_dev` when that is non-NULL.   */
-LGK_API int lgk_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
+ * captured CUDA graph can be replayed -- read from the device counter `step_dev` when that is non-NULL.
+ * zero_grad != 0: every gradient is set to zero once it has been consumed (optimizer.zero_grad() of the next
+ * step without its own launch).                                                                               */
+LGK_API int lgk_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
                   float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
-                  const int64_t* step_dev, float grad_scale, int adamw, void* stream);
+                  const int64_t* step_dev, float grad_scale, int adamw, int zero_grad, void* stream);
 
 /* Clamped regression loss of the reference's training step, forward and gradient in one launch
  * (models/base.py:196-199 `criterion(logits, y)` with the regression clamp of models/gat.py:94-95:

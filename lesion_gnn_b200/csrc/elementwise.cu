@@ -50,10 +50,10 @@ __global__ void __launch_bounds__(256) elu_bwd_kernel(const T* __restrict__ y, c
   }
 }
 
-__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
                                                    float wd, float bc1, float bc2_sqrt, const int64_t* __restrict__ step_dev,
-                                                   float gscale, int adamw) {
+                                                   float gscale, int adamw, int zero_grad) {
   const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n) return;
   if (step_dev) {  // graph-replay mode: bias corrections from the device-resident step counter
@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
   float param = p[i];
   float grad = g[i] * gscale;
+  if (zero_grad) g[i] = 0.f;  // the bucket is ready for the next backward: no separate fill launch
   if (adamw) param *= 1.f - lr * wd;        // decoupled decay (torch.optim.AdamW)
   else grad = fmaf(wd, param, grad);        // L2 penalty folded into the gradient (torch.optim.Adam)
   const float mi = fmaf(b1, m[i], (1.f - b1) * grad);
@@ -113,9 +114,9 @@ extern "C" int lgk_elu_bwd(const void* y, const void* dy, void* dx, int64_t n, i
   return LGK_OK;
 }
 
-extern "C" int lgk_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+extern "C" int lgk_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                              float beta1, float beta2, float eps, float weight_decay, int64_t step, const int64_t* step_dev,
-                             float grad_scale, int adamw, void* stream_) {
+                             float grad_scale, int adamw, int zero_grad, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && (step >= 1 || step_dev), LGK_ERR_BAD_ARG, "lgk_adam_step: bad size or step");
   if (step < 1) step = 1;
@@ -124,7 +125,7 @@ extern "C" int lgk_adam_step(float* param, const float* grad, float* exp_avg, fl
   const double bc1 = 1.0 - pow(double(beta1), double(step));
   const double bc2 = 1.0 - pow(double(beta2), double(step));
   adam_kernel<<<unsigned(ceil_div(n, 256)), 256, 0, stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
-                                                              weight_decay, float(bc1), float(sqrt(bc2)), step_dev, grad_scale, adamw);
+                                                              weight_decay, float(bc1), float(sqrt(bc2)), step_dev, grad_scale, adamw, zero_grad);
   LGK_CHECK_LAUNCH("adam_kernel");
   return LGK_OK;
 }

@@ -53,7 +53,10 @@ class FlatParams:
         self.numel = total
 
     def zero_grad(self) -> None:
-        self.grad.zero_()
+        if getattr(self, "_grad_is_zero", False):
+            self._grad_is_zero = False  # cleared by the last optimiser step (FlatAdam.step); the backward dirties it
+        else:
+            self.grad.zero_()
         for p, o in zip(self.params, self.offsets):  # keep .grad bound to the bucket
             if p.grad is None or p.grad.data_ptr() != self.grad.data_ptr() + 4 * o:
                 p.grad = self.grad[o:o + p.numel()].view_as(p)
@@ -90,7 +93,8 @@ class FlatAdam(FlatParams):
         self.step_dev.add_(1)
         ops.adam_step(self.param, self.grad, self.exp_avg, self.exp_avg_sq, lr=self.lr, betas=self.betas, eps=self.eps,
                       weight_decay=self.weight_decay, step=0, step_dev=self.step_dev, grad_scale=grad_scale,
-                      adamw=self.adamw)
+                      adamw=self.adamw, zero_grad=_ADAM_ZEROES_GRAD)
+        self._grad_is_zero = _ADAM_ZEROES_GRAD  # the kernel cleared the bucket: the next zero_grad() launches nothing
 
 
 class _ClampedRegressionLoss(torch.autograd.Function):
@@ -114,6 +118,8 @@ def _fused_regression(logits: Tensor, y: Tensor, loss_type: str) -> bool:
             and logits.dim() == 2 and logits.size(1) == 1)
 
 
+# profiling knob: 0 = zero_grad() is its own fill launch at the head of every step
+_ADAM_ZEROES_GRAD = os.environ.get("LGK_ADAM_ZEROES_GRAD", "1") != "0"
 # profiling knob: 0 = the loss goes through its autograd node (ones_like seed + multiply by the upstream gradient)
 _DIRECT_LOSS_GRAD = os.environ.get("LGK_DIRECT_LOSS_GRAD", "1") != "0"
 
