@@ -256,10 +256,12 @@ LGK_API int lgk_elu_bwd(const void* y, const void* dy, void* dx, int64_t n, int 
  * (1/world_size after the data-parallel all-reduce).  The 1-based step count is `step`, or -- so that a
  * captured CUDA graph can be replayed -- read from the device counter `step_dev` when that is non-NULL.
  * zero_grad != 0: every gradient is set to zero once it has been consumed (optimizer.zero_grad() of the next
- * step without its own launch).                                                                               */
+ * step without its own launch).  advance_step != 0 (needs step_dev, an int64[2]: {steps completed, scratch = 0}):
+ * the launch uses step_dev[0] + 1 as its step count and stores it back when its last CTA retires, so the caller
+ * launches no increment.                                                                                      */
 LGK_API int lgk_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
                   float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
-                  const int64_t* step_dev, float grad_scale, int adamw, int zero_grad, void* stream);
+                  int64_t* step_dev, float grad_scale, int adamw, int zero_grad, int advance_step, void* stream);
 
 /* Clamped regression loss of the reference's training step, forward and gradient in one launch
  * (models/base.py:196-199 `criterion(logits, y)` with the regression clamp of models/gat.py:94-95:

@@ -52,15 +52,29 @@ __global__ void __launch_bounds__(256) elu_bwd_kernel(const T* __restrict__ y, c
 
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
-                                                   float wd, float bc1, float bc2_sqrt, const int64_t* __restrict__ step_dev,
-                                                   float gscale, int adamw, int zero_grad) {
+                                                   float wd, float bc1, float bc2_sqrt, int64_t* __restrict__ step_dev,
+                                                   float gscale, int adamw, int zero_grad, int advance) {
   const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= n) return;
   if (step_dev) {  // graph-replay mode: bias corrections from the device-resident step counter
-    const double t = double(*step_dev);
+    // advance: the counter holds the steps COMPLETED so far and this launch moves it on -- by the CTA that finishes
+    // last (step_dev[1] counts finished CTAs), i.e. after every CTA has read it: no separate increment launch
+    const int64_t steps = *reinterpret_cast<volatile int64_t*>(step_dev) + (advance ? 1 : 0);
+    const double t = double(steps);
     bc1 = float(1.0 - pow(double(b1), t));
     bc2_sqrt = float(sqrt(1.0 - pow(double(b2), t)));
+    if (advance) {
+      __syncthreads();  // every thread of this CTA has read the counter
+      if (threadIdx.x == 0) {
+        __threadfence();
+        unsigned long long* done = reinterpret_cast<unsigned long long*>(step_dev + 1);
+        if (atomicAdd(done, 1ull) == gridDim.x - 1) {
+          *done = 0ull;
+          step_dev[0] = steps;
+        }
+      }
+    }
   }
+  if (i >= n) return;
   float param = p[i];
   float grad = g[i] * gscale;
   if (zero_grad) g[i] = 0.f;  // the bucket is ready for the next backward: no separate fill launch
@@ -115,8 +129,8 @@ extern "C" int lgk_elu_bwd(const void* y, const void* dy, void* dx, int64_t n, i
 }
 
 extern "C" int lgk_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
-                             float beta1, float beta2, float eps, float weight_decay, int64_t step, const int64_t* step_dev,
-                             float grad_scale, int adamw, int zero_grad, void* stream_) {
+                             float beta1, float beta2, float eps, float weight_decay, int64_t step, int64_t* step_dev,
+                             float grad_scale, int adamw, int zero_grad, int advance_step, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && (step >= 1 || step_dev), LGK_ERR_BAD_ARG, "lgk_adam_step: bad size or step");
   if (step < 1) step = 1;
@@ -125,7 +139,7 @@ extern "C" int lgk_adam_step(float* param, float* grad, float* exp_avg, float* e
   const double bc1 = 1.0 - pow(double(beta1), double(step));
   const double bc2 = 1.0 - pow(double(beta2), double(step));
   adam_kernel<<<unsigned(ceil_div(n, 256)), 256, 0, stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
-                                                              weight_decay, float(bc1), float(sqrt(bc2)), step_dev, grad_scale, adamw, zero_grad);
+                                                              weight_decay, float(bc1), float(sqrt(bc2)), step_dev, grad_scale, adamw, zero_grad, advance_step);
   LGK_CHECK_LAUNCH("adam_kernel");
   return LGK_OK;
 }

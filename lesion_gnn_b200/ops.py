@@ -382,13 +382,16 @@ def elu_bwd(y: Tensor, dy: Tensor) -> Tensor:
 
 def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, *, lr: float, betas=(0.9, 0.999),
               eps: float = 1e-8, weight_decay: float = 0.0, step: int = 1, step_dev: Optional[Tensor] = None,
-              grad_scale: float = 1.0, adamw: bool = False, zero_grad: bool = False) -> None:
-    """zero_grad: the kernel clears every gradient it has consumed (the next step needs no fill launch)"""
+              grad_scale: float = 1.0, adamw: bool = False, zero_grad: bool = False, advance_step: bool = False) -> None:
+    """zero_grad: the kernel clears every gradient it has consumed (the next step needs no fill launch);
+    advance_step: step_dev is int64[2] = {steps completed, 0} and the kernel itself moves it on by one"""
+    if advance_step and (step_dev is None or step_dev.numel() < 2):
+        raise ValueError("advance_step needs a two-element device step counter")
     L = _lib.lib()
     f32 = torch.float32
     L.call("lgk_adam_step", _chk(param, f32, "param"), _chk(grad, f32, "grad"), _chk(exp_avg, f32), _chk(exp_avg_sq, f32),
            param.numel(), float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
-           _chk(step_dev, torch.int64, "step_dev"), float(grad_scale), int(adamw), int(zero_grad), _stream())
+           _chk(step_dev, torch.int64, "step_dev"), float(grad_scale), int(adamw), int(zero_grad), int(advance_step), _stream())
 
 
 def clamped_regression_loss(logits: Tensor, y: Tensor, lo: float, hi: float, kind: int, want_grad: bool = True,

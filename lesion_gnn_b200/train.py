@@ -85,15 +85,17 @@ class FlatAdam(FlatParams):
             raise RuntimeError("FlatAdam needs the module on a CUDA device: lesion_gnn_b200 has no CPU path")
         self.exp_avg = torch.zeros_like(self.param)
         self.exp_avg_sq = torch.zeros_like(self.param)
-        self.step_dev = torch.zeros(1, dtype=torch.int64, device=self.param.device)
+        self.step_dev = torch.zeros(2, dtype=torch.int64, device=self.param.device)  # {steps completed, kernel scratch}
         self.lr, self.betas, self.eps, self.weight_decay, self.adamw = lr, betas, eps, weight_decay, adamw
 
     def step(self, grad_scale: float = 1.0) -> None:
-        """one fused kernel; the step counter lives on the device so the call can be graph-captured"""
-        self.step_dev.add_(1)
+        """one fused kernel; the step counter lives on the device (and is advanced by the kernel) so the call can be
+        graph-captured"""
+        if not _ADAM_ADVANCES_STEP:
+            self.step_dev[:1].add_(1)
         ops.adam_step(self.param, self.grad, self.exp_avg, self.exp_avg_sq, lr=self.lr, betas=self.betas, eps=self.eps,
                       weight_decay=self.weight_decay, step=0, step_dev=self.step_dev, grad_scale=grad_scale,
-                      adamw=self.adamw, zero_grad=_ADAM_ZEROES_GRAD)
+                      adamw=self.adamw, zero_grad=_ADAM_ZEROES_GRAD, advance_step=_ADAM_ADVANCES_STEP)
         self._grad_is_zero = _ADAM_ZEROES_GRAD  # the kernel cleared the bucket: the next zero_grad() launches nothing
 
 
@@ -118,6 +120,8 @@ def _fused_regression(logits: Tensor, y: Tensor, loss_type: str) -> bool:
             and logits.dim() == 2 and logits.size(1) == 1)
 
 
+# 1 = the Adam kernel advances the step counter itself (measured slower than the 1-element add launch: off)
+_ADAM_ADVANCES_STEP = os.environ.get("LGK_ADAM_ADVANCES_STEP", "0") != "0"
 # profiling knob: 0 = zero_grad() is its own fill launch at the head of every step
 _ADAM_ZEROES_GRAD = os.environ.get("LGK_ADAM_ZEROES_GRAD", "1") != "0"
 # profiling knob: 0 = the loss goes through its autograd node (ones_like seed + multiply by the upstream gradient)

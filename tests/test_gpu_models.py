@@ -138,6 +138,21 @@ def test_adam_matches_torch(dev):
                 step_dev.add_(1)
                 ops.adam_step(pg, g.float().to(dev), m, v, lr=1e-2, weight_decay=wd, step=0, step_dev=step_dev, adamw=adamw)
         assert_close(pg, ref, 1e-5, f"adam adamw={adamw} wd={wd}")
+        # the kernel advances the counter itself (int64[2] = {steps completed, scratch}) and clears the gradients
+        ref2 = p.clone().requires_grad_(True)
+        opt2 = (torch.optim.AdamW if adamw else torch.optim.Adam)([ref2], lr=1e-2, weight_decay=wd)
+        pg2 = p.float().to(dev)
+        m2, v2 = torch.zeros_like(pg2), torch.zeros_like(pg2)
+        counter = torch.zeros(2, dtype=torch.int64, device=dev)
+        for step in range(1, 6):
+            g = torch.randn(1000, dtype=torch.float64)
+            ref2.grad = g.clone()
+            opt2.step()
+            gg = g.float().to(dev)
+            ops.adam_step(pg2, gg, m2, v2, lr=1e-2, weight_decay=wd, step=0, step_dev=counter, adamw=adamw,
+                          zero_grad=True, advance_step=True)
+            assert counter.tolist() == [step, 0] and float(gg.abs().max()) == 0.0
+        assert_close(pg2, ref2, 1e-5, f"adam (self-advancing) adamw={adamw} wd={wd}")
 
 
 @pytest.mark.parametrize("use_graph", [False, True])
