@@ -12,6 +12,7 @@
 // (thread per entry, coalesced window load); larger buckets get one CTA each and a bitonic network
 // (shared memory up to 4096 entries, in place in global memory beyond).
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace lgk {
 namespace {
@@ -399,7 +400,9 @@ extern "C" int lgk_csr_build(const int64_t* edge_index, int64_t E, int64_t N, in
   sa.in[1] = w.cnt_src; sa.out[1] = colptr; sa.sums[1] = w.sums_b;
   int nblocks = int(ceil_div(N, kScanTile));
   dim3 sgrid(nblocks, want_csc ? 2 : 1);
-  if (N <= int64_t(kSingleThreads) * kSingleItems) {
+  // LGK_CSR_SINGLE_SCAN=0: always the three-kernel scan (profiling knob)
+  static const bool single_scan = [] { const char* v = getenv("LGK_CSR_SINGLE_SCAN"); return !(v && *v == '0'); }();
+  if (single_scan && N <= int64_t(kSingleThreads) * kSingleItems) {
     scan_single_kernel<<<dim3(1, want_csc ? 2 : 1), kSingleThreads, 0, stream>>>(sa, N);
     LGK_CHECK_LAUNCH("scan_single_kernel");
   } else {
