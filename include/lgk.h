@@ -136,6 +136,24 @@ LGK_API int lgk_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* emap
              const void* x, const float* bias, void* out, int32_t* arg_out,
              int64_t n_rows, int64_t feat, int reduce, int dtype, void* stream);
 
+/* Row-blocked ("quad") form of a CSR / CSC for lgk_spmm_blocked: four consecutive rows 4g..4g+3 share one merged
+ * neighbour list, ascending by source id, qent[ptr[4g] + t] = source | membership << 28 (bit r: row 4g+r has the entry;
+ * a duplicate edge of one row is emitted as a second entry), t < qlen[g].  cmin / cmax [lgk_quad_chunks(n_rows)]: smallest /
+ * largest source id referenced by each chunk of 64 quads (INT32_MAX / -1 for a chunk without entries).  Built once per
+ * batch next to the CSR / CSC (lgk_csr_build) and shared by every layer; n_rows < 2^28.  qent has room for E entries. */
+LGK_API int64_t lgk_quad_chunks(int64_t n_rows);
+LGK_API int lgk_quad_build(const int32_t* ptr, const int32_t* idx, int64_t n_rows, int32_t* qlen, uint32_t* qent,
+                   int32_t* cmin, int32_t* cmax, void* stream);
+/* lgk_spmm for large graphs whose neighbours lie in a window of node ids (collated lesion graphs: block diagonal,
+ * raster node order): same result as lgk_spmm without edge values (`ew`), reduce = LGK_SUM | LGK_MEAN, fp32, feat % 4 == 0,
+ * summation in ascending source order.  Source rows are streamed once per CTA into a shared-memory ring by TMA and every
+ * gathered row feeds the up to four destination rows of its quad; chunks whose window does not fit the ring are reduced
+ * with global gathers by the same launch.  Same self-loop / pre / post / bias semantics as lgk_spmm.              */
+LGK_API int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const uint32_t* qent, const int32_t* cmin,
+                     const int32_t* cmax, const float* pre, const float* post, const float* selfw, float self_fill,
+                     int self_mode, const void* x, const float* bias, void* out, int64_t n_rows, int64_t feat,
+                     int reduce, int dtype, void* stream);
+
 /* backward of the max aggregation: dx[j,f] = sum over CSC entries q of column j with
  * arg[row[q], f] == csr2csc[q] of dy[row[q], f]                                                        */
 LGK_API int lgk_spmm_max_bwd(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const int32_t* arg,
@@ -160,18 +178,21 @@ LGK_API int lgk_gat_alpha(const void* h, const float* att_src, const float* att_
  * with denominator + 1e-16; N(i) = stored non-loop entries + one self loop if add_self_loops (GATConv's
  * remove_self_loops + add_self_loops), else the stored entries.  Single pass, online softmax.
  * rowmax/rowsum [N,H]: saved softmax statistics for the backward pass.
- * dropout_p > 0: attention dropout with a counter-based RNG keyed on (seed, CSR slot, head).           */
+ * dropout_p > 0: attention dropout with a counter-based RNG keyed on (seed, CSR slot, head).  seed_dev (may be NULL):
+ * a device-side int64 counter mixed into the seed at run time -- a captured CUDA graph freezes `seed`, so the training
+ * step passes its optimiser step counter here and every replay draws a new mask; the forward and both backward
+ * launches of one step must see the same value.                                                         */
 LGK_API int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
                 const float* bias, void* out, float* rowmax, float* rowsum,
                 int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
-                float dropout_p, uint64_t seed, int dtype, void* stream);
+                float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype, void* stream);
 
 /* lgk_gat_fwd with the activation that follows every GAT layer of the reference (models/gat.py:51 `F.elu(conv(x))`)
  * written by the same launch: out as above (the backward needs it), out_elu = elu(out).                        */
 LGK_API int lgk_gat_fwd_elu(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
                     const float* bias, void* out, void* out_elu, float* rowmax, float* rowsum,
                     int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
-                    float dropout_p, uint64_t seed, int dtype, void* stream);
+                    float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype, void* stream);
 
 /* backward, dst side (CSR): da_dst[i,h] = sum_j dz_ij, and the packed per-(node, head) statistics
  * stats[i,h] = {a_dst, rowmax, 1/(rowsum + 1e-16), delta} with delta = <dout[i,h,:], out[i,h,:] - bias>
@@ -180,7 +201,7 @@ LGK_API int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const voi
                     const float* rowmax, const float* rowsum, const void* out, const float* bias, const void* dout,
                     float* stats, float* da_dst,
                     int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
-                    float dropout_p, uint64_t seed, int dtype, void* stream);
+                    float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype, void* stream);
 /* lgk_gat_bwd_dst for a layer run with lgk_gat_fwd_elu: dy is the gradient of elu(out); the kernel forms
  * dout = dy * elu'(out) on the fly, uses it as above and writes it to `dout` (same type and shape as out) for
  * lgk_gat_bwd_src and the bias gradient -- no separate lgk_elu_bwd launch.                                    */
@@ -188,7 +209,7 @@ LGK_API int lgk_gat_bwd_dst_elu(const int32_t* rowptr, const int32_t* col, const
                         const float* rowmax, const float* rowsum, const void* out, const float* bias, const void* dy,
                         void* dout, float* stats, float* da_dst,
                         int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
-                        float dropout_p, uint64_t seed, int dtype, void* stream);
+                        float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype, void* stream);
 /* backward, src side (CSC): dh[j,h,:] = sum_i alpha_ij dout[i,h,:] + da_src[j,h] att_src[h,:] + da_dst[j,h] att_dst[h,:],
  * da_src[j,h] = sum_i dz_ij                                                                             */
 LGK_API int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const void* h,
@@ -196,7 +217,7 @@ LGK_API int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int
                     const float* stats, const float* da_dst, const float* att_src, const float* att_dst,
                     const void* dout, void* dh, float* da_src,
                     int64_t num_nodes, int heads, int chan, float negative_slope, int add_self_loops,
-                    float dropout_p, uint64_t seed, int dtype, void* stream);
+                    float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype, void* stream);
 /* datt_src[h,c] (+)= sum_n da_src[n,h] h[n,h,c]; datt_dst likewise (two-stage, deterministic); accumulate != 0 adds to
  * the outputs (gradient buckets) instead of overwriting them */
 LGK_API int64_t lgk_gat_datt_workspace_bytes(int64_t num_nodes, int heads, int chan);

@@ -39,6 +39,7 @@ struct GatArgs {
   float drop_p;
   float drop_scale;
   uint64_t seed;
+  const int64_t* seed_dev;  // optional device-side step counter mixed into the seed (CUDA-graph replays draw new masks)
 };
 
 template <int LPR>
@@ -63,10 +64,17 @@ __device__ __forceinline__ float group_max(float v, unsigned mask) {
   return v;
 }
 __device__ __forceinline__ float lrelu(float z, float slope) { return z > 0.f ? z : slope * z; }
-__device__ __forceinline__ float keep_scale(const GatArgs& a, uint32_t slot, int head) {
+// seed of this launch: the host seed, advanced by the device-side counter when there is one -- a captured CUDA graph
+// bakes the host value into its kernel nodes, the counter (the optimiser's step count) is what changes between replays;
+// forward and both backward passes of a step read the same value
+__device__ __forceinline__ uint64_t launch_seed(const GatArgs& a) {
+  if (a.drop_p <= 0.f || !a.seed_dev) return a.seed;
+  return a.seed + 0xD1B54A32D192ED03ull * uint64_t(__ldg(a.seed_dev));
+}
+__device__ __forceinline__ float keep_scale(const GatArgs& a, uint64_t seed, uint32_t slot, int head) {
   // attention dropout: 0 (dropped) or 1/(1-p) (kept); identical in forward and both backward passes
   if (a.drop_p <= 0.f) return 1.f;
-  return uniform_hash(a.seed, slot, uint32_t(head)) < a.drop_p ? 0.f : a.drop_scale;
+  return uniform_hash(seed, slot, uint32_t(head)) < a.drop_p ? 0.f : a.drop_scale;
 }
 constexpr uint32_t kSelfSlotBit = 0x80000000u;
 
@@ -108,6 +116,7 @@ __global__ void __launch_bounds__(kThreads) gat_fwd_kernel(GatArgs a, const T* _
   const int64_t item = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * GPW + ((threadIdx.x & 31) / LPR);
   if (item >= a.n_nodes * H) return;
   const unsigned mask = gmask<LPR>();
+  const uint64_t seed = launch_seed(a);
   const int i = int(item / H), head = int(item - int64_t(i) * H);
   const int64_t F = int64_t(H) * C;
   const int start = a.ptr[i], end = a.ptr[i + 1];
@@ -121,7 +130,7 @@ __global__ void __launch_bounds__(kThreads) gat_fwd_kernel(GatArgs a, const T* _
   if (a.add_self) {  // GATConv: remove_self_loops + add_self_loops => exactly one (i,i) entry
     m = lrelu(__ldg(a.a_src + item) + ad, a.slope);
     s = 1.f;
-    const float ks = keep_scale(a, kSelfSlotBit | uint32_t(i), head);
+    const float ks = keep_scale(a, seed, kSelfSlotBit | uint32_t(i), head);
 #pragma unroll
     for (int v = 0; v < VPL; ++v) {
       const int vec = gl + v * LPR;
@@ -146,7 +155,7 @@ __global__ void __launch_bounds__(kThreads) gat_fwd_kernel(GatArgs a, const T* _
     const float rescale = expf(m - m_new);  // m = -inf on the first chunk -> 0
     float my_p = expf(my_e - m_new);        // my_e = -inf -> 0
     s = s * rescale + group_sum<LPR>(my_p, mask);
-    if (a.drop_p > 0.f && p < end) my_p *= keep_scale(a, uint32_t(p), head);
+    if (a.drop_p > 0.f && p < end) my_p *= keep_scale(a, seed, uint32_t(p), head);
 #pragma unroll
     for (int v = 0; v < VPL; ++v) { acc[v].x *= rescale; acc[v].y *= rescale; acc[v].z *= rescale; acc[v].w *= rescale; }
     m = m_new;
@@ -199,6 +208,7 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_dst_kernel(GatArgs a, const 
   const int64_t item = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * GPW + ((threadIdx.x & 31) / LPR);
   if (item >= a.n_nodes * H) return;
   const unsigned mask = gmask<LPR>();
+  const uint64_t seed = launch_seed(a);
   const int i = int(item / H), head = int(item - int64_t(i) * H);
   const int64_t F = int64_t(H) * C;
   const int start = a.ptr[i], end = a.ptr[i + 1];
@@ -244,7 +254,7 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_dst_kernel(GatArgs a, const 
     dotp = group_sum<LPR>(dotp, mask);
     const float z = __ldg(a.a_src + int64_t(j) * H + head) + ad;
     const float alpha = expf(lrelu(z, a.slope) - m) * inv;
-    const float dalpha = keep_scale(a, slot, head) * dotp;
+    const float dalpha = keep_scale(a, seed, slot, head) * dotp;
     da += alpha * (dalpha - delta) * (z > 0.f ? 1.f : a.slope);
   };
 
@@ -279,6 +289,7 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
   const int64_t item = (int64_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * GPW + ((threadIdx.x & 31) / LPR);
   if (item >= a.n_nodes * H) return;
   const unsigned mask = gmask<LPR>();
+  const uint64_t seed = launch_seed(a);
   const int j = int(item / H), head = int(item - int64_t(j) * H);
   const int64_t F = int64_t(H) * C;
   const int start = a.ptr[j], end = a.ptr[j + 1];
@@ -311,7 +322,7 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
     dotp = group_sum<LPR>(dotp, mask);
     const float z = as + st.x;
     const float alpha = expf(lrelu(z, a.slope) - st.y) * st.z;
-    const float ks = keep_scale(a, slot, head);
+    const float ks = keep_scale(a, seed, slot, head);
     da += alpha * (ks * dotp - st.w) * (z > 0.f ? 1.f : a.slope);
     const float w = alpha * ks;
 #pragma unroll
@@ -419,10 +430,10 @@ int check_shape(const char* who, int64_t N, int H, int C) {
     else KERNEL<T, 32, 8><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);                        \
   } while (0)
 
-GatArgs base_args(int64_t N, int H, int C, float slope, int add_self, float drop_p, uint64_t seed) {
+GatArgs base_args(int64_t N, int H, int C, float slope, int add_self, float drop_p, uint64_t seed, const int64_t* seed_dev) {
   GatArgs a{};
   a.n_nodes = N; a.heads = H; a.chan = C; a.slope = slope; a.add_self = add_self;
-  a.drop_p = drop_p; a.drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f; a.seed = seed;
+  a.drop_p = drop_p; a.drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f; a.seed = seed; a.seed_dev = seed_dev;
   return a;
 }
 
@@ -450,14 +461,14 @@ extern "C" int lgk_gat_alpha(const void* h, const float* att_src, const float* a
 
 static int gat_fwd_impl(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
                            const float* bias, void* out, float* rowmax, float* rowsum, int64_t N, int H, int C,
-                        float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                        float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype,
                         void* stream_, void* out_elu) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_shape("lgk_gat_fwd", N, H, C)) return rc;
   if (N == 0) return LGK_OK;
   LGK_REQUIRE(rowptr && h && a_src && a_dst && out, LGK_ERR_BAD_ARG, "lgk_gat_fwd: null pointer");
   LGK_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_gat_fwd: dropout must be in [0,1)");
-  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
+  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed, seed_dev);
   a.ptr = rowptr; a.idx = col; a.a_src = a_src; a.a_dst = a_dst; a.bias = bias; a.rowmax = rowmax; a.rowsum = rowsum;
   a.act_out = out_elu;
   const int64_t items = N * H;
@@ -473,32 +484,32 @@ static int gat_fwd_impl(const int32_t* rowptr, const int32_t* col, const void* h
 
 extern "C" int lgk_gat_fwd(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src, const float* a_dst,
                            const float* bias, void* out, float* rowmax, float* rowsum, int64_t N, int H, int C,
-                           float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                           float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype,
                            void* stream_) {
   return gat_fwd_impl(rowptr, col, h, a_src, a_dst, bias, out, rowmax, rowsum, N, H, C, negative_slope, add_self_loops,
-                      dropout_p, seed, dtype, stream_, nullptr);
+                      dropout_p, seed, seed_dev, dtype, stream_, nullptr);
 }
 
 extern "C" int lgk_gat_fwd_elu(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
                                const float* a_dst, const float* bias, void* out, void* out_elu, float* rowmax,
                                float* rowsum, int64_t N, int H, int C, float negative_slope, int add_self_loops,
-                               float dropout_p, uint64_t seed, int dtype, void* stream_) {
+                               float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype, void* stream_) {
   LGK_REQUIRE(out_elu || N == 0, LGK_ERR_BAD_ARG, "lgk_gat_fwd_elu: null pointer");
   return gat_fwd_impl(rowptr, col, h, a_src, a_dst, bias, out, rowmax, rowsum, N, H, C, negative_slope, add_self_loops,
-                      dropout_p, seed, dtype, stream_, out_elu);
+                      dropout_p, seed, seed_dev, dtype, stream_, out_elu);
 }
 
 static int gat_bwd_dst_impl(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
                                const float* a_dst, const float* rowmax, const float* rowsum, const void* out,
                                const float* bias, const void* dout, float* delta, float* da_dst, int64_t N, int H, int C,
-                               float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                               float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype,
                                void* stream_, void* dpre_out) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_shape("lgk_gat_bwd_dst", N, H, C)) return rc;
   if (N == 0) return LGK_OK;
   LGK_REQUIRE(rowptr && h && a_src && a_dst && rowmax && rowsum && out && dout && delta && da_dst, LGK_ERR_BAD_ARG,
               "lgk_gat_bwd_dst: null pointer");
-  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
+  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed, seed_dev);
   a.ptr = rowptr; a.idx = col; a.a_src = a_src; a.a_dst = a_dst; a.bias = bias;
   a.rowmax = const_cast<float*>(rowmax); a.rowsum = const_cast<float*>(rowsum);
   a.stats = reinterpret_cast<float4*>(delta); a.da_out = da_dst; a.act_out = dpre_out;
@@ -516,27 +527,27 @@ static int gat_bwd_dst_impl(const int32_t* rowptr, const int32_t* col, const voi
 extern "C" int lgk_gat_bwd_dst(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
                                const float* a_dst, const float* rowmax, const float* rowsum, const void* out,
                                const float* bias, const void* dout, float* delta, float* da_dst, int64_t N, int H, int C,
-                               float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, int dtype,
+                               float negative_slope, int add_self_loops, float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype,
                                void* stream_) {
   return gat_bwd_dst_impl(rowptr, col, h, a_src, a_dst, rowmax, rowsum, out, bias, dout, delta, da_dst, N, H, C,
-                          negative_slope, add_self_loops, dropout_p, seed, dtype, stream_, nullptr);
+                          negative_slope, add_self_loops, dropout_p, seed, seed_dev, dtype, stream_, nullptr);
 }
 
 extern "C" int lgk_gat_bwd_dst_elu(const int32_t* rowptr, const int32_t* col, const void* h, const float* a_src,
                                    const float* a_dst, const float* rowmax, const float* rowsum, const void* out,
                                    const float* bias, const void* dy, void* dout, float* delta, float* da_dst, int64_t N,
                                    int H, int C, float negative_slope, int add_self_loops, float dropout_p, uint64_t seed,
-                                   int dtype, void* stream_) {
+                                   const int64_t* seed_dev, int dtype, void* stream_) {
   LGK_REQUIRE(dout || N == 0, LGK_ERR_BAD_ARG, "lgk_gat_bwd_dst_elu: null pointer");
   return gat_bwd_dst_impl(rowptr, col, h, a_src, a_dst, rowmax, rowsum, out, bias, dy, delta, da_dst, N, H, C,
-                          negative_slope, add_self_loops, dropout_p, seed, dtype, stream_, dout);
+                          negative_slope, add_self_loops, dropout_p, seed, seed_dev, dtype, stream_, dout);
 }
 
 extern "C" int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const int32_t* csr2csc, const void* h,
                                const float* a_src, const float* a_dst, const float* rowmax, const float* rowsum,
                                const float* delta, const float* da_dst, const float* att_src, const float* att_dst,
                                const void* dout, void* dh, float* da_src, int64_t N, int H, int C, float negative_slope,
-                               int add_self_loops, float dropout_p, uint64_t seed, int dtype, void* stream_) {
+                               int add_self_loops, float dropout_p, uint64_t seed, const int64_t* seed_dev, int dtype, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   (void)a_dst; (void)rowmax; (void)rowsum;  // carried inside the packed statistics written by lgk_gat_bwd_dst
   if (int rc = check_shape("lgk_gat_bwd_src", N, H, C)) return rc;
@@ -544,7 +555,7 @@ extern "C" int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const 
   LGK_REQUIRE(colptr && h && a_src && delta && da_dst && att_src && att_dst && dout && dh && da_src, LGK_ERR_BAD_ARG,
               "lgk_gat_bwd_src: null pointer");
   LGK_REQUIRE(dropout_p <= 0.f || csr2csc, LGK_ERR_BAD_ARG, "lgk_gat_bwd_src: dropout needs csr2csc");
-  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed);
+  GatArgs a = base_args(N, H, C, negative_slope, add_self_loops, dropout_p, seed, seed_dev);
   a.ptr = colptr; a.idx = row; a.slotmap = csr2csc; a.a_src = a_src;
   a.stats = reinterpret_cast<float4*>(const_cast<float*>(delta)); a.da_dst = da_dst; a.da_out = da_src;
   a.att_src = att_src; a.att_dst = att_dst;

@@ -281,7 +281,11 @@ int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n,
     set_error("grad_w_tc: unsupported shape n=%lld k=%lld m=%lld", (long long)n, (long long)k, (long long)m);
     return LGK_ERR_UNSUPPORTED;
   }
-  static bool configured = false;
+  // the attribute is per device: one flag per device ordinal
+  static bool configured_dev[64] = {};
+  int dev_ord = 0;
+  cudaGetDevice(&dev_ord);
+  bool& configured = configured_dev[dev_ord & 63];
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(grad_w_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<2>());
     if (e == cudaSuccess)

@@ -278,7 +278,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
 // used by lgk_linear_fwd (linear.cu) when the product is large enough to be worth a tensor-core launch
 int launch_linear_tc(const float* x, const float* w, const float* bias, const float* rowscale, float* out, int64_t n,
                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream) {
-  static bool configured = false;
+  // the attribute is per device: one flag per device ordinal
+  static bool configured_dev[64] = {};
+  int dev_ord = 0;
+  cudaGetDevice(&dev_ord);
+  bool& configured = configured_dev[dev_ord & 63];
   if (!configured) {
     cudaError_t e = cudaSuccess;
     for (auto* fn : {linear_tc_kernel<4>, linear_tc_kernel<5>, linear_tc_kernel<6>, linear_tc_kernel<7>, linear_tc_kernel<8>})

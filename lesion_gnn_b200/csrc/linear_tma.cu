@@ -327,7 +327,11 @@ int launch_linear_tma(const float* x, const float* w, const float* bias, const f
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(out) |
                          reinterpret_cast<uintptr_t>(bias)) & 15) == 0;
   if (!aligned || (k & 3) || n >= (int64_t(1) << 31) || k >= (int64_t(1) << 31)) return LGK_OK;
-  static bool configured = false;
+  // the attribute is per device: one flag per device ordinal
+  static bool configured_dev[64] = {};
+  int dev_ord = 0;
+  cudaGetDevice(&dev_ord);
+  bool& configured = configured_dev[dev_ord & 63];
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(linear_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     if (e != cudaSuccess) {

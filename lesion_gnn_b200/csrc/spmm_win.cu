@@ -1,0 +1,572 @@
+// (2)+(4) windowed, row-blocked aggregation: the sum / mean SpMM of large banded graphs at HBM speed.
+//
+// Why a second aggregation kernel (measurements: profiles/README.md r01 v1, r02): spmm_vec_kernel lands every
+// gathered neighbour row in registers through the L1 data path -- d x F x 4 bytes per output row against
+// 2 x F x 4 compulsory HBM bytes -- and each batch of gathers waits on an L2 round trip, so at d = 16 it sits
+// at 0.3-0.4 of the HBM roofline.  Two changes remove both costs:
+//
+//   (i)  quad-blocked CSR (lgk_quad_build, built once per batch next to the CSR / CSC): four consecutive
+//        destination rows share ONE merged, sorted neighbour list with a 4-bit membership mask per entry.
+//        Neighbouring rows of a lesion / superpixel graph share most of their neighbours (raster order), so a
+//        gathered row feeds up to four accumulators: 2.1x fewer gathers on the config-4 stress graph.
+//   (ii) the source rows a chunk of 256 destination rows needs form a contiguous WINDOW of node ids (graphs of
+//        a collated batch are block diagonal, and inside a graph the node order follows the image raster).
+//        A producer warp streams that window into a shared-memory ring with TMA (tensor-map boxes of 32 rows x
+//        128 bytes, mbarrier-completed, several chunks ahead); the consumers gather from shared memory only:
+//        no register-landing global gathers, no L2 round trips on the critical path, every source row is
+//        read from L2/HBM once per CTA.
+//
+// A row is cut into 128-byte slices (32 fp32): a CTA owns one slice of a contiguous span of chunks, 8 lanes
+// cover a slice (LDS.128), a warp reduces four quads (16 rows) at once; the accumulation is FFMA2 / FADD2
+// (packed fp32x2, sm_100).  A chunk whose window does not fit the ring (wide band, random node order) is
+// reduced by the same code with global gathers, so the kernel is correct for every graph.
+// Atomic-free, fixed summation order (ascending source id): deterministic.
+#include "common.cuh"
+#include "umma.cuh"
+#include <cuda.h>  // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
+#include <limits.h>
+#include <stdlib.h>
+
+namespace lgk {
+namespace {
+
+constexpr int kQuadsPerChunk = 64;               // 256 destination rows per chunk (granularity of cmin / cmax)
+constexpr int kBlkRows = 32;                     // source rows per ring block = height of a TMA box
+constexpr int kSliceBytes = 128;                 // bytes of a feature row per slice
+constexpr int kSliceF4 = kSliceBytes / 16;       // 8 float4 columns = 8 lanes
+constexpr int kBlkBytes = kBlkRows * kSliceBytes;
+constexpr int kStages = 8;                       // chunks in flight between producer and consumers
+constexpr int kConsumerWarps = 16;
+constexpr int kThreadsWin = 32 * (kConsumerWarps + 1);
+constexpr int kBatch = 16;                       // merged entries staged per group and batch (two per lane)
+constexpr int kSmemMax = 232448;                 // 227 KB
+constexpr unsigned kColMask = 0x0FFFFFFFu;
+
+// ---- quad-blocked CSR builder -------------------------------------------------------------------------------
+// thread per quad: four-way merge of the quad's sorted rows.  Entry = col | mask << 28, written in place of the
+// quad's first row (ptr[4g] + t): the merged list is never longer than the four rows together.
+__global__ void __launch_bounds__(kQuadsPerChunk) quad_build_kernel(const int* __restrict__ ptr, const int* __restrict__ idx,
+                                                                    int64_t n_rows, int64_t n_quads, int* __restrict__ qlen,
+                                                                    unsigned* __restrict__ qent, int* __restrict__ cmin,
+                                                                    int* __restrict__ cmax) {
+  const int64_t g = int64_t(blockIdx.x) * kQuadsPerChunk + threadIdx.x;
+  int lo = INT_MAX, hi = -1;
+  if (g < n_quads) {
+    int pos[4], end[4], c[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t r = min(g * 4 + k, n_rows);
+      pos[k] = __ldg(ptr + r);
+      end[k] = __ldg(ptr + min(r + 1, n_rows));
+      c[k] = pos[k] < end[k] ? __ldg(idx + pos[k]) : INT_MAX;
+    }
+    const int start = pos[0];
+    int out = start;
+    while (true) {
+      const int m = min(min(c[0], c[1]), min(c[2], c[3]));
+      if (m == INT_MAX) break;
+      unsigned mask = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (c[k] == m) {  // a duplicate edge of the same row stays at the head and is emitted again
+          mask |= 1u << k;
+          ++pos[k];
+          c[k] = pos[k] < end[k] ? __ldg(idx + pos[k]) : INT_MAX;
+        }
+      }
+      qent[out++] = unsigned(m) | (mask << 28);
+      lo = min(lo, m);
+      hi = max(hi, m);
+    }
+    qlen[g] = out - start;
+  }
+  __shared__ int s_lo[kQuadsPerChunk / 32], s_hi[kQuadsPerChunk / 32];
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 1; w < kQuadsPerChunk / 32; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
+    cmin[blockIdx.x] = lo;
+    cmax[blockIdx.x] = hi;
+  }
+}
+
+// ---- PTX helpers ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_box_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(umma::smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(umma::smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u2(uint32_t addr, unsigned a, unsigned b) {
+  asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
+// packed fp32x2 arithmetic (FFMA2 / FADD2): two lanes of a float4 per instruction, one issue slot
+__device__ __forceinline__ void fma2(float2& acc, const float2 v, const float2 w) {
+  unsigned long long a = *reinterpret_cast<unsigned long long*>(&acc);
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a) : "l"(*reinterpret_cast<const unsigned long long*>(&v)),
+      "l"(*reinterpret_cast<const unsigned long long*>(&w)));
+  acc = *reinterpret_cast<float2*>(&a);
+}
+__device__ __forceinline__ void add2(float2& acc, const float2 v) {
+  unsigned long long a = *reinterpret_cast<unsigned long long*>(&acc);
+  asm("add.rn.f32x2 %0, %0, %1;" : "+l"(a) : "l"(*reinterpret_cast<const unsigned long long*>(&v)));
+  acc = *reinterpret_cast<float2*>(&a);
+}
+
+struct WinArgs {
+  const int* ptr;        // [n_rows + 1] CSR / CSC row pointer (quad g's merged list starts at ptr[4g])
+  const int* qlen;       // [n_quads]
+  const unsigned* qent;  // merged entries
+  const int* cmin;       // [n_chunks] smallest / largest source id of a chunk (INT_MAX / -1 when it has no entries)
+  const int* cmax;
+  const float* pre;
+  const float* post;
+  const float* selfw;
+  const float* bias;
+  const float* x;
+  float* out;
+  float self_fill;
+  int self_mode;
+  int mean;
+  int64_t n_rows, n_quads, n_chunks;
+  int feat, slices, nb;  // nb: ring blocks
+};
+
+struct WinShared {
+  uint64_t full[kStages], empty[kStages];
+  int direct[kStages];   // chunk is reduced with global gathers (its window does not fit the ring)
+  int lo_blk[kStages];   // first ring block the chunk reads (INT_MAX: none), for the eviction rule
+};
+
+// Accumulate one staged entry into the quad's four accumulators.  `o` carries the membership mask in bits 28..31.
+template <bool HAS_PRE>
+__device__ __forceinline__ void accumulate(float2 (&acc)[4][2], const float4 v, const unsigned o, const float w) {
+  const float2 lo = make_float2(v.x, v.y), hi = make_float2(v.z, v.w);
+  const float2 ww = make_float2(w, w);
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    if (o & (1u << (28 + r))) {
+      if (HAS_PRE) {
+        fma2(acc[r][0], lo, ww);
+        fma2(acc[r][1], hi, ww);
+      } else {
+        add2(acc[r][0], lo);
+        add2(acc[r][1], hi);
+      }
+    }
+  }
+}
+
+// DBG (profiling ablations, LGK_WIN_DEBUG; results are wrong when != 0): 1 = one unpredicated accumulator update per entry
+// instead of the masked four, 2 = no shared-memory / global gathers (the staged words stand in for the data),
+// 4 = the producer issues no TMA loads
+template <bool HAS_PRE, int DBG>
+__global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs a, const __grid_constant__ CUtensorMap map_x) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  // layout: ring [nb][32 rows][128 B] | ring_pre [nb][32] floats | staging [warps][8 pairs][4 groups][16 B] | WinShared
+  const uint32_t ring = umma::smem_u32(smem_raw);
+  float* ring_pre = reinterpret_cast<float*>(smem_raw + size_t(a.nb) * kBlkBytes);
+  unsigned char* stage_raw = reinterpret_cast<unsigned char*>(ring_pre + (HAS_PRE ? a.nb * kBlkRows : 0));
+  WinShared* sh = reinterpret_cast<WinShared*>(stage_raw + kConsumerWarps * 512);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slice = blockIdx.x % a.slices;
+  const int span = blockIdx.x / a.slices, spans = gridDim.x / a.slices;
+  if (span >= spans) return;  // CTAs beyond the last whole group of slices
+  const int64_t c_begin = a.n_chunks * span / spans, c_end = a.n_chunks * (span + 1) / spans;
+  const int n_my = int(c_end - c_begin);
+  const int nb = a.nb;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      umma::mbar_init(&sh->full[s], 1);
+      umma::mbar_init(&sh->empty[s], kConsumerWarps);
+    }
+    umma::mbar_init_fence();
+  }
+  __syncthreads();
+
+  if (warp == kConsumerWarps) {
+    // ===================== producer: keep the ring ahead of the consumers =====================
+    int base_blk = 0, top_blk = 0;  // resident source blocks [base_blk, top_blk); block b lives in slot b % nb
+    int oldest = 0;                 // oldest chunk (local index) whose completion has not been waited for
+    const int64_t n_src_blocks = (a.n_rows + kBlkRows - 1) / kBlkRows;
+    for (int i = 0; i < n_my; ++i) {
+      const int s = i % kStages;
+      // stage s still belongs to chunk i - kStages until every consumer warp has released it
+      while (oldest + kStages <= i) {
+        umma::mbar_wait_relaxed(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
+        ++oldest;
+      }
+      const int lo = __ldg(a.cmin + c_begin + i), hi = __ldg(a.cmax + c_begin + i);
+      int direct = 0, lo_b = INT_MAX, load_from = 0, load_to = 0;
+      if (hi >= lo) {
+        lo_b = lo / kBlkRows;
+        const int hi_b = hi / kBlkRows + 1;
+        if (hi_b - lo_b > nb) {
+          direct = 1;
+          lo_b = INT_MAX;
+        } else {
+          if (lo_b < base_blk) {  // backward jump: drain everything in flight, restart the window
+            while (oldest < i) {
+              umma::mbar_wait_relaxed(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
+              ++oldest;
+            }
+            base_blk = top_blk = lo_b;
+          } else if (lo_b > top_blk) {  // gap (next graph starts further on): nothing below is needed again
+            base_blk = top_blk = lo_b;
+          }
+          const int new_top = max(top_blk, hi_b);
+          // a block may only replace another one of its slot when no chunk in flight still reads from that slot:
+          // every in-flight window [lo'', lo'' + nb) must contain the new blocks
+          int need = oldest;
+          for (int j = oldest; j < i; ++j)
+            if (sh->lo_blk[j % kStages] != INT_MAX && sh->lo_blk[j % kStages] + nb < new_top) need = j + 1;
+          while (oldest < need) {
+            umma::mbar_wait_relaxed(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
+            ++oldest;
+          }
+          load_from = top_blk;
+          load_to = new_top;
+          top_blk = new_top;
+          base_blk = max(base_blk, top_blk - nb);
+        }
+      }
+      if (HAS_PRE) {
+        for (int b = load_from; b < load_to; ++b) {
+          const int64_t r = int64_t(b) * kBlkRows + lane;
+          ring_pre[(b % nb) * kBlkRows + lane] = r < a.n_rows ? __ldg(a.pre + r) : 0.f;
+        }
+      }
+      if (lane == 0) {
+        sh->direct[s] = direct;
+        sh->lo_blk[s] = lo_b;
+      }
+      __syncwarp();
+      if (lane == 0) {
+        const int nload = (DBG & 4) ? 0 : load_to - load_from;
+        if (nload > 0) mbar_arrive_expect_tx(&sh->full[s], uint32_t(nload) * kBlkBytes);
+        else umma::mbar_arrive(&sh->full[s]);
+        for (int b = load_from; b < load_from + nload; ++b)
+          tma_box_2d(ring + uint32_t(b % nb) * kBlkBytes, &map_x, slice * (kSliceBytes / 4), b * kBlkRows, &sh->full[s]);
+      }
+      __syncwarp();
+      (void)n_src_blocks;
+    }
+    return;
+  }
+
+  // ===================== consumers: 4 groups of 8 lanes per warp, one quad per group and chunk =====================
+  static_assert(kConsumerWarps * 4 == kQuadsPerChunk, "one quad per group and chunk");
+  const int gl = lane & 7, grp = lane >> 3;
+  const int group = warp * 4 + grp;
+  const int F4 = a.feat >> 2;
+  const int vec = slice * kSliceF4 + gl;  // this lane's float4 column
+  const bool lane_on = vec < F4;
+  const uint32_t stage_base = umma::smem_u32(stage_raw) + warp * 512 + grp * 16;  // + pair * 64
+  const float4* xv = reinterpret_cast<const float4*>(a.x) + (lane_on ? vec : 0);
+  float4* ov = reinterpret_cast<float4*>(a.out) + vec;
+  const uint32_t lane_off = uint32_t(gl) * 16;
+  const unsigned nb_magic = unsigned((uint64_t(1) << 32) / unsigned(nb)) + 1u;  // blk % nb without a divide (blk < 2^23)
+  const int* qent_i = reinterpret_cast<const int*>(a.qent);
+  float4 bias4 = f4_zero();
+  if (a.bias && lane_on) bias4 = __ldg(reinterpret_cast<const float4*>(a.bias) + vec);
+
+  // software pipeline over the quads of this group: header (start, len) and first batch of entries one quad ahead
+  int start_n = 0, len_n = 0;
+  unsigned wn0 = 0, wn1 = 0;
+  {
+    const int64_t g0 = c_begin * kQuadsPerChunk + group;
+    if (n_my > 0 && g0 < a.n_quads) {
+      start_n = __ldg(a.ptr + g0 * 4);
+      len_n = __ldg(a.qlen + g0);
+      if (gl < len_n) wn0 = unsigned(ld_stream_i32(qent_i + start_n + gl));
+      if (gl + 8 < len_n) wn1 = unsigned(ld_stream_i32(qent_i + start_n + gl + 8));
+    }
+  }
+
+  for (int i = 0; i < n_my; ++i) {
+    const int s = i % kStages;
+    const int64_t g = (c_begin + i) * kQuadsPerChunk + group;
+    const bool quad_on = g < a.n_quads;
+    const int64_t row0 = g * 4;
+    const int start = start_n, len = len_n;
+    unsigned w0 = wn0, w1 = wn1;
+    // next quad's header, and everything the epilogue of this quad reads, go out before the wait
+    {
+      const int64_t gn = g + kQuadsPerChunk;
+      start_n = len_n = 0;
+      if (i + 1 < n_my && gn < a.n_quads) {
+        start_n = __ldg(a.ptr + gn * 4);
+        len_n = __ldg(a.qlen + gn);
+      }
+    }
+    float scale[4], cself[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int64_t row = row0 + r;
+      scale[r] = 1.f;
+      cself[r] = 0.f;
+      if (quad_on && row < a.n_rows) {
+        if (a.mean) scale[r] = 1.f / float(max(__ldg(a.ptr + row + 1) - __ldg(a.ptr + row), 1));
+        if (a.post) scale[r] *= __ldg(a.post + row);
+        if (a.self_mode != LGK_SELF_NONE) {
+          cself[r] = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
+        }
+      }
+    }
+    umma::mbar_wait_relaxed(&sh->full[s], (i / kStages) & 1);
+    const int direct = sh->direct[s];
+    const int maxlen = __reduce_max_sync(0xffffffffu, len);
+    float2 acc[4][2];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) acc[r][0] = acc[r][1] = make_float2(0.f, 0.f);
+    unsigned selfcnt = 0;  // stored (i, i) entries per row, 8 bits each (SELF_REPLACE only)
+
+    for (int b0 = 0; b0 < maxlen; b0 += kBatch) {
+      const unsigned word[2] = {w0, w1};
+      w0 = w1 = 0;
+      if (b0 + kBatch < maxlen) {  // next batch of this quad
+        const int e = b0 + kBatch + gl;
+        if (e < len) w0 = unsigned(ld_stream_i32(qent_i + start + e));
+        if (e + 8 < len) w1 = unsigned(ld_stream_i32(qent_i + start + e + 8));
+      }
+      // ---- stage: every lane resolves two entries (ring address | mask, weight) ----
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const unsigned col = word[h] & kColMask, mask = word[h] >> 28;
+        if (a.self_mode == LGK_SELF_REPLACE) {
+          const unsigned d = col - unsigned(row0);
+          if (d < 4u && ((mask >> d) & 1u)) selfcnt += 1u << (8 * d);
+        }
+        unsigned o;
+        float w = 1.f;
+        if (!direct) {
+          const unsigned blk = col / kBlkRows, slot = blk - __umulhi(blk, nb_magic) * unsigned(nb);
+          const unsigned rib = slot * kBlkRows + (col & (kBlkRows - 1));
+          o = ring + rib * kSliceBytes;
+          if (HAS_PRE) w = ring_pre[rib];
+        } else {
+          o = col;
+          if (HAS_PRE) w = __ldg(a.pre + col);
+        }
+        // pair p = entry / 2, half = entry & 1: [pair][group][half] -> one 16-byte read serves two entries
+        const int ent = gl + 8 * h;
+        sts_u2(stage_base + (ent >> 1) * 64 + (ent & 1) * 8, o | (mask << 28), __float_as_uint(w));
+      }
+      __syncwarp();
+      const int cnt = min(kBatch, maxlen - b0);
+      if (!direct) {
+#pragma unroll 2
+        for (int t = 0; t < cnt; t += 2) {
+          const uint4 st = lds_u4(stage_base + (t >> 1) * 64);
+          float4 v0, v1;
+          if (DBG & 2) {
+            v0 = make_float4(__uint_as_float(st.x), __uint_as_float(st.y), 0.f, 1.f);
+            v1 = make_float4(__uint_as_float(st.z), __uint_as_float(st.w), 0.f, 1.f);
+          } else {
+            v0 = lds_f4((st.x & kColMask) + lane_off);
+            v1 = lds_f4((st.z & kColMask) + lane_off);
+          }
+          if (DBG & 1) {
+            add2(acc[0][0], make_float2(v0.x, v0.y)); add2(acc[0][1], make_float2(v0.z, v0.w));
+            add2(acc[1][0], make_float2(v1.x, v1.y)); add2(acc[1][1], make_float2(v1.z, v1.w));
+          } else {
+            accumulate<HAS_PRE>(acc, v0, st.x, __uint_as_float(st.y));
+            accumulate<HAS_PRE>(acc, v1, st.z, __uint_as_float(st.w));
+          }
+        }
+      } else {
+#pragma unroll 2
+        for (int t = 0; t < cnt; t += 2) {
+          const uint4 st = lds_u4(stage_base + (t >> 1) * 64);
+          const float4 v0 = __ldg(xv + size_t(st.x & kColMask) * F4);
+          const float4 v1 = __ldg(xv + size_t(st.z & kColMask) * F4);
+          accumulate<HAS_PRE>(acc, v0, st.x, __uint_as_float(st.y));
+          accumulate<HAS_PRE>(acc, v1, st.z, __uint_as_float(st.w));
+        }
+      }
+      __syncwarp();
+    }
+    // first batch of the next quad (its header has arrived by now)
+    wn0 = wn1 = 0;
+    if (gl < len_n) wn0 = unsigned(ld_stream_i32(qent_i + start_n + gl));
+    if (gl + 8 < len_n) wn1 = unsigned(ld_stream_i32(qent_i + start_n + gl + 8));
+
+    // ---- epilogue: self term, mean / post scale, bias, store ----
+    if (a.self_mode == LGK_SELF_REPLACE) {
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) selfcnt += __shfl_xor_sync(0xffffffffu, selfcnt, o);
+    }
+    if (quad_on) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int64_t row = row0 + r;
+        if (row < a.n_rows) {
+          float4 res = make_float4(acc[r][0].x, acc[r][0].y, acc[r][1].x, acc[r][1].y);
+          if (a.self_mode != LGK_SELF_NONE) {
+            float c = cself[r];
+            if (a.self_mode == LGK_SELF_REPLACE) c -= float((selfcnt >> (8 * r)) & 0xffu);
+            if (c != 0.f) {
+              if (HAS_PRE) c *= __ldg(a.pre + row);
+              if (lane_on) f4_fma(res, c, __ldg(xv + size_t(row) * F4));
+            }
+          }
+          res.x = fmaf(res.x, scale[r], bias4.x);
+          res.y = fmaf(res.y, scale[r], bias4.y);
+          res.z = fmaf(res.z, scale[r], bias4.z);
+          res.w = fmaf(res.w, scale[r], bias4.w);
+          if (lane_on) st_stream_f4(ov + size_t(row) * F4, res);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) umma::mbar_arrive(&sh->empty[s]);
+  }
+}
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_win() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// x [rows, feat] fp32 row-major as a 2-D tensor; boxes of {32 floats, 32 rows}, no swizzle, zero fill outside
+bool make_row_map(CUtensorMap* map, const float* base, int64_t rows, int64_t feat) {
+  EncodeTiledFn enc = encode_tiled_win();
+  if (!enc) return false;
+  const cuuint64_t dims[2] = {cuuint64_t(feat), cuuint64_t(rows)};
+  const cuuint64_t strides[1] = {cuuint64_t(4 * feat)};
+  const cuuint32_t box[2] = {cuuint32_t(kSliceBytes / 4), cuuint32_t(kBlkRows)};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+int env_int_win(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+}  // namespace
+}  // namespace lgk
+
+using namespace lgk;
+
+extern "C" int64_t lgk_quad_chunks(int64_t n_rows) {
+  const int64_t quads = ceil_div(n_rows, 4);
+  return ceil_div(quads, kQuadsPerChunk);
+}
+
+extern "C" int lgk_quad_build(const int32_t* ptr, const int32_t* idx, int64_t n_rows, int32_t* qlen, uint32_t* qent,
+                              int32_t* cmin, int32_t* cmax, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n_rows >= 0, LGK_ERR_BAD_ARG, "lgk_quad_build: negative size");
+  if (n_rows == 0) return LGK_OK;
+  LGK_REQUIRE(ptr && qlen && cmin && cmax, LGK_ERR_BAD_ARG, "lgk_quad_build: null pointer");
+  LGK_REQUIRE(n_rows <= int64_t(kColMask), LGK_ERR_UNSUPPORTED, "lgk_quad_build: more than 2^28 - 1 rows");
+  const int64_t quads = ceil_div(n_rows, 4);
+  quad_build_kernel<<<unsigned(ceil_div(quads, kQuadsPerChunk)), kQuadsPerChunk, 0, stream>>>(ptr, idx, n_rows, quads, qlen, qent,
+                                                                                              cmin, cmax);
+  LGK_CHECK_LAUNCH("quad_build_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const uint32_t* qent, const int32_t* cmin,
+                                const int32_t* cmax, const float* pre, const float* post, const float* selfw, float self_fill,
+                                int self_mode, const void* x, const float* bias, void* out, int64_t n_rows, int64_t feat,
+                                int reduce, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n_rows >= 0 && feat >= 0, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: negative size");
+  if (n_rows == 0 || feat == 0) return LGK_OK;
+  LGK_REQUIRE(ptr && qlen && qent && cmin && cmax && x && out, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: null pointer");
+  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: fp32 features only");
+  LGK_REQUIRE(reduce == LGK_SUM || reduce == LGK_MEAN, LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: sum or mean only");
+  LGK_REQUIRE(reduce == LGK_SUM || self_mode == LGK_SELF_NONE, LGK_ERR_BAD_ARG,
+              "lgk_spmm_blocked: self-loop handling is defined for the sum reduction only");
+  LGK_REQUIRE(self_mode >= LGK_SELF_NONE && self_mode <= LGK_SELF_ADD, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: bad self_mode");
+  LGK_REQUIRE(feat % 4 == 0 && feat < (1 << 20), LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: feat must be a multiple of 4");
+  LGK_REQUIRE(n_rows <= int64_t(kColMask), LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: more than 2^28 - 1 rows");
+  LGK_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0,
+              LGK_ERR_BAD_ARG, "lgk_spmm_blocked: x, out and bias must be 16-byte aligned");
+  LGK_REQUIRE(x != out, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: in-place aggregation is not possible");
+
+  WinArgs a{};
+  a.ptr = ptr; a.qlen = qlen; a.qent = qent; a.cmin = cmin; a.cmax = cmax;
+  a.pre = pre; a.post = post; a.selfw = selfw; a.bias = bias;
+  a.x = static_cast<const float*>(x);
+  a.out = static_cast<float*>(out);
+  a.self_fill = self_fill; a.self_mode = self_mode; a.mean = reduce == LGK_MEAN;
+  a.n_rows = n_rows;
+  a.n_quads = ceil_div(n_rows, 4);
+  a.n_chunks = ceil_div(a.n_quads, kQuadsPerChunk);
+  a.feat = int(feat);
+  a.slices = int(ceil_div(feat * 4, kSliceBytes));
+  const int fixed = kConsumerWarps * 512 + int(sizeof(WinShared)) + 128;
+  const int per_blk = kBlkBytes + (pre ? kBlkRows * 4 : 0);
+  static const int nb_cap = env_int_win("LGK_WIN_BLOCKS", 1 << 30);  // tuning / test knob: fewer ring blocks
+  a.nb = std::min((kSmemMax - fixed) / per_blk, nb_cap);
+  LGK_REQUIRE(a.nb >= 2, LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: no room for the ring");
+  const int smem = a.nb * per_blk + fixed;
+
+  CUtensorMap map_x;
+  LGK_REQUIRE(make_row_map(&map_x, a.x, n_rows, feat), LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: cannot encode the tensor map");
+
+  // one CTA per SM; a group of `slices` CTAs shares a span of chunks
+  const int spans = int(std::max<int64_t>(1, std::min<int64_t>(kNumSMs / std::max(1, std::min(a.slices, kNumSMs)), a.n_chunks)));
+  const unsigned grid = unsigned(spans * a.slices);
+  // more slices than SMs (feat > 4736): every slice still needs its CTA; they queue
+  int dev = 0;
+  cudaGetDevice(&dev);
+  static bool configured[64][2] = {};
+  const int hp = pre ? 1 : 0;
+  static const int dbg = env_int_win("LGK_WIN_DEBUG", 0);
+  void (*kern)(const WinArgs, const CUtensorMap) = nullptr;
+#define LGK_WIN_PICK(D) case D: kern = hp ? spmm_win_kernel<true, D> : spmm_win_kernel<false, D>; break;
+  switch (dbg) {
+    LGK_WIN_PICK(0) LGK_WIN_PICK(1) LGK_WIN_PICK(2) LGK_WIN_PICK(3) LGK_WIN_PICK(4) LGK_WIN_PICK(7)
+    default: LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "LGK_WIN_DEBUG=%d is not instantiated", dbg);
+  }
+#undef LGK_WIN_PICK
+  if (dev < 64 && !configured[dev][hp]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax);
+    if (e != cudaSuccess) {
+      set_error("spmm_win_kernel: cannot reserve %d bytes of shared memory: %s", kSmemMax, cudaGetErrorString(e));
+      return LGK_ERR_LAUNCH;
+    }
+    configured[dev][hp] = true;
+  }
+  kern<<<grid, kThreadsWin, smem, stream>>>(a, map_x);
+  LGK_CHECK_LAUNCH("spmm_win_kernel");
+  return LGK_OK;
+}

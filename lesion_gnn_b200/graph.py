@@ -22,7 +22,7 @@ class CSRGraph:
     """rowptr/col/perm: CSR by destination, entries ordered by (dst, src, original edge id).
     colptr/row/csr2csc: CSC by source, entries ordered by CSR slot.  value: edge weights in CSR order."""
 
-    __slots__ = ("num_nodes", "num_edges", "rowptr", "col", "perm", "colptr", "row", "csr2csc", "value", "_norm", "_ready")
+    __slots__ = ("num_nodes", "num_edges", "rowptr", "col", "perm", "colptr", "row", "csr2csc", "value", "_norm", "_ready", "_quads")
 
     def __init__(self, num_nodes, num_edges, rowptr, col, perm, colptr=None, row=None, csr2csc=None, value=None):
         self.num_nodes, self.num_edges = int(num_nodes), int(num_edges)
@@ -30,6 +30,7 @@ class CSRGraph:
         self.colptr, self.row, self.csr2csc = colptr, row, csr2csc
         self.value = value
         self._norm = {}
+        self._quads = {}  # row-blocked forms of the CSR ("csr") / CSC ("csc"), built on first use (quads())
         self._ready = None  # event recorded on the stream that built the graph (from_edge_index(..., stream=))
 
     @staticmethod
@@ -77,6 +78,7 @@ class CSRGraph:
     def with_value(self, edge_weight: Optional[Tensor]) -> "CSRGraph":
         """same structure, different edge weights (shares the index tensors)"""
         g = CSRGraph(self.num_nodes, self.num_edges, self.rowptr, self.col, self.perm, self.colptr, self.row, self.csr2csc)
+        g._quads = self._quads  # same structure
         g.value = None if edge_weight is None else self.permute_edge_values(edge_weight)
         return g
 
@@ -86,6 +88,22 @@ class CSRGraph:
         if key not in self._norm:
             self._norm[key] = ops.gcn_norm(self.rowptr, self.col, self.value, 2.0 if improved else 1.0, add_self_loops)
         return self._norm[key]
+
+    def quads(self, which: str = "csr") -> "ops.Quads":
+        """row-blocked form of the CSR (forward aggregation) or the CSC (backward) for the windowed aggregation kernel
+        (ops.spmm(..., quads=)); built once per graph and direction, shared by every layer"""
+        q = self._quads.get(which)
+        if q is None:
+            if which == "csr":
+                q = ops.quad_build(self.rowptr, self.col)
+            elif which == "csc":
+                if self.colptr is None:
+                    raise RuntimeError("this CSRGraph was built without the CSC transpose index")
+                q = ops.quad_build(self.colptr, self.row)
+            else:
+                raise ValueError(which)
+            self._quads[which] = q
+        return q
 
     def to_edge_index(self) -> Tensor:
         """[2, E] int64 in CSR order (row 0 = src, row 1 = dst)"""

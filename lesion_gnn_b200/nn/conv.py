@@ -30,6 +30,30 @@ def _next_seed() -> int:
     return (torch.initial_seed() * 0x9E3779B1 + _seed_counter[0] * 0x85EBCA6B) & 0xFFFFFFFFFFFFFFFF
 
 
+# A captured CUDA graph replays the launch arguments it recorded, so a host seed alone would freeze the attention-dropout
+# mask of every replay.  While a clock is installed (train.TrainStep installs the optimiser's device step counter), the
+# kernels mix its current value into the seed at run time: forward and backward of one step agree, the next step differs.
+_DROPOUT_CLOCK = [None]
+
+
+class dropout_clock:
+    """context manager: `with dropout_clock(step_counter_int64_device_tensor): ...`"""
+
+    def __init__(self, counter: Optional[Tensor]):
+        if counter is not None and (counter.dtype != torch.int64 or not counter.is_cuda or counter.numel() < 1):
+            raise TypeError("the dropout clock is a CUDA int64 tensor")
+        self.counter = counter
+
+    def __enter__(self):
+        self._old = _DROPOUT_CLOCK[0]
+        _DROPOUT_CLOCK[0] = self.counter
+        return self
+
+    def __exit__(self, *exc):
+        _DROPOUT_CLOCK[0] = self._old
+        return False
+
+
 def _glorot(t: Tensor) -> None:
     a = math.sqrt(6.0 / (t.size(-2) + t.size(-1)))
     with torch.no_grad():
@@ -128,7 +152,8 @@ class GATConv(nn.Module):
         seed = _next_seed() if p > 0 else 0
         fused_bias = self.bias if self.concat else None
         out = F.gat_attention(h, self.att_src, self.att_dst, fused_bias, g, self.heads, self.out_channels,
-                              self.negative_slope, self.add_self_loops, p, seed, fused_elu=self.fused_elu)
+                              self.negative_slope, self.add_self_loops, p, seed, fused_elu=self.fused_elu,
+                              seed_dev=_DROPOUT_CLOCK[0] if p > 0 else None)
         if not self.concat:
             out = out.view(-1, self.heads, self.out_channels).mean(dim=1)
             if self.bias is not None:

@@ -131,7 +131,7 @@ class _Aggregate(torch.autograd.Function):
             deg = (g.rowptr[1:] - g.rowptr[:-1]).clamp(min=1).float()
             ctx.inv_deg = deg.reciprocal()
         return ops.spmm(g.rowptr, g.col, x, reduce, ew=ew, pre=pre, post=post, selfw=selfw, self_fill=self_fill,
-                        self_mode=self_mode, bias=bias)
+                        self_mode=self_mode, bias=bias, quads=g.quads("csr") if ops.blocked_eligible(x, reduce, ew) else None)
 
     @staticmethod
     def backward(ctx, dout):
@@ -144,11 +144,13 @@ class _Aggregate(torch.autograd.Function):
                 dx = ops.spmm_max_bwd(g.colptr, g.row, g.csr2csc, ctx.arg, dout)
             elif ctx.reduce == "mean":
                 # d x_j = sum_{i : j -> i} dout_i / max(deg_i, 1)
-                dx = ops.spmm(g.colptr, g.row, dout, "sum", pre=ctx.inv_deg)
+                dx = ops.spmm(g.colptr, g.row, dout, "sum", pre=ctx.inv_deg,
+                              quads=g.quads("csc") if ops.blocked_eligible(dout, "sum", None) else None)
             else:
                 # transpose: scale on the gathered side <-> scale on the output side
                 dx = ops.spmm(g.colptr, g.row, dout, "sum", emap=g.csr2csc if ctx.ew is not None else None, ew=ctx.ew,
-                              pre=ctx.post, post=ctx.pre, selfw=ctx.selfw, self_fill=ctx.self_fill, self_mode=ctx.self_mode)
+                              pre=ctx.post, post=ctx.pre, selfw=ctx.selfw, self_fill=ctx.self_fill, self_mode=ctx.self_mode,
+                              quads=g.quads("csc") if ops.blocked_eligible(dout, "sum", ctx.ew) else None)
         if ctx.has_bias and ctx.needs_input_grad[1]:
             d32 = dout.float() if dout.dtype != torch.float32 else dout
             gb = _bucket(ctx.bias_ref)
@@ -173,13 +175,14 @@ class _GatAttention(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, h, att_src, att_dst, bias, g: CSRGraph, heads, chan, negative_slope, add_self_loops, dropout_p, seed,
-                fused_elu=False):
+                fused_elu=False, seed_dev=None):
         h = h.contiguous()
         a_s = att_src.detach().reshape(-1).contiguous()
         a_d = att_dst.detach().reshape(-1).contiguous()
         a_src, a_dst = ops.gat_alpha(h, a_s, a_d, heads, chan)
         res = ops.gat_fwd(g.rowptr, g.col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p,
-                          seed, with_elu=fused_elu)
+                          seed, with_elu=fused_elu, seed_dev=seed_dev)
+        ctx.seed_dev = seed_dev
         out, rowmax, rowsum = res[:3]
         y = res[3] if fused_elu else h.new_empty(0)
         ctx.fused_elu = fused_elu
@@ -199,7 +202,8 @@ class _GatAttention(torch.autograd.Function):
         dout = dout.contiguous()
         p_src, p_dst, p_bias = ctx.refs
         res = ops.gat_bwd(g, h, a_src, a_dst, rowmax, rowsum, out, bias if ctx.has_bias else None,
-                          a_s, a_d, dout, heads, chan, slope, add_self, p, seed, through_elu=ctx.fused_elu)
+                          a_s, a_d, dout, heads, chan, slope, add_self, p, seed, through_elu=ctx.fused_elu,
+                          seed_dev=ctx.seed_dev)
         dh, da_src, da_dst = res[:3]
         if ctx.fused_elu:
             dout = res[3]  # gradient w.r.t. the pre-activation output (formed by the dst-side kernel), for db below
@@ -218,14 +222,15 @@ class _GatAttention(torch.autograd.Function):
                 _on_side(lambda: ops.colsum(d32, out=gb), d32, key=gb.data_ptr())
             else:
                 dbias = ops.colsum(d32)
-        return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None, None)
+        return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None, None, None)
 
 
 def gat_attention(h, att_src, att_dst, bias, g, heads, chan, negative_slope=0.2, add_self_loops=True, dropout_p=0.0,
-                  seed=0, fused_elu=False) -> Tensor:
-    """fused_elu: return elu(attention output + bias) from the same launch (the bias must be the fused one)"""
+                  seed=0, fused_elu=False, seed_dev: Optional[Tensor] = None) -> Tensor:
+    """fused_elu: return elu(attention output + bias) from the same launch (the bias must be the fused one).
+    seed_dev: int64 device counter mixed into the dropout seed by the kernels (see conv.dropout_clock)"""
     return _GatAttention.apply(h, att_src, att_dst, bias, g, int(heads), int(chan), float(negative_slope),
-                               bool(add_self_loops), float(dropout_p), int(seed), bool(fused_elu))
+                               bool(add_self_loops), float(dropout_p), int(seed), bool(fused_elu), seed_dev)
 
 
 class _Linear(torch.autograd.Function):

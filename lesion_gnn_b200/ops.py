@@ -6,6 +6,7 @@ Nothing here synchronises, so all of it can be captured into a CUDA graph.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -149,13 +150,55 @@ def gaussian_distance(pos: Tensor, edge_index: Tensor, sigma: float) -> Tensor:
 # -------------------------------------------------------------------------------------------- aggregation
 
 
+class Quads:
+    """Row-blocked form of a CSR / CSC (lgk_quad_build): merged neighbour lists of four consecutive rows with
+    membership masks, plus the source-id range of every chunk of 64 quads.  Index work, built once per batch."""
+
+    __slots__ = ("qlen", "qent", "cmin", "cmax")
+
+    def __init__(self, qlen, qent, cmin, cmax):
+        self.qlen, self.qent, self.cmin, self.cmax = qlen, qent, cmin, cmax
+
+
+def quad_build(ptr: Tensor, idx: Tensor) -> Quads:
+    L = _lib.lib()
+    n = ptr.numel() - 1
+    dev = ptr.device
+    i32 = dict(dtype=torch.int32, device=dev)
+    nq = (n + 3) // 4
+    nc = int(L.query("lgk_quad_chunks", n))
+    q = Quads(torch.empty(max(nq, 1), **i32), torch.empty(max(idx.numel(), 1), **i32), torch.empty(max(nc, 1), **i32),
+              torch.empty(max(nc, 1), **i32))
+    L.call("lgk_quad_build", _chk(ptr, torch.int32, "ptr"), _chk(idx, torch.int32, "idx"), n, q.qlen.data_ptr(),
+           q.qent.data_ptr(), q.cmin.data_ptr(), q.cmax.data_ptr(), _stream())
+    return q
+
+
+# rows x features from which the windowed, row-blocked aggregation kernel takes over (tuning / test knob)
+_WIN_MIN_ELEMS = int(os.environ.get("LGK_WIN_MIN_ELEMS", str(1 << 23)))
+
+
+def blocked_eligible(x: Tensor, reduce: str, ew) -> bool:
+    return (ew is None and _REDUCE[reduce] in (SUM, MEAN) and x.dtype == torch.float32 and x.dim() == 2
+            and x.size(1) % 4 == 0 and x.numel() >= _WIN_MIN_ELEMS and x.size(0) < (1 << 28))
+
+
 def spmm(ptr: Tensor, idx: Tensor, x: Tensor, reduce: str = "sum", *, emap: Optional[Tensor] = None,
          ew: Optional[Tensor] = None, pre: Optional[Tensor] = None, post: Optional[Tensor] = None,
          selfw: Optional[Tensor] = None, self_fill: float = 1.0, self_mode: int = SELF_NONE,
-         bias: Optional[Tensor] = None, want_arg: bool = False):
+         bias: Optional[Tensor] = None, want_arg: bool = False, quads: Optional[Quads] = None):
+    """quads: the row-blocked form of (ptr, idx); when given (and the call is eligible: see blocked_eligible) the
+    windowed kernel lgk_spmm_blocked runs instead of lgk_spmm -- same result up to fp32 summation order"""
     L = _lib.lib()
     n, f = x.shape
     out = torch.empty_like(x)
+    if quads is not None and not want_arg and blocked_eligible(x, reduce, ew):
+        f32 = torch.float32
+        L.call("lgk_spmm_blocked", _chk(ptr, torch.int32, "ptr"), _chk(quads.qlen, torch.int32), _chk(quads.qent, torch.int32),
+               _chk(quads.cmin, torch.int32), _chk(quads.cmax, torch.int32), _chk(pre, f32, "pre"), _chk(post, f32, "post"),
+               _chk(selfw, f32, "selfw"), float(self_fill), int(self_mode), _chk(x, None, "x"), _chk(bias, f32, "bias"),
+               _chk(out), n, f, _REDUCE[reduce], _dt(x), _stream())
+        return out
     arg = torch.empty(n, f, dtype=torch.int32, device=x.device) if (want_arg and _REDUCE[reduce] == MAX) else None
     f32 = torch.float32
     L.call("lgk_spmm", _chk(ptr, torch.int32, "ptr"), _chk(idx, torch.int32, "idx"), _chk(emap, torch.int32, "emap"),
@@ -197,8 +240,8 @@ def gat_alpha(h: Tensor, att_src: Tensor, att_dst: Tensor, heads: int, chan: int
 
 
 def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p=0.0, seed=0,
-            with_elu=False):
-    """-> out, rowmax, rowsum [, elu(out)]"""
+            with_elu=False, seed_dev: Optional[Tensor] = None):
+    """-> out, rowmax, rowsum [, elu(out)].  seed_dev: int64 device counter mixed into the dropout seed at run time"""
     L = _lib.lib()
     n = h.size(0)
     out = torch.empty_like(h)
@@ -208,16 +251,18 @@ def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add
         y = torch.empty_like(h)
         L.call("lgk_gat_fwd_elu", _chk(rowptr, torch.int32), _chk(col, torch.int32), _chk(h, None, "h"), _chk(a_src, torch.float32),
                _chk(a_dst, torch.float32), _chk(bias, torch.float32, "bias"), _chk(out), _chk(y), _chk(rowmax), _chk(rowsum), n,
-               heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), _dt(h), _stream())
+               heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), _chk(seed_dev, torch.int64, "seed_dev"),
+               _dt(h), _stream())
         return out, rowmax, rowsum, y
     L.call("lgk_gat_fwd", _chk(rowptr, torch.int32), _chk(col, torch.int32), _chk(h, None, "h"), _chk(a_src, torch.float32),
            _chk(a_dst, torch.float32), _chk(bias, torch.float32, "bias"), _chk(out), _chk(rowmax), _chk(rowsum), n, heads, chan,
-           float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), _dt(h), _stream())
+           float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), _chk(seed_dev, torch.int64, "seed_dev"),
+           _dt(h), _stream())
     return out, rowmax, rowsum
 
 
 def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst, dout, heads, chan, negative_slope,
-            add_self_loops, dropout_p=0.0, seed=0, through_elu=False):
+            add_self_loops, dropout_p=0.0, seed=0, through_elu=False, seed_dev: Optional[Tensor] = None):
     """-> dh, da_src [N,H], da_dst [N,H] (the attention-vector gradients follow from gat_datt).
     through_elu: `dout` is the gradient of elu(out) (layer run with gat_fwd(with_elu=True)); the gradient of out is
     formed by the dst-side kernel and returned as a fourth value"""
@@ -229,19 +274,20 @@ def gat_bwd(graph, h, a_src, a_dst, rowmax, rowsum, out, bias, att_src, att_dst,
     da_src = torch.empty(n, heads, **f32)
     dh = torch.empty_like(h)
     dt, st = _dt(h), _stream()
+    sd = _chk(seed_dev, torch.int64, "seed_dev")
     if through_elu:
         dy, dout = dout, torch.empty_like(h)
         L.call("lgk_gat_bwd_dst_elu", _chk(graph.rowptr), _chk(graph.col), _chk(h), _chk(a_src), _chk(a_dst), _chk(rowmax),
                _chk(rowsum), _chk(out, None, "out"), _chk(bias, torch.float32), _chk(dy, h.dtype, "dy"), _chk(dout), _chk(stats),
-               _chk(da_dst), n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), dt, st)
+               _chk(da_dst), n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), sd, dt, st)
     else:
         L.call("lgk_gat_bwd_dst", _chk(graph.rowptr), _chk(graph.col), _chk(h), _chk(a_src), _chk(a_dst), _chk(rowmax),
                _chk(rowsum), _chk(out, None, "out"), _chk(bias, torch.float32), _chk(dout, h.dtype, "dout"), _chk(stats),
-               _chk(da_dst), n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), dt, st)
+               _chk(da_dst), n, heads, chan, float(negative_slope), int(add_self_loops), float(dropout_p), int(seed), sd, dt, st)
     L.call("lgk_gat_bwd_src", _chk(graph.colptr), _chk(graph.row), _chk(graph.csr2csc), _chk(h), _chk(a_src), _chk(a_dst),
            _chk(rowmax), _chk(rowsum), _chk(stats), _chk(da_dst), _chk(att_src, torch.float32), _chk(att_dst, torch.float32),
            _chk(dout), _chk(dh), _chk(da_src), n, heads, chan, float(negative_slope), int(add_self_loops),
-           float(dropout_p), int(seed), dt, st)
+           float(dropout_p), int(seed), sd, dt, st)
     return (dh, da_src, da_dst, dout) if through_elu else (dh, da_src, da_dst)
 
 

@@ -21,6 +21,7 @@ from torch import Tensor
 from . import ops
 from .data import HostBatch
 from .graph import CSRGraph
+from .nn.conv import dropout_clock
 from .nn.functional import direct_param_grads, side_stream
 from .nn.pool import Segments
 
@@ -206,7 +207,8 @@ class TrainStep:
         # the backward kernels add weight / bias / attention gradients straight into the flat bucket (no per-parameter
         # autograd `add` launches); the bucket was just zeroed, so this equals plain accumulation
         # ... and run on a side stream, overlapping the main backward chain; joined before the optimiser reads them
-        with direct_param_grads(), side_stream(self._side):
+        # ... attention dropout is keyed on the optimiser's device-side step counter, so graph replays draw fresh masks
+        with direct_param_grads(), side_stream(self._side), dropout_clock(getattr(self.opt, "step_dev", None)):
             loss = forward_backward(self.model, db, self.loss_type, self.num_classes, self._build)
         if self.world_size == 1:
             self.opt.step()

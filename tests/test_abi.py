@@ -48,7 +48,7 @@ def test_bad_arguments_return_status_without_a_device(liblgk):
     assert rc == -2 and "k must be" in L.last_error()
     assert L.query("lgk_csr_workspace_bytes", 100, 1000) >= 16 * 1000
     with pytest.raises(RuntimeError, match="lgk_gat_fwd failed"):
-        L.call("lgk_gat_fwd", None, None, None, None, None, None, None, None, None, 4, 2, 3, 0.2, 1, 0.0, 0, 0, None)
+        L.call("lgk_gat_fwd", None, None, None, None, None, None, None, None, None, 4, 2, 3, 0.2, 1, 0.0, 0, None, 0, None)
 
 
 def test_product_refuses_cpu_tensors(liblgk):

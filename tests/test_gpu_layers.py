@@ -6,14 +6,16 @@ import pytest
 import torch
 
 from oracle import pyg_semantics as O
-from tests.util import TOL_F32, assert_close, random_graph
+from tests.util import TOL_F32, assert_close, assert_parity, random_graph, row_rel_err
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden", "layers.pt")
 
 
-def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what="", tol_grad=None):
-    """same weights, same inputs; compares output, dx and every parameter gradient"""
+def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what="", tol_grad=None, fp32_floor=False):
+    """same weights, same inputs; compares output, dx and every parameter gradient, whole-tensor and per-row.
+    fp32_floor: the bound is max(tol, 4 x the error of the oracle itself run in fp32 on the CPU) -- tests/util.assert_parity"""
+    import copy
     layer_gpu.load_state_dict({k: v.float() for k, v in layer_ref.state_dict().items()})
     layer_gpu = layer_gpu.to(dev)
     xr = x.clone().requires_grad_(True)
@@ -21,12 +23,28 @@ def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what="", tol_grad=
     gen = torch.Generator().manual_seed(17)
     dy = torch.randn(want.shape, generator=gen, dtype=torch.float64)
     want.backward(dy)
+    want32 = x32 = grads32 = None
+    if fp32_floor:
+        ref32 = copy.deepcopy(layer_ref).float()
+        ref32.zero_grad()
+        x32 = x.float().requires_grad_(True)
+        want32 = ref32(x32, *[a if a.dtype == torch.int64 else a.float() for a in args_ref])
+        want32.backward(dy.float())
+        grads32 = {k: p.grad for k, p in ref32.named_parameters()}
     xg = x.float().to(dev).requires_grad_(True)
     args_gpu = [a.to(dev) if a.dtype == torch.int64 else a.float().to(dev) for a in args_ref]
     got = layer_gpu(xg, *args_gpu)
     got.backward(dy.float().to(dev))
-    assert_close(got, want, tol, what + " out")
-    assert_close(xg.grad, xr.grad, tol_grad or tol, what + " dx")
+
+    def check(a, b, b32, t, name):
+        if fp32_floor:
+            assert_parity(a, b, b32, name, t)
+        else:
+            assert_close(a, b, t, name)
+            assert row_rel_err(a, b) <= 10 * t, f"{name}: per-row error {row_rel_err(a, b):.3e}"
+
+    check(got, want, want32, tol, what + " out")
+    check(xg.grad, xr.grad, None if x32 is None else x32.grad, tol_grad or tol, what + " dx")
     ref_grads = {k: p.grad for k, p in layer_ref.named_parameters()}
     scale = max(float(g.abs().max()) for g in ref_grads.values() if g is not None)
     for k, p in layer_gpu.named_parameters():
@@ -36,7 +54,7 @@ def _run(layer_gpu, layer_ref, x, args_ref, dev, tol=TOL_F32, what="", tol_grad=
                 # analytically zero gradient (a bias in front of BatchNorm): only rounding noise on either side
                 assert float(p.grad.abs().max()) < 1e-4 * scale, k
                 continue
-            assert_close(p.grad.view_as(ref_grads[k]), ref_grads[k], tol_grad or tol, f"{what} d{k}")
+            check(p.grad.view_as(ref_grads[k]), ref_grads[k], None if grads32 is None else grads32[k], tol_grad or tol, f"{what} d{k}")
 
 
 @pytest.mark.parametrize("n,k,m", [(1, 1, 1), (7, 3, 5), (300, 16, 64), (1000, 64, 64), (513, 1025, 64), (2000, 128, 128),
@@ -162,6 +180,36 @@ def test_gat_attention_dropout_is_consistent_and_unbiased(dev):
     assert abs(fd - an) <= 2e-2 * max(abs(fd), abs(an), 1.0), (fd, an)
 
 
+def test_gat_dropout_clock_changes_the_mask_and_keeps_fwd_bwd_consistent(dev):
+    """the device-side counter mixed into the seed (a captured graph freezes the host seed): same counter ->
+    same mask, next counter -> another mask, and the backward of a step uses the forward's mask"""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200.nn import functional as F
+    n, H, C = 1500, 4, 16
+    ei = random_graph(n, 12000, 4)
+    g = lg.CSRGraph.from_edge_index(ei.to(dev), n)
+    h = torch.randn(n, H * C, device=dev)
+    att = torch.randn(1, H, C, device=dev)
+    clock = torch.tensor([7, 0], dtype=torch.int64, device=dev)
+    kw = dict(dropout_p=0.35, seed=5, seed_dev=clock)
+    a = F.gat_attention(h, att, att, None, g, H, C, **kw)
+    b = F.gat_attention(h, att, att, None, g, H, C, **kw)
+    assert torch.equal(a, b)
+    clock[0] += 1
+    c = F.gat_attention(h, att, att, None, g, H, C, **kw)
+    assert not torch.equal(a, c)
+    assert not torch.equal(c, F.gat_attention(h, att, att, None, g, H, C, dropout_p=0.35, seed=5))
+    r = torch.randn_like(a)
+    hh = h.clone().requires_grad_(True)
+    F.gat_attention(hh, att, att, None, g, H, C, fused_elu=False, **kw).mul(r).sum().backward()
+    d = torch.randn_like(h)
+    eps, hd = 1e-2, h.double()
+    fp = F.gat_attention((hd + eps * d).float(), att, att, None, g, H, C, **kw).double().mul(r).sum()
+    fm = F.gat_attention((hd - eps * d).float(), att, att, None, g, H, C, **kw).double().mul(r).sum()
+    fd, an = float((fp - fm) / (2 * eps)), float((hh.grad.double() * d).sum())
+    assert abs(fd - an) <= 2e-2 * max(abs(fd), abs(an), 1.0), (fd, an)
+
+
 @pytest.mark.parametrize("fin,fout", [(16, 64), (64, 64), (128, 128), (7, 5)])
 @pytest.mark.parametrize("weighted", [False, True])
 def test_gcnconv(dev, fin, fout, weighted):
@@ -217,7 +265,7 @@ def test_ginconv(dev, norm):
     torch.manual_seed(7)
     ref = O.GINConv(O.MLP([64, 64, 64], act="ELU", dropout=0.0, norm=norm)).double()
     got = lg.nn.GINConv(lg.nn.MLP([64, 64, 64], act="ELU", dropout=0.0, norm=norm))
-    _run(got, ref, x, [ei], dev, tol=2e-5 if norm else TOL_F32, what=f"GIN norm={norm}")
+    _run(got, ref, x, [ei], dev, tol=TOL_F32, what=f"GIN norm={norm}", fp32_floor=True)
 
 
 def test_state_dict_keys_match_pyg_names():
