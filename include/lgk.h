@@ -293,6 +293,20 @@ LGK_API int lgk_adam_step(float* param, float* grad, float* exp_avg, float* exp_
 LGK_API int lgk_clamped_regression_loss(const float* logits, const int64_t* y, int64_t n, float lo, float hi, int kind,
                                 float grad_scale, float* loss_out, float* dlogits, void* stream);
 
+/* torch.optim.SGD over one flat fp32 buffer (reference models/base.py:167-168: lr and weight_decay; momentum /
+ * nesterov with dampening 0 are supported through a zero-initialised momentum_buf, NULL when momentum == 0):
+ * g = grad_scale * grad + weight_decay * p; [b = momentum * b + g; g = nesterov ? g + momentum * b : b;] p -= lr * g.
+ * zero_grad != 0 clears every gradient once consumed.                                                            */
+LGK_API int lgk_sgd_step(float* param, float* grad, float* momentum_buf, int64_t n, float lr, float momentum,
+                 float weight_decay, int nesterov, float grad_scale, int zero_grad, void* stream);
+
+/* nn.CrossEntropyLoss(weight=class_weights) of the reference's classification mode (models/base.py:93-94,196-199),
+ * forward and gradient in one launch: loss = sum_i w[y_i] * (-log softmax(logits[i])[y_i]) / sum_i w[y_i]
+ * (class_weight may be NULL: w = 1).  logits [n, num_classes] fp32 row-major, y int64 [n]; targets outside
+ * [0, num_classes) contribute nothing.  dlogits (may be NULL) = grad_scale * d loss / d logits.  One CTA.        */
+LGK_API int lgk_cross_entropy_loss(const float* logits, const int64_t* y, const float* class_weight, int64_t n,
+                           int64_t num_classes, float grad_scale, float* loss_out, float* dlogits, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -188,3 +188,91 @@ extern "C" int lgk_clamped_regression_loss(const float* logits, const int64_t* y
   LGK_CHECK_LAUNCH("clamped_loss_kernel");
   return LGK_OK;
 }
+
+// ---- SGD (torch.optim.SGD; reference models/base.py:167-168 uses lr and weight_decay only) ---------------------------
+namespace lgk {
+namespace {
+__global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ buf, int64_t n,
+                                                  float lr, float momentum, float wd, int nesterov, float gscale, int zero_grad) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float param = p[i];
+  float grad = fmaf(wd, param, g[i] * gscale);  // L2 penalty folded into the gradient, as torch.optim.SGD
+  if (zero_grad) g[i] = 0.f;
+  if (buf) {  // momentum buffer, zero-initialised: b = mu b + g reproduces torch's first step (b = g) with dampening 0
+    const float b = fmaf(momentum, buf[i], grad);
+    buf[i] = b;
+    grad = nesterov ? fmaf(momentum, b, grad) : b;
+  }
+  p[i] = param - lr * grad;
+}
+
+// ---- (weighted) cross-entropy, forward + gradient (nn.CrossEntropyLoss(weight=class_weights), models/base.py:93-94) --
+// One CTA: thread per graph (strided).  loss = sum_i w[y_i] nll_i / sum_i w[y_i]; fixed reduction tree: deterministic.
+__global__ void __launch_bounds__(1024) cross_entropy_kernel(const float* __restrict__ logits, const int64_t* __restrict__ y,
+                                                             const float* __restrict__ weight, int64_t n, int C, float grad_scale,
+                                                             float* __restrict__ loss_out, float* __restrict__ dlogits) {
+  __shared__ float red_l[1024], red_w[1024];
+  float sl = 0.f, sw = 0.f;
+  for (int64_t i = threadIdx.x; i < n; i += 1024) {
+    const float* row = logits + i * C;
+    float m = -INFINITY;
+    for (int c = 0; c < C; ++c) m = fmaxf(m, row[c]);
+    float s = 0.f;
+    for (int c = 0; c < C; ++c) s += expf(row[c] - m);
+    const int64_t t = y[i];
+    const bool ok = t >= 0 && t < C;  // ignore_index-style targets contribute nothing
+    const float w = ok ? (weight ? weight[t] : 1.f) : 0.f;
+    if (ok) sl += w * (logf(s) + m - row[t]);
+    sw += w;
+  }
+  red_l[threadIdx.x] = sl;
+  red_w[threadIdx.x] = sw;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (threadIdx.x < o) { red_l[threadIdx.x] += red_l[threadIdx.x + o]; red_w[threadIdx.x] += red_w[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  const float wsum = red_w[0];
+  if (threadIdx.x == 0) loss_out[0] = red_l[0] / wsum;
+  if (!dlogits) return;
+  const float k = grad_scale / wsum;
+  for (int64_t i = threadIdx.x; i < n; i += 1024) {
+    const float* row = logits + i * C;
+    float m = -INFINITY;
+    for (int c = 0; c < C; ++c) m = fmaxf(m, row[c]);
+    float s = 0.f;
+    for (int c = 0; c < C; ++c) s += expf(row[c] - m);
+    const int64_t t = y[i];
+    const bool ok = t >= 0 && t < C;
+    const float w = ok ? (weight ? weight[t] : 1.f) * k : 0.f;
+    const float inv = 1.f / s;
+    for (int c = 0; c < C; ++c) dlogits[i * C + c] = w * (expf(row[c] - m) * inv - (c == t ? 1.f : 0.f));
+  }
+}
+}  // namespace
+}  // namespace lgk
+
+extern "C" int lgk_sgd_step(float* param, float* grad, float* momentum_buf, int64_t n, float lr, float momentum,
+                            float weight_decay, int nesterov, float grad_scale, int zero_grad, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0, LGK_ERR_BAD_ARG, "lgk_sgd_step: negative size");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(param && grad, LGK_ERR_BAD_ARG, "lgk_sgd_step: null pointer");
+  LGK_REQUIRE(momentum == 0.f || momentum_buf, LGK_ERR_BAD_ARG, "lgk_sgd_step: momentum needs its buffer");
+  LGK_REQUIRE(!nesterov || momentum > 0.f, LGK_ERR_BAD_ARG, "lgk_sgd_step: nesterov needs momentum");
+  lgk::sgd_kernel<<<unsigned(ceil_div(n, 256)), 256, 0, stream>>>(param, grad, momentum == 0.f ? nullptr : momentum_buf, n, lr,
+                                                                  momentum, weight_decay, nesterov, grad_scale, zero_grad);
+  LGK_CHECK_LAUNCH("sgd_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_cross_entropy_loss(const float* logits, const int64_t* y, const float* class_weight, int64_t n,
+                                      int64_t num_classes, float grad_scale, float* loss_out, float* dlogits, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n > 0 && num_classes > 0 && num_classes < (1 << 20), LGK_ERR_BAD_ARG, "lgk_cross_entropy_loss: bad sizes");
+  LGK_REQUIRE(logits && y && loss_out, LGK_ERR_BAD_ARG, "lgk_cross_entropy_loss: null pointer");
+  lgk::cross_entropy_kernel<<<1, 1024, 0, stream>>>(logits, y, class_weight, n, int(num_classes), grad_scale, loss_out, dlogits);
+  LGK_CHECK_LAUNCH("cross_entropy_kernel");
+  return LGK_OK;
+}

@@ -451,3 +451,26 @@ def clamped_regression_loss(logits: Tensor, y: Tensor, lo: float, hi: float, kin
     L.call("lgk_clamped_regression_loss", _chk(logits, torch.float32, "logits"), _chk(y, torch.int64, "y"), n,
            float(lo), float(hi), int(kind), float(grad_scale), loss.data_ptr(), _chk(dl, torch.float32, "dlogits"), _stream())
     return loss, dl
+
+
+def sgd_step(param: Tensor, grad: Tensor, momentum_buf: Optional[Tensor] = None, *, lr: float, momentum: float = 0.0,
+             weight_decay: float = 0.0, nesterov: bool = False, grad_scale: float = 1.0, zero_grad: bool = False) -> None:
+    """torch.optim.SGD over flat buffers (reference models/base.py:167-168), one launch"""
+    L = _lib.lib()
+    f32 = torch.float32
+    L.call("lgk_sgd_step", _chk(param, f32, "param"), _chk(grad, f32, "grad"), _chk(momentum_buf, f32, "momentum_buf"),
+           param.numel(), float(lr), float(momentum), float(weight_decay), int(nesterov), float(grad_scale), int(zero_grad), _stream())
+
+
+def cross_entropy_loss(logits: Tensor, y: Tensor, class_weight: Optional[Tensor] = None, want_grad: bool = True,
+                       grad_scale: float = 1.0):
+    """-> (loss [] f32, grad_scale * d loss / d logits [n, C] | None): nn.CrossEntropyLoss(weight=class_weight), forward and
+    gradient in one launch (reference models/base.py:93-94)"""
+    L = _lib.lib()
+    n, c = logits.shape
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    dl = torch.empty(n, c, dtype=torch.float32, device=logits.device) if want_grad else None
+    L.call("lgk_cross_entropy_loss", _chk(logits, torch.float32, "logits"), _chk(y, torch.int64, "y"),
+           _chk(class_weight, torch.float32, "class_weight"), n, c, float(grad_scale), loss.data_ptr(),
+           _chk(dl, torch.float32, "dlogits"), _stream())
+    return loss, dl

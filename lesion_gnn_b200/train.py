@@ -89,6 +89,9 @@ class FlatAdam(FlatParams):
         self.step_dev = torch.zeros(2, dtype=torch.int64, device=self.param.device)  # {steps completed, kernel scratch}
         self.lr, self.betas, self.eps, self.weight_decay, self.adamw = lr, betas, eps, weight_decay, adamw
 
+    def state_tensors(self):
+        return [self.param, self.exp_avg, self.exp_avg_sq, self.step_dev]
+
     def step(self, grad_scale: float = 1.0) -> None:
         """one fused kernel; the step counter lives on the device (and is advanced by the kernel) so the call can be
         graph-captured"""
@@ -98,6 +101,57 @@ class FlatAdam(FlatParams):
                       weight_decay=self.weight_decay, step=0, step_dev=self.step_dev, grad_scale=grad_scale,
                       adamw=self.adamw, zero_grad=_ADAM_ZEROES_GRAD, advance_step=_ADAM_ADVANCES_STEP)
         self._grad_is_zero = _ADAM_ZEROES_GRAD  # the kernel cleared the bucket: the next zero_grad() launches nothing
+
+
+class FlatSGD(FlatParams):
+    """torch.optim.SGD (reference models/base.py:167-168: lr and weight_decay) as one lgk_sgd_step launch over the flat
+    buffers; momentum / nesterov (dampening 0) are available although the reference leaves them at 0.  CUDA only."""
+
+    def __init__(self, module: nn.Module, lr: float = 1e-3, momentum: float = 0.0, weight_decay: float = 0.0,
+                 nesterov: bool = False):
+        super().__init__(module)
+        if self.param.device.type != "cuda":
+            raise RuntimeError("FlatSGD needs the module on a CUDA device: lesion_gnn_b200 has no CPU path")
+        self.lr, self.momentum, self.weight_decay, self.nesterov = lr, momentum, weight_decay, nesterov
+        self.momentum_buf = torch.zeros_like(self.param) if momentum != 0.0 else None
+        self.step_dev = torch.zeros(2, dtype=torch.int64, device=self.param.device)  # step count: the dropout clock
+
+    def state_tensors(self):
+        return [t for t in (self.param, self.momentum_buf, self.step_dev) if t is not None]
+
+    def step(self, grad_scale: float = 1.0) -> None:
+        self.step_dev[:1].add_(1)
+        ops.sgd_step(self.param, self.grad, self.momentum_buf, lr=self.lr, momentum=self.momentum,
+                     weight_decay=self.weight_decay, nesterov=self.nesterov, grad_scale=grad_scale,
+                     zero_grad=_ADAM_ZEROES_GRAD)
+        self._grad_is_zero = _ADAM_ZEROES_GRAD
+
+
+def make_optimizer(module: nn.Module, algo: str = "adam", lr: float = 1e-3, weight_decay: float = 0.0):
+    """reference models/base.py:162-170 `configure_optimizers`: OptimizerAlgo ADAM / ADAMW / SGD"""
+    algo = algo.lower()
+    if algo == "adam":
+        return FlatAdam(module, lr=lr, weight_decay=weight_decay)
+    if algo == "adamw":
+        return FlatAdam(module, lr=lr, weight_decay=weight_decay, adamw=True)
+    if algo == "sgd":
+        return FlatSGD(module, lr=lr, weight_decay=weight_decay)
+    raise ValueError(f"unknown optimizer {algo!r}")
+
+
+class _CrossEntropyLoss(torch.autograd.Function):
+    """(weighted) cross-entropy and its gradient from one launch (ops.cross_entropy_loss)"""
+
+    @staticmethod
+    def forward(ctx, logits, y, weight):
+        loss, dl = ops.cross_entropy_loss(logits, y, weight, want_grad=ctx.needs_input_grad[0])
+        ctx.save_for_backward(dl)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl * g, None, None
 
 
 class _ClampedRegressionLoss(torch.autograd.Function):
@@ -129,8 +183,14 @@ _ADAM_ZEROES_GRAD = os.environ.get("LGK_ADAM_ZEROES_GRAD", "1") != "0"
 _DIRECT_LOSS_GRAD = os.environ.get("LGK_DIRECT_LOSS_GRAD", "1") != "0"
 
 
-def loss_fn(logits: Tensor, y: Tensor, loss_type: str = "MSE", num_classes: int = 5) -> Tensor:
-    """reference models/base.py:88-96,196-199 and the regression clamp of models/gat.py:94-95"""
+def _fused_ce(logits: Tensor, y: Tensor) -> bool:
+    return logits.is_cuda and logits.dtype == torch.float32 and y.dtype == torch.int64 and logits.dim() == 2
+
+
+def loss_fn(logits: Tensor, y: Tensor, loss_type: str = "MSE", num_classes: int = 5,
+            class_weights: Optional[Tensor] = None) -> Tensor:
+    """reference models/base.py:88-96,196-199 and the regression clamp of models/gat.py:94-95; class_weights is the
+    `weight` of nn.CrossEntropyLoss (base.py:93-94)"""
     if _fused_regression(logits, y, loss_type):
         return _ClampedRegressionLoss.apply(logits.contiguous(), y.contiguous(), float(num_classes - 1),
                                             0 if loss_type == "MSE" else 1)
@@ -139,7 +199,10 @@ def loss_fn(logits: Tensor, y: Tensor, loss_type: str = "MSE", num_classes: int 
     if loss_type == "SmoothL1":
         return TF.smooth_l1_loss(torch.clamp(logits.squeeze(1), min=0, max=num_classes - 1), y.float())
     if loss_type == "CE":
-        return TF.cross_entropy(logits, y)
+        if _fused_ce(logits, y):
+            w = None if class_weights is None else class_weights.to(device=logits.device, dtype=torch.float32).contiguous()
+            return _CrossEntropyLoss.apply(logits.contiguous(), y.contiguous(), w)
+        return TF.cross_entropy(logits, y, weight=class_weights)
     raise ValueError(loss_type)
 
 
@@ -164,7 +227,8 @@ class DeviceBatch:
             self.edge_weight.copy_(hb.edge_weight, non_blocking=True)
 
 
-def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_classes: int, build_stream=None) -> Tensor:
+def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_classes: int, build_stream=None,
+                     class_weights: Optional[Tensor] = None) -> Tensor:
     """CSR/CSC build + segment pointer + forward + loss + backward for the batch resident in `db`.  With
     `build_stream` the CSR/CSC build runs beside the model's first transform (in_proj needs no graph)."""
     graph = CSRGraph.from_edge_index(db.edge_index, db.num_nodes, db.edge_weight, stream=build_stream)
@@ -178,7 +242,11 @@ def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_clas
                                                0 if loss_type == "MSE" else 1, grad_scale=db.loss_weight)
         logits.backward(dl.view_as(logits))
         return loss
-    loss = loss_fn(logits, db.y, loss_type, num_classes)
+    if _DIRECT_LOSS_GRAD and loss_type == "CE" and _fused_ce(logits, db.y) and logits.requires_grad:
+        loss, dl = ops.cross_entropy_loss(logits.detach().contiguous(), db.y, class_weights, grad_scale=db.loss_weight)
+        logits.backward(dl)
+        return loss
+    loss = loss_fn(logits, db.y, loss_type, num_classes, class_weights)
     (loss * db.loss_weight if db.loss_weight != 1.0 else loss).backward()
     return loss.detach()
 
@@ -191,9 +259,12 @@ class TrainStep:
     """
 
     def __init__(self, model: nn.Module, opt: FlatAdam, loss_type: str = "MSE", num_classes: int = 5,
-                 use_cuda_graph: bool = True, process_group=None, world_size: int = 1):
+                 use_cuda_graph: bool = True, process_group=None, world_size: int = 1,
+                 class_weights: Optional[Tensor] = None):
         self.model, self.opt = model, opt
         self.loss_type, self.num_classes = loss_type, num_classes
+        dev = opt.param.device
+        self.class_weights = None if class_weights is None else class_weights.to(device=dev, dtype=torch.float32).contiguous()
         self.use_cuda_graph = use_cuda_graph
         self.pg, self.world_size = process_group, world_size
         self._graphs = {}
@@ -209,7 +280,7 @@ class TrainStep:
         # ... and run on a side stream, overlapping the main backward chain; joined before the optimiser reads them
         # ... attention dropout is keyed on the optimiser's device-side step counter, so graph replays draw fresh masks
         with direct_param_grads(), side_stream(self._side), dropout_clock(getattr(self.opt, "step_dev", None)):
-            loss = forward_backward(self.model, db, self.loss_type, self.num_classes, self._build)
+            loss = forward_backward(self.model, db, self.loss_type, self.num_classes, self._build, self.class_weights)
         if self.world_size == 1:
             self.opt.step()
         return loss
@@ -230,7 +301,8 @@ class TrainStep:
             # -- the warm-up runs must not train: optimiser state, parameters and module buffers (BatchNorm
             # running statistics) are restored afterwards
             opt = self.opt
-            saved = [t.clone() for t in (opt.param, opt.exp_avg, opt.exp_avg_sq, opt.step_dev)]
+            state = opt.state_tensors()
+            saved = [t.clone() for t in state]
             bufs = [(b, b.clone()) for b in self.model.buffers()]
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
@@ -239,7 +311,7 @@ class TrainStep:
                     self._body(db)
                     self._finish_dp()
             torch.cuda.current_stream().wait_stream(s)
-            for dst, src in zip((opt.param, opt.exp_avg, opt.exp_avg_sq, opt.step_dev), saved):
+            for dst, src in zip(state, saved):
                 dst.copy_(src)
             for b, src in bufs:
                 b.copy_(src)

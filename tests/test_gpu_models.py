@@ -225,6 +225,74 @@ def test_adam_matches_torch(dev):
         assert_close(pg2, ref2, 1e-5, f"adam (self-advancing) adamw={adamw} wd={wd}")
 
 
+@pytest.mark.parametrize("momentum,nesterov,wd", [(0.0, False, 0.0), (0.0, False, 2e-6), (0.9, False, 0.01), (0.9, True, 0.0)])
+def test_sgd_matches_torch(dev, momentum, nesterov, wd):
+    """torch.optim.SGD (reference models/base.py:167-168) as one launch over the flat buffers"""
+    from lesion_gnn_b200 import ops
+    torch.manual_seed(0)
+    p = torch.randn(1000, dtype=torch.float64)
+    ref = p.clone().requires_grad_(True)
+    opt = torch.optim.SGD([ref], lr=1e-2, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    pg = p.float().to(dev)
+    buf = torch.zeros_like(pg) if momentum else None
+    for _ in range(5):
+        g = torch.randn(1000, dtype=torch.float64)
+        ref.grad = g.clone()
+        opt.step()
+        gg = (2 * g).float().to(dev)
+        ops.sgd_step(pg, gg, buf, lr=1e-2, momentum=momentum, weight_decay=wd, nesterov=nesterov, grad_scale=0.5, zero_grad=True)
+        assert float(gg.abs().max()) == 0.0
+    assert_close(pg, ref, 1e-6, "sgd")
+
+
+@pytest.mark.parametrize("weighted", [False, True])
+def test_cross_entropy_loss_matches_torch(dev, weighted):
+    """nn.CrossEntropyLoss(weight=class_weights) (reference models/base.py:93-94): loss and gradient in one launch"""
+    from lesion_gnn_b200 import train
+    torch.manual_seed(4)
+    n, C = 1300, 5
+    x = torch.randn(n, C, dtype=torch.float64) * 4
+    y = torch.randint(0, C, (n,))
+    w = torch.tensor([0.3, 1.0, 2.5, 0.7, 4.0], dtype=torch.float64) if weighted else None
+    xr = x.clone().requires_grad_(True)
+    want = torch.nn.functional.cross_entropy(xr, y, weight=w)
+    (want * 0.7).backward()
+    xg = x.float().to(dev).requires_grad_(True)
+    got = train.loss_fn(xg, y.to(dev), "CE", C, class_weights=None if w is None else w.float())
+    (got * 0.7).backward()
+    assert_close(got, want, TOL_F32, "loss")
+    assert_close(xg.grad, xr.grad, TOL_F32, "dlogits")
+    assert row_rel_err(xg.grad, xr.grad) < 1e-4
+
+
+def test_train_step_sgd_weighted_ce_matches_oracle(dev):
+    """the reference's other optimiser / loss branch: SGD + class-weighted cross-entropy, 3 steps, graph replay"""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import train
+    hb = knn_batch(16, "ddr", 24, 6, seed=9)
+    torch.manual_seed(6)
+    w = torch.tensor([0.5, 1.0, 2.0, 1.5, 3.0])
+    ref = O.GAT(24, [32, 32], 5, heads=2, dropout=0.0).double()
+    mod = lg.models.GAT(24, [32, 32], 5, heads=2, dropout=0.0)
+    mod.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    mod = mod.to(dev)
+    opt_r = torch.optim.SGD(ref.parameters(), lr=5e-2, weight_decay=2e-6)
+    opt = train.make_optimizer(mod, "sgd", lr=5e-2, weight_decay=2e-6)
+    step = train.TrainStep(mod, opt, "CE", 5, use_cuda_graph=True, class_weights=w)
+    db = train.DeviceBatch(hb, dev)
+    db.copy_from(hb)
+    for it in range(3):
+        opt_r.zero_grad()
+        out = ref(hb.x.double(), hb.edge_index, hb.batch, num_graphs=hb.num_graphs)
+        loss_r = torch.nn.functional.cross_entropy(out, hb.y, weight=w.double())
+        loss_r.backward()
+        opt_r.step()
+        loss = step(db)
+        assert rel_err(loss, loss_r) < 1e-5, (it, float(loss), float(loss_r))
+    for (k, p), (_, pr) in zip(mod.named_parameters(), ref.named_parameters()):
+        assert_close(p, pr, 1e-5, "param " + k)
+
+
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_train_step_matches_oracle_training(dev, use_graph):
     """5 optimisation steps (fwd + loss + bwd + Adam): eager and CUDA-graph replay vs the oracle's training_step"""
@@ -233,21 +301,27 @@ def test_train_step_matches_oracle_training(dev, use_graph):
     hb = knn_batch(16, "ddr", 40, 6, seed=2)
     torch.manual_seed(5)
     ref = O.GAT(40, [32, 32, 32], 1, heads=4, dropout=0.0).double()
+    ref32 = O.GAT(40, [32, 32, 32], 1, heads=4, dropout=0.0).float()
+    ref32.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
     mod = lg.models.GAT(40, [32, 32, 32], 1, heads=4, dropout=0.0)
     mod.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
     mod = mod.to(dev)
     opt_r = torch.optim.Adam(ref.parameters(), lr=1e-3)
+    opt_32 = torch.optim.Adam(ref32.parameters(), lr=1e-3)
     opt = train.FlatAdam(mod, lr=1e-3)
     step = train.TrainStep(mod, opt, "MSE", 5, use_cuda_graph=use_graph)
     db = train.DeviceBatch(hb, dev)
     hb_p = hb.pin()
     for it in range(5):
         loss_r = O.training_step(ref, opt_r, hb.x.double(), hb.edge_index, hb.batch, hb.y, hb.num_graphs, "MSE", 5)
+        loss_32 = O.training_step(ref32, opt_32, hb.x, hb.edge_index, hb.batch, hb.y, hb.num_graphs, "MSE", 5)
         db.copy_from(hb_p)
         loss = step(db)
-        assert rel_err(loss, loss_r) < 1e-4, (it, float(loss), float(loss_r))
-    for (k, p), (_, pr) in zip(mod.named_parameters(), ref.named_parameters()):
-        assert_close(p, pr, 1e-4, "param " + k)
+        # Adam divides by sqrt(v): early steps amplify fp32 rounding of tiny gradients, so the bound is what the oracle
+        # itself loses when it trains in fp32 (x4), never below the stated 1e-5
+        assert_parity(loss, loss_r, loss_32, f"loss at step {it}")
+    for (k, p), (_, pr), (_, p32) in zip(mod.named_parameters(), ref.named_parameters(), ref32.named_parameters()):
+        assert_parity(p, pr, p32, "param " + k)
 
 
 def test_full_size_properties_config4(dev):
