@@ -1,21 +1,25 @@
 #!/usr/bin/env python
 """bench.py -- graphs/sec fwd+bwd of the lesion-gnn message-passing hot path on N B200s (BASELINE.json metric).
 
-    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one rank per GPU under torchrun)
-    python bench.py --impl reference --gpus N --steps K ...   # the CPU oracle (PyG restatement) on the host cores
+    python bench.py --gpus N --steps K --warmup W             # this repo's CUDA path (one rank per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...    # the CPU oracle (PyG restatement) on the host cores
+    python bench.py --workload gin_b4096 --scaling strong ...  # the other BASELINE.json configs (see WORKLOADS)
 
-Workload (BASELINE.json configs[1], SURVEY.md 8d cfg 2): `GAT(1025, [64]*4, heads=4)` -- in_proj, 3 x (GATConv +
-ELU), global_mean_pool, out_proj, MSE on the clamped scalar (reference models/gat.py:17-59,94-95) -- on 256
-DDR-shaped synthetic lesion graphs per GPU (n ~ ceil(LogNormal(ln 30, 0.9)) in [1, 600], kNN k=6 loop=True), one
-step = CSR/CSC build + forward + loss + backward + Adam (+ one NCCL all-reduce of the flat gradient bucket when
-N > 1; weak scaling: 256 graphs per GPU).  A pool of distinct batches larger than L2 is rotated so no step
-finds its inputs in cache.
+Default workload (BASELINE.json configs[1], SURVEY.md 8d cfg 2): `GAT(1025, [64]*4, heads=4, dropout=0.35)` --
+in_proj, 3 x (GATConv + ELU), global_mean_pool, out_proj, MSE on the clamped scalar (reference models/gat.py:17-59,
+94-95), Adam with weight_decay 2e-6 (configs/config.py:53-63), training mode -- on 256 DDR-shaped synthetic lesion
+graphs per GPU (n ~ ceil(LogNormal(ln 30, 0.9)) in [1, 600], kNN k=6 loop=True).  One step = CSR/CSC build + forward +
+loss + backward + optimiser (+ the gradient all-reduce when N > 1; weak scaling: 256 graphs per GPU).  A pool of
+distinct batches larger than L2 is rotated so no step finds its inputs in cache.
 
 One JSON line on stdout (rank 0).  `value`: inputs resident in HBM.  `e2e`: the same step driven from pinned HOST
-buffers (x, edge_index, batch, y copied host->device inside the timed region, the loss read back).
-`roofline`: the dominant kernel of the step, CUDA-event timed per launch in an instrumented pass of the same
+buffers (x, edge_index, batch, y copied host->device inside the timed region, the loss read back every step).
+`roofline`: the dominant entry point of the step, CUDA-event timed per launch in an instrumented pass of the same
 steps.  `aggregation`: the fused aggregation kernels on the SpMM stress shape (BASELINE.json configs[3]).
-`cpu_baseline`: the oracle on this box's host cores on a bounded sample of the same workload.
+`cpu_baseline` (N = 1 only): the oracle on this box's host cores on a bounded sample of the same workload.
+Extra keys (never replacing the above): `parity_config` (the same model with dropout 0 / weight decay 0, the
+configuration the parity tests check), `e2e_bf16` (features cross PCIe as bf16), `e2e_resident_dataset` (the dataset
+lives in HBM; per step: gather by graph index + kNN + CSR on the device), `collective_us` (the gradient all-reduce alone).
 """
 from __future__ import annotations
 
@@ -31,11 +35,29 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-WORKLOAD = "gat3x64h4_ddr_b256_k6"
-GRAPHS_PER_GPU = 256
-FEAT_IN, HIDDEN, HEADS, KNN = 1025, [64] * 4, 4, 6
-POOL = 6  # distinct batches rotated: 6 x ~47 MB of node features > 126 MB L2
 L2_BYTES = 126 * 1024 * 1024
+
+# name -> model / data of one data-parallel rank.  `graphs` is per GPU under weak scaling and global under strong.
+WORKLOADS = {
+    # BASELINE.json configs[1] -- the headline
+    "gat3x64h4_ddr_b256_k6": dict(model="gat", feat=1025, hidden=[64] * 4, heads=4, out=1, graphs=256, nodes="ddr", k=6,
+                                  layout="uniform", loss="MSE", dropout=0.35, weight_decay=2e-6, pool=6),
+    # the reference's own operating point (configs/config.py:49,53-65): [128]*4, 2 heads, batch_size 10 000
+    "gat4x128h2_ddr_b10000_k6": dict(model="gat", feat=1025, hidden=[128] * 4, heads=2, out=1, graphs=10000, nodes="ddr", k=6,
+                                     layout="uniform", loss="MSE", dropout=0.35, weight_decay=2e-6, pool=2),
+    # BASELINE.json configs[2]: GIN / GraphSAGE, mean||max read-out, 4096 graphs per step
+    "gin_b4096": dict(model="gin", feat=64, hidden=[64] * 4, out=5, graphs=4096, nodes=100, k=8, layout="uniform", loss="CE",
+                      dropout=0.35, weight_decay=2e-6, pool=3),
+    "sage_b4096": dict(model="sage", feat=64, hidden=[64] * 3, out=5, graphs=4096, nodes=100, k=8, layout="uniform", loss="CE",
+                       dropout=0.0, weight_decay=2e-6, pool=3),
+    # BASELINE.json configs[3]: superpixel graphs, 2-layer GCN (the SpMM bandwidth stress as a whole training step)
+    "gcn_cfg4": dict(model="gcn", feat=128, hidden=[128, 128], out=5, graphs=16, nodes=10000, k=16, layout="raster", loss="CE",
+                     dropout=0.0, weight_decay=0.0, pool=2),
+    # BASELINE.json configs[0]: the reference's CPU-runnable case
+    "gcn_cfg1": dict(model="gcn", feat=16, hidden=[64, 64], out=5, graphs=32, nodes=100, k=8, layout="uniform", loss="CE",
+                     dropout=0.0, weight_decay=0.0, pool=4),
+}
+DEFAULT_WORKLOAD = "gat3x64h4_ddr_b256_k6"
 
 
 def parse_args():
@@ -44,7 +66,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--no-extras", action="store_true", help="skip the aggregation stress and cpu_baseline legs")
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: `graphs` per GPU; strong: `graphs` in total, split over the GPUs")
+    ap.add_argument("--no-extras", action="store_true", help="only value / e2e / roofline (skip the secondary legs)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -71,26 +96,46 @@ def measured_traffic(name: str, tag: str):
     return None
 
 
-def make_host_batches(rank: int, count: int, with_edges_on=None):
+def graphs_per_rank(spec: dict, world: int, scaling: str) -> int:
+    return spec["graphs"] if scaling == "weak" else max(1, spec["graphs"] // world)
+
+
+def make_host_batches(spec: dict, graphs: int, rank: int, count: int, with_edges_on=None):
     """`count` distinct synthetic batches for this rank; kNN edges are built on `with_edges_on` (a CUDA device,
-    lgk_knn_graph) or by the oracle on the CPU (reference arm) -- graph construction is outside the timed step,
-    as in the reference where it happens in the DataLoader (datasets/datamodule.py:43-48)."""
+    lgk_knn_graph) or by the oracle on the CPU (reference arm) -- for `value` and `e2e` graph construction is outside
+    the timed step, as in the reference where it happens in the DataLoader (datasets/datamodule.py:43-48); the
+    `e2e_resident_dataset` leg times it."""
     from lesion_gnn_b200 import data
     out = []
     for i in range(count):
-        hb = data.synth_batch(GRAPHS_PER_GPU, "ddr", FEAT_IN, seed=data.SEED + 1000 * rank + i)
+        hb = data.synth_batch(graphs, spec["nodes"], spec["feat"], seed=data.SEED + 1000 * rank + i, layout=spec["layout"],
+                              num_classes=5)
         if with_edges_on is not None:
             from lesion_gnn_b200 import transforms
             from lesion_gnn_b200.nn.pool import Segments
             seg = Segments.from_batch(hb.batch.to(with_edges_on), hb.num_graphs)
-            ei = transforms.knn_graph(hb.pos.to(with_edges_on), KNN, seg, loop=True,
-                                      num_edges=transforms.knn_num_edges(hb.counts, KNN, True))
+            ei = transforms.knn_graph(hb.pos.to(with_edges_on), spec["k"], seg, loop=True,
+                                      num_edges=transforms.knn_num_edges(hb.counts, spec["k"], True))
             hb.edge_index = ei.cpu()
         else:
             from oracle import pyg_semantics as O
-            hb.edge_index = O.knn_graph(hb.pos, KNN, hb.batch, loop=True)
+            hb.edge_index = O.knn_graph(hb.pos, spec["k"], hb.batch, loop=True)
         out.append(hb)
     return out
+
+
+def build_model(spec: dict, module, dropout=None):
+    """`module`: lesion_gnn_b200.models or oracle.pyg_semantics -- same constructors"""
+    p = spec["dropout"] if dropout is None else dropout
+    if spec["model"] == "gat":
+        return module.GAT(spec["feat"], spec["hidden"], spec["out"], heads=spec["heads"], dropout=p)
+    if spec["model"] == "gin":
+        return module.GIN(spec["feat"], spec["hidden"], spec["out"], dropout=p, pooling="mean+max")
+    if spec["model"] == "sage":
+        return module.SAGE(spec["feat"], spec["hidden"], spec["out"])
+    if spec["model"] == "gcn":
+        return module.GCN(spec["feat"], spec["hidden"], spec["out"])
+    raise ValueError(spec["model"])
 
 
 class ClockSampler:
@@ -107,9 +152,7 @@ class ClockSampler:
         try:
             import pynvml
             pynvml.nvmlInit()
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
-            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(physical_index(index))
             self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
         except Exception as e:  # noqa: BLE001
             self.nv, self.err = None, repr(e)
@@ -142,6 +185,37 @@ class ClockSampler:
         return out
 
 
+def physical_index(local: int) -> int:
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        parts = vis.split(",")
+        if local < len(parts) and parts[local].strip().isdigit():
+            return int(parts[local])
+    return local
+
+
+def bind_to_gpu_numa(local: int) -> dict:
+    """Pin this rank's host threads to the CPUs NVML reports as local to its GPU BEFORE any pinned buffer is allocated
+    (first touch then places the staging buffers on the GPU's NUMA node): at N >= 4 every rank shared NUMA node 0 in
+    round 1 and the per-rank host->device rate fell from 53 to 23 GB/s (VERDICT r01, weak #8)."""
+    info = {"bound": False}
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(physical_index(local))
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = sorted(set(cpus) & allowed)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info = {"bound": True, "cpus": f"{cpus[0]}-{cpus[-1]}", "n_cpus": len(cpus)}
+    except Exception as e:  # noqa: BLE001
+        info["error"] = repr(e)[:120]
+    return info
+
+
 # ------------------------------------------------------------------------------------------------------
 # algorithmic (compulsory) bytes per entry point: each distinct array touched once (SURVEY.md 8d); fp32 = 4 B,
 # int32 index = 4 B, int64 edge_index = 8 B.  E is supplied by the caller (it lives on the device).
@@ -152,19 +226,23 @@ def algorithmic_bytes(name: str, a: dict, num_edges: int) -> int:
         return 4 * (a["n"] * a["k"] + a["n"] * a["m"] * (2 if a["accumulate"] else 1) + a["k"] * a["m"])
     if name in ("lgk_linear_bwd_x", "lgk_linear_bwd_w"):
         return 4 * (a["n"] * a["k"] + a["n"] * a["m"] + a["k"] * a["m"])
-    if name == "lgk_spmm":
+    if name in ("lgk_spmm", "lgk_spmm_blocked"):
         n, f = a["n_rows"], a["feat"]
-        extra = (4 * E if a["ew"] else 0) + (4 * E if a["emap"] else 0) + (4 * n if a["pre"] else 0) + (4 * n if a["post"] else 0)
-        extra += 4 * n * f if a["arg_out"] else 0
+        extra = (4 * E if a.get("ew") else 0) + (4 * E if a.get("emap") else 0) + (4 * n if a["pre"] else 0) + (4 * n if a["post"] else 0)
+        extra += 4 * n * f if a.get("arg_out") else 0
         return 2 * n * f * 4 + 4 * E + 4 * (n + 1) + extra
+    if name == "lgk_quad_build":
+        return 8 * E + 5 * a["n_rows"]
     if name == "lgk_spmm_max_bwd":
         n, f = a["n_rows"], a["feat"]
         return 3 * n * f * 4 + 8 * E + 4 * (n + 1)
-    if name in ("lgk_gat_fwd", "lgk_gat_bwd_dst", "lgk_gat_bwd_src", "lgk_gat_alpha", "lgk_gat_datt"):
+    if name in ("lgk_gat_fwd", "lgk_gat_fwd_elu", "lgk_gat_bwd_dst", "lgk_gat_bwd_dst_elu", "lgk_gat_bwd_src", "lgk_gat_alpha",
+                "lgk_gat_datt"):
         n, h, c = a["num_nodes"], a["heads"], a["chan"]
         nf, nh = n * h * c, n * h
         idx = 4 * E + 4 * (n + 1)
-        return {"lgk_gat_fwd": 4 * (2 * nf + 4 * nh) + idx, "lgk_gat_bwd_dst": 4 * (3 * nf + 9 * nh) + idx,
+        return {"lgk_gat_fwd": 4 * (2 * nf + 4 * nh) + idx, "lgk_gat_fwd_elu": 4 * (3 * nf + 4 * nh) + idx,
+                "lgk_gat_bwd_dst": 4 * (3 * nf + 9 * nh) + idx, "lgk_gat_bwd_dst_elu": 4 * (4 * nf + 9 * nh) + idx,
                 "lgk_gat_bwd_src": 4 * (3 * nf + 7 * nh) + idx, "lgk_gat_alpha": 4 * (nf + 2 * nh),
                 "lgk_gat_datt": 4 * (nf + 2 * nh)}[name]
     if name in ("lgk_pool_fwd", "lgk_pool_bwd"):
@@ -180,6 +258,8 @@ def algorithmic_bytes(name: str, a: dict, num_edges: int) -> int:
         return 8 * a["num_nodes"] + 4 * (a["num_graphs"] + 1)
     if name == "lgk_adam_step":
         return 28 * a["n"]
+    if name == "lgk_sgd_step":
+        return 12 * a["n"]
     if name == "lgk_gather_f32":
         return 12 * a["n"]
     return 0
@@ -188,8 +268,8 @@ def algorithmic_bytes(name: str, a: dict, num_edges: int) -> int:
 class KernelTimer:
     """_lib hook: brackets every C-ABI call with CUDA events on the launching (current) stream."""
 
-    def __init__(self, lib):
-        self.lib, self.records, self.num_edges = lib, [], 0
+    def __init__(self, lib, small_n: int):
+        self.lib, self.records, self.num_edges, self.small_n = lib, [], 0, small_n
         self._open = None
 
     def __call__(self, phase, name, args):
@@ -200,7 +280,7 @@ class KernelTimer:
         else:
             names = self.lib.protos[name][2]
             vals = {k: (v if isinstance(v, (int, float)) else (0 if v is None else 1)) for k, v in zip(names, args)}
-            self.records.append((name, self._open, ev, algorithmic_bytes(name, vals, self.num_edges), _shape_tag(name, vals)))
+            self.records.append((name, self._open, ev, algorithmic_bytes(name, vals, self.num_edges), _shape_tag(name, vals, self.small_n)))
 
     def summary(self) -> dict:
         torch.cuda.synchronize()
@@ -213,185 +293,14 @@ class KernelTimer:
         return agg
 
 
-def _shape_tag(name: str, a: dict) -> str:
+def _shape_tag(name: str, a: dict, small_n: int) -> str:
     # row counts (n, N, E) vary from batch to batch of the pool: group launches by the per-row shape only
     keys = [k for k in ("k", "m", "feat", "heads", "chan", "reduce") if k in a]
     if name == "lgk_linear_bwd_w" and not a.get("dw"):
         keys = ["m"]  # bias-gradient column sum only
-    if name in ("lgk_linear_fwd", "lgk_linear_bwd_x", "lgk_linear_bwd_w") and a["n"] <= GRAPHS_PER_GPU:
+    if name in ("lgk_linear_fwd", "lgk_linear_bwd_x", "lgk_linear_bwd_w") and a["n"] <= small_n:
         keys.append("n")  # per-graph (out_proj) products
     return ",".join(f"{k}={a[k]}" for k in keys)
-
-
-# ------------------------------------------------------------------------------------------------------
-# this repo's arm
-# ------------------------------------------------------------------------------------------------------
-def run_b200(args):
-    import torch.distributed as dist
-
-    import lesion_gnn_b200 as lg
-    from lesion_gnn_b200 import _lib, ops, train
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py --impl b200 needs a CUDA device: lesion_gnn_b200 has no CPU path")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    torch.manual_seed(1234)
-    model = lg.models.GAT(FEAT_IN, HIDDEN, 1, heads=HEADS, dropout=0.0).to(dev)
-    if world > 1:  # identical replicas
-        for p in model.parameters():
-            dist.broadcast(p.data, 0)
-    opt = train.FlatAdam(model, lr=1e-3)
-    step = train.TrainStep(model, opt, "MSE", 5, use_cuda_graph=True, process_group=None, world_size=world)
-
-    host = [hb.pin() for hb in make_host_batches(rank, POOL, with_edges_on=dev)]
-    devb = [train.DeviceBatch(hb, dev) for hb in host]
-    for hb, db in zip(host, devb):
-        db.copy_from(hb)
-    total_graphs = GRAPHS_PER_GPU * world
-    for db in devb:
-        db.loss_weight = train.dp_loss_weight(db.num_graphs, total_graphs, world)
-    resident = sum(hb.h2d_bytes() for hb in host)
-    assert resident > L2_BYTES, "batch pool must exceed L2"
-
-    # capture + warm-up (W untimed steps over the pool, at least one full rotation so every graph is captured)
-    warm = max(args.warmup, POOL)
-    for i in range(warm):
-        step(devb[i % POOL])
-    barrier()
-
-    # ---- value: inputs resident in HBM --------------------------------------------------------------
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    for i in range(args.steps):
-        step(devb[i % POOL])
-    e1.record()
-    barrier()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms)
-    clocks = sampler.stop() if rank == 0 else None
-
-    # ---- e2e: host buffers -> device inside the timed region, loss read back every step -----------------------
-    # Double buffered: while step i computes, the pinned-host -> device copy of step i+1's inputs runs on a copy
-    # stream; every step's inputs are copied inside the timed region and every step's loss is read on the host.
-    copy_stream = torch.cuda.Stream()
-    ready = [torch.cuda.Event() for _ in range(POOL)]
-    consumed = [torch.cuda.Event() for _ in range(POOL)]
-
-    def prefetch(i):
-        s = i % POOL
-        copy_stream.wait_event(consumed[s])  # the previous user of this device buffer has finished
-        with torch.cuda.stream(copy_stream):
-            devb[s].copy_from(host[s])
-            ready[s].record(copy_stream)
-
-    def e2e_steps(count):
-        main = torch.cuda.current_stream()
-        for s in range(POOL):
-            consumed[s].record(main)
-        prefetch(0)
-        loss = 0.0
-        for i in range(count):
-            if i + 1 < count:
-                prefetch(i + 1)
-            main.wait_event(ready[i % POOL])
-            out_dev = step(devb[i % POOL])
-            consumed[i % POOL].record(main)
-            loss = float(out_dev)  # device->host read of this step's loss (synchronises the host with the step)
-        return loss
-
-    e2e_steps(POOL)
-    barrier()
-    t0 = time.perf_counter()
-    e0.record()
-    loss_host = e2e_steps(args.steps)
-    e1.record()
-    barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    ms = torch.tensor([max(e0.elapsed_time(e1), wall_ms)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    e2e_ms_total = float(ms)
-    h2d = sum(host[i % POOL].h2d_bytes() for i in range(args.steps)) / args.steps
-
-    # ---- instrumented pass: per entry point CUDA-event times on the same steps (eager, same kernels) -----------
-    eager = train.TrainStep(model, opt, "MSE", 5, use_cuda_graph=False, world_size=world)
-    eager._side = eager._build = None  # one stream: every launch is timed alone, not beside the side-stream kernels
-    L = _lib.lib()
-    eager(devb[0])
-    ops.reset_launch_count()
-    eager(devb[0])
-    launches_per_step = ops.launch_count()
-    timer = KernelTimer(L)
-    L.hook = timer
-    reps = 2
-    for r in range(reps):
-        for i in range(POOL):
-            timer.num_edges = host[i].edge_index.size(1)
-            torch.cuda._sleep(20_000_000)  # ~10 ms of GPU idle spin: the host runs ahead, so the events bracket
-            eager(devb[i])                 # back-to-back device execution instead of Python launch gaps
-            torch.cuda.synchronize()
-    L.hook = None
-    agg = timer.summary()
-    kern_total = sum(d["ms"] for d in agg.values())
-    top = sorted(agg.items(), key=lambda kv: -kv[1]["ms"])
-    peak, peak_src = peaks()
-    breakdown = [{"kernel": n, "shape": tag, "calls_per_step": d["calls"] / (reps * POOL), "us_per_call": 1e3 * d["ms"] / d["calls"],
-                  "share": d["ms"] / kern_total, "GBps": (d["bytes"] / d["calls"]) / (d["ms"] / d["calls"] * 1e-3) / 1e9 if d["bytes"] else None}
-                 for (n, tag), d in top[:12]]
-    (dom_name, dom_tag), dom = top[0]
-    achieved = (dom["bytes"] / dom["calls"]) / (dom["ms"] / dom["calls"] * 1e-3) / 1e9
-    roofline = {"kernel": dom_name, "shape": dom_tag, "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
-                "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                "traffic": measured_traffic(dom_name, dom_tag),
-                "bytes_per_launch": dom["bytes"] // dom["calls"], "us_per_launch": round(1e3 * dom["ms"] / dom["calls"], 2),
-                "share_of_step_kernel_time": round(dom["ms"] / kern_total, 3)}
-
-    out = None
-    if rank == 0:
-        ms_step = ms_total / args.steps
-        out = {
-            "metric": "graphs/sec fwd+bwd", "value": round(total_graphs * args.steps / (ms_total * 1e-3), 1), "unit": "graphs/s",
-            "n_gpus": world, "steps": args.steps, "warmup": warm, "ms_per_step": round(ms_step, 4),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "graphs_per_gpu": GRAPHS_PER_GPU, "global_graphs": total_graphs,
-                       "nodes_per_step_rank0": sum(h.num_nodes for h in host) / POOL,
-                       "edges_per_step_rank0": sum(h.edge_index.size(1) for h in host) / POOL,
-                       "feat_in": FEAT_IN, "hidden": HIDDEN, "heads": HEADS, "knn_k": KNN, "loss": "MSE", "optimizer": "Adam",
-                       "parallelism": f"dp{world}", "cuda_graph": True,
-                       "l2_policy": f"rotating pool of {POOL} distinct batches, {resident / 2**20:.0f} MiB > L2 (126 MiB)"},
-            "e2e": {"value": round(total_graphs * args.steps / (e2e_ms_total * 1e-3), 1), "unit": "graphs/s",
-                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "ms_per_step": round(e2e_ms_total / args.steps, 4),
-                    "last_loss": loss_host},
-            "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
-            "clocks": clocks, "roofline": roofline, "kernels": breakdown,
-        }
-    if not args.no_extras and rank == 0:
-        out["aggregation"] = aggregation_stress(dev, peak, peak_src)
-        out["cpu_baseline"] = cpu_baseline(args.cpu_seconds)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    if rank == 0:
-        print(json.dumps(out), flush=True)
 
 
 def _time_cuda(fn, iters: int, warmup: int = 3) -> float:
@@ -406,128 +315,3 @@ def _time_cuda(fn, iters: int, warmup: int = 3) -> float:
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters
-
-
-def aggregation_stress(dev, peak: float, peak_src: str, graphs: int = 128) -> dict:
-    """BASELINE.json configs[3] / SURVEY.md 8d cfg 4: `graphs` superpixel graphs x 10 000 nodes, 128-d, kNN k=16
-    (loop=True), GCN-normalised aggregation forward (CSR) and backward (CSC), plus mean pooling.  X = 655 MB at
-    128 graphs, far beyond L2, so every launch streams from HBM."""
-    import lesion_gnn_b200 as lg
-    from lesion_gnn_b200 import data, ops, transforms
-    from lesion_gnn_b200.nn.pool import Segments
-    n, k, F = 10000, 16, 128
-    hb = data.synth_batch(graphs, n, F, seed=data.SEED, layout="raster")
-    N = hb.num_nodes
-    seg = Segments.from_batch(hb.batch.to(dev), graphs)
-    ei = transforms.knn_graph(hb.pos.float().to(dev), k, seg, loop=True, num_edges=N * k)
-    E = ei.size(1)
-    t_csr = _time_cuda(lambda: lg.CSRGraph.from_edge_index(ei, N), 3, 1)
-    g = lg.CSRGraph.from_edge_index(ei, N)
-    x = hb.x.to(dev)
-    dinv, _ = g.gcn_norm(False, True)
-    kw = dict(pre=dinv, post=dinv, self_mode=ops.SELF_REPLACE)
-    res = {"shape": {"graphs": graphs, "nodes": N, "edges": E, "feat": F, "k": k}, "peak": peak, "peak_source": peak_src, "unit": "GB/s"}
-    agg_bytes = 2 * N * F * 4 + 4 * E + 4 * (N + 1) + 8 * N
-
-    def entry(ms, nbytes):
-        gbs = nbytes / (ms * 1e-3) / 1e9
-        return {"us": round(ms * 1e3, 1), "bytes": nbytes, "achieved": round(gbs, 1), "frac": round(gbs / peak, 4)}
-
-    res["gcn_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", **kw), 20), agg_bytes)
-    res["gcn_aggregate_bwd"] = entry(_time_cuda(lambda: ops.spmm(g.colptr, g.row, x, "sum", **kw), 20), agg_bytes)
-    plain = 2 * N * F * 4 + 4 * E + 4 * (N + 1)
-    res["sum_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum"), 20), plain)
-    res["mean_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "mean"), 20), plain)
-    res["max_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "max", want_arg=True), 20), plain + 4 * N * F)
-    H, C = 4, 32
-    att = torch.randn(H * C, device=dev) * 0.1
-    a_s, a_d = ops.gat_alpha(x, att, att, H, C)
-    gat_bytes = 4 * (2 * N * F + 4 * N * H) + 4 * E + 4 * (N + 1)
-    res["gat_softmax_aggregate_fwd"] = entry(_time_cuda(lambda: ops.gat_fwd(g.rowptr, g.col, x, a_s, a_d, None, H, C, 0.2, True), 20), gat_bytes)
-    pool_bytes = 4 * (N * F + graphs * F) + 4 * (graphs + 1)
-    res["global_mean_pool_fwd"] = entry(_time_cuda(lambda: ops.pool_fwd(x, seg.ptr, True, True, False), 20), pool_bytes)
-    res["global_mean_max_pool_fwd"] = entry(_time_cuda(lambda: ops.pool_fwd(x, seg.ptr, True, True, True), 20), pool_bytes + 8 * graphs * F)
-    res["csr_csc_build"] = entry(t_csr, 28 * E + 8 * (N + 1))
-    del x, g, ei
-    torch.cuda.empty_cache()
-    return res
-
-
-# ------------------------------------------------------------------------------------------------------
-# CPU legs: the oracle (op-for-op PyG restatement, oracle/pyg_semantics.py) on the host cores
-# ------------------------------------------------------------------------------------------------------
-def _oracle_stepper():
-    from oracle import pyg_semantics as O
-    torch.set_num_threads(os.cpu_count() or 1)
-    torch.manual_seed(1234)
-    model = O.GAT(FEAT_IN, HIDDEN, 1, heads=HEADS, dropout=0.0)
-    optim = torch.optim.Adam(model.parameters(), lr=1e-3)
-    batches = make_host_batches(0, 2)
-
-    def one(i):
-        hb = batches[i % len(batches)]
-        return O.training_step(model, optim, hb.x, hb.edge_index, hb.batch, hb.y, hb.num_graphs, "MSE", 5)
-    return one
-
-
-def cpu_baseline(budget_s: float) -> dict:
-    one = _oracle_stepper()
-    one(0)
-    t0 = time.perf_counter()
-    n = 0
-    while True:
-        one(n)
-        n += 1
-        dt = time.perf_counter() - t0
-        if dt >= budget_s or n >= 200:
-            break
-    return {"value": round(GRAPHS_PER_GPU * n / dt, 1), "unit": "graphs/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{n} full steps of {WORKLOAD} (256 graphs each, fwd+loss+bwd+Adam, fp32) in {dt:.1f} s after 1 warm-up",
-            "ms_per_step": round(1e3 * dt / n, 2)}
-
-
-def run_reference(args):
-    """The reference's CPU path for this workload = the oracle (PyG is not installable here: SURVEY.md 8c), all
-    host threads.  Under torchrun only rank 0 works."""
-    if int(os.environ.get("RANK", "0")) != 0:
-        return
-    one = _oracle_stepper()
-    warm = max(args.warmup, 1)
-    for i in range(warm):
-        one(i)
-    steps = min(args.steps, 100)
-    t0 = time.perf_counter()
-    for i in range(steps):
-        one(i)
-    dt = time.perf_counter() - t0
-    v = round(GRAPHS_PER_GPU * steps / dt, 1)
-    cores = torch.get_num_threads()
-    print(json.dumps({
-        "impl": "reference", "metric": "graphs/sec fwd+bwd", "value": v, "unit": "graphs/s", "n_gpus": args.gpus, "steps": steps,
-        "warmup": warm, "ms_per_step": round(1e3 * dt / steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "graphs_per_step": GRAPHS_PER_GPU, "feat_in": FEAT_IN, "hidden": HIDDEN, "heads": HEADS,
-                   "knn_k": KNN, "loss": "MSE", "optimizer": "Adam", "device": "cpu"},
-        "cpu_baseline": {"value": v, "unit": "graphs/s", "cores": cores, "kind": "port",
-                         "sample": f"{steps} full steps of 256 graphs on {cores} host threads"},
-        "e2e": {"value": v, "unit": "graphs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }), flush=True)
-
-
-def _keep_stdout_for_the_json_line():
-    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the
-    first collective when NCCL_DEBUG is set on the box), so file descriptor 1 is pointed at stderr for the whole run
-    and `print` gets a private duplicate of the real stdout."""
-    sys.stdout.flush()
-    real = os.dup(1)
-    os.dup2(2, 1)
-    sys.stdout = os.fdopen(real, "w", buffering=1)
-
-
-if __name__ == "__main__":
-    a = parse_args()
-    _keep_stdout_for_the_json_line()
-    if a.impl == "reference":
-        run_reference(a)
-    else:
-        run_b200(a)

@@ -10,11 +10,18 @@ from tests.util import TOL_BF16, TOL_F32, assert_close, assert_parity, knn_batch
 pytestmark = pytest.mark.gpu
 
 
-def _model_parity(make_gpu, make_ref, hb, dev, loss_type, tol=TOL_F32, edge_weight=None, train_mode=None):
+ROW_TOL = 2e-5  # per-row L2 metric (stricter than the north_star's whole-tensor metric): twice the whole-tensor bar
+
+
+def _model_parity(make_gpu, make_ref, hb, dev, loss_type, tol=TOL_F32, edge_weight=None, train_mode=None, route_max=False):
     """forward, loss and EVERY gradient (inputs and parameters) of a whole model against the fp64 oracle at the stated
-    1e-5 bar, in the whole-tensor and the per-row metric; where fp32 cannot hold it the bound is 4x the fp32 oracle's own
-    error on the same inputs (tests/util.assert_parity)"""
+    1e-5 bar (whole-tensor metric) and 2e-5 per row; where fp32 cannot hold it the bound is 4x the fp32 oracle's own
+    error on the same inputs (tests/util.assert_parity).  route_max: the oracle's max read-out routes its gradient
+    through the arg-max the CUDA forward chose (tests/util.routed_max_pool: near-ties are decisions, not arithmetic)."""
+    import contextlib
     import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import ops
+    from tests.util import routed_max_pool
     torch.manual_seed(11)
     ref = make_ref().double()
     ref32 = make_ref().float()
@@ -25,10 +32,31 @@ def _model_parity(make_gpu, make_ref, hb, dev, loss_type, tol=TOL_F32, edge_weig
     if train_mode is not None:
         ref.train(train_mode), ref32.train(train_mode), mod.train(train_mode)
 
+    # CUDA first: its read-out arg-max is what the oracle's gradient is routed through (route_max)
+    args_seen = []
+    real_pool_fwd = ops.pool_fwd
+
+    def spy(*a, **k):
+        res = real_pool_fwd(*a, **k)
+        args_seen.append(res[2])
+        return res
+
+    ops.pool_fwd = spy
+    try:
+        xg = hb.x.detach().clone().to(dev).requires_grad_(True)
+        args = [] if edge_weight is None else [edge_weight.float().to(dev)]
+        out = mod(xg, hb.edge_index.to(dev), hb.batch.to(dev), *args)
+    finally:
+        ops.pool_fwd = real_pool_fwd
+    loss = lg.train.loss_fn(out, hb.y.to(dev), loss_type, 5)
+    loss.backward()
+
     def run_ref(model, dt):
-        x = hb.x.to(dt).requires_grad_(True)
+        x = hb.x.detach().clone().to(dt).requires_grad_(True)
         kw = {} if edge_weight is None else {"edge_weight": edge_weight.to(dt)}
-        out = model(x, hb.edge_index, hb.batch, num_graphs=hb.num_graphs, **kw)
+        ctx = routed_max_pool(args_seen[-1]) if route_max else contextlib.nullcontext()
+        with ctx:
+            out = model(x, hb.edge_index, hb.batch, num_graphs=hb.num_graphs, **kw)
         if loss_type == "MSE":
             loss = torch.nn.functional.mse_loss(torch.clamp(out.squeeze(1), 0, 4), hb.y.to(dt))
         else:
@@ -38,18 +66,19 @@ def _model_parity(make_gpu, make_ref, hb, dev, loss_type, tol=TOL_F32, edge_weig
 
     xr, out_r, loss_r = run_ref(ref, torch.float64)
     x32, out_32, loss_32 = run_ref(ref32, torch.float32)
-    xg = hb.x.to(dev).requires_grad_(True)
-    args = [] if edge_weight is None else [edge_weight.float().to(dev)]
-    out = mod(xg, hb.edge_index.to(dev), hb.batch.to(dev), *args)
-    loss = lg.train.loss_fn(out, hb.y.to(dev), loss_type, 5)
-    loss.backward()
-    assert_parity(out, out_r, out_32, "logits", tol)
-    assert_parity(loss, loss_r, loss_32, "loss", tol)
-    assert_parity(xg.grad, xr.grad, x32.grad, "dx", tol)
+    kw = dict(tol=tol, row_tol=ROW_TOL)
+    assert_parity(out, out_r, out_32, "logits", **kw)
+    assert_parity(loss, loss_r, loss_32, "loss", **kw)
+    assert_parity(xg.grad, xr.grad, x32.grad, "dx", **kw)
     refg, ref32g = dict(ref.named_parameters()), dict(ref32.named_parameters())
+    scale = max(float(g.grad.abs().max()) for g in refg.values() if g.grad is not None)
     for k, p in mod.named_parameters():
-        if refg[k].grad is not None and float(refg[k].grad.abs().max()) > 0:
-            assert_parity(p.grad.view_as(refg[k].grad), refg[k].grad, ref32g[k].grad, "d" + k, tol)
+        if refg[k].grad is None:
+            continue
+        if float(refg[k].grad.abs().max()) < 1e-9 * scale:  # analytically zero (a bias in front of BatchNorm)
+            assert float(p.grad.abs().max()) < 1e-4 * scale, k
+            continue
+        assert_parity(p.grad.view_as(refg[k].grad), refg[k].grad, ref32g[k].grad, "d" + k, **kw)
 
 
 def test_gcn_config1(dev):
@@ -91,14 +120,18 @@ def test_gin_config3(dev, train_mode):
     import lesion_gnn_b200 as lg
     hb = knn_batch(512, 100, 64, 8, seed=5)
     _model_parity(lambda: lg.models.GIN(64, [64] * 4, 5, dropout=0.0, pooling="mean+max"),
-                  lambda: O.GIN(64, [64] * 4, 5, dropout=0.0, pooling="mean+max"), hb, dev, "CE", train_mode=train_mode)
+                  lambda: O.GIN(64, [64] * 4, 5, dropout=0.0, pooling="mean+max"), hb, dev, "CE", train_mode=train_mode,
+                  route_max=True)
+    # the reference's own read-out (gin.py:33: global_mean_pool), no arg-max decisions anywhere
+    _model_parity(lambda: lg.models.GIN(64, [64] * 4, 5, dropout=0.0), lambda: O.GIN(64, [64] * 4, 5, dropout=0.0), hb, dev, "CE",
+                  train_mode=train_mode)
 
 
 def test_sage_config3(dev):
     """BASELINE.json config 3, GraphSAGE variant at 512 graphs x 100 nodes"""
     import lesion_gnn_b200 as lg
     hb = knn_batch(512, 100, 64, 8, seed=6)
-    _model_parity(lambda: lg.models.SAGE(64, [64] * 3, 5), lambda: O.SAGE(64, [64] * 3, 5), hb, dev, "CE")
+    _model_parity(lambda: lg.models.SAGE(64, [64] * 3, 5), lambda: O.SAGE(64, [64] * 3, 5), hb, dev, "CE", route_max=True)
 
 
 def test_gcn_config4_one_graph(dev):
@@ -260,9 +293,13 @@ def test_cross_entropy_loss_matches_torch(dev, weighted):
     xg = x.float().to(dev).requires_grad_(True)
     got = train.loss_fn(xg, y.to(dev), "CE", C, class_weights=None if w is None else w.float())
     (got * 0.7).backward()
-    assert_close(got, want, TOL_F32, "loss")
-    assert_close(xg.grad, xr.grad, TOL_F32, "dlogits")
-    assert row_rel_err(xg.grad, xr.grad) < 1e-4
+    # rows whose softmax has saturated carry gradients of a few ulp: the per-row bound is what torch's own fp32
+    # cross-entropy loses on the same logits (assert_parity), the whole-tensor bound is the stated 1e-5
+    x32 = x.float().requires_grad_(True)
+    want32 = torch.nn.functional.cross_entropy(x32, y, weight=None if w is None else w.float())
+    (want32 * 0.7).backward()
+    assert_parity(got, want, want32, "loss")
+    assert_parity(xg.grad, xr.grad, x32.grad, "dlogits")
 
 
 def test_train_step_sgd_weighted_ce_matches_oracle(dev):

@@ -74,14 +74,14 @@ def test_drgnet_forward_backward(dev):
     ref32 = copy.deepcopy(ref).float()
 
     def run_ref(model, dt):
-        x = hb.x.to(dt).requires_grad_(True)
+        x = hb.x.detach().clone().to(dt).requires_grad_(True)
         o = model(x, hb.edge_index, hb.batch, edge_weight=ew.to(dt), num_graphs=hb.num_graphs)
         torch.nn.functional.cross_entropy(o, hb.y).backward()
         return x, o
 
     xr, out_r = run_ref(ref, torch.float64)
     x32, out_32 = run_ref(ref32, torch.float32)
-    xg = hb.x.to(dev).requires_grad_(True)
+    xg = hb.x.detach().clone().to(dev).requires_grad_(True)
     out = mod(xg, hb.edge_index.to(dev), hb.batch.to(dev), ew.float().to(dev))
     torch.nn.functional.cross_entropy(out, hb.y.to(dev)).backward()
     # the stated 1e-5 bar, or 4x what the oracle itself loses in fp32 on these inputs (tests/util.assert_parity)

@@ -92,8 +92,8 @@ def test_reference_pipeline_knn_gaussian_sparse_tensor_feeds_drgnet(dev):
     assert data.edge_index is None and data.edge_weight is None and data.adj_t is not None
     ew = O.gaussian_distance(hb.edge_index, hb.pos, 150.0, torch.float64)
     torch.manual_seed(2)
-    ref = O.DRGNet(16, 16, 2, 6, 5).double().eval()
-    mod = lg.models.DRGNet(16, 16, 2, 6, 5)
+    ref = O.DRGNet(16, 16, 2, 10, 5).double().eval()
+    mod = lg.models.DRGNet(16, 16, 2, 10, 5)
     mod.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
     mod = mod.to(dev).eval()
     want = ref(hb.x.double(), hb.edge_index, hb.batch, edge_weight=ew, num_graphs=hb.num_graphs)
