@@ -139,18 +139,19 @@ LGK_API int lgk_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* emap
 /* Row-blocked ("quad") form of a CSR / CSC for lgk_spmm_blocked: four consecutive rows 4g..4g+3 share one merged
  * neighbour list, ascending by source id, qent[ptr[4g] + t] = source | membership << 28 (bit r: row 4g+r has the entry;
  * a duplicate edge of one row is emitted as a second entry), t < qlen[g].  cmin / cmax [lgk_quad_chunks(n_rows)]: smallest /
- * largest source id referenced by each chunk of 64 quads (INT32_MAX / -1 for a chunk without entries).  Built once per
+ * largest source id referenced by each chunk of 16 quads (INT32_MAX / -1 for a chunk without entries); qmeta int32[4] =
+ * {widest chunk window in rows, number of chunks too wide for the 256-byte-slice ring, 0, 0}, read on the device only.  Built once per
  * batch next to the CSR / CSC (lgk_csr_build) and shared by every layer; n_rows < 2^28.  qent has room for E entries. */
 LGK_API int64_t lgk_quad_chunks(int64_t n_rows);
 LGK_API int lgk_quad_build(const int32_t* ptr, const int32_t* idx, int64_t n_rows, int32_t* qlen, uint32_t* qent,
-                   int32_t* cmin, int32_t* cmax, void* stream);
+                   int32_t* cmin, int32_t* cmax, int32_t* qmeta, void* stream);
 /* lgk_spmm for large graphs whose neighbours lie in a window of node ids (collated lesion graphs: block diagonal,
  * raster node order): same result as lgk_spmm without edge values (`ew`), reduce = LGK_SUM | LGK_MEAN, fp32, feat % 4 == 0,
  * summation in ascending source order.  Source rows are streamed once per CTA into a shared-memory ring by TMA and every
  * gathered row feeds the up to four destination rows of its quad; chunks whose window does not fit the ring are reduced
  * with global gathers by the same launch.  Same self-loop / pre / post / bias semantics as lgk_spmm.              */
 LGK_API int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const uint32_t* qent, const int32_t* cmin,
-                     const int32_t* cmax, const float* pre, const float* post, const float* selfw, float self_fill,
+                     const int32_t* cmax, const int32_t* qmeta, const float* pre, const float* post, const float* selfw, float self_fill,
                      int self_mode, const void* x, const float* bias, void* out, int64_t n_rows, int64_t feat,
                      int reduce, int dtype, void* stream);
 

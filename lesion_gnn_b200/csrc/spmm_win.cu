@@ -30,26 +30,29 @@
 namespace lgk {
 namespace {
 
-constexpr int kQuadsPerChunk = 64;               // 256 destination rows per chunk (granularity of cmin / cmax)
-constexpr int kBlkRows = 32;                     // source rows per ring block = height of a TMA box
-constexpr int kSliceBytes = 128;                 // bytes of a feature row per slice
-constexpr int kSliceF4 = kSliceBytes / 16;       // 8 float4 columns = 8 lanes
-constexpr int kBlkBytes = kBlkRows * kSliceBytes;
+constexpr int kQuadsPerChunk = 16;               // 64 destination rows per chunk (granularity of cmin / cmax)
+constexpr int kBlkBytes = 4096;                  // bytes of a ring block = one TMA box (32 rows x 128 B or 16 rows x 256 B)
 constexpr int kStages = 8;                       // chunks in flight between producer and consumers
-constexpr int kConsumerWarps = 16;
-constexpr int kThreadsWin = 32 * (kConsumerWarps + 1);
-constexpr int kBatch = 16;                       // merged entries staged per group and batch (two per lane)
+constexpr int kMaxConsumerWarps = 24;
+constexpr int kBatch = 16;                       // merged entries staged per group and batch (two per lane at 8 lanes)
 constexpr int kSmemMax = 232448;                 // 227 KB
 constexpr unsigned kColMask = 0x0FFFFFFFu;
+// A chunk whose source window (largest - smallest source id + 1) exceeds this many rows does not leave the 256-byte-slice
+// ring (~830 rows) room to run two chunks ahead; lgk_quad_build counts them (qmeta[1]) and the launch picks the slice
+// width from that count on the device.
+constexpr int kWide256Rows = 700;
 
 // ---- quad-blocked CSR builder -------------------------------------------------------------------------------
-// thread per quad: four-way merge of the quad's sorted rows.  Entry = col | mask << 28, written in place of the
-// quad's first row (ptr[4g] + t): the merged list is never longer than the four rows together.
-__global__ void __launch_bounds__(kQuadsPerChunk) quad_build_kernel(const int* __restrict__ ptr, const int* __restrict__ idx,
-                                                                    int64_t n_rows, int64_t n_quads, int* __restrict__ qlen,
-                                                                    unsigned* __restrict__ qent, int* __restrict__ cmin,
-                                                                    int* __restrict__ cmax) {
-  const int64_t g = int64_t(blockIdx.x) * kQuadsPerChunk + threadIdx.x;
+// thread per quad (a warp per chunk): four-way merge of the quad's sorted rows.  Entry = col | mask << 28, written in
+// place of the quad's first row (ptr[4g] + t): the merged list is never longer than the four rows together.
+// qmeta[0] = widest chunk window in rows, qmeta[1] = chunks wider than kWide256Rows (both accumulated atomically:
+// integer max / count, order independent).
+__global__ void __launch_bounds__(128) quad_build_kernel(const int* __restrict__ ptr, const int* __restrict__ idx,
+                                                         int64_t n_rows, int64_t n_quads, int* __restrict__ qlen,
+                                                         unsigned* __restrict__ qent, int* __restrict__ cmin,
+                                                         int* __restrict__ cmax, int* __restrict__ qmeta) {
+  const int64_t chunk = (int64_t(blockIdx.x) * 128 + threadIdx.x) / kQuadsPerChunk;
+  const int64_t g = int64_t(blockIdx.x) * 128 + threadIdx.x;
   int lo = INT_MAX, hi = -1;
   if (g < n_quads) {
     int pos[4], end[4], c[4];
@@ -80,19 +83,19 @@ __global__ void __launch_bounds__(kQuadsPerChunk) quad_build_kernel(const int* _
     }
     qlen[g] = out - start;
   }
-  __shared__ int s_lo[kQuadsPerChunk / 32], s_hi[kQuadsPerChunk / 32];
 #pragma unroll
-  for (int o = 16; o; o >>= 1) {
+  for (int o = kQuadsPerChunk / 2; o; o >>= 1) {  // reduce over the chunk's lanes (a chunk never straddles a warp)
     lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
     hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
   }
-  if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-#pragma unroll
-    for (int w = 1; w < kQuadsPerChunk / 32; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
-    cmin[blockIdx.x] = lo;
-    cmax[blockIdx.x] = hi;
+  if ((threadIdx.x & (kQuadsPerChunk - 1)) == 0 && chunk * kQuadsPerChunk < n_quads) {
+    cmin[chunk] = lo;
+    cmax[chunk] = hi;
+    if (hi >= lo) {
+      const int width = hi - lo + 1;
+      atomicMax(qmeta, width);
+      if (width > kWide256Rows) atomicAdd(qmeta + 1, 1);
+    }
   }
 }
 
@@ -103,8 +106,14 @@ __device__ __forceinline__ void tma_box_2d(uint32_t dst, const CUtensorMap* map,
       ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(umma::smem_u32(bar))
       : "memory");
 }
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(umma::smem_u32(bar)), "r"(bytes) : "memory");
+// Every wait of this kernel is bounded: a protocol error (or a TMA fault) must surface as a launch failure, not as a
+// hung GPU.  ~2^22 polls x >= 200 ns is seconds, orders of magnitude beyond any legitimate wait.
+__device__ __forceinline__ void win_wait(uint64_t* bar, uint32_t parity) {
+  if (umma::mbar_try_wait(bar, parity)) return;
+  for (unsigned n = 0; !umma::mbar_try_wait(bar, parity); ++n) {
+    __nanosleep(200);
+    if (n > (1u << 22)) __trap();
+  }
 }
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
   float4 v;
@@ -138,6 +147,7 @@ struct WinArgs {
   const unsigned* qent;  // merged entries
   const int* cmin;       // [n_chunks] smallest / largest source id of a chunk (INT_MAX / -1 when it has no entries)
   const int* cmax;
+  const int* qmeta;      // {widest chunk window, chunks wider than kWide256Rows}: device-side choice of the slice width
   const float* pre;
   const float* post;
   const float* selfw;
@@ -147,6 +157,7 @@ struct WinArgs {
   float self_fill;
   int self_mode;
   int mean;
+  int select;            // 1: run only if qmeta selects this slice width; 0: run unconditionally
   int64_t n_rows, n_quads, n_chunks;
   int feat, slices, nb;  // nb: ring blocks
 };
@@ -156,6 +167,11 @@ struct WinShared {
   int direct[kStages];   // chunk is reduced with global gathers (its window does not fit the ring)
   int lo_blk[kStages];   // first ring block the chunk reads (INT_MAX: none), for the eviction rule
 };
+
+// the 256-byte-slice kernel runs when at most 1 chunk in 32 is too wide for its ring, the 128-byte one otherwise
+__device__ __forceinline__ bool select_wide_slices(const WinArgs& a) {
+  return int64_t(__ldg(a.qmeta + 1)) * 32 <= a.n_chunks;
+}
 
 // Accumulate one staged entry into the quad's four accumulators.  `o` carries the membership mask in bits 28..31.
 template <bool HAS_PRE>
@@ -176,30 +192,47 @@ __device__ __forceinline__ void accumulate(float2 (&acc)[4][2], const float4 v, 
   }
 }
 
+// LPG: lanes per group = 16-byte pieces of a slice (8: 128-byte slices, 4 quads per warp, 2 sets of 8 warps working on
+// alternate chunks; 16: 256-byte slices, 2 quads per warp, 1 set).
 // DBG (profiling ablations, LGK_WIN_DEBUG; results are wrong when != 0): 1 = one unpredicated accumulator update per entry
 // instead of the masked four, 2 = no shared-memory / global gathers (the staged words stand in for the data),
 // 4 = the producer issues no TMA loads
-template <bool HAS_PRE, int DBG>
-__global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs a, const __grid_constant__ CUtensorMap map_x) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  // layout: ring [nb][32 rows][128 B] | ring_pre [nb][32] floats | staging [warps][8 pairs][4 groups][16 B] | WinShared
+// NW: consumer warps (+ 1 producer warp); 24 need the kernel to fit 80 registers
+template <bool HAS_PRE, int LPG, int NW, int DBG>
+__global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArgs a, const __grid_constant__ CUtensorMap map_x) {
+  constexpr int kConsumerWarps = NW;
+  constexpr int kSliceBytes = LPG * 16;
+  constexpr int kBlkRows = kBlkBytes / kSliceBytes;
+  constexpr int GPW = 32 / LPG;                          // groups (quads in flight) per warp
+  // work unit of the pipeline = `kSuper` consecutive chunks of the quad structure: one for the 256-byte slices (their
+  // ring only holds a 64-row chunk's window plus look-ahead), four for the 128-byte slices (fewer, larger hand-offs)
+  constexpr int kSuper = LPG == 16 ? 1 : 4;
+  constexpr int kUnitQuads = kQuadsPerChunk * kSuper;
+  constexpr int kSets = kConsumerWarps * GPW / kUnitQuads >= 1 ? kConsumerWarps * GPW / kUnitQuads : 1;
+  constexpr int kWarpsPerSet = kConsumerWarps / kSets;
+  constexpr int EPL = kBatch / LPG;                      // entries a lane stages per batch
+  static_assert(kWarpsPerSet * GPW == kUnitQuads && kSets * kWarpsPerSet == kConsumerWarps, "one quad per group and unit");
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  if (a.select && select_wide_slices(a) != (LPG == 16)) return;
+  // layout: ring [nb][4096 B] | ring_pre [nb][kBlkRows] floats | staging [warps][8 pairs][GPW][16 B] | WinShared
   const uint32_t ring = umma::smem_u32(smem_raw);
   float* ring_pre = reinterpret_cast<float*>(smem_raw + size_t(a.nb) * kBlkBytes);
-  unsigned char* stage_raw = reinterpret_cast<unsigned char*>(ring_pre + (HAS_PRE ? a.nb * kBlkRows : 0));
+  unsigned char* stage_raw = reinterpret_cast<unsigned char*>(ring_pre + (HAS_PRE ? a.nb * 32 : 0));
   WinShared* sh = reinterpret_cast<WinShared*>(stage_raw + kConsumerWarps * 512);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x % a.slices;
   const int span = blockIdx.x / a.slices, spans = gridDim.x / a.slices;
-  if (span >= spans) return;  // CTAs beyond the last whole group of slices
-  const int64_t c_begin = a.n_chunks * span / spans, c_end = a.n_chunks * (span + 1) / spans;
+  const int64_t n_units = (a.n_chunks + kSuper - 1) / kSuper;
+  const int64_t c_begin = n_units * span / spans, c_end = n_units * (span + 1) / spans;  // in units
   const int n_my = int(c_end - c_begin);
   const int nb = a.nb;
 
   if (threadIdx.x == 0) {
+    if (ring & (kSliceBytes - 1)) __trap();  // the gather address is formed as ring-row address | lane offset
     for (int s = 0; s < kStages; ++s) {
       umma::mbar_init(&sh->full[s], 1);
-      umma::mbar_init(&sh->empty[s], kConsumerWarps);
+      umma::mbar_init(&sh->empty[s], kWarpsPerSet);
     }
     umma::mbar_init_fence();
   }
@@ -207,17 +240,51 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
 
   if (warp == kConsumerWarps) {
     // ===================== producer: keep the ring ahead of the consumers =====================
+    // full[s] of chunk i completes when its own boxes have landed AND the producer has arrived on it -- which it does
+    // one iteration later, after it has seen full of chunk i - 1 complete.  So "full[i] complete" implies that the
+    // boxes of every earlier chunk have landed too: a consumer set that skipped those chunks (they belong to the other
+    // sets) still finds the older part of its window in the ring.
     int base_blk = 0, top_blk = 0;  // resident source blocks [base_blk, top_blk); block b lives in slot b % nb
     int oldest = 0;                 // oldest chunk (local index) whose completion has not been waited for
-    const int64_t n_src_blocks = (a.n_rows + kBlkRows - 1) / kBlkRows;
+    // chunk windows: lane l holds chunk 32 k + l of the current and of the next group of 32 (loaded a group ahead, so the
+    // loop never waits on them)
+    auto load_range = [&](int first, int& lo_r, int& hi_r) {
+      lo_r = INT_MAX;
+      hi_r = -1;
+      if (first + lane < n_my) {
+#pragma unroll
+        for (int u = 0; u < kSuper; ++u) {
+          const int64_t c = (c_begin + first + lane) * kSuper + u;
+          if (c < a.n_chunks) {
+            lo_r = min(lo_r, __ldg(a.cmin + c));
+            hi_r = max(hi_r, __ldg(a.cmax + c));
+          }
+        }
+      }
+    };
+    int cur_lo, cur_hi, nxt_lo, nxt_hi;
+    load_range(0, cur_lo, cur_hi);
+    load_range(32, nxt_lo, nxt_hi);
     for (int i = 0; i < n_my; ++i) {
       const int s = i % kStages;
-      // stage s still belongs to chunk i - kStages until every consumer warp has released it
+      if ((i & 31) == 0 && i > 0) {
+        cur_lo = nxt_lo;
+        cur_hi = nxt_hi;
+        load_range(i + 32, nxt_lo, nxt_hi);
+      }
+      const int lo = __shfl_sync(0xffffffffu, cur_lo, i & 31), hi = __shfl_sync(0xffffffffu, cur_hi, i & 31);
+      // deferred arrival on the previous chunk's barrier (see above) -- FIRST, so that every chunk this iteration may
+      // have to drain below can actually start
+      if (lane == 0 && i >= 1) {
+        if (i >= 2) win_wait(&sh->full[(i - 2) % kStages], ((i - 2) / kStages) & 1);
+        umma::mbar_arrive(&sh->full[(i - 1) % kStages]);
+      }
+      __syncwarp();
+      // stage s still belongs to chunk i - kStages until every consumer warp of its set has released it
       while (oldest + kStages <= i) {
-        umma::mbar_wait_relaxed(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
+        win_wait(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
         ++oldest;
       }
-      const int lo = __ldg(a.cmin + c_begin + i), hi = __ldg(a.cmax + c_begin + i);
       int direct = 0, lo_b = INT_MAX, load_from = 0, load_to = 0;
       if (hi >= lo) {
         lo_b = lo / kBlkRows;
@@ -228,7 +295,7 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
         } else {
           if (lo_b < base_blk) {  // backward jump: drain everything in flight, restart the window
             while (oldest < i) {
-              umma::mbar_wait_relaxed(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
+              win_wait(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
               ++oldest;
             }
             base_blk = top_blk = lo_b;
@@ -242,7 +309,7 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
           for (int j = oldest; j < i; ++j)
             if (sh->lo_blk[j % kStages] != INT_MAX && sh->lo_blk[j % kStages] + nb < new_top) need = j + 1;
           while (oldest < need) {
-            umma::mbar_wait_relaxed(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
+            win_wait(&sh->empty[oldest % kStages], (oldest / kStages) & 1);
             ++oldest;
           }
           load_from = top_blk;
@@ -251,11 +318,23 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
           base_blk = max(base_blk, top_blk - nb);
         }
       }
-      if (HAS_PRE) {
-        for (int b = load_from; b < load_to; ++b) {
-          const int64_t r = int64_t(b) * kBlkRows + lane;
-          ring_pre[(b % nb) * kBlkRows + lane] = r < a.n_rows ? __ldg(a.pre + r) : 0.f;
-        }
+      // the pre-scale factors of the new rows travel like the rows themselves: 1-D bulk copies (at most two: the ring
+      // wraps) completing on the same barrier; only a ragged tail of < 4 rows at the very end of the array is stored by hand
+      uint32_t pre_bytes[2] = {0, 0};
+      int64_t pre_row[2] = {0, 0};
+      if (HAS_PRE && load_to > load_from) {
+        const int64_t R = int64_t(nb) * kBlkRows;
+        const int64_t r_first = int64_t(load_from) * kBlkRows;
+        const int64_t v_last = min(int64_t(load_to) * kBlkRows, a.n_rows);
+        const int64_t p0 = r_first % R;
+        const int64_t n1 = max(int64_t(0), min(v_last - r_first, R - p0)), n2 = max(int64_t(0), v_last - r_first - n1);
+        pre_row[0] = r_first;
+        pre_row[1] = r_first + n1;
+        pre_bytes[0] = uint32_t(n1 * 4) & ~15u;
+        pre_bytes[1] = uint32_t(n2 * 4) & ~15u;
+        const int64_t tail0 = r_first + pre_bytes[0] / 4, tail1 = pre_row[1] + pre_bytes[1] / 4;
+        if (tail0 + lane < pre_row[1]) ring_pre[(tail0 + lane) % R] = __ldg(a.pre + tail0 + lane);
+        if (tail1 + lane < v_last) ring_pre[(tail1 + lane) % R] = __ldg(a.pre + tail1 + lane);
       }
       if (lane == 0) {
         sh->direct[s] = direct;
@@ -264,62 +343,83 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
       __syncwarp();
       if (lane == 0) {
         const int nload = (DBG & 4) ? 0 : load_to - load_from;
-        if (nload > 0) mbar_arrive_expect_tx(&sh->full[s], uint32_t(nload) * kBlkBytes);
-        else umma::mbar_arrive(&sh->full[s]);
+        const uint32_t tx = uint32_t(nload) * kBlkBytes + pre_bytes[0] + pre_bytes[1];
+        if (tx > 0) umma::mbar_expect_tx(&sh->full[s], tx);
+        if (HAS_PRE) {
+          const int64_t R = int64_t(nb) * kBlkRows;
+#pragma unroll
+          for (int k = 0; k < 2; ++k)
+            if (pre_bytes[k]) umma::bulk_g2s(ring_pre + pre_row[k] % R, a.pre + pre_row[k], pre_bytes[k], &sh->full[s]);
+        }
         for (int b = load_from; b < load_from + nload; ++b)
           tma_box_2d(ring + uint32_t(b % nb) * kBlkBytes, &map_x, slice * (kSliceBytes / 4), b * kBlkRows, &sh->full[s]);
       }
       __syncwarp();
-      (void)n_src_blocks;
+    }
+    if (lane == 0 && n_my >= 1) {
+      if (n_my >= 2) win_wait(&sh->full[(n_my - 2) % kStages], ((n_my - 2) / kStages) & 1);
+      umma::mbar_arrive(&sh->full[(n_my - 1) % kStages]);
     }
     return;
   }
 
-  // ===================== consumers: 4 groups of 8 lanes per warp, one quad per group and chunk =====================
-  static_assert(kConsumerWarps * 4 == kQuadsPerChunk, "one quad per group and chunk");
-  const int gl = lane & 7, grp = lane >> 3;
-  const int group = warp * 4 + grp;
+  // ===================== consumers: GPW groups of LPG lanes per warp, one quad per group and chunk =====================
+  const int gl = lane & (LPG - 1), grp = lane / LPG;
+  const int set = warp / kWarpsPerSet;
+  const int group = (warp % kWarpsPerSet) * GPW + grp;  // quad of the chunk this group reduces
   const int F4 = a.feat >> 2;
-  const int vec = slice * kSliceF4 + gl;  // this lane's float4 column
+  const int vec = slice * LPG + gl;  // this lane's float4 column
   const bool lane_on = vec < F4;
-  const uint32_t stage_base = umma::smem_u32(stage_raw) + warp * 512 + grp * 16;  // + pair * 64
+  const uint32_t stage_base = umma::smem_u32(stage_raw) + warp * 512 + grp * 16;  // + pair * (GPW * 16)
   const float4* xv = reinterpret_cast<const float4*>(a.x) + (lane_on ? vec : 0);
   float4* ov = reinterpret_cast<float4*>(a.out) + vec;
   const uint32_t lane_off = uint32_t(gl) * 16;
-  const unsigned nb_magic = unsigned((uint64_t(1) << 32) / unsigned(nb)) + 1u;  // blk % nb without a divide (blk < 2^23)
+  const unsigned nb_magic = unsigned((uint64_t(1) << 32) / unsigned(nb)) + 1u;  // blk % nb without a divide (blk < 2^24)
   const int* qent_i = reinterpret_cast<const int*>(a.qent);
   float4 bias4 = f4_zero();
   if (a.bias && lane_on) bias4 = __ldg(reinterpret_cast<const float4*>(a.bias) + vec);
 
-  // software pipeline over the quads of this group: header (start, len) and first batch of entries one quad ahead
-  int start_n = 0, len_n = 0;
-  unsigned wn0 = 0, wn1 = 0;
-  {
-    const int64_t g0 = c_begin * kQuadsPerChunk + group;
-    if (n_my > 0 && g0 < a.n_quads) {
-      start_n = __ldg(a.ptr + g0 * 4);
-      len_n = __ldg(a.qlen + g0);
-      if (gl < len_n) wn0 = unsigned(ld_stream_i32(qent_i + start_n + gl));
-      if (gl + 8 < len_n) wn1 = unsigned(ld_stream_i32(qent_i + start_n + gl + 8));
+  // software pipeline over the quads of this group, two deep: while quad q is reduced, the first two batches of merged
+  // entries of quad q + 1 and the header (start, len) of quad q + 2 are in flight -- the entry stream comes from HBM
+  // (~1 us), one quad of work per warp is less than that
+  auto quad_of = [&](int i) { return (c_begin + i) * kUnitQuads + group; };
+  auto load_header = [&](int i, int& st, int& ln) {
+    st = ln = 0;
+    if (i < n_my && quad_of(i) < a.n_quads) {
+      st = __ldg(a.ptr + quad_of(i) * 4);
+      ln = __ldg(a.qlen + quad_of(i));
     }
-  }
+  };
+  auto load_batch = [&](int st, int ln, int b0, unsigned (&wd)[EPL]) {
+#pragma unroll
+    for (int h = 0; h < EPL; ++h) {
+      const int e = b0 + gl + LPG * h;
+      wd[h] = 0;
+      if (e < ln) wd[h] = unsigned(ld_stream_i32(qent_i + st + e));
+    }
+  };
+  int start_c, len_c, start_1, len_1;
+  unsigned wc0[EPL], wc1[EPL];
+  load_header(set, start_c, len_c);
+  load_header(set + kSets, start_1, len_1);
+  load_batch(start_c, len_c, 0, wc0);
+  load_batch(start_c, len_c, kBatch, wc1);
 
-  for (int i = 0; i < n_my; ++i) {
+  for (int i = set; i < n_my; i += kSets) {
     const int s = i % kStages;
-    const int64_t g = (c_begin + i) * kQuadsPerChunk + group;
+    const int64_t g = quad_of(i);
     const bool quad_on = g < a.n_quads;
     const int64_t row0 = g * 4;
-    const int start = start_n, len = len_n;
-    unsigned w0 = wn0, w1 = wn1;
-    // next quad's header, and everything the epilogue of this quad reads, go out before the wait
-    {
-      const int64_t gn = g + kQuadsPerChunk;
-      start_n = len_n = 0;
-      if (i + 1 < n_my && gn < a.n_quads) {
-        start_n = __ldg(a.ptr + gn * 4);
-        len_n = __ldg(a.qlen + gn);
-      }
-    }
+    const int start = start_c, len = len_c;
+    unsigned w[EPL], w2[EPL];
+#pragma unroll
+    for (int h = 0; h < EPL; ++h) { w[h] = wc0[h]; w2[h] = wc1[h]; }
+    // next quad's entries and the header after it go out before anything of this quad is touched
+    load_batch(start_1, len_1, 0, wc0);
+    load_batch(start_1, len_1, kBatch, wc1);
+    start_c = start_1;
+    len_c = len_1;
+    load_header(i + 2 * kSets, start_1, len_1);
     float scale[4], cself[4];
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
@@ -329,12 +429,10 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
       if (quad_on && row < a.n_rows) {
         if (a.mean) scale[r] = 1.f / float(max(__ldg(a.ptr + row + 1) - __ldg(a.ptr + row), 1));
         if (a.post) scale[r] *= __ldg(a.post + row);
-        if (a.self_mode != LGK_SELF_NONE) {
-          cself[r] = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
-        }
+        if (a.self_mode != LGK_SELF_NONE) cself[r] = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
       }
     }
-    umma::mbar_wait_relaxed(&sh->full[s], (i / kStages) & 1);
+    win_wait(&sh->full[s], (i / kStages) & 1);
     const int direct = sh->direct[s];
     const int maxlen = __reduce_max_sync(0xffffffffu, len);
     float2 acc[4][2];
@@ -343,49 +441,46 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
     unsigned selfcnt = 0;  // stored (i, i) entries per row, 8 bits each (SELF_REPLACE only)
 
     for (int b0 = 0; b0 < maxlen; b0 += kBatch) {
-      const unsigned word[2] = {w0, w1};
-      w0 = w1 = 0;
-      if (b0 + kBatch < maxlen) {  // next batch of this quad
-        const int e = b0 + kBatch + gl;
-        if (e < len) w0 = unsigned(ld_stream_i32(qent_i + start + e));
-        if (e + 8 < len) w1 = unsigned(ld_stream_i32(qent_i + start + e + 8));
-      }
-      // ---- stage: every lane resolves two entries (ring address | mask, weight) ----
+      unsigned word[EPL];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < EPL; ++h) { word[h] = w[h]; w[h] = w2[h]; }
+      load_batch(start, b0 + 2 * kBatch < maxlen ? len : 0, b0 + 2 * kBatch, w2);  // two batches ahead
+      // ---- stage: every lane resolves its entries (ring address | mask, weight) ----
+#pragma unroll
+      for (int h = 0; h < EPL; ++h) {
         const unsigned col = word[h] & kColMask, mask = word[h] >> 28;
         if (a.self_mode == LGK_SELF_REPLACE) {
           const unsigned d = col - unsigned(row0);
           if (d < 4u && ((mask >> d) & 1u)) selfcnt += 1u << (8 * d);
         }
         unsigned o;
-        float w = 1.f;
+        float wt = 1.f;
         if (!direct) {
           const unsigned blk = col / kBlkRows, slot = blk - __umulhi(blk, nb_magic) * unsigned(nb);
           const unsigned rib = slot * kBlkRows + (col & (kBlkRows - 1));
           o = ring + rib * kSliceBytes;
-          if (HAS_PRE) w = ring_pre[rib];
+          if (HAS_PRE) wt = ring_pre[rib];
         } else {
           o = col;
-          if (HAS_PRE) w = __ldg(a.pre + col);
+          if (HAS_PRE) wt = __ldg(a.pre + col);
         }
         // pair p = entry / 2, half = entry & 1: [pair][group][half] -> one 16-byte read serves two entries
-        const int ent = gl + 8 * h;
-        sts_u2(stage_base + (ent >> 1) * 64 + (ent & 1) * 8, o | (mask << 28), __float_as_uint(w));
+        const int ent = gl + LPG * h;
+        sts_u2(stage_base + (ent >> 1) * (GPW * 16) + (ent & 1) * 8, o | (mask << 28), __float_as_uint(wt));
       }
       __syncwarp();
       const int cnt = min(kBatch, maxlen - b0);
       if (!direct) {
 #pragma unroll 2
         for (int t = 0; t < cnt; t += 2) {
-          const uint4 st = lds_u4(stage_base + (t >> 1) * 64);
+          const uint4 st = lds_u4(stage_base + (t >> 1) * (GPW * 16));
           float4 v0, v1;
           if (DBG & 2) {
             v0 = make_float4(__uint_as_float(st.x), __uint_as_float(st.y), 0.f, 1.f);
             v1 = make_float4(__uint_as_float(st.z), __uint_as_float(st.w), 0.f, 1.f);
           } else {
-            v0 = lds_f4((st.x & kColMask) + lane_off);
-            v1 = lds_f4((st.z & kColMask) + lane_off);
+            v0 = lds_f4((st.x & kColMask) | lane_off);
+            v1 = lds_f4((st.z & kColMask) | lane_off);
           }
           if (DBG & 1) {
             add2(acc[0][0], make_float2(v0.x, v0.y)); add2(acc[0][1], make_float2(v0.z, v0.w));
@@ -398,7 +493,7 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
       } else {
 #pragma unroll 2
         for (int t = 0; t < cnt; t += 2) {
-          const uint4 st = lds_u4(stage_base + (t >> 1) * 64);
+          const uint4 st = lds_u4(stage_base + (t >> 1) * (GPW * 16));
           const float4 v0 = __ldg(xv + size_t(st.x & kColMask) * F4);
           const float4 v1 = __ldg(xv + size_t(st.z & kColMask) * F4);
           accumulate<HAS_PRE>(acc, v0, st.x, __uint_as_float(st.y));
@@ -407,15 +502,10 @@ __global__ void __launch_bounds__(kThreadsWin, 1) spmm_win_kernel(const WinArgs 
       }
       __syncwarp();
     }
-    // first batch of the next quad (its header has arrived by now)
-    wn0 = wn1 = 0;
-    if (gl < len_n) wn0 = unsigned(ld_stream_i32(qent_i + start_n + gl));
-    if (gl + 8 < len_n) wn1 = unsigned(ld_stream_i32(qent_i + start_n + gl + 8));
-
     // ---- epilogue: self term, mean / post scale, bias, store ----
     if (a.self_mode == LGK_SELF_REPLACE) {
 #pragma unroll
-      for (int o = 1; o < 8; o <<= 1) selfcnt += __shfl_xor_sync(0xffffffffu, selfcnt, o);
+      for (int o = 1; o < LPG; o <<= 1) selfcnt += __shfl_xor_sync(0xffffffffu, selfcnt, o);
     }
     if (quad_on) {
 #pragma unroll
@@ -460,13 +550,13 @@ EncodeTiledFn encode_tiled_win() {
   return fn;
 }
 
-// x [rows, feat] fp32 row-major as a 2-D tensor; boxes of {32 floats, 32 rows}, no swizzle, zero fill outside
-bool make_row_map(CUtensorMap* map, const float* base, int64_t rows, int64_t feat) {
+// x [rows, feat] fp32 row-major as a 2-D tensor; boxes of {slice floats, 4096 / slice bytes rows}, no swizzle, zero fill
+bool make_row_map(CUtensorMap* map, const float* base, int64_t rows, int64_t feat, int slice_bytes) {
   EncodeTiledFn enc = encode_tiled_win();
   if (!enc) return false;
   const cuuint64_t dims[2] = {cuuint64_t(feat), cuuint64_t(rows)};
   const cuuint64_t strides[1] = {cuuint64_t(4 * feat)};
-  const cuuint32_t box[2] = {cuuint32_t(kSliceBytes / 4), cuuint32_t(kBlkRows)};
+  const cuuint32_t box[2] = {cuuint32_t(slice_bytes / 4), cuuint32_t(kBlkBytes / slice_bytes)};
   const cuuint32_t estr[2] = {1, 1};
   return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -476,6 +566,60 @@ bool make_row_map(CUtensorMap* map, const float* base, int64_t rows, int64_t fea
 int env_int_win(const char* name, int dflt) {
   const char* v = getenv(name);
   return (v && *v) ? atoi(v) : dflt;
+}
+
+using WinKernel = void (*)(const WinArgs, const CUtensorMap);
+
+template <int LPG, int NW>
+WinKernel pick_kernel(bool has_pre, int dbg) {
+#define LGK_WIN_PICK(D) case D: return has_pre ? spmm_win_kernel<true, LPG, NW, D> : spmm_win_kernel<false, LPG, NW, D>;
+  switch (dbg) {
+    LGK_WIN_PICK(0) LGK_WIN_PICK(1) LGK_WIN_PICK(2) LGK_WIN_PICK(3) LGK_WIN_PICK(4) LGK_WIN_PICK(7)
+  }
+#undef LGK_WIN_PICK
+  return nullptr;
+}
+
+// one launch of the slice width LPG * 16 bytes
+template <int LPG>
+int launch_win(WinArgs a, int select, int dbg, cudaStream_t stream) {
+  // consumer warps (tuning knob; 24 exist for the 256-byte slices only)
+  static const int warps_env = env_int_win("LGK_WIN_WARPS", 16) == 24 ? 24 : 16;
+  const int warps = LPG == 16 ? warps_env : 16;
+  constexpr int slice_bytes = LPG * 16;
+  a.select = select;
+  a.slices = int(ceil_div(int64_t(a.feat) * 4, slice_bytes));
+  const int fixed = warps * 512 + int(sizeof(WinShared)) + 128;
+  const int per_blk = kBlkBytes + (a.pre ? 32 * 4 : 0);
+  static const int nb_cap = env_int_win("LGK_WIN_BLOCKS", 1 << 30);  // tuning / test knob: fewer ring blocks
+  a.nb = std::min((kSmemMax - fixed) / per_blk, nb_cap);
+  LGK_REQUIRE(a.nb >= 2, LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: no room for the ring");
+  const int smem = a.nb * per_blk + fixed;
+  CUtensorMap map_x;
+  LGK_REQUIRE(make_row_map(&map_x, a.x, a.n_rows, a.feat, slice_bytes), LGK_ERR_UNSUPPORTED,
+              "lgk_spmm_blocked: cannot encode the tensor map");
+  // one CTA per SM; a group of `slices` CTAs shares a span of chunks (more slices than SMs: the CTAs queue)
+  const int spans = int(std::max<int64_t>(1, std::min<int64_t>(kNumSMs / std::max(1, std::min(a.slices, kNumSMs)), a.n_chunks)));
+  const unsigned grid = unsigned(spans * a.slices);
+  WinKernel kern;
+  if constexpr (LPG == 16) kern = warps == 24 ? pick_kernel<LPG, 24>(a.pre != nullptr, dbg) : pick_kernel<LPG, 16>(a.pre != nullptr, dbg);
+  else kern = pick_kernel<LPG, 16>(a.pre != nullptr, dbg);
+  LGK_REQUIRE(kern, LGK_ERR_BAD_ARG, "LGK_WIN_DEBUG=%d is not instantiated", dbg);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  static bool configured[64][2][8] = {};
+  bool& done = configured[dev & 63][a.pre ? 1 : 0][dbg & 7];
+  if (!done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax);
+    if (e != cudaSuccess) {
+      set_error("spmm_win_kernel: cannot reserve %d bytes of shared memory: %s", kSmemMax, cudaGetErrorString(e));
+      return LGK_ERR_LAUNCH;
+    }
+    done = true;
+  }
+  kern<<<grid, 32 * (warps + 1), smem, stream>>>(a, map_x);
+  LGK_CHECK_LAUNCH("spmm_win_kernel");
+  return LGK_OK;
 }
 
 }  // namespace
@@ -489,27 +633,29 @@ extern "C" int64_t lgk_quad_chunks(int64_t n_rows) {
 }
 
 extern "C" int lgk_quad_build(const int32_t* ptr, const int32_t* idx, int64_t n_rows, int32_t* qlen, uint32_t* qent,
-                              int32_t* cmin, int32_t* cmax, void* stream_) {
+                              int32_t* cmin, int32_t* cmax, int32_t* qmeta, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n_rows >= 0, LGK_ERR_BAD_ARG, "lgk_quad_build: negative size");
+  LGK_REQUIRE(qmeta, LGK_ERR_BAD_ARG, "lgk_quad_build: null pointer");
+  cudaMemsetAsync(qmeta, 0, 4 * sizeof(int32_t), stream);
   if (n_rows == 0) return LGK_OK;
   LGK_REQUIRE(ptr && qlen && cmin && cmax, LGK_ERR_BAD_ARG, "lgk_quad_build: null pointer");
   LGK_REQUIRE(n_rows <= int64_t(kColMask), LGK_ERR_UNSUPPORTED, "lgk_quad_build: more than 2^28 - 1 rows");
   const int64_t quads = ceil_div(n_rows, 4);
-  quad_build_kernel<<<unsigned(ceil_div(quads, kQuadsPerChunk)), kQuadsPerChunk, 0, stream>>>(ptr, idx, n_rows, quads, qlen, qent,
-                                                                                              cmin, cmax);
+  const int64_t chunks = ceil_div(quads, kQuadsPerChunk);
+  quad_build_kernel<<<unsigned(ceil_div(quads, 128)), 128, 0, stream>>>(ptr, idx, n_rows, quads, qlen, qent, cmin, cmax, qmeta);
   LGK_CHECK_LAUNCH("quad_build_kernel");
   return LGK_OK;
 }
 
 extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const uint32_t* qent, const int32_t* cmin,
-                                const int32_t* cmax, const float* pre, const float* post, const float* selfw, float self_fill,
-                                int self_mode, const void* x, const float* bias, void* out, int64_t n_rows, int64_t feat,
-                                int reduce, int dtype, void* stream_) {
+                                const int32_t* cmax, const int32_t* qmeta, const float* pre, const float* post,
+                                const float* selfw, float self_fill, int self_mode, const void* x, const float* bias,
+                                void* out, int64_t n_rows, int64_t feat, int reduce, int dtype, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n_rows >= 0 && feat >= 0, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: negative size");
   if (n_rows == 0 || feat == 0) return LGK_OK;
-  LGK_REQUIRE(ptr && qlen && qent && cmin && cmax && x && out, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: null pointer");
+  LGK_REQUIRE(ptr && qlen && qent && cmin && cmax && qmeta && x && out, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: null pointer");
   LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: fp32 features only");
   LGK_REQUIRE(reduce == LGK_SUM || reduce == LGK_MEAN, LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: sum or mean only");
   LGK_REQUIRE(reduce == LGK_SUM || self_mode == LGK_SELF_NONE, LGK_ERR_BAD_ARG,
@@ -520,9 +666,10 @@ extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const u
   LGK_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0,
               LGK_ERR_BAD_ARG, "lgk_spmm_blocked: x, out and bias must be 16-byte aligned");
   LGK_REQUIRE(x != out, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: in-place aggregation is not possible");
+  LGK_REQUIRE((reinterpret_cast<uintptr_t>(pre) & 15) == 0, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: pre must be 16-byte aligned");
 
   WinArgs a{};
-  a.ptr = ptr; a.qlen = qlen; a.qent = qent; a.cmin = cmin; a.cmax = cmax;
+  a.ptr = ptr; a.qlen = qlen; a.qent = qent; a.cmin = cmin; a.cmax = cmax; a.qmeta = qmeta;
   a.pre = pre; a.post = post; a.selfw = selfw; a.bias = bias;
   a.x = static_cast<const float*>(x);
   a.out = static_cast<float*>(out);
@@ -531,42 +678,13 @@ extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const u
   a.n_quads = ceil_div(n_rows, 4);
   a.n_chunks = ceil_div(a.n_quads, kQuadsPerChunk);
   a.feat = int(feat);
-  a.slices = int(ceil_div(feat * 4, kSliceBytes));
-  const int fixed = kConsumerWarps * 512 + int(sizeof(WinShared)) + 128;
-  const int per_blk = kBlkBytes + (pre ? kBlkRows * 4 : 0);
-  static const int nb_cap = env_int_win("LGK_WIN_BLOCKS", 1 << 30);  // tuning / test knob: fewer ring blocks
-  a.nb = std::min((kSmemMax - fixed) / per_blk, nb_cap);
-  LGK_REQUIRE(a.nb >= 2, LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: no room for the ring");
-  const int smem = a.nb * per_blk + fixed;
-
-  CUtensorMap map_x;
-  LGK_REQUIRE(make_row_map(&map_x, a.x, n_rows, feat), LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: cannot encode the tensor map");
-
-  // one CTA per SM; a group of `slices` CTAs shares a span of chunks
-  const int spans = int(std::max<int64_t>(1, std::min<int64_t>(kNumSMs / std::max(1, std::min(a.slices, kNumSMs)), a.n_chunks)));
-  const unsigned grid = unsigned(spans * a.slices);
-  // more slices than SMs (feat > 4736): every slice still needs its CTA; they queue
-  int dev = 0;
-  cudaGetDevice(&dev);
-  static bool configured[64][2] = {};
-  const int hp = pre ? 1 : 0;
   static const int dbg = env_int_win("LGK_WIN_DEBUG", 0);
-  void (*kern)(const WinArgs, const CUtensorMap) = nullptr;
-#define LGK_WIN_PICK(D) case D: kern = hp ? spmm_win_kernel<true, D> : spmm_win_kernel<false, D>; break;
-  switch (dbg) {
-    LGK_WIN_PICK(0) LGK_WIN_PICK(1) LGK_WIN_PICK(2) LGK_WIN_PICK(3) LGK_WIN_PICK(4) LGK_WIN_PICK(7)
-    default: LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "LGK_WIN_DEBUG=%d is not instantiated", dbg);
-  }
-#undef LGK_WIN_PICK
-  if (dev < 64 && !configured[dev][hp]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax);
-    if (e != cudaSuccess) {
-      set_error("spmm_win_kernel: cannot reserve %d bytes of shared memory: %s", kSmemMax, cudaGetErrorString(e));
-      return LGK_ERR_LAUNCH;
-    }
-    configured[dev][hp] = true;
-  }
-  kern<<<grid, kThreadsWin, smem, stream>>>(a, map_x);
-  LGK_CHECK_LAUNCH("spmm_win_kernel");
-  return LGK_OK;
+  // LGK_WIN_SLICE = 128 | 256 forces one slice width (A/B measurements); default: both are launched and the one the
+  // graph's windows select (qmeta, written by lgk_quad_build) does the work -- the other returns at once.  The host
+  // never reads the statistic (no synchronisation, CUDA-graph-capture safe).  Rows narrower than 256 bytes: 128 only.
+  static const int force = env_int_win("LGK_WIN_SLICE", 0);
+  if (force == 128 || feat * 4 <= 128) return launch_win<8>(a, 0, dbg, stream);
+  if (force == 256) return launch_win<16>(a, 0, dbg, stream);
+  if (int rc = launch_win<16>(a, 1, dbg, stream)) return rc;
+  return launch_win<8>(a, 1, dbg, stream);
 }

@@ -154,10 +154,10 @@ class Quads:
     """Row-blocked form of a CSR / CSC (lgk_quad_build): merged neighbour lists of four consecutive rows with
     membership masks, plus the source-id range of every chunk of 64 quads.  Index work, built once per batch."""
 
-    __slots__ = ("qlen", "qent", "cmin", "cmax")
+    __slots__ = ("qlen", "qent", "cmin", "cmax", "qmeta")
 
-    def __init__(self, qlen, qent, cmin, cmax):
-        self.qlen, self.qent, self.cmin, self.cmax = qlen, qent, cmin, cmax
+    def __init__(self, qlen, qent, cmin, cmax, qmeta):
+        self.qlen, self.qent, self.cmin, self.cmax, self.qmeta = qlen, qent, cmin, cmax, qmeta
 
 
 def quad_build(ptr: Tensor, idx: Tensor) -> Quads:
@@ -168,9 +168,9 @@ def quad_build(ptr: Tensor, idx: Tensor) -> Quads:
     nq = (n + 3) // 4
     nc = int(L.query("lgk_quad_chunks", n))
     q = Quads(torch.empty(max(nq, 1), **i32), torch.empty(max(idx.numel(), 1), **i32), torch.empty(max(nc, 1), **i32),
-              torch.empty(max(nc, 1), **i32))
+              torch.empty(max(nc, 1), **i32), torch.empty(4, **i32))
     L.call("lgk_quad_build", _chk(ptr, torch.int32, "ptr"), _chk(idx, torch.int32, "idx"), n, q.qlen.data_ptr(),
-           q.qent.data_ptr(), q.cmin.data_ptr(), q.cmax.data_ptr(), _stream())
+           q.qent.data_ptr(), q.cmin.data_ptr(), q.cmax.data_ptr(), q.qmeta.data_ptr(), _stream())
     return q
 
 
@@ -195,7 +195,7 @@ def spmm(ptr: Tensor, idx: Tensor, x: Tensor, reduce: str = "sum", *, emap: Opti
     if quads is not None and not want_arg and blocked_eligible(x, reduce, ew):
         f32 = torch.float32
         L.call("lgk_spmm_blocked", _chk(ptr, torch.int32, "ptr"), _chk(quads.qlen, torch.int32), _chk(quads.qent, torch.int32),
-               _chk(quads.cmin, torch.int32), _chk(quads.cmax, torch.int32), _chk(pre, f32, "pre"), _chk(post, f32, "post"),
+               _chk(quads.cmin, torch.int32), _chk(quads.cmax, torch.int32), _chk(quads.qmeta, torch.int32), _chk(pre, f32, "pre"), _chk(post, f32, "post"),
                _chk(selfw, f32, "selfw"), float(self_fill), int(self_mode), _chk(x, None, "x"), _chk(bias, f32, "bias"),
                _chk(out), n, f, _REDUCE[reduce], _dt(x), _stream())
         return out

@@ -51,10 +51,11 @@ qc, qr = g.quads("csr"), g.quads("csc")
 torch.cuda.synchronize()
 merged = int(qc.qlen.sum().item())
 merged_t = int(qr.qlen.sum().item())
-band = (qc.cmax - qc.cmin)[: (N // 4 + 63) // 64]
+band = (qc.cmax - qc.cmin + 1)[: (N // 4 + 15) // 16]
 print(json.dumps({"what": "quad_build", "us": round(t_q * 1e3, 1), "N": N, "E": E, "merged_csr": merged, "merged_csc": merged_t,
                   "gathers_saved": round(E / merged, 3), "chunk_window_rows_max": int(band.max().item()),
-                  "chunk_window_rows_median": int(band.float().median().item())}), flush=True)
+                  "chunk_window_rows_median": int(band.float().median().item()), "qmeta": qc.qmeta.tolist(),
+                  "slice": os.environ.get("LGK_WIN_SLICE", "auto")}), flush=True)
 
 plain = 2 * N * F * 4 + 4 * E + 4 * (N + 1)
 gcn = plain + 8 * N

@@ -47,7 +47,7 @@ def _host_quads(rowptr, col, n):
     return quads
 
 
-def _band_graph(n, k, seed, width=40):
+def _band_graph(n, k, seed, width=40):  # noqa: E302
     """every node i receives k edges from nodes within +-width (raster-like band), duplicates possible"""
     g = torch.Generator().manual_seed(seed)
     dst = torch.arange(n).repeat_interleave(k)
@@ -68,7 +68,9 @@ def _anti_diagonal_graph(n, k, seed, block=300):
 
 
 GRAPHS = {
-    "band": lambda: (_band_graph(3001, 9, 1), 3001),
+    "band": lambda: (_band_graph(3001, 9, 1), 3001),                                # narrow windows: 256-byte slices
+    "band_mid": lambda: (_band_graph(9000, 6, 7, width=500), 9000),                 # too wide for those: 128-byte slices
+    "band_few_wide": lambda: (torch.cat([_band_graph(40000, 5, 8), torch.tensor([[39000, 5], [17, 20001], [3, 20002]]).t()], 1), 40000),
     "band_wide_direct": lambda: (_band_graph(9000, 6, 2, width=4000), 9000),       # window > ring: global gathers
     "random_direct": lambda: (random_graph(6000, 40000, 3), 6000),
     "anti_diagonal": lambda: (_anti_diagonal_graph(2500, 7, 4), 2500),             # backward jumps, drains
@@ -100,12 +102,15 @@ def test_quad_structure_is_the_four_way_merge(dev, name):
             words = qent[start:start + len(ent)].tolist()
             got = [((w & 0xFFFFFFFF) & 0x0FFFFFFF, ((w & 0xFFFFFFFF) >> 28) & 0xF) for w in words]
             assert got == ent, (which, gq)
-        for c in range((len(want) + 63) // 64):
-            cols = [m for ent in want[64 * c:64 * c + 64] for m, _ in ent]
+        for c in range((len(want) + 15) // 16):
+            cols = [m for ent in want[16 * c:16 * c + 16] for m, _ in ent]
             los.append(min(cols) if cols else 2 ** 31 - 1)
             his.append(max(cols) if cols else -1)
         nc = len(los)
         assert q.cmin.cpu().tolist()[:nc] == los and q.cmax.cpu().tolist()[:nc] == his, which
+        widths = [h - l + 1 for l, h in zip(los, his) if h >= l]
+        meta = q.qmeta.cpu().tolist()
+        assert meta[0] == (max(widths) if widths else 0) and meta[1] == sum(w > 700 for w in widths), (which, meta)
 
 
 @pytest.mark.parametrize("feat", [4, 32, 64, 100, 128, 132])
