@@ -315,3 +315,503 @@ def _time_cuda(fn, iters: int, warmup: int = 3) -> float:
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters
+
+
+# ------------------------------------------------------------------------------------------------------
+# this repo's arm
+# ------------------------------------------------------------------------------------------------------
+class E2EPipe:
+    """Double-buffered host -> device feed: while step i computes, the pinned-host -> device copy of step i+1's inputs
+    runs on a copy stream; every step's inputs are copied inside the timed region and every step's loss is read on
+    the host.  `stage(slot)` does the copies of one slot (and whatever device-side preparation belongs to them)."""
+
+    def __init__(self, n_slots, stage):
+        self.n, self.stage = n_slots, stage
+        self.copy_stream = torch.cuda.Stream()
+        self.ready = [torch.cuda.Event() for _ in range(n_slots)]
+        self.consumed = [torch.cuda.Event() for _ in range(n_slots)]
+
+    def _prefetch(self, i):
+        s = i % self.n
+        self.copy_stream.wait_event(self.consumed[s])  # the previous user of this device buffer has finished
+        with torch.cuda.stream(self.copy_stream):
+            self.stage(s)
+            self.ready[s].record(self.copy_stream)
+
+    def run(self, count, step):
+        main = torch.cuda.current_stream()
+        for s in range(self.n):
+            self.consumed[s].record(main)
+        self._prefetch(0)
+        loss = 0.0
+        for i in range(count):
+            if i + 1 < count:
+                self._prefetch(i + 1)
+            main.wait_event(self.ready[i % self.n])
+            out_dev = step(i % self.n)
+            self.consumed[i % self.n].record(main)
+            loss = float(out_dev)  # device->host read of this step's loss (synchronises the host with the step)
+        return loss
+
+
+def run_b200(args):
+    import torch.distributed as dist
+
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import _lib, ops, train
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl b200 needs a CUDA device: lesion_gnn_b200 has no CPU path")
+    spec = WORKLOADS[args.workload]
+    # the CPU leg runs first, at N = 1 only: under torchrun OMP_NUM_THREADS is 1 and the other ranks would spin
+    cpu = None
+    if world == 1 and not args.no_extras:
+        cpu = cpu_baseline(spec, args.workload, args.cpu_seconds)
+    numa = bind_to_gpu_numa(local)  # before any pinned allocation
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    graphs = graphs_per_rank(spec, world, args.scaling)
+    total_graphs = graphs * world
+    POOL = spec["pool"]
+
+    def make_step(dropout=None, weight_decay=None):
+        torch.manual_seed(1234)
+        model = build_model(spec, lg.models, dropout).to(dev).train()
+        if world > 1:  # identical replicas
+            for p in model.parameters():
+                dist.broadcast(p.data, 0)
+        opt = train.FlatAdam(model, lr=1e-3, weight_decay=spec["weight_decay"] if weight_decay is None else weight_decay)
+        return model, opt, train.TrainStep(model, opt, spec["loss"], 5, use_cuda_graph=True, process_group=None, world_size=world)
+
+    model, opt, step = make_step()
+    host = [hb.pin() for hb in make_host_batches(spec, graphs, rank, POOL, with_edges_on=dev)]
+    devb = [train.DeviceBatch(hb, dev) for hb in host]
+    for hb, db in zip(host, devb):
+        db.copy_from(hb)
+        db.loss_weight = train.dp_loss_weight(db.num_graphs, total_graphs, world)
+    resident = sum(hb.h2d_bytes() for hb in host)
+    l2_policy = (f"rotating pool of {POOL} distinct batches, {resident / 2**20:.0f} MiB > L2 (126 MiB)" if resident > L2_BYTES else
+                 f"rotating pool of {POOL} distinct batches ({resident / 2**20:.0f} MiB) + a {2 * L2_BYTES >> 20} MiB L2 flush write between steps")
+    flush = None if resident > L2_BYTES else torch.empty(2 * L2_BYTES // 4, dtype=torch.float32, device=dev)
+
+    def run_steps(count, stepper, batches):
+        for i in range(count):
+            if flush is not None:
+                flush.zero_()
+            stepper(batches[i % len(batches)])
+
+    def timed(count, stepper, batches):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        if flush is None:
+            e0.record()
+            run_steps(count, stepper, batches)
+            e1.record()
+            barrier()
+            return max_over_ranks(e0.elapsed_time(e1))
+        # with the L2 flush between steps only the steps themselves are timed (event pairs per step)
+        evs = []
+        for i in range(count):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            stepper(batches[i % len(batches)])
+            b.record()
+            evs.append((a, b))
+        barrier()
+        return max_over_ranks(sum(a.elapsed_time(b) for a, b in evs))
+
+    # setup (not a warm-up step: the CUDA graph of every pool batch is captured once, training state restored),
+    # then EXACTLY --warmup untimed steps and --steps timed ones
+    for db in devb:
+        step(db)
+    barrier()
+    run_steps(args.warmup, step, devb)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_total = timed(args.steps, step, devb)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- e2e: host buffers -> device inside the timed region, loss read back every step -----------------------
+    pipe = E2EPipe(POOL, lambda s: devb[s].copy_from(host[s]))
+    pipe.run(POOL, lambda s: step(devb[s]))
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    loss_host = pipe.run(args.steps, lambda s: step(devb[s]))
+    e1.record()
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms_total = max_over_ranks(max(e0.elapsed_time(e1), wall_ms))
+    h2d = sum(host[i % POOL].h2d_bytes() for i in range(args.steps)) / args.steps
+
+    # ---- instrumented pass: per entry point CUDA-event times on the same steps (eager, same kernels) -----------
+    eager = train.TrainStep(model, opt, spec["loss"], 5, use_cuda_graph=False, world_size=world)
+    eager._side = eager._build = None  # one stream: every launch is timed alone, not beside the side-stream kernels
+    L = _lib.lib()
+    eager(devb[0])
+    ops.reset_launch_count()
+    eager(devb[0])
+    launches_per_step = ops.launch_count()
+    timer = KernelTimer(L, graphs)
+    L.hook = timer
+    reps = 2
+    for r in range(reps):
+        for i in range(POOL):
+            timer.num_edges = host[i].edge_index.size(1)
+            torch.cuda._sleep(20_000_000)  # ~10 ms of GPU idle spin: the host runs ahead, so the events bracket
+            eager(devb[i])                 # back-to-back device execution instead of Python launch gaps
+            torch.cuda.synchronize()
+    L.hook = None
+    agg = timer.summary()
+    kern_total = sum(d["ms"] for d in agg.values())
+    top = sorted(agg.items(), key=lambda kv: -kv[1]["ms"])
+    peak, peak_src = peaks()
+    breakdown = [{"kernel": n, "shape": tag, "calls_per_step": d["calls"] / (reps * POOL), "us_per_call": 1e3 * d["ms"] / d["calls"],
+                  "share": d["ms"] / kern_total, "GBps": (d["bytes"] / d["calls"]) / (d["ms"] / d["calls"] * 1e-3) / 1e9 if d["bytes"] else None}
+                 for (n, tag), d in top[:12]]
+    (dom_name, dom_tag), dom = top[0]
+    achieved = (dom["bytes"] / dom["calls"]) / (dom["ms"] / dom["calls"] * 1e-3) / 1e9
+    roofline = {"kernel": dom_name, "shape": dom_tag, "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
+                "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                "traffic": measured_traffic(dom_name, dom_tag),
+                "bytes_per_launch": dom["bytes"] // dom["calls"], "us_per_launch": round(1e3 * dom["ms"] / dom["calls"], 2),
+                "share_of_step_kernel_time": round(dom["ms"] / kern_total, 3)}
+
+    out = None
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        e2e_ms = e2e_ms_total / args.steps
+        out = {
+            "metric": "graphs/sec fwd+bwd", "value": round(total_graphs * args.steps / (ms_total * 1e-3), 1), "unit": "graphs/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "graphs_per_gpu": graphs, "global_graphs": total_graphs,
+                       "nodes_per_step_rank0": sum(h.num_nodes for h in host) / POOL,
+                       "edges_per_step_rank0": sum(h.edge_index.size(1) for h in host) / POOL,
+                       "model": spec["model"], "feat_in": spec["feat"], "hidden": spec["hidden"], "heads": spec.get("heads"),
+                       "knn_k": spec["k"], "loss": spec["loss"], "optimizer": "Adam", "dropout": spec["dropout"],
+                       "weight_decay": spec["weight_decay"], "train_mode": True,
+                       "parallelism": f"dp{world}", "cuda_graph": True, "l2_policy": l2_policy,
+                       "setup": f"{POOL} graph captures before the {args.warmup} warm-up steps (training state restored)"},
+            "e2e": {"value": round(total_graphs * args.steps / (e2e_ms_total * 1e-3), 1), "unit": "graphs/s",
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "ms_per_step": round(e2e_ms, 4),
+                    "h2d_GBps_per_rank": round(h2d / (e2e_ms * 1e-3) / 1e9, 2), "numa": numa, "last_loss": loss_host},
+            "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
+            "clocks": clocks, "roofline": roofline, "kernels": breakdown,
+        }
+    if not args.no_extras:
+        extras = secondary_legs(args, spec, graphs, total_graphs, world, rank, dev, host, devb, make_step, timed, barrier,
+                                max_over_ranks, opt)
+        if rank == 0:
+            out.update(extras)
+            if world == 1:
+                out["aggregation"] = aggregation_stress(dev, peak, peak_src)
+                out["cpu_baseline"] = cpu
+            else:
+                out["cpu_baseline"] = {"skipped": "N > 1: the CPU leg is timed at N = 1 only (torchrun pins OMP_NUM_THREADS=1 and "
+                                                  "the other ranks would spin in a barrier); see --impl reference"}
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+
+
+def secondary_legs(args, spec, graphs, total_graphs, world, rank, dev, host, devb, make_step, timed, barrier, max_over_ranks, opt):
+    """Extra keys, each a separate measurement that never replaces value / e2e: see the module docstring."""
+    import torch.distributed as dist
+
+    from lesion_gnn_b200 import ops, train, transforms
+    from lesion_gnn_b200.nn.pool import Segments
+    POOL = len(devb)
+    steps = max(20, min(args.steps, 300))
+    out = {}
+
+    def e2e_time(pipe, stepper, h2d_bytes):
+        pipe.run(POOL, stepper)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        loss = pipe.run(steps, stepper)
+        e1.record()
+        barrier()
+        ms = max_over_ranks(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3))
+        return {"value": round(total_graphs * steps / (ms * 1e-3), 1), "unit": "graphs/s", "ms_per_step": round(ms / steps, 4),
+                "steps": steps, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4,
+                "h2d_GBps_per_rank": round(h2d_bytes / (ms / steps * 1e-3) / 1e9, 2), "last_loss": loss}
+
+    # ---- parity_config: the configuration the parity tests check (dropout 0, weight decay 0), resident inputs ----
+    if spec["dropout"] != 0.0 or spec["weight_decay"] != 0.0:
+        _, _, step0 = make_step(dropout=0.0, weight_decay=0.0)
+        for db in devb:
+            step0(db)
+        ms = timed(steps, step0, devb)
+        out["parity_config"] = {"dropout": 0.0, "weight_decay": 0.0, "value": round(total_graphs * steps / (ms * 1e-3), 1),
+                                "unit": "graphs/s", "ms_per_step": round(ms / steps, 4), "steps": steps}
+        del step0
+
+    model, opt2, step = make_step()
+    for db in devb:
+        step(db)
+
+    # ---- e2e_bf16: node features cross PCIe as bf16 and are widened on the device (1e-2 bar: inputs are rounded) ----
+    x16_host = [hb.x.to(torch.bfloat16).pin_memory() for hb in host]
+    x16_dev = [torch.empty_like(t, device=dev) for t in x16_host]
+
+    def stage_bf16(s):
+        hb, db = host[s], devb[s]
+        x16_dev[s].copy_(x16_host[s], non_blocking=True)
+        db.batch.copy_(hb.batch, non_blocking=True)
+        db.y.copy_(hb.y, non_blocking=True)
+        db.edge_index.copy_(hb.edge_index, non_blocking=True)
+        db.x.copy_(x16_dev[s])  # bf16 -> fp32 on the device
+
+    h2d16 = sum(x16_host[s].numel() * 2 + sum(t.numel() * t.element_size() for t in (host[s].batch, host[s].y, host[s].edge_index))
+                for s in range(POOL)) / POOL
+    out["e2e_bf16"] = e2e_time(E2EPipe(POOL, stage_bf16), lambda s: step(devb[s]), h2d16)
+    out["e2e_bf16"]["note"] = "features rounded to bf16 on the host, fp32 arithmetic on the device; separate from the fp32 e2e"
+    del x16_host, x16_dev
+
+    # ---- e2e_resident_dataset: the reference's InMemoryDataset (datasets/base.py:49) lives in HBM; per step the batch is
+    # collated on the device by graph index (lgk_gather_rows) and its kNN graph + CSR are built inside the timed region
+    # (what datasets/datamodule.py:43-48,64-69 do per sample on the CPU) -------------------------------------------------
+    x_all = torch.cat([hb.x for hb in host]).to(dev)
+    pos_all = torch.cat([hb.pos for hb in host]).to(dev)
+    y_all = torch.cat([hb.y for hb in host]).to(dev)
+    counts_all = [c for hb in host for c in hb.counts]
+    starts, acc = [], 0
+    for c in counts_all:
+        starts.append(acc)
+        acc += c
+    gen = torch.Generator().manual_seed(4321 + rank)
+    sets = []
+    for s in range(POOL):
+        gid = torch.randperm(len(counts_all), generator=gen)[:graphs]
+        cnt = [counts_all[g] for g in gid.tolist()]
+        node_index = torch.cat([torch.arange(starts[g], starts[g] + counts_all[g]) for g in gid.tolist()])
+        batch = torch.repeat_interleave(torch.arange(graphs), torch.tensor(cnt))
+        sets.append({"gid": gid.pin_memory(), "node_index": node_index.pin_memory(), "batch": batch.pin_memory(), "counts": cnt,
+                     "E": transforms.knn_num_edges(cnt, spec["k"], True)})
+
+    class _Shape:  # what train.DeviceBatch needs to size its buffers
+        pass
+
+    rbatch = []
+    for st in sets:
+        n = st["node_index"].numel()
+        hb = _Shape()
+        hb.num_graphs, hb.num_nodes = graphs, n
+        hb.x = torch.empty(n, spec["feat"])
+        hb.batch = torch.empty(n, dtype=torch.long)
+        hb.y = torch.empty(graphs, dtype=torch.long)
+        hb.edge_index = torch.empty(2, st["E"], dtype=torch.long)
+        hb.edge_weight = None
+        db = train.DeviceBatch(hb, dev)
+        db.loss_weight = train.dp_loss_weight(graphs, total_graphs, world)
+        st["node_index_dev"] = torch.empty(n, dtype=torch.long, device=dev)
+        st["gid_dev"] = torch.empty(graphs, dtype=torch.long, device=dev)
+        st["pos"] = torch.empty(n, 2, dtype=pos_all.dtype, device=dev)
+        rbatch.append(db)
+
+    def stage_resident(s):
+        st, db = sets[s], rbatch[s]
+        st["node_index_dev"].copy_(st["node_index"], non_blocking=True)
+        st["gid_dev"].copy_(st["gid"], non_blocking=True)
+        db.batch.copy_(st["batch"], non_blocking=True)
+        ops.gather_rows(x_all, st["node_index_dev"], db.x)
+        ops.gather_rows(pos_all, st["node_index_dev"], st["pos"])
+        ops.gather_rows(y_all, st["gid_dev"], db.y)
+        seg = Segments.from_batch(db.batch, graphs)
+        ei = transforms.knn_graph(st["pos"], spec["k"], seg, loop=True, num_edges=st["E"])
+        db.edge_index.copy_(ei)
+        ei.record_stream(torch.cuda.current_stream())
+
+    for s in range(POOL):
+        stage_resident(s)
+    torch.cuda.synchronize()
+    for db in rbatch:
+        step(db)
+    h2dr = sum(st["node_index"].numel() * 8 * 2 + graphs * 8 for st in sets) / POOL
+    out["e2e_resident_dataset"] = e2e_time(E2EPipe(POOL, stage_resident), lambda s: step(rbatch[s]), h2dr)
+    out["e2e_resident_dataset"]["note"] = ("dataset of %d graphs resident in HBM; per step: node / graph indices host->device, "
+                                           "device gather of x, pos, y, kNN graph, CSR/CSC build, fwd, bwd, optimiser" % len(counts_all))
+    del x_all, pos_all, rbatch
+
+    # ---- collective_us: the gradient all-reduce alone ----------------------------------------------------------------
+    if world > 1:
+        for _ in range(10):
+            dist.all_reduce(opt.grad)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(100):
+            dist.all_reduce(opt.grad)
+        e1.record()
+        torch.cuda.synchronize()
+        out["collective_us"] = round(max_over_ranks(e0.elapsed_time(e1)) * 10.0, 2)
+        out["collective_bytes"] = int(opt.grad.numel() * 4)
+    return out
+
+
+def aggregation_stress(dev, peak: float, peak_src: str, graphs: int = 128) -> dict:
+    """BASELINE.json configs[3] / SURVEY.md 8d cfg 4: `graphs` superpixel graphs x 10 000 nodes, 128-d, kNN k=16
+    (loop=True), GCN-normalised aggregation forward (CSR) and backward (CSC), plus mean pooling.  X = 655 MB at
+    128 graphs, far beyond L2, so every launch streams from HBM.  The aggregation entries run the kernel the layers run
+    at this size (the windowed, row-blocked lgk_spmm_blocked); `*_lgk_spmm` are the register-landing kernel beside it."""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import data, ops, transforms
+    from lesion_gnn_b200.nn.pool import Segments
+    n, k, F = 10000, 16, 128
+    hb = data.synth_batch(graphs, n, F, seed=data.SEED, layout="raster")
+    N = hb.num_nodes
+    seg = Segments.from_batch(hb.batch.to(dev), graphs)
+    ei = transforms.knn_graph(hb.pos.float().to(dev), k, seg, loop=True, num_edges=N * k)
+    E = ei.size(1)
+    t_csr = _time_cuda(lambda: lg.CSRGraph.from_edge_index(ei, N), 3, 1)
+    g = lg.CSRGraph.from_edge_index(ei, N)
+    x = hb.x.to(dev)
+    dinv, _ = g.gcn_norm(False, True)
+    kw = dict(pre=dinv, post=dinv, self_mode=ops.SELF_REPLACE)
+    res = {"shape": {"graphs": graphs, "nodes": N, "edges": E, "feat": F, "k": k}, "peak": peak, "peak_source": peak_src, "unit": "GB/s"}
+    agg_bytes = 2 * N * F * 4 + 4 * E + 4 * (N + 1) + 8 * N
+
+    def entry(ms, nbytes):
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        return {"us": round(ms * 1e3, 1), "bytes": nbytes, "achieved": round(gbs, 1), "frac": round(gbs / peak, 4)}
+
+    t_quads = _time_cuda(lambda: ops.quad_build(g.rowptr, g.col), 3, 1)
+    qc, qr = g.quads("csr"), g.quads("csc")
+    assert ops.blocked_eligible(x, "sum", None)
+    res["quad_build"] = entry(t_quads, 8 * E + 5 * N)
+    res["gcn_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", quads=qc, **kw), 20), agg_bytes)
+    res["gcn_aggregate_bwd"] = entry(_time_cuda(lambda: ops.spmm(g.colptr, g.row, x, "sum", quads=qr, **kw), 20), agg_bytes)
+    plain = 2 * N * F * 4 + 4 * E + 4 * (N + 1)
+    res["sum_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", quads=qc), 20), plain)
+    res["mean_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "mean", quads=qc), 20), plain)
+    res["gcn_aggregate_fwd_lgk_spmm"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", **kw), 10), agg_bytes)
+    res["gcn_aggregate_bwd_lgk_spmm"] = entry(_time_cuda(lambda: ops.spmm(g.colptr, g.row, x, "sum", **kw), 10), agg_bytes)
+    res["sum_aggregate_fwd_lgk_spmm"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum"), 10), plain)
+    res["max_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "max", want_arg=True), 20), plain + 4 * N * F)
+    H, C = 4, 32
+    att = torch.randn(H * C, device=dev) * 0.1
+    a_s, a_d = ops.gat_alpha(x, att, att, H, C)
+    gat_bytes = 4 * (2 * N * F + 4 * N * H) + 4 * E + 4 * (N + 1)
+    res["gat_softmax_aggregate_fwd"] = entry(_time_cuda(lambda: ops.gat_fwd(g.rowptr, g.col, x, a_s, a_d, None, H, C, 0.2, True), 20), gat_bytes)
+    pool_bytes = 4 * (N * F + graphs * F) + 4 * (graphs + 1)
+    res["global_mean_pool_fwd"] = entry(_time_cuda(lambda: ops.pool_fwd(x, seg.ptr, True, True, False), 20), pool_bytes)
+    res["global_mean_max_pool_fwd"] = entry(_time_cuda(lambda: ops.pool_fwd(x, seg.ptr, True, True, True), 20), pool_bytes + 8 * graphs * F)
+    res["csr_csc_build"] = entry(t_csr, 28 * E + 8 * (N + 1))
+    del x, g, ei
+    torch.cuda.empty_cache()
+    return res
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU legs: the oracle (op-for-op PyG restatement, oracle/pyg_semantics.py) on the host cores
+# ------------------------------------------------------------------------------------------------------
+def _oracle_stepper(spec: dict):
+    from oracle import pyg_semantics as O
+    torch.set_num_threads(os.cpu_count() or 1)  # explicit: torchrun exports OMP_NUM_THREADS=1
+    torch.manual_seed(1234)
+    model = build_model(spec, O).train()
+    optim = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=spec["weight_decay"])
+    graphs = min(spec["graphs"], 4096)
+    batches = make_host_batches(spec, graphs, 0, 2)
+
+    def one(i):
+        hb = batches[i % len(batches)]
+        return O.training_step(model, optim, hb.x, hb.edge_index, hb.batch, hb.y, hb.num_graphs, spec["loss"], 5)
+    return one, graphs
+
+
+def cpu_baseline(spec: dict, name: str, budget_s: float) -> dict:
+    one, graphs = _oracle_stepper(spec)
+    one(0)
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        one(n)
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or n >= 200:
+            break
+    return {"value": round(graphs * n / dt, 1), "unit": "graphs/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{n} full steps of {name} ({graphs} graphs each, fwd+loss+bwd+Adam, fp32, dropout {spec['dropout']}) in {dt:.1f} s "
+                      "after 1 warm-up", "ms_per_step": round(1e3 * dt / n, 2)}
+
+
+def run_reference(args):
+    """The reference's CPU path for this workload = the oracle (PyG is not installable here: SURVEY.md 8c), all
+    host threads, the same model / dropout / weight decay as the CUDA arm.  Under torchrun only rank 0 works; the
+    step is always one rank's batch (`graphs` graphs), whatever --gpus says: a throughput, not a scaling run."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    spec = WORKLOADS[args.workload]
+    one, graphs = _oracle_stepper(spec)
+    warm = max(args.warmup, 1)
+    t_w = time.perf_counter()
+    one(0)
+    per_step = time.perf_counter() - t_w
+    warm = min(warm, max(1, int(20.0 / max(per_step, 1e-3))))
+    for i in range(1, warm):
+        one(i)
+    steps = max(1, min(args.steps, int(120.0 / max(per_step, 1e-3)), 100))
+    t0 = time.perf_counter()
+    for i in range(steps):
+        one(i)
+    dt = time.perf_counter() - t0
+    v = round(graphs * steps / dt, 1)
+    cores = torch.get_num_threads()
+    print(json.dumps({
+        "impl": "reference", "metric": "graphs/sec fwd+bwd", "value": v, "unit": "graphs/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": round(1e3 * dt / steps, 3), "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "graphs_per_gpu": graphs, "global_graphs": graphs, "model": spec["model"],
+                   "feat_in": spec["feat"], "hidden": spec["hidden"], "heads": spec.get("heads"), "knn_k": spec["k"], "loss": spec["loss"],
+                   "optimizer": "Adam", "dropout": spec["dropout"], "weight_decay": spec["weight_decay"], "train_mode": True,
+                   "device": "cpu", "note": "one rank's batch per step on the host cores, whatever --gpus says"},
+        "cpu_baseline": {"value": v, "unit": "graphs/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} full steps of {graphs} graphs on {cores} host threads"},
+        "e2e": {"value": v, "unit": "graphs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def _keep_stdout_for_the_json_line():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the
+    first collective when NCCL_DEBUG is set on the box), so file descriptor 1 is pointed at stderr for the whole run
+    and `print` gets a private duplicate of the real stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    _keep_stdout_for_the_json_line()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -294,6 +294,12 @@ LGK_API int lgk_adam_step(float* param, float* grad, float* exp_avg, float* exp_
 LGK_API int lgk_clamped_regression_loss(const float* logits, const int64_t* y, int64_t n, float lo, float hi, int kind,
                                 float grad_scale, float* loss_out, float* dlogits, void* stream);
 
+/* out[i, :] = src[index[i], :], rows of row_bytes bytes (a multiple of 4), index int64 in [0, src_rows): collation of a
+ * device-resident dataset by node index -- Batch.from_data_list of the reference's DataLoader (datasets/datamodule.py:64-69)
+ * without the host round trip.  Rows with an out-of-range index are left untouched.                              */
+LGK_API int lgk_gather_rows(const void* src, const int64_t* index, void* out, int64_t n, int64_t row_bytes,
+                    int64_t src_rows, void* stream);
+
 /* torch.optim.SGD over one flat fp32 buffer (reference models/base.py:167-168: lr and weight_decay; momentum /
  * nesterov with dampening 0 are supported through a zero-initialised momentum_buf, NULL when momentum == 0):
  * g = grad_scale * grad + weight_decay * p; [b = momentum * b + g; g = nesterov ? g + momentum * b : b;] p -= lr * g.

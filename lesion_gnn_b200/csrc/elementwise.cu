@@ -276,3 +276,38 @@ extern "C" int lgk_cross_entropy_loss(const float* logits, const int64_t* y, con
   LGK_CHECK_LAUNCH("cross_entropy_kernel");
   return LGK_OK;
 }
+
+// ---- row gather: out[i, :] = src[index[i], :] (collation of a device-resident dataset by node index: what
+// Batch.from_data_list does on the host in the reference's DataLoader, datasets/datamodule.py:64-69) --------------------
+namespace lgk {
+namespace {
+__global__ void __launch_bounds__(256) gather_rows_kernel(const uint32_t* __restrict__ src, const int64_t* __restrict__ index,
+                                                          uint32_t* __restrict__ out, int64_t n, int64_t row_words, int64_t src_rows) {
+  const int lane = threadIdx.x & 31;
+  const int64_t i = int64_t(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (i >= n) return;
+  const int64_t j = index[i];
+  if (uint64_t(j) >= uint64_t(src_rows)) return;  // out of range: the row is left untouched
+  const uint32_t* s = src + j * row_words;
+  uint32_t* d = out + i * row_words;
+  if ((row_words & 3) == 0 && ((reinterpret_cast<uintptr_t>(s) | reinterpret_cast<uintptr_t>(d)) & 15) == 0) {
+    for (int64_t w = lane; w < row_words / 4; w += 32) reinterpret_cast<uint4*>(d)[w] = __ldg(reinterpret_cast<const uint4*>(s) + w);
+  } else {
+    for (int64_t w = lane; w < row_words; w += 32) d[w] = __ldg(s + w);
+  }
+}
+}  // namespace
+}  // namespace lgk
+
+extern "C" int lgk_gather_rows(const void* src, const int64_t* index, void* out, int64_t n, int64_t row_bytes,
+                               int64_t src_rows, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && row_bytes >= 0 && src_rows >= 0, LGK_ERR_BAD_ARG, "lgk_gather_rows: negative size");
+  if (n == 0 || row_bytes == 0) return LGK_OK;
+  LGK_REQUIRE(src && index && out, LGK_ERR_BAD_ARG, "lgk_gather_rows: null pointer");
+  LGK_REQUIRE(row_bytes % 4 == 0, LGK_ERR_UNSUPPORTED, "lgk_gather_rows: rows must be a multiple of 4 bytes");
+  lgk::gather_rows_kernel<<<unsigned(ceil_div(n, 8)), 256, 0, stream>>>(static_cast<const uint32_t*>(src), index,
+                                                                        static_cast<uint32_t*>(out), n, row_bytes / 4, src_rows);
+  LGK_CHECK_LAUNCH("gather_rows_kernel");
+  return LGK_OK;
+}

@@ -474,3 +474,15 @@ def cross_entropy_loss(logits: Tensor, y: Tensor, class_weight: Optional[Tensor]
            _chk(class_weight, torch.float32, "class_weight"), n, c, float(grad_scale), loss.data_ptr(),
            _chk(dl, torch.float32, "dlogits"), _stream())
     return loss, dl
+
+
+def gather_rows(src: Tensor, index: Tensor, out: Optional[Tensor] = None) -> Tensor:
+    """out[i] = src[index[i]] for a [R, ...] tensor of any 4-byte-multiple row size (device-side collation by node index)"""
+    L = _lib.lib()
+    n = index.numel()
+    if out is None:
+        out = torch.empty((n,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    row_bytes = src[0].numel() * src.element_size() if src.size(0) else 0
+    L.call("lgk_gather_rows", _chk(src, None, "src"), _chk(index, torch.int64, "index"), _chk(out, src.dtype, "out"), n, row_bytes,
+           src.size(0), _stream())
+    return out
