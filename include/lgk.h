@@ -52,7 +52,8 @@ enum { LGK_ACT_NONE = 0, LGK_ACT_ELU = 1, LGK_ACT_RELU = 2 };
 
 LGK_API const char* lgk_last_error(void);
 LGK_API int lgk_version(void);
-/* number of kernel launches this thread has enqueued through the library since the last reset */
+/* number of kernel launches enqueued through the library (by any thread of the process: autograd runs the backward on
+ * its own) since the last reset */
 LGK_API int64_t lgk_launch_count(void);
 LGK_API void lgk_reset_launch_count(void);
 
@@ -299,6 +300,32 @@ LGK_API int lgk_clamped_regression_loss(const float* logits, const int64_t* y, i
  * without the host round trip.  Rows with an out-of-range index are left untouched.                              */
 LGK_API int lgk_gather_rows(const void* src, const int64_t* index, void* out, int64_t n, int64_t row_bytes,
                     int64_t src_rows, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * BatchNorm1d + activation + dropout of GIN's MLP (torch_geometric.nn.models.MLP = Linear -> BatchNorm1d -> ELU ->
+ * Dropout -> Linear; reference models/gin.py:23) and the activation + dropout after every GIN layer (gin.py:31-32)
+ * ------------------------------------------------------------------------------------------------ */
+/* y = dropout(act(batch_norm(x))), x, y [n, d] fp32.  training != 0: batch statistics (biased variance), running_mean /
+ * running_var updated in place with `momentum` (unbiased variance) and *num_batches_tracked += 1 (each may be NULL), n > 1;
+ * training == 0: the running statistics normalise.  save_mean / save_invstd [d] receive the statistics used (the backward
+ * reads them).  weight / bias may be NULL (affine=False).  dropout: counter RNG keyed on (seed, *seed_dev, element), the
+ * same function in the backward -- no mask is stored.  workspace: lgk_bn_workspace_bytes(n, d).                    */
+LGK_API int64_t lgk_bn_workspace_bytes(int64_t n, int64_t d);
+LGK_API int lgk_bn_act_fwd(const float* x, const float* weight, const float* bias, float* running_mean, float* running_var,
+                   int64_t* num_batches_tracked, float* y, float* save_mean, float* save_invstd, int64_t n, int64_t d,
+                   float eps, float momentum, int training, int act, float dropout_p, uint64_t seed, const int64_t* seed_dev,
+                   void* workspace, int64_t workspace_bytes, void* stream);
+/* dx, dweight (+)= sum g xhat, dbias (+)= sum g with g = dy * dropout keep * act'(z), recomputed from x and the saved
+ * statistics; training != 0: the batch statistics take part in dx.  dweight / dbias may be NULL.                  */
+LGK_API int lgk_bn_act_bwd(const float* x, const float* dy, const float* weight, const float* bias, const float* save_mean,
+                   const float* save_invstd, float* dx, float* dweight, float* dbias, int accumulate, int64_t n, int64_t d,
+                   int training, int act, float dropout_p, uint64_t seed, const int64_t* seed_dev,
+                   void* workspace, int64_t workspace_bytes, void* stream);
+/* y = dropout(act(x)) and dx = dy * keep * act'(x) (x = the pre-activation input), n elements fp32 */
+LGK_API int lgk_act_dropout_fwd(const float* x, float* y, int64_t n, int act, float dropout_p, uint64_t seed,
+                        const int64_t* seed_dev, void* stream);
+LGK_API int lgk_act_dropout_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, float dropout_p, uint64_t seed,
+                        const int64_t* seed_dev, void* stream);
 
 /* torch.optim.SGD over one flat fp32 buffer (reference models/base.py:167-168: lr and weight_decay; momentum /
  * nesterov with dampening 0 are supported through a zero-initialised momentum_buf, NULL when momentum == 0):

@@ -2,11 +2,13 @@
 // drgnet.py:55), the fused multi-tensor Adam/AdamW step over one flat buffer (torch.optim.Adam at
 // models/base.py:162-170), and the library-global error / launch bookkeeping.
 #include "common.cuh"
+#include <atomic>
 
 namespace lgk {
 
 static thread_local char g_error[512] = "";
-static thread_local int64_t g_launches = 0;
+// process-wide: autograd runs the backward launches on its own thread
+static std::atomic<int64_t> g_launches{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -14,7 +16,7 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_error, sizeof(g_error), fmt, ap);
   va_end(ap);
 }
-void count_launch(int n) { g_launches += n; }
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 namespace {
 
@@ -95,8 +97,8 @@ using namespace lgk;
 
 extern "C" const char* lgk_last_error(void) { return g_error; }
 extern "C" int lgk_version(void) { return 100; }
-extern "C" int64_t lgk_launch_count(void) { return g_launches; }
-extern "C" void lgk_reset_launch_count(void) { g_launches = 0; }
+extern "C" int64_t lgk_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+extern "C" void lgk_reset_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }
 
 static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 

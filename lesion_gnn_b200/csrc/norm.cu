@@ -1,0 +1,309 @@
+// BatchNorm1d + activation + dropout of GIN's MLP as three launches forward and three backward
+// (torch_geometric.nn.models.MLP: Linear -> BatchNorm1d -> ELU -> Dropout -> Linear; reference models/gin.py:23,
+// SURVEY.md 8a a-4), and the activation + dropout pair that follows every GIN layer (gin.py:31-32).
+//
+// HBM-bound column statistics over a tall [N, d] matrix (d = 32..512): a CTA owns a slab of rows and all columns, a
+// thread a float4 of columns; per slab and column (mean, M2) are formed around the slab's first row (no cancellation),
+// the slabs are combined with Chan's formula in double precision by a one-CTA finalise that also updates the running
+// statistics (momentum, unbiased variance, num_batches_tracked) -- no atomics, deterministic.  The normalise + affine +
+// ELU + dropout pass and the two backward passes recompute everything from x and the saved (mean, invstd): nothing of
+// size [N, d] is stored besides the layer's own input and output.
+#include "common.cuh"
+#include <math.h>
+
+namespace lgk {
+namespace {
+
+constexpr int kThreads = 256;
+
+int norm_slabs(int64_t n) {
+  int64_t s = ceil_div(n, 256);
+  if (s > 2 * kNumSMs) s = 2 * kNumSMs;
+  return int(s < 1 ? 1 : s);
+}
+
+// counter RNG for feature dropout: (seed, element index) -> uniform in [0,1)
+__device__ __forceinline__ float uniform_hash64(uint64_t seed, uint64_t idx) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (idx + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z = z ^ (z >> 31);
+  return float(uint32_t(z >> 40)) * (1.0f / 16777216.0f);
+}
+__device__ __forceinline__ uint64_t launch_seed(uint64_t seed, const int64_t* seed_dev) {
+  return seed_dev ? seed + 0xD1B54A32D192ED03ull * uint64_t(__ldg(seed_dev)) : seed;
+}
+__device__ __forceinline__ float act_fwd(float z, int act) {
+  if (act == LGK_ACT_ELU) return elu1(z);
+  if (act == LGK_ACT_RELU) return fmaxf(z, 0.f);
+  return z;
+}
+// derivative of the activation at pre-activation z
+__device__ __forceinline__ float act_grad(float z, int act) {
+  if (act == LGK_ACT_ELU) return z > 0.f ? 1.f : expm1f(z) + 1.f;
+  if (act == LGK_ACT_RELU) return z > 0.f ? 1.f : 0.f;
+  return 1.f;
+}
+
+// ---- pass 1: per-slab column statistics around the slab's first row ------------------------------------------
+// partial[slab][0][c] = sum (x - K_c), partial[slab][1][c] = sum (x - K_c)^2, partial[slab][2][c] = K_c
+__global__ void __launch_bounds__(kThreads) bn_stats_partial_kernel(const float* __restrict__ x, float* __restrict__ partial,
+                                                                    int64_t n, int d, int64_t slab_rows) {
+  __shared__ float red[2][kThreads];
+  const int64_t r0 = int64_t(blockIdx.x) * slab_rows, r1 = min(n, r0 + slab_rows);
+  float* p = partial + int64_t(blockIdx.x) * 3 * d;
+  for (int c0 = 0; c0 < d; c0 += kThreads) {
+    const int width = min(kThreads, d - c0);
+    const int lanes = kThreads / width;  // row lanes per column
+    const int c = threadIdx.x % width, rl = threadIdx.x / width;
+    float s = 0.f, q = 0.f;
+    const float K = (r0 < r1) ? __ldg(x + r0 * d + c0 + c) : 0.f;
+    if (rl < lanes) {
+      for (int64_t r = r0 + rl; r < r1; r += lanes) {
+        const float v = ld_stream_f32(x + r * d + c0 + c) - K;
+        s += v;
+        q = fmaf(v, v, q);
+      }
+    }
+    __syncthreads();
+    red[0][threadIdx.x] = s;
+    red[1][threadIdx.x] = q;
+    __syncthreads();
+    if (rl == 0) {
+      for (int l = 1; l < lanes; ++l) { s += red[0][l * width + c]; q += red[1][l * width + c]; }
+      p[c0 + c] = s;
+      p[d + c0 + c] = q;
+      p[2 * d + c0 + c] = K;
+    }
+  }
+}
+
+// ---- pass 2: combine the slabs (Chan), write mean / invstd, update the running statistics -----------------------
+__global__ void __launch_bounds__(kThreads) bn_stats_finalize_kernel(const float* __restrict__ partial, int slabs, int64_t n, int d,
+                                                                     int64_t slab_rows, float eps, float momentum,
+                                                                     float* __restrict__ mean_out, float* __restrict__ invstd_out,
+                                                                     float* __restrict__ running_mean, float* __restrict__ running_var,
+                                                                     int64_t* __restrict__ num_batches_tracked) {
+  for (int c = blockIdx.x * kThreads + threadIdx.x; c < d; c += gridDim.x * kThreads) {
+    double cnt = 0.0, mean = 0.0, m2 = 0.0;
+    for (int sl = 0; sl < slabs; ++sl) {
+      const int64_t rows = min(n, int64_t(sl + 1) * slab_rows) - int64_t(sl) * slab_rows;
+      if (rows <= 0) break;
+      const float* p = partial + int64_t(sl) * 3 * d;
+      const double nb = double(rows), sb = double(p[c]), qb = double(p[d + c]), Kb = double(p[2 * d + c]);
+      const double mb = Kb + sb / nb, m2b = qb - sb * sb / nb;
+      const double delta = mb - mean, tot = cnt + nb;
+      mean += delta * nb / tot;
+      m2 += m2b + delta * delta * cnt * nb / tot;
+      cnt = tot;
+    }
+    const double var = cnt > 0 ? m2 / cnt : 0.0;
+    mean_out[c] = float(mean);
+    invstd_out[c] = float(1.0 / sqrt(var + double(eps)));
+    if (running_mean) running_mean[c] = float((1.0 - momentum) * double(running_mean[c]) + momentum * mean);
+    if (running_var) running_var[c] = float((1.0 - momentum) * double(running_var[c]) + momentum * (cnt > 1 ? m2 / (cnt - 1) : var));
+  }
+  if (num_batches_tracked && blockIdx.x == 0 && threadIdx.x == 0) *num_batches_tracked += 1;
+}
+
+// eval mode: mean / invstd from the running statistics
+__global__ void __launch_bounds__(kThreads) bn_eval_stats_kernel(const float* __restrict__ running_mean, const float* __restrict__ running_var,
+                                                                 float eps, int d, float* __restrict__ mean_out, float* __restrict__ invstd_out) {
+  const int c = blockIdx.x * kThreads + threadIdx.x;
+  if (c < d) {
+    mean_out[c] = running_mean[c];
+    invstd_out[c] = 1.0f / sqrtf(running_var[c] + eps);
+  }
+}
+
+// ---- pass 3: y = dropout(act((x - mean) * invstd * w + b)) --------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) bn_act_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                                                              const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                              float* __restrict__ y, int64_t total, int d, int act, float drop_p, uint64_t seed,
+                                                              const int64_t* __restrict__ seed_dev) {
+  const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
+  if (i >= total) return;
+  const int c = int(i % d);
+  const float scale = __ldg(invstd + c) * (w ? __ldg(w + c) : 1.f);
+  const float shift = (b ? __ldg(b + c) : 0.f) - __ldg(mean + c) * scale;
+  float v = act_fwd(fmaf(ld_stream_f32(x + i), scale, shift), act);
+  if (drop_p > 0.f) v = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : v * (1.f / (1.f - drop_p));
+  y[i] = v;
+}
+
+// ---- backward pass 1: per-slab sums of g and g * xhat, g = dy * keep * act'(z) ------------------------------------
+__global__ void __launch_bounds__(kThreads) bn_bwd_partial_kernel(const float* __restrict__ x, const float* __restrict__ dy, const float* __restrict__ w,
+                                                                  const float* __restrict__ b, const float* __restrict__ mean,
+                                                                  const float* __restrict__ invstd, float* __restrict__ partial, int64_t n,
+                                                                  int d, int64_t slab_rows, int act, float drop_p, uint64_t seed,
+                                                                  const int64_t* __restrict__ seed_dev) {
+  __shared__ float red[2][kThreads];
+  const int64_t r0 = int64_t(blockIdx.x) * slab_rows, r1 = min(n, r0 + slab_rows);
+  float* p = partial + int64_t(blockIdx.x) * 2 * d;
+  const uint64_t sd = drop_p > 0.f ? launch_seed(seed, seed_dev) : 0;
+  const float keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  for (int c0 = 0; c0 < d; c0 += kThreads) {
+    const int width = min(kThreads, d - c0);
+    const int lanes = kThreads / width;
+    const int c = threadIdx.x % width, rl = threadIdx.x / width;
+    const float m = __ldg(mean + c0 + c), is = __ldg(invstd + c0 + c);
+    const float wc = w ? __ldg(w + c0 + c) : 1.f, bc = b ? __ldg(b + c0 + c) : 0.f;
+    float sg = 0.f, sgx = 0.f;
+    if (rl < lanes) {
+      for (int64_t r = r0 + rl; r < r1; r += lanes) {
+        const int64_t i = r * d + c0 + c;
+        const float xh = (ld_stream_f32(x + i) - m) * is;
+        float g = ld_stream_f32(dy + i) * act_grad(fmaf(xh, wc, bc), act);
+        if (drop_p > 0.f) g = uniform_hash64(sd, uint64_t(i)) < drop_p ? 0.f : g * keep;
+        sg += g;
+        sgx = fmaf(g, xh, sgx);
+      }
+    }
+    __syncthreads();
+    red[0][threadIdx.x] = sg;
+    red[1][threadIdx.x] = sgx;
+    __syncthreads();
+    if (rl == 0) {
+      for (int l = 1; l < lanes; ++l) { sg += red[0][l * width + c]; sgx += red[1][l * width + c]; }
+      p[c0 + c] = sg;          // -> d bias
+      p[d + c0 + c] = sgx;     // -> d weight
+    }
+  }
+}
+
+// ---- backward pass 3: dx (training: batch statistics take part in the gradient; eval: plain scale) ----------------
+// sums[0..d) = sum g, sums[d..2d) = sum g * xhat.  Block 0 also adds them into the parameter gradients when asked to.
+__global__ void __launch_bounds__(kThreads) bn_bwd_dx_kernel(const float* __restrict__ x, const float* __restrict__ dy, const float* __restrict__ w,
+                                                             const float* __restrict__ b, const float* __restrict__ mean,
+                                                             const float* __restrict__ invstd, const float* __restrict__ sums,
+                                                             float* __restrict__ dx, int64_t n, int d, int training, int act, float drop_p,
+                                                             uint64_t seed, const int64_t* __restrict__ seed_dev) {
+  const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
+  if (i >= n * d) return;
+  const int c = int(i % d);
+  const float m = __ldg(mean + c), is = __ldg(invstd + c);
+  const float wc = w ? __ldg(w + c) : 1.f, bc = b ? __ldg(b + c) : 0.f;
+  const float xh = (ld_stream_f32(x + i) - m) * is;
+  float g = ld_stream_f32(dy + i) * act_grad(fmaf(xh, wc, bc), act);
+  if (drop_p > 0.f) g = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : g * (1.f / (1.f - drop_p));
+  float r;
+  if (training) {
+    const float inv_n = 1.f / float(n);
+    r = wc * is * (g - (__ldg(sums + c) + xh * __ldg(sums + d + c)) * inv_n);
+  } else {
+    r = g * wc * is;
+  }
+  dx[i] = r;
+}
+
+// ---- activation + dropout (the ELU and Dropout after every GIN layer, gin.py:31-32) -------------------------------
+__global__ void __launch_bounds__(kThreads) act_dropout_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t total, int act,
+                                                                   float drop_p, uint64_t seed, const int64_t* __restrict__ seed_dev) {
+  const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
+  if (i >= total) return;
+  float v = act_fwd(ld_stream_f32(x + i), act);
+  if (drop_p > 0.f) v = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : v * (1.f / (1.f - drop_p));
+  y[i] = v;
+}
+// dx = dy * keep * act'(x): x is the pre-activation input
+__global__ void __launch_bounds__(kThreads) act_dropout_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dx,
+                                                                   int64_t total, int act, float drop_p, uint64_t seed,
+                                                                   const int64_t* __restrict__ seed_dev) {
+  const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
+  if (i >= total) return;
+  float g = ld_stream_f32(dy + i) * act_grad(ld_stream_f32(x + i), act);
+  if (drop_p > 0.f) g = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : g * (1.f / (1.f - drop_p));
+  dx[i] = g;
+}
+
+}  // namespace
+}  // namespace lgk
+
+using namespace lgk;
+
+extern "C" int64_t lgk_bn_workspace_bytes(int64_t n, int64_t d) {
+  if (n <= 0 || d <= 0) return 0;
+  return (int64_t(norm_slabs(n)) * 3 * d + 2 * d) * 4;
+}
+
+extern "C" int lgk_bn_act_fwd(const float* x, const float* weight, const float* bias, float* running_mean, float* running_var,
+                              int64_t* num_batches_tracked, float* y, float* save_mean, float* save_invstd, int64_t n, int64_t d,
+                              float eps, float momentum, int training, int act, float dropout_p, uint64_t seed,
+                              const int64_t* seed_dev, void* workspace, int64_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && d > 0 && d < (1 << 24), LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: bad sizes");
+  LGK_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: dropout must be in [0,1)");
+  LGK_REQUIRE(act >= LGK_ACT_NONE && act <= LGK_ACT_RELU, LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: bad activation");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(x && y && save_mean && save_invstd, LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: null pointer");
+  if (training) {
+    LGK_REQUIRE(n > 1, LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: batch statistics need more than one row (as nn.BatchNorm1d)");
+    LGK_REQUIRE(workspace && workspace_bytes >= lgk_bn_workspace_bytes(n, d), LGK_ERR_WORKSPACE, "lgk_bn_act_fwd: workspace too small");
+    const int slabs = norm_slabs(n);
+    const int64_t slab_rows = ceil_div(n, slabs);
+    float* partial = static_cast<float*>(workspace);
+    bn_stats_partial_kernel<<<slabs, kThreads, 0, stream>>>(x, partial, n, int(d), slab_rows);
+    LGK_CHECK_LAUNCH("bn_stats_partial_kernel");
+    bn_stats_finalize_kernel<<<unsigned(std::min<int64_t>(ceil_div(d, kThreads), 64)), kThreads, 0, stream>>>(
+        partial, slabs, n, int(d), slab_rows, eps, momentum, save_mean, save_invstd, running_mean, running_var, num_batches_tracked);
+    LGK_CHECK_LAUNCH("bn_stats_finalize_kernel");
+  } else {
+    LGK_REQUIRE(running_mean && running_var, LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: eval mode needs the running statistics");
+    bn_eval_stats_kernel<<<unsigned(ceil_div(d, kThreads)), kThreads, 0, stream>>>(running_mean, running_var, eps, int(d), save_mean, save_invstd);
+    LGK_CHECK_LAUNCH("bn_eval_stats_kernel");
+  }
+  bn_act_fwd_kernel<<<unsigned(ceil_div(n * d, kThreads)), kThreads, 0, stream>>>(x, weight, bias, save_mean, save_invstd, y, n * d, int(d), act,
+                                                                                  dropout_p, seed, seed_dev);
+  LGK_CHECK_LAUNCH("bn_act_fwd_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_bn_act_bwd(const float* x, const float* dy, const float* weight, const float* bias, const float* save_mean,
+                              const float* save_invstd, float* dx, float* dweight, float* dbias, int accumulate, int64_t n,
+                              int64_t d, int training, int act, float dropout_p, uint64_t seed, const int64_t* seed_dev,
+                              void* workspace, int64_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && d > 0 && d < (1 << 24), LGK_ERR_BAD_ARG, "lgk_bn_act_bwd: bad sizes");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(x && dy && save_mean && save_invstd && dx, LGK_ERR_BAD_ARG, "lgk_bn_act_bwd: null pointer");
+  LGK_REQUIRE(workspace && workspace_bytes >= lgk_bn_workspace_bytes(n, d), LGK_ERR_WORKSPACE, "lgk_bn_act_bwd: workspace too small");
+  const int slabs = norm_slabs(n);
+  const int64_t slab_rows = ceil_div(n, slabs);
+  float* partial = static_cast<float*>(workspace);
+  float* sums = partial + int64_t(slabs) * 3 * d;  // [2 d]: sum g, sum g xhat
+  bn_bwd_partial_kernel<<<slabs, kThreads, 0, stream>>>(x, dy, weight, bias, save_mean, save_invstd, partial, n, int(d), slab_rows, act,
+                                                        dropout_p, seed, seed_dev);
+  LGK_CHECK_LAUNCH("bn_bwd_partial_kernel");
+  slab_reduce_kernel<<<slab_reduce_grid(2 * d), 256, 0, stream>>>(partial, sums, sums + d, d, d, slabs, 0);
+  LGK_CHECK_LAUNCH("slab_reduce_kernel(bn)");
+  if (dweight || dbias) {  // parameter gradients: (added to) the caller's buffers, same fixed order
+    slab_reduce_kernel<<<slab_reduce_grid(2 * d), 256, 0, stream>>>(partial, dbias, dweight, d, d, slabs, accumulate);
+    LGK_CHECK_LAUNCH("slab_reduce_kernel(bn params)");
+  }
+  bn_bwd_dx_kernel<<<unsigned(ceil_div(n * d, kThreads)), kThreads, 0, stream>>>(x, dy, weight, bias, save_mean, save_invstd, sums, dx, n, int(d),
+                                                                                 training, act, dropout_p, seed, seed_dev);
+  LGK_CHECK_LAUNCH("bn_bwd_dx_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_act_dropout_fwd(const float* x, float* y, int64_t n, int act, float dropout_p, uint64_t seed,
+                                   const int64_t* seed_dev, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_act_dropout_fwd: bad arguments");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(x && y, LGK_ERR_BAD_ARG, "lgk_act_dropout_fwd: null pointer");
+  act_dropout_fwd_kernel<<<unsigned(ceil_div(n, kThreads)), kThreads, 0, stream>>>(x, y, n, act, dropout_p, seed, seed_dev);
+  LGK_CHECK_LAUNCH("act_dropout_fwd_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_act_dropout_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, float dropout_p, uint64_t seed,
+                                   const int64_t* seed_dev, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_act_dropout_bwd: bad arguments");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(x && dy && dx, LGK_ERR_BAD_ARG, "lgk_act_dropout_bwd: null pointer");
+  act_dropout_bwd_kernel<<<unsigned(ceil_div(n, kThreads)), kThreads, 0, stream>>>(x, dy, dx, n, act, dropout_p, seed, seed_dev);
+  LGK_CHECK_LAUNCH("act_dropout_bwd_kernel");
+  return LGK_OK;
+}

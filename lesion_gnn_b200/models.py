@@ -86,9 +86,11 @@ class GIN(nn.Module):
 
     def forward(self, x: Tensor, edge_index, batch) -> Tensor:
         x = self.in_proj(x)
-        for conv in self.convs:
-            x = elu(conv(x, edge_index))
-            x = self.dropout(x)
+        from .nn import functional as F
+        from .nn.conv import _DROPOUT_CLOCK, _next_seed
+        p = self.dropout.p if self.training else 0.0
+        for conv in self.convs:  # F.elu + nn.Dropout of gin.py:31-32 as one launch
+            x = F.act_dropout(conv(x, edge_index), ACT_ELU, p, _next_seed() if p > 0 else 0, _DROPOUT_CLOCK[0] if p > 0 else None)
         return self.out_proj(_readout(x, batch, self.pooling))
 
 

@@ -193,14 +193,18 @@ class MLP(nn.Module):
 
     def forward(self, x: Tensor) -> Tensor:
         for i, (lin, norm) in enumerate(zip(self.lins, self.norms)):
+            p = self.dropout[i] if self.training else 0.0
             if isinstance(norm, nn.Identity):
                 x = lin(x, act=ACT_ELU)  # ELU fused into the transform's epilogue
-            else:
-                x = F.elu(norm(lin(x)))
-            x = TF.dropout(x, p=self.dropout[i], training=self.training)
+                if p > 0:
+                    x = F.act_dropout(x, ACT_NONE, p, _next_seed(), _DROPOUT_CLOCK[0])
+            else:  # BatchNorm1d + ELU + Dropout: lgk_bn_act_fwd / bwd (no ATen kernel inside the MLP)
+                x = F.bn_act(lin(x), norm.module, ACT_ELU, p, _next_seed() if p > 0 else 0, _DROPOUT_CLOCK[0] if p > 0 else None)
         if self.plain_last:
             x = self.lins[-1](x)
-            x = TF.dropout(x, p=self.dropout[-1], training=self.training)
+            p = self.dropout[-1] if self.training else 0.0
+            if p > 0:
+                x = F.act_dropout(x, ACT_NONE, p, _next_seed(), _DROPOUT_CLOCK[0])
         return x
 
 

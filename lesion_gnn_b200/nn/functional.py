@@ -328,6 +328,68 @@ def elu(x: Tensor) -> Tensor:
     return _Elu.apply(x)
 
 
+class _BnAct(torch.autograd.Function):
+    """dropout(act(batch_norm(x))) -- BatchNorm1d + ELU + Dropout of PyG's MLP (reference models/gin.py:23) in three
+    launches; saves x and the [d] statistics only (the mask is a function of (seed, device clock, element))."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, bn, act, dropout_p, seed, seed_dev):
+        x = x.contiguous()
+        training = bn.training or bn.running_mean is None
+        if bn.momentum is None:
+            raise NotImplementedError("BatchNorm with momentum=None (cumulative average) is not on the reference's path")
+        track = bn.track_running_stats and bn.training
+        y, mean, invstd = ops.bn_act_fwd(x, weight, bias, bn.running_mean if (track or not training) else None,
+                                         bn.running_var if (track or not training) else None,
+                                         bn.num_batches_tracked if track else None, bn.eps, bn.momentum, training, act,
+                                         dropout_p, seed, seed_dev)
+        ctx.save_for_backward(x, mean, invstd, weight if weight is not None else x.new_empty(0), bias if bias is not None else x.new_empty(0))
+        ctx.cfg = (training, act, dropout_p, seed, seed_dev, weight is not None, bias is not None)
+        ctx.refs = (weight, bias)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, mean, invstd, w, b = ctx.saved_tensors
+        training, act, p, seed, seed_dev, has_w, has_b = ctx.cfg
+        pw, pb = ctx.refs
+        want_dw, want_db = has_w and ctx.needs_input_grad[1], has_b and ctx.needs_input_grad[2]
+        gw, gb = (_bucket(pw) if want_dw else None), (_bucket(pb) if want_db else None)
+        direct = (not want_dw or gw is not None) and (not want_db or gb is not None) and (want_dw or want_db)
+        dx, dw, db = ops.bn_act_bwd(x, dy.contiguous(), w if has_w else None, b if has_b else None, mean, invstd, training, act, p, seed,
+                                    seed_dev, want_dw=want_dw, want_db=want_db, dw_out=gw if direct else None,
+                                    db_out=gb if direct else None)
+        return dx, dw, db, None, None, None, None, None
+
+
+def bn_act(x: Tensor, bn: "torch.nn.BatchNorm1d", act: int = ACT_ELU, dropout_p: float = 0.0, seed: int = 0,
+           seed_dev: Optional[Tensor] = None) -> Tensor:
+    """dropout(act(bn(x))) with torch.nn.BatchNorm1d semantics (training / eval, running statistics, momentum)"""
+    if x.dim() != 2:
+        raise NotImplementedError("bn_act takes [N, d] node features")
+    return _BnAct.apply(x, bn.weight, bn.bias, bn, int(act), float(dropout_p), int(seed), seed_dev)
+
+
+class _ActDropout(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, act, dropout_p, seed, seed_dev):
+        x = x.contiguous()
+        ctx.save_for_backward(x)
+        ctx.cfg = (act, dropout_p, seed, seed_dev)
+        return ops.act_dropout_fwd(x, act, dropout_p, seed, seed_dev)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        act, p, seed, seed_dev = ctx.cfg
+        return ops.act_dropout_bwd(x, dy.contiguous(), act, p, seed, seed_dev), None, None, None, None
+
+
+def act_dropout(x: Tensor, act: int = ACT_ELU, dropout_p: float = 0.0, seed: int = 0, seed_dev: Optional[Tensor] = None) -> Tensor:
+    """dropout(act(x)) in one launch (the F.elu + nn.Dropout after every GIN layer, reference models/gin.py:31-32)"""
+    return _ActDropout.apply(x, int(act), float(dropout_p), int(seed), seed_dev)
+
+
 class _Pool(torch.autograd.Function):
     """segment reduce over graphs; mode in {'sum','mean','max','mean+max'}"""
 

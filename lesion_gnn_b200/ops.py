@@ -486,3 +486,54 @@ def gather_rows(src: Tensor, index: Tensor, out: Optional[Tensor] = None) -> Ten
     L.call("lgk_gather_rows", _chk(src, None, "src"), _chk(index, torch.int64, "index"), _chk(out, src.dtype, "out"), n, row_bytes,
            src.size(0), _stream())
     return out
+
+
+def bn_act_fwd(x: Tensor, weight, bias, running_mean, running_var, num_batches_tracked, eps: float, momentum: float,
+               training: bool, act: int, dropout_p: float = 0.0, seed: int = 0, seed_dev: Optional[Tensor] = None):
+    """-> y, save_mean, save_invstd: dropout(act(batch_norm(x))) in three launches (two in eval mode)"""
+    L = _lib.lib()
+    n, d = x.shape
+    f32 = torch.float32
+    y = torch.empty_like(x)
+    mean = torch.empty(d, dtype=f32, device=x.device)
+    invstd = torch.empty(d, dtype=f32, device=x.device)
+    ws = _ws(L.query("lgk_bn_workspace_bytes", n, d), x.device)
+    L.call("lgk_bn_act_fwd", _chk(x, f32, "x"), _chk(weight, f32, "weight"), _chk(bias, f32, "bias"), _chk(running_mean, f32),
+           _chk(running_var, f32), _chk(num_batches_tracked, torch.int64), _chk(y), _chk(mean), _chk(invstd), n, d, float(eps),
+           float(momentum), int(training), int(act), float(dropout_p), int(seed), _chk(seed_dev, torch.int64), ws.data_ptr(),
+           ws.numel(), _stream())
+    return y, mean, invstd
+
+
+def bn_act_bwd(x: Tensor, dy: Tensor, weight, bias, mean: Tensor, invstd: Tensor, training: bool, act: int, dropout_p: float = 0.0,
+               seed: int = 0, seed_dev: Optional[Tensor] = None, want_dw: bool = True, want_db: bool = True,
+               dw_out: Optional[Tensor] = None, db_out: Optional[Tensor] = None):
+    """-> dx, dweight | None, dbias | None; dw_out / db_out: ADD into these (gradient bucket) and return None for them"""
+    L = _lib.lib()
+    n, d = x.shape
+    f32 = torch.float32
+    dx = torch.empty_like(x)
+    accumulate = dw_out is not None or db_out is not None
+    dw = (dw_out if accumulate else torch.empty(d, dtype=f32, device=x.device)) if want_dw else None
+    db = (db_out if accumulate else torch.empty(d, dtype=f32, device=x.device)) if want_db else None
+    ws = _ws(L.query("lgk_bn_workspace_bytes", n, d), x.device)
+    L.call("lgk_bn_act_bwd", _chk(x, f32, "x"), _chk(dy, f32, "dy"), _chk(weight, f32), _chk(bias, f32), _chk(mean, f32), _chk(invstd, f32),
+           _chk(dx), _chk(dw, f32, "dweight"), _chk(db, f32, "dbias"), int(accumulate), n, d, int(training), int(act), float(dropout_p),
+           int(seed), _chk(seed_dev, torch.int64), ws.data_ptr(), ws.numel(), _stream())
+    return dx, (None if accumulate else dw), (None if accumulate else db)
+
+
+def act_dropout_fwd(x: Tensor, act: int, dropout_p: float, seed: int = 0, seed_dev: Optional[Tensor] = None) -> Tensor:
+    L = _lib.lib()
+    y = torch.empty_like(x)
+    L.call("lgk_act_dropout_fwd", _chk(x, torch.float32, "x"), _chk(y), x.numel(), int(act), float(dropout_p), int(seed),
+           _chk(seed_dev, torch.int64), _stream())
+    return y
+
+
+def act_dropout_bwd(x: Tensor, dy: Tensor, act: int, dropout_p: float, seed: int = 0, seed_dev: Optional[Tensor] = None) -> Tensor:
+    L = _lib.lib()
+    dx = torch.empty_like(x)
+    L.call("lgk_act_dropout_bwd", _chk(x, torch.float32, "x"), _chk(dy, torch.float32, "dy"), _chk(dx), x.numel(), int(act),
+           float(dropout_p), int(seed), _chk(seed_dev, torch.int64), _stream())
+    return dx

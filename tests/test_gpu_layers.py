@@ -285,6 +285,67 @@ def test_ginconv(dev, norm):
     _run(got, ref, x, [ei], dev, tol=TOL_F32, what=f"GIN norm={norm}", fp32_floor=True)
 
 
+@pytest.mark.parametrize("n,d", [(2, 4), (777, 64), (5000, 100), (60000, 64)])
+@pytest.mark.parametrize("affine", [True, False])
+def test_bn_act_matches_torch_batchnorm_elu(dev, n, d, affine):
+    """lgk_bn_act_fwd / bwd (BatchNorm1d + ELU of PyG's MLP, reference models/gin.py:23) against torch.nn.BatchNorm1d + F.elu in
+    fp64: training mode (batch statistics, running statistics and num_batches_tracked updated), then eval mode"""
+    from lesion_gnn_b200.nn import functional as F
+    from lesion_gnn_b200._lib import ACT_ELU
+    gen = torch.Generator().manual_seed(n + d)
+    x = torch.randn(n, d, generator=gen, dtype=torch.float64) * 3 + 7        # a large mean: cancellation in naive variance
+    dy = torch.randn(n, d, generator=gen, dtype=torch.float64)
+    ref = torch.nn.BatchNorm1d(d, affine=affine).double()
+    got = torch.nn.BatchNorm1d(d, affine=affine).to(dev)
+    if affine:
+        with torch.no_grad():
+            ref.weight.copy_(torch.rand(d, generator=gen, dtype=torch.float64) + 0.5)
+            ref.bias.copy_(torch.randn(d, generator=gen, dtype=torch.float64))
+            got.weight.copy_(ref.weight.float())
+            got.bias.copy_(ref.bias.float())
+    for mode in ("train", "train", "eval"):
+        ref.train(mode == "train"), got.train(mode == "train")
+        ref.zero_grad(), got.zero_grad()
+        xr = x.clone().requires_grad_(True)
+        want = torch.nn.functional.elu(ref(xr))
+        want.backward(dy)
+        xg = x.float().to(dev).requires_grad_(True)
+        out = F.bn_act(xg, got, ACT_ELU)
+        out.backward(dy.float().to(dev))
+        assert_close(out, want, TOL_F32, f"{mode} y")
+        assert_close(xg.grad, xr.grad, 2e-5 if mode == "train" else TOL_F32, f"{mode} dx")
+        if affine:
+            assert_close(got.weight.grad, ref.weight.grad, TOL_F32, f"{mode} dweight")
+            assert_close(got.bias.grad, ref.bias.grad, TOL_F32, f"{mode} dbias")
+        assert_close(got.running_mean, ref.running_mean, TOL_F32, "running_mean")
+        assert_close(got.running_var, ref.running_var, TOL_F32, "running_var")
+        assert int(got.num_batches_tracked) == int(ref.num_batches_tracked)
+
+
+def test_act_dropout_masks_are_consistent(dev):
+    """dropout(elu(x)) in one launch: kept elements are elu(x) / (1 - p), the backward zeroes exactly the dropped ones, the
+    mask is a function of (seed, device clock) and changes with either"""
+    from lesion_gnn_b200.nn import functional as F
+    from lesion_gnn_b200._lib import ACT_ELU
+    x = torch.randn(4000, 64, device=dev)
+    p = 0.35
+    clock = torch.tensor([3, 0], dtype=torch.int64, device=dev)
+    xg = x.clone().requires_grad_(True)
+    y = F.act_dropout(xg, ACT_ELU, p, 11, clock)
+    y.backward(torch.ones_like(y))
+    e = torch.nn.functional.elu(x)
+    kept = y != 0
+    assert 0.63 < float(kept.float().mean()) < 0.67
+    assert_close(y[kept], (e / (1 - p))[kept], TOL_F32, "kept values")
+    de = torch.where(x > 0, torch.ones_like(x), e + 1) / (1 - p)
+    assert_close(xg.grad[kept], de[kept], TOL_F32, "kept gradients")
+    assert float(xg.grad[~kept].abs().max()) == 0.0
+    assert torch.equal(y, F.act_dropout(x, ACT_ELU, p, 11, clock))
+    clock[0] += 1
+    assert not torch.equal(y, F.act_dropout(x, ACT_ELU, p, 11, clock))
+    assert torch.equal(F.act_dropout(x, ACT_ELU, 0.0), e) or float((F.act_dropout(x, ACT_ELU, 0.0) - e).abs().max()) < 1e-6
+
+
 def test_state_dict_keys_match_pyg_names():
     import lesion_gnn_b200 as lg
     assert set(lg.nn.GATConv(8, 4, heads=2).state_dict()) == {"att_src", "att_dst", "bias", "lin.weight"}
