@@ -306,6 +306,7 @@ def test_bn_act_matches_torch_batchnorm_elu(dev, n, d, affine):
     for mode in ("train", "train", "eval"):
         ref.train(mode == "train"), got.train(mode == "train")
         ref.zero_grad(), got.zero_grad()
+        state_before = {k: v.clone() for k, v in ref.state_dict().items()}
         xr = x.clone().requires_grad_(True)
         want = torch.nn.functional.elu(ref(xr))
         want.backward(dy)
@@ -313,7 +314,14 @@ def test_bn_act_matches_torch_batchnorm_elu(dev, n, d, affine):
         out = F.bn_act(xg, got, ACT_ELU)
         out.backward(dy.float().to(dev))
         assert_close(out, want, TOL_F32, f"{mode} y")
-        assert_close(xg.grad, xr.grad, 2e-5 if mode == "train" else TOL_F32, f"{mode} dx")
+        # dx of batch statistics is a difference of nearly equal terms (exactly zero for n = 2): its bar is what torch's
+        # own fp32 BatchNorm loses on these inputs (x4), never below 1e-5
+        ref32 = torch.nn.BatchNorm1d(d, affine=affine)
+        ref32.load_state_dict({k: v.float() if v.is_floating_point() else v for k, v in state_before.items()})
+        ref32.train(mode == "train")
+        x32 = x.float().requires_grad_(True)
+        torch.nn.functional.elu(ref32(x32)).backward(dy.float())
+        assert_parity(xg.grad, xr.grad, x32.grad, f"{mode} dx")
         if affine:
             assert_close(got.weight.grad, ref.weight.grad, TOL_F32, f"{mode} dweight")
             assert_close(got.bias.grad, ref.bias.grad, TOL_F32, f"{mode} dbias")
