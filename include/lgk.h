@@ -113,6 +113,23 @@ LGK_API int lgk_radius_graph(const void* pos, int pos_dtype, int dim, const int3
                      double r, int loop, int max_num_neighbors, int32_t* counts, const int64_t* offsets,
                      int64_t* edge_index_out, int64_t num_edges_total, void* stream);
 
+/* PointNet++ set abstraction (reference models/pointnet.py:13-29).
+ * lgk_fps = torch_cluster.fps: per graph g the out_ptr[g+1] - out_ptr[g] = ceil(ratio * n_g) farthest-point samples (squared
+ * L2 in the dtype of pos, ties to the lower index), first sample = start[g] (index inside the graph; NULL: node 0);
+ * out_index[out_ptr[g] + s] = global node index of sample s.  dist_ws: [N] elements of the dtype of pos.            */
+LGK_API int lgk_fps(const void* pos, int pos_dtype, int dim, const int32_t* ptr, const int64_t* out_ptr, const int64_t* start,
+            int64_t num_graphs, int64_t num_nodes, void* dist_ws, int64_t* out_index, void* stream);
+/* lgk_radius = torch_cluster.radius(x, y, r, batch_x, batch_y, max_num_neighbors): for every query y_i the points x_j of
+ * the same graph with |x_j - y_i|^2 < r^2, ascending j, at most max_num_neighbors.  Pass 1 (row_out == NULL): counts[i];
+ * pass 2: offsets = exclusive scan of the counts, row_out[e] = i (query), col_out[e] = j (point).                  */
+LGK_API int lgk_radius(const void* x, const void* y, int pos_dtype, int dim, const int32_t* ptr_x, const int32_t* ptr_y,
+               int64_t num_graphs, int64_t num_x, int64_t num_y, double r, int max_num_neighbors, int32_t* counts,
+               const int64_t* offsets, int64_t* row_out, int64_t* col_out, void* stream);
+/* message input of torch_geometric.nn.PointNetConv: out[e, :] = cat[x[src[e], :F], pos_src[src[e], :D] - pos_dst[dst[e], :D]]
+ * (fp32; F may be 0 with x NULL)                                                                                */
+LGK_API int lgk_edge_concat(const float* x, const float* pos_src, const float* pos_dst, const int64_t* src, const int64_t* dst,
+                    float* out, int64_t num_edges, int64_t feat, int64_t pos_dim, void* stream);
+
 /* Gaussian edge weights exp(-d^2 / 2 sigma^2) / sqrt(2 pi sigma^2) (reference src/lesion_gnn/transforms.py:50-58) */
 LGK_API int lgk_gaussian_distance(const void* pos, int pos_dtype, int dim, const int64_t* edge_index, int64_t num_edges,
                           double sigma, float* edge_weight, void* stream);

@@ -170,6 +170,102 @@ int launch_knn(const void* pos, int dim, const int* ptr, const int64_t* eptr, in
   return LGK_OK;
 }
 
+
+// ---- PointNet++ set abstraction (reference models/pointnet.py:13-29): farthest point sampling,
+// the bipartite radius query and the edge features cat[x_j, pos_j - pos_i] of PointNetConv ----------------------------
+
+// torch_cluster.fps: one CTA per graph; sample s+1 = the node farthest (squared L2, dtype of pos) from the s samples
+// chosen so far, ties to the lower index; the first sample is start[g] (local index) or node 0.
+// out[out_ptr[g] + s] = global node index.  dist: [N] scratch in the dtype of pos.
+template <typename P>
+__global__ void __launch_bounds__(256) fps_kernel(const P* __restrict__ pos, int dim, const int* __restrict__ ptr,
+                                                  const int64_t* __restrict__ out_ptr, const int64_t* __restrict__ start,
+                                                  P* __restrict__ dist, int64_t* __restrict__ out) {
+  __shared__ P s_val[256];
+  __shared__ int s_idx[256];
+  __shared__ int s_cur;
+  const int g = blockIdx.x;
+  const int lo = ptr[g], n = ptr[g + 1] - lo;
+  const int64_t o0 = out_ptr[g];
+  const int m = int(out_ptr[g + 1] - o0);
+  if (n <= 0 || m <= 0) return;
+  for (int i = threadIdx.x; i < n; i += 256) dist[lo + i] = big<P>();
+  int cur = 0;
+  if (start) { const int64_t st = start[g]; cur = st < 0 ? 0 : (st >= n ? n - 1 : int(st)); }
+  for (int s = 0; s < m; ++s) {
+    if (threadIdx.x == 0) out[o0 + s] = lo + cur;
+    P pc[kMaxDim];
+    for (int d = 0; d < dim; ++d) pc[d] = pos[int64_t(lo + cur) * dim + d];
+    P best = P(-1);
+    int bidx = 0x7fffffff;
+    for (int i = threadIdx.x; i < n; i += 256) {
+      P acc = P(0);
+      for (int d = 0; d < dim; ++d) acc = sq_add(acc, pos[int64_t(lo + i) * dim + d], pc[d]);
+      const P dm = min(dist[lo + i], acc);
+      dist[lo + i] = dm;
+      if (dm > best) { best = dm; bidx = i; }  // ascending i per thread: the first maximum stays
+    }
+    s_val[threadIdx.x] = best;
+    s_idx[threadIdx.x] = bidx;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) {
+        const P v = s_val[threadIdx.x + o];
+        const int j = s_idx[threadIdx.x + o];
+        if (v > s_val[threadIdx.x] || (v == s_val[threadIdx.x] && j < s_idx[threadIdx.x])) { s_val[threadIdx.x] = v; s_idx[threadIdx.x] = j; }
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) s_cur = s_idx[0];
+    __syncthreads();
+    cur = s_cur;
+    __syncthreads();
+  }
+}
+
+// torch_cluster.radius(x, y, r, batch_x, batch_y, max_num_neighbors): for every query y_i the points x_j of the same graph
+// with |x_j - y_i|^2 < r^2, ascending j, at most max_nb.  Pass 1: counts[i]; pass 2 (offsets): row_out = i, col_out = j.
+template <typename P, bool FILL>
+__global__ void __launch_bounds__(128) radius_bipartite_kernel(const P* __restrict__ x, const P* __restrict__ y, int dim,
+                                                               const int* __restrict__ ptr_x, const int* __restrict__ ptr_y, int B,
+                                                               int64_t Ny, P r2, int max_nb, int* __restrict__ counts,
+                                                               const int64_t* __restrict__ offsets, int64_t* __restrict__ row_out,
+                                                               int64_t* __restrict__ col_out) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= Ny) return;
+  const int g = graph_of(ptr_y, B, int(i));
+  const int lo = ptr_x[g], hi = ptr_x[g + 1];
+  P yi[kMaxDim];
+  for (int d = 0; d < dim; ++d) yi[d] = y[i * dim + d];
+  int cnt = 0;
+  const int64_t base = FILL ? offsets[i] : 0;
+  for (int j = lo; j < hi && cnt < max_nb; ++j) {
+    P acc = P(0);
+    for (int d = 0; d < dim; ++d) acc = sq_add(acc, x[int64_t(j) * dim + d], yi[d]);
+    if (acc < r2) {
+      if (FILL) {
+        row_out[base + cnt] = i;
+        col_out[base + cnt] = j;
+      }
+      ++cnt;
+    }
+  }
+  if (!FILL) counts[i] = cnt;
+}
+
+// PointNetConv message input: out[e, :] = cat[x[src[e], :], pos_src[src[e], :] - pos_dst[dst[e], :]]  (fp32)
+__global__ void __launch_bounds__(256) edge_concat_kernel(const float* __restrict__ x, const float* __restrict__ pos_src,
+                                                          const float* __restrict__ pos_dst, const int64_t* __restrict__ src,
+                                                          const int64_t* __restrict__ dst, float* __restrict__ out, int64_t E, int F,
+                                                          int D) {
+  const int lane = threadIdx.x & 31;
+  const int64_t e = int64_t(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (e >= E) return;
+  const int64_t j = src[e], i = dst[e];
+  float* o = out + e * (F + D);
+  for (int f = lane; f < F; f += 32) o[f] = __ldg(x + j * F + f);
+  if (lane < D) o[F + lane] = __ldg(pos_src + j * D + lane) - __ldg(pos_dst + i * D + lane);
+}
 }  // namespace
 }  // namespace lgk
 
@@ -271,5 +367,58 @@ extern "C" int lgk_gaussian_distance(const void* pos, int pos_dtype, int dim, co
   else
     LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gaussian_distance: bad pos_dtype");
   LGK_CHECK_LAUNCH("gaussian_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_fps(const void* pos, int pos_dtype, int dim, const int32_t* ptr, const int64_t* out_ptr, const int64_t* start,
+                       int64_t B, int64_t N, void* dist_ws, int64_t* out_index, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(B >= 0 && N >= 0, LGK_ERR_BAD_ARG, "lgk_fps: negative size");
+  LGK_REQUIRE(dim > 0 && dim <= kMaxDim, LGK_ERR_UNSUPPORTED, "lgk_fps: dim must be in [1, %d]", kMaxDim);
+  LGK_REQUIRE(pos_dtype == 0 || pos_dtype == 1, LGK_ERR_BAD_ARG, "lgk_fps: pos_dtype must be 0 (f32) or 1 (f64)");
+  if (B == 0 || N == 0) return LGK_OK;
+  LGK_REQUIRE(pos && ptr && out_ptr && dist_ws && out_index, LGK_ERR_BAD_ARG, "lgk_fps: null pointer");
+  if (pos_dtype == 0)
+    fps_kernel<float><<<unsigned(B), 256, 0, stream>>>(static_cast<const float*>(pos), dim, ptr, out_ptr, start, static_cast<float*>(dist_ws), out_index);
+  else
+    fps_kernel<double><<<unsigned(B), 256, 0, stream>>>(static_cast<const double*>(pos), dim, ptr, out_ptr, start, static_cast<double*>(dist_ws), out_index);
+  LGK_CHECK_LAUNCH("fps_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_radius(const void* x, const void* y, int pos_dtype, int dim, const int32_t* ptr_x, const int32_t* ptr_y,
+                          int64_t B, int64_t Nx, int64_t Ny, double r, int max_num_neighbors, int32_t* counts,
+                          const int64_t* offsets, int64_t* row_out, int64_t* col_out, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(B >= 0 && Nx >= 0 && Ny >= 0 && r >= 0 && max_num_neighbors > 0, LGK_ERR_BAD_ARG, "lgk_radius: bad argument");
+  LGK_REQUIRE(dim > 0 && dim <= kMaxDim, LGK_ERR_UNSUPPORTED, "lgk_radius: dim must be in [1, %d]", kMaxDim);
+  LGK_REQUIRE(pos_dtype == 0 || pos_dtype == 1, LGK_ERR_BAD_ARG, "lgk_radius: pos_dtype must be 0 (f32) or 1 (f64)");
+  const bool fill = row_out != nullptr;
+  LGK_REQUIRE(fill ? (offsets != nullptr && col_out != nullptr) : counts != nullptr, LGK_ERR_BAD_ARG,
+              "lgk_radius: counts (pass 1) or offsets + row_out + col_out (pass 2)");
+  if (Ny == 0) return LGK_OK;
+  LGK_REQUIRE(x && y && ptr_x && ptr_y, LGK_ERR_BAD_ARG, "lgk_radius: null pointer");
+  const unsigned grid = unsigned(ceil_div(Ny, 128));
+  if (pos_dtype == 0) {
+    const float r2 = float(r) * float(r);
+    if (fill) radius_bipartite_kernel<float, true><<<grid, 128, 0, stream>>>(static_cast<const float*>(x), static_cast<const float*>(y), dim, ptr_x, ptr_y, int(B), Ny, r2, max_num_neighbors, nullptr, offsets, row_out, col_out);
+    else radius_bipartite_kernel<float, false><<<grid, 128, 0, stream>>>(static_cast<const float*>(x), static_cast<const float*>(y), dim, ptr_x, ptr_y, int(B), Ny, r2, max_num_neighbors, counts, nullptr, nullptr, nullptr);
+  } else {
+    const double r2 = r * r;
+    if (fill) radius_bipartite_kernel<double, true><<<grid, 128, 0, stream>>>(static_cast<const double*>(x), static_cast<const double*>(y), dim, ptr_x, ptr_y, int(B), Ny, r2, max_num_neighbors, nullptr, offsets, row_out, col_out);
+    else radius_bipartite_kernel<double, false><<<grid, 128, 0, stream>>>(static_cast<const double*>(x), static_cast<const double*>(y), dim, ptr_x, ptr_y, int(B), Ny, r2, max_num_neighbors, counts, nullptr, nullptr, nullptr);
+  }
+  LGK_CHECK_LAUNCH("radius_bipartite_kernel");
+  return LGK_OK;
+}
+
+extern "C" int lgk_edge_concat(const float* x, const float* pos_src, const float* pos_dst, const int64_t* src, const int64_t* dst,
+                               float* out, int64_t E, int64_t F, int64_t D, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(E >= 0 && F >= 0 && D >= 0 && D <= 32, LGK_ERR_BAD_ARG, "lgk_edge_concat: bad sizes");
+  if (E == 0 || F + D == 0) return LGK_OK;
+  LGK_REQUIRE((F == 0 || x) && (D == 0 || (pos_src && pos_dst)) && src && dst && out, LGK_ERR_BAD_ARG, "lgk_edge_concat: null pointer");
+  edge_concat_kernel<<<unsigned(ceil_div(E, 8)), 256, 0, stream>>>(x, pos_src, pos_dst, src, dst, out, E, int(F), int(D));
+  LGK_CHECK_LAUNCH("edge_concat_kernel");
   return LGK_OK;
 }

@@ -18,8 +18,8 @@ import torch.nn as nn
 from torch import Tensor
 
 from ._lib import ACT_ELU
-from .nn import (GATConv, GCNConv, GINConv, GraphConv, MLP, SAGEConv, SortAggregation, Linear, elu, global_max_pool,
-                 global_mean_max_pool, global_mean_pool, linear)
+from .nn import (GATConv, GCNConv, GINConv, GraphConv, MLP, PointNetConv, SAGEConv, SortAggregation, Linear, elu, fps,
+                 global_max_pool, global_mean_max_pool, global_mean_pool, linear, radius)
 
 
 _FUSED_ELU = os.environ.get("LGK_FUSED_ELU", "1") != "0"  # profiling knob: 0 = separate lgk_elu_fwd launch after every GAT layer
@@ -168,3 +168,52 @@ class DRGNet(nn.Module):
         x = linear(win.reshape(B * L, -1), c2.weight.reshape(c2.out_channels, -1), c2.bias, act=ACT_ELU)
         x = x.reshape(B, L, -1).transpose(1, 2)  # [B, C2, L], the layout the reference flattens
         return self.mlp(x.reshape(B, -1))
+
+
+class SAModule(nn.Module):
+    """reference models/pointnet.py:13-29: farthest point sampling, radius query, PointNetConv (max of an edge MLP)"""
+
+    def __init__(self, ratio: float, radius_: float, nn_: nn.Module, random_start: bool = True):
+        super().__init__()
+        self.ratio, self.r, self.random_start = ratio, radius_, random_start
+        self.conv = PointNetConv(nn_, add_self_loops=False)
+
+    def forward(self, x: Tensor, pos: Tensor, batch: Tensor):
+        pos = pos.to(x.dtype)
+        idx = fps(pos, batch, ratio=self.ratio, random_start=self.random_start)
+        row, col = radius(pos, pos[idx], self.r, batch, batch[idx], max_num_neighbors=64)
+        edge_index = torch.stack([col, row], dim=0)
+        x_dst = None if x is None else x[idx]
+        x = self.conv((x, x_dst), (pos, pos[idx]), edge_index)
+        return x, pos[idx], batch[idx]
+
+
+class GlobalSAModule(nn.Module):
+    """reference models/pointnet.py:32-40"""
+
+    def __init__(self, nn_: nn.Module):
+        super().__init__()
+        self.nn = nn_
+
+    def forward(self, x: Tensor, pos: Tensor, batch: Tensor, size=None) -> Tensor:
+        x = self.nn(torch.cat([x, pos], dim=1))
+        return global_max_pool(x, batch, size)
+
+
+class PointNet(nn.Module):
+    """reference models/pointnet.py:43-59 on the lgk kernels.  `radii` (the reference hard-codes 0.2 / 0.4, i.e. unit-cube
+    coordinates) and `random_start` (torch_cluster's default True; False for reproducible sampling) are extra arguments."""
+
+    def __init__(self, input_features: int, pos_dim: int, num_classes: int, radii=(0.2, 0.4), random_start: bool = True):
+        super().__init__()
+        self.sa1_module = SAModule(0.5, radii[0], MLP([input_features + pos_dim, 64, 64, 128]), random_start)
+        self.sa2_module = SAModule(0.25, radii[1], MLP([128 + pos_dim, 128, 128, 256]), random_start)
+        self.sa3_module = GlobalSAModule(MLP([256 + pos_dim, 256, 512, 1024]))
+        self.mlp = MLP([1024, 512, 256, num_classes], dropout=0.5, norm=None)
+
+    def forward(self, x: Tensor, pos: Tensor, batch: Tensor) -> Tensor:
+        size = int(batch[-1].item()) + 1 if batch.numel() else 0
+        x, pos, batch = self.sa1_module(x, pos, batch)
+        x, pos, batch = self.sa2_module(x, pos, batch)
+        x = self.sa3_module(x, pos, batch, size)
+        return self.mlp(x).log_softmax(dim=-1)

@@ -17,7 +17,7 @@ import torch.nn as nn
 import torch.nn.functional as TF
 from torch import Tensor
 
-from .._lib import ACT_ELU, ACT_NONE, SELF_ADD, SELF_NONE, SELF_REPLACE
+from .._lib import ACT_ELU, ACT_NONE, ACT_RELU, SELF_ADD, SELF_NONE, SELF_REPLACE
 from ..graph import CSRGraph, as_graph
 from . import functional as F
 
@@ -176,7 +176,7 @@ class MLP(nn.Module):
     """torch_geometric.nn.models.MLP as the reference uses it: gin.py:23 `MLP([d1, d2, d2], act="ELU", dropout=p)`
     and drgnet.py:48 `MLP([dense, 128, C], dropout=0.5, norm=None, act=F.elu)`."""
 
-    def __init__(self, channel_list, act="ELU", dropout: float = 0.0, norm: Optional[str] = "batch_norm",
+    def __init__(self, channel_list, act="relu", dropout: float = 0.0, norm: Optional[str] = "batch_norm",
                  plain_last: bool = True, bias: bool = True):
         super().__init__()
         channel_list = list(channel_list)
@@ -185,8 +185,12 @@ class MLP(nn.Module):
         self.dropout = [dropout] * n_lin
         if plain_last:
             self.dropout[-1] = 0.0
-        if not (act in ("ELU", "elu") or act is TF.elu):
-            raise NotImplementedError("only the ELU activation is on the reference's path")
+        if act in ("ELU", "elu") or act is TF.elu:
+            self.act = ACT_ELU
+        elif act in ("relu", "ReLU") or act is TF.relu:  # PyG's default (reference models/pointnet.py:48-52)
+            self.act = ACT_RELU
+        else:
+            raise NotImplementedError("only the ELU and ReLU activations are on the reference's path")
         self.lins = nn.ModuleList(Linear(a, b, bias=bias) for a, b in pairwise(channel_list))
         hidden = channel_list[1:-1] if plain_last else channel_list[1:]
         self.norms = nn.ModuleList(BatchNorm(d) if norm is not None else nn.Identity() for d in hidden)
@@ -195,11 +199,12 @@ class MLP(nn.Module):
         for i, (lin, norm) in enumerate(zip(self.lins, self.norms)):
             p = self.dropout[i] if self.training else 0.0
             if isinstance(norm, nn.Identity):
-                x = lin(x, act=ACT_ELU)  # ELU fused into the transform's epilogue
-                if p > 0:
-                    x = F.act_dropout(x, ACT_NONE, p, _next_seed(), _DROPOUT_CLOCK[0])
-            else:  # BatchNorm1d + ELU + Dropout: lgk_bn_act_fwd / bwd (no ATen kernel inside the MLP)
-                x = F.bn_act(lin(x), norm.module, ACT_ELU, p, _next_seed() if p > 0 else 0, _DROPOUT_CLOCK[0] if p > 0 else None)
+                if self.act == ACT_ELU and p == 0:
+                    x = lin(x, act=ACT_ELU)  # ELU fused into the transform's epilogue
+                else:
+                    x = F.act_dropout(lin(x), self.act, p, _next_seed() if p > 0 else 0, _DROPOUT_CLOCK[0] if p > 0 else None)
+            else:  # BatchNorm1d + activation + Dropout: lgk_bn_act_fwd / bwd (no ATen kernel inside the MLP)
+                x = F.bn_act(lin(x), norm.module, self.act, p, _next_seed() if p > 0 else 0, _DROPOUT_CLOCK[0] if p > 0 else None)
         if self.plain_last:
             x = self.lins[-1](x)
             p = self.dropout[-1] if self.training else 0.0
