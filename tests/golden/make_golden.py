@@ -67,7 +67,7 @@ def main():
         case["gcn"] = run_layer(lambda: O.GCNConv(16, 8), x, ei)
         case["gcn_w"] = run_layer(lambda: O.GCNConv(16, 8), x, ei, ew)
         case["gat"] = run_layer(lambda: O.GATConv(16, 4, heads=2), x, ei)
-        case["gin"] = run_layer(lambda: O.GINConv(O.MLP([16, 8, 8], norm=None)), x, ei)
+        case["gin"] = run_layer(lambda: O.GINConv(O.MLP([16, 8, 8], act="ELU", norm=None)), x, ei)
         case["sage_mean"] = run_layer(lambda: O.SAGEConv(16, 8, aggr="mean"), x, ei)
         case["sage_max"] = run_layer(lambda: O.SAGEConv(16, 8, aggr="max"), x, ei)
         case["graphconv_w"] = run_layer(lambda: O.GraphConv(16, 8), x, ei, ew)

@@ -372,7 +372,7 @@ def test_golden_vectors(dev):
     makers = {
         "gcn": (lambda: lg.nn.GCNConv(16, 8), False), "gcn_w": (lambda: lg.nn.GCNConv(16, 8), True),
         "gat": (lambda: lg.nn.GATConv(16, 4, heads=2), False),
-        "gin": (lambda: lg.nn.GINConv(lg.nn.MLP([16, 8, 8], norm=None)), False),
+        "gin": (lambda: lg.nn.GINConv(lg.nn.MLP([16, 8, 8], act="ELU", norm=None)), False),
         "sage_mean": (lambda: lg.nn.SAGEConv(16, 8, aggr="mean"), False),
         "sage_max": (lambda: lg.nn.SAGEConv(16, 8, aggr="max"), False),
         "graphconv_w": (lambda: lg.nn.GraphConv(16, 8), True),
