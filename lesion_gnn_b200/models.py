@@ -82,15 +82,13 @@ class GIN(nn.Module):
         self.pooling = pooling
         mult = 2 if pooling == "mean+max" else 1
         self.out_proj = _TorchInitLinear(mult * hidden_channels[-1], num_classes)
-        self.dropout = nn.Dropout(dropout)
+        from .nn.functional import ActDropout
+        self.dropout = ActDropout(ACT_ELU, dropout)  # `F.elu(...)` then `self.dropout(...)` of gin.py:31-32 (no parameters)
 
     def forward(self, x: Tensor, edge_index, batch) -> Tensor:
         x = self.in_proj(x)
-        from .nn import functional as F
-        from .nn.conv import _DROPOUT_CLOCK, _next_seed
-        p = self.dropout.p if self.training else 0.0
         for conv in self.convs:  # F.elu + nn.Dropout of gin.py:31-32 as one launch
-            x = F.act_dropout(conv(x, edge_index), ACT_ELU, p, _next_seed() if p > 0 else 0, _DROPOUT_CLOCK[0] if p > 0 else None)
+            x = self.dropout(conv(x, edge_index))
         return self.out_proj(_readout(x, batch, self.pooling))
 
 

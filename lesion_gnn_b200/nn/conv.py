@@ -18,6 +18,7 @@ import torch.nn.functional as TF
 from torch import Tensor
 
 from .._lib import ACT_ELU, ACT_NONE, ACT_RELU, SELF_ADD, SELF_NONE, SELF_REPLACE
+from ..compile import OpaqueModule
 from ..graph import CSRGraph, as_graph
 from . import functional as F
 
@@ -60,8 +61,8 @@ def _glorot(t: Tensor) -> None:
         t.uniform_(-a, a)
 
 
-class Linear(nn.Module):
-    """torch_geometric.nn.dense.linear.Linear: weight [out, in]; runs on the lgk FFMA transform kernel."""
+class Linear(OpaqueModule, nn.Module):
+    """torch_geometric.nn.dense.linear.Linear: weight [out, in]; runs on the lgk transform kernels."""
 
     def __init__(self, in_channels: int, out_channels: int, bias: bool = True, weight_initializer: Optional[str] = None):
         super().__init__()
@@ -70,6 +71,7 @@ class Linear(nn.Module):
         self.bias = nn.Parameter(torch.empty(out_channels)) if bias else None
         self.weight_initializer = weight_initializer
         self.reset_parameters()
+        self._register_opaque()
 
     def reset_parameters(self):
         if self.weight_initializer == "glorot":
@@ -84,10 +86,18 @@ class Linear(nn.Module):
                 nn.init.uniform_(self.bias, -bound, bound)
 
     def forward(self, x: Tensor, act: int = ACT_NONE) -> Tensor:
-        return F.linear(x, self.weight, self.bias, act=act)
+        if act != ACT_NONE:  # fused-activation form: used by MLP, itself an opaque layer
+            return F.linear(x, self.weight, self.bias, act=act)
+        return self._dispatch(x)
+
+    def _forward_eager(self, x: Tensor) -> Tensor:
+        return F.linear(x, self.weight, self.bias)
+
+    def _fake(self, x: Tensor) -> Tensor:
+        return x.new_empty(tuple(x.shape[:-1]) + (self.out_channels,))
 
 
-class GCNConv(nn.Module):
+class GCNConv(OpaqueModule, nn.Module):
     """D^-1/2 (A + I) D^-1/2 X W^T + b.  Transform first, then one fused aggregation in which
     the symmetric normalisation is applied on the fly from a per-node deg^-1/2 vector (no [E] weight array)."""
 
@@ -98,8 +108,15 @@ class GCNConv(nn.Module):
         self.improved, self.cached, self.add_self_loops, self.normalize = improved, cached, add_self_loops, normalize
         self.lin = Linear(in_channels, out_channels, bias=False, weight_initializer="glorot")
         self.bias = nn.Parameter(torch.zeros(out_channels)) if bias else None
+        self._register_opaque()
 
     def forward(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None) -> Tensor:
+        return self._dispatch(x, edge_index, edge_weight)
+
+    def _fake(self, x: Tensor, edge_index=None, edge_weight=None) -> Tensor:
+        return x.new_empty((x.size(0), self.out_channels))
+
+    def _forward_eager(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None) -> Tensor:
         h = self.lin(x)  # before as_graph: the transform does not read the graph, whose build may still be running on
         g = as_graph(edge_index, x.size(0), edge_weight)  # its own stream (as_graph joins it)
         if not self.normalize:
@@ -113,7 +130,7 @@ class GCNConv(nn.Module):
                            self_mode=SELF_REPLACE if self.add_self_loops else SELF_NONE, bias=self.bias)
 
 
-class GATConv(nn.Module):
+class GATConv(OpaqueModule, nn.Module):
     """Multi-head graph attention (reference models/gat.py:31,51): transform, then ONE kernel
     for leaky_relu + per-destination softmax + attention dropout + weighted aggregation + bias."""
 
@@ -142,10 +159,17 @@ class GATConv(nn.Module):
             self.bias = None
         _glorot(self.att_src)
         _glorot(self.att_dst)
+        self._register_opaque()
 
     def forward(self, x: Tensor, edge_index, edge_attr=None, size=None, return_attention_weights=None) -> Tensor:
         if edge_attr is not None or return_attention_weights:
             raise NotImplementedError("edge_attr / return_attention_weights are not on the reference's path")
+        return self._dispatch(x, edge_index)
+
+    def _fake(self, x: Tensor, edge_index=None) -> Tensor:
+        return x.new_empty((x.size(0), self.heads * self.out_channels if self.concat else self.out_channels))
+
+    def _forward_eager(self, x: Tensor, edge_index) -> Tensor:
         h = self.lin(x)  # before as_graph: the transform does not read the graph, whose build may still be running on
         g = as_graph(edge_index, x.size(0))  # its own stream (as_graph joins it)
         p = self.dropout if self.training else 0.0
@@ -172,7 +196,7 @@ class BatchNorm(nn.Module):
         return self.module(x)
 
 
-class MLP(nn.Module):
+class MLP(OpaqueModule, nn.Module):
     """torch_geometric.nn.models.MLP as the reference uses it: gin.py:23 `MLP([d1, d2, d2], act="ELU", dropout=p)`
     and drgnet.py:48 `MLP([dense, 128, C], dropout=0.5, norm=None, act=F.elu)`."""
 
@@ -194,8 +218,15 @@ class MLP(nn.Module):
         self.lins = nn.ModuleList(Linear(a, b, bias=bias) for a, b in pairwise(channel_list))
         hidden = channel_list[1:-1] if plain_last else channel_list[1:]
         self.norms = nn.ModuleList(BatchNorm(d) if norm is not None else nn.Identity() for d in hidden)
+        self._register_opaque()
 
     def forward(self, x: Tensor) -> Tensor:
+        return self._dispatch(x)
+
+    def _fake(self, x: Tensor) -> Tensor:
+        return x.new_empty((x.size(0), self.channel_list[-1]))
+
+    def _forward_eager(self, x: Tensor) -> Tensor:
         for i, (lin, norm) in enumerate(zip(self.lins, self.norms)):
             p = self.dropout[i] if self.training else 0.0
             if isinstance(norm, nn.Identity):
@@ -213,7 +244,7 @@ class MLP(nn.Module):
         return x
 
 
-class GINConv(nn.Module):
+class GINConv(OpaqueModule, nn.Module):
     """nn((1 + eps) x_i + sum_j x_j) (reference models/gin.py:23,31): the (1+eps) x_i term is an
     extra self entry inside the aggregation kernel."""
 
@@ -227,6 +258,7 @@ class GINConv(nn.Module):
             self.register_buffer("eps", torch.tensor([eps], dtype=torch.float32))
         self._eps_host = float(eps)
         self.train_eps = train_eps
+        self._register_opaque()
 
     def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
         super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
@@ -234,6 +266,15 @@ class GINConv(nn.Module):
             self._eps_host = float(self.eps.detach().cpu())
 
     def forward(self, x: Tensor, edge_index, size=None) -> Tensor:
+        return self._dispatch(x, edge_index)
+
+    def _fake(self, x: Tensor, edge_index=None) -> Tensor:
+        if hasattr(self.nn, "_fake"):
+            return self.nn._fake(x)
+        last = [m for m in self.nn.modules() if isinstance(m, (Linear, nn.Linear))][-1]
+        return x.new_empty((x.size(0), last.weight.size(0)))
+
+    def _forward_eager(self, x: Tensor, edge_index) -> Tensor:
         g = as_graph(edge_index, x.size(0))
         if self.train_eps:
             out = F.aggregate(x, g, "sum") + (1 + self.eps) * x
@@ -242,7 +283,7 @@ class GINConv(nn.Module):
         return self.nn(out)
 
 
-class SAGEConv(nn.Module):
+class SAGEConv(OpaqueModule, nn.Module):
     """W_l aggr_j x_j + b_l + W_r x_i: aggregate at input width, then both products in one
     accumulating transform."""
 
@@ -255,8 +296,15 @@ class SAGEConv(nn.Module):
         self.aggr, self.normalize, self.root_weight = aggr, normalize, root_weight
         self.lin_l = Linear(in_channels, out_channels, bias=bias)
         self.lin_r = Linear(in_channels, out_channels, bias=False) if root_weight else None
+        self._register_opaque()
 
     def forward(self, x: Tensor, edge_index, size=None) -> Tensor:
+        return self._dispatch(x, edge_index)
+
+    def _fake(self, x: Tensor, edge_index=None) -> Tensor:
+        return x.new_empty((x.size(0), self.out_channels))
+
+    def _forward_eager(self, x: Tensor, edge_index) -> Tensor:
         g = as_graph(edge_index, x.size(0))
         agg = F.aggregate(x, g, self.aggr)
         if self.lin_r is not None:
@@ -268,7 +316,7 @@ class SAGEConv(nn.Module):
         return out
 
 
-class GraphConv(nn.Module):
+class GraphConv(OpaqueModule, nn.Module):
     """W_rel sum_j e_ji x_j + b + W_root x_i (reference models/drgnet.py:31,33,55)."""
 
     def __init__(self, in_channels: int, out_channels: int, aggr: str = "add", bias: bool = True):
@@ -276,8 +324,15 @@ class GraphConv(nn.Module):
         self.in_channels, self.out_channels, self.aggr = in_channels, out_channels, aggr
         self.lin_rel = Linear(in_channels, out_channels, bias=bias)
         self.lin_root = Linear(in_channels, out_channels, bias=False)
+        self._register_opaque()
 
     def forward(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None, size=None) -> Tensor:
+        return self._dispatch(x, edge_index, edge_weight)
+
+    def _fake(self, x: Tensor, edge_index=None, edge_weight=None) -> Tensor:
+        return x.new_empty((x.size(0), self.out_channels))
+
+    def _forward_eager(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None) -> Tensor:
         g = as_graph(edge_index, x.size(0), edge_weight)
         if g.value is not None and self.aggr not in ("add", "sum"):
             raise NotImplementedError("edge weights are defined for the sum aggregation only")

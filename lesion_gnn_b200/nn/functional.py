@@ -10,6 +10,7 @@ from typing import Optional
 import torch
 from torch import Tensor
 
+from .. import compile as _compile
 from .. import ops
 from .._lib import ACT_ELU, ACT_NONE, SELF_ADD, SELF_NONE, SELF_REPLACE  # noqa: F401
 from ..graph import CSRGraph
@@ -303,8 +304,18 @@ class _Linear(torch.autograd.Function):
         return dx, dw, db, None, None, None, None
 
 
+def _linear_fake(x, weight, bias=None):
+    return x.new_empty(tuple(x.shape[:-1]) + (weight.size(0),))
+
+
+_LINEAR_OPS = {act: _compile.opaque_function((lambda act: lambda x, w, b=None: linear(x, w, b, act=act))(act), _linear_fake)
+               for act in (ACT_NONE, ACT_ELU)}
+
+
 def linear(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None, *, rowscale: Optional[Tensor] = None,
            act: int = ACT_NONE, x2: Optional[Tensor] = None, weight2: Optional[Tensor] = None) -> Tensor:
+    if _compile.is_compiling() and rowscale is None and x2 is None and act in _LINEAR_OPS:
+        return _LINEAR_OPS[act](x, weight, bias)
     if x.dim() != 2:
         lead = x.shape[:-1]
         return linear(x.reshape(-1, x.size(-1)), weight, bias, rowscale=rowscale, act=act).reshape(*lead, weight.size(0))
@@ -324,8 +335,11 @@ class _Elu(torch.autograd.Function):
         return ops.elu_bwd(y, dy.contiguous())
 
 
-def elu(x: Tensor) -> Tensor:
+def _elu_eager(x: Tensor) -> Tensor:
     return _Elu.apply(x)
+
+
+elu = _compile.opaque_function(_elu_eager, lambda x: torch.empty_like(x))
 
 
 class _BnAct(torch.autograd.Function):
@@ -388,6 +402,26 @@ class _ActDropout(torch.autograd.Function):
 def act_dropout(x: Tensor, act: int = ACT_ELU, dropout_p: float = 0.0, seed: int = 0, seed_dev: Optional[Tensor] = None) -> Tensor:
     """dropout(act(x)) in one launch (the F.elu + nn.Dropout after every GIN layer, reference models/gin.py:31-32)"""
     return _ActDropout.apply(x, int(act), float(dropout_p), int(seed), seed_dev)
+
+
+class ActDropout(_compile.OpaqueModule, torch.nn.Module):
+    """nn.Sequential(activation, nn.Dropout(p)) as one launch and, under torch.compile, one opaque operator"""
+
+    def __init__(self, act: int = ACT_ELU, p: float = 0.0):
+        super().__init__()
+        self.act, self.p = int(act), float(p)
+        self._register_opaque()
+
+    def forward(self, x: Tensor) -> Tensor:
+        return self._dispatch(x)
+
+    def _fake(self, x: Tensor) -> Tensor:
+        return torch.empty_like(x)
+
+    def _forward_eager(self, x: Tensor) -> Tensor:
+        from .conv import _DROPOUT_CLOCK, _next_seed
+        p = self.p if self.training else 0.0
+        return act_dropout(x, self.act, p, _next_seed() if p > 0 else 0, _DROPOUT_CLOCK[0] if p > 0 else None)
 
 
 class _Pool(torch.autograd.Function):
