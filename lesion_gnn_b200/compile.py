@@ -121,7 +121,7 @@ def _backward(ctx, grads):
     res = torch.ops.lgk.opaque_bwd(ctx.key, ctx.need, ctx.n_inputs, ticket, gs, list(tensors))
     it = iter(res)
     full = [next(it) if (ctx.need >> i) & 1 and t.is_floating_point() else None for i, t in enumerate(tensors)]
-    return None, None, None, full, None
+    return None, None, None, full, ([] if not ctx.ints else None)  # pytree: an empty int list is a node, a filled one a leaf
 
 
 opaque_fwd.register_autograd(_backward, setup_context=_setup)

@@ -88,7 +88,8 @@ def test_compiled_model_equals_eager(dev, backend, name):
         got = compiled(xc, ei, b)
         got.square().sum().backward()
         assert torch.equal(got, want), name
-        assert torch.equal(xc.grad, xe.grad)
+        # same kernels; autograd may add the partial gradients of a tensor in another order (last-bit differences)
+        torch.testing.assert_close(xc.grad, xe.grad, rtol=1e-6, atol=1e-9)
         for k, p in model.named_parameters():
             if k in grads:
-                assert torch.equal(p.grad, grads[k]), k
+                torch.testing.assert_close(p.grad, grads[k], rtol=1e-6, atol=1e-9, msg=k)
