@@ -156,7 +156,8 @@ LGK_API int lgk_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* emap
 
 /* Row-blocked ("quad") form of a CSR / CSC for lgk_spmm_blocked: four consecutive rows 4g..4g+3 share one merged
  * neighbour list, ascending by source id, qent[ptr[4g] + t] = source | membership << 28 (bit r: row 4g+r has the entry;
- * a duplicate edge of one row is emitted as a second entry), t < qlen[g].  cmin / cmax [lgk_quad_chunks(n_rows)]: smallest /
+ * a duplicate edge of one row is emitted as a second entry), t < qlen[2g]; qlen[2g+1] = number of stored (i, i)
+ * entries of each of the four rows, 8 bits per row (int32 [n_quads, 2]).  cmin / cmax [lgk_quad_chunks(n_rows)]: smallest /
  * largest source id referenced by each chunk of 16 quads (INT32_MAX / -1 for a chunk without entries); qmeta int32[4] =
  * {widest chunk window in rows, number of chunks too wide for the 256-byte-slice ring, 0, 0}, read on the device only.  Built once per
  * batch next to the CSR / CSC (lgk_csr_build) and shared by every layer; n_rows < 2^28.  qent has room for E entries. */

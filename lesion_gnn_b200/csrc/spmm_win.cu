@@ -34,9 +34,10 @@ constexpr int kQuadsPerChunk = 16;               // 64 destination rows per chun
 constexpr int kBlkBytes = 4096;                  // bytes of a ring block = one TMA box (32 rows x 128 B or 16 rows x 256 B)
 constexpr int kStages = 8;                       // chunks in flight between producer and consumers
 constexpr int kMaxConsumerWarps = 24;
-constexpr int kBatch = 16;                       // merged entries staged per group and batch (two per lane at 8 lanes)
+constexpr int kBatch = 32;                       // merged entries staged per group and batch (four per lane at 8 lanes)
 constexpr int kSmemMax = 232448;                 // 227 KB
 constexpr unsigned kColMask = 0x0FFFFFFFu;
+constexpr int kStageBytes = (kBatch / 2) * 64;   // staging area of a warp: [pair][4 groups][16 B]
 // A chunk whose source window (largest - smallest source id + 1) exceeds this many rows does not leave the 256-byte-slice
 // ring (~830 rows) room to run two chunks ahead; lgk_quad_build counts them (qmeta[1]) and the launch picks the slice
 // width from that count on the device.
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(128) quad_build_kernel(const int* __restrict__
     }
     const int start = pos[0];
     int out = start;
+    unsigned selfc = 0;  // stored (i, i) entries of the four rows, 8 bits each (saturating)
     while (true) {
       const int m = min(min(c[0], c[1]), min(c[2], c[3]));
       if (m == INT_MAX) break;
@@ -73,6 +75,7 @@ __global__ void __launch_bounds__(128) quad_build_kernel(const int* __restrict__
       for (int k = 0; k < 4; ++k) {
         if (c[k] == m) {  // a duplicate edge of the same row stays at the head and is emitted again
           mask |= 1u << k;
+          if (int64_t(m) == g * 4 + k && ((selfc >> (8 * k)) & 0xffu) < 255u) selfc += 1u << (8 * k);
           ++pos[k];
           c[k] = pos[k] < end[k] ? __ldg(idx + pos[k]) : INT_MAX;
         }
@@ -81,7 +84,8 @@ __global__ void __launch_bounds__(128) quad_build_kernel(const int* __restrict__
       lo = min(lo, m);
       hi = max(hi, m);
     }
-    qlen[g] = out - start;
+    qlen[2 * g] = out - start;
+    qlen[2 * g + 1] = int(selfc);
   }
 #pragma unroll
   for (int o = kQuadsPerChunk / 2; o; o >>= 1) {  // reduce over the chunk's lanes (a chunk never straddles a warp)
@@ -143,7 +147,7 @@ __device__ __forceinline__ void add2(float2& acc, const float2 v) {
 
 struct WinArgs {
   const int* ptr;        // [n_rows + 1] CSR / CSC row pointer (quad g's merged list starts at ptr[4g])
-  const int* qlen;       // [n_quads]
+  const int* qlen;       // [n_quads][2]: {merged entries, stored self loops of the four rows (8 bits each)}
   const unsigned* qent;  // merged entries
   const int* cmin;       // [n_chunks] smallest / largest source id of a chunk (INT_MAX / -1 when it has no entries)
   const int* cmax;
@@ -166,6 +170,7 @@ struct WinShared {
   uint64_t full[kStages], empty[kStages];
   int direct[kStages];   // chunk is reduced with global gathers (its window does not fit the ring)
   int lo_blk[kStages];   // first ring block the chunk reads (INT_MAX: none), for the eviction rule
+  int hi_blk[kStages];   // one past the last ring block of the chunk's window
 };
 
 // the 256-byte-slice kernel runs when at most 1 chunk in 32 is too wide for its ring, the 128-byte one otherwise
@@ -194,19 +199,19 @@ __device__ __forceinline__ void accumulate(float2 (&acc)[4][2], const float4 v, 
 
 // LPG: lanes per group = 16-byte pieces of a slice (8: 128-byte slices, 4 quads per warp, 2 sets of 8 warps working on
 // alternate chunks; 16: 256-byte slices, 2 quads per warp, 1 set).
-// DBG (profiling ablations, LGK_WIN_DEBUG; results are wrong when != 0): 1 = one unpredicated accumulator update per entry
-// instead of the masked four, 2 = no shared-memory / global gathers (the staged words stand in for the data),
-// 4 = the producer issues no TMA loads
-// NW: consumer warps (+ 1 producer warp); 24 need the kernel to fit 80 registers
-template <bool HAS_PRE, int LPG, int NW, int DBG>
+// NW: consumer warps (+ 1 producer warp); 24 need the kernel to fit 80 registers.
+// SELF (LGK_SELF_*) and SCALE (mean or post-scale present) are compile-time: per quad the kernel spends as many
+// instructions on bookkeeping as on a third of its gathers (ncu, profiles/r02), so nothing optional stays in that path.
+template <bool HAS_PRE, int LPG, int NW, int SELF, bool SCALE>
 __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArgs a, const __grid_constant__ CUtensorMap map_x) {
+  constexpr int DBG = 0;
   constexpr int kConsumerWarps = NW;
   constexpr int kSliceBytes = LPG * 16;
   constexpr int kBlkRows = kBlkBytes / kSliceBytes;
   constexpr int GPW = 32 / LPG;                          // groups (quads in flight) per warp
   // work unit of the pipeline = `kSuper` consecutive chunks of the quad structure: one for the 256-byte slices (their
   // ring only holds a 64-row chunk's window plus look-ahead), four for the 128-byte slices (fewer, larger hand-offs)
-  constexpr int kSuper = LPG == 16 ? 1 : 4;
+  constexpr int kSuper = LPG == 16 ? 1 : NW / 4;  // 4 chunks (256 rows) at 16 warps, 6 (384 rows) at 24
   constexpr int kUnitQuads = kQuadsPerChunk * kSuper;
   constexpr int kSets = kConsumerWarps * GPW / kUnitQuads >= 1 ? kConsumerWarps * GPW / kUnitQuads : 1;
   constexpr int kWarpsPerSet = kConsumerWarps / kSets;
@@ -218,7 +223,7 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
   const uint32_t ring = umma::smem_u32(smem_raw);
   float* ring_pre = reinterpret_cast<float*>(smem_raw + size_t(a.nb) * kBlkBytes);
   unsigned char* stage_raw = reinterpret_cast<unsigned char*>(ring_pre + (HAS_PRE ? a.nb * 32 : 0));
-  WinShared* sh = reinterpret_cast<WinShared*>(stage_raw + kConsumerWarps * 512);
+  WinShared* sh = reinterpret_cast<WinShared*>(stage_raw + kConsumerWarps * kStageBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x % a.slices;
@@ -339,6 +344,7 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
       if (lane == 0) {
         sh->direct[s] = direct;
         sh->lo_blk[s] = lo_b;
+        sh->hi_blk[s] = lo_b == INT_MAX ? 0 : hi / kBlkRows + 1;
       }
       __syncwarp();
       if (lane == 0) {
@@ -363,31 +369,38 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
     return;
   }
 
-  // ===================== consumers: GPW groups of LPG lanes per warp, one quad per group and chunk =====================
+  // ===================== consumers: GPW groups of LPG lanes per warp, one quad per group and unit =====================
+  // all index arithmetic is 32-bit: the launcher checks n_rows * feat / 4 < 2^31
   const int gl = lane & (LPG - 1), grp = lane / LPG;
   const int set = warp / kWarpsPerSet;
-  const int group = (warp % kWarpsPerSet) * GPW + grp;  // quad of the chunk this group reduces
-  const int F4 = a.feat >> 2;
-  const int vec = slice * LPG + gl;  // this lane's float4 column
+  const int group = (warp % kWarpsPerSet) * GPW + grp;  // quad of the unit this group reduces
+  const unsigned F4 = unsigned(a.feat) >> 2;
+  const unsigned vec = unsigned(slice) * LPG + gl;  // this lane's float4 column
   const bool lane_on = vec < F4;
-  const uint32_t stage_base = umma::smem_u32(stage_raw) + warp * 512 + grp * 16;  // + pair * (GPW * 16)
-  const float4* xv = reinterpret_cast<const float4*>(a.x) + (lane_on ? vec : 0);
+  const uint32_t stage_base = umma::smem_u32(stage_raw) + warp * kStageBytes + grp * 16;  // + pair * (GPW * 16)
+  const float4* xv = reinterpret_cast<const float4*>(a.x) + (lane_on ? vec : 0u);
   float4* ov = reinterpret_cast<float4*>(a.out) + vec;
   const uint32_t lane_off = uint32_t(gl) * 16;
   const unsigned nb_magic = unsigned((uint64_t(1) << 32) / unsigned(nb)) + 1u;  // blk % nb without a divide (blk < 2^24)
   const int* qent_i = reinterpret_cast<const int*>(a.qent);
+  const int n_rows = int(a.n_rows), n_quads = int(a.n_quads);
+  const int unit0 = int(c_begin);
+  const bool has_mean = a.mean != 0, has_post = a.post != nullptr, has_selfw = a.selfw != nullptr;
   float4 bias4 = f4_zero();
   if (a.bias && lane_on) bias4 = __ldg(reinterpret_cast<const float4*>(a.bias) + vec);
 
   // software pipeline over the quads of this group, two deep: while quad q is reduced, the first two batches of merged
   // entries of quad q + 1 and the header (start, len) of quad q + 2 are in flight -- the entry stream comes from HBM
   // (~1 us), one quad of work per warp is less than that
-  auto quad_of = [&](int i) { return (c_begin + i) * kUnitQuads + group; };
-  auto load_header = [&](int i, int& st, int& ln) {
+  auto load_header = [&](int i, int& st, int& ln, unsigned& sc) {
+    const int g = (unit0 + i) * kUnitQuads + group;
     st = ln = 0;
-    if (i < n_my && quad_of(i) < a.n_quads) {
-      st = __ldg(a.ptr + quad_of(i) * 4);
-      ln = __ldg(a.qlen + quad_of(i));
+    sc = 0;
+    if (i < n_my && g < n_quads) {
+      st = __ldg(a.ptr + 4 * g);
+      const int2 h = __ldg(reinterpret_cast<const int2*>(a.qlen) + g);
+      ln = h.x;
+      sc = unsigned(h.y);
     }
   };
   auto load_batch = [&](int st, int ln, int b0, unsigned (&wd)[EPL]) {
@@ -399,18 +412,19 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
     }
   };
   int start_c, len_c, start_1, len_1;
+  unsigned self_c, self_1;
   unsigned wc0[EPL], wc1[EPL];
-  load_header(set, start_c, len_c);
-  load_header(set + kSets, start_1, len_1);
+  load_header(set, start_c, len_c, self_c);
+  load_header(set + kSets, start_1, len_1, self_1);
   load_batch(start_c, len_c, 0, wc0);
   load_batch(start_c, len_c, kBatch, wc1);
 
   for (int i = set; i < n_my; i += kSets) {
     const int s = i % kStages;
-    const int64_t g = quad_of(i);
-    const bool quad_on = g < a.n_quads;
-    const int64_t row0 = g * 4;
+    const int g = (unit0 + i) * kUnitQuads + group;
+    const int row0 = 4 * g;
     const int start = start_c, len = len_c;
+    const unsigned selfcnt = self_c;  // stored (i, i) entries per row, 8 bits each
     unsigned w[EPL], w2[EPL];
 #pragma unroll
     for (int h = 0; h < EPL; ++h) { w[h] = wc0[h]; w2[h] = wc1[h]; }
@@ -419,26 +433,31 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
     load_batch(start_1, len_1, kBatch, wc1);
     start_c = start_1;
     len_c = len_1;
-    load_header(i + 2 * kSets, start_1, len_1);
-    float scale[4], cself[4];
+    self_c = self_1;
+    load_header(i + 2 * kSets, start_1, len_1, self_1);
+    // what the epilogue reads goes out now and is only touched there (rows past the end of the array read row n_rows - 1
+    // and are not stored)
+    float postv[4], cself[4];
+    int deg[4];
+    if (SCALE || SELF != LGK_SELF_NONE) {
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const int64_t row = row0 + r;
-      scale[r] = 1.f;
-      cself[r] = 0.f;
-      if (quad_on && row < a.n_rows) {
-        if (a.mean) scale[r] = 1.f / float(max(__ldg(a.ptr + row + 1) - __ldg(a.ptr + row), 1));
-        if (a.post) scale[r] *= __ldg(a.post + row);
-        if (a.self_mode != LGK_SELF_NONE) cself[r] = a.selfw ? __ldg(a.selfw + row) : a.self_fill;
+      for (int r = 0; r < 4; ++r) {
+        const int row = min(row0 + r, n_rows - 1);
+        postv[r] = 1.f;
+        deg[r] = 1;
+        cself[r] = a.self_fill;
+        if (SCALE && has_mean) deg[r] = __ldg(a.ptr + row + 1) - __ldg(a.ptr + row);
+        if (SCALE && has_post) postv[r] = __ldg(a.post + row);
+        if (SELF != LGK_SELF_NONE && has_selfw) cself[r] = __ldg(a.selfw + row);
       }
     }
     win_wait(&sh->full[s], (i / kStages) & 1);
     const int direct = sh->direct[s];
+    const int win_lo = sh->lo_blk[s] == INT_MAX ? INT_MAX : sh->lo_blk[s] * kBlkRows, win_hi = sh->hi_blk[s] * kBlkRows;
     const int maxlen = __reduce_max_sync(0xffffffffu, len);
     float2 acc[4][2];
 #pragma unroll
     for (int r = 0; r < 4; ++r) acc[r][0] = acc[r][1] = make_float2(0.f, 0.f);
-    unsigned selfcnt = 0;  // stored (i, i) entries per row, 8 bits each (SELF_REPLACE only)
 
     for (int b0 = 0; b0 < maxlen; b0 += kBatch) {
       unsigned word[EPL];
@@ -449,10 +468,6 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
 #pragma unroll
       for (int h = 0; h < EPL; ++h) {
         const unsigned col = word[h] & kColMask, mask = word[h] >> 28;
-        if (a.self_mode == LGK_SELF_REPLACE) {
-          const unsigned d = col - unsigned(row0);
-          if (d < 4u && ((mask >> d) & 1u)) selfcnt += 1u << (8 * d);
-        }
         unsigned o;
         float wt = 1.f;
         if (!direct) {
@@ -466,68 +481,89 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
         }
         // pair p = entry / 2, half = entry & 1: [pair][group][half] -> one 16-byte read serves two entries
         const int ent = gl + LPG * h;
-        sts_u2(stage_base + (ent >> 1) * (GPW * 16) + (ent & 1) * 8, o | (mask << 28), __float_as_uint(wt));
+        // with weights: [pair][group][{word, weight} x 2]; without: [four entries][group][word x 4] -- one 16-byte read
+        // serves two / four entries
+        if (HAS_PRE) sts_u2(stage_base + (ent >> 1) * (GPW * 16) + (ent & 1) * 8, o | (mask << 28), __float_as_uint(wt));
+        else umma::sts_f32(stage_base + (ent >> 2) * (GPW * 16) + (ent & 3) * 4, __uint_as_float(o | (mask << 28)));
       }
       __syncwarp();
       const int cnt = min(kBatch, maxlen - b0);
-      if (!direct) {
+      if (!direct && !HAS_PRE) {
 #pragma unroll 2
+        for (int t = 0; t < cnt; t += 4) {  // entries past cnt are staged with an empty mask
+          const uint4 st = lds_u4(stage_base + (t >> 2) * (GPW * 16));
+          const float4 v0 = lds_f4((st.x & kColMask) | lane_off);
+          const float4 v1 = lds_f4((st.y & kColMask) | lane_off);
+          const float4 v2 = lds_f4((st.z & kColMask) | lane_off);
+          const float4 v3 = lds_f4((st.w & kColMask) | lane_off);
+          accumulate<false>(acc, v0, st.x, 1.f);
+          accumulate<false>(acc, v1, st.y, 1.f);
+          accumulate<false>(acc, v2, st.z, 1.f);
+          accumulate<false>(acc, v3, st.w, 1.f);
+        }
+      } else if (!direct) {
+#pragma unroll 4
         for (int t = 0; t < cnt; t += 2) {
           const uint4 st = lds_u4(stage_base + (t >> 1) * (GPW * 16));
-          float4 v0, v1;
-          if (DBG & 2) {
-            v0 = make_float4(__uint_as_float(st.x), __uint_as_float(st.y), 0.f, 1.f);
-            v1 = make_float4(__uint_as_float(st.z), __uint_as_float(st.w), 0.f, 1.f);
-          } else {
-            v0 = lds_f4((st.x & kColMask) | lane_off);
-            v1 = lds_f4((st.z & kColMask) | lane_off);
-          }
-          if (DBG & 1) {
-            add2(acc[0][0], make_float2(v0.x, v0.y)); add2(acc[0][1], make_float2(v0.z, v0.w));
-            add2(acc[1][0], make_float2(v1.x, v1.y)); add2(acc[1][1], make_float2(v1.z, v1.w));
-          } else {
-            accumulate<HAS_PRE>(acc, v0, st.x, __uint_as_float(st.y));
-            accumulate<HAS_PRE>(acc, v1, st.z, __uint_as_float(st.w));
-          }
+          const float4 v0 = lds_f4((st.x & kColMask) | lane_off);
+          const float4 v1 = lds_f4((st.z & kColMask) | lane_off);
+          accumulate<HAS_PRE>(acc, v0, st.x, __uint_as_float(st.y));
+          accumulate<HAS_PRE>(acc, v1, st.z, __uint_as_float(st.w));
         }
       } else {
 #pragma unroll 2
         for (int t = 0; t < cnt; t += 2) {
-          const uint4 st = lds_u4(stage_base + (t >> 1) * (GPW * 16));
-          const float4 v0 = __ldg(xv + size_t(st.x & kColMask) * F4);
-          const float4 v1 = __ldg(xv + size_t(st.z & kColMask) * F4);
-          accumulate<HAS_PRE>(acc, v0, st.x, __uint_as_float(st.y));
-          accumulate<HAS_PRE>(acc, v1, st.z, __uint_as_float(st.w));
+          unsigned o0, o1;
+          float w0 = 1.f, w1 = 1.f;
+          if (HAS_PRE) {
+            const uint4 st = lds_u4(stage_base + (t >> 1) * (GPW * 16));
+            o0 = st.x; o1 = st.z;
+            w0 = __uint_as_float(st.y); w1 = __uint_as_float(st.w);
+          } else {
+            o0 = __float_as_uint(umma::lds_f32(stage_base + (t >> 2) * (GPW * 16) + (t & 3) * 4));
+            o1 = __float_as_uint(umma::lds_f32(stage_base + (t >> 2) * (GPW * 16) + (t & 3) * 4 + 4));
+          }
+          const float4 v0 = __ldg(xv + (o0 & kColMask) * F4);
+          const float4 v1 = __ldg(xv + (o1 & kColMask) * F4);
+          accumulate<HAS_PRE>(acc, v0, o0, w0);
+          accumulate<HAS_PRE>(acc, v1, o1, w1);
         }
       }
       __syncwarp();
     }
+
     // ---- epilogue: self term, mean / post scale, bias, store ----
-    if (a.self_mode == LGK_SELF_REPLACE) {
+    const int rows_here = n_rows - row0;  // >= 4 everywhere but in the last quad of the array (<= 0: no quad)
 #pragma unroll
-      for (int o = 1; o < LPG; o <<= 1) selfcnt += __shfl_xor_sync(0xffffffffu, selfcnt, o);
-    }
-    if (quad_on) {
-#pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int64_t row = row0 + r;
-        if (row < a.n_rows) {
-          float4 res = make_float4(acc[r][0].x, acc[r][0].y, acc[r][1].x, acc[r][1].y);
-          if (a.self_mode != LGK_SELF_NONE) {
-            float c = cself[r];
-            if (a.self_mode == LGK_SELF_REPLACE) c -= float((selfcnt >> (8 * r)) & 0xffu);
-            if (c != 0.f) {
-              if (HAS_PRE) c *= __ldg(a.pre + row);
-              if (lane_on) f4_fma(res, c, __ldg(xv + size_t(row) * F4));
-            }
+    for (int r = 0; r < 4; ++r) {
+      float4 res = make_float4(acc[r][0].x, acc[r][0].y, acc[r][1].x, acc[r][1].y);
+      const unsigned ro = unsigned(row0 + r) * F4;
+      if (SELF != LGK_SELF_NONE) {
+        float c = cself[r];
+        if (SELF == LGK_SELF_REPLACE) c -= float((selfcnt >> (8 * r)) & 0xffu);
+        if (c != 0.f && r < rows_here) {
+          const int row = row0 + r;
+          if (HAS_PRE) c *= __ldg(a.pre + row);
+          float4 xs;
+          if (row >= win_lo && row < win_hi) {  // the row itself is part of the unit's window: it is in the ring
+            const unsigned blk = unsigned(row) / kBlkRows, slot = blk - __umulhi(blk, nb_magic) * unsigned(nb);
+            xs = lds_f4((ring + (slot * kBlkRows + (unsigned(row) & (kBlkRows - 1))) * kSliceBytes) | lane_off);
+          } else {
+            xs = __ldg(xv + ro);
           }
-          res.x = fmaf(res.x, scale[r], bias4.x);
-          res.y = fmaf(res.y, scale[r], bias4.y);
-          res.z = fmaf(res.z, scale[r], bias4.z);
-          res.w = fmaf(res.w, scale[r], bias4.w);
-          if (lane_on) st_stream_f4(ov + size_t(row) * F4, res);
+          f4_fma(res, c, xs);
         }
       }
+      if (SCALE) {
+        const float sc = has_mean ? postv[r] / float(max(deg[r], 1)) : postv[r];
+        res.x = fmaf(res.x, sc, bias4.x);
+        res.y = fmaf(res.y, sc, bias4.y);
+        res.z = fmaf(res.z, sc, bias4.z);
+        res.w = fmaf(res.w, sc, bias4.w);
+      } else {
+        res.x += bias4.x; res.y += bias4.y; res.z += bias4.z; res.w += bias4.w;
+      }
+      if (lane_on && r < rows_here) st_stream_f4(ov + ro, res);
     }
     __syncwarp();
     if (lane == 0) umma::mbar_arrive(&sh->empty[s]);
@@ -571,25 +607,24 @@ int env_int_win(const char* name, int dflt) {
 using WinKernel = void (*)(const WinArgs, const CUtensorMap);
 
 template <int LPG, int NW>
-WinKernel pick_kernel(bool has_pre, int dbg) {
-#define LGK_WIN_PICK(D) case D: return has_pre ? spmm_win_kernel<true, LPG, NW, D> : spmm_win_kernel<false, LPG, NW, D>;
-  switch (dbg) {
-    LGK_WIN_PICK(0) LGK_WIN_PICK(1) LGK_WIN_PICK(2) LGK_WIN_PICK(3) LGK_WIN_PICK(4) LGK_WIN_PICK(7)
-  }
-#undef LGK_WIN_PICK
+WinKernel pick_kernel(bool has_pre, int self_mode, bool scale) {
+#define LGK_WIN_ROW(P, S)                                                                    \
+  if (has_pre == P && self_mode == S) return scale ? spmm_win_kernel<P, LPG, NW, S, true> : spmm_win_kernel<P, LPG, NW, S, false>;
+  LGK_WIN_ROW(false, LGK_SELF_NONE) LGK_WIN_ROW(false, LGK_SELF_REPLACE) LGK_WIN_ROW(false, LGK_SELF_ADD)
+  LGK_WIN_ROW(true, LGK_SELF_NONE) LGK_WIN_ROW(true, LGK_SELF_REPLACE) LGK_WIN_ROW(true, LGK_SELF_ADD)
+#undef LGK_WIN_ROW
   return nullptr;
 }
 
 // one launch of the slice width LPG * 16 bytes
 template <int LPG>
 int launch_win(WinArgs a, int select, int dbg, cudaStream_t stream) {
-  // consumer warps (tuning knob; 24 exist for the 256-byte slices only)
-  static const int warps_env = env_int_win("LGK_WIN_WARPS", 16) == 24 ? 24 : 16;
-  const int warps = LPG == 16 ? warps_env : 16;
+  // consumer warps (tuning knob)
+  static const int warps = env_int_win("LGK_WIN_WARPS", 16) == 24 ? 24 : 16;
   constexpr int slice_bytes = LPG * 16;
   a.select = select;
   a.slices = int(ceil_div(int64_t(a.feat) * 4, slice_bytes));
-  const int fixed = warps * 512 + int(sizeof(WinShared)) + 128;
+  const int fixed = warps * kStageBytes + int(sizeof(WinShared)) + 128;
   const int per_blk = kBlkBytes + (a.pre ? 32 * 4 : 0);
   static const int nb_cap = env_int_win("LGK_WIN_BLOCKS", 1 << 30);  // tuning / test knob: fewer ring blocks
   a.nb = std::min((kSmemMax - fixed) / per_blk, nb_cap);
@@ -601,14 +636,14 @@ int launch_win(WinArgs a, int select, int dbg, cudaStream_t stream) {
   // one CTA per SM; a group of `slices` CTAs shares a span of chunks (more slices than SMs: the CTAs queue)
   const int spans = int(std::max<int64_t>(1, std::min<int64_t>(kNumSMs / std::max(1, std::min(a.slices, kNumSMs)), a.n_chunks)));
   const unsigned grid = unsigned(spans * a.slices);
-  WinKernel kern;
-  if constexpr (LPG == 16) kern = warps == 24 ? pick_kernel<LPG, 24>(a.pre != nullptr, dbg) : pick_kernel<LPG, 16>(a.pre != nullptr, dbg);
-  else kern = pick_kernel<LPG, 16>(a.pre != nullptr, dbg);
-  LGK_REQUIRE(kern, LGK_ERR_BAD_ARG, "LGK_WIN_DEBUG=%d is not instantiated", dbg);
+  const bool scale = a.mean || a.post != nullptr;
+  WinKernel kern = warps == 24 ? pick_kernel<LPG, 24>(a.pre != nullptr, a.self_mode, scale) : pick_kernel<LPG, 16>(a.pre != nullptr, a.self_mode, scale);
+  LGK_REQUIRE(kern, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: no kernel for this mode");
+  (void)dbg;
   int dev = 0;
   cudaGetDevice(&dev);
-  static bool configured[64][2][8] = {};
-  bool& done = configured[dev & 63][a.pre ? 1 : 0][dbg & 7];
+  static bool configured[64][2][3][2] = {};
+  bool& done = configured[dev & 63][a.pre ? 1 : 0][a.self_mode][scale ? 1 : 0];
   if (!done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax);
     if (e != cudaSuccess) {
@@ -663,6 +698,7 @@ extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const u
   LGK_REQUIRE(self_mode >= LGK_SELF_NONE && self_mode <= LGK_SELF_ADD, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: bad self_mode");
   LGK_REQUIRE(feat % 4 == 0 && feat < (1 << 20), LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: feat must be a multiple of 4");
   LGK_REQUIRE(n_rows <= int64_t(kColMask), LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: more than 2^28 - 1 rows");
+  LGK_REQUIRE(n_rows * (feat / 4) < (int64_t(1) << 31), LGK_ERR_UNSUPPORTED, "lgk_spmm_blocked: n_rows * feat / 4 must be below 2^31");
   LGK_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0,
               LGK_ERR_BAD_ARG, "lgk_spmm_blocked: x, out and bias must be 16-byte aligned");
   LGK_REQUIRE(x != out, LGK_ERR_BAD_ARG, "lgk_spmm_blocked: in-place aggregation is not possible");
@@ -679,12 +715,18 @@ extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const u
   a.n_chunks = ceil_div(a.n_quads, kQuadsPerChunk);
   a.feat = int(feat);
   static const int dbg = env_int_win("LGK_WIN_DEBUG", 0);
-  // LGK_WIN_SLICE = 128 | 256 forces one slice width (A/B measurements); default: both are launched and the one the
-  // graph's windows select (qmeta, written by lgk_quad_build) does the work -- the other returns at once.  The host
-  // never reads the statistic (no synchronisation, CUDA-graph-capture safe).  Rows narrower than 256 bytes: 128 only.
-  static const int force = env_int_win("LGK_WIN_SLICE", 0);
-  if (force == 128 || feat * 4 <= 128) return launch_win<8>(a, 0, dbg, stream);
-  if (force == 256) return launch_win<16>(a, 0, dbg, stream);
-  if (int rc = launch_win<16>(a, 1, dbg, stream)) return rc;
-  return launch_win<8>(a, 1, dbg, stream);
+  // 128-byte slices (ring of ~1700 source rows, units of 256 destination rows) are the default: measured faster than the
+  // 256-byte variant even where the latter's ring suffices (profiles/README.md r02).  LGK_WIN_SLICE=256 forces that variant,
+  // LGK_WIN_SLICE=auto launches both and lets the window statistic of lgk_quad_build choose on the device.
+  static const int force = [] {
+    const char* v = getenv("LGK_WIN_SLICE");
+    if (!v || !*v) return 128;
+    return v[0] == 'a' ? 0 : atoi(v);
+  }();
+  if (force == 256 && feat * 4 > 128) return launch_win<16>(a, 0, dbg, stream);
+  if (force == 0 && feat * 4 > 128) {
+    if (int rc = launch_win<16>(a, 1, dbg, stream)) return rc;
+    return launch_win<8>(a, 1, dbg, stream);
+  }
+  return launch_win<8>(a, 0, dbg, stream);
 }

@@ -167,7 +167,7 @@ def quad_build(ptr: Tensor, idx: Tensor) -> Quads:
     i32 = dict(dtype=torch.int32, device=dev)
     nq = (n + 3) // 4
     nc = int(L.query("lgk_quad_chunks", n))
-    q = Quads(torch.empty(max(nq, 1), **i32), torch.empty(max(idx.numel(), 1), **i32), torch.empty(max(nc, 1), **i32),
+    q = Quads(torch.empty(2 * max(nq, 1), **i32), torch.empty(max(idx.numel(), 1), **i32), torch.empty(max(nc, 1), **i32),
               torch.empty(max(nc, 1), **i32), torch.empty(4, **i32))
     L.call("lgk_quad_build", _chk(ptr, torch.int32, "ptr"), _chk(idx, torch.int32, "idx"), n, q.qlen.data_ptr(),
            q.qent.data_ptr(), q.cmin.data_ptr(), q.cmax.data_ptr(), q.qmeta.data_ptr(), _stream())
@@ -180,7 +180,7 @@ _WIN_MIN_ELEMS = int(os.environ.get("LGK_WIN_MIN_ELEMS", str(1 << 23)))
 
 def blocked_eligible(x: Tensor, reduce: str, ew) -> bool:
     return (ew is None and _REDUCE[reduce] in (SUM, MEAN) and x.dtype == torch.float32 and x.dim() == 2
-            and x.size(1) % 4 == 0 and x.numel() >= _WIN_MIN_ELEMS and x.size(0) < (1 << 28))
+            and x.size(1) % 4 == 0 and x.numel() >= _WIN_MIN_ELEMS and x.size(0) < (1 << 28) and x.numel() // 4 < (1 << 31))
 
 
 def spmm(ptr: Tensor, idx: Tensor, x: Tensor, reduce: str = "sum", *, emap: Optional[Tensor] = None,

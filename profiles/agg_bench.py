@@ -49,8 +49,8 @@ def timeit(fn, iters=iters, warm=3):
 t_q = timeit(lambda: ops.quad_build(g.rowptr, g.col), 5, 1)
 qc, qr = g.quads("csr"), g.quads("csc")
 torch.cuda.synchronize()
-merged = int(qc.qlen.sum().item())
-merged_t = int(qr.qlen.sum().item())
+merged = int(qc.qlen.view(-1, 2)[:, 0].sum().item())
+merged_t = int(qr.qlen.view(-1, 2)[:, 0].sum().item())
 band = (qc.cmax - qc.cmin + 1)[: (N // 4 + 15) // 16]
 print(json.dumps({"what": "quad_build", "us": round(t_q * 1e3, 1), "N": N, "E": E, "merged_csr": merged, "merged_csc": merged_t,
                   "gathers_saved": round(E / merged, 3), "chunk_window_rows_max": int(band.max().item()),
@@ -65,7 +65,16 @@ cases = [
     ("gcn_fwd", lambda q: ops.spmm(g.rowptr, g.col, x, "sum", quads=q and qc, **kw), gcn),
     ("gcn_bwd", lambda q: ops.spmm(g.colptr, g.row, x, "sum", quads=q and qr, **kw), gcn),
     ("mean_fwd", lambda q: ops.spmm(g.rowptr, g.col, x, "mean", quads=q and qc), plain),
+    ("sum_pre_only", lambda q: ops.spmm(g.rowptr, g.col, x, "sum", quads=q and qc, pre=dinv), plain + 4 * N),
+    ("sum_post_only", lambda q: ops.spmm(g.rowptr, g.col, x, "sum", quads=q and qc, post=dinv), plain + 4 * N),
+    ("sum_selfreplace_only", lambda q: ops.spmm(g.rowptr, g.col, x, "sum", quads=q and qc, self_mode=ops.SELF_REPLACE), plain),
+    ("sum_selfadd_only", lambda q: ops.spmm(g.rowptr, g.col, x, "sum", quads=q and qc, self_mode=ops.SELF_ADD, self_fill=1.5), plain),
 ]
+if os.environ.get("AGG_ONLY_BLOCKED"):
+    for name, fn, nbytes in cases:
+        ms = timeit(lambda: fn(True))
+        print(json.dumps({"what": name, "kernel": "lgk_spmm_blocked", "us": round(ms * 1e3, 1), "frac": round(nbytes / (ms * 1e-3) / 1e9 / peak, 4)}), flush=True)
+    sys.exit(0)
 for name, fn, nbytes in cases:
     a = fn(None)
     b = fn(True)

@@ -94,7 +94,8 @@ def test_quad_structure_is_the_four_way_merge(dev, name):
         q = g.quads(which)
         ptr_h, idx_h = ptr.cpu(), idx.cpu()
         want = _host_quads(ptr_h, idx_h, n)
-        qlen, qent = q.qlen.cpu().tolist(), q.qent.cpu()
+        qhdr = q.qlen.cpu().view(-1, 2)
+        qlen, qent = qhdr[:, 0].tolist(), q.qent.cpu()
         los, his = [], []
         for gq, ent in enumerate(want):
             assert qlen[gq] == len(ent), (which, gq)
@@ -102,6 +103,8 @@ def test_quad_structure_is_the_four_way_merge(dev, name):
             words = qent[start:start + len(ent)].tolist()
             got = [((w & 0xFFFFFFFF) & 0x0FFFFFFF, ((w & 0xFFFFFFFF) >> 28) & 0xF) for w in words]
             assert got == ent, (which, gq)
+            selfc = sum(min(255, sum(1 for m, k in ent if m == 4 * gq + r and (k >> r) & 1)) << (8 * r) for r in range(4))
+            assert int(qhdr[gq, 1]) & 0xFFFFFFFF == selfc, (which, gq)
         for c in range((len(want) + 15) // 16):
             cols = [m for ent in want[16 * c:16 * c + 16] for m, _ in ent]
             los.append(min(cols) if cols else 2 ** 31 - 1)
