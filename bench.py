@@ -398,7 +398,10 @@ def run_b200(args):
         if world > 1:  # identical replicas
             for p in model.parameters():
                 dist.broadcast(p.data, 0)
-        opt = train.FlatAdam(model, lr=1e-3, weight_decay=spec["weight_decay"] if weight_decay is None else weight_decay)
+        # N > 1: gradients in a peer-visible bucket; the all-reduce is fused with Adam inside the captured step (csrc/dp.cu)
+        bucket = train.PeerBucket(dist.group.WORLD) if world > 1 and train.DP_FUSED else None
+        opt = train.FlatAdam(model, lr=1e-3, weight_decay=spec["weight_decay"] if weight_decay is None else weight_decay,
+                             peer_bucket=bucket)
         return model, opt, train.TrainStep(model, opt, spec["loss"], 5, use_cuda_graph=True, process_group=None, world_size=world)
 
     model, opt, step = make_step()
@@ -659,19 +662,42 @@ def secondary_legs(args, spec, graphs, total_graphs, world, rank, dev, host, dev
                                            "device gather of x, pos, y, kNN graph, CSR/CSC build, fwd, bwd, optimiser" % len(counts_all))
     del x_all, pos_all, rbatch
 
-    # ---- collective_us: the gradient all-reduce alone ----------------------------------------------------------------
+    # ---- collective_us: the gradient exchange alone -------------------------------------------------------------------
+    # fused: lgk_dp_allreduce_adam (peer-memory all-reduce + Adam + bucket release, two kernels) in a CUDA graph of 20 calls;
+    # nccl: dist.all_reduce of the same bucket, eager, as the unfused step issues it
     if world > 1:
-        for _ in range(10):
-            dist.all_reduce(opt.grad)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(100):
-            dist.all_reduce(opt.grad)
-        e1.record()
-        torch.cuda.synchronize()
-        out["collective_us"] = round(max_over_ranks(e0.elapsed_time(e1)) * 10.0, 2)
+        def per_call_us(fn, graph_calls):
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+            if graph_calls:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    for _ in range(graph_calls):
+                        fn()
+                run, calls = g.replay, 5 * graph_calls
+                reps = 5
+            else:
+                run, calls, reps = fn, 100, 100
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                run()
+            e1.record()
+            torch.cuda.synchronize()
+            return round(max_over_ranks(e0.elapsed_time(e1)) * 1000.0 / calls, 2)
+
+        state = [t.clone() for t in opt.state_tensors()]
+        if getattr(opt, "peer_bucket", None) is not None:
+            out["collective_us"] = per_call_us(opt.step_dp, 20)
+            out["collective_kind"] = "lgk_dp_allreduce_adam (NVLink peer loads, fused with Adam; in-graph)"
+        out["collective_nccl_us"] = per_call_us(lambda: dist.all_reduce(opt.grad), 0)
+        if "collective_us" not in out:
+            out["collective_us"], out["collective_kind"] = out["collective_nccl_us"], "NCCL all-reduce (eager) + lgk_adam_step"
         out["collective_bytes"] = int(opt.grad.numel() * 4)
+        for dst, src in zip(opt.state_tensors(), state):
+            dst.copy_(src)
     return out
 
 

@@ -345,6 +345,23 @@ LGK_API int lgk_act_dropout_fwd(const float* x, float* y, int64_t n, int act, fl
 LGK_API int lgk_act_dropout_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, float dropout_p, uint64_t seed,
                         const int64_t* seed_dev, void* stream);
 
+/* Data-parallel step without NCCL: the gradient all-reduce over NVLink peer memory fused with Adam / AdamW.
+ * Every rank owns a symmetric allocation of lgk_dp_buffer_bytes(n, world) bytes that is mapped into all peers (layout: 8 KB
+ * of flags, the n fp32 gradients at lgk_dp_grad_offset_bytes(), then receive slots float [2][world][n]); peer_base_dev is
+ * a DEVICE array of `world` pointers to those allocations, in rank order (entry `rank` is the caller's own).  One call
+ * enqueues ONE kernel: every CTA pushes its chunk of the own gradients into its slot of every peer, raises a per-chunk
+ * flag there, waits for the peers' flags of the same chunk, sums all ranks' chunks in rank order (bit-identical on every
+ * rank), scales by 1/world, applies Adam to the caller's parameters and clears the own bucket.  epoch_dev is int64[2],
+ * zero at start, advanced by the call itself and never rewound; *step_dev = the Adam step count for the bias corrections: of
+ * THIS update (>= 1) when advance_step = 0, of the updates completed so far when advance_step = 1 (the kernel adds one
+ * and stores it back).  n % 4 == 0, world <= 16.  Capturable in a CUDA graph; all ranks must enqueue the call once per
+ * step with the same n.                                                                                              */
+LGK_API int64_t lgk_dp_buffer_bytes(int64_t n, int world);
+LGK_API int64_t lgk_dp_grad_offset_bytes(void);
+LGK_API int lgk_dp_allreduce_adam(const uint64_t* peer_base_dev, int rank, int world, int64_t n, float* param, float* exp_avg,
+                          float* exp_avg_sq, float lr, float beta1, float beta2, float eps, float weight_decay,
+                          int64_t* step_dev, int64_t* epoch_dev, int adamw, int advance_step, void* stream);
+
 /* torch.optim.SGD over one flat fp32 buffer (reference models/base.py:167-168: lr and weight_decay; momentum /
  * nesterov with dampening 0 are supported through a zero-initialised momentum_buf, NULL when momentum == 0):
  * g = grad_scale * grad + weight_decay * p; [b = momentum * b + g; g = nesterov ? g + momentum * b : b;] p -= lr * g.

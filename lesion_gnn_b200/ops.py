@@ -440,6 +440,18 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
            _chk(step_dev, torch.int64, "step_dev"), float(grad_scale), int(adamw), int(zero_grad), int(advance_step), _stream())
 
 
+def dp_allreduce_adam(peer_base_dev: int, rank: int, world: int, param: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, *, lr: float,
+                      betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0, step_dev: Tensor, epoch_dev: Tensor,
+                      adamw: bool = False, advance_step: bool = False) -> None:
+    """gradient all-reduce over peer memory fused with Adam (include/lgk.h lgk_dp_allreduce_adam); peer_base_dev: address of the
+    device array of the ranks' symmetric buffers; advance_step: the kernel itself moves step_dev[0] on by one"""
+    f32 = torch.float32
+    _lib.lib().call("lgk_dp_allreduce_adam", int(peer_base_dev), int(rank), int(world), param.numel(), _chk(param, f32, "param"),
+                    _chk(exp_avg, f32), _chk(exp_avg_sq, f32), float(lr), float(betas[0]), float(betas[1]), float(eps),
+                    float(weight_decay), _chk(step_dev, torch.int64, "step_dev"), _chk(epoch_dev, torch.int64, "epoch_dev"),
+                    int(adamw), int(advance_step), _stream())
+
+
 def clamped_regression_loss(logits: Tensor, y: Tensor, lo: float, hi: float, kind: int, want_grad: bool = True,
                             grad_scale: float = 1.0):
     """-> (loss [] f32, grad_scale * d loss / d logits [n] f32 | None): MSE (kind 0) / SmoothL1 (kind 1) of clamp(logits, lo, hi)

@@ -33,7 +33,9 @@ class FlatParams:
     views, backward accumulates straight into the gradient bucket, and the data-parallel all-reduce is ONE
     collective over `grad`."""
 
-    def __init__(self, module: nn.Module):
+    def __init__(self, module: nn.Module, grad_alloc: Optional[Callable[[int, torch.device], Tensor]] = None):
+        """grad_alloc(numel, device) -> the fp32 gradient bucket (default: a plain zeroed buffer; PeerBucket places it in
+        memory that the other ranks can read)"""
         params = [p for p in module.parameters() if p.requires_grad]
         if not params:
             raise ValueError("no trainable parameters")
@@ -45,7 +47,9 @@ class FlatParams:
             offs.append(total)
             total += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
         self.param = torch.zeros(total, dtype=torch.float32, device=dev)
-        self.grad = torch.zeros_like(self.param)
+        self.grad = torch.zeros_like(self.param) if grad_alloc is None else grad_alloc(total, dev)
+        if self.grad.shape != self.param.shape or self.grad.dtype != torch.float32:
+            raise ValueError("grad_alloc must return a float32 tensor of the bucket's length")
         self.params, self.offsets = params, offs
         for p, o in zip(params, offs):
             self.param[o:o + p.numel()].view_as(p).copy_(p.data)
@@ -75,13 +79,52 @@ def dp_loss_weight(local_graphs: int, global_graphs: int, world_size: int) -> fl
     return float(local_graphs) * world_size / float(global_graphs)
 
 
+class PeerBucket:
+    """The gradient bucket of one rank inside a SYMMETRIC allocation that every peer GPU of the node maps over NVLink
+    (torch.distributed._symmetric_memory), laid out as lgk_dp_allreduce_adam wants it (include/lgk.h): flags, the gradients,
+    then the slots the peers push their gradients into.  `group=None` gives a single-rank bucket in ordinary device memory (tests, world size 1)."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.buffer = self.grad = self.peer_base = self.handle = None
+        self.rank, self.world = 0, 1
+
+    def __call__(self, numel: int, device: torch.device) -> Tensor:
+        from . import _lib
+        L = _lib.lib()
+        off = int(L.query("lgk_dp_grad_offset_bytes"))
+        if self.group is not None:
+            import torch.distributed as dist
+            self.world = dist.get_world_size(self.group)
+        nbytes = int(L.query("lgk_dp_buffer_bytes", numel, self.world))
+        if self.group is None:
+            self.buffer = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+            self.peer_base = torch.tensor([self.buffer.data_ptr()], dtype=torch.int64, device=device)
+            self.peer_base_ptr = self.peer_base.data_ptr()
+        else:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buffer = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+            self.handle = symm_mem.rendezvous(self.buffer, self.group)
+            self.rank, self.world = self.handle.rank, self.handle.world_size
+            self.buffer.zero_()
+            torch.cuda.synchronize(device)
+            dist.barrier(group=self.group)  # every pad is zero before the first signal can arrive
+            self.peer_base_ptr = int(self.handle.buffer_ptrs_dev)
+        self.grad = self.buffer[off:off + 4 * numel].view(torch.float32)
+        self.epoch_dev = torch.zeros(2, dtype=torch.int64, device=device)  # never rewound (unlike the optimiser's step count)
+        return self.grad
+
+
 class FlatAdam(FlatParams):
     """torch.optim.Adam / AdamW (reference models/base.py:162-170) as one lgk_adam_step launch over the flat
-    buffers.  CUDA only."""
+    buffers.  CUDA only.  With `peer_bucket` (a PeerBucket) the gradients live in peer-visible memory and `step_dp()`
+    is the data-parallel step: all-reduce over NVLink fused with the update, no NCCL call (csrc/dp.cu)."""
 
     def __init__(self, module: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0, adamw: bool = False):
-        super().__init__(module)
+                 weight_decay: float = 0.0, adamw: bool = False, peer_bucket: Optional["PeerBucket"] = None):
+        super().__init__(module, grad_alloc=peer_bucket)
+        self.peer_bucket = peer_bucket
         if self.param.device.type != "cuda":
             raise RuntimeError("FlatAdam needs the module on a CUDA device: lesion_gnn_b200 has no CPU path")
         self.exp_avg = torch.zeros_like(self.param)
@@ -101,6 +144,18 @@ class FlatAdam(FlatParams):
                       weight_decay=self.weight_decay, step=0, step_dev=self.step_dev, grad_scale=grad_scale,
                       adamw=self.adamw, zero_grad=_ADAM_ZEROES_GRAD, advance_step=_ADAM_ADVANCES_STEP)
         self._grad_is_zero = _ADAM_ZEROES_GRAD  # the kernel cleared the bucket: the next zero_grad() launches nothing
+
+    def step_dp(self) -> None:
+        """data-parallel step: mean of all ranks' gradient buckets (read through NVLink peer mappings, summed in rank order)
+        and the Adam update in ONE kernel (pushed over NVLink into per-rank slots, summed in rank order); capturable, no host sync.  Every
+        rank of the bucket's group must call it once per step."""
+        pb = self.peer_bucket
+        if pb is None:
+            raise RuntimeError("step_dp() needs FlatAdam(..., peer_bucket=PeerBucket(group))")
+        ops.dp_allreduce_adam(pb.peer_base_ptr, pb.rank, pb.world, self.param, self.exp_avg, self.exp_avg_sq, lr=self.lr,
+                              betas=self.betas, eps=self.eps, weight_decay=self.weight_decay, step_dev=self.step_dev,
+                              epoch_dev=pb.epoch_dev, adamw=self.adamw, advance_step=True)
+        self._grad_is_zero = True
 
 
 class FlatSGD(FlatParams):
@@ -127,16 +182,28 @@ class FlatSGD(FlatParams):
         self._grad_is_zero = _ADAM_ZEROES_GRAD
 
 
-def make_optimizer(module: nn.Module, algo: str = "adam", lr: float = 1e-3, weight_decay: float = 0.0):
-    """reference models/base.py:162-170 `configure_optimizers`: OptimizerAlgo ADAM / ADAMW / SGD"""
+# 0 = data-parallel steps use one NCCL all-reduce of the bucket + lgk_adam_step instead of the fused peer-memory kernel
+DP_FUSED = os.environ.get("LGK_DP_FUSED", "1") != "0"
+
+
+def make_optimizer(module: nn.Module, algo: str = "adam", lr: float = 1e-3, weight_decay: float = 0.0, process_group=None,
+                   world_size: int = 1):
+    """reference models/base.py:162-170 `configure_optimizers`: OptimizerAlgo ADAM / ADAMW / SGD.  With world_size > 1 the
+    Adam variants keep their gradients in a PeerBucket (fused NVLink all-reduce + update) unless LGK_DP_FUSED=0."""
     algo = algo.lower()
+    pb = PeerBucket(process_group if process_group is not None else _world_group()) if world_size > 1 and DP_FUSED and algo != "sgd" else None
     if algo == "adam":
-        return FlatAdam(module, lr=lr, weight_decay=weight_decay)
+        return FlatAdam(module, lr=lr, weight_decay=weight_decay, peer_bucket=pb)
     if algo == "adamw":
-        return FlatAdam(module, lr=lr, weight_decay=weight_decay, adamw=True)
+        return FlatAdam(module, lr=lr, weight_decay=weight_decay, adamw=True, peer_bucket=pb)
     if algo == "sgd":
         return FlatSGD(module, lr=lr, weight_decay=weight_decay)
     raise ValueError(f"unknown optimizer {algo!r}")
+
+
+def _world_group():
+    import torch.distributed as dist
+    return dist.group.WORLD
 
 
 class _CrossEntropyLoss(torch.autograd.Function):
@@ -254,8 +321,9 @@ def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_clas
 class TrainStep:
     """One optimisation step over a resident DeviceBatch; optionally CUDA-graph captured.
 
-    world_size > 1: fwd+bwd (graph) -> one NCCL all-reduce of the flat gradient bucket -> fused Adam with
-    grad_scale = 1/world_size.
+    world_size > 1: the optimiser's gradients live in a PeerBucket and the all-reduce is fused with Adam INSIDE the graph
+    (FlatAdam.step_dp, csrc/dp.cu); without a PeerBucket (LGK_DP_FUSED=0, SGD) fwd+bwd (graph) -> one NCCL all-reduce of the
+    flat gradient bucket -> fused Adam with grad_scale = 1/world_size.
     """
 
     def __init__(self, model: nn.Module, opt: FlatAdam, loss_type: str = "MSE", num_classes: int = 5,
@@ -267,6 +335,7 @@ class TrainStep:
         self.class_weights = None if class_weights is None else class_weights.to(device=dev, dtype=torch.float32).contiguous()
         self.use_cuda_graph = use_cuda_graph
         self.pg, self.world_size = process_group, world_size
+        self._fused_dp = world_size > 1 and getattr(opt, "peer_bucket", None) is not None and opt.peer_bucket.world == world_size
         self._graphs = {}
         # parameter-gradient kernels are dealt over this many side streams (tuning knob: LGK_SIDE_STREAMS, 0 = none)
         nside = int(os.environ.get("LGK_SIDE_STREAMS", "2"))
@@ -283,10 +352,12 @@ class TrainStep:
             loss = forward_backward(self.model, db, self.loss_type, self.num_classes, self._build, self.class_weights)
         if self.world_size == 1:
             self.opt.step()
+        elif self._fused_dp:
+            self.opt.step_dp()  # inside the captured graph: no NCCL call, no eager tail
         return loss
 
     def _finish_dp(self) -> None:
-        if self.world_size > 1:
+        if self.world_size > 1 and not self._fused_dp:
             self.opt.all_reduce(self.pg)
             self.opt.step(grad_scale=1.0 / self.world_size)
 

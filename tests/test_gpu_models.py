@@ -180,15 +180,16 @@ def test_graph_replays_draw_fresh_attention_dropout_masks(dev):
     hb = knn_batch(12, "ddr", 24, 6, seed=5)
     torch.manual_seed(1)
     for graphed in (True, False):
-        mod = lg.models.GAT(24, [32, 32, 32], 1, heads=4, dropout=0.35).to(dev).train()
+        # 5 logits + cross-entropy: no clamp that could hide the masks (the regression loss clamps logits to [0, 4])
+        mod = lg.models.GAT(24, [32, 32, 32], 5, heads=4, dropout=0.35).to(dev).train()
         opt = train.FlatAdam(mod, lr=0.0)
-        step = train.TrainStep(mod, opt, "MSE", 5, use_cuda_graph=graphed)
+        step = train.TrainStep(mod, opt, "CE", 5, use_cuda_graph=graphed)
         db = train.DeviceBatch(hb, dev)
         db.copy_from(hb)
         losses = [float(step(db)) for _ in range(4)]
         assert len(set(losses)) == 4, (graphed, losses)
         mod.eval()
-        ev = train.TrainStep(mod, train.FlatAdam(mod, lr=0.0), "MSE", 5, use_cuda_graph=graphed)
+        ev = train.TrainStep(mod, train.FlatAdam(mod, lr=0.0), "CE", 5, use_cuda_graph=graphed)
         l0, l1 = float(ev(db)), float(ev(db))
         assert l0 == l1, "eval mode must not drop anything"
 
