@@ -276,9 +276,19 @@ LGK_API int lgk_sort_pool_bwd(const void* dy, const int32_t* sel, void* dx,
  * ------------------------------------------------------------------------------------------------ */
 
 /* out[n,m] = act( rowscale[n] * sum_k x[n,k] W[m,k] + bias[m] + (accumulate ? out[n,m] : 0) )
- * fp32: FFMA (TF32 would break the 1e-5 parity bar); rowscale, bias may be NULL.                      */
+ * `dtype` is the storage type of the ACTIVATIONS (x, out, dy, dx): LGK_F32 or LGK_BF16; weights, biases, their
+ * gradients and all accumulators are fp32.  fp32: 3xTF32 on tcgen05 for tall products (single-pass TF32 would break the
+ * 1e-5 bar), FFMA otherwise; bf16: FFMA on bf16 loads.  rowscale, bias may be NULL.                     */
 LGK_API int lgk_linear_fwd(const void* x, const float* weight, const float* bias, const float* rowscale, void* out,
                    int64_t n, int64_t k, int64_t m, int act, int accumulate, int dtype, void* stream);
+/* GATConv.lin fused with the attention-logit halves (reference models/gat.py:31,51; PyG GATConv.forward: x = lin(x),
+ * alpha_src = (x * att_src).sum(-1)):  out[n, H*C] = x W^T (no bias) and a_src[n,H] = <out[n,h,:], att_src[h,:]>, a_dst
+ * likewise, formed from the fp32 ACCUMULATORS in the transform's epilogue (before out is rounded to `dtype`) whenever the
+ * head width allows it (chan in {16, 32, 64} on the tensor-core path, chan % 4 == 0 and chan | 64 on the FFMA path);
+ * other widths run the transform and then lgk_gat_alpha on the stored out.                                   */
+LGK_API int lgk_linear_gat_fused(int64_t n, int64_t k, int heads, int chan, int dtype); /* 1: epilogue form (aligned pointers assumed) */
+LGK_API int lgk_linear_gat_fwd(const void* x, const float* weight, const float* att_src, const float* att_dst, void* out,
+                       float* a_src, float* a_dst, int64_t n, int64_t k, int heads, int chan, int dtype, void* stream);
 /* dx[n,k] = sum_m dy[n,m] W[m,k]  (+ dx if accumulate) */
 LGK_API int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, int64_t n, int64_t k, int64_t m,
                      int accumulate, int dtype, void* stream);
@@ -329,21 +339,21 @@ LGK_API int lgk_gather_rows(const void* src, const int64_t* index, void* out, in
  * reads them).  weight / bias may be NULL (affine=False).  dropout: counter RNG keyed on (seed, *seed_dev, element), the
  * same function in the backward -- no mask is stored.  workspace: lgk_bn_workspace_bytes(n, d).                    */
 LGK_API int64_t lgk_bn_workspace_bytes(int64_t n, int64_t d);
-LGK_API int lgk_bn_act_fwd(const float* x, const float* weight, const float* bias, float* running_mean, float* running_var,
-                   int64_t* num_batches_tracked, float* y, float* save_mean, float* save_invstd, int64_t n, int64_t d,
+LGK_API int lgk_bn_act_fwd(const void* x, const float* weight, const float* bias, float* running_mean, float* running_var,
+                   int64_t* num_batches_tracked, void* y, float* save_mean, float* save_invstd, int64_t n, int64_t d,
                    float eps, float momentum, int training, int act, float dropout_p, uint64_t seed, const int64_t* seed_dev,
-                   void* workspace, int64_t workspace_bytes, void* stream);
+                   void* workspace, int64_t workspace_bytes, int dtype, void* stream);
 /* dx, dweight (+)= sum g xhat, dbias (+)= sum g with g = dy * dropout keep * act'(z), recomputed from x and the saved
  * statistics; training != 0: the batch statistics take part in dx.  dweight / dbias may be NULL.                  */
-LGK_API int lgk_bn_act_bwd(const float* x, const float* dy, const float* weight, const float* bias, const float* save_mean,
-                   const float* save_invstd, float* dx, float* dweight, float* dbias, int accumulate, int64_t n, int64_t d,
+LGK_API int lgk_bn_act_bwd(const void* x, const void* dy, const float* weight, const float* bias, const float* save_mean,
+                   const float* save_invstd, void* dx, float* dweight, float* dbias, int accumulate, int64_t n, int64_t d,
                    int training, int act, float dropout_p, uint64_t seed, const int64_t* seed_dev,
-                   void* workspace, int64_t workspace_bytes, void* stream);
+                   void* workspace, int64_t workspace_bytes, int dtype, void* stream);
 /* y = dropout(act(x)) and dx = dy * keep * act'(x) (x = the pre-activation input), n elements fp32 */
-LGK_API int lgk_act_dropout_fwd(const float* x, float* y, int64_t n, int act, float dropout_p, uint64_t seed,
-                        const int64_t* seed_dev, void* stream);
-LGK_API int lgk_act_dropout_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, float dropout_p, uint64_t seed,
-                        const int64_t* seed_dev, void* stream);
+LGK_API int lgk_act_dropout_fwd(const void* x, void* y, int64_t n, int act, float dropout_p, uint64_t seed,
+                        const int64_t* seed_dev, int dtype, void* stream);
+LGK_API int lgk_act_dropout_bwd(const void* x, const void* dy, void* dx, int64_t n, int act, float dropout_p, uint64_t seed,
+                        const int64_t* seed_dev, int dtype, void* stream);
 
 /* Data-parallel step without NCCL: the gradient all-reduce over NVLink peer memory fused with Adam / AdamW.
  * Every rank owns a symmetric allocation of lgk_dp_buffer_bytes(n, world) bytes that is mapped into all peers (layout: 8 KB

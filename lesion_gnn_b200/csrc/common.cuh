@@ -175,6 +175,15 @@ __device__ __forceinline__ float uniform_hash(uint64_t seed, uint32_t slot, uint
   return float(uint32_t(z >> 40)) * (1.0f / 16777216.0f);
 }
 
+// attention-logit halves computed in the epilogue of GATConv's transform (lgk_linear_gat_fwd)
+struct GatAlpha {
+  const float* att_src;  // [heads * chan]
+  const float* att_dst;
+  float* a_src;          // [n, heads]
+  float* a_dst;
+  int heads, chan;
+};
+
 // Second stage of every slab reduction in the library (weight / bias / attention-vector gradients): out (+)= sum over
 // slabs of partial[slab][t], t < count_a goes to out_a, the rest to out_b.  32 outputs x 8 slab lanes per CTA: a
 // lane adds its slabs in ascending order, the 8 lane sums are combined in a fixed order -- deterministic, and the

@@ -27,7 +27,7 @@ bool grad_w_tc_fuses_db(int64_t k);
 int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n, int64_t k, int64_t m, int fuse_db,
                      cudaStream_t stream);
 int launch_linear_tma(const float* x, const float* w, const float* bias, const float* rowscale, float* out, int64_t n,
-                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream, bool* done);
+                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream, bool* done, const GatAlpha* alpha = nullptr);
 namespace {
 
 // Products with at least this many rows and a reduction of at least 32 go to the tensor cores; below that the
@@ -41,10 +41,21 @@ bool use_tensor_cores(int64_t n, int64_t k) {
 constexpr int BI = 128, BJ = 64, BR = 16, PAD = 4, kThreads = 256;
 constexpr int TI = 8, TJ = 4;
 
+// activations (x, out, dy, dx) are float or bf16; weights, biases and every gradient of a parameter stay fp32, as do all
+// accumulators.  4 consecutive elements per load: 16 bytes of fp32, 8 bytes of bf16.
+template <typename T>
+__device__ __forceinline__ float4 ld4(const T* p);
+template <>
+__device__ __forceinline__ float4 ld4<float>(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+template <>
+__device__ __forceinline__ float4 ld4<__nv_bfloat16>(const __nv_bfloat16* p) {
+  return bf16x4_to_f4(__ldg(reinterpret_cast<const uint2*>(p)));
+}
+
 struct GemmArgs {
-  const float* A;
-  const float* B;
-  float* C;
+  const void* A;
+  const void* B;
+  void* C;
   int64_t I, J, R;
   int64_t lda, ldb;   // stride of the non-contiguous index of A / B
   int64_t sCi, sCj;   // output strides
@@ -54,11 +65,12 @@ struct GemmArgs {
   int accumulate;
   int64_t r_chunk;        // rows of R per blockIdx.z (split)
   int64_t split_stride;   // elements between split partials (0 when not split)
+  GatAlpha alpha;         // a_src != nullptr: attention-logit halves from the accumulators (forward of GATConv.lin only)
 };
 
 // load one [rows x BR] tile of an operand whose element (i, r) sits at base[i * ld + r]  (r contiguous)
-template <int ROWS, bool VEC>
-__device__ __forceinline__ void load_rc(const float* __restrict__ base, int64_t ld, int64_t i0, int64_t imax, int64_t r0,
+template <int ROWS, bool VEC, typename T>
+__device__ __forceinline__ void load_rc(const T* __restrict__ base, int64_t ld, int64_t i0, int64_t imax, int64_t r0,
                                         int64_t rmax, float (&reg)[ROWS / 16]) {
   if (VEC) {
     const int r4 = threadIdx.x & 3, ii = threadIdx.x >> 2;  // 64 rows per pass, 4 floats each
@@ -66,7 +78,7 @@ __device__ __forceinline__ void load_rc(const float* __restrict__ base, int64_t 
     for (int u = 0; u < ROWS / 64; ++u) {
       const int64_t i = i0 + ii + 64 * u, r = r0 + r4 * 4;
       float4 v = f4_zero();
-      if (i < imax && r < rmax) v = __ldg(reinterpret_cast<const float4*>(base + i * ld + r));
+      if (i < imax && r < rmax) v = ld4<T>(base + i * ld + r);
       reg[u * 4 + 0] = v.x; reg[u * 4 + 1] = v.y; reg[u * 4 + 2] = v.z; reg[u * 4 + 3] = v.w;
     }
   } else {
@@ -74,7 +86,7 @@ __device__ __forceinline__ void load_rc(const float* __restrict__ base, int64_t 
 #pragma unroll
     for (int u = 0; u < ROWS / 16; ++u) {
       const int64_t i = i0 + ii + 16 * u, r = r0 + rr;
-      reg[u] = (i < imax && r < rmax) ? __ldg(base + i * ld + r) : 0.f;
+      reg[u] = (i < imax && r < rmax) ? Vec4<T>::load1(base, i * ld + r) : 0.f;
     }
   }
 }
@@ -93,8 +105,8 @@ __device__ __forceinline__ void store_rc(float (*s)[ROWS + PAD], const float (&r
   }
 }
 // operand whose element (i, r) sits at base[r * ld + i]  (i contiguous)
-template <int ROWS, bool VEC>
-__device__ __forceinline__ void load_ic(const float* __restrict__ base, int64_t ld, int64_t i0, int64_t imax, int64_t r0,
+template <int ROWS, bool VEC, typename T>
+__device__ __forceinline__ void load_ic(const T* __restrict__ base, int64_t ld, int64_t i0, int64_t imax, int64_t r0,
                                         int64_t rmax, float (&reg)[ROWS / 16]) {
   if (VEC) {
     constexpr int V = ROWS / 4;           // float4 per r
@@ -104,7 +116,7 @@ __device__ __forceinline__ void load_ic(const float* __restrict__ base, int64_t 
     for (int u = 0; u < BR / RP; ++u) {
       const int64_t i = i0 + i4 * 4, r = r0 + rr + RP * u;
       float4 v = f4_zero();
-      if (i < imax && r < rmax) v = __ldg(reinterpret_cast<const float4*>(base + r * ld + i));
+      if (i < imax && r < rmax) v = ld4<T>(base + r * ld + i);
       reg[u * 4 + 0] = v.x; reg[u * 4 + 1] = v.y; reg[u * 4 + 2] = v.z; reg[u * 4 + 3] = v.w;
     }
   } else {
@@ -113,7 +125,7 @@ __device__ __forceinline__ void load_ic(const float* __restrict__ base, int64_t 
 #pragma unroll
     for (int u = 0; u < BR / RP; ++u) {
       const int64_t i = i0 + ii, r = r0 + rr + RP * u;
-      reg[u] = (i < imax && r < rmax) ? __ldg(base + r * ld + i) : 0.f;
+      reg[u] = (i < imax && r < rmax) ? Vec4<T>::load1(base, r * ld + i) : 0.f;
     }
   }
 }
@@ -135,8 +147,10 @@ __device__ __forceinline__ void store_ic(float (*s)[ROWS + PAD], const float (&r
   }
 }
 
-template <bool A_RC, bool B_RC, bool VEC>
+template <bool A_RC, bool B_RC, bool VEC, typename TA, typename TB, typename TC>
 __global__ void __launch_bounds__(kThreads, 2) gemm_kernel(GemmArgs g) {
+  const TA* gA = static_cast<const TA*>(g.A);
+  const TB* gB = static_cast<const TB*>(g.B);
   __shared__ __align__(16) float As[BR][BI + PAD];
   __shared__ __align__(16) float Bs[BR][BJ + PAD];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -152,8 +166,8 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_kernel(GemmArgs g) {
 
   float ra[BI / 16], rb[BJ / 16];
   auto gload = [&](int64_t r0) {
-    if (A_RC) load_rc<BI, VEC>(g.A, g.lda, i0, g.I, r0, rend, ra); else load_ic<BI, VEC>(g.A, g.lda, i0, g.I, r0, rend, ra);
-    if (B_RC) load_rc<BJ, VEC>(g.B, g.ldb, j0, g.J, r0, rend, rb); else load_ic<BJ, VEC>(g.B, g.ldb, j0, g.J, r0, rend, rb);
+    if (A_RC) load_rc<BI, VEC>(gA, g.lda, i0, g.I, r0, rend, ra); else load_ic<BI, VEC>(gA, g.lda, i0, g.I, r0, rend, ra);
+    if (B_RC) load_rc<BJ, VEC>(gB, g.ldb, j0, g.J, r0, rend, rb); else load_ic<BJ, VEC>(gB, g.ldb, j0, g.J, r0, rend, rb);
   };
   auto sstore = [&]() {
     if (A_RC) store_rc<BI, VEC>(As, ra); else store_ic<BI, VEC>(As, ra);
@@ -180,8 +194,34 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_kernel(GemmArgs g) {
     __syncthreads();
   }
 
-  float* C = g.C + int64_t(blockIdx.z) * g.split_stride;
+  TC* C = static_cast<TC*>(g.C) + int64_t(blockIdx.z) * g.split_stride;
   const bool split = g.split_stride != 0;
+  if (g.alpha.a_src) {
+    // a_src[i, head] = <acc row i, att_src> over the head's columns: chan % 4 == 0 and chan | BJ, so the chan / 4 threads
+    // that hold a head's columns of a row are adjacent lanes of one 16-lane half warp (xor shuffles stay inside it)
+    const int lanes = g.alpha.chan >> 2;
+    const int64_t j = j0 + tx * TJ;
+    float4 as4 = f4_zero(), ad4 = f4_zero();
+    if (j < g.J) {
+      as4 = __ldg(reinterpret_cast<const float4*>(g.alpha.att_src + j));
+      ad4 = __ldg(reinterpret_cast<const float4*>(g.alpha.att_dst + j));
+    }
+#pragma unroll
+    for (int a = 0; a < TI; ++a) {
+      float s = fmaf(acc[a][0], as4.x, fmaf(acc[a][1], as4.y, fmaf(acc[a][2], as4.z, acc[a][3] * as4.w)));
+      float d = fmaf(acc[a][0], ad4.x, fmaf(acc[a][1], ad4.y, fmaf(acc[a][2], ad4.z, acc[a][3] * ad4.w)));
+      for (int off = 1; off < lanes; off <<= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, off);
+        d += __shfl_xor_sync(0xffffffffu, d, off);
+      }
+      const int64_t i = i0 + ty * TI + a;
+      if ((tx & (lanes - 1)) == 0 && i < g.I && j < g.J) {
+        const int head = int(j) / g.alpha.chan;
+        g.alpha.a_src[i * g.alpha.heads + head] = s;
+        g.alpha.a_dst[i * g.alpha.heads + head] = d;
+      }
+    }
+  }
 #pragma unroll
   for (int a = 0; a < TI; ++a) {
     const int64_t i = i0 + ty * TI + a;
@@ -192,15 +232,15 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_kernel(GemmArgs g) {
       const int64_t j = j0 + tx * TJ + b;
       if (j >= g.J) continue;
       float v = acc[a][b];
-      float* dst = C + i * g.sCi + j * g.sCj;
+      const int64_t at = i * g.sCi + j * g.sCj;
       if (!split) {
         v *= rs;
         if (g.bias) v += __ldg(g.bias + j);
-        if (g.accumulate) v += *dst;
+        if (g.accumulate) v += Vec4<TC>::load1(C, at);
         if (g.act == LGK_ACT_ELU) v = elu1(v);
         else if (g.act == LGK_ACT_RELU) v = fmaxf(v, 0.f);
       }
-      *dst = v;
+      Vec4<TC>::store1(C, at, v);
     }
   }
 }
@@ -224,8 +264,8 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
 // (deterministic, no atomics).  This replaced a generic split GEMM + a separate column-sum pass that together cost
 // ~50 us per layer on the headline batch.
 constexpr int kSlabChunk = 32;
-template <int KB, int MB, bool VEC>  // 64-wide output blocks along k and m; VEC: 16-byte loads (K, M % 4 == 0, aligned)
-__global__ void __launch_bounds__(256) bwd_w_slab_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+template <int KB, int MB, bool VEC, typename T>  // 64-wide output blocks along k and m; VEC: 4-element loads (K, M % 4 == 0, aligned)
+__global__ void __launch_bounds__(256) bwd_w_slab_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                          float* __restrict__ partial, int64_t N, int K, int M,
                                                          int64_t slab_rows, int want_db) {
   extern __shared__ __align__(16) float sm[];
@@ -256,20 +296,20 @@ __global__ void __launch_bounds__(256) bwd_w_slab_kernel(const float* __restrict
     if (VEC) {
       for (int e = threadIdx.x; e < kSlabChunk * kp / 4; e += 256) {
         const int r = e / (kp / 4), c = (e - r * (kp / 4)) * 4;
-        reinterpret_cast<float4*>(xs)[e] = (r < rows && c < K) ? __ldg(reinterpret_cast<const float4*>(x + (c0 + r) * K + c)) : f4_zero();
+        reinterpret_cast<float4*>(xs)[e] = (r < rows && c < K) ? ld4<T>(x + (c0 + r) * K + c) : f4_zero();
       }
       for (int e = threadIdx.x; e < kSlabChunk * mp / 4; e += 256) {
         const int r = e / (mp / 4), c = (e - r * (mp / 4)) * 4;
-        reinterpret_cast<float4*>(ds)[e] = (r < rows && c < M) ? __ldg(reinterpret_cast<const float4*>(dy + (c0 + r) * M + c)) : f4_zero();
+        reinterpret_cast<float4*>(ds)[e] = (r < rows && c < M) ? ld4<T>(dy + (c0 + r) * M + c) : f4_zero();
       }
     } else {
       for (int e = threadIdx.x; e < kSlabChunk * kp; e += 256) {
         const int r = e / kp, c = e - r * kp;
-        xs[e] = (r < rows && c < K) ? __ldg(x + (c0 + r) * K + c) : 0.f;
+        xs[e] = (r < rows && c < K) ? Vec4<T>::load1(x, (c0 + r) * K + c) : 0.f;
       }
       for (int e = threadIdx.x; e < kSlabChunk * mp; e += 256) {
         const int r = e / mp, c = e - r * mp;
-        ds[e] = (r < rows && c < M) ? __ldg(dy + (c0 + r) * M + c) : 0.f;
+        ds[e] = (r < rows && c < M) ? Vec4<T>::load1(dy, (c0 + r) * M + c) : 0.f;
       }
     }
     __syncthreads();
@@ -327,12 +367,13 @@ __global__ void __launch_bounds__(256) bwd_w_slab_kernel(const float* __restrict
 
 // db[m] = sum_n dy[n,m] alone (bias gradients of the fused aggregation kernels): slab partials, same second stage.
 // Threads = (row lane, float4 column); M % 4 == 0 fast path, scalar otherwise.
-__global__ void __launch_bounds__(256) colsum_slab_kernel(const float* __restrict__ dy, float* __restrict__ partial,
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_slab_kernel(const T* __restrict__ dy, float* __restrict__ partial,
                                                           int64_t N, int M, int64_t slab_rows) {
   __shared__ float red[256 * 4];
   const int64_t r0 = int64_t(blockIdx.x) * slab_rows, r1 = min(N, r0 + slab_rows);
   float* p = partial + int64_t(blockIdx.x) * M;
-  const bool vec = (M & 3) == 0 && ((reinterpret_cast<uintptr_t>(dy) & 15) == 0);
+  const bool vec = (M & 3) == 0 && ((reinterpret_cast<uintptr_t>(dy) & (4 * sizeof(T) - 1)) == 0);
   const int cols = vec ? M / 4 : M;  // column groups
   for (int c0 = 0; c0 < cols; c0 += 256) {
     const int width = min(256, cols - c0);   // column groups handled in this pass
@@ -342,11 +383,11 @@ __global__ void __launch_bounds__(256) colsum_slab_kernel(const float* __restric
     if (rl < lanes) {
       if (vec) {
         for (int64_t r = r0 + rl; r < r1; r += lanes) {
-          const float4 v = __ldg(reinterpret_cast<const float4*>(dy + r * M) + c0 + c);
+          const float4 v = ld4<T>(dy + r * M + 4 * (c0 + c));
           acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
         }
       } else {
-        for (int64_t r = r0 + rl; r < r1; r += lanes) acc.x += __ldg(dy + r * M + c0 + c);
+        for (int64_t r = r0 + rl; r < r1; r += lanes) acc.x += Vec4<T>::load1(dy, r * M + c0 + c);
       }
     }
     __syncthreads();
@@ -373,14 +414,16 @@ bool small_weight(int64_t k, int64_t m) { return k <= 128 && m <= 128; }
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <bool A_RC, bool B_RC>
+template <bool A_RC, bool B_RC, typename TA, typename TB, typename TC>
 int launch_gemm(const GemmArgs& g, int splits, bool vec, cudaStream_t stream, const char* name) {
   dim3 grid(unsigned(ceil_div(g.I, BI)), unsigned(ceil_div(g.J, BJ)), unsigned(splits));
-  if (vec) gemm_kernel<A_RC, B_RC, true><<<grid, kThreads, 0, stream>>>(g);
-  else gemm_kernel<A_RC, B_RC, false><<<grid, kThreads, 0, stream>>>(g);
+  if (vec) gemm_kernel<A_RC, B_RC, true, TA, TB, TC><<<grid, kThreads, 0, stream>>>(g);
+  else gemm_kernel<A_RC, B_RC, false, TA, TB, TC><<<grid, kThreads, 0, stream>>>(g);
   LGK_CHECK_LAUNCH(name);
   return LGK_OK;
 }
+using bf16 = __nv_bfloat16;
+bool known_dtype(int dtype) { return dtype == LGK_F32 || dtype == LGK_BF16; }
 
 // LGK_GRAD_W_TC=0 keeps the weight gradient of wide transforms on the FFMA split GEMM (profiling only)
 bool use_grad_w_tc() {
@@ -409,10 +452,10 @@ extern "C" int lgk_linear_fwd(const void* x, const float* weight, const float* b
                               int64_t n, int64_t k, int64_t m, int act, int accumulate, int dtype, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && k > 0 && m > 0, LGK_ERR_BAD_ARG, "lgk_linear_fwd: bad sizes");
-  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_fwd: only fp32 is implemented");
+  LGK_REQUIRE(known_dtype(dtype), LGK_ERR_UNSUPPORTED, "lgk_linear_fwd: dtype must be LGK_F32 or LGK_BF16");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(x && weight && out, LGK_ERR_BAD_ARG, "lgk_linear_fwd: null pointer");
-  if (use_tensor_cores(n, k)) {
+  if (dtype == LGK_F32 && use_tensor_cores(n, k)) {
     bool done = false;
     if ((k & 3) == 0) {  // aligned rows: tensor-map TMA feeds the tensor core
       if (int rc = launch_linear_tma(static_cast<const float*>(x), weight, bias, rowscale, static_cast<float*>(out), n, k, m,
@@ -424,26 +467,70 @@ extern "C" int lgk_linear_fwd(const void* x, const float* weight, const float* b
                             accumulate, stream);
   }
   GemmArgs g{};
-  g.A = static_cast<const float*>(x); g.B = weight; g.C = static_cast<float*>(out);
+  g.A = x; g.B = weight; g.C = out;
   g.I = n; g.J = m; g.R = k; g.lda = k; g.ldb = k; g.sCi = m; g.sCj = 1;
   g.bias = bias; g.rowscale = rowscale; g.act = act; g.accumulate = accumulate; g.r_chunk = k; g.split_stride = 0;
   const bool vec = (k % 4 == 0) && aligned16(x) && aligned16(weight);
-  return launch_gemm<true, true>(g, 1, vec, stream, "gemm_kernel(fwd)");
+  if (dtype == LGK_BF16) return launch_gemm<true, true, bf16, float, bf16>(g, 1, vec, stream, "gemm_kernel(fwd,bf16)");
+  return launch_gemm<true, true, float, float, float>(g, 1, vec, stream, "gemm_kernel(fwd)");
+}
+
+extern "C" int lgk_gat_alpha(const void* h, const float* att_src, const float* att_dst, float* a_src, float* a_dst, int64_t N, int H,
+                             int C, int dtype, void* stream_);
+
+// 1 when lgk_linear_gat_fwd forms the logit halves in the transform's epilogue (from the fp32 accumulators) for this shape
+extern "C" int lgk_linear_gat_fused(int64_t n, int64_t k, int heads, int chan, int dtype) {
+  if (n <= 0 || k <= 0 || heads <= 0 || chan <= 0) return 0;
+  if (dtype == LGK_F32 && use_tensor_cores(n, k))
+    return (k & 3) == 0 && chan >= 16 && chan <= 64 && 64 % chan == 0 && n < (int64_t(1) << 31);
+  return chan % 4 == 0 && BJ % chan == 0;
+}
+
+extern "C" int lgk_linear_gat_fwd(const void* x, const float* weight, const float* att_src, const float* att_dst, void* out,
+                                  float* a_src, float* a_dst, int64_t n, int64_t k, int heads, int chan, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int64_t m = int64_t(heads) * chan;
+  LGK_REQUIRE(n >= 0 && k > 0 && heads > 0 && chan > 0, LGK_ERR_BAD_ARG, "lgk_linear_gat_fwd: bad sizes");
+  LGK_REQUIRE(known_dtype(dtype), LGK_ERR_UNSUPPORTED, "lgk_linear_gat_fwd: dtype must be LGK_F32 or LGK_BF16");
+  if (n == 0) return LGK_OK;
+  LGK_REQUIRE(x && weight && att_src && att_dst && out && a_src && a_dst, LGK_ERR_BAD_ARG, "lgk_linear_gat_fwd: null pointer");
+  GatAlpha alpha{att_src, att_dst, a_src, a_dst, heads, chan};
+  const bool att_aligned = aligned16(att_src) && aligned16(att_dst);
+  if (dtype == LGK_F32 && use_tensor_cores(n, k) && (k & 3) == 0 && att_aligned) {
+    bool done = false;
+    if (int rc = launch_linear_tma(static_cast<const float*>(x), weight, nullptr, nullptr, static_cast<float*>(out), n, k, m,
+                                   LGK_ACT_NONE, 0, stream, &done, &alpha))
+      return rc;
+    if (done) return LGK_OK;
+  }
+  const bool fuse = (chan % 4 == 0) && (BJ % chan == 0) && att_aligned && !(dtype == LGK_F32 && use_tensor_cores(n, k));
+  if (!fuse) {  // head widths the epilogues do not cover: the transform, then the logit halves from the stored h
+    if (int rc = lgk_linear_fwd(x, weight, nullptr, nullptr, out, n, k, m, LGK_ACT_NONE, 0, dtype, stream_)) return rc;
+    return lgk_gat_alpha(out, att_src, att_dst, a_src, a_dst, n, heads, chan, dtype, stream_);
+  }
+  GemmArgs g{};
+  g.A = x; g.B = weight; g.C = out;
+  g.I = n; g.J = m; g.R = k; g.lda = k; g.ldb = k; g.sCi = m; g.sCj = 1;
+  g.act = LGK_ACT_NONE; g.r_chunk = k; g.split_stride = 0; g.alpha = alpha;
+  const bool vec = (k % 4 == 0) && aligned16(x) && aligned16(weight);
+  if (dtype == LGK_BF16) return launch_gemm<true, true, bf16, float, bf16>(g, 1, vec, stream, "gemm_kernel(gat fwd,bf16)");
+  return launch_gemm<true, true, float, float, float>(g, 1, vec, stream, "gemm_kernel(gat fwd)");
 }
 
 extern "C" int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, int64_t n, int64_t k, int64_t m,
                                 int accumulate, int dtype, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && k > 0 && m > 0, LGK_ERR_BAD_ARG, "lgk_linear_bwd_x: bad sizes");
-  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_bwd_x: only fp32 is implemented");
+  LGK_REQUIRE(known_dtype(dtype), LGK_ERR_UNSUPPORTED, "lgk_linear_bwd_x: dtype must be LGK_F32 or LGK_BF16");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(dy && weight && dx, LGK_ERR_BAD_ARG, "lgk_linear_bwd_x: null pointer");
   GemmArgs g{};
-  g.A = static_cast<const float*>(dy); g.B = weight; g.C = static_cast<float*>(dx);
+  g.A = dy; g.B = weight; g.C = dx;
   g.I = n; g.J = k; g.R = m; g.lda = m; g.ldb = k; g.sCi = k; g.sCj = 1;
   g.accumulate = accumulate; g.r_chunk = m; g.split_stride = 0;
   const bool vec = (m % 4 == 0) && (k % 4 == 0) && aligned16(dy) && aligned16(weight);
-  return launch_gemm<true, false>(g, 1, vec, stream, "gemm_kernel(bwd_x)");
+  if (dtype == LGK_BF16) return launch_gemm<true, false, bf16, float, bf16>(g, 1, vec, stream, "gemm_kernel(bwd_x,bf16)");
+  return launch_gemm<true, false, float, float, float>(g, 1, vec, stream, "gemm_kernel(bwd_x)");
 }
 
 extern "C" int64_t lgk_linear_bwd_w_workspace_bytes(int64_t n, int64_t k, int64_t m) {
@@ -458,7 +545,8 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
                                 int accumulate, void* workspace, int64_t workspace_bytes, int dtype, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && k > 0 && m > 0, LGK_ERR_BAD_ARG, "lgk_linear_bwd_w: bad sizes");
-  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_linear_bwd_w: only fp32 is implemented");
+  LGK_REQUIRE(known_dtype(dtype), LGK_ERR_UNSUPPORTED, "lgk_linear_bwd_w: dtype must be LGK_F32 or LGK_BF16");
+  const bool is_bf16 = dtype == LGK_BF16;
   LGK_REQUIRE(dw || db, LGK_ERR_BAD_ARG, "lgk_linear_bwd_w: nothing to compute");
   if (n == 0) {
     if (!accumulate) {
@@ -477,8 +565,10 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
   const float* dyf = static_cast<const float*>(dy);
   float* partial = static_cast<float*>(workspace);
 
+  const bf16* dyh = static_cast<const bf16*>(dy);
   if (!dw) {  // bias gradient only
-    colsum_slab_kernel<<<slabs, 256, 0, stream>>>(dyf, partial, n, int(m), slab_rows);
+    if (is_bf16) colsum_slab_kernel<bf16><<<slabs, 256, 0, stream>>>(dyh, partial, n, int(m), slab_rows);
+    else colsum_slab_kernel<float><<<slabs, 256, 0, stream>>>(dyf, partial, n, int(m), slab_rows);
     LGK_CHECK_LAUNCH("colsum_slab_kernel");
     slab_reduce_kernel<<<slab_reduce_grid(m), 256, 0, stream>>>(partial, nullptr, db, 0, m, slabs, accumulate);
     LGK_CHECK_LAUNCH("slab_reduce_kernel(db)");
@@ -489,11 +579,18 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
     const int kb = int(ceil_div(k, 64)), mb = int(ceil_div(m, 64));
     const size_t smem = size_t(kSlabChunk) * (kb + mb) * 64 * sizeof(float);
     const float* xf = static_cast<const float*>(x);
+    const bf16* xh = static_cast<const bf16*>(x);
     const bool vec = (k % 4 == 0) && (m % 4 == 0) && aligned16(x) && aligned16(dy);
-#define LGK_SLAB(KB, MB)                                                                                                       \
-  do {                                                                                                                         \
-    if (vec) bwd_w_slab_kernel<KB, MB, true><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, db != nullptr); \
-    else bwd_w_slab_kernel<KB, MB, false><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, db != nullptr);    \
+    const int wdb = db != nullptr;
+#define LGK_SLAB(KB, MB)                                                                                                              \
+  do {                                                                                                                                \
+    if (is_bf16) {                                                                                                                    \
+      if (vec) bwd_w_slab_kernel<KB, MB, true, bf16><<<slabs, 256, smem, stream>>>(dyh, xh, partial, n, int(k), int(m), slab_rows, wdb);  \
+      else bwd_w_slab_kernel<KB, MB, false, bf16><<<slabs, 256, smem, stream>>>(dyh, xh, partial, n, int(k), int(m), slab_rows, wdb);     \
+    } else {                                                                                                                          \
+      if (vec) bwd_w_slab_kernel<KB, MB, true, float><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, wdb); \
+      else bwd_w_slab_kernel<KB, MB, false, float><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, wdb);    \
+    }                                                                                                                                 \
   } while (0)
     if (kb == 1 && mb == 1) LGK_SLAB(1, 1);
     else if (kb == 1) LGK_SLAB(1, 2);
@@ -507,12 +604,12 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
   }
 
   // wide weights (the 1025-wide in_proj): split GEMM over the rows + deterministic reduce, db from a slab pass
-  const int tc_slabs = use_grad_w_tc() ? grad_w_tc_slabs(n, k, m, nullptr) : 0;
+  const int tc_slabs = (use_grad_w_tc() && !is_bf16) ? grad_w_tc_slabs(n, k, m, nullptr) : 0;
   const int s = choose_wsplits(n, k, m);
   float* colpart = reinterpret_cast<float*>(static_cast<char*>(workspace) +
                                             align_up(int64_t(std::max(s, grad_w_tc_slabs(n, k, m, nullptr))) * (k * m + m) * 4, 256));
   GemmArgs g{};
-  g.A = static_cast<const float*>(x); g.B = dyf;
+  g.A = x; g.B = dy;
   g.I = k; g.J = m; g.R = n; g.lda = k; g.ldb = m; g.sCi = 1; g.sCj = k;  // C(i=k_idx, j=m_idx) -> dW[m*K + k]
   g.r_chunk = align_up(ceil_div(n, s), BR);
   const bool vec = (k % 4 == 0) && (m % 4 == 0) && aligned16(x) && aligned16(dy);
@@ -525,15 +622,20 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
     if (fuse_db) return LGK_OK;
   } else if (s == 1) {
     g.C = dw; g.split_stride = 0; g.accumulate = accumulate;
-    if (int rc = launch_gemm<false, false>(g, 1, vec, stream, "gemm_kernel(bwd_w)")) return rc;
+    if (int rc = is_bf16 ? launch_gemm<false, false, bf16, bf16, float>(g, 1, vec, stream, "gemm_kernel(bwd_w,bf16)")
+                         : launch_gemm<false, false, float, float, float>(g, 1, vec, stream, "gemm_kernel(bwd_w)"))
+      return rc;
   } else {
     g.C = partial; g.split_stride = k * m;
-    if (int rc = launch_gemm<false, false>(g, s, vec, stream, "gemm_kernel(bwd_w,split)")) return rc;
+    if (int rc = is_bf16 ? launch_gemm<false, false, bf16, bf16, float>(g, s, vec, stream, "gemm_kernel(bwd_w,split,bf16)")
+                         : launch_gemm<false, false, float, float, float>(g, s, vec, stream, "gemm_kernel(bwd_w,split)"))
+      return rc;
     splitk_reduce_kernel<<<unsigned(ceil_div(k * m, 256)), 256, 0, stream>>>(partial, dw, k * m, s, accumulate);
     LGK_CHECK_LAUNCH("splitk_reduce_kernel");
   }
   if (db) {
-    colsum_slab_kernel<<<slabs, 256, 0, stream>>>(dyf, colpart, n, int(m), slab_rows);
+    if (is_bf16) colsum_slab_kernel<bf16><<<slabs, 256, 0, stream>>>(dyh, colpart, n, int(m), slab_rows);
+    else colsum_slab_kernel<float><<<slabs, 256, 0, stream>>>(dyf, colpart, n, int(m), slab_rows);
     LGK_CHECK_LAUNCH("colsum_slab_kernel");
     slab_reduce_kernel<<<slab_reduce_grid(m), 256, 0, stream>>>(colpart, nullptr, db, 0, m, slabs, accumulate);
     LGK_CHECK_LAUNCH("slab_reduce_kernel(db)");

@@ -51,6 +51,13 @@ struct TcArgs {
   int64_t tiles_n;      // column tiles (fastest tile index)
   int64_t tiles_total;
   int debug;            // profiling only (LGK_TC_DEBUG bit mask): 1 = no MMAs, 2 = no split, 4 = no TMA loads
+  // GATConv.lin: the attention logit halves a_src[n, H] = <h[n, h, :], att_src[h, :]> (and a_dst) from the fp32
+  // accumulators, in the epilogue -- no separate pass over h.  chan divides BN, so a tile holds whole heads.
+  const float* att_src;
+  const float* att_dst;
+  float* a_src;
+  float* a_dst;
+  int heads, chan;
 };
 
 struct Bars {
@@ -102,6 +109,7 @@ __device__ __forceinline__ void epilogue_tile(const TcArgs& g, uint32_t tmem_acc
                                               int64_t j0) {
   const int64_t i = i0 + warp * 32 + lane;
   const float rs = (g.rowscale && i < g.n) ? __ldg(g.rowscale + i) : 1.f;
+  float as_acc = 0.f, ad_acc = 0.f;
 #pragma unroll 1
   for (int c = 0; c < BN / 16; ++c) {
     float v[16];
@@ -113,6 +121,22 @@ __device__ __forceinline__ void epilogue_tile(const TcArgs& g, uint32_t tmem_acc
       for (int t = 0; t < 16; ++t) v[t] += u[t];
     }
     if (i >= g.n) continue;
+    if (g.a_src) {  // chan = 16, 32 or 64: heads never straddle a tile or split a 16-column chunk; m = heads * chan
+      const int jc = int(j0) + c * 16;
+      if (jc < g.m) {
+        if (jc % g.chan == 0) { as_acc = 0.f; ad_acc = 0.f; }
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+          as_acc = fmaf(v[t], __ldg(g.att_src + jc + t), as_acc);
+          ad_acc = fmaf(v[t], __ldg(g.att_dst + jc + t), ad_acc);
+        }
+        if ((jc + 16) % g.chan == 0) {
+          const int head = jc / g.chan;
+          g.a_src[i * g.heads + head] = as_acc;
+          g.a_dst[i * g.heads + head] = ad_acc;
+        }
+      }
+    }
     float* dst = g.out + i * g.m + j0 + c * 16;
     if (j0 + c * 16 + 16 <= g.m && (g.m & 3) == 0) {
 #pragma unroll
@@ -322,8 +346,10 @@ bool make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t k, int 
 // Used by lgk_linear_fwd (linear.cu).  *done = false when the shape / alignment is not eligible (the caller then takes
 // another kernel).
 int launch_linear_tma(const float* x, const float* w, const float* bias, const float* rowscale, float* out, int64_t n,
-                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream, bool* done) {
+                      int64_t k, int64_t m, int act, int accumulate, cudaStream_t stream, bool* done, const GatAlpha* alpha) {
   *done = false;
+  if (alpha && (alpha->chan < 16 || alpha->chan > BN || BN % alpha->chan != 0 || int64_t(alpha->heads) * alpha->chan != m))
+    return LGK_OK;
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(out) |
                          reinterpret_cast<uintptr_t>(bias)) & 15) == 0;
   if (!aligned || (k & 3) || n >= (int64_t(1) << 31) || k >= (int64_t(1) << 31)) return LGK_OK;
@@ -342,7 +368,11 @@ int launch_linear_tma(const float* x, const float* w, const float* bias, const f
   }
   CUtensorMap map_x, map_w;
   if (!make_map(&map_x, x, n, k, BM) || !make_map(&map_w, w, m, k, BN)) return LGK_OK;
-  TcArgs g{bias, rowscale, out, n, k, m, act, accumulate, 0, 0, 0};
+  TcArgs g{bias, rowscale, out, n, k, m, act, accumulate, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, 0, 0};
+  if (alpha) {
+    g.att_src = alpha->att_src; g.att_dst = alpha->att_dst; g.a_src = alpha->a_src; g.a_dst = alpha->a_dst;
+    g.heads = alpha->heads; g.chan = alpha->chan;
+  }
   static const int debug = [] { const char* v = getenv("LGK_TC_DEBUG"); return (v && *v) ? atoi(v) : 0; }();
   g.debug = debug;
   g.tiles_n = ceil_div(m, BN);

@@ -45,9 +45,18 @@ __device__ __forceinline__ float act_grad(float z, int act) {
   return 1.f;
 }
 
+// activations are float or bf16 (statistics, parameters and every accumulator fp32)
+template <typename T>
+__device__ __forceinline__ float ldx(const T* p, int64_t i);
+template <>
+__device__ __forceinline__ float ldx<float>(const float* p, int64_t i) { return ld_stream_f32(p + i); }
+template <>
+__device__ __forceinline__ float ldx<__nv_bfloat16>(const __nv_bfloat16* p, int64_t i) { return __bfloat162float(p[i]); }
+
 // ---- pass 1: per-slab column statistics around the slab's first row ------------------------------------------
 // partial[slab][0][c] = sum (x - K_c), partial[slab][1][c] = sum (x - K_c)^2, partial[slab][2][c] = K_c
-__global__ void __launch_bounds__(kThreads) bn_stats_partial_kernel(const float* __restrict__ x, float* __restrict__ partial,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_stats_partial_kernel(const T* __restrict__ x, float* __restrict__ partial,
                                                                     int64_t n, int d, int64_t slab_rows) {
   __shared__ float red[2][kThreads];
   const int64_t r0 = int64_t(blockIdx.x) * slab_rows, r1 = min(n, r0 + slab_rows);
@@ -57,10 +66,10 @@ __global__ void __launch_bounds__(kThreads) bn_stats_partial_kernel(const float*
     const int lanes = kThreads / width;  // row lanes per column
     const int c = threadIdx.x % width, rl = threadIdx.x / width;
     float s = 0.f, q = 0.f;
-    const float K = (r0 < r1) ? __ldg(x + r0 * d + c0 + c) : 0.f;
+    const float K = (r0 < r1) ? ldx(x, r0 * d + c0 + c) : 0.f;
     if (rl < lanes) {
       for (int64_t r = r0 + rl; r < r1; r += lanes) {
-        const float v = ld_stream_f32(x + r * d + c0 + c) - K;
+        const float v = ldx(x, r * d + c0 + c) - K;
         s += v;
         q = fmaf(v, v, q);
       }
@@ -117,22 +126,24 @@ __global__ void __launch_bounds__(kThreads) bn_eval_stats_kernel(const float* __
 }
 
 // ---- pass 3: y = dropout(act((x - mean) * invstd * w + b)) --------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) bn_act_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_act_fwd_kernel(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                                                               const float* __restrict__ mean, const float* __restrict__ invstd,
-                                                              float* __restrict__ y, int64_t total, int d, int act, float drop_p, uint64_t seed,
+                                                              T* __restrict__ y, int64_t total, int d, int act, float drop_p, uint64_t seed,
                                                               const int64_t* __restrict__ seed_dev) {
   const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
   if (i >= total) return;
   const int c = int(i % d);
   const float scale = __ldg(invstd + c) * (w ? __ldg(w + c) : 1.f);
   const float shift = (b ? __ldg(b + c) : 0.f) - __ldg(mean + c) * scale;
-  float v = act_fwd(fmaf(ld_stream_f32(x + i), scale, shift), act);
+  float v = act_fwd(fmaf(ldx(x, i), scale, shift), act);
   if (drop_p > 0.f) v = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : v * (1.f / (1.f - drop_p));
-  y[i] = v;
+  Vec4<T>::store1(y, i, v);
 }
 
 // ---- backward pass 1: per-slab sums of g and g * xhat, g = dy * keep * act'(z) ------------------------------------
-__global__ void __launch_bounds__(kThreads) bn_bwd_partial_kernel(const float* __restrict__ x, const float* __restrict__ dy, const float* __restrict__ w,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_bwd_partial_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ w,
                                                                   const float* __restrict__ b, const float* __restrict__ mean,
                                                                   const float* __restrict__ invstd, float* __restrict__ partial, int64_t n,
                                                                   int d, int64_t slab_rows, int act, float drop_p, uint64_t seed,
@@ -152,8 +163,8 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_partial_kernel(const float* _
     if (rl < lanes) {
       for (int64_t r = r0 + rl; r < r1; r += lanes) {
         const int64_t i = r * d + c0 + c;
-        const float xh = (ld_stream_f32(x + i) - m) * is;
-        float g = ld_stream_f32(dy + i) * act_grad(fmaf(xh, wc, bc), act);
+        const float xh = (ldx(x, i) - m) * is;
+        float g = ldx(dy, i) * act_grad(fmaf(xh, wc, bc), act);
         if (drop_p > 0.f) g = uniform_hash64(sd, uint64_t(i)) < drop_p ? 0.f : g * keep;
         sg += g;
         sgx = fmaf(g, xh, sgx);
@@ -173,18 +184,19 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_partial_kernel(const float* _
 
 // ---- backward pass 3: dx (training: batch statistics take part in the gradient; eval: plain scale) ----------------
 // sums[0..d) = sum g, sums[d..2d) = sum g * xhat.  Block 0 also adds them into the parameter gradients when asked to.
-__global__ void __launch_bounds__(kThreads) bn_bwd_dx_kernel(const float* __restrict__ x, const float* __restrict__ dy, const float* __restrict__ w,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_bwd_dx_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ w,
                                                              const float* __restrict__ b, const float* __restrict__ mean,
                                                              const float* __restrict__ invstd, const float* __restrict__ sums,
-                                                             float* __restrict__ dx, int64_t n, int d, int training, int act, float drop_p,
+                                                             T* __restrict__ dx, int64_t n, int d, int training, int act, float drop_p,
                                                              uint64_t seed, const int64_t* __restrict__ seed_dev) {
   const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
   if (i >= n * d) return;
   const int c = int(i % d);
   const float m = __ldg(mean + c), is = __ldg(invstd + c);
   const float wc = w ? __ldg(w + c) : 1.f, bc = b ? __ldg(b + c) : 0.f;
-  const float xh = (ld_stream_f32(x + i) - m) * is;
-  float g = ld_stream_f32(dy + i) * act_grad(fmaf(xh, wc, bc), act);
+  const float xh = (ldx(x, i) - m) * is;
+  float g = ldx(dy, i) * act_grad(fmaf(xh, wc, bc), act);
   if (drop_p > 0.f) g = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : g * (1.f / (1.f - drop_p));
   float r;
   if (training) {
@@ -193,27 +205,29 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_dx_kernel(const float* __rest
   } else {
     r = g * wc * is;
   }
-  dx[i] = r;
+  Vec4<T>::store1(dx, i, r);
 }
 
 // ---- activation + dropout (the ELU and Dropout after every GIN layer, gin.py:31-32) -------------------------------
-__global__ void __launch_bounds__(kThreads) act_dropout_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t total, int act,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) act_dropout_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t total, int act,
                                                                    float drop_p, uint64_t seed, const int64_t* __restrict__ seed_dev) {
   const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
   if (i >= total) return;
-  float v = act_fwd(ld_stream_f32(x + i), act);
+  float v = act_fwd(ldx(x, i), act);
   if (drop_p > 0.f) v = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : v * (1.f / (1.f - drop_p));
-  y[i] = v;
+  Vec4<T>::store1(y, i, v);
 }
 // dx = dy * keep * act'(x): x is the pre-activation input
-__global__ void __launch_bounds__(kThreads) act_dropout_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dx,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) act_dropout_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __restrict__ dx,
                                                                    int64_t total, int act, float drop_p, uint64_t seed,
                                                                    const int64_t* __restrict__ seed_dev) {
   const int64_t i = int64_t(blockIdx.x) * kThreads + threadIdx.x;
   if (i >= total) return;
-  float g = ld_stream_f32(dy + i) * act_grad(ld_stream_f32(x + i), act);
+  float g = ldx(dy, i) * act_grad(ldx(x, i), act);
   if (drop_p > 0.f) g = uniform_hash64(launch_seed(seed, seed_dev), uint64_t(i)) < drop_p ? 0.f : g * (1.f / (1.f - drop_p));
-  dx[i] = g;
+  Vec4<T>::store1(dx, i, g);
 }
 
 }  // namespace
@@ -226,12 +240,15 @@ extern "C" int64_t lgk_bn_workspace_bytes(int64_t n, int64_t d) {
   return (int64_t(norm_slabs(n)) * 3 * d + 2 * d) * 4;
 }
 
-extern "C" int lgk_bn_act_fwd(const float* x, const float* weight, const float* bias, float* running_mean, float* running_var,
-                              int64_t* num_batches_tracked, float* y, float* save_mean, float* save_invstd, int64_t n, int64_t d,
+extern "C" int lgk_bn_act_fwd(const void* x, const float* weight, const float* bias, float* running_mean, float* running_var,
+                              int64_t* num_batches_tracked, void* y, float* save_mean, float* save_invstd, int64_t n, int64_t d,
                               float eps, float momentum, int training, int act, float dropout_p, uint64_t seed,
-                              const int64_t* seed_dev, void* workspace, int64_t workspace_bytes, void* stream_) {
+                              const int64_t* seed_dev, void* workspace, int64_t workspace_bytes, int dtype, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && d > 0 && d < (1 << 24), LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: bad sizes");
+  LGK_REQUIRE(dtype == LGK_F32 || dtype == LGK_BF16, LGK_ERR_UNSUPPORTED, "lgk_bn_act_fwd: dtype must be LGK_F32 or LGK_BF16");
+  const bool h = dtype == LGK_BF16;
+  using bf16 = __nv_bfloat16;
   LGK_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: dropout must be in [0,1)");
   LGK_REQUIRE(act >= LGK_ACT_NONE && act <= LGK_ACT_RELU, LGK_ERR_BAD_ARG, "lgk_bn_act_fwd: bad activation");
   if (n == 0) return LGK_OK;
@@ -242,7 +259,8 @@ extern "C" int lgk_bn_act_fwd(const float* x, const float* weight, const float* 
     const int slabs = norm_slabs(n);
     const int64_t slab_rows = ceil_div(n, slabs);
     float* partial = static_cast<float*>(workspace);
-    bn_stats_partial_kernel<<<slabs, kThreads, 0, stream>>>(x, partial, n, int(d), slab_rows);
+    if (h) bn_stats_partial_kernel<bf16><<<slabs, kThreads, 0, stream>>>(static_cast<const bf16*>(x), partial, n, int(d), slab_rows);
+    else bn_stats_partial_kernel<float><<<slabs, kThreads, 0, stream>>>(static_cast<const float*>(x), partial, n, int(d), slab_rows);
     LGK_CHECK_LAUNCH("bn_stats_partial_kernel");
     bn_stats_finalize_kernel<<<unsigned(std::min<int64_t>(ceil_div(d, kThreads), 64)), kThreads, 0, stream>>>(
         partial, slabs, n, int(d), slab_rows, eps, momentum, save_mean, save_invstd, running_mean, running_var, num_batches_tracked);
@@ -252,18 +270,24 @@ extern "C" int lgk_bn_act_fwd(const float* x, const float* weight, const float* 
     bn_eval_stats_kernel<<<unsigned(ceil_div(d, kThreads)), kThreads, 0, stream>>>(running_mean, running_var, eps, int(d), save_mean, save_invstd);
     LGK_CHECK_LAUNCH("bn_eval_stats_kernel");
   }
-  bn_act_fwd_kernel<<<unsigned(ceil_div(n * d, kThreads)), kThreads, 0, stream>>>(x, weight, bias, save_mean, save_invstd, y, n * d, int(d), act,
-                                                                                  dropout_p, seed, seed_dev);
+  const unsigned grid = unsigned(ceil_div(n * d, kThreads));
+  if (h) bn_act_fwd_kernel<bf16><<<grid, kThreads, 0, stream>>>(static_cast<const bf16*>(x), weight, bias, save_mean, save_invstd,
+                                                               static_cast<bf16*>(y), n * d, int(d), act, dropout_p, seed, seed_dev);
+  else bn_act_fwd_kernel<float><<<grid, kThreads, 0, stream>>>(static_cast<const float*>(x), weight, bias, save_mean, save_invstd,
+                                                              static_cast<float*>(y), n * d, int(d), act, dropout_p, seed, seed_dev);
   LGK_CHECK_LAUNCH("bn_act_fwd_kernel");
   return LGK_OK;
 }
 
-extern "C" int lgk_bn_act_bwd(const float* x, const float* dy, const float* weight, const float* bias, const float* save_mean,
-                              const float* save_invstd, float* dx, float* dweight, float* dbias, int accumulate, int64_t n,
+extern "C" int lgk_bn_act_bwd(const void* x, const void* dy, const float* weight, const float* bias, const float* save_mean,
+                              const float* save_invstd, void* dx, float* dweight, float* dbias, int accumulate, int64_t n,
                               int64_t d, int training, int act, float dropout_p, uint64_t seed, const int64_t* seed_dev,
-                              void* workspace, int64_t workspace_bytes, void* stream_) {
+                              void* workspace, int64_t workspace_bytes, int dtype, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && d > 0 && d < (1 << 24), LGK_ERR_BAD_ARG, "lgk_bn_act_bwd: bad sizes");
+  LGK_REQUIRE(dtype == LGK_F32 || dtype == LGK_BF16, LGK_ERR_UNSUPPORTED, "lgk_bn_act_bwd: dtype must be LGK_F32 or LGK_BF16");
+  const bool h = dtype == LGK_BF16;
+  using bf16 = __nv_bfloat16;
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(x && dy && save_mean && save_invstd && dx, LGK_ERR_BAD_ARG, "lgk_bn_act_bwd: null pointer");
   LGK_REQUIRE(workspace && workspace_bytes >= lgk_bn_workspace_bytes(n, d), LGK_ERR_WORKSPACE, "lgk_bn_act_bwd: workspace too small");
@@ -271,8 +295,12 @@ extern "C" int lgk_bn_act_bwd(const float* x, const float* dy, const float* weig
   const int64_t slab_rows = ceil_div(n, slabs);
   float* partial = static_cast<float*>(workspace);
   float* sums = partial + int64_t(slabs) * 3 * d;  // [2 d]: sum g, sum g xhat
-  bn_bwd_partial_kernel<<<slabs, kThreads, 0, stream>>>(x, dy, weight, bias, save_mean, save_invstd, partial, n, int(d), slab_rows, act,
-                                                        dropout_p, seed, seed_dev);
+  if (h) bn_bwd_partial_kernel<bf16><<<slabs, kThreads, 0, stream>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(dy), weight, bias,
+                                                                    save_mean, save_invstd, partial, n, int(d), slab_rows, act, dropout_p, seed,
+                                                                    seed_dev);
+  else bn_bwd_partial_kernel<float><<<slabs, kThreads, 0, stream>>>(static_cast<const float*>(x), static_cast<const float*>(dy), weight, bias,
+                                                                   save_mean, save_invstd, partial, n, int(d), slab_rows, act, dropout_p, seed,
+                                                                   seed_dev);
   LGK_CHECK_LAUNCH("bn_bwd_partial_kernel");
   slab_reduce_kernel<<<slab_reduce_grid(2 * d), 256, 0, stream>>>(partial, sums, sums + d, d, d, slabs, 0);
   LGK_CHECK_LAUNCH("slab_reduce_kernel(bn)");
@@ -280,30 +308,47 @@ extern "C" int lgk_bn_act_bwd(const float* x, const float* dy, const float* weig
     slab_reduce_kernel<<<slab_reduce_grid(2 * d), 256, 0, stream>>>(partial, dbias, dweight, d, d, slabs, accumulate);
     LGK_CHECK_LAUNCH("slab_reduce_kernel(bn params)");
   }
-  bn_bwd_dx_kernel<<<unsigned(ceil_div(n * d, kThreads)), kThreads, 0, stream>>>(x, dy, weight, bias, save_mean, save_invstd, sums, dx, n, int(d),
-                                                                                 training, act, dropout_p, seed, seed_dev);
+  const unsigned grid = unsigned(ceil_div(n * d, kThreads));
+  if (h) bn_bwd_dx_kernel<bf16><<<grid, kThreads, 0, stream>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(dy), weight, bias, save_mean,
+                                                              save_invstd, sums, static_cast<bf16*>(dx), n, int(d), training, act, dropout_p,
+                                                              seed, seed_dev);
+  else bn_bwd_dx_kernel<float><<<grid, kThreads, 0, stream>>>(static_cast<const float*>(x), static_cast<const float*>(dy), weight, bias, save_mean,
+                                                             save_invstd, sums, static_cast<float*>(dx), n, int(d), training, act, dropout_p,
+                                                             seed, seed_dev);
   LGK_CHECK_LAUNCH("bn_bwd_dx_kernel");
   return LGK_OK;
 }
 
-extern "C" int lgk_act_dropout_fwd(const float* x, float* y, int64_t n, int act, float dropout_p, uint64_t seed,
-                                   const int64_t* seed_dev, void* stream_) {
+extern "C" int lgk_act_dropout_fwd(const void* x, void* y, int64_t n, int act, float dropout_p, uint64_t seed,
+                                   const int64_t* seed_dev, int dtype, void* stream_) {
+  using bf16 = __nv_bfloat16;
+  LGK_REQUIRE(dtype == LGK_F32 || dtype == LGK_BF16, LGK_ERR_UNSUPPORTED, "lgk_act_dropout_fwd: dtype must be LGK_F32 or LGK_BF16");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_act_dropout_fwd: bad arguments");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(x && y, LGK_ERR_BAD_ARG, "lgk_act_dropout_fwd: null pointer");
-  act_dropout_fwd_kernel<<<unsigned(ceil_div(n, kThreads)), kThreads, 0, stream>>>(x, y, n, act, dropout_p, seed, seed_dev);
+  const unsigned grid = unsigned(ceil_div(n, kThreads));
+  if (dtype == LGK_BF16) act_dropout_fwd_kernel<bf16><<<grid, kThreads, 0, stream>>>(static_cast<const bf16*>(x), static_cast<bf16*>(y), n, act,
+                                                                                    dropout_p, seed, seed_dev);
+  else act_dropout_fwd_kernel<float><<<grid, kThreads, 0, stream>>>(static_cast<const float*>(x), static_cast<float*>(y), n, act, dropout_p,
+                                                                   seed, seed_dev);
   LGK_CHECK_LAUNCH("act_dropout_fwd_kernel");
   return LGK_OK;
 }
 
-extern "C" int lgk_act_dropout_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, float dropout_p, uint64_t seed,
-                                   const int64_t* seed_dev, void* stream_) {
+extern "C" int lgk_act_dropout_bwd(const void* x, const void* dy, void* dx, int64_t n, int act, float dropout_p, uint64_t seed,
+                                   const int64_t* seed_dev, int dtype, void* stream_) {
+  using bf16 = __nv_bfloat16;
+  LGK_REQUIRE(dtype == LGK_F32 || dtype == LGK_BF16, LGK_ERR_UNSUPPORTED, "lgk_act_dropout_bwd: dtype must be LGK_F32 or LGK_BF16");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   LGK_REQUIRE(n >= 0 && dropout_p >= 0.f && dropout_p < 1.f, LGK_ERR_BAD_ARG, "lgk_act_dropout_bwd: bad arguments");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(x && dy && dx, LGK_ERR_BAD_ARG, "lgk_act_dropout_bwd: null pointer");
-  act_dropout_bwd_kernel<<<unsigned(ceil_div(n, kThreads)), kThreads, 0, stream>>>(x, dy, dx, n, act, dropout_p, seed, seed_dev);
+  const unsigned grid = unsigned(ceil_div(n, kThreads));
+  if (dtype == LGK_BF16) act_dropout_bwd_kernel<bf16><<<grid, kThreads, 0, stream>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
+                                                                                    static_cast<bf16*>(dx), n, act, dropout_p, seed, seed_dev);
+  else act_dropout_bwd_kernel<float><<<grid, kThreads, 0, stream>>>(static_cast<const float*>(x), static_cast<const float*>(dy),
+                                                                   static_cast<float*>(dx), n, act, dropout_p, seed, seed_dev);
   LGK_CHECK_LAUNCH("act_dropout_bwd_kernel");
   return LGK_OK;
 }

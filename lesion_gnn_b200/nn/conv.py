@@ -8,6 +8,8 @@ sites (models/gat.py:31,51; gin.py:23,31; drgnet.py:31,33,55): `conv(x, edge_ind
 """
 from __future__ import annotations
 
+import os
+
 import math
 from itertools import pairwise
 from typing import Optional
@@ -22,6 +24,8 @@ from ..compile import OpaqueModule
 from ..graph import CSRGraph, as_graph
 from . import functional as F
 
+# profiling knob: 0 = the attention-logit halves come from a separate lgk_gat_alpha launch over the stored h
+_FUSED_ALPHA = os.environ.get("LGK_GAT_FUSED_ALPHA", "1") != "0"
 _seed_counter = [0]
 
 
@@ -170,14 +174,21 @@ class GATConv(OpaqueModule, nn.Module):
         return x.new_empty((x.size(0), self.heads * self.out_channels if self.concat else self.out_channels))
 
     def _forward_eager(self, x: Tensor, edge_index) -> Tensor:
-        h = self.lin(x)  # before as_graph: the transform does not read the graph, whose build may still be running on
-        g = as_graph(edge_index, x.size(0))  # its own stream (as_graph joins it)
+        # before as_graph: the transform does not read the graph, whose build may still be running on its own stream
+        # (as_graph joins it).  The attention-logit halves fall out of the transform's epilogue.
+        alpha = None
+        if self.lin.bias is None and x.dim() == 2 and _FUSED_ALPHA:
+            h, a_src, a_dst = F.linear_gat(x, self.lin.weight, self.att_src, self.att_dst, self.heads, self.out_channels)
+            alpha = (a_src, a_dst)
+        else:
+            h = self.lin(x)
+        g = as_graph(edge_index, x.size(0))
         p = self.dropout if self.training else 0.0
         seed = _next_seed() if p > 0 else 0
         fused_bias = self.bias if self.concat else None
         out = F.gat_attention(h, self.att_src, self.att_dst, fused_bias, g, self.heads, self.out_channels,
                               self.negative_slope, self.add_self_loops, p, seed, fused_elu=self.fused_elu,
-                              seed_dev=_DROPOUT_CLOCK[0] if p > 0 else None)
+                              seed_dev=_DROPOUT_CLOCK[0] if p > 0 else None, alpha=alpha)
         if not self.concat:
             out = out.view(-1, self.heads, self.out_channels).mean(dim=1)
             if self.bias is not None:

@@ -153,7 +153,7 @@ class _Aggregate(torch.autograd.Function):
                               pre=ctx.post, post=ctx.pre, selfw=ctx.selfw, self_fill=ctx.self_fill, self_mode=ctx.self_mode,
                               quads=g.quads("csc") if ops.blocked_eligible(dout, "sum", ctx.ew) else None)
         if ctx.has_bias and ctx.needs_input_grad[1]:
-            d32 = dout.float() if dout.dtype != torch.float32 else dout
+            d32 = dout  # the column-sum kernel reads fp32 or bf16 and accumulates in fp32
             gb = _bucket(ctx.bias_ref)
             if gb is not None:
                 _on_side(lambda: ops.colsum(d32, out=gb), d32, key=gb.data_ptr())
@@ -176,11 +176,12 @@ class _GatAttention(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, h, att_src, att_dst, bias, g: CSRGraph, heads, chan, negative_slope, add_self_loops, dropout_p, seed,
-                fused_elu=False, seed_dev=None):
+                fused_elu=False, seed_dev=None, alpha=None):
         h = h.contiguous()
         a_s = att_src.detach().reshape(-1).contiguous()
         a_d = att_dst.detach().reshape(-1).contiguous()
-        a_src, a_dst = ops.gat_alpha(h, a_s, a_d, heads, chan)
+        # alpha: (a_src, a_dst) already formed by the transform's epilogue (linear_gat)
+        a_src, a_dst = alpha if alpha is not None else ops.gat_alpha(h, a_s, a_d, heads, chan)
         res = ops.gat_fwd(g.rowptr, g.col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p,
                           seed, with_elu=fused_elu, seed_dev=seed_dev)
         ctx.seed_dev = seed_dev
@@ -217,30 +218,46 @@ class _GatAttention(torch.autograd.Function):
             datt_src, datt_dst = datt_src.view(ctx.att_shape), datt_dst.view(ctx.att_shape)
         dbias = None
         if ctx.has_bias and ctx.needs_input_grad[3]:
-            d32 = dout if dout.dtype == torch.float32 else dout.float()
+            d32 = dout  # fp32 or bf16 in, fp32 sums out
             gb = _bucket(p_bias)
             if gb is not None:
                 _on_side(lambda: ops.colsum(d32, out=gb), d32, key=gb.data_ptr())
             else:
                 dbias = ops.colsum(d32)
-        return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None, None, None)
+        return (dh, datt_src, datt_dst, dbias, None, None, None, None, None, None, None, None, None, None)
 
 
 def gat_attention(h, att_src, att_dst, bias, g, heads, chan, negative_slope=0.2, add_self_loops=True, dropout_p=0.0,
-                  seed=0, fused_elu=False, seed_dev: Optional[Tensor] = None) -> Tensor:
+                  seed=0, fused_elu=False, seed_dev: Optional[Tensor] = None, alpha=None) -> Tensor:
     """fused_elu: return elu(attention output + bias) from the same launch (the bias must be the fused one).
     seed_dev: int64 device counter mixed into the dropout seed by the kernels (see conv.dropout_clock)"""
     return _GatAttention.apply(h, att_src, att_dst, bias, g, int(heads), int(chan), float(negative_slope),
-                               bool(add_self_loops), float(dropout_p), int(seed), bool(fused_elu), seed_dev)
+                               bool(add_self_loops), float(dropout_p), int(seed), bool(fused_elu), seed_dev, alpha)
 
 
 class _Linear(torch.autograd.Function):
     """out = act(rowscale * x W^T + bias) [+ second product x2 W2^T fused by accumulation]."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, rowscale, act, x2, weight2):
+    def forward(ctx, x, weight, bias, rowscale, act, x2, weight2, gat=None):
         x = x.contiguous()
         w = weight.contiguous()
+        if gat is not None:
+            # GATConv.lin: h = x W^T and the attention-logit halves from the transform's fp32 accumulators (no pass over h;
+            # in bf16 mode the logits do not see h's rounding).  a_src / a_dst are by-products: their gradient reaches h
+            # and the attention vectors inside the attention kernels' backward.
+            att_src, att_dst, heads, chan = gat
+            if bias is not None or rowscale is not None or act != ACT_NONE or x2 is not None:
+                raise ValueError("the GAT transform takes no bias / rowscale / activation / second operand")
+            out, a_src, a_dst = ops.linear_gat_fwd(x, w, att_src.detach().reshape(-1).contiguous(),
+                                                   att_dst.detach().reshape(-1).contiguous(), heads, chan)
+            ctx.save_for_backward(x, w, x.new_empty(0), x.new_empty(0))
+            ctx.two, ctx.act, ctx.has_bias, ctx.has_rs = False, act, False, False
+            ctx.refs = (weight, None, None)
+            ctx.mark_non_differentiable(a_src, a_dst)
+            ctx.gat = True
+            return out, a_src, a_dst
+        ctx.gat = False
         if x2 is not None:
             # out = x W^T + bias + x2 W2^T  (SAGEConv / GraphConv root term): second kernel accumulates in place
             if rowscale is not None or act != ACT_NONE:
@@ -258,7 +275,7 @@ class _Linear(torch.autograd.Function):
         return out
 
     @staticmethod
-    def backward(ctx, dout):
+    def backward(ctx, dout, *unused):
         dout = dout.contiguous()
         ni = ctx.needs_input_grad
         p_w, p_b, p_w2 = ctx.refs
@@ -280,7 +297,7 @@ class _Linear(torch.autograd.Function):
             dw, db = grads_w(dout, x, ni[1], ctx.has_bias and ni[2], p_w, p_b)
             dx2 = ops.linear_bwd_x(dout, w2) if ni[5] else None
             dw2 = grads_w(dout, x2, ni[6], False, p_w2, None)[0]
-            return dx, dw, db, None, None, dx2, dw2
+            return dx, dw, db, None, None, dx2, dw2, None
         x, w, out, rs = ctx.saved_tensors
         if ctx.act == ACT_ELU:
             dout = ops.elu_bwd(out, dout)
@@ -296,12 +313,18 @@ class _Linear(torch.autograd.Function):
                     _on_side(lambda: ops.colsum(d0, out=gb), d0, key=gb.data_ptr())
                 else:
                     db = ops.colsum(d0)
-            dout = dout * rs.unsqueeze(1)
+            dout = (dout * rs.unsqueeze(1)).to(dout.dtype)
             dw = grads_w(dout, x, ni[1], False, p_w, None)[0]
         else:
             dw, db = grads_w(dout, x, ni[1], want_db, p_w, p_b)  # one pass: db falls out of the dy tiles of dW
         dx = ops.linear_bwd_x(dout, w) if ni[0] else None
-        return dx, dw, db, None, None, None, None
+        return dx, dw, db, None, None, None, None, None
+
+
+def linear_gat(x: Tensor, weight: Tensor, att_src: Tensor, att_dst: Tensor, heads: int, chan: int):
+    """-> (h [N, H*C], a_src [N, H], a_dst [N, H]): GATConv's transform with the attention-logit halves computed in its
+    epilogue (ops.linear_gat_fwd); differentiable in x and weight through h"""
+    return _Linear.apply(x, weight, None, None, ACT_NONE, None, None, (att_src, att_dst, int(heads), int(chan)))
 
 
 def _linear_fake(x, weight, bias=None):

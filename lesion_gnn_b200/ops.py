@@ -363,9 +363,29 @@ def linear_fwd(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None, rowscal
     accumulate = out is not None
     if out is None:
         out = torch.empty(n, m, dtype=x.dtype, device=x.device)
-    L.call("lgk_linear_fwd", _chk(x, torch.float32, "x"), _chk(weight, torch.float32, "weight"), _chk(bias, torch.float32, "bias"),
-           _chk(rowscale, torch.float32, "rowscale"), _chk(out, torch.float32, "out"), n, k, m, int(act), int(accumulate), F32, _stream())
+    L.call("lgk_linear_fwd", _chk(x, None, "x"), _chk(weight, torch.float32, "weight"), _chk(bias, torch.float32, "bias"),
+           _chk(rowscale, torch.float32, "rowscale"), _chk(out, x.dtype, "out"), n, k, m, int(act), int(accumulate), _dt(x), _stream())
     return out
+
+
+def linear_gat_fwd(x: Tensor, weight: Tensor, att_src: Tensor, att_dst: Tensor, heads: int, chan: int):
+    """-> (h = x W^T [n, H*C] in x.dtype, a_src [n, H] f32, a_dst [n, H] f32): include/lgk.h lgk_linear_gat_fwd"""
+    n, k = x.shape
+    if weight.size(0) != heads * chan:
+        raise ValueError("weight must have heads * chan rows")
+    L = _lib.lib()
+    if x.dtype == torch.bfloat16 and not L.query("lgk_linear_gat_fused", n, k, int(heads), int(chan), BF16):
+        # a head width the epilogues do not cover (chan does not divide 64): keep the promise that the logits never see
+        # h's bf16 rounding -- transform in fp32, logit halves from it, then round h.  Off the reference's shapes.
+        h32, a_src, a_dst = linear_gat_fwd(x.float(), weight, att_src, att_dst, heads, chan)
+        return h32.to(torch.bfloat16), a_src, a_dst
+    out = torch.empty(n, heads * chan, dtype=x.dtype, device=x.device)
+    a_src = torch.empty(n, heads, dtype=torch.float32, device=x.device)
+    a_dst = torch.empty_like(a_src)
+    L.call("lgk_linear_gat_fwd", _chk(x, None, "x"), _chk(weight, torch.float32, "weight"), _chk(att_src, torch.float32, "att_src"),
+                    _chk(att_dst, torch.float32, "att_dst"), _chk(out), _chk(a_src), _chk(a_dst), n, k, int(heads), int(chan), _dt(x),
+                    _stream())
+    return out, a_src, a_dst
 
 
 def linear_bwd_x(dy: Tensor, weight: Tensor, out: Optional[Tensor] = None) -> Tensor:
@@ -375,13 +395,13 @@ def linear_bwd_x(dy: Tensor, weight: Tensor, out: Optional[Tensor] = None) -> Te
     L = _lib.lib()
     n, m = dy.shape
     k = weight.size(1)
-    if n >= 32768 and m >= 32 and m % 4 == 0 and k % 4 == 0:
+    if n >= 32768 and m >= 32 and m % 4 == 0 and k % 4 == 0 and dy.dtype == torch.float32:
         return linear_fwd(dy, weight.t().contiguous(), out=out)
     accumulate = out is not None
     if out is None:
         out = torch.empty(n, k, dtype=dy.dtype, device=dy.device)
-    L.call("lgk_linear_bwd_x", _chk(dy, torch.float32, "dy"), _chk(weight, torch.float32, "weight"), _chk(out, torch.float32),
-           n, k, m, int(accumulate), F32, _stream())
+    L.call("lgk_linear_bwd_x", _chk(dy, None, "dy"), _chk(weight, torch.float32, "weight"), _chk(out, dy.dtype),
+           n, k, m, int(accumulate), _dt(dy), _stream())
     return out
 
 
@@ -399,9 +419,9 @@ def linear_bwd_w(dy: Tensor, x: Optional[Tensor], want_dw: bool = True, want_db:
     dw = (dw_out if accumulate else torch.empty(m, k, dtype=torch.float32, device=dev)) if want_dw else None
     db = (db_out if accumulate else torch.empty(m, dtype=torch.float32, device=dev)) if want_db else None
     ws = _ws(L.query("lgk_linear_bwd_w_workspace_bytes", n, k, m), dev)
-    L.call("lgk_linear_bwd_w", _chk(dy, torch.float32, "dy"), _chk(x, torch.float32, "x") if want_dw else None,
+    L.call("lgk_linear_bwd_w", _chk(dy, None, "dy"), _chk(x, dy.dtype, "x") if want_dw else None,
            _chk(dw, torch.float32, "dw"), _chk(db, torch.float32, "db"),
-           n, k, m, int(accumulate), ws.data_ptr(), ws.numel(), F32, _stream())
+           n, k, m, int(accumulate), ws.data_ptr(), ws.numel(), _dt(dy), _stream())
     return (None, None) if accumulate else (dw, db)
 
 
@@ -510,10 +530,10 @@ def bn_act_fwd(x: Tensor, weight, bias, running_mean, running_var, num_batches_t
     mean = torch.empty(d, dtype=f32, device=x.device)
     invstd = torch.empty(d, dtype=f32, device=x.device)
     ws = _ws(L.query("lgk_bn_workspace_bytes", n, d), x.device)
-    L.call("lgk_bn_act_fwd", _chk(x, f32, "x"), _chk(weight, f32, "weight"), _chk(bias, f32, "bias"), _chk(running_mean, f32),
+    L.call("lgk_bn_act_fwd", _chk(x, None, "x"), _chk(weight, f32, "weight"), _chk(bias, f32, "bias"), _chk(running_mean, f32),
            _chk(running_var, f32), _chk(num_batches_tracked, torch.int64), _chk(y), _chk(mean), _chk(invstd), n, d, float(eps),
            float(momentum), int(training), int(act), float(dropout_p), int(seed), _chk(seed_dev, torch.int64), ws.data_ptr(),
-           ws.numel(), _stream())
+           ws.numel(), _dt(x), _stream())
     return y, mean, invstd
 
 
@@ -529,23 +549,23 @@ def bn_act_bwd(x: Tensor, dy: Tensor, weight, bias, mean: Tensor, invstd: Tensor
     dw = (dw_out if accumulate else torch.empty(d, dtype=f32, device=x.device)) if want_dw else None
     db = (db_out if accumulate else torch.empty(d, dtype=f32, device=x.device)) if want_db else None
     ws = _ws(L.query("lgk_bn_workspace_bytes", n, d), x.device)
-    L.call("lgk_bn_act_bwd", _chk(x, f32, "x"), _chk(dy, f32, "dy"), _chk(weight, f32), _chk(bias, f32), _chk(mean, f32), _chk(invstd, f32),
+    L.call("lgk_bn_act_bwd", _chk(x, None, "x"), _chk(dy, x.dtype, "dy"), _chk(weight, f32), _chk(bias, f32), _chk(mean, f32), _chk(invstd, f32),
            _chk(dx), _chk(dw, f32, "dweight"), _chk(db, f32, "dbias"), int(accumulate), n, d, int(training), int(act), float(dropout_p),
-           int(seed), _chk(seed_dev, torch.int64), ws.data_ptr(), ws.numel(), _stream())
+           int(seed), _chk(seed_dev, torch.int64), ws.data_ptr(), ws.numel(), _dt(x), _stream())
     return dx, (None if accumulate else dw), (None if accumulate else db)
 
 
 def act_dropout_fwd(x: Tensor, act: int, dropout_p: float, seed: int = 0, seed_dev: Optional[Tensor] = None) -> Tensor:
     L = _lib.lib()
     y = torch.empty_like(x)
-    L.call("lgk_act_dropout_fwd", _chk(x, torch.float32, "x"), _chk(y), x.numel(), int(act), float(dropout_p), int(seed),
-           _chk(seed_dev, torch.int64), _stream())
+    L.call("lgk_act_dropout_fwd", _chk(x, None, "x"), _chk(y), x.numel(), int(act), float(dropout_p), int(seed),
+           _chk(seed_dev, torch.int64), _dt(x), _stream())
     return y
 
 
 def act_dropout_bwd(x: Tensor, dy: Tensor, act: int, dropout_p: float, seed: int = 0, seed_dev: Optional[Tensor] = None) -> Tensor:
     L = _lib.lib()
     dx = torch.empty_like(x)
-    L.call("lgk_act_dropout_bwd", _chk(x, torch.float32, "x"), _chk(dy, torch.float32, "dy"), _chk(dx), x.numel(), int(act),
-           float(dropout_p), int(seed), _chk(seed_dev, torch.int64), _stream())
+    L.call("lgk_act_dropout_bwd", _chk(x, None, "x"), _chk(dy, x.dtype, "dy"), _chk(dx), x.numel(), int(act),
+           float(dropout_p), int(seed), _chk(seed_dev, torch.int64), _dt(x), _stream())
     return dx

@@ -302,6 +302,8 @@ def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_clas
     seg = Segments.from_batch(db.batch, db.num_graphs)
     logits = model(db.x, graph, seg)
     graph.join()  # a model that never touched the graph must still join the build stream
+    if logits.dtype != torch.float32:  # bf16 activations: the [B, out] logits are widened, the loss is always fp32
+        logits = logits.float()
     if _DIRECT_LOSS_GRAD and _fused_regression(logits, db.y, loss_type) and logits.requires_grad:
         # loss and (weighted) d loss / d logits from one launch; the backward starts at the logits: no autograd node
         # for the loss, no ones_like seed, no multiply by the upstream gradient

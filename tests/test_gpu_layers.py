@@ -81,6 +81,26 @@ def test_linear_fwd_bwd(dev, n, k, m):
     assert_close(bg.grad, br.grad, TOL_F32, "linear db")
 
 
+@pytest.mark.parametrize("n", [300, 5000])
+@pytest.mark.parametrize("k", [64, 36, 1025])
+@pytest.mark.parametrize("heads,chan", [(4, 16), (2, 32), (2, 64), (1, 64), (8, 8), (16, 4), (3, 20), (1, 260)])
+def test_gat_transform_with_logit_halves(dev, n, k, heads, chan):
+    """lgk_linear_gat_fwd: h = x W^T and a_src / a_dst = <h[n, h, :], att[h, :]> from the transform's accumulators (tensor-core
+    epilogue for tall aligned products, FFMA epilogue otherwise, separate kernel for head widths neither covers)"""
+    from lesion_gnn_b200 import ops
+    gen = torch.Generator().manual_seed(n + k + heads * chan)
+    x = torch.randn(n, k, generator=gen, dtype=torch.float64)
+    w = torch.randn(heads * chan, k, generator=gen, dtype=torch.float64) / k ** 0.5
+    a_s, a_d = (torch.randn(heads * chan, generator=gen, dtype=torch.float64) for _ in range(2))
+    h = x @ w.t()
+    want_s = (h.view(n, heads, chan) * a_s.view(1, heads, chan)).sum(-1)
+    want_d = (h.view(n, heads, chan) * a_d.view(1, heads, chan)).sum(-1)
+    got_h, got_s, got_d = ops.linear_gat_fwd(x.float().to(dev), w.float().to(dev), a_s.float().to(dev), a_d.float().to(dev), heads, chan)
+    assert_close(got_h, h, TOL_F32, "h")
+    assert_close(got_s, want_s, TOL_F32, "a_src")
+    assert_close(got_d, want_d, TOL_F32, "a_dst")
+
+
 def test_linear_two_operand_form(dev):
     from lesion_gnn_b200.nn import functional as F
     gen = torch.Generator().manual_seed(0)
