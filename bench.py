@@ -595,7 +595,31 @@ def secondary_legs(args, spec, graphs, total_graphs, world, rank, dev, host, dev
                 for s in range(POOL)) / POOL
     out["e2e_bf16"] = e2e_time(E2EPipe(POOL, stage_bf16), lambda s: step(devb[s]), h2d16)
     out["e2e_bf16"]["note"] = "features rounded to bf16 on the host, fp32 arithmetic on the device; separate from the fp32 e2e"
-    del x16_host, x16_dev
+
+    # ---- bf16_activations: the bf16 mode of the north_star (1e-2 bar, tests/test_gpu_bf16.py): every stored activation is
+    # bf16, parameters / accumulators / optimiser fp32; resident and end to end (features cross PCIe as bf16 and stay bf16)
+    import copy
+    host16 = []
+    for hb, x16 in zip(host, x16_host):
+        h16 = copy.copy(hb)
+        h16.x = x16
+        host16.append(h16)
+    devb16 = [train.DeviceBatch(hb, dev) for hb in host16]
+    for hb, db in zip(host16, devb16):
+        db.copy_from(hb)
+        db.loss_weight = train.dp_loss_weight(db.num_graphs, total_graphs, world)
+    _, _, step16 = make_step()
+    for db in devb16:
+        step16(db)
+    ms = timed(steps, step16, devb16)
+    leg = {"value": round(total_graphs * steps / (ms * 1e-3), 1), "unit": "graphs/s", "ms_per_step": round(ms / steps, 4), "steps": steps}
+
+    def stage16(s):
+        devb16[s].copy_from(host16[s])
+
+    leg["e2e"] = e2e_time(E2EPipe(POOL, stage16), lambda s: step16(devb16[s]), h2d16)
+    out["bf16_activations"] = leg
+    del x16_host, x16_dev, devb16, step16
 
     # ---- e2e_resident_dataset: the reference's InMemoryDataset (datasets/base.py:49) lives in HBM; per step the batch is
     # collated on the device by graph index (lgk_gather_rows) and its kNN graph + CSR are built inside the timed region

@@ -24,8 +24,13 @@ from ..compile import OpaqueModule
 from ..graph import CSRGraph, as_graph
 from . import functional as F
 
-# profiling knob: 0 = the attention-logit halves come from a separate lgk_gat_alpha launch over the stored h
-_FUSED_ALPHA = os.environ.get("LGK_GAT_FUSED_ALPHA", "1") != "0"
+# The attention-logit halves can come out of the transform's epilogue (lgk_linear_gat_fwd) instead of a separate
+# lgk_gat_alpha launch over the stored h.  bf16 activations: always (the logits must not see h's rounding: 4x smaller
+# gradient error, tests/test_gpu_bf16.py).  fp32: measured on the headline step (B200, 300 steps, same box, A/B/A/B):
+# separate 0.3266-0.3268 ms, fused 0.3308-0.3316 ms -- the tensor-core kernel's 4-warp epilogue is fully exposed (one tile
+# per CTA) and the 128 extra FMAs per row cost more there than the 2.6 us launch they replace -- so fp32 keeps the
+# separate launch unless LGK_GAT_FUSED_ALPHA=1.
+_FUSED_ALPHA_F32 = os.environ.get("LGK_GAT_FUSED_ALPHA", "0") != "0"
 _seed_counter = [0]
 
 
@@ -177,7 +182,7 @@ class GATConv(OpaqueModule, nn.Module):
         # before as_graph: the transform does not read the graph, whose build may still be running on its own stream
         # (as_graph joins it).  The attention-logit halves fall out of the transform's epilogue.
         alpha = None
-        if self.lin.bias is None and x.dim() == 2 and _FUSED_ALPHA:
+        if self.lin.bias is None and x.dim() == 2 and (x.dtype == torch.bfloat16 or _FUSED_ALPHA_F32):
             h, a_src, a_dst = F.linear_gat(x, self.lin.weight, self.att_src, self.att_dst, self.heads, self.out_channels)
             alpha = (a_src, a_dst)
         else:

@@ -255,6 +255,7 @@ class _Linear(torch.autograd.Function):
             ctx.two, ctx.act, ctx.has_bias, ctx.has_rs = False, act, False, False
             ctx.refs = (weight, None, None)
             ctx.mark_non_differentiable(a_src, a_dst)
+            ctx.set_materialize_grads(False)  # no zero tensors for the two by-products in the backward
             ctx.gat = True
             return out, a_src, a_dst
         ctx.gat = False
