@@ -76,6 +76,17 @@ LGK_API int lgk_csr_build(const int64_t* edge_index, int64_t num_edges, int64_t 
                   int32_t* colptr, int32_t* row, int32_t* csr2csc,
                   void* workspace, int64_t workspace_bytes, void* stream);
 
+/* The same build for edges ALREADY GROUPED BY DESTINATION (edge_index[1] non-decreasing): the output order of
+ * lgk_knn_graph / lgk_radius_graph and of the reference's per-sample KNNGraph + Batch.from_data_list collation
+ * (datasets/datamodule.py:45-48, transforms.py:23).  rowptr comes from boundary detection on the sorted row -- no histogram,
+ * scan or bucket fill for the CSR side -- and both in-bucket sorts run on 32-bit ids.  Outputs are bit-identical to
+ * lgk_csr_build's.  `violation` (int32 device scalar, may be NULL) is set to 1 when the input is not sorted by destination
+ * or holds an index outside [0, N) (the outputs are then unspecified but every access stays in bounds), else 0.
+ * Workspace: lgk_csr_workspace_bytes.                                                                              */
+LGK_API int lgk_csr_build_sorted(const int64_t* edge_index, int64_t num_edges, int64_t num_nodes, int32_t* rowptr, int32_t* col,
+                         int32_t* perm, int32_t* colptr, int32_t* row, int32_t* csr2csc, int32_t* violation,
+                         void* workspace, int64_t workspace_bytes, void* stream);
+
 /* Graph segment pointer from the sorted `batch` vector of PyG collation:
  * ptr[g] = first node of graph g, ptr[B] = N; empty graphs get empty segments.
  * Replaces the implicit segmentation done by scatter(x, batch) in global_*_pool

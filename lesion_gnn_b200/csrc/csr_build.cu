@@ -299,6 +299,128 @@ __global__ void __launch_bounds__(kSortThreads) sort_window_kernel(const int* __
   }
 }
 
+// ---- fast path for edges already grouped by destination (dst non-decreasing: what lgk_knn_graph, lgk_radius_graph and
+//      the reference's per-sample kNN + collate emit).  No histogram / scan / bucket fill for the CSR side at all:
+//        bounds   rowptr[r] = first edge with dst >= r (boundary detection on the sorted dst row) + histogram of src
+//        rows     per window of 128 rows: src ids staged as int32, STABLE rank by counting on the 32-bit id (entries of a
+//                 row are in edge-id order already, so (src, edge id) order = stable order on src alone: half the
+//                 shared memory and a third of the instructions of the 64-bit key compare), col / perm written, and the
+//                 entry dropped into its CSC bucket as two 4-byte values (CSR slot, dst)
+//        cols     per window of 128 buckets: rank by the (unique) CSR slot, csr2csc / row written
+//      Same outputs, bit for bit, as the general path on the same edges.
+constexpr int kFastSmall = 256;   // rank-by-counting per entry up to this row length; longer rows: the CTA together
+
+__global__ void __launch_bounds__(256) sorted_bounds_kernel(const int64_t* __restrict__ src, const int64_t* __restrict__ dst,
+                                                            int64_t E, int64_t N, int* __restrict__ rowptr,
+                                                            int* __restrict__ cnt_src, int* __restrict__ flags) {
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  const int64_t t0 = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (int64_t e = t0; e < E; e += stride) {
+    const int64_t d = __ldg(dst + e), dp = e > 0 ? __ldg(dst + e - 1) : -1;
+    if (d < dp || uint64_t(d) >= uint64_t(N)) { flags[0] = 1; continue; }  // contract violated: reported, never out of bounds
+    for (int64_t r = dp + 1; r <= d; ++r) rowptr[r] = int(e);
+    if (cnt_src) {
+      const int64_t s = __ldg(src + e);
+      if (uint64_t(s) < uint64_t(N)) atomicAdd(cnt_src + s, 1); else flags[0] = 1;
+    }
+  }
+  const int64_t last = __ldg(dst + E - 1);
+  if (uint64_t(last) < uint64_t(N))
+    for (int64_t r = last + 1 + t0; r <= N; r += stride) rowptr[r] = int(E);
+}
+
+struct FastArgs {
+  const int64_t* src;   // edge_index row 0 (rows pass) / unused
+  const int* tmp_slot;  // cols pass: unsorted CSR slots / dst per CSC bucket
+  const int* tmp_dst;
+  int* out_a;           // rows: col       cols: csr2csc
+  int* out_b;           // rows: perm      cols: row
+  const int* colptr;    // rows pass, CSC wanted: bucket fill
+  int* cursor2;
+  int* drop_slot;
+  int* drop_dst;
+  const int* flags;     // flags[0] != 0: the bounds pass found the contract violated -- rowptr is not to be trusted
+};
+
+// ROWS = true: CSR rows from the dst-sorted edge list; false: CSC buckets from the dropped (slot, dst) pairs
+template <bool ROWS>
+__global__ void __launch_bounds__(kSortThreads) sorted_window_kernel(const int* __restrict__ ptr, int64_t N, FastArgs fa) {
+  __shared__ int s_ptr[kSortRows + 1];
+  __shared__ int s_key[kSortCap];
+  __shared__ int s_pay[ROWS ? 1 : kSortCap];
+  __shared__ unsigned char s_row[kSortCap];
+  if (*reinterpret_cast<const volatile int*>(fa.flags) != 0) return;
+  const int64_t r0 = int64_t(blockIdx.x) * kSortRows;
+  const int nrows = int(min(int64_t(kSortRows), N - r0));
+  for (int t = threadIdx.x; t <= nrows; t += blockDim.x) s_ptr[t] = ptr[r0 + t];
+  __syncthreads();
+  const int w0 = s_ptr[0], wn = s_ptr[nrows] - w0;
+  const bool staged = wn <= kSortCap;
+  auto key_at = [&](int p) -> int { return ROWS ? int(__ldg(fa.src + w0 + p)) : __ldg(fa.tmp_slot + w0 + p); };
+  if (staged) {
+    for (int p = threadIdx.x; p < wn; p += blockDim.x) {
+      s_key[p] = key_at(p);
+      if (!ROWS) s_pay[p] = __ldg(fa.tmp_dst + w0 + p);
+    }
+    for (int rr = threadIdx.x; rr < nrows; rr += blockDim.x)
+      for (int p = s_ptr[rr] - w0, pe = s_ptr[rr + 1] - w0; p < pe; ++p) s_row[p] = static_cast<unsigned char>(rr);
+  }
+  __syncthreads();
+  auto emit = [&](int f, int bucket, int key, int p) {
+    fa.out_a[f] = key;
+    if (ROWS) {
+      fa.out_b[f] = w0 + p;  // the edge id: rowptr indexes the (sorted) input directly
+      if (fa.drop_slot) {
+        const int slot2 = __ldg(fa.colptr + key) + atomicAdd(fa.cursor2 + key, 1);
+        fa.drop_slot[slot2] = f;
+        fa.drop_dst[slot2] = bucket;
+      }
+    } else {
+      fa.out_b[f] = staged ? s_pay[p] : __ldg(fa.tmp_dst + w0 + p);
+    }
+  };
+  bool saw_big = false;
+  for (int p = threadIdx.x; p < wn; p += blockDim.x) {
+    int rr;
+    if (staged) {
+      rr = s_row[p];
+    } else {  // row of slot p: last rr with s_ptr[rr] <= w0 + p
+      int lo = 0, hi = nrows;
+      const int g = w0 + p;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (s_ptr[mid] <= g) lo = mid; else hi = mid;
+      }
+      rr = lo;
+    }
+    const int a = s_ptr[rr] - w0, b = s_ptr[rr + 1] - w0;
+    if (b - a > kFastSmall) { saw_big = true; continue; }
+    int rank = 0, mine;
+    if (staged) {
+      mine = s_key[p];
+      for (int q = a; q < p; ++q) rank += (s_key[q] <= mine);      // stable: equal ids keep their (edge id) order
+      for (int q = p + 1; q < b; ++q) rank += (s_key[q] < mine);
+    } else {
+      mine = key_at(p);
+      for (int q = a; q < p; ++q) rank += (key_at(q) <= mine);
+      for (int q = p + 1; q < b; ++q) rank += (key_at(q) < mine);
+    }
+    emit(w0 + a + rank, int(r0) + rr, mine, p);
+  }
+  if (!__syncthreads_or(saw_big)) return;
+  for (int rr = 0; rr < nrows; ++rr) {  // hubs: the CTA ranks one long row together, keys read through L1 / L2
+    const int a = s_ptr[rr] - w0, b = s_ptr[rr + 1] - w0;
+    if (b - a <= kFastSmall) continue;
+    for (int p = a + threadIdx.x; p < b; p += blockDim.x) {
+      const int mine = key_at(p);
+      int rank = 0;
+      for (int q = a; q < p; ++q) rank += (key_at(q) <= mine);
+      for (int q = p + 1; q < b; ++q) rank += (key_at(q) < mine);
+      emit(w0 + a + rank, int(r0) + rr, mine, p);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) batch_ptr_kernel(const int64_t* __restrict__ batch, int64_t N, int64_t B,
                                                         int* __restrict__ ptr) {
   int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -430,6 +552,65 @@ extern "C" int lgk_csr_build(const int64_t* edge_index, int64_t E, int64_t N, in
     EmitArgs ea2{csr2csc, row, nullptr, nullptr, nullptr};
     sort_window_kernel<<<sgrid1, kSortThreads, 0, stream>>>(colptr, keys2, N, ea2);
     LGK_CHECK_LAUNCH("sort_window_kernel(csc)");
+  }
+  return LGK_OK;
+}
+
+extern "C" int lgk_csr_build_sorted(const int64_t* edge_index, int64_t E, int64_t N, int32_t* rowptr, int32_t* col, int32_t* perm,
+                                    int32_t* colptr, int32_t* row, int32_t* csr2csc, int32_t* violation, void* workspace,
+                                    int64_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(E >= 0 && N >= 0, LGK_ERR_BAD_ARG, "lgk_csr_build_sorted: negative size");
+  LGK_REQUIRE(N < (int64_t(1) << 31) - 1 && E < (int64_t(1) << 31) - 1, LGK_ERR_UNSUPPORTED,
+              "lgk_csr_build_sorted: N and E must be < 2^31 - 1");
+  LGK_REQUIRE(rowptr && (E == 0 || (edge_index && col && perm)), LGK_ERR_BAD_ARG, "lgk_csr_build_sorted: null pointer");
+  const bool want_csc = colptr != nullptr;
+  LGK_REQUIRE(!want_csc || (E == 0 || (row && csr2csc)), LGK_ERR_BAD_ARG, "lgk_csr_build_sorted: partial CSC outputs");
+  Workspace w = carve(workspace, N, E);
+  LGK_REQUIRE(workspace && workspace_bytes >= w.bytes, LGK_ERR_WORKSPACE, "lgk_csr_build_sorted: workspace %lld < %lld bytes",
+              (long long)workspace_bytes, (long long)w.bytes);
+  if (E == 0 || N == 0) {
+    cudaMemsetAsync(rowptr, 0, 4 * (N + 1), stream);
+    if (want_csc) cudaMemsetAsync(colptr, 0, 4 * (N + 1), stream);
+    if (violation) cudaMemsetAsync(violation, 0, 4, stream);
+    LGK_CHECK_LAUNCH("lgk_csr_build_sorted(memset)");
+    return LGK_OK;
+  }
+  const int64_t* src = edge_index;
+  const int64_t* dst = edge_index + E;
+  // cnt_src | block sums | flags: one contiguous region, one memset (cnt_dst is not used on this path)
+  cudaMemsetAsync(w.cnt_src, 0, size_t(reinterpret_cast<char*>(w.flags) + 16 - reinterpret_cast<char*>(w.cnt_src)), stream);
+  int* flag = violation ? violation : w.flags;
+  if (violation) cudaMemsetAsync(violation, 0, 4, stream);
+  sorted_bounds_kernel<<<grid_for(E, 256), 256, 0, stream>>>(src, dst, E, N, rowptr, want_csc ? w.cnt_src : nullptr, flag);
+  LGK_CHECK_LAUNCH("sorted_bounds_kernel");
+  if (want_csc) {
+    ScanArgs sa;
+    sa.in[0] = w.cnt_src; sa.out[0] = colptr; sa.sums[0] = w.sums_b;
+    sa.in[1] = nullptr; sa.out[1] = nullptr; sa.sums[1] = nullptr;
+    const int nblocks = int(ceil_div(N, kScanTile));
+    if (N <= int64_t(kSingleThreads) * kSingleItems) {
+      scan_single_kernel<<<dim3(1, 1), kSingleThreads, 0, stream>>>(sa, N);
+      LGK_CHECK_LAUNCH("scan_single_kernel");
+    } else {
+      scan_reduce_kernel<<<dim3(nblocks, 1), kScanThreads, 0, stream>>>(sa, N);
+      LGK_CHECK_LAUNCH("scan_reduce_kernel");
+      scan_sums_kernel<<<dim3(1, 1), kScanThreads, 0, stream>>>(sa, nblocks);
+      LGK_CHECK_LAUNCH("scan_sums_kernel");
+      scan_apply_kernel<<<dim3(nblocks, 1), kScanThreads, 0, stream>>>(sa, N);
+      LGK_CHECK_LAUNCH("scan_apply_kernel");
+    }
+  }
+  int* tmp_slot = reinterpret_cast<int*>(w.keys);
+  int* tmp_dst = tmp_slot + E;
+  const int windows = int(ceil_div(N, kSortRows));
+  FastArgs fr{src, nullptr, nullptr, col, perm, colptr, w.cnt_src, want_csc ? tmp_slot : nullptr, tmp_dst, flag};
+  sorted_window_kernel<true><<<windows, kSortThreads, 0, stream>>>(rowptr, N, fr);
+  LGK_CHECK_LAUNCH("sorted_window_kernel(rows)");
+  if (want_csc) {
+    FastArgs fc{nullptr, tmp_slot, tmp_dst, csr2csc, row, nullptr, nullptr, nullptr, nullptr, flag};
+    sorted_window_kernel<false><<<windows, kSortThreads, 0, stream>>>(colptr, N, fc);
+    LGK_CHECK_LAUNCH("sorted_window_kernel(cols)");
   }
   return LGK_OK;
 }

@@ -27,6 +27,21 @@ class HostBatch:
     edge_weight: Optional[Tensor] = None  # [E] float32
 
     @property
+    def dst_sorted(self) -> bool:
+        """edge_index[1] non-decreasing (kNN graphs collated sample by sample are): checked once on the host and cached;
+        lets the device build its CSR by boundary detection (graph.CSRGraph.from_edge_index(dst_sorted=True))"""
+        ei = self.edge_index
+        if ei is None:
+            return False
+        key = (ei.data_ptr(), ei.size(1))
+        cached = self.__dict__.get("_dst_sorted")
+        if cached is None or cached[0] != key:
+            d = ei[1]
+            cached = (key, bool(ei.size(1) == 0 or bool((d[1:] >= d[:-1]).all())) if not ei.is_cuda else (key, False))
+            self.__dict__["_dst_sorted"] = cached
+        return cached[1]
+
+    @property
     def num_graphs(self) -> int:
         return len(self.counts)
 

@@ -35,8 +35,11 @@ class CSRGraph:
 
     @staticmethod
     def from_edge_index(edge_index: Tensor, num_nodes: int, edge_weight: Optional[Tensor] = None,
-                        with_csc: bool = True, stream: Optional["torch.cuda.Stream"] = None) -> "CSRGraph":
-        """`stream`: build on that stream, forked from the current one (the build overlaps whatever the current
+                        with_csc: bool = True, stream: Optional["torch.cuda.Stream"] = None,
+                        dst_sorted: bool = False) -> "CSRGraph":
+        """`dst_sorted`: edge_index[1] is known to be non-decreasing (the output order of knn_graph / radius_graph and of
+        collated per-sample kNN graphs): the faster boundary-detection build runs (ops.csr_build).
+        `stream`: build on that stream, forked from the current one (the build overlaps whatever the current
         stream does next, e.g. the in_proj transform, which does not need the graph); the first layer that uses
         the graph joins it (`join()`, called by `as_graph`)."""
         if not edge_index.is_cuda:
@@ -44,14 +47,14 @@ class CSRGraph:
         if stream is not None:
             stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(stream):
-                g = CSRGraph.from_edge_index(edge_index, num_nodes, edge_weight, with_csc)
+                g = CSRGraph.from_edge_index(edge_index, num_nodes, edge_weight, with_csc, dst_sorted=dst_sorted)
                 g._ready = torch.cuda.Event()
                 g._ready.record(stream)
             return g
         if edge_index.dtype != torch.int64:
             edge_index = edge_index.long()
         edge_index = edge_index.contiguous()
-        rowptr, col, perm, colptr, row, csr2csc = ops.csr_build(edge_index, num_nodes, with_csc)
+        rowptr, col, perm, colptr, row, csr2csc = ops.csr_build(edge_index, num_nodes, with_csc, dst_sorted=dst_sorted)
         g = CSRGraph(num_nodes, edge_index.size(1), rowptr, col, perm, colptr, row, csr2csc)
         if edge_weight is not None:
             g.value = g.permute_edge_values(edge_weight)

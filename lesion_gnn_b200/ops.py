@@ -58,8 +58,14 @@ def reset_launch_count() -> None:
 # ---------------------------------------------------------------------------------------------- structure
 
 
-def csr_build(edge_index: Tensor, num_nodes: int, with_csc: bool = True):
-    """-> rowptr, col, perm, colptr, row, csr2csc (int32); the last three are None without with_csc."""
+# set by csr_build(..., dst_sorted=True): int32 device scalar, 1 when the last sorted build found its contract violated
+last_sorted_violation: Optional[Tensor] = None
+
+
+def csr_build(edge_index: Tensor, num_nodes: int, with_csc: bool = True, dst_sorted: bool = False):
+    """-> rowptr, col, perm, colptr, row, csr2csc (int32); the last three are None without with_csc.
+    dst_sorted: the caller guarantees edge_index[1] is non-decreasing (kNN / radius graphs, collated kNN samples): the
+    boundary-detection build lgk_csr_build_sorted runs instead of the general bucket sort (same outputs)."""
     L = _lib.lib()
     if edge_index.dim() != 2 or edge_index.size(0) != 2:
         raise ValueError("edge_index must have shape [2, E]")
@@ -74,6 +80,13 @@ def csr_build(edge_index: Tensor, num_nodes: int, with_csc: bool = True):
         colptr = row = csr2csc = None
     nbytes = L.query("lgk_csr_workspace_bytes", N, E)
     ws = _ws(nbytes, dev)
+    if dst_sorted:
+        global last_sorted_violation
+        last_sorted_violation = torch.empty(1, **i32)
+        L.call("lgk_csr_build_sorted", ei, E, N, rowptr.data_ptr(), _chk(col), _chk(perm),
+               None if colptr is None else colptr.data_ptr(), _chk(row), _chk(csr2csc), last_sorted_violation.data_ptr(),
+               ws.data_ptr(), ws.numel(), _stream())
+        return rowptr, col, perm, colptr, row, csr2csc
     L.call("lgk_csr_build", ei, E, N, rowptr.data_ptr(), _chk(col), _chk(perm),
            None if colptr is None else colptr.data_ptr(), _chk(row), _chk(csr2csc),
            ws.data_ptr(), ws.numel(), _stream())

@@ -284,8 +284,14 @@ class DeviceBatch:
         self.y = torch.empty_like(hb.y, device=device)
         self.edge_index = torch.empty_like(hb.edge_index, device=device)
         self.edge_weight = torch.empty_like(hb.edge_weight, device=device) if hb.edge_weight is not None else None
+        # edges grouped by destination (collated kNN samples are): the CSR comes from boundary detection, not a bucket
+        # sort.  A property of the loader's output, decided once on the host; every batch copied into this buffer
+        # must share it (copy_from checks).
+        self.dst_sorted = bool(getattr(hb, "dst_sorted", False))
 
     def copy_from(self, hb: HostBatch) -> None:
+        if self.dst_sorted and not getattr(hb, "dst_sorted", False):
+            raise ValueError("this DeviceBatch was sized for destination-sorted edges; the batch copied in is not marked so")
         self.x.copy_(hb.x, non_blocking=True)
         self.batch.copy_(hb.batch, non_blocking=True)
         self.y.copy_(hb.y, non_blocking=True)
@@ -298,7 +304,8 @@ def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_clas
                      class_weights: Optional[Tensor] = None) -> Tensor:
     """CSR/CSC build + segment pointer + forward + loss + backward for the batch resident in `db`.  With
     `build_stream` the CSR/CSC build runs beside the model's first transform (in_proj needs no graph)."""
-    graph = CSRGraph.from_edge_index(db.edge_index, db.num_nodes, db.edge_weight, stream=build_stream)
+    graph = CSRGraph.from_edge_index(db.edge_index, db.num_nodes, db.edge_weight, stream=build_stream,
+                                     dst_sorted=getattr(db, "dst_sorted", False))
     seg = Segments.from_batch(db.batch, db.num_graphs)
     logits = model(db.x, graph, seg)
     graph.join()  # a model that never touched the graph must still join the build stream

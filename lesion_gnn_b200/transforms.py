@@ -101,6 +101,7 @@ class Data:
         self.edge_weight, self.batch, self.adj_t = edge_weight, batch, adj_t
         self.num_graphs = num_graphs
         self.counts = None if counts is None else list(counts)  # host-side graph sizes (avoids device->host reads)
+        self.edges_grouped_by_dst = False  # set by KNNGraph / RadiusGraph: ToSparseTensor then takes the sorted-input build
 
     @property
     def num_nodes(self) -> int:
@@ -114,6 +115,7 @@ class Data:
         for f in self._FIELDS:
             v = getattr(self, f)
             setattr(d, f, v.clone() if isinstance(v, Tensor) else v)
+        d.edges_grouped_by_dst = getattr(self, "edges_grouped_by_dst", False)
         return d
 
     def to(self, device, non_blocking: bool = False) -> "Data":
@@ -121,6 +123,7 @@ class Data:
         for f in self._FIELDS:
             v = getattr(self, f)
             setattr(d, f, v.to(device, non_blocking=non_blocking) if isinstance(v, Tensor) else v)
+        d.edges_grouped_by_dst = getattr(self, "edges_grouped_by_dst", False)
         return d
 
     @staticmethod
@@ -128,6 +131,7 @@ class Data:
         """a collated data.HostBatch as a Data object (optionally moved to `device`)"""
         d = Data(x=hb.x, pos=hb.pos, y=hb.y, batch=hb.batch, edge_index=hb.edge_index, edge_weight=hb.edge_weight,
                  num_graphs=hb.num_graphs, counts=hb.counts)
+        d.edges_grouped_by_dst = bool(getattr(hb, "dst_sorted", False))
         return d if device is None else d.to(device)
 
     def segments(self) -> Optional[Segments]:
@@ -173,6 +177,7 @@ class KNNGraph(BaseTransform):
         data.edge_attr = None
         num_edges = knn_num_edges(data.counts, self.k, self.loop) if data.counts is not None else None
         data.edge_index = knn_graph(data.pos, self.k, data.segments(), loop=self.loop, flow=self.flow, num_edges=num_edges)
+        data.edges_grouped_by_dst = self.flow == "source_to_target"  # lgk_knn_graph emits the k neighbours of node 0, 1, 2, ...
         return data
 
     def __repr__(self) -> str:
@@ -190,6 +195,7 @@ class RadiusGraph(BaseTransform):
         data.edge_attr = None
         data.edge_index = radius_graph(data.pos, self.r, data.segments(), loop=self.loop,
                                        max_num_neighbors=self.max_num_neighbors, flow=self.flow)
+        data.edges_grouped_by_dst = self.flow == "source_to_target"
         return data
 
     def __repr__(self) -> str:
@@ -207,7 +213,9 @@ class ToSparseTensor(BaseTransform):
     def __call__(self, data: Data) -> Data:
         from .graph import CSRGraph
         value = getattr(data, self.attr) if self.attr else None
-        data.adj_t = CSRGraph.from_edge_index(data.edge_index, data.num_nodes, value)
+        # edges made by KNNGraph / RadiusGraph on the device are grouped by destination: the sorted-input build applies
+        data.adj_t = CSRGraph.from_edge_index(data.edge_index, data.num_nodes, value,
+                                              dst_sorted=bool(getattr(data, "edges_grouped_by_dst", False)))
         if self.remove_edge_index:
             data.edge_index = None
             if self.attr:

@@ -156,3 +156,64 @@ def test_radius_graph_empty_and_single(dev):
     assert got.shape == (2, 0)
     got = transforms.radius_graph(pos.to(dev), 5.0001)
     assert torch.equal(got.cpu(), torch.tensor([[1, 0], [0, 1]]))
+
+
+def _sorted_case(n, e, seed, hub=None):
+    """random multigraph (self loops, duplicates, empty rows) with its edges grouped by destination, sources in random
+    order inside a row; hub: (node, degree) gets that many extra in-edges"""
+    ei = random_graph(n, e, seed)
+    if hub is not None:
+        g = torch.Generator().manual_seed(seed + 1)
+        extra = torch.stack([torch.randint(0, n, (hub[1],), generator=g), torch.full((hub[1],), hub[0], dtype=torch.long)])
+        ei = torch.cat([ei, extra], 1)
+    ei = ei[:, ei[1] != min(3, n - 1)] if n > 1 else ei   # an empty row in the middle
+    order = torch.sort(ei[1], stable=True).indices
+    return ei[:, order].contiguous()
+
+
+@pytest.mark.parametrize("n,e,hub", [(1, 5, None), (50, 0, None), (300, 2500, None), (5000, 80000, None), (2000, 9000, (17, 6000)),
+                                     (129, 6000, None), (100000, 1600000, None)])
+@pytest.mark.parametrize("with_csc", [True, False])
+def test_sorted_input_build_equals_general_build(dev, n, e, hub, with_csc):
+    """lgk_csr_build_sorted (boundary detection + 32-bit stable ranks) against lgk_csr_build on the same destination-sorted
+    edges: all six index arrays bit for bit, incl. a 6000-wide hub row (cooperative ranking), windows too wide to stage
+    (129 nodes x 6000 edges), empty rows and an edgeless graph"""
+    from lesion_gnn_b200 import ops
+    ei = _sorted_case(n, e, seed=n + e).to(dev)
+    want = ops.csr_build(ei, n, with_csc)
+    got = ops.csr_build(ei, n, with_csc, dst_sorted=True)
+    assert int(ops.last_sorted_violation) == 0
+    for a, b, name in zip(got, want, ("rowptr", "col", "perm", "colptr", "row", "csr2csc")):
+        assert (a is None) == (b is None), name
+        if a is not None:
+            assert torch.equal(a, b), name
+
+
+def test_sorted_input_build_reports_a_violated_contract(dev):
+    from lesion_gnn_b200 import ops
+    ei = random_graph(400, 3000, 5).to(dev)  # not sorted by destination
+    ops.csr_build(ei, 400, True, dst_sorted=True)
+    torch.cuda.synchronize()
+    assert int(ops.last_sorted_violation) == 1
+    bad = _sorted_case(400, 3000, 6).to(dev)
+    bad[0, 7] = 400  # source out of range
+    ops.csr_build(bad, 400, True, dst_sorted=True)
+    torch.cuda.synchronize()
+    assert int(ops.last_sorted_violation) == 1
+
+
+def test_knn_graph_feeds_the_sorted_build(dev):
+    """knn_graph / radius_graph emit edges grouped by destination: the transform pipeline (KNNGraph -> ToSparseTensor) takes
+    the sorted build and gets the general build's graph"""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import data, ops, transforms
+    hb = data.synth_batch(40, "ddr", 8, seed=3)
+    d = transforms.Data(x=hb.x.to(dev), pos=hb.pos.float().to(dev), batch=hb.batch.to(dev))
+    d = transforms.KNNGraph(k=6, loop=True)(d)
+    assert d.edges_grouped_by_dst and bool((d.edge_index[1][1:] >= d.edge_index[1][:-1]).all())
+    ei = d.edge_index.clone()
+    d = transforms.ToSparseTensor(attr=None)(d)
+    assert int(ops.last_sorted_violation) == 0
+    want = lg.CSRGraph.from_edge_index(ei, hb.num_nodes)
+    for name in ("rowptr", "col", "perm", "colptr", "row", "csr2csc"):
+        assert torch.equal(getattr(d.adj_t, name), getattr(want, name)), name
