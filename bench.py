@@ -621,6 +621,43 @@ def secondary_legs(args, spec, graphs, total_graphs, world, rank, dev, host, dev
     out["bf16_activations"] = leg
     del x16_host, x16_dev, devb16, step16
 
+    # ---- e2e_distinct_batches: what a DataLoader does -- a NEW batch shape every step (reference training.py:64-72).
+    # 50 distinct batches stream from pinned host memory through train.BucketedTrainStep: padded into a few (N, E) buckets,
+    # one captured graph per bucket (models with BatchNorm in training mode are refused by it: GAT / SAGE / GCN only)
+    # N = 1 only: under data parallelism the ranks would meet new buckets (warm-up + capture, i.e. extra collective calls) at
+    # different steps
+    if spec["model"] in ("gat", "sage", "gcn") and spec["graphs"] <= 1024 and world == 1:
+        distinct = 50
+        hosts50 = [hb.pin() for hb in make_host_batches(spec, graphs, rank + 64, distinct, with_edges_on=dev)]
+        model50, opt50, _ = make_step()
+        kdeg = spec["k"] + 1
+        bstep = train.BucketedTrainStep(model50, opt50, num_graphs=graphs, max_degree=kdeg, loss_type=spec["loss"], node_step=1024,
+                                        process_group=None, world_size=world)
+        for pb_hb in hosts50:  # captures happen here, outside the timed region
+            bstep(pb_hb)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        rounds = max(1, steps // distinct)
+        for _ in range(rounds):
+            for pb_hb in hosts50:
+                loss50 = bstep(pb_hb)
+        last = float(loss50)  # device -> host read of the result
+        e1.record()
+        barrier()
+        ms = max_over_ranks(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3))
+        n50 = rounds * distinct
+        out["e2e_distinct_batches"] = {
+            "value": round(total_graphs * n50 / (ms * 1e-3), 1), "unit": "graphs/s", "ms_per_step": round(ms / n50, 4), "steps": n50,
+            "distinct_batches": distinct, "distinct_shapes": len({(h.num_nodes, h.edge_index.size(1)) for h in hosts50}),
+            "captured_graphs": bstep.captures, "h2d_bytes_per_step": int(sum(h.h2d_bytes() for h in hosts50) / distinct),
+            "d2h_bytes_per_step": 4, "last_loss": last,
+            "note": "every step a batch of a different (N, E): host -> padded bucket buffers -> replay of the bucket's graph; "
+                    "copy and compute are NOT overlapped in this leg (one buffer per bucket)"}
+        del hosts50, bstep, model50, opt50
+
     # ---- e2e_resident_dataset: the reference's InMemoryDataset (datasets/base.py:49) lives in HBM; per step the batch is
     # collated on the device by graph index (lgk_gather_rows) and its kNN graph + CSR are built inside the timed region
     # (what datasets/datamodule.py:43-48,64-69 do per sample on the CPU) -------------------------------------------------

@@ -311,18 +311,22 @@ def forward_backward(model: nn.Module, db: DeviceBatch, loss_type: str, num_clas
     graph.join()  # a model that never touched the graph must still join the build stream
     if logits.dtype != torch.float32:  # bf16 activations: the [B, out] logits are widened, the loss is always fp32
         logits = logits.float()
-    if _DIRECT_LOSS_GRAD and _fused_regression(logits, db.y, loss_type) and logits.requires_grad:
+    y = db.y
+    valid = getattr(db, "valid_graphs", None)
+    if valid is not None and valid < logits.size(0):  # PaddedBatch: the trailing graph holds the padding nodes
+        logits, y = logits[:valid], y[:valid]
+    if _DIRECT_LOSS_GRAD and _fused_regression(logits, y, loss_type) and logits.requires_grad:
         # loss and (weighted) d loss / d logits from one launch; the backward starts at the logits: no autograd node
         # for the loss, no ones_like seed, no multiply by the upstream gradient
-        loss, dl = ops.clamped_regression_loss(logits.detach().reshape(-1), db.y, 0.0, float(num_classes - 1),
+        loss, dl = ops.clamped_regression_loss(logits.detach().reshape(-1), y, 0.0, float(num_classes - 1),
                                                0 if loss_type == "MSE" else 1, grad_scale=db.loss_weight)
         logits.backward(dl.view_as(logits))
         return loss
-    if _DIRECT_LOSS_GRAD and loss_type == "CE" and _fused_ce(logits, db.y) and logits.requires_grad:
-        loss, dl = ops.cross_entropy_loss(logits.detach().contiguous(), db.y, class_weights, grad_scale=db.loss_weight)
+    if _DIRECT_LOSS_GRAD and loss_type == "CE" and _fused_ce(logits, y) and logits.requires_grad:
+        loss, dl = ops.cross_entropy_loss(logits.detach().contiguous(), y, class_weights, grad_scale=db.loss_weight)
         logits.backward(dl)
         return loss
-    loss = loss_fn(logits, db.y, loss_type, num_classes, class_weights)
+    loss = loss_fn(logits, y, loss_type, num_classes, class_weights)
     (loss * db.loss_weight if db.loss_weight != 1.0 else loss).backward()
     return loss.detach()
 
@@ -403,3 +407,101 @@ class TrainStep:
         entry[0].replay()
         self._finish_dp()
         return entry[1]
+
+
+class PaddedBatch(DeviceBatch):
+    """Static device buffers for a BUCKET of batch shapes: room for `node_cap` nodes, `edge_cap` edges and `num_graphs` real
+    graphs plus ONE trailing padding graph.  `load(hb)` copies a host batch of any smaller shape into the front and turns
+    the rest into padding that cannot influence the real graphs: the spare nodes have zero features and belong to the
+    padding graph, the spare edges are self loops on the last (always spare) node, and the padding graph's logit is left
+    out of the loss (`valid_graphs`), so it receives a zero gradient and contributes exact zeros to every parameter
+    gradient.  Every kernel of the captured step sees the bucket's sizes: one CUDA graph serves all shapes of the bucket
+    (SURVEY.md 7 hard part 10; reference training.py:64-72 steps over DataLoader batches of varying (N, E)).
+    Not for models with BatchNorm in training mode: batch statistics would see the padding rows."""
+
+    def __init__(self, node_cap: int, edge_cap: int, num_graphs: int, feat: int, device, x_dtype=torch.float32,
+                 with_edge_weight: bool = False, dst_sorted: bool = True):
+        self.num_nodes, self.num_graphs, self.valid_graphs = int(node_cap), int(num_graphs) + 1, int(num_graphs)
+        self.num_edges = int(edge_cap)
+        self.loss_weight = 1.0
+        self.dst_sorted = bool(dst_sorted)
+        self.x = torch.zeros(node_cap, feat, dtype=x_dtype, device=device)
+        self.batch = torch.full((node_cap,), num_graphs, dtype=torch.int64, device=device)
+        self.y = torch.zeros(num_graphs + 1, dtype=torch.int64, device=device)
+        self.edge_index = torch.full((2, edge_cap), node_cap - 1, dtype=torch.int64, device=device)
+        self.edge_weight = torch.zeros(edge_cap, dtype=torch.float32, device=device) if with_edge_weight else None
+        self._dirty_nodes = 0   # rows of x / batch that the previous load wrote
+        self._dirty_edges = 0
+
+    def fits(self, hb: HostBatch) -> bool:
+        return (hb.num_nodes < self.num_nodes and hb.edge_index.size(1) <= self.num_edges and hb.num_graphs == self.valid_graphs
+                and hb.x.size(1) == self.x.size(1))
+
+    def load(self, hb: HostBatch) -> None:
+        """host -> device copy of `hb` into the front of the buffers (stream-ordered, non-blocking from pinned memory); only
+        the part of the padding that the previous, larger batch had overwritten is re-initialised"""
+        if not self.fits(hb):
+            raise ValueError("the batch does not fit this bucket (needs num_nodes < node_cap, E <= edge_cap, the same number "
+                             "of graphs and feature width)")
+        if self.dst_sorted and not hb.dst_sorted:
+            raise ValueError("this bucket was declared destination-sorted; the batch is not")
+        n, e = hb.num_nodes, hb.edge_index.size(1)
+        self.x[:n].copy_(hb.x, non_blocking=True)
+        self.batch[:n].copy_(hb.batch, non_blocking=True)
+        self.y[:self.valid_graphs].copy_(hb.y, non_blocking=True)
+        self.edge_index[:, :e].copy_(hb.edge_index, non_blocking=True)
+        if self.edge_weight is not None:
+            self.edge_weight[:e].copy_(hb.edge_weight, non_blocking=True)
+        if self._dirty_nodes > n:
+            self.x[n:self._dirty_nodes].zero_()
+            self.batch[n:self._dirty_nodes].fill_(self.valid_graphs)
+        if self._dirty_edges > e:
+            self.edge_index[:, e:self._dirty_edges].fill_(self.num_nodes - 1)
+            if self.edge_weight is not None:
+                self.edge_weight[e:self._dirty_edges].zero_()
+        self._dirty_nodes, self._dirty_edges = n, e
+
+    def copy_from(self, hb: HostBatch) -> None:
+        self.load(hb)
+
+
+class BucketedTrainStep:
+    """TrainStep over batches of VARYING shape with a handful of captured graphs: a batch goes into the PaddedBatch of its
+    bucket -- node capacity = num_nodes rounded up to `node_step` (plus the one node the padding needs), edge capacity =
+    node capacity x `max_degree` -- and the bucket's CUDA graph, captured on first use, is replayed.  `captures` counts
+    the graphs captured so far."""
+
+    def __init__(self, model: nn.Module, opt, num_graphs: int, max_degree: int, loss_type: str = "MSE", num_classes: int = 5,
+                 node_step: int = 4096, with_edge_weight: bool = False, x_dtype=torch.float32, dst_sorted: bool = True,
+                 **train_step_kwargs):
+        for m in model.modules():
+            if isinstance(m, nn.modules.batchnorm._BatchNorm) and model.training:
+                raise NotImplementedError("padded batches would enter BatchNorm's batch statistics: use TrainStep per shape")
+        self.step = TrainStep(model, opt, loss_type, num_classes, use_cuda_graph=True, **train_step_kwargs)
+        self.num_graphs, self.max_degree, self.node_step = int(num_graphs), int(max_degree), int(node_step)
+        self.with_edge_weight, self.x_dtype, self.dst_sorted = with_edge_weight, x_dtype, dst_sorted
+        self.device = opt.param.device
+        self.buckets = {}
+
+    @property
+    def captures(self) -> int:
+        return len(self.step._graphs)
+
+    def bucket_of(self, hb: HostBatch) -> int:
+        cap = (hb.num_nodes + 1 + self.node_step - 1) // self.node_step * self.node_step
+        while hb.edge_index.size(1) > cap * self.max_degree:  # a batch denser than declared: the next bucket up
+            cap += self.node_step
+        return cap
+
+    def __call__(self, hb: HostBatch) -> Tensor:
+        if hb.num_graphs != self.num_graphs:
+            raise ValueError(f"bucketed steps take batches of {self.num_graphs} graphs (the DataLoader's batch_size); "
+                             f"got {hb.num_graphs}: run the last, smaller batch of an epoch through its own BucketedTrainStep")
+        cap = self.bucket_of(hb)
+        pb = self.buckets.get(cap)
+        if pb is None:
+            pb = PaddedBatch(cap, cap * self.max_degree, self.num_graphs, hb.x.size(1), self.device, self.x_dtype,
+                             self.with_edge_weight, self.dst_sorted)
+            self.buckets[cap] = pb
+        pb.load(hb)
+        return self.step(pb)

@@ -1,0 +1,83 @@
+"""Shape-polymorphic captured training step (SURVEY.md 7 hard part 10; reference training.py:64-72 steps over DataLoader
+batches whose (N, E) change every step): 50 different DDR-shaped batches go through train.BucketedTrainStep with at most
+4 captured CUDA graphs, and every loss and the final parameters equal those of the plain eager step on the unpadded
+batches."""
+import pytest
+import torch
+
+from tests.util import knn_batch, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _batches(count, graphs, feat, k):
+    return [knn_batch(graphs, "ddr", feat, k, seed=100 + i).pin() for i in range(count)]
+
+
+@pytest.mark.parametrize("name", ["gat", "sage"])
+def test_fifty_shapes_four_graphs(dev, name):
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import train
+    graphs, feat, k = 16, 24, 6
+    hbs = _batches(50, graphs, feat, k)
+    shapes = {(hb.num_nodes, hb.edge_index.size(1)) for hb in hbs}
+    assert len(shapes) >= 40, "the batches must really differ in shape"
+    assert all(hb.dst_sorted for hb in hbs)  # collated kNN samples: grouped by destination
+
+    def make():
+        torch.manual_seed(7)
+        if name == "gat":
+            m = lg.models.GAT(feat, [32, 32, 32], 1, heads=4, dropout=0.0)
+        else:
+            m = lg.models.SAGE(feat, [32, 32], 1, aggr="mean", pooling="mean")
+        m = m.to(dev).train()
+        return m, train.FlatAdam(m, lr=2e-3, weight_decay=1e-5)
+
+    m_ref, o_ref = make()
+    eager = train.TrainStep(m_ref, o_ref, "MSE", 5, use_cuda_graph=False)
+    m_b, o_b = make()
+    bucketed = train.BucketedTrainStep(m_b, o_b, num_graphs=graphs, max_degree=k + 1, loss_type="MSE", node_step=256)
+    for i, hb in enumerate(hbs):
+        db = train.DeviceBatch(hb, dev)
+        db.copy_from(hb)
+        want = float(eager(db))
+        got = float(bucketed(hb))
+        assert abs(got - want) <= 1e-4 * max(abs(want), 1e-3), (i, got, want)
+    assert bucketed.captures <= 4, bucketed.captures
+    assert len(bucketed.buckets) == bucketed.captures
+    assert int(o_b.step_dev[0]) == int(o_ref.step_dev[0]) == 50
+    assert rel_err(o_b.param, o_ref.param) <= 1e-3
+
+
+def test_padding_contributes_exact_zeros(dev):
+    """one batch, padded vs unpadded: identical loss and parameter gradients up to the summation order of the slab
+    reductions (the padding rows add exact zeros)"""
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import train
+    hb = knn_batch(12, "ddr", 24, 6, seed=3).pin()
+    grads = []
+    for padded in (False, True):
+        torch.manual_seed(1)
+        m = lg.models.GAT(24, [32, 32, 32], 1, heads=4, dropout=0.0).to(dev).train()
+        opt = train.FlatAdam(m, lr=0.0)
+        if padded:
+            db = train.PaddedBatch(hb.num_nodes + 500, (hb.num_nodes + 500) * 7, hb.num_graphs, 24, dev)
+            db.load(hb)
+        else:
+            db = train.DeviceBatch(hb, dev)
+            db.copy_from(hb)
+        opt.zero_grad()
+        with train.direct_param_grads():
+            loss = train.forward_backward(m, db, "MSE", 5)
+        torch.cuda.synchronize()
+        grads.append((float(loss), opt.grad.clone()))
+    assert abs(grads[0][0] - grads[1][0]) <= 1e-6 * abs(grads[0][0])
+    assert rel_err(grads[1][1], grads[0][1]) <= 1e-5
+
+
+def test_batchnorm_models_are_refused(dev):
+    import lesion_gnn_b200 as lg
+    from lesion_gnn_b200 import train
+    m = lg.models.GIN(8, [8, 8], 5, dropout=0.0).to(dev).train()
+    with pytest.raises(NotImplementedError):
+        train.BucketedTrainStep(m, train.FlatAdam(m), num_graphs=4, max_degree=7)
