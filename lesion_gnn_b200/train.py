@@ -242,6 +242,8 @@ def _fused_regression(logits: Tensor, y: Tensor, loss_type: str) -> bool:
             and logits.dim() == 2 and logits.size(1) == 1)
 
 
+# profiling knob: 0 = batches whose edges are grouped by destination still take the general CSR/CSC build
+_SORTED_BUILD = os.environ.get("LGK_CSR_SORTED", "1") != "0"
 # 1 = the Adam kernel advances the step counter itself (measured slower than the 1-element add launch: off)
 _ADAM_ADVANCES_STEP = os.environ.get("LGK_ADAM_ADVANCES_STEP", "0") != "0"
 # profiling knob: 0 = zero_grad() is its own fill launch at the head of every step
@@ -287,7 +289,7 @@ class DeviceBatch:
         # edges grouped by destination (collated kNN samples are): the CSR comes from boundary detection, not a bucket
         # sort.  A property of the loader's output, decided once on the host; every batch copied into this buffer
         # must share it (copy_from checks).
-        self.dst_sorted = bool(getattr(hb, "dst_sorted", False))
+        self.dst_sorted = bool(getattr(hb, "dst_sorted", False)) and _SORTED_BUILD
 
     def copy_from(self, hb: HostBatch) -> None:
         if self.dst_sorted and not getattr(hb, "dst_sorted", False):
@@ -413,9 +415,10 @@ class PaddedBatch(DeviceBatch):
     """Static device buffers for a BUCKET of batch shapes: room for `node_cap` nodes, `edge_cap` edges and `num_graphs` real
     graphs plus ONE trailing padding graph.  `load(hb)` copies a host batch of any smaller shape into the front and turns
     the rest into padding that cannot influence the real graphs: the spare nodes have zero features and belong to the
-    padding graph, the spare edges are self loops on the last (always spare) node, and the padding graph's logit is left
+    padding graph, the spare edges are self loops on the spare nodes, and the padding graph's logit is left
     out of the loss (`valid_graphs`), so it receives a zero gradient and contributes exact zeros to every parameter
-    gradient.  Every kernel of the captured step sees the bucket's sizes: one CUDA graph serves all shapes of the bucket
+    gradient.  The spare edges are spread evenly over the spare nodes (a single hub of thousands of self loops would be one
+    serial row in every per-node kernel: measured 70 ms per step instead of 0.4 ms).  Every kernel of the captured step sees the bucket's sizes: one CUDA graph serves all shapes of the bucket
     (SURVEY.md 7 hard part 10; reference training.py:64-72 steps over DataLoader batches of varying (N, E)).
     Not for models with BatchNorm in training mode: batch statistics would see the padding rows."""
 
@@ -428,10 +431,21 @@ class PaddedBatch(DeviceBatch):
         self.x = torch.zeros(node_cap, feat, dtype=x_dtype, device=device)
         self.batch = torch.full((node_cap,), num_graphs, dtype=torch.int64, device=device)
         self.y = torch.zeros(num_graphs + 1, dtype=torch.int64, device=device)
-        self.edge_index = torch.full((2, edge_cap), node_cap - 1, dtype=torch.int64, device=device)
+        self.edge_index = torch.empty((2, edge_cap), dtype=torch.int64, device=device)
         self.edge_weight = torch.zeros(edge_cap, dtype=torch.float32, device=device) if with_edge_weight else None
+        self._iota = torch.arange(edge_cap, dtype=torch.int64, device=device)
         self._dirty_nodes = 0   # rows of x / batch that the previous load wrote
         self._dirty_edges = 0
+        self._pad_edges(0, 0)
+
+    def _pad_edges(self, n: int, e: int) -> None:
+        """spare edge slots e.. -> self loops (j, j) on the spare nodes n.., spread evenly and ascending (the edge list stays
+        grouped by destination)"""
+        spare_e, spare_n = self.num_edges - e, self.num_nodes - n
+        if spare_e > 0:
+            tail = (self._iota[:spare_e] * spare_n).div_(spare_e, rounding_mode="floor").add_(n)
+            self.edge_index[0, e:].copy_(tail)
+            self.edge_index[1, e:].copy_(tail)
 
     def fits(self, hb: HostBatch) -> bool:
         return (hb.num_nodes < self.num_nodes and hb.edge_index.size(1) <= self.num_edges and hb.num_graphs == self.valid_graphs
@@ -455,10 +469,9 @@ class PaddedBatch(DeviceBatch):
         if self._dirty_nodes > n:
             self.x[n:self._dirty_nodes].zero_()
             self.batch[n:self._dirty_nodes].fill_(self.valid_graphs)
-        if self._dirty_edges > e:
-            self.edge_index[:, e:self._dirty_edges].fill_(self.num_nodes - 1)
-            if self.edge_weight is not None:
-                self.edge_weight[e:self._dirty_edges].zero_()
+        self._pad_edges(n, e)  # depends on (n, e): recomputed per load, a handful of launches over the spare slots
+        if self._dirty_edges > e and self.edge_weight is not None:
+            self.edge_weight[e:self._dirty_edges].zero_()
         self._dirty_nodes, self._dirty_edges = n, e
 
     def copy_from(self, hb: HostBatch) -> None:

@@ -75,6 +75,22 @@ def test_padding_contributes_exact_zeros(dev):
     assert rel_err(grads[1][1], grads[0][1]) <= 1e-5
 
 
+def test_padding_edges_make_no_hub(dev):
+    """the spare edges are spread over the spare nodes: no padded node ends up with more than ~max_degree in-edges, even
+    when a single spare node remains"""
+    from lesion_gnn_b200 import train
+    hb = knn_batch(12, "ddr", 8, 6, seed=4).pin()
+    for cap in (hb.num_nodes + 1, hb.num_nodes + 37, hb.num_nodes + 4000):
+        pb = train.PaddedBatch(cap, cap * 7, hb.num_graphs, 8, dev)
+        pb.load(hb)
+        dst = pb.edge_index[1]
+        assert bool((dst[1:] >= dst[:-1]).all()) and int(dst.max()) == cap - 1 and torch.equal(pb.edge_index[0, hb.edge_index.size(1):],
+                                                                                                   dst[hb.edge_index.size(1):])
+        deg = torch.bincount(dst[hb.edge_index.size(1):] - hb.num_nodes, minlength=cap - hb.num_nodes)
+        spare_e, spare_n = cap * 7 - hb.edge_index.size(1), cap - hb.num_nodes
+        assert int(deg.max()) <= -(-spare_e // spare_n) and int(deg.sum()) == spare_e
+
+
 def test_batchnorm_models_are_refused(dev):
     import lesion_gnn_b200 as lg
     from lesion_gnn_b200 import train

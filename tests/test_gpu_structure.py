@@ -209,11 +209,13 @@ def test_knn_graph_feeds_the_sorted_build(dev):
     from lesion_gnn_b200 import data, ops, transforms
     hb = data.synth_batch(40, "ddr", 8, seed=3)
     d = transforms.Data(x=hb.x.to(dev), pos=hb.pos.float().to(dev), batch=hb.batch.to(dev))
+    lg.graph._SORTED_MIN_EDGES = 0  # small graphs normally keep the general build (faster below ~1 M edges)
     d = transforms.KNNGraph(k=6, loop=True)(d)
     assert d.edges_grouped_by_dst and bool((d.edge_index[1][1:] >= d.edge_index[1][:-1]).all())
     ei = d.edge_index.clone()
     d = transforms.ToSparseTensor(attr=None)(d)
     assert int(ops.last_sorted_violation) == 0
+    lg.graph._SORTED_MIN_EDGES = 1 << 20
     want = lg.CSRGraph.from_edge_index(ei, hb.num_nodes)
     for name in ("rowptr", "col", "perm", "colptr", "row", "csr2csc"):
         assert torch.equal(getattr(d.adj_t, name), getattr(want, name)), name
