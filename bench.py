@@ -262,6 +262,20 @@ def algorithmic_bytes(name: str, a: dict, num_edges: int) -> int:
         return 12 * a["n"]
     if name == "lgk_gather_f32":
         return 12 * a["n"]
+    es = 2 if a.get("dtype") == 1 else 4  # activation element size (LGK_BF16 = 1)
+    if name == "lgk_bn_act_fwd":    # x read for the statistics and again for the output, y written
+        return (3 if a.get("training") else 2) * a["n"] * a["d"] * es
+    if name == "lgk_bn_act_bwd":    # x and dy read for the sums and again for dx, dx written
+        return 5 * a["n"] * a["d"] * es
+    if name == "lgk_act_dropout_fwd":
+        return 2 * a["n"] * es
+    if name == "lgk_act_dropout_bwd":
+        return 3 * a["n"] * es
+    if name == "lgk_csr_build_sorted":
+        return 28 * a["num_edges"] + 8 * (a["num_nodes"] + 1)
+    if name == "lgk_linear_gat_fwd":
+        m = a["heads"] * a["chan"]
+        return (a["n"] * a["k"] + a["n"] * m) * es + 4 * a["k"] * m + 8 * a["n"] * a["heads"]
     return 0
 
 

@@ -365,6 +365,119 @@ __global__ void __launch_bounds__(256) bwd_w_slab_kernel(const T* __restrict__ d
   }
 }
 
+// The same slab reduction with the 32-row chunks of x and dy streamed through a three-stage cp.async ring (fp32, 16-byte
+// aligned rows): chunk c + 2 is in flight while chunk c is multiplied.  r02: the single-buffered kernel above (load, barrier,
+// multiply, barrier) moved 1.08 TB/s on config 3's 409 600-row products, 26 % of the GIN step.
+constexpr int kPipeStages = 3;
+__device__ __forceinline__ void cp_async_16_zfill(float* smem_dst, const float* gmem_src, bool valid) {
+  const int bytes = valid ? 16 : 0;  // src-size 0: the 16 bytes are zero-filled, nothing is read
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(uint32_t(__cvta_generic_to_shared(smem_dst))), "l"(gmem_src), "r"(bytes)
+               : "memory");
+}
+template <int KB, int MB>
+__global__ void __launch_bounds__(256) bwd_w_slab_pipe_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                              float* __restrict__ partial, int64_t N, int K, int M,
+                                                              int64_t slab_rows, int want_db) {
+  extern __shared__ __align__(16) float sm[];
+  constexpr int kp = KB * 64, mp = MB * 64, stage_f = kSlabChunk * (kp + mp);
+  const int tk = threadIdx.x >> 4, tm = threadIdx.x & 15;
+  const int64_t r0 = int64_t(blockIdx.x) * slab_rows;
+  const int64_t r1 = min(N, r0 + slab_rows);
+  const int nchunks = r1 > r0 ? int((r1 - r0 + kSlabChunk - 1) / kSlabChunk) : 0;
+  float acc[KB][MB][4][4];
+  float dbs[MB][4];
+#pragma unroll
+  for (int a = 0; a < KB; ++a)
+#pragma unroll
+    for (int b = 0; b < MB; ++b)
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[a][b][i][j] = 0.f;
+#pragma unroll
+  for (int b = 0; b < MB; ++b)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dbs[b][j] = 0.f;
+
+  auto issue = [&](int ci) {
+    if (ci < nchunks) {
+      float* xs = sm + (ci % kPipeStages) * stage_f;
+      float* ds = xs + kSlabChunk * kp;
+      const int64_t c0 = r0 + int64_t(ci) * kSlabChunk;
+      const int rows = (r1 - c0 < kSlabChunk) ? int(r1 - c0) : kSlabChunk;
+      for (int e = threadIdx.x; e < kSlabChunk * kp / 4; e += 256) {
+        const int r = e / (kp / 4), c = (e - r * (kp / 4)) * 4;
+        const bool ok = r < rows && c < K;
+        cp_async_16_zfill(xs + e * 4, ok ? x + (c0 + r) * K + c : x, ok);
+      }
+      for (int e = threadIdx.x; e < kSlabChunk * mp / 4; e += 256) {
+        const int r = e / (mp / 4), c = (e - r * (mp / 4)) * 4;
+        const bool ok = r < rows && c < M;
+        cp_async_16_zfill(ds + e * 4, ok ? dy + (c0 + r) * M + c : dy, ok);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");  // an empty group past the end keeps the wait count uniform
+  };
+#pragma unroll
+  for (int st = 0; st < kPipeStages - 1; ++st) issue(st);
+  for (int ci = 0; ci < nchunks; ++ci) {
+    issue(ci + kPipeStages - 1);
+    asm volatile("cp.async.wait_group %0;" ::"n"(kPipeStages - 1) : "memory");
+    __syncthreads();
+    const float* xs = sm + (ci % kPipeStages) * stage_f;
+    const float* ds = xs + kSlabChunk * kp;
+#pragma unroll 4
+    for (int r = 0; r < kSlabChunk; ++r) {
+      float4 a4[KB], b4[MB];
+#pragma unroll
+      for (int a = 0; a < KB; ++a) a4[a] = *reinterpret_cast<const float4*>(xs + r * kp + a * 64 + tk * 4);
+#pragma unroll
+      for (int b = 0; b < MB; ++b) b4[b] = *reinterpret_cast<const float4*>(ds + r * mp + b * 64 + tm * 4);
+#pragma unroll
+      for (int a = 0; a < KB; ++a) {
+        const float av[4] = {a4[a].x, a4[a].y, a4[a].z, a4[a].w};
+#pragma unroll
+        for (int b = 0; b < MB; ++b) {
+          const float bv[4] = {b4[b].x, b4[b].y, b4[b].z, b4[b].w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[a][b][i][j] = fmaf(av[i], bv[j], acc[a][b][i][j]);
+        }
+      }
+      if (tk == 0) {
+#pragma unroll
+        for (int b = 0; b < MB; ++b) { dbs[b][0] += b4[b].x; dbs[b][1] += b4[b].y; dbs[b][2] += b4[b].z; dbs[b][3] += b4[b].w; }
+      }
+    }
+    __syncthreads();  // the stage is refilled by the next iteration's issue
+  }
+  float* p = partial + int64_t(blockIdx.x) * (int64_t(K) * M + M);
+#pragma unroll
+  for (int a = 0; a < KB; ++a)
+#pragma unroll
+    for (int b = 0; b < MB; ++b)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int mi = b * 64 + tm * 4 + j;
+        if (mi >= M) continue;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int ki = a * 64 + tk * 4 + i;
+          if (ki < K) p[int64_t(mi) * K + ki] = acc[a][b][i][j];
+        }
+      }
+  if (want_db && tk == 0) {
+#pragma unroll
+    for (int b = 0; b < MB; ++b)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int mi = b * 64 + tm * 4 + j;
+        if (mi < M) p[int64_t(K) * M + mi] = dbs[b][j];
+      }
+  }
+}
+
 // db[m] = sum_n dy[n,m] alone (bias gradients of the fused aggregation kernels): slab partials, same second stage.
 // Threads = (row lane, float4 column); M % 4 == 0 fast path, scalar otherwise.
 template <typename T>
@@ -592,7 +705,29 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
       else bwd_w_slab_kernel<KB, MB, false, float><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, wdb);    \
     }                                                                                                                                 \
   } while (0)
-    if (kb == 1 && mb == 1) LGK_SLAB(1, 1);
+    // LGK_SLAB_PIPE=0: the single-buffered kernel for fp32 too (profiling knob)
+    static const bool pipe_on = [] { const char* v = getenv("LGK_SLAB_PIPE"); return !(v && *v == '0'); }();
+    // measured: 194 -> 128 us per call at n = 409 600 (config 3), but the headline step (n = 11 k, kernels of three
+    // streams sharing the SMs) is 2.5 us slower with the 48 KB ring than with the 16 KB single buffer: tall products only
+    if (vec && !is_bf16 && pipe_on && n >= 65536) {
+      const size_t psm = size_t(kPipeStages) * smem;
+#define LGK_SLAB_PIPE(KB, MB)                                                                                             \
+  do {                                                                                                                    \
+    static bool cfg[64] = {};                                                                                             \
+    int dev_ord = 0;                                                                                                      \
+    cudaGetDevice(&dev_ord);                                                                                              \
+    if (!cfg[dev_ord & 63]) {                                                                                             \
+      cudaFuncSetAttribute(bwd_w_slab_pipe_kernel<KB, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeStages) * kSlabChunk * (KB + MB) * 64 * 4); \
+      cfg[dev_ord & 63] = true;                                                                                           \
+    }                                                                                                                     \
+    bwd_w_slab_pipe_kernel<KB, MB><<<slabs, 256, psm, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, wdb);       \
+  } while (0)
+      if (kb == 1 && mb == 1) LGK_SLAB_PIPE(1, 1);
+      else if (kb == 1) LGK_SLAB_PIPE(1, 2);
+      else if (mb == 1) LGK_SLAB_PIPE(2, 1);
+      else LGK_SLAB_PIPE(2, 2);
+#undef LGK_SLAB_PIPE
+    } else if (kb == 1 && mb == 1) LGK_SLAB(1, 1);
     else if (kb == 1) LGK_SLAB(1, 2);
     else if (mb == 1) LGK_SLAB(2, 1);
     else LGK_SLAB(2, 2);
