@@ -308,6 +308,19 @@ LGK_API int64_t lgk_linear_bwd_w_workspace_bytes(int64_t n, int64_t k, int64_t m
 LGK_API int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float* db, int64_t n, int64_t k, int64_t m,
                      int accumulate, void* workspace, int64_t workspace_bytes, int dtype, void* stream);
 
+/* db[m] (+)= sum_n dy[n,m] -- the bias-gradient column sum of lgk_linear_bwd_w(dw = NULL) -- WITHOUT a caller workspace
+ * and without any allocation: the slab partials live in a device array inside the library.  This entry point has no
+ * counterpart in the reference; it was added for callers that cannot call
+ * cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  It calls no cudaMalloc / cudaFree and
+ * no allocating library routine.  Limit: m <= LGK_COLSUM_STATIC_MAX_M (any n); larger m returns LGK_ERR_UNSUPPORTED with
+ * a message naming the limit.  Cost: 296 x 1024 x 4 B = 1.16 MiB of device memory on every GPU that loads the library,
+ * held until the process exits.  All calls on one GPU share that scratch and it keeps the last call's contents (each call
+ * overwrites everything it reads, nothing needs clearing): calls that OVERLAP on the GPU (different streams, concurrent
+ * graph launches) race -- order them on one stream or with events.  dy: [n, m] row-major `dtype`; db: fp32 [m];
+ * result bit-identical to lgk_linear_bwd_w(dy, NULL, NULL, db, ...).                                                  */
+#define LGK_COLSUM_STATIC_MAX_M 1024
+LGK_API int lgk_colsum_static(const void* dy, float* db, int64_t n, int64_t m, int accumulate, int dtype, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * elementwise helpers of the step (activation after each conv: F.elu at reference models/gat.py:51, gin.py:31,
  * drgnet.py:55; optimiser: torch.optim.Adam at models/base.py:162-170)

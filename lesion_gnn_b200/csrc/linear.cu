@@ -777,3 +777,70 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
   }
   return LGK_OK;
 }
+
+// ---- lgk_colsum_static: the bias-gradient column sum with its scratch inside the library ---------------------------
+// Same two kernels as lgk_linear_bwd_w(dw = NULL) -- slab partials, then the fixed-order second stage -- but the
+// [slabs, m] partials live in the file-scope device array below instead of a caller-provided workspace, for callers that
+// cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The array costs 296 x 1024 x 4 B = 1.16 MiB on every GPU that loads the
+// library, until the process exits.  Every call shares it and it keeps the last call's contents: nothing has to be
+// cleared, because each call's first kernel writes every partial [slab < slabs][column < m] that its second kernel reads;
+// two calls that OVERLAP on one GPU (different streams, concurrent graphs) race on it -- serialise them.
+#include <mutex>
+
+constexpr int kStaticMaxSlabs = 2 * lgk::kNumSMs;   // what slab_count() can return at most
+constexpr int kStaticMaxM = 1024;                    // LGK_COLSUM_STATIC_MAX_M in include/lgk.h
+static __device__ __align__(256) float g_colsum_scratch[kStaticMaxSlabs * kStaticMaxM];
+
+// The array's name is a host-side stand-in in host code, not a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static float* colsum_scratch_of_current_device(int* rc) {
+  static std::mutex mu;
+  static float* ptr_of[64] = {};
+  *rc = LGK_OK;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("lgk_colsum_static: cudaGetDevice failed or device ordinal %d out of range: %s", dev, cudaGetErrorString(e));
+    *rc = LGK_ERR_LAUNCH;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr_of[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_colsum_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("lgk_colsum_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      *rc = LGK_ERR_LAUNCH;
+      return nullptr;
+    }
+    ptr_of[dev] = static_cast<float*>(p);
+  }
+  return ptr_of[dev];
+}
+
+extern "C" int lgk_colsum_static(const void* dy, float* db, int64_t n, int64_t m, int accumulate, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n >= 0 && m > 0, LGK_ERR_BAD_ARG, "lgk_colsum_static: bad sizes");
+  LGK_REQUIRE(m <= kStaticMaxM, LGK_ERR_UNSUPPORTED,
+              "lgk_colsum_static: m = %lld exceeds the built-in scratch (LGK_COLSUM_STATIC_MAX_M = %d columns); use "
+              "lgk_linear_bwd_w with a caller-provided workspace", (long long)m, kStaticMaxM);
+  LGK_REQUIRE(known_dtype(dtype), LGK_ERR_UNSUPPORTED, "lgk_colsum_static: dtype must be LGK_F32 or LGK_BF16");
+  LGK_REQUIRE(db, LGK_ERR_BAD_ARG, "lgk_colsum_static: null pointer");
+  const int slabs = n > 0 ? slab_count(n) : 0;   // <= kStaticMaxSlabs by construction
+  LGK_REQUIRE(slabs <= kStaticMaxSlabs, LGK_ERR_UNSUPPORTED, "lgk_colsum_static: %d slabs exceed the built-in scratch", slabs);
+  int rc = LGK_OK;
+  float* partial = colsum_scratch_of_current_device(&rc);
+  if (rc != LGK_OK) return rc;
+  if (n > 0) {
+    LGK_REQUIRE(dy, LGK_ERR_BAD_ARG, "lgk_colsum_static: null pointer");
+    const int64_t slab_rows = ceil_div(n, slabs);
+    if (dtype == LGK_BF16) colsum_slab_kernel<bf16><<<slabs, 256, 0, stream>>>(static_cast<const bf16*>(dy), partial, n, int(m), slab_rows);
+    else colsum_slab_kernel<float><<<slabs, 256, 0, stream>>>(static_cast<const float*>(dy), partial, n, int(m), slab_rows);
+    LGK_CHECK_LAUNCH("colsum_slab_kernel(static)");
+  }
+  // slabs = 0 (no rows): the second stage reads nothing and writes the empty sum (0, or db unchanged when accumulating)
+  slab_reduce_kernel<<<slab_reduce_grid(m), 256, 0, stream>>>(partial, nullptr, db, 0, m, slabs, accumulate);
+  LGK_CHECK_LAUNCH("slab_reduce_kernel(static)");
+  return LGK_OK;
+}
