@@ -823,7 +823,8 @@ def aggregation_stress(dev, peak: float, peak_src: str, graphs: int = 128) -> di
     att = torch.randn(H * C, device=dev) * 0.1
     a_s, a_d = ops.gat_alpha(x, att, att, H, C)
     gat_bytes = 4 * (2 * N * F + 4 * N * H) + 4 * E + 4 * (N + 1)
-    res["gat_softmax_aggregate_fwd"] = entry(_time_cuda(lambda: ops.gat_fwd(g.rowptr, g.col, x, a_s, a_d, None, H, C, 0.2, True), 20), gat_bytes)
+    res["gat_softmax_aggregate_fwd"] = entry(_time_cuda(lambda: ops.gat_fwd(g.rowptr, g.col, x, a_s, a_d, None, H, C, 0.2, True, quads=qc), 20), gat_bytes)
+    res["gat_softmax_aggregate_fwd_lgk_gat_fwd"] = entry(_time_cuda(lambda: ops.gat_fwd(g.rowptr, g.col, x, a_s, a_d, None, H, C, 0.2, True), 10), gat_bytes)
     pool_bytes = 4 * (N * F + graphs * F) + 4 * (graphs + 1)
     res["global_mean_pool_fwd"] = entry(_time_cuda(lambda: ops.pool_fwd(x, seg.ptr, True, True, False), 20), pool_bytes)
     res["global_mean_max_pool_fwd"] = entry(_time_cuda(lambda: ops.pool_fwd(x, seg.ptr, True, True, True), 20), pool_bytes + 8 * graphs * F)

@@ -281,6 +281,20 @@ LGK_API int lgk_sort_pool_fwd(const void* x, const int32_t* ptr, void* out, int3
 LGK_API int lgk_sort_pool_bwd(const void* dy, const int32_t* sel, void* dx,
                       int64_t num_nodes, int64_t num_graphs, int64_t feat, int64_t k, int dtype, void* stream);
 
+/* GATConv forward on the windowed, row-blocked structure (lgk_quad_build of the CSR) for large graphs: the same outputs as
+ * lgk_gat_fwd / lgk_gat_fwd_elu (out, optional ELU(out), rowmax, rowsum -- the statistics lgk_gat_bwd_* read), attention
+ * dropout 0 only, chan % 32 == 0 (a 128-byte feature slice then lies inside one head), fp32.  Source rows are staged once
+ * per CTA in a shared-memory ring by TMA together with their logit halves a_src[j, head]; four destination rows share one
+ * merged neighbour list; the soft-max is online at batch granularity (32 merged entries).  Summation order differs from
+ * lgk_gat_fwd (ascending source id over the merged list, self loop last): results agree to fp32 rounding, not bit for
+ * bit; deterministic run to run.  workspace: lgk_gat_blocked_workspace_bytes (the transposed a_src).          */
+LGK_API int64_t lgk_gat_blocked_workspace_bytes(int64_t n_rows, int heads);
+LGK_API int lgk_gat_fwd_blocked(const int32_t* ptr, const int32_t* qlen, const uint32_t* qent, const int32_t* cmin,
+                        const int32_t* cmax, const int32_t* qmeta, const void* h, const float* a_src, const float* a_dst,
+                        const float* bias, void* out, void* out_elu, float* rowmax, float* rowsum, int64_t n_rows,
+                        int heads, int chan, float negative_slope, int add_self_loops, void* workspace,
+                        int64_t workspace_bytes, int dtype, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * (5) node-feature transform (the torch_geometric Linear inside every conv: `lin`, `lin_l`, `lin_r`,
  *     `lin_rel`, `lin_root`, MLP.lins; reference models/gat.py:29,31,46, gin.py:21,23,25)

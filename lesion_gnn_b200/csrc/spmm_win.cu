@@ -38,6 +38,9 @@ constexpr int kBatch = 32;                       // merged entries staged per gr
 constexpr int kSmemMax = 232448;                 // 227 KB
 constexpr unsigned kColMask = 0x0FFFFFFFu;
 constexpr int kStageBytes = (kBatch / 2) * 64;   // staging area of a warp: [pair][4 groups][16 B]
+// GAT mode: an entry carries one soft-max weight per row of the quad: [entry][group]{address | mask, w0, w1, w2} + [entry][group]{w3}
+constexpr int kStageBytesGat = kBatch * 4 * 20;
+constexpr float kLog2e = 1.4426950408889634f;
 // A chunk whose source window (largest - smallest source id + 1) exceeds this many rows does not leave the 256-byte-slice
 // ring (~830 rows) room to run two chunks ahead; lgk_quad_build counts them (qmeta[1]) and the launch picks the slice
 // width from that count on the device.
@@ -129,8 +132,22 @@ __device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ void sts_u4(uint32_t addr, unsigned a, unsigned b, unsigned c, unsigned d) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 __device__ __forceinline__ void sts_u2(uint32_t addr, unsigned a, unsigned b) {
   asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
+// exp(d) for d <= 0 as one MUFU: ex2.approx(log2e * d); ex2.approx(-inf) = +0, ex2.approx(0) = 1 exactly, 2 ulp
+__device__ __forceinline__ float exp_neg(float d) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d * 1.4426950408889634f));
+  return r;
+}
+__device__ __forceinline__ float rcp_fast(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
 }
 // packed fp32x2 arithmetic (FFMA2 / FADD2): two lanes of a float4 per instruction, one issue slot
 __device__ __forceinline__ void fma2(float2& acc, const float2 v, const float2 w) {
@@ -164,6 +181,15 @@ struct WinArgs {
   int select;            // 1: run only if qmeta selects this slice width; 0: run unconditionally
   int64_t n_rows, n_quads, n_chunks;
   int feat, slices, nb;  // nb: ring blocks
+  // GAT mode (edge soft-max + aggregate; pre = a_src TRANSPOSED [heads][pre_stride], one head per 128-byte slice group)
+  const float* a_dst;    // transposed like pre: [heads][pre_stride]
+  float* rowmax;         // [n_rows, heads] soft-max statistics for the backward (may be NULL)
+  float* rowsum;
+  float* act_out;        // ELU(out) as a second output (may be NULL)
+  int heads, chan;
+  int64_t pre_stride;
+  float slope;
+  int add_self;
 };
 
 struct WinShared {
@@ -202,8 +228,12 @@ __device__ __forceinline__ void accumulate(float2 (&acc)[4][2], const float4 v, 
 // NW: consumer warps (+ 1 producer warp); 24 need the kernel to fit 80 registers.
 // SELF (LGK_SELF_*) and SCALE (mean or post-scale present) are compile-time: per quad the kernel spends as many
 // instructions on bookkeeping as on a third of its gathers (ncu, profiles/r02), so nothing optional stays in that path.
-template <bool HAS_PRE, int LPG, int NW, int SELF, bool SCALE>
+// GAT: edge soft-max + aggregation (lgk_gat_fwd_blocked): the staged factor of a source row is its attention logit half
+// a_src[j, head], every (entry, row) pair gets the weight exp(e - running max) -- online soft-max at batch granularity --
+// and the epilogue normalises, adds the GATConv self loop and writes the soft-max statistics.
+template <bool HAS_PRE, int LPG, int NW, int SELF, bool SCALE, bool GAT = false>
 __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArgs a, const __grid_constant__ CUtensorMap map_x) {
+  static_assert(!GAT || (HAS_PRE && LPG == 8 && SELF == LGK_SELF_NONE && !SCALE), "GAT mode: 128-byte slices, logit halves staged");
   constexpr int DBG = 0;
   constexpr int kConsumerWarps = NW;
   constexpr int kSliceBytes = LPG * 16;
@@ -223,10 +253,15 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
   const uint32_t ring = umma::smem_u32(smem_raw);
   float* ring_pre = reinterpret_cast<float*>(smem_raw + size_t(a.nb) * kBlkBytes);
   unsigned char* stage_raw = reinterpret_cast<unsigned char*>(ring_pre + (HAS_PRE ? a.nb * 32 : 0));
-  WinShared* sh = reinterpret_cast<WinShared*>(stage_raw + kConsumerWarps * kStageBytes);
+  constexpr int kStageW = GAT ? kStageBytesGat : kStageBytes;
+  WinShared* sh = reinterpret_cast<WinShared*>(stage_raw + kConsumerWarps * kStageW);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x % a.slices;
+  // GAT: a slice lies inside one head (chan % 32 == 0) and the staged factors are that head's row of the transposed logits
+  const int head = GAT ? (slice * (kSliceBytes / 4)) / a.chan : 0;
+  const float* pre_g = GAT ? a.pre + int64_t(head) * a.pre_stride : a.pre;
+  const float* adst_g = GAT ? a.a_dst + int64_t(head) * a.pre_stride : nullptr;  // GAT: a_dst transposed like a_src
   const int span = blockIdx.x / a.slices, spans = gridDim.x / a.slices;
   const int64_t n_units = (a.n_chunks + kSuper - 1) / kSuper;
   const int64_t c_begin = n_units * span / spans, c_end = n_units * (span + 1) / spans;  // in units
@@ -338,8 +373,8 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
         pre_bytes[0] = uint32_t(n1 * 4) & ~15u;
         pre_bytes[1] = uint32_t(n2 * 4) & ~15u;
         const int64_t tail0 = r_first + pre_bytes[0] / 4, tail1 = pre_row[1] + pre_bytes[1] / 4;
-        if (tail0 + lane < pre_row[1]) ring_pre[(tail0 + lane) % R] = __ldg(a.pre + tail0 + lane);
-        if (tail1 + lane < v_last) ring_pre[(tail1 + lane) % R] = __ldg(a.pre + tail1 + lane);
+        if (tail0 + lane < pre_row[1]) ring_pre[(tail0 + lane) % R] = __ldg(pre_g + tail0 + lane);
+        if (tail1 + lane < v_last) ring_pre[(tail1 + lane) % R] = __ldg(pre_g + tail1 + lane);
       }
       if (lane == 0) {
         sh->direct[s] = direct;
@@ -355,7 +390,7 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
           const int64_t R = int64_t(nb) * kBlkRows;
 #pragma unroll
           for (int k = 0; k < 2; ++k)
-            if (pre_bytes[k]) umma::bulk_g2s(ring_pre + pre_row[k] % R, a.pre + pre_row[k], pre_bytes[k], &sh->full[s]);
+            if (pre_bytes[k]) umma::bulk_g2s(ring_pre + pre_row[k] % R, pre_g + pre_row[k], pre_bytes[k], &sh->full[s]);
         }
         for (int b = load_from; b < load_from + nload; ++b)
           tma_box_2d(ring + uint32_t(b % nb) * kBlkBytes, &map_x, slice * (kSliceBytes / 4), b * kBlkRows, &sh->full[s]);
@@ -377,7 +412,8 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
   const unsigned F4 = unsigned(a.feat) >> 2;
   const unsigned vec = unsigned(slice) * LPG + gl;  // this lane's float4 column
   const bool lane_on = vec < F4;
-  const uint32_t stage_base = umma::smem_u32(stage_raw) + warp * kStageBytes + grp * 16;  // + pair * (GPW * 16)
+  const uint32_t stage_base = umma::smem_u32(stage_raw) + warp * kStageW + grp * 16;  // + pair * (GPW * 16)
+  const uint32_t stage_w3 = umma::smem_u32(stage_raw) + warp * kStageW + kBatch * GPW * 16 + grp * 4;  // GAT: + entry * (GPW * 4)
   const float4* xv = reinterpret_cast<const float4*>(a.x) + (lane_on ? vec : 0u);
   float4* ov = reinterpret_cast<float4*>(a.out) + vec;
   const uint32_t lane_off = uint32_t(gl) * 16;
@@ -451,6 +487,20 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
         if (SELF != LGK_SELF_NONE && has_selfw) cself[r] = __ldg(a.selfw + row);
       }
     }
+    // GAT: destination-side logit halves of the quad's rows, and the source-side ones of the rows themselves (self loop)
+    float adst[4], aself[4], mrow[4], lsum[4];
+    if (GAT) {
+      // both logit halves are stored transposed [head][row] (row stride a multiple of 4): one 16-byte load each per quad
+      const float4 d4 = (i < n_my && g < n_quads) ? __ldg(reinterpret_cast<const float4*>(adst_g + row0)) : f4_zero();
+      const float4 s4 = (a.add_self && i < n_my && g < n_quads) ? __ldg(reinterpret_cast<const float4*>(pre_g + row0)) : f4_zero();
+      adst[0] = d4.x; adst[1] = d4.y; adst[2] = d4.z; adst[3] = d4.w;
+      aself[0] = s4.x; aself[1] = s4.y; aself[2] = s4.z; aself[3] = s4.w;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        mrow[r] = -INFINITY;
+        lsum[r] = 0.f;
+      }
+    }
     win_wait(&sh->full[s], (i / kStages) & 1);
     const int direct = sh->direct[s];
     const int win_lo = sh->lo_blk[s] == INT_MAX ? INT_MAX : sh->lo_blk[s] * kBlkRows, win_hi = sh->hi_blk[s] * kBlkRows;
@@ -464,6 +514,100 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
 #pragma unroll
       for (int h = 0; h < EPL; ++h) { word[h] = w[h]; w[h] = w2[h]; }
       load_batch(start, b0 + 2 * kBatch < maxlen ? len : 0, b0 + 2 * kBatch, w2);  // two batches ahead
+      if constexpr (GAT) {
+        // Groups of a warp work independently here (their merged lists differ in length: a warp-wide batch count made every
+        // group pay the staging arithmetic of the longest one): group-masked shuffles and barriers, per-group entry count.
+        const unsigned gmask = (LPG == 32 ? 0xffffffffu : ((1u << LPG) - 1u)) << (grp * LPG);
+        const int cnt = min(kBatch, len - b0);
+        if (cnt > 0) {
+          // ---- GAT stage: logits of every (entry, member row), batch maximum per row, rescale, weights.  Logits and maxima
+          // are formed exactly as lgk_gat_fwd forms them (the stored row maximum is bit-identical); exp(d) = exp2(log2e * d).
+          float ev[EPL][4];
+          unsigned oo[EPL];
+          float bm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+          for (int h = 0; h < EPL; ++h) {
+            const unsigned col = word[h] & kColMask;
+            unsigned mask = word[h] >> 28;
+            if (a.add_self) {  // GATConv: stored self loops are removed (one is added in the epilogue)
+              const unsigned d = col - unsigned(row0);
+              if (d < 4u) mask &= ~(1u << d);
+            }
+            unsigned o;
+            float pj;
+            if (!direct) {
+              const unsigned blk = col / kBlkRows, slot = blk - __umulhi(blk, nb_magic) * unsigned(nb);
+              const unsigned rib = slot * kBlkRows + (col & (kBlkRows - 1));
+              o = ring + rib * kSliceBytes;
+              pj = ring_pre[rib];
+            } else {
+              o = col;
+              pj = __ldg(pre_g + col);
+            }
+            oo[h] = o | (mask << 28);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const float z = pj + adst[r];
+              ev[h][r] = (mask & (1u << r)) ? fmaxf(z, a.slope * z) : -INFINITY;  // leaky-relu, slope in [0, 1]
+              bm[r] = fmaxf(bm[r], ev[h][r]);
+            }
+          }
+          float msafe[4];
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+#pragma unroll
+            for (int o = 1; o < LPG; o <<= 1) bm[r] = fmaxf(bm[r], __shfl_xor_sync(gmask, bm[r], o));
+            // branch-free rescale: factor 1 when the maximum stands (exp_neg(0) = 1), 0 on the first members of the row
+            // (mrow = -inf: exp_neg(-inf) = 0); a row without any member so far (both -inf) keeps its zeros
+            const float m_new = fmaxf(mrow[r], bm[r]);
+            msafe[r] = m_new == -INFINITY ? 0.f : m_new;
+            const float sc = exp_neg(mrow[r] - msafe[r]);
+            acc[r][0].x *= sc; acc[r][0].y *= sc; acc[r][1].x *= sc; acc[r][1].y *= sc;
+            lsum[r] *= sc;
+            mrow[r] = m_new;
+          }
+#pragma unroll
+          for (int h = 0; h < EPL; ++h) {
+            float wv[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              wv[r] = exp_neg(ev[h][r] - msafe[r]);  // non-members hold -inf: weight +0
+              lsum[r] += wv[r];
+            }
+            const int ent = gl + LPG * h;
+            sts_u4(stage_base + ent * (GPW * 16), oo[h], __float_as_uint(wv[0]), __float_as_uint(wv[1]), __float_as_uint(wv[2]));
+            umma::sts_f32(stage_w3 + ent * (GPW * 4), wv[3]);
+          }
+          __syncwarp(gmask);
+          auto gat_entry = [&](const uint4 st, const float w3, const float4 v) {
+            const float2 lo = make_float2(v.x, v.y), hi = make_float2(v.z, v.w);
+            const float wr[4] = {__uint_as_float(st.y), __uint_as_float(st.z), __uint_as_float(st.w), w3};
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              if (st.x & (1u << (28 + r))) {
+                const float2 ww = make_float2(wr[r], wr[r]);
+                fma2(acc[r][0], lo, ww);
+                fma2(acc[r][1], hi, ww);
+              }
+            }
+          };
+          if (!direct) {
+#pragma unroll 4
+            for (int t = 0; t < cnt; ++t) {
+              const uint4 st = lds_u4(stage_base + t * (GPW * 16));
+              gat_entry(st, umma::lds_f32(stage_w3 + t * (GPW * 4)), lds_f4((st.x & kColMask) | lane_off));
+            }
+          } else {
+#pragma unroll 2
+            for (int t = 0; t < cnt; ++t) {
+              const uint4 st = lds_u4(stage_base + t * (GPW * 16));
+              gat_entry(st, umma::lds_f32(stage_w3 + t * (GPW * 4)), __ldg(xv + (st.x & kColMask) * F4));
+            }
+          }
+          __syncwarp(gmask);
+        }
+        continue;
+      }
       // ---- stage: every lane resolves its entries (ring address | mask, weight) ----
 #pragma unroll
       for (int h = 0; h < EPL; ++h) {
@@ -477,7 +621,7 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
           if (HAS_PRE) wt = ring_pre[rib];
         } else {
           o = col;
-          if (HAS_PRE) wt = __ldg(a.pre + col);
+          if (HAS_PRE) wt = __ldg(pre_g + col);
         }
         // pair p = entry / 2, half = entry & 1: [pair][group][half] -> one 16-byte read serves two entries
         const int ent = gl + LPG * h;
@@ -534,6 +678,55 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
 
     // ---- epilogue: self term, mean / post scale, bias, store ----
     const int rows_here = n_rows - row0;  // >= 4 everywhere but in the last quad of the array (<= 0: no quad)
+    if constexpr (GAT) {
+      const bool stats_lane = gl == 0 && (unsigned(slice) * (kSliceBytes / 4)) % unsigned(a.chan) == 0 && a.rowmax != nullptr;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        float ssum = lsum[r];
+#pragma unroll
+        for (int o = 1; o < LPG; o <<= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, o);
+        float4 res = make_float4(acc[r][0].x, acc[r][0].y, acc[r][1].x, acc[r][1].y);
+        float m = mrow[r];
+        const unsigned row = unsigned(row0 + r);
+        const unsigned ro = row * F4;
+        if (a.add_self) {  // exactly one (i, i) entry
+          const float z = aself[r] + adst[r];
+          const float es = fmaxf(z, a.slope * z);
+          const float m_new = fmaxf(m, es);  // finite
+          const float sc = exp_neg(m - m_new);  // m = -inf (no other entry): 0
+          const float ws = exp_neg(es - m_new);
+          float4 xs = f4_zero();
+          if (int(row) >= win_lo && int(row) < win_hi) {
+            const unsigned blk = row / kBlkRows, slot = blk - __umulhi(blk, nb_magic) * unsigned(nb);
+            xs = lds_f4((ring + (slot * kBlkRows + (row & (kBlkRows - 1))) * kSliceBytes) | lane_off);
+          } else if (r < rows_here) {
+            xs = __ldg(xv + ro);
+          }
+          res.x = fmaf(res.x, sc, ws * xs.x); res.y = fmaf(res.y, sc, ws * xs.y);
+          res.z = fmaf(res.z, sc, ws * xs.z); res.w = fmaf(res.w, sc, ws * xs.w);
+          ssum = fmaf(ssum, sc, ws);
+          m = m_new;
+        }
+        const float inv = rcp_fast(ssum + 1e-16f);
+        res.x = fmaf(res.x, inv, bias4.x); res.y = fmaf(res.y, inv, bias4.y);
+        res.z = fmaf(res.z, inv, bias4.z); res.w = fmaf(res.w, inv, bias4.w);
+        if (lane_on && r < rows_here) {
+          st_stream_f4(ov + ro, res);
+          if (a.act_out) {
+            res.x = elu1(res.x); res.y = elu1(res.y); res.z = elu1(res.z); res.w = elu1(res.w);
+            st_stream_f4(reinterpret_cast<float4*>(a.act_out) + vec + ro, res);
+          }
+          // the first slice of a head records the soft-max statistics (all slices of a head compute the same ones)
+          if (stats_lane) {
+            a.rowmax[row * unsigned(a.heads) + unsigned(head)] = m;
+            a.rowsum[row * unsigned(a.heads) + unsigned(head)] = ssum;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) umma::mbar_arrive(&sh->empty[s]);
+      continue;
+    }
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
       float4 res = make_float4(acc[r][0].x, acc[r][0].y, acc[r][1].x, acc[r][1].y);
@@ -543,7 +736,7 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
         if (SELF == LGK_SELF_REPLACE) c -= float((selfcnt >> (8 * r)) & 0xffu);
         if (c != 0.f && r < rows_here) {
           const int row = row0 + r;
-          if (HAS_PRE) c *= __ldg(a.pre + row);
+          if (HAS_PRE) c *= __ldg(pre_g + row);
           float4 xs;
           if (row >= win_lo && row < win_hi) {  // the row itself is part of the unit's window: it is in the ring
             const unsigned blk = unsigned(row) / kBlkRows, slot = blk - __umulhi(blk, nb_magic) * unsigned(nb);
@@ -657,6 +850,49 @@ int launch_win(WinArgs a, int select, int dbg, cudaStream_t stream) {
   return LGK_OK;
 }
 
+// a_src [n, heads] -> [heads][stride] (stride = n rounded up to 4: every head's row starts 16-byte aligned for the bulk copies)
+__global__ void __launch_bounds__(256) transpose_heads_kernel(const float* __restrict__ in, const float* __restrict__ in2,
+                                                              float* __restrict__ out, float* __restrict__ out2, int64_t n, int heads,
+                                                              int64_t stride) {
+  const int64_t i = int64_t(blockIdx.x) * 256 + threadIdx.x;
+  if (i >= stride) return;
+  for (int h = 0; h < heads; ++h) {  // the padding rows [n, stride) read as zeros (they belong to no stored row)
+    out[int64_t(h) * stride + i] = i < n ? __ldg(in + i * heads + h) : 0.f;
+    out2[int64_t(h) * stride + i] = i < n ? __ldg(in2 + i * heads + h) : 0.f;
+  }
+}
+
+int launch_win_gat(WinArgs a, cudaStream_t stream) {
+  constexpr int warps = 16;
+  a.select = 0;
+  a.slices = int(ceil_div(int64_t(a.feat) * 4, 128));
+  const int fixed = warps * kStageBytesGat + int(sizeof(WinShared)) + 128;
+  const int per_blk = kBlkBytes + 32 * 4;
+  static const int nb_cap = env_int_win("LGK_WIN_BLOCKS", 1 << 30);
+  a.nb = std::min((kSmemMax - fixed) / per_blk, nb_cap);
+  LGK_REQUIRE(a.nb >= 2, LGK_ERR_UNSUPPORTED, "lgk_gat_fwd_blocked: no room for the ring");
+  const int smem = a.nb * per_blk + fixed;
+  CUtensorMap map_x;
+  LGK_REQUIRE(make_row_map(&map_x, a.x, a.n_rows, a.feat, 128), LGK_ERR_UNSUPPORTED, "lgk_gat_fwd_blocked: cannot encode the tensor map");
+  const int spans = int(std::max<int64_t>(1, std::min<int64_t>(kNumSMs / std::max(1, std::min(a.slices, kNumSMs)), a.n_chunks)));
+  const unsigned grid = unsigned(spans * a.slices);
+  WinKernel kern = spmm_win_kernel<true, 8, warps, LGK_SELF_NONE, false, true>;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  static bool configured[64] = {};
+  if (!configured[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax);
+    if (e != cudaSuccess) {
+      set_error("spmm_win_kernel(gat): cannot reserve %d bytes of shared memory: %s", kSmemMax, cudaGetErrorString(e));
+      return LGK_ERR_LAUNCH;
+    }
+    configured[dev & 63] = true;
+  }
+  kern<<<grid, 32 * (warps + 1), smem, stream>>>(a, map_x);
+  LGK_CHECK_LAUNCH("spmm_win_kernel(gat)");
+  return LGK_OK;
+}
+
 }  // namespace
 }  // namespace lgk
 
@@ -729,4 +965,54 @@ extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const u
     return launch_win<8>(a, 1, dbg, stream);
   }
   return launch_win<8>(a, 0, dbg, stream);
+}
+
+extern "C" int64_t lgk_gat_blocked_workspace_bytes(int64_t n_rows, int heads) {
+  if (n_rows <= 0 || heads <= 0) return 0;
+  return 2 * int64_t(heads) * ((n_rows + 3) / 4 * 4) * 4;  // a_src and a_dst, transposed
+}
+
+extern "C" int lgk_gat_fwd_blocked(const int32_t* ptr, const int32_t* qlen, const uint32_t* qent, const int32_t* cmin,
+                                   const int32_t* cmax, const int32_t* qmeta, const void* h, const float* a_src, const float* a_dst,
+                                   const float* bias, void* out, void* out_elu, float* rowmax, float* rowsum, int64_t n_rows,
+                                   int heads, int chan, float negative_slope, int add_self_loops, void* workspace,
+                                   int64_t workspace_bytes, int dtype, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LGK_REQUIRE(n_rows >= 0 && heads > 0 && chan > 0, LGK_ERR_BAD_ARG, "lgk_gat_fwd_blocked: bad sizes");
+  if (n_rows == 0) return LGK_OK;
+  LGK_REQUIRE(ptr && qlen && qent && cmin && cmax && qmeta && h && a_src && a_dst && out, LGK_ERR_BAD_ARG,
+              "lgk_gat_fwd_blocked: null pointer");
+  LGK_REQUIRE(dtype == LGK_F32, LGK_ERR_UNSUPPORTED, "lgk_gat_fwd_blocked: fp32 features only");
+  LGK_REQUIRE(chan % 32 == 0, LGK_ERR_UNSUPPORTED, "lgk_gat_fwd_blocked: channels per head must be a multiple of 32 (a 128-byte slice lies in one head)");
+  const int64_t feat = int64_t(heads) * chan;
+  LGK_REQUIRE(feat < (1 << 20), LGK_ERR_UNSUPPORTED, "lgk_gat_fwd_blocked: heads * chan too large");
+  LGK_REQUIRE(n_rows <= int64_t(kColMask), LGK_ERR_UNSUPPORTED, "lgk_gat_fwd_blocked: more than 2^28 - 1 rows");
+  LGK_REQUIRE(n_rows * (feat / 4) < (int64_t(1) << 31) && n_rows * heads < (int64_t(1) << 31), LGK_ERR_UNSUPPORTED,
+              "lgk_gat_fwd_blocked: n_rows * feat / 4 must be below 2^31");
+  LGK_REQUIRE(((reinterpret_cast<uintptr_t>(h) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(bias) |
+                reinterpret_cast<uintptr_t>(out_elu) | reinterpret_cast<uintptr_t>(workspace)) & 15) == 0,
+              LGK_ERR_BAD_ARG, "lgk_gat_fwd_blocked: h, out, out_elu, bias and workspace must be 16-byte aligned");
+  LGK_REQUIRE(h != out, LGK_ERR_BAD_ARG, "lgk_gat_fwd_blocked: in-place aggregation is not possible");
+  const int64_t need = lgk_gat_blocked_workspace_bytes(n_rows, heads);
+  LGK_REQUIRE(workspace && workspace_bytes >= need, LGK_ERR_WORKSPACE, "lgk_gat_fwd_blocked: workspace %lld < %lld bytes",
+              (long long)workspace_bytes, (long long)need);
+  const int64_t stride = (n_rows + 3) / 4 * 4;
+  float* a_src_t = static_cast<float*>(workspace);
+  float* a_dst_t = a_src_t + int64_t(heads) * stride;
+  transpose_heads_kernel<<<unsigned(ceil_div(stride, 256)), 256, 0, stream>>>(a_src, a_dst, a_src_t, a_dst_t, n_rows, heads, stride);
+  LGK_CHECK_LAUNCH("transpose_heads_kernel");
+  WinArgs a{};
+  a.ptr = ptr; a.qlen = qlen; a.qent = qent; a.cmin = cmin; a.cmax = cmax; a.qmeta = qmeta;
+  a.pre = a_src_t; a.pre_stride = stride; a.a_dst = a_dst_t; a.bias = bias;
+  a.x = static_cast<const float*>(h);
+  a.out = static_cast<float*>(out);
+  a.act_out = static_cast<float*>(out_elu);
+  a.rowmax = rowmax; a.rowsum = rowsum;
+  a.heads = heads; a.chan = chan; a.slope = negative_slope; a.add_self = add_self_loops;
+  a.self_mode = LGK_SELF_NONE;
+  a.n_rows = n_rows;
+  a.n_quads = ceil_div(n_rows, 4);
+  a.n_chunks = ceil_div(a.n_quads, kQuadsPerChunk);
+  a.feat = int(feat);
+  return launch_win_gat(a, stream);
 }

@@ -183,7 +183,8 @@ class _GatAttention(torch.autograd.Function):
         # alpha: (a_src, a_dst) already formed by the transform's epilogue (linear_gat)
         a_src, a_dst = alpha if alpha is not None else ops.gat_alpha(h, a_s, a_d, heads, chan)
         res = ops.gat_fwd(g.rowptr, g.col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p,
-                          seed, with_elu=fused_elu, seed_dev=seed_dev)
+                          seed, with_elu=fused_elu, seed_dev=seed_dev,
+                          quads=g.quads("csr") if ops.gat_blocked_eligible(h, chan, dropout_p) else None)
         ctx.seed_dev = seed_dev
         out, rowmax, rowsum = res[:3]
         y = res[3] if fused_elu else h.new_empty(0)

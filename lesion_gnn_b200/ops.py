@@ -252,14 +252,30 @@ def gat_alpha(h: Tensor, att_src: Tensor, att_dst: Tensor, heads: int, chan: int
     return a_src, a_dst
 
 
+def gat_blocked_eligible(h: Tensor, chan: int, dropout_p: float) -> bool:
+    """the windowed GAT forward takes over on large graphs: fp32, no attention dropout, a 128-byte slice inside one head"""
+    return (h.dtype == torch.float32 and dropout_p == 0.0 and chan % 32 == 0 and h.numel() >= _WIN_MIN_ELEMS
+            and h.size(0) < (1 << 28) and h.numel() // 4 < (1 << 31))
+
+
 def gat_fwd(rowptr, col, h, a_src, a_dst, bias, heads, chan, negative_slope, add_self_loops, dropout_p=0.0, seed=0,
-            with_elu=False, seed_dev: Optional[Tensor] = None):
-    """-> out, rowmax, rowsum [, elu(out)].  seed_dev: int64 device counter mixed into the dropout seed at run time"""
+            with_elu=False, seed_dev: Optional[Tensor] = None, quads: Optional[Quads] = None):
+    """-> out, rowmax, rowsum [, elu(out)].  seed_dev: int64 device counter mixed into the dropout seed at run time.
+    quads: the row-blocked form of (rowptr, col); when given and gat_blocked_eligible, lgk_gat_fwd_blocked runs (same result
+    up to fp32 summation order)"""
     L = _lib.lib()
     n = h.size(0)
     out = torch.empty_like(h)
     rowmax = torch.empty(n, heads, dtype=torch.float32, device=h.device)
     rowsum = torch.empty_like(rowmax)
+    if quads is not None and gat_blocked_eligible(h, chan, dropout_p):
+        y = torch.empty_like(h) if with_elu else None
+        ws = _ws(L.query("lgk_gat_blocked_workspace_bytes", n, heads), h.device)
+        L.call("lgk_gat_fwd_blocked", _chk(rowptr, torch.int32), _chk(quads.qlen, torch.int32), _chk(quads.qent), _chk(quads.cmin, torch.int32),
+               _chk(quads.cmax, torch.int32), _chk(quads.qmeta, torch.int32), _chk(h, torch.float32, "h"), _chk(a_src, torch.float32),
+               _chk(a_dst, torch.float32), _chk(bias, torch.float32, "bias"), _chk(out), _chk(y), _chk(rowmax), _chk(rowsum), n,
+               heads, chan, float(negative_slope), int(add_self_loops), ws.data_ptr(), ws.numel(), F32, _stream())
+        return (out, rowmax, rowsum, y) if with_elu else (out, rowmax, rowsum)
     if with_elu:
         y = torch.empty_like(h)
         L.call("lgk_gat_fwd_elu", _chk(rowptr, torch.int32), _chk(col, torch.int32), _chk(h, None, "h"), _chk(a_src, torch.float32),

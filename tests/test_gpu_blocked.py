@@ -200,3 +200,71 @@ def test_blocked_kernel_is_selected_by_size(dev, monkeypatch):
     monkeypatch.setattr(ops, "_WIN_MIN_ELEMS", 0)
     F.aggregate(x, g, "sum")
     assert "lgk_spmm_blocked" in calls and "lgk_spmm" not in calls
+
+
+@pytest.mark.parametrize("heads,chan", [(1, 32), (4, 32), (2, 64), (3, 96)])
+@pytest.mark.parametrize("add_self_loops", [True, False])
+@pytest.mark.parametrize("name", sorted(GRAPHS) + ["knn_batch"])
+def test_blocked_gat_forward(dev, name, heads, chan, add_self_loops):
+    """lgk_gat_fwd_blocked (edge soft-max + aggregation on the windowed, row-blocked structure) against the fp64 oracle's
+    GATConv and against lgk_gat_fwd: output, fused ELU output and the soft-max statistics the backward reads -- on every
+    producer path (windowed, gaps, backward jumps, global-gather chunks), multigraph duplicates, stored self loops, rows
+    without in-edges"""
+    from lesion_gnn_b200 import ops
+    ei, n = _knn_batch_graph(13) if name == "knn_batch" else GRAPHS[name]()
+    fin = 12
+    gen = torch.Generator().manual_seed(heads * chan + n)
+    x = torch.randn(n, fin, generator=gen, dtype=torch.float64)
+    torch.manual_seed(3)
+    ref = O.GATConv(fin, chan, heads=heads, add_self_loops=add_self_loops).double()
+    ref.bias.data.normal_()
+    ref.att_src.data.mul_(3.0)  # logits of a few units: the soft-max is far from uniform
+    ref.att_dst.data.mul_(3.0)
+    want = ref(x, ei)
+    g = _graph(ei, n, dev)
+    w = ref.lin.weight.detach().float().to(dev)
+    h = ops.linear_fwd(x.float().to(dev), w)
+    a_s, a_d = ops.gat_alpha(h, ref.att_src.detach().float().reshape(-1).to(dev), ref.att_dst.detach().float().reshape(-1).to(dev), heads, chan)
+    bias = ref.bias.detach().float().to(dev)
+    base = ops.gat_fwd(g.rowptr, g.col, h, a_s, a_d, bias, heads, chan, 0.2, add_self_loops, with_elu=True)
+    q = g.quads("csr")
+    ops.reset_launch_count()
+    got = ops.gat_fwd(g.rowptr, g.col, h, a_s, a_d, bias, heads, chan, 0.2, add_self_loops, with_elu=True, quads=q)
+    assert ops.launch_count() == 2  # the transpose of a_src and the windowed kernel: the blocked path really ran
+    assert_close(got[0], want, TOL_F32, "out vs oracle")
+    assert_close(got[0], base[0], TOL_F32, "out vs lgk_gat_fwd")
+    assert_close(got[3], torch.nn.functional.elu(want), TOL_F32, "elu(out) vs oracle")
+    # statistics: rows with at least one entry (others hold -inf / 0 in both kernels)
+    live = torch.isfinite(base[1])
+    assert torch.equal(torch.isfinite(got[1]), live)
+    assert torch.equal(got[1][live], base[1][live]), "the row maximum is exact in any order"
+    assert_close(got[2], base[2], TOL_F32, "rowsum")
+    again = ops.gat_fwd(g.rowptr, g.col, h, a_s, a_d, bias, heads, chan, 0.2, add_self_loops, with_elu=True, quads=g.quads("csr"))
+    assert all(torch.equal(a, b) for a, b in zip(got, again)), "deterministic run to run"
+
+
+def test_blocked_gat_through_the_layer_backward(dev):
+    """GATConv with the blocked forward (forced by the size threshold) and the ordinary backward kernels, which read the
+    blocked kernel's statistics: output and all gradients against the fp64 oracle"""
+    import lesion_gnn_b200 as lg
+    ei, n = _knn_batch_graph(14)
+    x = torch.randn(n, 20, generator=torch.Generator().manual_seed(1), dtype=torch.float64)
+    torch.manual_seed(4)
+    ref = O.GATConv(20, 32, heads=2).double()
+    ref.bias.data.normal_()
+    mod = lg.nn.GATConv(20, 32, heads=2)
+    mod.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    mod = mod.to(dev)
+    xr = x.clone().requires_grad_(True)
+    want = ref(xr, ei)
+    dy = torch.randn(want.shape, generator=torch.Generator().manual_seed(2), dtype=torch.float64)
+    want.backward(dy)
+    xg = x.float().to(dev).requires_grad_(True)
+    from lesion_gnn_b200 import ops
+    ops.reset_launch_count()
+    got = mod(xg, ei.to(dev))
+    got.backward(dy.float().to(dev))
+    assert_close(got, want, TOL_F32, "out")
+    assert_close(xg.grad, xr.grad, TOL_F32, "dx")
+    for (k, p), (_, pr) in zip(mod.named_parameters(), ref.named_parameters()):
+        assert_close(p.grad.view_as(pr.grad), pr.grad, TOL_F32, "d" + k)
