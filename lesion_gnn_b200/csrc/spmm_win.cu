@@ -144,6 +144,11 @@ __device__ __forceinline__ float exp_neg(float d) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d * 1.4426950408889634f));
   return r;
 }
+__device__ __forceinline__ float ex2_fast(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 __device__ __forceinline__ float rcp_fast(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -567,11 +572,16 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
             mrow[r] = m_new;
           }
 #pragma unroll
+          for (int r = 0; r < 4; ++r) msafe[r] *= -kLog2e;
+#pragma unroll
           for (int h = 0; h < EPL; ++h) {
             float wv[4];
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-              wv[r] = exp_neg(ev[h][r] - msafe[r]);  // non-members hold -inf: weight +0
+              // exp(e - m) = ex2(e log2e - m log2e), one FFMA + one MUFU; non-members hold -inf: weight +0.  The rounding of
+              // m log2e is a factor common to the row's weights: it cancels in out = acc / sum and moves the stored sum by
+              // |m| 6e-8 relative
+              wv[r] = ex2_fast(fmaf(ev[h][r], kLog2e, msafe[r]));
               lsum[r] += wv[r];
             }
             const int ent = gl + LPG * h;
