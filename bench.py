@@ -100,7 +100,7 @@ def graphs_per_rank(spec: dict, world: int, scaling: str) -> int:
     return spec["graphs"] if scaling == "weak" else max(1, spec["graphs"] // world)
 
 
-def make_host_batches(spec: dict, graphs: int, rank: int, count: int, with_edges_on=None):
+def make_host_batches(spec: dict, graphs: int, rank: int, count: int, with_edges_on=None, world: int = 1):
     """`count` distinct synthetic batches for this rank; kNN edges are built on `with_edges_on` (a CUDA device,
     lgk_knn_graph) or by the oracle on the CPU (reference arm) -- for `value` and `e2e` graph construction is outside
     the timed step, as in the reference where it happens in the DataLoader (datasets/datamodule.py:43-48); the
@@ -108,7 +108,15 @@ def make_host_batches(spec: dict, graphs: int, rank: int, count: int, with_edges
     from lesion_gnn_b200 import data
     out = []
     for i in range(count):
-        hb = data.synth_batch(graphs, spec["nodes"], spec["feat"], seed=data.SEED + 1000 * rank + i, layout=spec["layout"],
+        nodes, n_graphs = spec["nodes"], graphs
+        if world > 1:
+            # data parallel: ONE global batch of graphs x world graphs, split over the ranks by node count (data.shard_counts:
+            # contiguous ranges of graphs, long-tailed sizes) -- every rank derives the same sizes from the shared seed and
+            # generates only its own shard
+            sizes = data.node_counts(graphs * world, spec["nodes"], torch.Generator().manual_seed(data.SEED + 7919 * (i + 1)))
+            lo, hi = data.shard_counts(sizes, world)[rank]
+            nodes, n_graphs = sizes[lo:hi], hi - lo
+        hb = data.synth_batch(n_graphs, nodes, spec["feat"], seed=data.SEED + 1000 * rank + i, layout=spec["layout"],
                               num_classes=5)
         if with_edges_on is not None:
             from lesion_gnn_b200 import transforms
@@ -419,7 +427,7 @@ def run_b200(args):
         return model, opt, train.TrainStep(model, opt, spec["loss"], 5, use_cuda_graph=True, process_group=None, world_size=world)
 
     model, opt, step = make_step()
-    host = [hb.pin() for hb in make_host_batches(spec, graphs, rank, POOL, with_edges_on=dev)]
+    host = [hb.pin() for hb in make_host_batches(spec, graphs, rank, POOL, with_edges_on=dev, world=world)]
     devb = [train.DeviceBatch(hb, dev) for hb in host]
     for hb, db in zip(host, devb):
         db.copy_from(hb)
@@ -530,6 +538,8 @@ def run_b200(args):
                        "knn_k": spec["k"], "loss": spec["loss"], "optimizer": "Adam", "dropout": spec["dropout"],
                        "weight_decay": spec["weight_decay"], "train_mode": True,
                        "parallelism": f"dp{world}", "cuda_graph": True, "l2_policy": l2_policy,
+                       "sharding": ("one global batch of graphs_per_gpu x n_gpus graphs per step, split over the ranks in contiguous "
+                                    "ranges balanced by node count (data.shard_counts); graphs_per_gpu is the mean" if world > 1 else "none"),
                        "setup": f"{POOL} graph captures before the {args.warmup} warm-up steps (training state restored)"},
             "e2e": {"value": round(total_graphs * args.steps / (e2e_ms_total * 1e-3), 1), "unit": "graphs/s",
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "ms_per_step": round(e2e_ms, 4),

@@ -119,6 +119,10 @@ def node_counts(num_graphs: int, spec, gen: torch.Generator) -> list:
     reference's DDR lesion graphs (notebooks/viz.ipynb cells 4-6); node 0 of each graph is the background."""
     if isinstance(spec, int):
         return [spec] * num_graphs
+    if isinstance(spec, (list, tuple)):  # explicit sizes (a rank's shard of a global batch)
+        if len(spec) != num_graphs:
+            raise ValueError("one node count per graph")
+        return [int(n) for n in spec]
     if spec == "ddr":
         z = torch.randn(num_graphs, generator=gen, dtype=torch.float64)
         n = torch.exp(math.log(30.0) + 0.9 * z).ceil().clamp(1, 600).long()
