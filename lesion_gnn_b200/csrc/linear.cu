@@ -14,6 +14,7 @@
 // 128 x 64 output tile, 16-deep r tile, 256 threads, 8 x 4 micro-tile, register-prefetch double buffering.
 #include "common.cuh"
 
+#include <cooperative_groups.h>
 #include <stdlib.h>
 
 namespace lgk {
@@ -478,6 +479,118 @@ __global__ void __launch_bounds__(256) bwd_w_slab_pipe_kernel(const float* __res
   }
 }
 
+// ---- small-weight gradient (k, m <= 64) in ONE launch: slab partials reduced through distributed shared memory ------
+// r01/r02's two-launch form (bwd_w_slab_kernel + slab_reduce_kernel) wrote ~180 partials of 16.6 KB and read them back in a
+// second launch: 1.48x the algorithmic DRAM traffic and two graph nodes per weight.  Here 8 consecutive slabs form a
+// thread-block CLUSTER: every CTA leaves its partial in its own shared memory, the cluster's CTAs add the eight partials
+// through DSMEM (CTA r owns every 8th block of 256 outputs, ranks added in rank order) and write ONE partial per cluster; the
+// cluster that finishes last (device-scope counter) adds the ~23 cluster partials in cluster order into dW / db.  Fixed
+// summation tree: deterministic.  fp32, any alignment (the VEC flag only selects the load width).
+constexpr int kDwCluster = 8;
+template <bool VEC>
+__global__ void __cluster_dims__(kDwCluster, 1, 1) __launch_bounds__(256)
+    bwd_w_cluster_kernel(const float* __restrict__ dy, const float* __restrict__ x, float* __restrict__ cpartial,
+                         unsigned* __restrict__ counter, float* __restrict__ dw, float* __restrict__ db, int64_t N, int K, int M,
+                         int64_t slab_rows, int want_db, int accumulate) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  __shared__ __align__(16) float xs[kSlabChunk * 64];
+  __shared__ __align__(16) float ds[kSlabChunk * 64];
+  __shared__ float part[64 * 64 + 64];
+  __shared__ int is_last;
+  const int tk = threadIdx.x >> 4, tm = threadIdx.x & 15;
+  const int64_t r0 = int64_t(blockIdx.x) * slab_rows;
+  const int64_t r1 = min(N, r0 + slab_rows);
+  float acc[4][4], dbs[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    dbs[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  }
+  for (int64_t c0 = r0; c0 < r1; c0 += kSlabChunk) {
+    const int rows = (r1 - c0 < kSlabChunk) ? int(r1 - c0) : kSlabChunk;
+    __syncthreads();
+    if (VEC) {
+      for (int e = threadIdx.x; e < kSlabChunk * 16; e += 256) {
+        const int r = e >> 4, c = (e & 15) * 4;
+        reinterpret_cast<float4*>(xs)[e] = (r < rows && c < K) ? __ldg(reinterpret_cast<const float4*>(x + (c0 + r) * K + c)) : f4_zero();
+        reinterpret_cast<float4*>(ds)[e] = (r < rows && c < M) ? __ldg(reinterpret_cast<const float4*>(dy + (c0 + r) * M + c)) : f4_zero();
+      }
+    } else {
+      for (int e = threadIdx.x; e < kSlabChunk * 64; e += 256) {
+        const int r = e >> 6, c = e & 63;
+        xs[e] = (r < rows && c < K) ? __ldg(x + (c0 + r) * K + c) : 0.f;
+        ds[e] = (r < rows && c < M) ? __ldg(dy + (c0 + r) * M + c) : 0.f;
+      }
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int r = 0; r < kSlabChunk; ++r) {
+      const float4 a4 = *reinterpret_cast<const float4*>(xs + r * 64 + tk * 4);
+      const float4 b4 = *reinterpret_cast<const float4*>(ds + r * 64 + tm * 4);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+      if (tk == 0) { dbs[0] += b4.x; dbs[1] += b4.y; dbs[2] += b4.z; dbs[3] += b4.w; }
+    }
+  }
+  // own partial, in the outputs' own layout: dW[mi * K + ki], then db[mi]
+  const int total = K * M + (want_db ? M : 0);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int mi = tm * 4 + j;
+    if (mi >= M) continue;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ki = tk * 4 + i;
+      if (ki < K) part[mi * K + ki] = acc[i][j];
+    }
+    if (want_db && tk == 0) part[K * M + mi] = dbs[j];
+  }
+  cluster.sync();
+  const unsigned rank = cluster.block_rank();
+  const int cid = blockIdx.x / kDwCluster, nclusters = gridDim.x / kDwCluster;
+  const float* peer[kDwCluster];
+#pragma unroll
+  for (int c = 0; c < kDwCluster; ++c) peer[c] = cluster.map_shared_rank(part, c);
+  for (int o = int(rank) * 256 + threadIdx.x; o < total; o += kDwCluster * 256) {
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < kDwCluster; ++c) sum += peer[c][o];
+    if (nclusters > 1) {
+      cpartial[int64_t(cid) * total + o] = sum;
+    } else {
+      float* dst = o < K * M ? dw + o : db + (o - K * M);
+      *dst = accumulate ? *dst + sum : sum;
+    }
+  }
+  if (nclusters == 1) {
+    cluster.sync();  // nobody leaves while a peer still reads its shared memory
+    return;
+  }
+  __threadfence();
+  cluster.sync();    // the cluster's partial is complete (and fenced), all remote reads are done
+  if (rank == 0 && threadIdx.x == 0) {
+    const unsigned ticket = atomicAdd(counter, 1u);
+    const int last = ticket == unsigned(nclusters - 1);
+    if (last) *counter = 0u;  // ready for the next call on this workspace
+#pragma unroll
+    for (int c = 0; c < kDwCluster; ++c) *cluster.map_shared_rank(&is_last, c) = last;
+  }
+  cluster.sync();
+  if (!is_last) return;
+  __threadfence();
+  for (int o = int(rank) * 256 + threadIdx.x; o < total; o += kDwCluster * 256) {
+    float sum = 0.f;
+    for (int c = 0; c < nclusters; ++c) sum += __ldcg(cpartial + int64_t(c) * total + o);  // cluster order
+    float* dst = o < K * M ? dw + o : db + (o - K * M);
+    *dst = accumulate ? *dst + sum : sum;
+  }
+}
+
 // db[m] = sum_n dy[n,m] alone (bias gradients of the fused aggregation kernels): slab partials, same second stage.
 // Threads = (row lane, float4 column); M % 4 == 0 fast path, scalar otherwise.
 template <typename T>
@@ -649,7 +762,7 @@ extern "C" int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, i
 extern "C" int64_t lgk_linear_bwd_w_workspace_bytes(int64_t n, int64_t k, int64_t m) {
   if (n <= 0 || k <= 0 || m <= 0) return 0;
   const int64_t slabs = slab_count(n);
-  if (small_weight(k, m)) return align_up(slabs * (k * m + m) * 4, 256);
+  if (small_weight(k, m)) return align_up(slabs * (k * m + m) * 4, 256) + 256;  // + the cluster kernel's counter
   const int s = std::max(choose_wsplits(n, k, m), grad_w_tc_slabs(n, k, m, nullptr));
   return align_up(int64_t(s) * (k * m + m) * 4, 256) + align_up(slabs * m * 4, 256);
 }
@@ -705,6 +818,24 @@ extern "C" int lgk_linear_bwd_w(const void* dy, const void* x, float* dw, float*
       else bwd_w_slab_kernel<KB, MB, false, float><<<slabs, 256, smem, stream>>>(dyf, xf, partial, n, int(k), int(m), slab_rows, wdb);    \
     }                                                                                                                                 \
   } while (0)
+    // k, m <= 64, fp32, not too tall: one cluster-reduced launch -- OPT-IN (LGK_DW_CLUSTER=1).  Measured on the headline step
+    // (B200, 300 steps, A/B/A/B on one box): two-launch form 0.3219-0.3248 ms per step, 21.1 us per call; cluster form
+    // 0.3526-0.3527 ms, 22.4 us per call, 49 instead of 53 launches.  The call itself is no faster (three cluster barriers
+    // and the DSMEM pass cost what the second launch cost) and the step is 30 us SLOWER: a cluster of 8 CTAs needs 8 free
+    // SMs of one GPC at the same moment, so these side-stream kernels no longer slip into the gaps of the main chain.
+    static const bool cluster_on = [] { const char* v = getenv("LGK_DW_CLUSTER"); return v && *v == '1'; }();
+    if (cluster_on && kb == 1 && mb == 1 && !is_bf16 && n < 65536) {
+      const int cslabs = int(align_up(slabs, kDwCluster));
+      const int64_t crows = ceil_div(n, cslabs);
+      unsigned* counter = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + align_up(int64_t(slabs) * (k * m + m) * 4, 256));
+      if (cslabs > kDwCluster) {
+        cudaMemsetAsync(counter, 0, sizeof(unsigned), stream);  // the workspace arrives uninitialised
+      }
+      if (vec) bwd_w_cluster_kernel<true><<<cslabs, 256, 0, stream>>>(dyf, xf, partial, counter, dw, db, n, int(k), int(m), crows, wdb, accumulate);
+      else bwd_w_cluster_kernel<false><<<cslabs, 256, 0, stream>>>(dyf, xf, partial, counter, dw, db, n, int(k), int(m), crows, wdb, accumulate);
+      LGK_CHECK_LAUNCH("bwd_w_cluster_kernel");
+      return LGK_OK;
+    }
     // LGK_SLAB_PIPE=0: the single-buffered kernel for fp32 too (profiling knob)
     static const bool pipe_on = [] { const char* v = getenv("LGK_SLAB_PIPE"); return !(v && *v == '0'); }();
     // measured: 194 -> 128 us per call at n = 409 600 (config 3), but the headline step (n = 11 k, kernels of three

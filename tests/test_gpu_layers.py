@@ -518,3 +518,39 @@ def test_gat_fused_elu_equals_separate_activation(dev):
     assert_close(xb.grad, xa.grad, TOL_F32, "dx")
     for (k, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
         assert_close(pb.grad, pa.grad, TOL_F32, "d" + k)
+
+
+def test_cluster_reduced_weight_gradient_opt_in(dev):
+    """LGK_DW_CLUSTER=1 (csrc/linear.cu bwd_w_cluster_kernel: slab partials reduced through distributed shared memory, one
+    launch): the knob is read once per process, so the check runs in a child process -- dW and db against fp64, plain and
+    accumulating, several cluster counts, unaligned widths, and bitwise run-to-run determinism"""
+    import os
+    import subprocess
+    import sys
+    code = r"""
+import torch
+from lesion_gnn_b200 import ops
+dev = torch.device("cuda")
+g = torch.Generator().manual_seed(0)
+for n, k, m in [(5, 3, 2), (300, 64, 64), (513, 60, 33), (11447, 64, 64), (40000, 64, 1), (2000, 17, 64)]:
+    x = torch.randn(n, k, generator=g, dtype=torch.float64); dy = torch.randn(n, m, generator=g, dtype=torch.float64)
+    xd, dyd = x.float().to(dev), dy.float().to(dev)
+    ops.reset_launch_count()
+    dw, db = ops.linear_bwd_w(dyd, xd, want_dw=True, want_db=True)
+    assert ops.launch_count() == 1, ops.launch_count()
+    dw2, db2 = ops.linear_bwd_w(dyd, xd, want_dw=True, want_db=True)
+    assert torch.equal(dw, dw2) and torch.equal(db, db2)
+    want_w, want_b = dy.t() @ x, dy.sum(0)
+    assert float((dw.double().cpu() - want_w).abs().max() / want_w.abs().max()) < 1e-5, (n, k, m)
+    assert float((db.double().cpu() - want_b).abs().max() / want_b.abs().max().clamp(min=1e-30)) < 1e-5, (n, k, m)
+    accw, accb = torch.ones(m, k, device=dev), torch.ones(m, device=dev)
+    ops.linear_bwd_w(dyd, xd, want_dw=True, want_db=True, dw_out=accw, db_out=accb)
+    assert float((accw.double().cpu() - 1 - want_w).abs().max() / want_w.abs().max()) < 1e-5
+    only_w, none_b = ops.linear_bwd_w(dyd, xd, want_dw=True, want_db=False)
+    assert none_b is None and torch.equal(only_w, dw)
+print("ok")
+"""
+    env = dict(os.environ, LGK_DW_CLUSTER="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and "ok" in res.stdout, res.stdout + res.stderr
