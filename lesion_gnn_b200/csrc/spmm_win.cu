@@ -873,7 +873,7 @@ __global__ void __launch_bounds__(256) transpose_heads_kernel(const float* __res
 }
 
 int launch_win_gat(WinArgs a, cudaStream_t stream) {
-  constexpr int warps = 16;
+  static const int warps = env_int_win("LGK_WIN_WARPS", 16) == 24 ? 24 : 16;  // consumer warps (tuning knob)
   a.select = 0;
   a.slices = int(ceil_div(int64_t(a.feat) * 4, 128));
   const int fixed = warps * kStageBytesGat + int(sizeof(WinShared)) + 128;
@@ -886,7 +886,7 @@ int launch_win_gat(WinArgs a, cudaStream_t stream) {
   LGK_REQUIRE(make_row_map(&map_x, a.x, a.n_rows, a.feat, 128), LGK_ERR_UNSUPPORTED, "lgk_gat_fwd_blocked: cannot encode the tensor map");
   const int spans = int(std::max<int64_t>(1, std::min<int64_t>(kNumSMs / std::max(1, std::min(a.slices, kNumSMs)), a.n_chunks)));
   const unsigned grid = unsigned(spans * a.slices);
-  WinKernel kern = spmm_win_kernel<true, 8, warps, LGK_SELF_NONE, false, true>;
+  WinKernel kern = warps == 24 ? spmm_win_kernel<true, 8, 24, LGK_SELF_NONE, false, true> : spmm_win_kernel<true, 8, 16, LGK_SELF_NONE, false, true>;
   int dev = 0;
   cudaGetDevice(&dev);
   static bool configured[64] = {};
