@@ -632,7 +632,9 @@ __global__ void __launch_bounds__(256) colsum_slab_kernel(const T* __restrict__ 
 
 // slabs for a reduction over n rows: at most two CTAs per SM, at least 64 rows each
 int slab_count(int64_t n) {
-  int64_t g = ceil_div(n, 64);
+  // rows per slab (tuning knob LGK_SLAB_ROWS): fewer, taller slabs mean fewer partials for the second stage to read back
+  static const int min_rows = [] { const char* v = getenv("LGK_SLAB_ROWS"); const int r = (v && *v) ? atoi(v) : 64; return r < 32 ? 32 : r; }();
+  int64_t g = ceil_div(n, min_rows);
   if (g > 2 * kNumSMs) g = 2 * kNumSMs;
   return int(g < 1 ? 1 : g);
 }
