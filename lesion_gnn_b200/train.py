@@ -482,11 +482,12 @@ class BucketedTrainStep:
     """TrainStep over batches of VARYING shape with a handful of captured graphs: a batch goes into the PaddedBatch of its
     bucket -- node capacity = num_nodes rounded up to `node_step` (plus the one node the padding needs), edge capacity =
     node capacity x `max_degree` -- and the bucket's CUDA graph, captured on first use, is replayed.  `captures` counts
-    the graphs captured so far."""
+    the graphs captured so far.  `buffers=2` + stage() / run(): double buffering -- the next batch is copied while the
+    current one trains."""
 
     def __init__(self, model: nn.Module, opt, num_graphs: int, max_degree: int, loss_type: str = "MSE", num_classes: int = 5,
                  node_step: int = 4096, with_edge_weight: bool = False, x_dtype=torch.float32, dst_sorted: bool = True,
-                 **train_step_kwargs):
+                 buffers: int = 1, **train_step_kwargs):
         for m in model.modules():
             if isinstance(m, nn.modules.batchnorm._BatchNorm) and model.training:
                 raise NotImplementedError("padded batches would enter BatchNorm's batch statistics: use TrainStep per shape")
@@ -494,7 +495,8 @@ class BucketedTrainStep:
         self.num_graphs, self.max_degree, self.node_step = int(num_graphs), int(max_degree), int(node_step)
         self.with_edge_weight, self.x_dtype, self.dst_sorted = with_edge_weight, x_dtype, dst_sorted
         self.device = opt.param.device
-        self.buckets = {}
+        self.buffers = max(1, int(buffers))  # device buffers (and captured graphs) per bucket; 2 = copy / compute overlap
+        self.buckets, self._turn, self._free, self._copy_stream = {}, {}, {}, None
 
     @property
     def captures(self) -> int:
@@ -506,15 +508,56 @@ class BucketedTrainStep:
             cap += self.node_step
         return cap
 
-    def __call__(self, hb: HostBatch) -> Tensor:
+    def _buffer(self, hb: HostBatch) -> "PaddedBatch":
         if hb.num_graphs != self.num_graphs:
             raise ValueError(f"bucketed steps take batches of {self.num_graphs} graphs (the DataLoader's batch_size); "
                              f"got {hb.num_graphs}: run the last, smaller batch of an epoch through its own BucketedTrainStep")
         cap = self.bucket_of(hb)
-        pb = self.buckets.get(cap)
-        if pb is None:
-            pb = PaddedBatch(cap, cap * self.max_degree, self.num_graphs, hb.x.size(1), self.device, self.x_dtype,
-                             self.with_edge_weight, self.dst_sorted)
-            self.buckets[cap] = pb
+        bufs = self.buckets.get(cap)
+        if bufs is None:
+            bufs = [PaddedBatch(cap, cap * self.max_degree, self.num_graphs, hb.x.size(1), self.device, self.x_dtype,
+                                self.with_edge_weight, self.dst_sorted) for _ in range(self.buffers)]
+            self.buckets[cap] = bufs
+            self._turn[cap] = 0
+            if torch.cuda.is_available():
+                # the buffers were just initialised by kernels on the CURRENT stream: a first load on the copy stream must
+                # not overtake them (a host that never synchronises would otherwise see the zero-fill land after the copy)
+                born = torch.cuda.Event()
+                born.record(torch.cuda.current_stream())
+                for b in bufs:
+                    self._free[id(b)] = born
+        pb = bufs[self._turn[cap] % len(bufs)]
+        self._turn[cap] += 1
+        return pb
+
+    def __call__(self, hb: HostBatch) -> Tensor:
+        pb = self._buffer(hb)
         pb.load(hb)
         return self.step(pb)
+
+    # ---- prefetching form: `h = stage(next_batch)` while the previous step runs, then `loss = run(h)` ------------------
+    def stage(self, hb: HostBatch):
+        """Start the host -> device copy of `hb` into a free buffer of its bucket on the copy stream and return a handle for
+        run().  With `buffers=2` the copy of batch i + 1 overlaps the step of batch i (each buffer has its own captured
+        graph: up to 2 graphs per bucket).  `hb` must stay alive (and pinned, for a truly asynchronous copy) until run()."""
+        pb = self._buffer(hb)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        free = self._free.get(id(pb))
+        with torch.cuda.stream(self._copy_stream):
+            if free is not None:
+                self._copy_stream.wait_event(free)  # the last step that read this buffer has finished
+            pb.load(hb)
+            ready = torch.cuda.Event()
+            ready.record(self._copy_stream)
+        return pb, ready
+
+    def run(self, handle) -> Tensor:
+        pb, ready = handle
+        cur = torch.cuda.current_stream()
+        cur.wait_event(ready)
+        loss = self.step(pb)
+        free = torch.cuda.Event()
+        free.record(cur)
+        self._free[id(pb)] = free
+        return loss
