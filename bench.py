@@ -824,7 +824,13 @@ def aggregation_stress(dev, peak: float, peak_src: str, graphs: int = 128) -> di
     qc, qr = g.quads("csr"), g.quads("csc")
     assert ops.blocked_eligible(x, "sum", None)
     res["quad_build"] = entry(t_quads, 8 * E + 5 * N)
-    res["gcn_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", quads=qc, **kw), 20), agg_bytes)
+    # forward as GCNConv launches it on an unweighted graph: the source-side d^-1/2 was applied by the transform's epilogue
+    # (nn.functional.gcn_conv), the aggregation scales its output rows and adds the self loop; `_pre_in_kernel`: both factors
+    # inside the aggregation (weighted graphs, the first layer of a captured step, and the backward pass)
+    kw_fwd = dict(post=dinv, self_mode=ops.SELF_REPLACE)
+    res["gcn_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", quads=qc, **kw_fwd), 20), agg_bytes - 4 * N)
+    res["gcn_aggregate_fwd"]["path"] = "post-scale + self loop in the aggregation, pre-scale in the transform's epilogue (GCNConv, unweighted graph)"
+    res["gcn_aggregate_fwd_pre_in_kernel"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", quads=qc, **kw), 20), agg_bytes)
     res["gcn_aggregate_bwd"] = entry(_time_cuda(lambda: ops.spmm(g.colptr, g.row, x, "sum", quads=qr, **kw), 20), agg_bytes)
     plain = 2 * N * F * 4 + 4 * E + 4 * (N + 1)
     res["sum_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", quads=qc), 20), plain)

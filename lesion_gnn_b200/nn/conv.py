@@ -31,6 +31,9 @@ from . import functional as F
 # per CTA) and the 128 extra FMAs per row cost more there than the 2.6 us launch they replace -- so fp32 keeps the
 # separate launch unless LGK_GAT_FUSED_ALPHA=1.
 _FUSED_ALPHA_F32 = os.environ.get("LGK_GAT_FUSED_ALPHA", "0") != "0"
+# profiling knob: 0 = GCNConv applies the source-side d^-1/2 inside the aggregation (per-entry weights) instead of in the
+# transform's epilogue
+_GCN_FUSED_SCALE = os.environ.get("LGK_GCN_FUSED_SCALE", "1") != "0"
 _seed_counter = [0]
 
 
@@ -126,8 +129,20 @@ class GCNConv(OpaqueModule, nn.Module):
         return x.new_empty((x.size(0), self.out_channels))
 
     def _forward_eager(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None) -> Tensor:
-        h = self.lin(x)  # before as_graph: the transform does not read the graph, whose build may still be running on
-        g = as_graph(edge_index, x.size(0), edge_weight)  # its own stream (as_graph joins it)
+        # a graph whose build is still running on its own stream (the first layer of a captured step): transform first, it
+        # does not read the graph and overlaps the build; as_graph joins the build stream
+        pending = isinstance(edge_index, CSRGraph) and edge_index._ready is not None
+        if (not pending and self.normalize and edge_weight is None and self.lin.bias is None and x.dim() == 2
+                and x.dtype == torch.float32 and _GCN_FUSED_SCALE):
+            g = as_graph(edge_index, x.size(0), edge_weight)
+            if g.value is None:
+                # unweighted graph: the source-side d^-1/2 rides in the transform's epilogue (free), the aggregation runs
+                # without per-entry weights
+                dinv, selfw = g.gcn_norm(False, self.add_self_loops)
+                return F.gcn_conv(x, self.lin.weight, self.bias, g, dinv, selfw, 1.0,
+                                  SELF_REPLACE if self.add_self_loops else SELF_NONE)
+        h = self.lin(x)
+        g = as_graph(edge_index, x.size(0), edge_weight)
         if not self.normalize:
             return F.aggregate(h, g, "sum", use_value=g.value is not None, bias=self.bias)
         # PyG 2.5.1's gcn_norm adds the remaining self loops BEFORE it defaults edge_weight to ones, so without

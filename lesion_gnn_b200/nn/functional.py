@@ -171,6 +171,60 @@ def aggregate(x: Tensor, g: CSRGraph, reduce: str = "sum", *, use_value: bool = 
     return _Aggregate.apply(x, bias, g, reduce, use_value, pre, post, selfw, float(self_fill), int(self_mode))
 
 
+class _GcnConv(torch.autograd.Function):
+    """GCNConv on an UNWEIGHTED graph as two launches: out = D^-1/2 (A + c I) D^-1/2 (x W^T) + b.
+
+    The source-side factor d_j^-1/2 is applied by the TRANSFORM's epilogue (h' = dinv * (x W^T), lgk_linear_fwd's
+    rowscale: free), so the aggregation runs without per-entry weights -- the cheaper path of both aggregation kernels
+    (config-4 shape: 449 -> ~420 us) -- and only scales its output rows.  The backward is that of the unfused form:
+    dh = D^-1/2 (A + c I)^T D^-1/2 dout (one aggregation over the CSC), then the plain transform gradients."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, g: CSRGraph, dinv, selfw, self_fill, self_mode):
+        x = x.contiguous()
+        w = weight.contiguous()
+        hs = ops.linear_fwd(x, w, None, dinv)
+        out = ops.spmm(g.rowptr, g.col, hs, "sum", post=dinv, selfw=selfw, self_fill=self_fill, self_mode=self_mode, bias=bias,
+                       quads=g.quads("csr") if ops.blocked_eligible(hs, "sum", None) else None)
+        ctx.save_for_backward(x, w)
+        ctx.g, ctx.dinv, ctx.selfw, ctx.self_fill, ctx.self_mode = g, dinv, selfw, self_fill, self_mode
+        ctx.refs = (weight, bias)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, w = ctx.saved_tensors
+        g = ctx.g
+        _need_csc(g)
+        dout = dout.contiguous()
+        p_w, p_b = ctx.refs
+        ni = ctx.needs_input_grad
+        dx = dw = db = None
+        if p_b is not None and ni[2]:
+            gb = _bucket(p_b)
+            if gb is not None:
+                _on_side(lambda: ops.colsum(dout, out=gb), dout, key=gb.data_ptr())
+            else:
+                db = ops.colsum(dout)
+        if ni[0] or ni[1]:
+            dh = ops.spmm(g.colptr, g.row, dout, "sum", pre=ctx.dinv, post=ctx.dinv, selfw=ctx.selfw, self_fill=ctx.self_fill,
+                          self_mode=ctx.self_mode, quads=g.quads("csc") if ops.blocked_eligible(dout, "sum", None) else None)
+            if ni[1]:
+                gw = _bucket(p_w)
+                if gw is not None:
+                    _on_side(lambda: ops.linear_bwd_w(dh, x, want_dw=True, want_db=False, dw_out=gw), dh, x, key=gw.data_ptr())
+                else:
+                    dw = ops.linear_bwd_w(dh, x, want_dw=True, want_db=False)[0]
+            if ni[0]:
+                dx = ops.linear_bwd_x(dh, w)
+        return dx, dw, db, None, None, None, None, None
+
+
+def gcn_conv(x: Tensor, weight: Tensor, bias: Optional[Tensor], g: CSRGraph, dinv: Tensor, selfw: Optional[Tensor],
+             self_fill: float, self_mode: int) -> Tensor:
+    return _GcnConv.apply(x, weight, bias, g, dinv, selfw, float(self_fill), int(self_mode))
+
+
 class _GatAttention(torch.autograd.Function):
     """h [N, H*C] -> edge-softmax attention output [N, H*C] (+ bias)."""
 
