@@ -483,7 +483,10 @@ class BucketedTrainStep:
     bucket -- node capacity = num_nodes rounded up to `node_step` (plus the one node the padding needs), edge capacity =
     node capacity x `max_degree` -- and the bucket's CUDA graph, captured on first use, is replayed.  `captures` counts
     the graphs captured so far.  `buffers=2` + stage() / run(): double buffering -- the next batch is copied while the
-    current one trains."""
+    current one trains.
+    Data parallel (world_size > 1): capturing a bucket's graph runs warm-up steps, which include the cross-rank gradient
+    exchange -- every rank must therefore meet new buckets at the same steps (e.g. run one batch of every bucket through
+    all ranks before training, or give all ranks the bucket of the largest shard)."""
 
     def __init__(self, model: nn.Module, opt, num_graphs: int, max_degree: int, loss_type: str = "MSE", num_classes: int = 5,
                  node_step: int = 4096, with_edge_weight: bool = False, x_dtype=torch.float32, dst_sorted: bool = True,
