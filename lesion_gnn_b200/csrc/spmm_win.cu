@@ -184,6 +184,7 @@ struct WinArgs {
   int self_mode;
   int mean;
   int select;            // 1: run only if qmeta selects this slice width; 0: run unconditionally
+  int vec_rows;          // ptr, post and selfw are 16-byte aligned: a quad's four values are one vector load
   int64_t n_rows, n_quads, n_chunks;
   int feat, slices, nb;  // nb: ring blocks
   // GAT mode (edge soft-max + aggregate; pre = a_src TRANSPOSED [heads][pre_stride], one head per 128-byte slice group)
@@ -481,15 +482,35 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
     float postv[4], cself[4];
     int deg[4];
     if (SCALE || SELF != LGK_SELF_NONE) {
+      const bool whole = a.vec_rows && row0 + 3 < n_rows;  // the quad's four rows as one 16-byte load per array
 #pragma unroll
       for (int r = 0; r < 4; ++r) {
-        const int row = min(row0 + r, n_rows - 1);
         postv[r] = 1.f;
         deg[r] = 1;
         cself[r] = a.self_fill;
-        if (SCALE && has_mean) deg[r] = __ldg(a.ptr + row + 1) - __ldg(a.ptr + row);
-        if (SCALE && has_post) postv[r] = __ldg(a.post + row);
-        if (SELF != LGK_SELF_NONE && has_selfw) cself[r] = __ldg(a.selfw + row);
+      }
+      if (whole) {
+        if (SCALE && has_post) {
+          const float4 p4 = __ldg(reinterpret_cast<const float4*>(a.post + row0));
+          postv[0] = p4.x; postv[1] = p4.y; postv[2] = p4.z; postv[3] = p4.w;
+        }
+        if (SELF != LGK_SELF_NONE && has_selfw) {
+          const float4 s4 = __ldg(reinterpret_cast<const float4*>(a.selfw + row0));
+          cself[0] = s4.x; cself[1] = s4.y; cself[2] = s4.z; cself[3] = s4.w;
+        }
+        if (SCALE && has_mean) {
+          const int4 q4 = __ldg(reinterpret_cast<const int4*>(a.ptr + row0));
+          const int q5 = __ldg(a.ptr + row0 + 4);
+          deg[0] = q4.y - q4.x; deg[1] = q4.z - q4.y; deg[2] = q4.w - q4.z; deg[3] = q5 - q4.w;
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int row = min(row0 + r, n_rows - 1);
+          if (SCALE && has_mean) deg[r] = __ldg(a.ptr + row + 1) - __ldg(a.ptr + row);
+          if (SCALE && has_post) postv[r] = __ldg(a.post + row);
+          if (SELF != LGK_SELF_NONE && has_selfw) cself[r] = __ldg(a.selfw + row);
+        }
       }
     }
     // GAT: destination-side logit halves of the quad's rows, and the source-side ones of the rows themselves (self loop)
@@ -737,13 +758,23 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
       if (lane == 0) umma::mbar_arrive(&sh->empty[s]);
       continue;
     }
+    // self term: with SELF_REPLACE on a graph that stores its loops (kNN with loop=True) every coefficient is 0 -- one
+    // warp-uniform vote skips the whole block instead of four predicated copies of it
+    bool self_work = false;
+    if (SELF != LGK_SELF_NONE) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        if (SELF == LGK_SELF_REPLACE) cself[r] -= float((selfcnt >> (8 * r)) & 0xffu);
+        self_work |= cself[r] != 0.f;
+      }
+      self_work = __any_sync(0xffffffffu, self_work);
+    }
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
       float4 res = make_float4(acc[r][0].x, acc[r][0].y, acc[r][1].x, acc[r][1].y);
       const unsigned ro = unsigned(row0 + r) * F4;
-      if (SELF != LGK_SELF_NONE) {
+      if (SELF != LGK_SELF_NONE && self_work) {
         float c = cself[r];
-        if (SELF == LGK_SELF_REPLACE) c -= float((selfcnt >> (8 * r)) & 0xffu);
         if (c != 0.f && r < rows_here) {
           const int row = row0 + r;
           if (HAS_PRE) c *= __ldg(pre_g + row);
@@ -758,7 +789,7 @@ __global__ void __launch_bounds__(32 * (NW + 1), 1) spmm_win_kernel(const WinArg
         }
       }
       if (SCALE) {
-        const float sc = has_mean ? postv[r] / float(max(deg[r], 1)) : postv[r];
+        const float sc = has_mean ? postv[r] * __frcp_rn(float(max(deg[r], 1))) : postv[r];
         res.x = fmaf(res.x, sc, bias4.x);
         res.y = fmaf(res.y, sc, bias4.y);
         res.z = fmaf(res.z, sc, bias4.z);
@@ -956,6 +987,7 @@ extern "C" int lgk_spmm_blocked(const int32_t* ptr, const int32_t* qlen, const u
   a.x = static_cast<const float*>(x);
   a.out = static_cast<float*>(out);
   a.self_fill = self_fill; a.self_mode = self_mode; a.mean = reduce == LGK_MEAN;
+  a.vec_rows = ((reinterpret_cast<uintptr_t>(ptr) | reinterpret_cast<uintptr_t>(post) | reinterpret_cast<uintptr_t>(selfw)) & 15) == 0;
   a.n_rows = n_rows;
   a.n_quads = ceil_div(n_rows, 4);
   a.n_chunks = ceil_div(a.n_quads, kQuadsPerChunk);

@@ -100,6 +100,14 @@ class CSRGraph:
             self._norm[key] = ops.gcn_norm(self.rowptr, self.col, self.value, 2.0 if improved else 1.0, add_self_loops)
         return self._norm[key]
 
+    def inv_degree(self) -> Tensor:
+        """1 / max(in-degree, 1) per node (the mean aggregation's backward scale); computed once per graph"""
+        t = self._norm.get("inv_degree")
+        if t is None:
+            t = (self.rowptr[1:] - self.rowptr[:-1]).clamp(min=1).float().reciprocal()
+            self._norm["inv_degree"] = t
+        return t
+
     def quads(self, which: str = "csr") -> "ops.Quads":
         """row-blocked form of the CSR (forward aggregation) or the CSC (backward) for the windowed aggregation kernel
         (ops.spmm(..., quads=)); built once per graph and direction, shared by every layer"""

@@ -129,8 +129,7 @@ class _Aggregate(torch.autograd.Function):
             ctx.arg = arg
             return out
         if reduce == "mean":
-            deg = (g.rowptr[1:] - g.rowptr[:-1]).clamp(min=1).float()
-            ctx.inv_deg = deg.reciprocal()
+            ctx.inv_deg = g.inv_degree()  # memoised on the graph: three small launches once per batch, not per layer
         return ops.spmm(g.rowptr, g.col, x, reduce, ew=ew, pre=pre, post=post, selfw=selfw, self_fill=self_fill,
                         self_mode=self_mode, bias=bias, quads=g.quads("csr") if ops.blocked_eligible(x, reduce, ew) else None)
 
