@@ -834,7 +834,10 @@ def aggregation_stress(dev, peak: float, peak_src: str, graphs: int = 128) -> di
     res["gcn_aggregate_bwd"] = entry(_time_cuda(lambda: ops.spmm(g.colptr, g.row, x, "sum", quads=qr, **kw), 20), agg_bytes)
     plain = 2 * N * F * 4 + 4 * E + 4 * (N + 1)
     res["sum_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", quads=qc), 20), plain)
-    res["mean_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "mean", quads=qc), 20), plain)
+    # what SAGEConv(aggr="mean") launches: the sum variant scaled on the way out by the memoised 1 / max(deg, 1)
+    inv_deg = g.inv_degree()
+    res["mean_aggregate_fwd"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", post=inv_deg, quads=qc), 20), plain + 4 * N)
+    res["mean_aggregate_fwd_degree_in_kernel"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "mean", quads=qc), 10), plain)
     res["gcn_aggregate_fwd_lgk_spmm"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum", **kw), 10), agg_bytes)
     res["gcn_aggregate_bwd_lgk_spmm"] = entry(_time_cuda(lambda: ops.spmm(g.colptr, g.row, x, "sum", **kw), 10), agg_bytes)
     res["sum_aggregate_fwd_lgk_spmm"] = entry(_time_cuda(lambda: ops.spmm(g.rowptr, g.col, x, "sum"), 10), plain)
