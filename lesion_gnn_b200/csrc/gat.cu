@@ -11,6 +11,10 @@
 #include "common.cuh"
 #include <math.h>
 
+#ifndef LGK_GAT_EDGE_BATCH
+#define LGK_GAT_EDGE_BATCH 4
+#endif
+
 namespace lgk {
 namespace {
 
@@ -77,6 +81,14 @@ __device__ __forceinline__ float keep_scale(const GatArgs& a, uint64_t seed, uin
   return uniform_hash(seed, slot, uint32_t(head)) < a.drop_p ? 0.f : a.drop_scale;
 }
 constexpr uint32_t kSelfSlotBit = 0x80000000u;
+// backward passes: edges of a (node, head) group whose gathers are issued together; wide rows (more than one 16-byte vector
+// per lane) keep the one-edge-at-a-time loop.  Measured on the headline batch (45 k groups of 4 lanes, ~7 edges each,
+// profiles/r02/gat_edge_batch_ab.log, two interleaved runs per setting): the two kernels alone do not change (21.3 us per
+// layer in-graph at 1, 2 or 4), the captured training step does: 0.3257-0.3267 ms at 1, 0.3277-0.3280 at 2, 0.3203-0.3204 at 4
+// (62 / 78 registers instead of 40 / 46: fewer resident warps of these kernels leave room for the parameter-gradient
+// kernels of the side streams that run beside them).
+template <int LPR, int VPL>
+constexpr int kEdgeBatch = VPL > 1 ? 1 : (LPR < LGK_GAT_EDGE_BATCH ? LPR : LGK_GAT_EDGE_BATCH);
 
 // ---- alpha = <h, att> ------------------------------------------------------------------------------------
 template <typename T, int LPR, int VPL>
@@ -243,22 +255,35 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_dst_kernel(GatArgs a, const 
   const float delta = group_sum<LPR>(part, mask);
   float da = 0.f;
 
-  auto edge = [&](int j, uint32_t slot) {
+  // One edge: its source row and logit half arrive as arguments so that the caller can issue the loads of several edges
+  // before the first dependent shuffle -- a (node, head) group walks only ~7 edges, the chain of L2 round trips is its time.
+  auto edge = [&](const float4 (&hv)[VPL], float a_src_j, uint32_t slot) {
     float dotp = 0.f;
-    const T* hr = h + int64_t(j) * F + head * C;
 #pragma unroll
-    for (int v = 0; v < VPL; ++v) {
-      const int vec = gl + v * LPR;
-      if (vec < C4) dotp += f4_dot(dO[v], Vec4<T>::gather(hr, vec * 4));
-    }
+    for (int v = 0; v < VPL; ++v) dotp += f4_dot(dO[v], hv[v]);  // vectors past C4: dO = 0
     dotp = group_sum<LPR>(dotp, mask);
-    const float z = __ldg(a.a_src + int64_t(j) * H + head) + ad;
+    const float z = a_src_j + ad;
     const float alpha = expf(lrelu(z, a.slope) - m) * inv;
     const float dalpha = keep_scale(a, seed, slot, head) * dotp;
     da += alpha * (dalpha - delta) * (z > 0.f ? 1.f : a.slope);
   };
+  auto load_row = [&](int j, float4 (&hv)[VPL], float& a_src_j) {
+    const T* hr = h + int64_t(j) * F + head * C;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int vec = gl + v * LPR;
+      hv[v] = vec < C4 ? Vec4<T>::gather(hr, vec * 4) : f4_zero();
+    }
+    a_src_j = __ldg(a.a_src + int64_t(j) * H + head);
+  };
 
-  if (a.add_self) edge(i, kSelfSlotBit | uint32_t(i));
+  if (a.add_self) {
+    float4 hv[VPL];
+    float as;
+    load_row(i, hv, as);
+    edge(hv, as, kSelfSlotBit | uint32_t(i));
+  }
+  constexpr int UB = kEdgeBatch<LPR, VPL>;  // edges whose loads are in flight together
   for (int base = start; base < end; base += LPR) {
     const int p = base + gl;
     int my_j = -1;
@@ -267,9 +292,18 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_dst_kernel(GatArgs a, const 
       if (!(a.add_self && j == i)) my_j = j;
     }
     const int cnt = min(LPR, end - base);
-    for (int u = 0; u < cnt; ++u) {
-      const int j = __shfl_sync(mask, my_j, u, LPR);
-      if (j >= 0) edge(j, uint32_t(base + u));  // uniform across the group
+    for (int u0 = 0; u0 < cnt; u0 += UB) {
+      int js[UB];
+      float4 hv[UB][VPL];
+      float as[UB];
+#pragma unroll
+      for (int t = 0; t < UB; ++t) {
+        js[t] = __shfl_sync(mask, my_j, u0 + t, LPR);  // lanes past the row's end and dropped stored loops hold -1
+        load_row(js[t] >= 0 ? js[t] : i, hv[t], as[t]);
+      }
+#pragma unroll
+      for (int t = 0; t < UB; ++t)
+        if (js[t] >= 0) edge(hv[t], as[t], uint32_t(base + u0 + t));  // uniform across the group, same order as before
     }
   }
   if (gl == 0) {
@@ -305,20 +339,10 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
   }
   float da = 0.f;
 
-  auto edge = [&](int i, uint32_t slot) {
-    const float4 st = __ldg(a.stats + int64_t(i) * H + head);  // {a_dst, m, inv, delta}, same address for the group
-    float4 dO[VPL];
+  auto edge = [&](const float4 st, const float4 (&dO)[VPL], uint32_t slot) {  // st = {a_dst, m, inv, delta} of the destination
     float dotp = 0.f;
-    const T* dr = dout + int64_t(i) * F + head * C;
 #pragma unroll
-    for (int v = 0; v < VPL; ++v) {
-      const int vec = gl + v * LPR;
-      dO[v] = f4_zero();
-      if (vec < C4) {
-        dO[v] = Vec4<T>::gather(dr, vec * 4);
-        dotp += f4_dot(dO[v], hj[v]);
-      }
-    }
+    for (int v = 0; v < VPL; ++v) dotp += f4_dot(dO[v], hj[v]);  // vectors past C4: both 0
     dotp = group_sum<LPR>(dotp, mask);
     const float z = as + st.x;
     const float alpha = expf(lrelu(z, a.slope) - st.y) * st.z;
@@ -328,8 +352,22 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
 #pragma unroll
     for (int v = 0; v < VPL; ++v) f4_fma(acc[v], w, dO[v]);
   };
+  auto load_row = [&](int i, float4& st, float4 (&dO)[VPL]) {
+    st = __ldg(a.stats + int64_t(i) * H + head);  // same address for the group
+    const T* dr = dout + int64_t(i) * F + head * C;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int vec = gl + v * LPR;
+      dO[v] = vec < C4 ? Vec4<T>::gather(dr, vec * 4) : f4_zero();
+    }
+  };
 
-  if (a.add_self) edge(j, kSelfSlotBit | uint32_t(j));
+  if (a.add_self) {
+    float4 st, dO[VPL];
+    load_row(j, st, dO);
+    edge(st, dO, kSelfSlotBit | uint32_t(j));
+  }
+  constexpr int UB = kEdgeBatch<LPR, VPL>;  // edges whose loads are in flight together (see gat_bwd_dst_kernel)
   for (int base = start; base < end; base += LPR) {
     const int q = base + gl;
     int my_i = -1, my_slot = 0;
@@ -341,10 +379,18 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
       }
     }
     const int cnt = min(LPR, end - base);
-    for (int u = 0; u < cnt; ++u) {
-      const int i = __shfl_sync(mask, my_i, u, LPR);
-      const int slot = __shfl_sync(mask, my_slot, u, LPR);
-      if (i >= 0) edge(i, uint32_t(slot));
+    for (int u0 = 0; u0 < cnt; u0 += UB) {
+      int is[UB], slots[UB];
+      float4 st[UB], dO[UB][VPL];
+#pragma unroll
+      for (int t = 0; t < UB; ++t) {
+        is[t] = __shfl_sync(mask, my_i, u0 + t, LPR);
+        slots[t] = __shfl_sync(mask, my_slot, u0 + t, LPR);
+        load_row(is[t] >= 0 ? is[t] : j, st[t], dO[t]);
+      }
+#pragma unroll
+      for (int t = 0; t < UB; ++t)
+        if (is[t] >= 0) edge(st[t], dO[t], uint32_t(slots[t]));
     }
   }
 
