@@ -26,11 +26,11 @@ from . import functional as F
 
 # The attention-logit halves can come out of the transform's epilogue (lgk_linear_gat_fwd) instead of a separate
 # lgk_gat_alpha launch over the stored h.  bf16 activations: always (the logits must not see h's rounding: 4x smaller
-# gradient error, tests/test_gpu_bf16.py).  fp32: measured on the headline step (B200, 300 steps, same box, A/B/A/B):
-# separate 0.3266-0.3268 ms, fused 0.3308-0.3316 ms -- the tensor-core kernel's 4-warp epilogue is fully exposed (one tile
-# per CTA) and the 128 extra FMAs per row cost more there than the 2.6 us launch they replace -- so fp32 keeps the
-# separate launch unless LGK_GAT_FUSED_ALPHA=1.
-_FUSED_ALPHA_F32 = os.environ.get("LGK_GAT_FUSED_ALPHA", "0") != "0"
+# gradient error, tests/test_gpu_bf16.py).  fp32: on by default since the main chain of the captured step runs on a
+# high-priority stream (train.TrainStep): headline step 0.3115 -> 0.3091 ms, 53 -> 50 launches (B200, 500 steps, same box,
+# A/B/A/B).  Before that the separate launch was the faster one (0.3267 vs 0.3312 ms: the transform's 4-warp epilogue is
+# fully exposed, one tile per CTA); LGK_GAT_FUSED_ALPHA=0 brings it back.
+_FUSED_ALPHA_F32 = os.environ.get("LGK_GAT_FUSED_ALPHA", "1") != "0"
 # profiling knob: 0 = GCNConv applies the source-side d^-1/2 inside the aggregation (per-entry weights) instead of in the
 # transform's epilogue
 _GCN_FUSED_SCALE = os.environ.get("LGK_GCN_FUSED_SCALE", "1") != "0"

@@ -353,9 +353,14 @@ class TrainStep:
         self._fused_dp = world_size > 1 and getattr(opt, "peer_bucket", None) is not None and opt.peer_bucket.world == world_size
         self._graphs = {}
         # parameter-gradient kernels are dealt over this many side streams (tuning knob: LGK_SIDE_STREAMS, 0 = none)
-        nside = int(os.environ.get("LGK_SIDE_STREAMS", "2"))
+        nside = int(os.environ.get("LGK_SIDE_STREAMS", "3"))
         self._side = [torch.cuda.Stream() for _ in range(nside)] if torch.cuda.is_available() and nside > 0 else None
         self._build = torch.cuda.Stream() if torch.cuda.is_available() else None
+        # the main chain is captured on a high-priority stream: its thread blocks are placed before those of the
+        # parameter-gradient kernels on the (default-priority) side streams whenever both are pending -- headline step
+        # 0.3199 -> 0.3131 ms (LGK_MAIN_PRIORITY=0 captures on torch's default capture stream as before)
+        self._capture = (torch.cuda.Stream(priority=-1)
+                         if torch.cuda.is_available() and os.environ.get("LGK_MAIN_PRIORITY", "1") != "0" else None)
 
     def _body(self, db: DeviceBatch) -> Tensor:
         self.opt.zero_grad()
@@ -402,7 +407,7 @@ class TrainStep:
             for b, src in bufs:
                 b.copy_(src)
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with (torch.cuda.graph(g, stream=self._capture) if self._capture is not None else torch.cuda.graph(g)):
                 loss = self._body(db)
             entry = (g, loss, db)
             self._graphs[id(db)] = entry
