@@ -638,6 +638,178 @@ int slab_count(int64_t n) {
   if (g > 2 * kNumSMs) g = 2 * kNumSMs;
   return int(g < 1 ? 1 : g);
 }
+// ---- products the tiled kernel is the wrong shape for (measured in-graph on the headline batch, profiles/chain_bench.py:
+//      out_proj forward [256 x 128] -> 1: 12.8 us, its dX 7.2 us, the 64 x 64 dX of a layer over 11 k rows 10.6 us -- eight
+//      dependent 16-deep reduction steps in two CTAs, or 90 CTAs on 148 SMs) ---------------------------------------------
+constexpr int kNarrowMax = 8;   // "narrow": at most this many output (forward) / input (dX) columns
+
+// forward with m <= 8 outputs: a warp per row of x, lanes stride over k with 16-byte loads, one shuffle reduction per output
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(256) linear_fwd_narrow_kernel(const T* __restrict__ x, const float* __restrict__ w,
+                                                                const float* __restrict__ bias, const float* __restrict__ rowscale,
+                                                                T* __restrict__ out, int64_t n, int k, int m, int act, int accumulate) {
+  const int lane = threadIdx.x & 31;
+  const int64_t i = int64_t(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= n) return;
+  float acc[kNarrowMax];
+#pragma unroll
+  for (int j = 0; j < kNarrowMax; ++j) acc[j] = 0.f;
+  const T* xr = x + i * k;
+  if (VEC) {
+    for (int r = lane * 4; r < k; r += 128) {
+      const float4 xv = ld4<T>(xr + r);
+#pragma unroll
+      for (int j = 0; j < kNarrowMax; ++j)
+        if (j < m) acc[j] += f4_dot(xv, __ldg(reinterpret_cast<const float4*>(w + int64_t(j) * k + r)));
+    }
+  } else {
+    for (int r = lane; r < k; r += 32) {
+      const float xv = Vec4<T>::load1(xr, r);
+#pragma unroll
+      for (int j = 0; j < kNarrowMax; ++j)
+        if (j < m) acc[j] = fmaf(xv, __ldg(w + int64_t(j) * k + r), acc[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kNarrowMax; ++j) {
+    if (j >= m) break;  // m is uniform across the warp
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
+  }
+  if (lane == 0) {
+    const float rs = rowscale ? __ldg(rowscale + i) : 1.f;
+#pragma unroll
+    for (int j = 0; j < kNarrowMax; ++j) {
+      if (j >= m) break;
+      float v = acc[j] * rs;
+      if (bias) v += __ldg(bias + j);
+      if (accumulate) v += Vec4<T>::load1(out, i * m + j);
+      if (act == LGK_ACT_ELU) v = elu1(v);
+      else if (act == LGK_ACT_RELU) v = fmaxf(v, 0.f);
+      Vec4<T>::store1(out, i * m + j, v);
+    }
+  }
+}
+
+// dX with m <= 8 columns of dy: dx[i, r] = sum_j dy[i, j] W[j, r] -- an outer-product shaped, element-wise kernel
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(256) linear_bwd_x_narrow_kernel(const T* __restrict__ dy, const float* __restrict__ w,
+                                                                  T* __restrict__ dx, int64_t n, int k, int m, int accumulate) {
+  const int per_row = VEC ? (k >> 2) : k;
+  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t >= n * per_row) return;
+  const int64_t i = t / per_row;
+  const int c = int(t - i * per_row);
+  float dv[kNarrowMax];
+#pragma unroll
+  for (int j = 0; j < kNarrowMax; ++j) dv[j] = j < m ? Vec4<T>::load1(dy, i * m + j) : 0.f;
+  if (VEC) {
+    float4 acc = f4_zero();
+#pragma unroll
+    for (int j = 0; j < kNarrowMax; ++j)
+      if (j < m) f4_fma(acc, dv[j], __ldg(reinterpret_cast<const float4*>(w + int64_t(j) * k) + c));
+    if (accumulate) {
+      const float4 o = ld4<T>(dx + i * k + c * 4);
+      acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
+    }
+    Vec4<T>::store(dx, i * k + c * 4, acc);
+  } else {
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < kNarrowMax; ++j)
+      if (j < m) acc = fmaf(dv[j], __ldg(w + int64_t(j) * k + c), acc);
+    if (accumulate) acc += Vec4<T>::load1(dx, i * k + c);
+    Vec4<T>::store1(dx, i * k + c, acc);
+  }
+}
+
+// dX against a small weight (k, m <= 128, both multiples of 4): dx[n, k] = dy[n, m] W[m, k].  The whole weight and a tile of
+// dy rows go to shared memory with ONE batch of loads per thread (a single round trip instead of m / 16 dependent ones), a
+// thread owns 4 rows x 4 columns, a CTA of 128 threads 4 * 128 / (k / 4 rounded up to a power of two) rows: 32 rows at k = 64,
+// i.e. 358 CTAs for the 11 k nodes of the headline batch instead of 90.
+constexpr int kDxThreads = 128;
+int dx_small_col_groups(int64_t k) {
+  int cg = 1;
+  while (cg * 4 < k) cg <<= 1;
+  return cg;  // 1 .. 32
+}
+size_t dx_small_smem(int64_t k, int64_t m) {
+  const int rows = 4 * (kDxThreads / dx_small_col_groups(k));
+  return size_t(m * k + rows * (m + 4)) * sizeof(float);
+}
+template <typename T>
+__global__ void __launch_bounds__(kDxThreads) linear_bwd_x_small_kernel(const T* __restrict__ dy, const float* __restrict__ w,
+                                                                        T* __restrict__ dx, int64_t n, int k, int m, int cgp,
+                                                                        int accumulate) {
+  extern __shared__ __align__(16) float dxs[];
+  float* Ws = dxs;              // [m][k]
+  float* Ds = dxs + m * k;      // [rows][m + 4]
+  const int rows = 4 * (kDxThreads / cgp), ds = m + 4;
+  const int64_t i0 = int64_t(blockIdx.x) * rows;
+  for (int t = threadIdx.x; t < (m * k) >> 2; t += kDxThreads)
+    reinterpret_cast<float4*>(Ws)[t] = __ldg(reinterpret_cast<const float4*>(w) + t);
+  const int m4 = m >> 2;
+  for (int t = threadIdx.x; t < rows * m4; t += kDxThreads) {
+    const int rr = t / m4, c4 = t - rr * m4;
+    const int64_t i = i0 + rr;
+    const float4 v = i < n ? ld4<T>(dy + i * m + c4 * 4) : f4_zero();
+    *reinterpret_cast<float4*>(Ds + rr * ds + c4 * 4) = v;
+  }
+  __syncthreads();
+  const int cg = threadIdx.x & (cgp - 1), rg = threadIdx.x / cgp;
+  if (cg * 4 >= k) return;
+  float4 acc[4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a) acc[a] = f4_zero();
+  const float* d0 = Ds + (rg * 4) * ds;
+  for (int r = 0; r < m; r += 4) {
+    float4 dv[4], wv[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) dv[a] = *reinterpret_cast<const float4*>(d0 + a * ds + r);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) wv[q] = *reinterpret_cast<const float4*>(Ws + (r + q) * k + cg * 4);
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      f4_fma(acc[a], dv[a].x, wv[0]);
+      f4_fma(acc[a], dv[a].y, wv[1]);
+      f4_fma(acc[a], dv[a].z, wv[2]);
+      f4_fma(acc[a], dv[a].w, wv[3]);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int64_t i = i0 + rg * 4 + a;
+    if (i >= n) break;
+    if (accumulate) {
+      const float4 o = ld4<T>(dx + i * k + cg * 4);
+      acc[a].x += o.x; acc[a].y += o.y; acc[a].z += o.z; acc[a].w += o.w;
+    }
+    Vec4<T>::store(dx, i * k + cg * 4, acc[a]);
+  }
+}
+
+template <typename T>
+int launch_bwd_x_small(const T* dy, const float* w, T* dx, int64_t n, int64_t k, int64_t m, int accumulate, cudaStream_t stream) {
+  const size_t smem = dx_small_smem(k, m);
+  if (smem > 48 * 1024) {
+    static bool configured_dev[64] = {};
+    int dev_ord = 0;
+    cudaGetDevice(&dev_ord);
+    if (!configured_dev[dev_ord & 63]) {
+      if (cudaFuncSetAttribute(linear_bwd_x_small_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024) != cudaSuccess) {
+        set_error("linear_bwd_x_small_kernel: cannot reserve shared memory");
+        return LGK_ERR_LAUNCH;
+      }
+      configured_dev[dev_ord & 63] = true;
+    }
+  }
+  const int cgp = dx_small_col_groups(k);
+  const int rows = 4 * (kDxThreads / cgp);
+  linear_bwd_x_small_kernel<T><<<unsigned(ceil_div(n, rows)), kDxThreads, smem, stream>>>(dy, w, dx, n, int(k), int(m), cgp, accumulate);
+  LGK_CHECK_LAUNCH("linear_bwd_x_small_kernel");
+  return LGK_OK;
+}
+
 bool small_weight(int64_t k, int64_t m) { return k <= 128 && m <= 128; }
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -683,6 +855,18 @@ extern "C" int lgk_linear_fwd(const void* x, const float* weight, const float* b
   LGK_REQUIRE(known_dtype(dtype), LGK_ERR_UNSUPPORTED, "lgk_linear_fwd: dtype must be LGK_F32 or LGK_BF16");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(x && weight && out, LGK_ERR_BAD_ARG, "lgk_linear_fwd: null pointer");
+  if (m <= kNarrowMax) {  // out_proj and other heads with a handful of outputs: a warp per row
+    const bool vec = (k % 4 == 0) && aligned16(x) && aligned16(weight);
+    const unsigned grid = unsigned(ceil_div(n, 8));
+#define LGK_NARROW_FWD(T, V)                                                                                                  \
+  linear_fwd_narrow_kernel<T, V><<<grid, 256, 0, stream>>>(static_cast<const T*>(x), weight, bias, rowscale, static_cast<T*>(out), \
+                                                           n, int(k), int(m), act, accumulate)
+    if (dtype == LGK_BF16) { if (vec) LGK_NARROW_FWD(bf16, true); else LGK_NARROW_FWD(bf16, false); }
+    else { if (vec) LGK_NARROW_FWD(float, true); else LGK_NARROW_FWD(float, false); }
+#undef LGK_NARROW_FWD
+    LGK_CHECK_LAUNCH("linear_fwd_narrow_kernel");
+    return LGK_OK;
+  }
   if (dtype == LGK_F32 && use_tensor_cores(n, k)) {
     bool done = false;
     if ((k & 3) == 0) {  // aligned rows: tensor-map TMA feeds the tensor core
@@ -752,6 +936,24 @@ extern "C" int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, i
   LGK_REQUIRE(known_dtype(dtype), LGK_ERR_UNSUPPORTED, "lgk_linear_bwd_x: dtype must be LGK_F32 or LGK_BF16");
   if (n == 0) return LGK_OK;
   LGK_REQUIRE(dy && weight && dx, LGK_ERR_BAD_ARG, "lgk_linear_bwd_x: null pointer");
+  if (m <= kNarrowMax) {  // dX of a head with a handful of outputs
+    const bool nvec = (k % 4 == 0) && aligned16(weight) && aligned16(dx);
+    const int64_t threads = n * (nvec ? k / 4 : k);
+    const unsigned grid = unsigned(ceil_div(threads, 256));
+#define LGK_NARROW_DX(T, V)                                                                                                    \
+  linear_bwd_x_narrow_kernel<T, V><<<grid, 256, 0, stream>>>(static_cast<const T*>(dy), weight, static_cast<T*>(dx), n, int(k), int(m), \
+                                                             accumulate)
+    if (dtype == LGK_BF16) { if (nvec) LGK_NARROW_DX(bf16, true); else LGK_NARROW_DX(bf16, false); }
+    else { if (nvec) LGK_NARROW_DX(float, true); else LGK_NARROW_DX(float, false); }
+#undef LGK_NARROW_DX
+    LGK_CHECK_LAUNCH("linear_bwd_x_narrow_kernel");
+    return LGK_OK;
+  }
+  if (small_weight(k, m) && (k % 4 == 0) && (m % 4 == 0) && n <= 65536 && aligned16(dy) && aligned16(weight) && aligned16(dx)) {
+    if (dtype == LGK_BF16)
+      return launch_bwd_x_small(static_cast<const bf16*>(dy), weight, static_cast<bf16*>(dx), n, k, m, accumulate, stream);
+    return launch_bwd_x_small(static_cast<const float*>(dy), weight, static_cast<float*>(dx), n, k, m, accumulate, stream);
+  }
   GemmArgs g{};
   g.A = dy; g.B = weight; g.C = dx;
   g.I = n; g.J = k; g.R = m; g.lda = m; g.ldb = k; g.sCi = k; g.sCj = 1;

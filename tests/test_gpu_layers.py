@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from oracle import pyg_semantics as O
-from tests.util import TOL_F32, assert_close, assert_parity, random_graph, row_rel_err
+from tests.util import TOL_BF16, TOL_F32, assert_close, assert_parity, random_graph, row_rel_err
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden", "layers.pt")
@@ -450,6 +450,54 @@ def test_layers_accept_adj_t_sparse_tensors(dev):
     gcn = lg.nn.GCNConv(32, 8).to(dev)
     unweighted = torch.sparse_csr_tensor(g.rowptr.long(), g.col.long(), torch.ones_like(g.value), size=(n, n))
     assert_close(gcn(x, unweighted), gcn(x, ei, torch.ones_like(w)), 1e-6, "gcn adj_t")
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_narrow_and_small_weight_products(dev, dtype):
+    """the products the tiled kernel is the wrong shape for (csrc/linear.cu): forward with <= 8 outputs (a warp per row; row
+    scale, bias, accumulate, activation), its dX (outer-product kernel) and the dX against a weight of at most 128 x 128 (weight
+    and a tile of dy rows in shared memory) -- aligned and unaligned reductions, column counts that leave lanes idle, ragged
+    last tiles, the accumulating forms"""
+    from lesion_gnn_b200 import ops
+    gen = torch.Generator().manual_seed(21)
+    tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
+
+    def dev_act(t):
+        return t.float().to(dev).to(dtype)
+
+    def rounded(t):  # what the kernel sees
+        return t.float().to(dtype).double()
+
+    for n, k, m in [(256, 128, 1), (4096, 64, 5), (37, 1025, 8), (1, 4, 1), (300, 30, 3)]:
+        x = torch.randn(n, k, generator=gen, dtype=torch.float64)
+        w = torch.randn(m, k, generator=gen, dtype=torch.float64) / k ** 0.5
+        b = torch.randn(m, generator=gen, dtype=torch.float64)
+        rs = torch.rand(n, generator=gen, dtype=torch.float64) + 0.5
+        base = torch.randn(n, m, generator=gen, dtype=torch.float64)
+        xw = rounded(x) @ w.float().double().t()
+        got = ops.linear_fwd(dev_act(x), w.float().to(dev), b.float().to(dev), rs.float().to(dev), act=1)
+        assert_close(got, torch.nn.functional.elu(rs.float().double()[:, None] * xw + b.float().double()), tol, f"narrow fwd {n}x{k}->{m}")
+        out = dev_act(base).clone()
+        ops.linear_fwd(dev_act(x), w.float().to(dev), out=out)
+        assert_close(out, rounded(base) + xw, tol, f"narrow fwd accumulate {n}x{k}->{m}")
+        dy = torch.randn(n, m, generator=gen, dtype=torch.float64)
+        want_dx = rounded(dy) @ w.float().double()
+        assert_close(ops.linear_bwd_x(dev_act(dy), w.float().to(dev)), want_dx, tol, f"narrow dX {n}x{m}->{k}")
+        acc = dev_act(x).clone()
+        ops.linear_bwd_x(dev_act(dy), w.float().to(dev), out=acc)
+        assert_close(acc, rounded(x) + want_dx, tol, f"narrow dX accumulate {n}x{m}->{k}")
+    for n, k, m in [(11447, 64, 64), (1000, 128, 128), (333, 16, 128), (70, 20, 12), (5, 128, 16), (4097, 100, 36)]:
+        dy = torch.randn(n, m, generator=gen, dtype=torch.float64)
+        w = torch.randn(m, k, generator=gen, dtype=torch.float64) / m ** 0.5
+        base = torch.randn(n, k, generator=gen, dtype=torch.float64)
+        want_dx = rounded(dy) @ w.float().double()
+        got = ops.linear_bwd_x(dev_act(dy), w.float().to(dev))
+        assert_close(got, want_dx, tol, f"small-weight dX {n}x{m}->{k}")
+        if dtype == torch.float32:  # every element on its own: a misplaced tile would hide under max-normalisation
+            assert float((got.double().cpu() - want_dx).abs().max()) <= 1e-5 * float(want_dx.abs().max())
+        acc = dev_act(base).clone()
+        ops.linear_bwd_x(dev_act(dy), w.float().to(dev), out=acc)
+        assert_close(acc, rounded(base) + want_dx, tol, f"small-weight dX accumulate {n}x{m}->{k}")
 
 
 def test_linear_tensor_core_epilogue_options(dev):
