@@ -189,6 +189,31 @@ __global__ void __launch_bounds__(kThreads) pool_bwd_kernel(PoolArgs a, const T*
   const float scale = a.mean ? 1.f / float(max(n, 1)) : 1.f;
   if (a.vec_ok) {
     const int F4 = F >> 2;
+    if (kThreads % F4 == 0) {
+      // the usual widths (F4 divides the CTA): a thread keeps ONE column group for all its rows, so the graph's gradient
+      // row, arg-max row and scale are loaded once and the row loop is compare / add / store (the general loop below divides
+      // a 64-bit counter per element: 6.8 us for the 11 k x 64 headline batch, where 3 MB move)
+      const int vec = threadIdx.x % F4, rstep = kThreads / F4;
+      float4 base = f4_zero(), dm = f4_zero();
+      int4 ar = make_int4(-1, -1, -1, -1);
+      if (dsum) {
+        base = Vec4<T>::gather(dsum + int64_t(g) * F, vec * 4);
+        base.x *= scale; base.y *= scale; base.z *= scale; base.w *= scale;
+      }
+      if (dmax) {
+        ar = __ldg(reinterpret_cast<const int4*>(a.arg + int64_t(g) * F) + vec);
+        dm = Vec4<T>::gather(dmax + int64_t(g) * F, vec * 4);
+      }
+      for (int r = r0 + threadIdx.x / F4; r < r1; r += rstep) {
+        float4 o = base;
+        if (ar.x == r) o.x += dm.x;
+        if (ar.y == r) o.y += dm.y;
+        if (ar.z == r) o.z += dm.z;
+        if (ar.w == r) o.w += dm.w;
+        Vec4<T>::store(dx + int64_t(r) * F, vec * 4, o);
+      }
+      return;
+    }
     // thread owns one float4 column group and walks down the rows; consecutive threads -> consecutive vectors
     const int64_t total = int64_t(r1 - r0) * F4;
     for (int64_t t = threadIdx.x; t < total; t += kThreads) {

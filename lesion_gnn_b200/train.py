@@ -244,8 +244,9 @@ def _fused_regression(logits: Tensor, y: Tensor, loss_type: str) -> bool:
 
 # profiling knob: 0 = batches whose edges are grouped by destination still take the general CSR/CSC build
 _SORTED_BUILD = os.environ.get("LGK_CSR_SORTED", "1") != "0"
-# 1 = the Adam kernel advances the step counter itself (measured slower than the 1-element add launch: off)
-_ADAM_ADVANCES_STEP = os.environ.get("LGK_ADAM_ADVANCES_STEP", "0") != "0"
+# 1 = the Adam kernel advances the step counter itself (its last CTA, after every CTA has read it) instead of a 1-element add
+# launch in front of it: headline step 0.2882 -> 0.2861 ms (slower, and off, before the main chain got its priority stream)
+_ADAM_ADVANCES_STEP = os.environ.get("LGK_ADAM_ADVANCES_STEP", "1") != "0"
 # profiling knob: 0 = zero_grad() is its own fill launch at the head of every step
 _ADAM_ZEROES_GRAD = os.environ.get("LGK_ADAM_ZEROES_GRAD", "1") != "0"
 # profiling knob: 0 = the loss goes through its autograd node (ones_like seed + multiply by the upstream gradient)
