@@ -10,6 +10,7 @@
 // groups of a warp are adjacent heads of the same node, so a warp still reads whole contiguous feature rows.
 #include "common.cuh"
 #include <math.h>
+#include <stdlib.h>
 
 #ifndef LGK_GAT_EDGE_BATCH
 #define LGK_GAT_EDGE_BATCH 4
@@ -87,6 +88,7 @@ constexpr uint32_t kSelfSlotBit = 0x80000000u;
 // layer in-graph at 1, 2 or 4), the captured training step does: 0.3257-0.3267 ms at 1, 0.3277-0.3280 at 2, 0.3203-0.3204 at 4
 // (62 / 78 registers instead of 40 / 46: fewer resident warps of these kernels leave room for the parameter-gradient
 // kernels of the side streams that run beside them).
+constexpr int kThinIds = 8, kThinRows = 2;  // thread-per-(node, head) mapping of the backward passes
 template <int LPR, int VPL>
 constexpr int kEdgeBatch = VPL > 1 ? 1 : (LPR < LGK_GAT_EDGE_BATCH ? LPR : LGK_GAT_EDGE_BATCH);
 
@@ -283,6 +285,36 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_dst_kernel(GatArgs a, const 
     load_row(i, hv, as);
     edge(hv, as, kSelfSlotBit | uint32_t(i));
   }
+  if constexpr (LPR == 1 && VPL > 1) {
+    // thread per (node, head) (narrow heads, see LGK_GAT_DISPATCH_BWD): no shuffles, the per-edge scalar work (logit, exp,
+    // dropout hash) once per edge instead of once per lane of a group.  Ids in chunks of kThinIds (one round trip), rows of
+    // kThinRows edges at a time (one round trip each).
+    for (int base = start; base < end; base += kThinIds) {
+      int js[kThinIds];
+#pragma unroll
+      for (int t = 0; t < kThinIds; ++t) {
+        js[t] = -1;
+        if (base + t < end) {
+          const int j = ld_stream_i32(a.idx + base + t);
+          if (!(a.add_self && j == i)) js[t] = j;
+        }
+      }
+#pragma unroll
+      for (int u0 = 0; u0 < kThinIds; u0 += kThinRows) {
+        if (base + u0 >= end) break;
+        float4 hv[kThinRows][VPL];
+        float as[kThinRows];
+#pragma unroll
+        for (int t = 0; t < kThinRows; ++t) load_row(js[u0 + t] >= 0 ? js[u0 + t] : i, hv[t], as[t]);
+#pragma unroll
+        for (int t = 0; t < kThinRows; ++t)
+          if (js[u0 + t] >= 0) edge(hv[t], as[t], uint32_t(base + u0 + t));
+      }
+    }
+    a.da_out[item] = da;
+    a.stats[item] = make_float4(ad, m, inv, delta);
+    return;
+  }
   constexpr int UB = kEdgeBatch<LPR, VPL>;  // edges whose loads are in flight together
   for (int base = start; base < end; base += LPR) {
     const int p = base + gl;
@@ -367,6 +399,33 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
     load_row(j, st, dO);
     edge(st, dO, kSelfSlotBit | uint32_t(j));
   }
+  if constexpr (LPR == 1 && VPL > 1) {  // thread per (node, head): see gat_bwd_dst_kernel
+    for (int base = start; base < end; base += kThinIds) {
+      int is[kThinIds], slots[kThinIds];
+#pragma unroll
+      for (int t = 0; t < kThinIds; ++t) {
+        is[t] = -1;
+        slots[t] = 0;
+        if (base + t < end) {
+          const int i = ld_stream_i32(a.idx + base + t);
+          if (!(a.add_self && i == j)) {
+            is[t] = i;
+            if (a.drop_p > 0.f) slots[t] = ld_stream_i32(a.slotmap + base + t);
+          }
+        }
+      }
+#pragma unroll
+      for (int u0 = 0; u0 < kThinIds; u0 += kThinRows) {
+        if (base + u0 >= end) break;
+        float4 st[kThinRows], dO[kThinRows][VPL];
+#pragma unroll
+        for (int t = 0; t < kThinRows; ++t) load_row(is[u0 + t] >= 0 ? is[u0 + t] : j, st[t], dO[t]);
+#pragma unroll
+        for (int t = 0; t < kThinRows; ++t)
+          if (is[u0 + t] >= 0) edge(st[t], dO[t], uint32_t(slots[u0 + t]));
+      }
+    }
+  } else {
   constexpr int UB = kEdgeBatch<LPR, VPL>;  // edges whose loads are in flight together (see gat_bwd_dst_kernel)
   for (int base = start; base < end; base += LPR) {
     const int q = base + gl;
@@ -394,6 +453,7 @@ __global__ void __launch_bounds__(kThreads) gat_bwd_src_kernel(GatArgs a, const 
     }
   }
 
+  }  // group-of-lanes mapping
   const float dad = __ldg(a.da_dst + item);
 #pragma unroll
   for (int v = 0; v < VPL; ++v) {
@@ -474,6 +534,24 @@ int check_shape(const char* who, int64_t N, int H, int C) {
     else if (c4__ <= 64) KERNEL<T, 32, 2><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);        \
     else if (c4__ <= 128) KERNEL<T, 32, 4><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);       \
     else KERNEL<T, 32, 8><<<grid__(32), kThreads, 0, stream>>>(__VA_ARGS__);                        \
+  } while (0)
+
+// Backward passes with narrow heads (2 <= C / 4 <= 4, the reference's 4 x 16 and 2 x 16 layers): ONE THREAD per (node, head)
+// instead of a group of C / 4 lanes.  The per-edge scalar work of these kernels (logit, exp, dropout hash, ~70 instructions) is
+// the same for every lane of a group, so the group mapping executes it C / 4 times; a thread that owns the head's whole
+// channel slice does it once, needs no shuffle, and issues its 2-4 16-byte gathers per edge back to back.  LGK_GAT_THIN=0 keeps
+// the group mapping.
+bool gat_thin() {
+  static const bool on = [] { const char* v = getenv("LGK_GAT_THIN"); return !(v && *v == '0'); }();
+  return on;
+}
+#define LGK_GAT_DISPATCH_BWD(KERNEL, T, n_items, C, stream, ...)                                                      \
+  do {                                                                                                               \
+    const int c4b__ = (C) / 4;                                                                                       \
+    const unsigned gridb__ = unsigned(ceil_div((n_items), int64_t(kThreads)));                                       \
+    if (gat_thin() && c4b__ == 2) KERNEL<T, 1, 2><<<gridb__, kThreads, 0, stream>>>(__VA_ARGS__);                   \
+    else if (gat_thin() && (c4b__ == 3 || c4b__ == 4)) KERNEL<T, 1, 4><<<gridb__, kThreads, 0, stream>>>(__VA_ARGS__); \
+    else LGK_GAT_DISPATCH(KERNEL, T, n_items, C, stream, __VA_ARGS__);                                               \
   } while (0)
 
 GatArgs base_args(int64_t N, int H, int C, float slope, int add_self, float drop_p, uint64_t seed, const int64_t* seed_dev) {
@@ -561,9 +639,9 @@ static int gat_bwd_dst_impl(const int32_t* rowptr, const int32_t* col, const voi
   a.stats = reinterpret_cast<float4*>(delta); a.da_out = da_dst; a.act_out = dpre_out;
   const int64_t items = N * H;
   if (dtype == LGK_F32)
-    LGK_GAT_DISPATCH(gat_bwd_dst_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<const float*>(out), static_cast<const float*>(dout));
+    LGK_GAT_DISPATCH_BWD(gat_bwd_dst_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<const float*>(out), static_cast<const float*>(dout));
   else if (dtype == LGK_BF16)
-    LGK_GAT_DISPATCH(gat_bwd_dst_kernel, __nv_bfloat16, items, C, stream, a, static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout));
+    LGK_GAT_DISPATCH_BWD(gat_bwd_dst_kernel, __nv_bfloat16, items, C, stream, a, static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout));
   else
     LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_bwd_dst: bad dtype");
   LGK_CHECK_LAUNCH("gat_bwd_dst_kernel");
@@ -607,9 +685,9 @@ extern "C" int lgk_gat_bwd_src(const int32_t* colptr, const int32_t* row, const 
   a.att_src = att_src; a.att_dst = att_dst;
   const int64_t items = N * H;
   if (dtype == LGK_F32)
-    LGK_GAT_DISPATCH(gat_bwd_src_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<const float*>(dout), static_cast<float*>(dh));
+    LGK_GAT_DISPATCH_BWD(gat_bwd_src_kernel, float, items, C, stream, a, static_cast<const float*>(h), static_cast<const float*>(dout), static_cast<float*>(dh));
   else if (dtype == LGK_BF16)
-    LGK_GAT_DISPATCH(gat_bwd_src_kernel, __nv_bfloat16, items, C, stream, a, static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(dout), static_cast<__nv_bfloat16*>(dh));
+    LGK_GAT_DISPATCH_BWD(gat_bwd_src_kernel, __nv_bfloat16, items, C, stream, a, static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(dout), static_cast<__nv_bfloat16*>(dh));
   else
     LGK_REQUIRE(false, LGK_ERR_BAD_ARG, "lgk_gat_bwd_src: bad dtype");
   LGK_CHECK_LAUNCH("gat_bwd_src_kernel");
