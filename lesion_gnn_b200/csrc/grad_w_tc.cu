@@ -57,6 +57,7 @@ struct GwArgs {
   int64_t slab_nodes;  // multiple of 32
   int fuse_db;         // feature row K of the last tile is fed with ones: D[K, :] = db
   int debug;           // profiling only (LGK_GW_DEBUG): 1 = no MMAs, 2 = no conversion, 4 = no global copies
+  int wide;            // LGK_GW_WIDE (default 1): two MMAs per K step where the shape allows it
 };
 
 struct Bars {
@@ -98,6 +99,9 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
   const int64_t slab = min(g.slab_nodes, g.n - node0);   // nodes of this slab (> 0 by construction of the grid)
   const int nkb = int((slab + BNODE - 1) / BNODE);
   const int ncols = int((g.m + 15) / 16) * 16;           // MMA N
+  // two MMAs per K step instead of three when [dy_hi | dy_lo] is one contiguous operand (the dy tile is exactly MG groups
+  // wide) that still fits an accumulator's 128 columns
+  const bool wide = g.wide && ncols == 32 * MG && 2 * ncols <= kAccCols;
 
   // operand tiles start as zeros: columns of the dy tiles between m and N are never written
   for (int i = threadIdx.x; i < kTileStages * kTileBytes / 16; i += kThreads)
@@ -118,7 +122,7 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
   const uint32_t tmem_base = bars->tmem_slot;
 
   if (warp == kWarpMma) {
-    const uint32_t idesc = idesc_tf32_mn(BF, ncols);
+    const uint32_t idesc = idesc_tf32_mn(BF, ncols), idesc_w = idesc_tf32_mn(BF, 2 * ncols);
     for (int kb = 0; kb < nkb; ++kb) {
       const int s = kb % kTileStages;
       umma::mbar_wait(bars->tile_full + s, (kb / kTileStages) & 1);  // acquires the stagers' generic-proxy writes
@@ -131,6 +135,21 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
         const uint32_t sa = tiles + s * kTileBytes;
         const uint64_t a_hi = smem_desc_mn_sw128(sa), a_lo = smem_desc_mn_sw128(sa + kTileA);
         const uint64_t b_hi = smem_desc_mn_sw128(sa + 2 * kTileA), b_lo = smem_desc_mn_sw128(sa + 2 * kTileA + kTileB);
+        if (wide) {
+          // the dy_lo tile follows the dy_hi tile group by group: [dy_hi | dy_lo] is ONE MN-major operand of 2 * ncols columns.
+          // Per K step x_hi^T [dy_hi | dy_lo] -> columns [hi*hi | hi*lo] (N = 128), then x_lo^T dy_hi added onto the second
+          // half: 8 MMAs per node block instead of 12 (the issue chain is what this kernel waits for, see linear_tc.cu)
+#pragma unroll
+          for (int kk = 0; kk < BNODE / 8; ++kk) {
+            const uint64_t adv = uint64_t(kk * kAtom >> 4);
+            umma::mma_tf32(tmem_base + uint32_t(kk) * kAccCols, a_hi + adv, b_hi + adv, idesc_w, kb > 0);
+          }
+#pragma unroll
+          for (int kk = 0; kk < BNODE / 8; ++kk) {
+            const uint64_t adv = uint64_t(kk * kAtom >> 4);
+            umma::mma_tf32(tmem_base + uint32_t(kk) * kAccCols + uint32_t(ncols), a_lo + adv, b_hi + adv, idesc, true);
+          }
+        } else
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
 #pragma unroll
@@ -240,6 +259,15 @@ __global__ void __launch_bounds__(kThreads, 1) grad_w_tc_kernel(GwArgs g) {
 #pragma unroll
         for (int t = 0; t < 16; ++t) v[t] += u[t];
       }
+      if (wide) {  // the small terms: second half of every accumulator
+#pragma unroll
+        for (int a = 0; a < kAcc; ++a) {
+          float u[16];
+          umma::tmem_ld16(tmem_base + (uint32_t(warp * 32) << 16) + a * kAccCols + ncols + c * 16, u);
+#pragma unroll
+          for (int t = 0; t < 16; ++t) v[t] += u[t];
+        }
+      }
 #pragma unroll
       for (int t = 0; t < 16; ++t) {
         const int64_t mc = c * 16 + t;
@@ -297,7 +325,8 @@ int launch_grad_w_tc(const float* dy, const float* x, float* partial, int64_t n,
     configured = true;
   }
   static const int debug = [] { const char* v = getenv("LGK_GW_DEBUG"); return (v && *v) ? atoi(v) : 0; }();
-  GwArgs g{dy, x, partial, n, k, m, slab_nodes, fuse_db, debug};
+  static const int wide = [] { const char* v = getenv("LGK_GW_WIDE"); return (v && *v) ? atoi(v) : 1; }();
+  GwArgs g{dy, x, partial, n, k, m, slab_nodes, fuse_db, debug, wide};
   const unsigned grid = unsigned(ceil_div(k, BF) * slabs);
   if (m <= 64) grad_w_tc_kernel<2><<<grid, kThreads, smem_bytes<2>(), stream>>>(g);
   else grad_w_tc_kernel<4><<<grid, kThreads, smem_bytes<4>(), stream>>>(g);

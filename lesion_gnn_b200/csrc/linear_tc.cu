@@ -57,6 +57,7 @@ struct TcArgs {
   int64_t tiles_n;      // column tiles (fastest tile index)
   int64_t tiles_total;
   int debug;  // profiling only (LGK_TC_DEBUG): 1 = no MMAs, 2 = no conversion, 4 = no global copies (bit mask)
+  int wide;   // 1: two MMAs per K step (A_hi x [B_hi; B_lo] as one N = 128 product, then A_lo x B_hi) instead of three N = 64 ones
 };
 
 struct Bars {
@@ -151,11 +152,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
 
   if (warp == kWarpMma) {
     // ---- MMA issuer ----
-    const uint32_t idesc = umma::idesc_tf32(BM, BN);
+    const uint32_t idesc = umma::idesc_tf32(BM, BN), idesc_w = umma::idesc_tf32(BM, 2 * BN);
+    const bool wide = g.wide != 0;
     uint32_t it = 0, li = 0;
     for (int64_t t = blockIdx.x; t < g.tiles_total; t += gridDim.x, ++li) {
-      const uint32_t ab = li & 1;
-      umma::mbar_wait(bars->acc_empty + ab, ((li >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator buffer
+      // wide: the four accumulators are 128 columns each ([hi*hi | hi*lo + lo*hi]) and fill the tensor memory: one buffer
+      const uint32_t ab = wide ? 0u : (li & 1);
+      umma::mbar_wait(bars->acc_empty + ab, (wide ? (li & 1) : ((li >> 1) & 1)) ^ 1);  // the epilogue has drained this buffer
       umma::tc_fence_after();
       for (int kb = 0; kb < nkb; ++kb, ++it) {
         const int s = it % kTileStages;
@@ -173,6 +176,22 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
           // size), so the four K steps of a block go to four different accumulators AND the issue order is
           // term-major: consecutive instructions always target different accumulators, a dependent one follows
           // four issue slots later.  Per accumulator the order of additions (lo*hi, hi*lo, hi*hi) is unchanged.
+          if (wide) {
+            // B_hi and B_lo tiles are adjacent in the stage: [B_hi; B_lo] is ONE K-major operand of 128 rows.  Per K step
+            // A_hi x [B_hi; B_lo] -> columns [hi*hi | hi*lo] (N = 128), then A_lo x B_hi added onto the second half (N = 64):
+            // 8 MMAs per block instead of 12 -- the MMA issue chain, ~60 cycles per instruction whatever N, is what a tile
+            // with 33 dependent K blocks waits for (LGK_TC_DEBUG ablation, profiles/README.md r02).
+#pragma unroll
+            for (int kk = 0; kk < BK / 8; ++kk) {
+              const uint64_t adv = uint64_t(kk * 32 >> 4);
+              umma::mma_tf32(tmem_base + uint32_t(kk) * 2 * BN, a_hi + adv, b_hi + adv, idesc_w, kb > 0);
+            }
+#pragma unroll
+            for (int kk = 0; kk < BK / 8; ++kk) {
+              const uint64_t adv = uint64_t(kk * 32 >> 4);
+              umma::mma_tf32(tmem_base + uint32_t(kk) * 2 * BN + BN, a_lo + adv, b_hi + adv, idesc, true);
+            }
+          } else
 #pragma unroll
           for (int term = 0; term < 3; ++term) {
 #pragma unroll
@@ -259,10 +278,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) linear_tc_kernel(TcArgs g) {
     uint32_t li = 0;
     for (int64_t t = blockIdx.x; t < g.tiles_total; t += gridDim.x, ++li) {
       const int64_t i0 = (t / g.tiles_n) * g.bm, j0 = (t % g.tiles_n) * BN;
-      const uint32_t ab = li & 1;
-      umma::mbar_wait_relaxed(bars->acc_full + ab, (li >> 1) & 1);
+      const bool wide = g.wide != 0;
+      const uint32_t ab = wide ? 0u : (li & 1);
+      umma::mbar_wait_relaxed(bars->acc_full + ab, wide ? (li & 1) : ((li >> 1) & 1));
       umma::tc_fence_after();
-      epilogue_tile(g, tmem_base + ab * kAcc * BN, nacc, warp, lane, i0, j0);
+      epilogue_tile(g, tmem_base + ab * kAcc * BN, wide ? 2 * nacc : nacc, warp, lane, i0, j0);
       umma::tc_fence_before();
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(bars->acc_empty + ab);
@@ -293,9 +313,10 @@ int launch_linear_tc(const float* x, const float* w, const float* bias, const fl
     }
     configured = true;
   }
-  TcArgs g{x, w, bias, rowscale, out, n, k, m, act, accumulate, BM, 0, 0, 0};
+  TcArgs g{x, w, bias, rowscale, out, n, k, m, act, accumulate, BM, 0, 0, 0, 0};
   static const int debug = [] { const char* v = getenv("LGK_TC_DEBUG"); return (v && *v) ? atoi(v) : 0; }();
   g.debug = debug;
+  static const int wide = [] { const char* v = getenv("LGK_TC_WIDE"); return (v && *v) ? atoi(v) : -1; }();
   g.tiles_n = ceil_div(m, BN);
   // tile height: the smallest multiple of 16 rows that still covers the matrix in the same number of waves, so that a
   // batch of 11 583 nodes becomes 145 tiles of 80 rows on 145 SMs instead of 91 tiles of 128 rows on 91 SMs (the
@@ -306,6 +327,10 @@ int launch_linear_tc(const float* x, const float* w, const float* bias, const fl
     g.bm = int(std::min<int64_t>(BM, std::max<int64_t>(64, align_up(ceil_div(n, row_tiles), 16))));
   }
   g.tiles_total = ceil_div(n, g.bm) * g.tiles_n;
+  // two MMAs per K step (see the kernel) when every CTA has a single tile: 36.5 -> 33.5 us on the headline batch.  With several
+  // tiles per CTA the wide accumulators leave no second tensor-memory buffer for the epilogue to overlap the next main loop:
+  // 409 600 x 1025 -> 64 runs 578 us with three MMAs and 703 us with two.  LGK_TC_WIDE=0 / 1 forces either.
+  g.wide = wide >= 0 ? wide : (g.tiles_total <= kNumSMs ? 1 : 0);
   const unsigned grid = unsigned(g.tiles_total < kNumSMs ? g.tiles_total : kNumSMs);
   switch (g.bm / kConvWarps) {  // x rows per stager warp
     case 4: linear_tc_kernel<4><<<grid, kThreadsTc, kSmemBytes, stream>>>(g); break;
