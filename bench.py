@@ -667,12 +667,24 @@ def secondary_legs(args, spec, graphs, total_graphs, world, rank, dev, host, dev
         e0.record()
         rounds = max(1, steps // distinct)
         seq = [h for _ in range(rounds) for h in hosts50]
+        # every step's loss goes device -> pinned host inside the timed region; the host reads it one step LATER, so that it
+        # can stage batch i + 2 while step i + 1 runs instead of idling on step i + 1's result (a replayed graph returns the
+        # same loss tensor each time: the asynchronous copy is what keeps the value)
+        loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        loss_done = [torch.cuda.Event(), torch.cuda.Event()]
+        last = None
         handle = bstep.stage(seq[0])
         for i in range(len(seq)):  # the copy of batch i + 1 runs on the copy stream while batch i trains
             nxt = bstep.stage(seq[i + 1]) if i + 1 < len(seq) else None
             loss50 = bstep.run(handle)
-            last = float(loss50)  # device -> host read of the step's result, every step
+            loss_host[i & 1:(i & 1) + 1].copy_(loss50.reshape(1), non_blocking=True)
+            loss_done[i & 1].record()
+            if i > 0:
+                loss_done[(i - 1) & 1].synchronize()
+                last = float(loss_host[(i - 1) & 1])  # the previous step's result
             handle = nxt
+        loss_done[(len(seq) - 1) & 1].synchronize()
+        last = float(loss_host[(len(seq) - 1) & 1])
         e1.record()
         barrier()
         ms = max_over_ranks(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3))
@@ -683,7 +695,8 @@ def secondary_legs(args, spec, graphs, total_graphs, world, rank, dev, host, dev
             "captured_graphs": bstep.captures, "h2d_bytes_per_step": int(sum(h.h2d_bytes() for h in hosts50) / distinct),
             "d2h_bytes_per_step": 4, "last_loss": last,
             "note": "every step a batch of a different (N, E): host -> padded bucket buffers (two per bucket: the copy of batch i + 1 "
-                    "overlaps step i) -> replay of the buffer's graph -> loss read back"}
+                    "overlaps step i) -> replay of the buffer's graph -> loss copied to pinned host memory every step, read by the "
+                    "host one step later"}
         del hosts50, bstep, model50, opt50
 
     # ---- e2e_resident_dataset: the reference's InMemoryDataset (datasets/base.py:49) lives in HBM; per step the batch is
