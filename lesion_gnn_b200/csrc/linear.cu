@@ -949,8 +949,7 @@ extern "C" int lgk_linear_bwd_x(const void* dy, const float* weight, void* dx, i
     LGK_CHECK_LAUNCH("linear_bwd_x_narrow_kernel");
     return LGK_OK;
   }
-  if (small_weight(k, m) && (k % 4 == 0) && (m % 4 == 0) && n <= (k * m <= 4096 ? 131072 : 65536) && aligned16(dy) && aligned16(weight) &&
-      aligned16(dx)) {
+  if (small_weight(k, m) && (k % 4 == 0) && (m % 4 == 0) && n <= 65536 && aligned16(dy) && aligned16(weight) && aligned16(dx)) {
     if (dtype == LGK_BF16)
       return launch_bwd_x_small(static_cast<const bf16*>(dy), weight, static_cast<bf16*>(dx), n, k, m, accumulate, stream);
     return launch_bwd_x_small(static_cast<const float*>(dy), weight, static_cast<float*>(dx), n, k, m, accumulate, stream);

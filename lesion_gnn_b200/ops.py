@@ -424,10 +424,7 @@ def linear_bwd_x(dy: Tensor, weight: Tensor, out: Optional[Tensor] = None) -> Te
     L = _lib.lib()
     n, m = dy.shape
     k = weight.size(1)
-    # measured (B200, 64 x 64 weight): the shared-memory FFMA kernel of lgk_linear_bwd_x takes 0.34 us per 1000 rows, the
-    # tensor-core route 20 us + 0.13 us per 1000 rows -- it pays from ~10^5 rows; a 128 x 128 weight is 4x the FMAs: from 32 768
-    tall = n >= (98304 if m * k <= 4096 else 32768)
-    if tall and m >= 32 and m % 4 == 0 and k % 4 == 0 and dy.dtype == torch.float32:
+    if n >= 32768 and m >= 32 and m % 4 == 0 and k % 4 == 0 and dy.dtype == torch.float32:
         return linear_fwd(dy, weight.t().contiguous(), out=out)
     accumulate = out is not None
     if out is None:
